@@ -1,0 +1,173 @@
+"""Ragged utterance batches: packing, length bucketing, sharding, fused pipelines.
+
+This is the batched form of what ``load_data.AudioDataset.__getitem__`` does one
+utterance at a time (load_data.py:50-70: ``speech.lmfe`` per file) plus the
+``processing.cmvnw`` post-processing of the speechpy examples
+(speech_feature_extraction/example/test_package.py:36-37).  One call featurises a
+whole ragged batch on the GPU.
+
+Multi-GPU: utterances are independent, so ranks take disjoint shards balanced by
+total samples and no collective is needed.
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import numpy as np
+
+from . import _lib
+from .speechpy import feature as _feature
+from .speechpy import processing as _processing
+
+
+def pack(signals, align: int = 4):
+    """Concatenate 1-D signals into one float32 arena.
+
+    Returns (arena, starts, lengths).  Every utterance starts on a multiple of
+    ``align`` samples so the kernels can stage tiles with 128-bit loads.
+    """
+    lengths = np.array([len(s) for s in signals], dtype=np.int64)
+    padded = (lengths + align - 1) // align * align
+    starts = np.zeros(len(signals), dtype=np.int64)
+    if len(signals) > 1:
+        np.cumsum(padded[:-1], out=starts[1:])
+    arena = np.zeros(int(padded.sum()), dtype=np.float32)
+    for s, st, n in zip(signals, starts, lengths):
+        arena[st:st + n] = s
+    return arena, starts, lengths
+
+
+def bucket_order(lengths, bucket_samples: int = 8000):
+    """Indices that visit utterances bucket by bucket (0.5 s buckets at 16 kHz by
+    default), longest bucket first; stable inside a bucket."""
+    lengths = np.asarray(lengths, dtype=np.int64)
+    buckets = lengths // int(bucket_samples)
+    return np.argsort(-buckets, kind="stable")
+
+
+def shard_indices(lengths, world_size: int, bucket_samples: int = 8000):
+    """Deal utterances to ``world_size`` ranks so that total samples per rank are
+    balanced: walk the length-bucketed order and always give the next utterance to
+    the currently lightest rank.  Returns a list of index arrays (one per rank), each
+    in bucketed order.  Deterministic; no communication needed to agree on it."""
+    lengths = np.asarray(lengths, dtype=np.int64)
+    order = bucket_order(lengths, bucket_samples)
+    if world_size == 1:
+        return [order]
+    loads = np.zeros(world_size, dtype=np.int64)
+    owner = np.empty(len(order), dtype=np.int64)
+    # round-robin inside runs of equal bucket keeps this O(U) and within one
+    # utterance of optimal per bucket; ties broken by rank id
+    for pos, u in enumerate(order):
+        r = int(np.argmin(loads))
+        owner[pos] = r
+        loads[r] += lengths[u]
+    return [order[owner == r] for r in range(world_size)]
+
+
+def shard_indices_fast(lengths, world_size: int, bucket_samples: int = 8000):
+    """Vectorised variant of :func:`shard_indices` for very large corpora: bucketed
+    order dealt in a serpentine (boustrophedon) pattern.  Imbalance is bounded by one
+    utterance per bucket pass."""
+    lengths = np.asarray(lengths, dtype=np.int64)
+    order = np.argsort(-lengths, kind="stable")
+    pos = np.arange(len(order))
+    rnd, slot = np.divmod(pos, world_size)
+    rank = np.where(rnd % 2 == 0, slot, world_size - 1 - slot)
+    return [order[rank == r] for r in range(world_size)]
+
+
+class FeatureBatch:
+    """Device descriptors of a ragged batch for one feature configuration.
+
+    Parameters mirror ``speechpy.feature.lmfe`` / ``mfcc`` (feature.py:102-112,222-223) and
+    ``processing.cmvnw`` (processing.py:274).
+    """
+
+    def __init__(self, starts, lengths, sampling_frequency=16000, frame_length=0.020,
+                 frame_stride=0.01, num_filters=40, fft_length=512, low_frequency=0,
+                 high_frequency=None, num_cepstral=13, dc_elimination=True, win_size=301,
+                 variance_normalization=True, device=None):
+        assert isinstance(win_size, int), "Size must be of type 'int'!"
+        assert win_size % 2 == 1, "Windows size must be odd!"
+        self.ctx = _lib.context(device)
+        self.starts = np.ascontiguousarray(starts, dtype=np.int64)
+        self.lengths = np.ascontiguousarray(lengths, dtype=np.int64)
+        L, S = _processing._geometry(0, sampling_frequency, frame_length, frame_stride)
+        high_frequency = high_frequency or sampling_frequency / 2
+        K = int(fft_length) // 2 + 1
+        bank = _feature.filterbanks(num_filters, K, sampling_frequency, low_frequency, high_frequency)
+        self.num_filters = int(num_filters)
+        self.num_cepstral = min(int(num_cepstral), int(num_filters))
+        self.plan = self.ctx.plan(L, int(S), int(fft_length), self.num_filters, self.num_cepstral,
+                                  1 if dc_elimination else 0, bank, int(win_size),
+                                  1 if variance_normalization else 0)
+        h = _lib.c_vp()
+        _lib.check(self.ctx.lib.spb_batch_create(self.ctx.handle, self.plan, _lib.ptr(self.starts),
+                                                 _lib.ptr(self.lengths), len(self.starts), C.byref(h)),
+                   self.ctx.handle)
+        self.handle = h
+        tf = _lib.c_i64()
+        _lib.check(self.ctx.lib.spb_batch_total_frames(h, C.byref(tf)))
+        self.total_frames = tf.value
+        self.frame_offsets = np.empty(len(self.starts) + 1, dtype=np.int64)
+        _lib.check(self.ctx.lib.spb_batch_frame_offsets(h, _lib.ptr(self.frame_offsets)))
+        self.min_arena = int((self.starts + self.lengths).max()) if len(self.starts) else 0
+
+    def close(self):
+        if self.handle:
+            self.ctx.lib.spb_batch_destroy(self.handle)
+            self.handle = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # ---- host (numpy) entry points -------------------------------------------------
+    def lmfe_cmvnw(self, arena: np.ndarray, out: np.ndarray | None = None) -> np.ndarray:
+        """lmfe + cmvnw of every utterance: (total_frames, num_filters) float32; rows of
+        utterance u are frame_offsets[u]:frame_offsets[u+1]."""
+        arena = np.ascontiguousarray(arena, dtype=np.float32)
+        if out is None:
+            out = np.empty((self.total_frames, self.num_filters), dtype=np.float32)
+        _lib.check(self.ctx.lib.spb_lmfe_cmvnw_batch(self.ctx.handle, self.handle, _lib.ptr(arena),
+                                                     arena.shape[0], _lib.ptr(out)), self.ctx.handle)
+        return out
+
+    def mfcc_delta(self, arena: np.ndarray, out: np.ndarray | None = None) -> np.ndarray:
+        """mfcc + extract_derivative_feature: (total_frames, num_cepstral, 3) float32."""
+        arena = np.ascontiguousarray(arena, dtype=np.float32)
+        if out is None:
+            out = np.empty((self.total_frames, self.num_cepstral, 3), dtype=np.float32)
+        _lib.check(self.ctx.lib.spb_mfcc_delta_batch(self.ctx.handle, self.handle, _lib.ptr(arena),
+                                                     arena.shape[0], _lib.ptr(out)), self.ctx.handle)
+        return out
+
+    # ---- device-pointer entry points (asynchronous on ctx.stream()) -----------------
+    def lmfe_cmvnw_dev(self, d_samples: int, arena_len: int, d_out: int):
+        _lib.check(self.ctx.lib.spb_lmfe_cmvnw_batch_dev(self.ctx.handle, self.handle, d_samples,
+                                                         arena_len, d_out), self.ctx.handle)
+
+    def lmfe_dev(self, d_samples: int, arena_len: int, d_out: int):
+        _lib.check(self.ctx.lib.spb_lmfe_batch_dev(self.ctx.handle, self.handle, d_samples, arena_len,
+                                                   d_out), self.ctx.handle)
+
+    def mfcc_delta_dev(self, d_samples: int, arena_len: int, d_out: int):
+        _lib.check(self.ctx.lib.spb_mfcc_delta_batch_dev(self.ctx.handle, self.handle, d_samples,
+                                                         arena_len, d_out), self.ctx.handle)
+
+    def split(self, flat: np.ndarray):
+        """Views of a batched result, one per utterance."""
+        return [flat[self.frame_offsets[u]:self.frame_offsets[u + 1]] for u in range(len(self.starts))]
+
+
+def lmfe_cmvnw(signals, **kw):
+    """Convenience: list of 1-D signals -> list of (F_u, M) float32 arrays."""
+    arena, starts, lengths = pack(signals)
+    fb = FeatureBatch(starts, lengths, **kw)
+    try:
+        return [a.copy() for a in fb.split(fb.lmfe_cmvnw(arena))]
+    finally:
+        fb.close()

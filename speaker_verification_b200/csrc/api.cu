@@ -1,0 +1,878 @@
+// C-ABI layer of libspeechpy_b200.so (declared in include/speechpy_b200.h).
+#include <math.h>
+#include <string.h>
+
+#include <algorithm>
+#include <new>
+
+#include "spb_internal.cuh"
+
+namespace spb {
+
+static thread_local std::string g_last_error;
+
+void set_global_error(const std::string &msg) { g_last_error = msg; }
+
+int fail(spb_context *ctx, int code, const std::string &msg) {
+  if (ctx) ctx->last_error = msg;
+  g_last_error = msg;
+  return code;
+}
+
+int cuda_fail(spb_context *ctx, cudaError_t e, const char *what) {
+  std::string msg = std::string("CUDA error: ") + cudaGetErrorString(e) + " in " + what;
+  cudaGetLastError();  // clear sticky-less errors
+  return fail(ctx, SPB_ERR_CUDA, msg);
+}
+
+void *scratch(spb_context *ctx, int slot, size_t bytes) {
+  DeviceBuffer &b = ctx->scratch[slot];
+  if (b.bytes >= bytes && b.ptr) return b.ptr;
+  if (b.ptr) {
+    cudaStreamSynchronize(ctx->stream);
+    cudaFree(b.ptr);
+    b.ptr = nullptr;
+    b.bytes = 0;
+  }
+  size_t want = std::max(bytes, (size_t)1 << 20);
+  want = (want + ((size_t)1 << 20) - 1) & ~(((size_t)1 << 20) - 1);
+  cudaError_t e = cudaMalloc(&b.ptr, want);
+  if (e != cudaSuccess) {
+    cuda_fail(ctx, e, "cudaMalloc(scratch)");
+    b.ptr = nullptr;
+    return nullptr;
+  }
+  b.bytes = want;
+  return b.ptr;
+}
+
+static bool is_pow2(int v) { return v > 0 && (v & (v - 1)) == 0; }
+
+int get_fft_tables(spb_context *ctx, int nfft, FftTables *out) {
+  auto it = ctx->fft_tables.find(nfft);
+  if (it != ctx->fft_tables.end()) {
+    *out = it->second;
+    return SPB_OK;
+  }
+  FftTables t;
+  const double two_pi = 6.283185307179586476925286766559;
+  {
+    std::vector<float2> tw(nfft / 2);
+    for (int k = 0; k < nfft / 2; ++k) {
+      const double a = -two_pi * (double)k / (double)nfft;
+      tw[k] = make_float2((float)cos(a), (float)sin(a));
+    }
+    SPB_CUDA(ctx, cudaMalloc(&t.d_tw, tw.size() * sizeof(float2)));
+    SPB_CUDA(ctx, cudaMemcpy(t.d_tw, tw.data(), tw.size() * sizeof(float2), cudaMemcpyHostToDevice));
+  }
+  if (nfft == 512) {
+    std::vector<float2> a(16 * 16), b(16 * 9);
+    for (int l = 0; l < 16; ++l)
+      for (int k1 = 0; k1 < 16; ++k1) {
+        const double ang = -two_pi * (double)((l * k1) % 256) / 256.0;
+        a[l * 16 + k1] = make_float2((float)cos(ang), (float)sin(ang));
+      }
+    for (int k1 = 0; k1 < 16; ++k1)
+      for (int k2 = 0; k2 < 9; ++k2) {
+        const double ang = -two_pi * (double)(k1 + 16 * k2) / 512.0;
+        b[k1 * 9 + k2] = make_float2((float)cos(ang), (float)sin(ang));
+      }
+    SPB_CUDA(ctx, cudaMalloc(&t.d_twA, a.size() * sizeof(float2)));
+    SPB_CUDA(ctx, cudaMemcpy(t.d_twA, a.data(), a.size() * sizeof(float2), cudaMemcpyHostToDevice));
+    SPB_CUDA(ctx, cudaMalloc(&t.d_twB, b.size() * sizeof(float2)));
+    SPB_CUDA(ctx, cudaMemcpy(t.d_twB, b.data(), b.size() * sizeof(float2), cudaMemcpyHostToDevice));
+  }
+  ctx->fft_tables[nfft] = t;
+  *out = t;
+  return SPB_OK;
+}
+
+// Python-compatible frame count (processing.py:103-104, 115-116): float division, then
+// ceil / floor.  Returns false when the count is negative.
+static bool frame_count(int64_t n, int L, int S, int zero_padding, int64_t *F) {
+  const double q = (double)(n - L) / (double)S;
+  const double f = zero_padding ? ceil(q) : floor(q);
+  *F = (int64_t)f;
+  return f >= 0.0;
+}
+
+}  // namespace spb
+
+using namespace spb;
+
+#define SPB_REQUIRE(ctx, cond, msg) \
+  do {                              \
+    if (!(cond)) return fail(ctx, SPB_ERR_INVALID, msg); \
+  } while (0)
+
+extern "C" {
+
+int spb_version(void) { return SPB_VERSION; }
+
+int spb_init(int device, spb_context **out) {
+  if (!out) return fail(nullptr, SPB_ERR_INVALID, "spb_init: ctx pointer is NULL");
+  *out = nullptr;
+  int count = 0;
+  cudaError_t e = cudaGetDeviceCount(&count);
+  if (e != cudaSuccess || count == 0) {
+    cudaGetLastError();
+    return fail(nullptr, SPB_ERR_CUDA,
+                std::string("spb_init: no usable CUDA device (") +
+                    (e != cudaSuccess ? cudaGetErrorString(e) : "device count is 0") +
+                    "); libspeechpy_b200 has no CPU fallback");
+  }
+  if (device < 0 || device >= count) return fail(nullptr, SPB_ERR_INVALID, "spb_init: bad device ordinal");
+  spb_context *ctx = new (std::nothrow) spb_context();
+  if (!ctx) return fail(nullptr, SPB_ERR_NOMEM, "spb_init: out of host memory");
+  ctx->device = device;
+  cudaDeviceProp prop;
+  if ((e = cudaSetDevice(device)) != cudaSuccess || (e = cudaGetDeviceProperties(&prop, device)) != cudaSuccess) {
+    delete ctx;
+    return cuda_fail(nullptr, e, "cudaSetDevice/cudaGetDeviceProperties");
+  }
+  ctx->sm_count = prop.multiProcessorCount;
+  ctx->cc_major = prop.major;
+  ctx->cc_minor = prop.minor;
+  ctx->total_mem = prop.totalGlobalMem;
+  if (prop.major < 10) {
+    delete ctx;
+    return fail(nullptr, SPB_ERR_UNSUPPORTED,
+                "spb_init: this library is built for sm_100a (B200) only");
+  }
+  if ((e = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking)) != cudaSuccess ||
+      (e = cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking)) != cudaSuccess ||
+      (e = cudaEventCreateWithFlags(&ctx->ev_a, cudaEventDisableTiming)) != cudaSuccess ||
+      (e = cudaEventCreateWithFlags(&ctx->ev_b, cudaEventDisableTiming)) != cudaSuccess) {
+    delete ctx;
+    return cuda_fail(nullptr, e, "stream/event creation");
+  }
+  *out = ctx;
+  return SPB_OK;
+}
+
+int spb_destroy(spb_context *ctx) {
+  if (!ctx) return SPB_OK;
+  cudaSetDevice(ctx->device);
+  cudaStreamSynchronize(ctx->stream);
+  cudaStreamSynchronize(ctx->copy_stream);
+  for (auto &b : ctx->scratch)
+    if (b.ptr) cudaFree(b.ptr);
+  for (int i = 0; i < 2; ++i)
+    if (ctx->pinned[i]) cudaFreeHost(ctx->pinned[i]);
+  for (auto &kv : ctx->fft_tables) {
+    if (kv.second.d_tw) cudaFree(kv.second.d_tw);
+    if (kv.second.d_twA) cudaFree(kv.second.d_twA);
+    if (kv.second.d_twB) cudaFree(kv.second.d_twB);
+  }
+  cudaEventDestroy(ctx->ev_a);
+  cudaEventDestroy(ctx->ev_b);
+  cudaStreamDestroy(ctx->stream);
+  cudaStreamDestroy(ctx->copy_stream);
+  delete ctx;
+  return SPB_OK;
+}
+
+const char *spb_last_error(spb_context *ctx) {
+  return ctx ? ctx->last_error.c_str() : g_last_error.c_str();
+}
+
+int spb_sync(spb_context *ctx) {
+  SPB_REQUIRE(ctx, ctx != nullptr, "spb_sync: NULL context");
+  SPB_CUDA(ctx, cudaSetDevice(ctx->device));
+  SPB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  return SPB_OK;
+}
+
+int spb_stream(spb_context *ctx, uint64_t *stream) {
+  SPB_REQUIRE(ctx, ctx && stream, "spb_stream: NULL argument");
+  *stream = (uint64_t)(uintptr_t)ctx->stream;
+  return SPB_OK;
+}
+
+int spb_device_info(spb_context *ctx, int32_t *sm_count, int32_t *cc_major, int32_t *cc_minor,
+                    uint64_t *total_mem) {
+  SPB_REQUIRE(ctx, ctx != nullptr, "spb_device_info: NULL context");
+  if (sm_count) *sm_count = ctx->sm_count;
+  if (cc_major) *cc_major = ctx->cc_major;
+  if (cc_minor) *cc_minor = ctx->cc_minor;
+  if (total_mem) *total_mem = ctx->total_mem;
+  return SPB_OK;
+}
+
+int spb_launch_count(spb_context *ctx, uint64_t *count) {
+  SPB_REQUIRE(ctx, ctx && count, "spb_launch_count: NULL argument");
+  *count = ctx->launches;
+  return SPB_OK;
+}
+
+int spb_host_alloc(void **ptr, size_t bytes) {
+  if (!ptr) return fail(nullptr, SPB_ERR_INVALID, "spb_host_alloc: NULL pointer");
+  cudaError_t e = cudaHostAlloc(ptr, bytes, cudaHostAllocDefault);
+  if (e != cudaSuccess) return cuda_fail(nullptr, e, "cudaHostAlloc");
+  return SPB_OK;
+}
+
+int spb_host_free(void *ptr) {
+  if (!ptr) return SPB_OK;
+  cudaError_t e = cudaFreeHost(ptr);
+  if (e != cudaSuccess) return cuda_fail(nullptr, e, "cudaFreeHost");
+  return SPB_OK;
+}
+
+// ------------------------------------------------------------------ stack_frames
+int spb_num_frames(int64_t num_samples, int32_t frame_len, int32_t frame_stride,
+                   int32_t zero_padding, int64_t *num_frames) {
+  if (!num_frames) return fail(nullptr, SPB_ERR_INVALID, "spb_num_frames: NULL output");
+  if (frame_len < 0 || frame_stride < 1 || num_samples < 0)
+    return fail(nullptr, SPB_ERR_INVALID, "spb_num_frames: frame_len >= 0, frame_stride >= 1, N >= 0 required");
+  int64_t F;
+  if (!frame_count(num_samples, frame_len, frame_stride, zero_padding, &F)) {
+    *num_frames = F;
+    return fail(nullptr, SPB_ERR_NEGATIVE_DIM, "negative dimensions are not allowed");
+  }
+  *num_frames = F;
+  return SPB_OK;
+}
+
+int spb_stack_frames(spb_context *ctx, const double *sig, int64_t num_samples, int32_t frame_len,
+                     int32_t frame_stride, const double *window, int64_t num_frames, double *out) {
+  SPB_REQUIRE(ctx, ctx != nullptr, "spb_stack_frames: NULL context");
+  SPB_REQUIRE(ctx, frame_len >= 1 && frame_stride >= 1, "spb_stack_frames: bad frame geometry");
+  SPB_REQUIRE(ctx, num_frames >= 0 && num_samples >= 0, "spb_stack_frames: negative size");
+  if (num_frames == 0) return SPB_OK;
+  SPB_REQUIRE(ctx, sig && out, "spb_stack_frames: NULL buffer");
+  SPB_CUDA(ctx, cudaSetDevice(ctx->device));
+  const size_t out_elems = (size_t)num_frames * frame_len;
+  double *d_sig = (double *)scratch(ctx, 0, (size_t)std::max<int64_t>(num_samples, 1) * 8);
+  double *d_out = (double *)scratch(ctx, 1, out_elems * 8);
+  double *d_win = nullptr;
+  if (!d_sig || !d_out) return SPB_ERR_CUDA;
+  if (window) {
+    d_win = (double *)scratch(ctx, 4, (size_t)frame_len * 8);
+    if (!d_win) return SPB_ERR_CUDA;
+    SPB_CUDA(ctx, cudaMemcpyAsync(d_win, window, (size_t)frame_len * 8, cudaMemcpyHostToDevice, ctx->stream));
+  }
+  SPB_CUDA(ctx, cudaMemcpyAsync(d_sig, sig, (size_t)num_samples * 8, cudaMemcpyHostToDevice, ctx->stream));
+  int rc = launch_stack_frames_f64(ctx, d_sig, num_samples, frame_len, frame_stride, d_win, num_frames, d_out);
+  if (rc) return rc;
+  SPB_CUDA(ctx, cudaMemcpyAsync(out, d_out, out_elems * 8, cudaMemcpyDeviceToHost, ctx->stream));
+  SPB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  return SPB_OK;
+}
+
+// ------------------------------------------------------------------ plans
+int spb_plan_create(spb_context *ctx, const spb_feature_params *params, const double *filterbank,
+                    spb_plan **plan) {
+  SPB_REQUIRE(ctx, ctx && params && plan, "spb_plan_create: NULL argument");
+  *plan = nullptr;
+  const spb_feature_params &q = *params;
+  SPB_REQUIRE(ctx, q.frame_len >= 1 && q.frame_stride >= 1, "plan: frame_len and frame_stride must be >= 1");
+  if (!(is_pow2(q.nfft) && q.nfft >= 32 && q.nfft <= 4096))
+    return fail(ctx, SPB_ERR_UNSUPPORTED, "plan: fft_length must be a power of two in [32, 4096]");
+  SPB_REQUIRE(ctx, q.num_filters >= 0 && q.num_filters <= 256, "plan: num_filters must be in [0, 256]");
+  SPB_REQUIRE(ctx, q.num_cepstral >= 0 && q.num_cepstral <= std::max(q.num_filters, 0),
+              "plan: num_cepstral must be in [0, num_filters]");
+  SPB_REQUIRE(ctx, q.num_filters == 0 || filterbank != nullptr, "plan: filterbank is NULL");
+  if (q.cmvn_window != 0) {
+    SPB_REQUIRE(ctx, q.cmvn_window > 0 && (q.cmvn_window & 1), "Windows size must be odd!");
+  }
+  SPB_CUDA(ctx, cudaSetDevice(ctx->device));
+  spb_plan *pl = new (std::nothrow) spb_plan();
+  if (!pl) return fail(ctx, SPB_ERR_NOMEM, "plan: out of host memory");
+  pl->ctx = ctx;
+  pl->p = q;
+  pl->K = q.nfft / 2 + 1;
+  const int M = q.num_filters, K = pl->K, C = q.num_cepstral;
+  std::vector<float> w;
+  pl->h_band_lo.assign(M, 0);
+  pl->h_band_n.assign(M, 0);
+  pl->h_band_off.assign(M, 0);
+  for (int m = 0; m < M; ++m) {
+    int lo = -1, hi = -1;
+    for (int k = 0; k < K; ++k)
+      if (filterbank[(size_t)m * K + k] != 0.0) {
+        if (lo < 0) lo = k;
+        hi = k;
+      }
+    pl->h_band_off[m] = (int)w.size();
+    if (lo >= 0) {
+      pl->h_band_lo[m] = lo;
+      pl->h_band_n[m] = hi - lo + 1;
+      for (int k = lo; k <= hi; ++k) w.push_back((float)filterbank[(size_t)m * K + k]);
+      pl->max_bin = std::max(pl->max_bin, hi);
+    }
+  }
+  pl->band_total = (int)w.size();
+  std::vector<float> dct((size_t)C * M);
+  const double pi = 3.14159265358979323846264338327950288;
+  for (int c = 0; c < C; ++c) {
+    const double s = (c == 0) ? sqrt(1.0 / M) : sqrt(2.0 / M);
+    for (int m = 0; m < M; ++m) dct[(size_t)c * M + m] = (float)(s * cos(pi * c * (2.0 * m + 1.0) / (2.0 * M)));
+  }
+  auto up = [&](void **dptr, const void *src, size_t bytes) -> cudaError_t {
+    cudaError_t e = cudaMalloc(dptr, std::max(bytes, (size_t)16));
+    if (e != cudaSuccess) return e;
+    if (bytes) e = cudaMemcpy(*dptr, src, bytes, cudaMemcpyHostToDevice);
+    return e;
+  };
+  cudaError_t e;
+  if ((e = up((void **)&pl->d_band_lo, pl->h_band_lo.data(), (size_t)M * 4)) != cudaSuccess ||
+      (e = up((void **)&pl->d_band_n, pl->h_band_n.data(), (size_t)M * 4)) != cudaSuccess ||
+      (e = up((void **)&pl->d_band_off, pl->h_band_off.data(), (size_t)M * 4)) != cudaSuccess ||
+      (e = up((void **)&pl->d_band_w, w.data(), w.size() * 4)) != cudaSuccess ||
+      (e = up((void **)&pl->d_dct, dct.data(), dct.size() * 4)) != cudaSuccess) {
+    spb_plan_destroy(pl);
+    return cuda_fail(ctx, e, "plan upload");
+  }
+  FftTables t;
+  int rc = get_fft_tables(ctx, q.nfft, &t);
+  if (rc) {
+    spb_plan_destroy(pl);
+    return rc;
+  }
+  *plan = pl;
+  return SPB_OK;
+}
+
+int spb_plan_destroy(spb_plan *pl) {
+  if (!pl) return SPB_OK;
+  if (pl->ctx) cudaSetDevice(pl->ctx->device);
+  cudaFree(pl->d_band_lo);
+  cudaFree(pl->d_band_n);
+  cudaFree(pl->d_band_off);
+  cudaFree(pl->d_band_w);
+  cudaFree(pl->d_dct);
+  delete pl;
+  return SPB_OK;
+}
+
+// ------------------------------------------------------------------ batches
+static constexpr int kFftTile = 32;
+static constexpr int64_t kChunkRows = 192 * 1024;  // ~30 MB of 40-wide fp32 rows: L2-resident
+
+int spb_batch_create(spb_context *ctx, const spb_plan *plan, const int64_t *starts,
+                     const int64_t *lengths, int64_t U, spb_batch **out) {
+  SPB_REQUIRE(ctx, ctx && plan && out, "spb_batch_create: NULL argument");
+  SPB_REQUIRE(ctx, U >= 0 && (U == 0 || (starts && lengths)), "spb_batch_create: bad utterance table");
+  SPB_REQUIRE(ctx, U < ((int64_t)1 << 31), "spb_batch_create: too many utterances");
+  *out = nullptr;
+  SPB_CUDA(ctx, cudaSetDevice(ctx->device));
+  const int L = plan->p.frame_len, S = plan->p.frame_stride;
+  spb_batch *b = new (std::nothrow) spb_batch();
+  if (!b) return fail(ctx, SPB_ERR_NOMEM, "batch: out of host memory");
+  b->ctx = ctx;
+  b->plan = plan;
+  b->U = U;
+  b->tile_frames = kFftTile;
+  const int win = plan->p.cmvn_window;
+  b->cm_tile_rows = (win > 0) ? cmvnw_tile_rows(plan->p.num_filters, win) : 0;
+  std::vector<int32_t> nframes(U);
+  std::vector<int64_t> tile_off(U + 1, 0), cm_off(U + 1, 0);
+  b->h_frame_offsets.assign(U + 1, 0);
+  spb_batch &ch = *b;
+  BatchChunk cur{0, 0, 0, 0, 0, 0, 0, 0};
+  for (int64_t u = 0; u < U; ++u) {
+    int64_t F;
+    if (starts[u] < 0 || lengths[u] < 0) {
+      delete b;
+      return fail(ctx, SPB_ERR_INVALID, "batch: negative start or length");
+    }
+    if (!frame_count(lengths[u], L, S, 0, &F)) {
+      delete b;
+      return fail(ctx, SPB_ERR_NEGATIVE_DIM, "negative dimensions are not allowed");
+    }
+    if (F >= ((int64_t)1 << 31) - 64) {
+      delete b;
+      return fail(ctx, SPB_ERR_INVALID, "batch: utterance too long");
+    }
+    nframes[u] = (int32_t)F;
+    b->h_frame_offsets[u + 1] = b->h_frame_offsets[u] + F;
+    tile_off[u + 1] = tile_off[u] + (F + kFftTile - 1) / kFftTile;
+    cm_off[u + 1] = cm_off[u] + (b->cm_tile_rows ? (F + b->cm_tile_rows - 1) / b->cm_tile_rows : 0);
+    b->max_end = std::max(b->max_end, starts[u] + lengths[u]);
+    // chunking by whole utterances
+    if (b->h_frame_offsets[u + 1] - cur.row0 > kChunkRows && u > cur.u0) {
+      cur.u1 = u;
+      cur.tile1 = tile_off[u];
+      cur.cm1 = cm_off[u];
+      cur.row1 = b->h_frame_offsets[u];
+      ch.chunks.push_back(cur);
+      ch.max_chunk_rows = std::max(ch.max_chunk_rows, cur.row1 - cur.row0);
+      cur = BatchChunk{u, u, tile_off[u], tile_off[u], cm_off[u], cm_off[u], cur.row1, cur.row1};
+    }
+  }
+  cur.u1 = U;
+  cur.tile1 = tile_off[U];
+  cur.cm1 = cm_off[U];
+  cur.row1 = b->h_frame_offsets[U];
+  if (cur.u1 > cur.u0) {
+    ch.chunks.push_back(cur);
+    ch.max_chunk_rows = std::max(ch.max_chunk_rows, cur.row1 - cur.row0);
+  }
+  b->total_frames = b->h_frame_offsets[U];
+  b->total_tiles = tile_off[U];
+  b->total_cm_tiles = cm_off[U];
+  auto cleanup = [&](cudaError_t e, const char *what) {
+    spb_batch_destroy(b);
+    return cuda_fail(ctx, e, what);
+  };
+  cudaError_t e;
+  const size_t u_bytes = (size_t)std::max<int64_t>(U, 1);
+  int64_t *d_tile_off = nullptr, *d_cm_off = nullptr;
+  if ((e = cudaMalloc(&b->d_starts, u_bytes * 8)) != cudaSuccess ||
+      (e = cudaMalloc(&b->d_nframes, u_bytes * 4)) != cudaSuccess ||
+      (e = cudaMalloc(&b->d_frame_offsets, (u_bytes + 1) * 8)) != cudaSuccess ||
+      (e = cudaMalloc(&b->d_tiles, (size_t)std::max<int64_t>(b->total_tiles, 1) * sizeof(int2))) != cudaSuccess ||
+      (e = cudaMalloc(&b->d_cm_tiles, (size_t)std::max<int64_t>(b->total_cm_tiles, 1) * sizeof(int2))) != cudaSuccess ||
+      (e = cudaMalloc(&d_tile_off, (u_bytes + 1) * 8)) != cudaSuccess ||
+      (e = cudaMalloc(&d_cm_off, (u_bytes + 1) * 8)) != cudaSuccess)
+    return cleanup(e, "cudaMalloc(batch)");
+  if (U > 0) {
+    if ((e = cudaMemcpyAsync(b->d_starts, starts, (size_t)U * 8, cudaMemcpyHostToDevice, ctx->stream)) != cudaSuccess ||
+        (e = cudaMemcpyAsync(b->d_nframes, nframes.data(), (size_t)U * 4, cudaMemcpyHostToDevice, ctx->stream)) != cudaSuccess ||
+        (e = cudaMemcpyAsync(b->d_frame_offsets, b->h_frame_offsets.data(), (size_t)(U + 1) * 8, cudaMemcpyHostToDevice, ctx->stream)) != cudaSuccess ||
+        (e = cudaMemcpyAsync(d_tile_off, tile_off.data(), (size_t)(U + 1) * 8, cudaMemcpyHostToDevice, ctx->stream)) != cudaSuccess ||
+        (e = cudaMemcpyAsync(d_cm_off, cm_off.data(), (size_t)(U + 1) * 8, cudaMemcpyHostToDevice, ctx->stream)) != cudaSuccess)
+      return cleanup(e, "cudaMemcpyAsync(batch)");
+    int rc = launch_build_tiles(ctx, b->d_nframes, d_tile_off, U, kFftTile, b->d_tiles);
+    if (!rc && b->cm_tile_rows)
+      rc = launch_build_tiles(ctx, b->d_nframes, d_cm_off, U, b->cm_tile_rows, b->d_cm_tiles);
+    if (rc) {
+      spb_batch_destroy(b);
+      return rc;
+    }
+  }
+  // the host vectors above are pageable: wait for the copies before they go out of scope
+  e = cudaStreamSynchronize(ctx->stream);
+  cudaFree(d_tile_off);
+  cudaFree(d_cm_off);
+  if (e != cudaSuccess) return cleanup(e, "cudaStreamSynchronize(batch)");
+  *out = b;
+  return SPB_OK;
+}
+
+int spb_batch_destroy(spb_batch *b) {
+  if (!b) return SPB_OK;
+  if (b->ctx) cudaSetDevice(b->ctx->device);
+  cudaFree(b->d_starts);
+  cudaFree(b->d_nframes);
+  cudaFree(b->d_frame_offsets);
+  cudaFree(b->d_tiles);
+  cudaFree(b->d_cm_tiles);
+  delete b;
+  return SPB_OK;
+}
+
+int spb_batch_total_frames(const spb_batch *b, int64_t *total_frames) {
+  if (!b || !total_frames) return fail(nullptr, SPB_ERR_INVALID, "spb_batch_total_frames: NULL argument");
+  *total_frames = b->total_frames;
+  return SPB_OK;
+}
+
+int spb_batch_frame_offsets(const spb_batch *b, int64_t *frame_offsets) {
+  if (!b || !frame_offsets) return fail(nullptr, SPB_ERR_INVALID, "spb_batch_frame_offsets: NULL argument");
+  memcpy(frame_offsets, b->h_frame_offsets.data(), (size_t)(b->U + 1) * 8);
+  return SPB_OK;
+}
+
+}  // extern "C"
+
+// ------------------------------------------------------------------ feature launches
+namespace spb {
+
+static void fill_feat_args(FeatArgs &a, const spb_batch *b, const float *d_samples, int64_t arena_len,
+                           int mode, float *d_out, float *d_energy) {
+  const spb_plan *pl = b->plan;
+  a.samples = d_samples;
+  a.arena_len = arena_len;
+  a.starts = b->d_starts;
+  a.nframes = b->d_nframes;
+  a.frame_offsets = b->d_frame_offsets;
+  a.tiles = b->d_tiles;
+  a.num_tiles = b->total_tiles;
+  a.tile_frames = b->tile_frames;
+  a.L = pl->p.frame_len;
+  a.S = pl->p.frame_stride;
+  a.nfft = pl->p.nfft;
+  a.K = pl->K;
+  a.M = pl->p.num_filters;
+  a.C = pl->p.num_cepstral;
+  a.dc_elim = pl->p.dc_elimination;
+  a.band_lo = pl->d_band_lo;
+  a.band_n = pl->d_band_n;
+  a.band_off = pl->d_band_off;
+  a.band_w = pl->d_band_w;
+  a.band_total = pl->band_total;
+  a.max_bin = pl->max_bin;
+  a.dct = pl->d_dct;
+  a.mode = mode;
+  a.out = d_out;
+  a.energy = d_energy;
+}
+
+// force_generic: 0 auto, 1 generic kernel (used by tests to cross-check the fast path)
+static int g_force_generic = 0;
+
+static int run_features(spb_context *ctx, FeatArgs &a) {
+  if (a.num_tiles <= 0) return SPB_OK;
+  FftTables t;
+  int rc = get_fft_tables(ctx, a.nfft, &t);
+  if (rc) return rc;
+  if (!g_force_generic && fast512_supported(a)) return launch_features_fast512(ctx, a, t);
+  return launch_features_generic(ctx, a, t);
+}
+
+static int check_batch(spb_context *ctx, const spb_batch *b, int64_t arena_len, const void *in,
+                       const void *out) {
+  SPB_REQUIRE(ctx, ctx && b, "batch call: NULL context or batch");
+  SPB_REQUIRE(ctx, b->ctx == ctx, "batch call: batch belongs to another context");
+  SPB_REQUIRE(ctx, arena_len >= b->max_end, "batch call: sample arena shorter than starts+lengths");
+  if (b->total_frames > 0) SPB_REQUIRE(ctx, in && out, "batch call: NULL buffer");
+  return SPB_OK;
+}
+
+// lmfe -> cmvnw over chunks of whole utterances; the lmfe and mean-subtracted
+// intermediates of a chunk live in two chunk-sized scratch buffers that stay in L2.
+static int run_lmfe_cmvnw(spb_context *ctx, const spb_batch *b, const float *d_samples,
+                          int64_t arena_len, float *d_out) {
+  const spb_plan *pl = b->plan;
+  const int M = pl->p.num_filters, win = pl->p.cmvn_window;
+  SPB_REQUIRE(ctx, win > 0 && (win & 1), "lmfe_cmvnw: plan has no (odd) cmvn_window");
+  SPB_REQUIRE(ctx, M >= 1, "lmfe_cmvnw: plan has no filterbank");
+  if (!cmvnw_supported(M, win)) return fail(ctx, SPB_ERR_UNSUPPORTED, "cmvnw: window x columns too large for shared memory");
+  const spb_batch &ch = *b;
+  if (ch.chunks.empty()) return SPB_OK;
+  const size_t chunk_bytes = (size_t)ch.max_chunk_rows * M * 4;
+  float *d_lmfe = (float *)scratch(ctx, 2, chunk_bytes);
+  float *d_ms = pl->p.cmvn_variance ? (float *)scratch(ctx, 3, chunk_bytes) : nullptr;
+  if (!d_lmfe || (pl->p.cmvn_variance && !d_ms)) return SPB_ERR_CUDA;
+  for (const BatchChunk &c : ch.chunks) {
+    FeatArgs a;
+    // rows are addressed by their global index; bias the scratch pointers so that row
+    // c.row0 lands at the start of the chunk buffer
+    float *lmfe_biased = d_lmfe - (ptrdiff_t)c.row0 * M;
+    fill_feat_args(a, b, d_samples, arena_len, FEAT_LMFE, lmfe_biased, nullptr);
+    a.tiles = b->d_tiles + c.tile0;
+    a.num_tiles = c.tile1 - c.tile0;
+    int rc = run_features(ctx, a);
+    if (rc) return rc;
+    float *ms_biased = d_ms ? d_ms - (ptrdiff_t)c.row0 * M : nullptr;
+    rc = launch_cmvnw_f32(ctx, lmfe_biased, ms_biased, d_out, b->d_nframes, b->d_frame_offsets,
+                          b->d_cm_tiles + c.cm0, c.cm1 - c.cm0, b->cm_tile_rows, M, M, win,
+                          pl->p.cmvn_variance);
+    if (rc) return rc;
+  }
+  return SPB_OK;
+}
+
+static int run_simple_mode(spb_context *ctx, const spb_batch *b, const float *d_samples,
+                           int64_t arena_len, int mode, float *d_out, float *d_energy) {
+  FeatArgs a;
+  fill_feat_args(a, b, d_samples, arena_len, mode, d_out, d_energy);
+  return run_features(ctx, a);
+}
+
+// Host signal of any supported dtype -> float32 on device (scratch slot 0).
+static int upload_signal(spb_context *ctx, const void *sig, int dtype, int64_t n, float **d_out) {
+  size_t esz = (dtype == SPB_F64) ? 8 : (dtype == SPB_I16 ? 2 : 4);
+  SPB_REQUIRE(ctx, dtype == SPB_F32 || dtype == SPB_F64 || dtype == SPB_I16 || dtype == SPB_I32,
+              "unsupported signal dtype");
+  float *d_f32 = (float *)scratch(ctx, 0, (size_t)std::max<int64_t>(n, 1) * 4);
+  if (!d_f32) return SPB_ERR_CUDA;
+  if (dtype == SPB_F32) {
+    SPB_CUDA(ctx, cudaMemcpyAsync(d_f32, sig, (size_t)n * 4, cudaMemcpyHostToDevice, ctx->stream));
+  } else {
+    void *d_raw = scratch(ctx, 5, (size_t)std::max<int64_t>(n, 1) * esz);
+    if (!d_raw) return SPB_ERR_CUDA;
+    SPB_CUDA(ctx, cudaMemcpyAsync(d_raw, sig, (size_t)n * esz, cudaMemcpyHostToDevice, ctx->stream));
+    int rc = launch_convert(ctx, d_raw, dtype, d_f32, SPB_F32, n);
+    if (rc) return rc;
+  }
+  *d_out = d_f32;
+  return SPB_OK;
+}
+
+// device float32 -> host float64 (widen on the host; D2H carries 4 bytes per value)
+static int download_as_f64(spb_context *ctx, const float *d_src, size_t n, double *dst) {
+  if (n == 0) return SPB_OK;
+  std::vector<float> tmp(n);
+  SPB_CUDA(ctx, cudaMemcpyAsync(tmp.data(), d_src, n * 4, cudaMemcpyDeviceToHost, ctx->stream));
+  SPB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  for (size_t i = 0; i < n; ++i) dst[i] = (double)tmp[i];
+  return SPB_OK;
+}
+
+static int single_signal(spb_context *ctx, const spb_plan *plan, const void *sig, int dtype,
+                         int64_t n, int mode, int width, double *out, double *energy) {
+  SPB_REQUIRE(ctx, ctx && plan, "feature call: NULL context or plan");
+  SPB_REQUIRE(ctx, plan->ctx == ctx, "feature call: plan belongs to another context");
+  SPB_REQUIRE(ctx, n >= 0, "feature call: negative length");
+  SPB_CUDA(ctx, cudaSetDevice(ctx->device));
+  int64_t F;
+  if (!frame_count(n, plan->p.frame_len, plan->p.frame_stride, 0, &F))
+    return fail(ctx, SPB_ERR_NEGATIVE_DIM, "negative dimensions are not allowed");
+  if (F == 0) return SPB_OK;
+  SPB_REQUIRE(ctx, sig && out, "feature call: NULL buffer");
+  float *d_sig = nullptr;
+  int rc = upload_signal(ctx, sig, dtype, n, &d_sig);
+  if (rc) return rc;
+  const int64_t start = 0;
+  spb_batch *b = nullptr;
+  rc = spb_batch_create(ctx, plan, &start, &n, 1, &b);
+  if (rc) return rc;
+  float *d_out = (float *)scratch(ctx, 1, (size_t)F * width * 4);
+  float *d_en = energy ? (float *)scratch(ctx, 4, (size_t)F * 4) : nullptr;
+  if (!d_out || (energy && !d_en)) {
+    spb_batch_destroy(b);
+    return SPB_ERR_CUDA;
+  }
+  rc = run_simple_mode(ctx, b, d_sig, n, mode, d_out, d_en);
+  if (!rc) rc = download_as_f64(ctx, d_out, (size_t)F * width, out);
+  if (!rc && energy) rc = download_as_f64(ctx, d_en, (size_t)F, energy);
+  cudaStreamSynchronize(ctx->stream);
+  spb_batch_destroy(b);
+  return rc;
+}
+
+}  // namespace spb
+
+extern "C" {
+
+// test hook (not in the public header): route every feature launch through the generic kernel
+SPB_API int spb_debug_force_generic(int on) {
+  g_force_generic = on;
+  return SPB_OK;
+}
+
+int spb_power_spectrum(spb_context *ctx, const double *frames, int64_t F, int32_t L, int32_t nfft,
+                       int32_t mode, double *out) {
+  SPB_REQUIRE(ctx, ctx != nullptr, "spb_power_spectrum: NULL context");
+  SPB_REQUIRE(ctx, F >= 0 && L >= 1, "spb_power_spectrum: bad shape");
+  SPB_REQUIRE(ctx, mode == 0 || mode == 1, "spb_power_spectrum: mode must be 0 or 1");
+  if (!(is_pow2(nfft) && nfft >= 32 && nfft <= 4096))
+    return fail(ctx, SPB_ERR_UNSUPPORTED, "fft_points must be a power of two in [32, 4096]");
+  if (F == 0) return SPB_OK;
+  SPB_REQUIRE(ctx, frames && out, "spb_power_spectrum: NULL buffer");
+  SPB_CUDA(ctx, cudaSetDevice(ctx->device));
+  // (F, L) row-major frames == one signal of F*L samples framed with length L, stride L
+  spb_feature_params q{};
+  q.frame_len = L;
+  q.frame_stride = L;
+  q.nfft = nfft;
+  spb_plan *pl = nullptr;
+  int rc = spb_plan_create(ctx, &q, nullptr, &pl);
+  if (rc) return rc;
+  const int64_t n = F * L;
+  float *d_sig = nullptr;
+  rc = upload_signal(ctx, frames, SPB_F64, n, &d_sig);
+  spb_batch *b = nullptr;
+  if (!rc) {
+    // F frames of length L at stride L need N = F*L + L samples under the mfe frame
+    // count floor((N-L)/S); describe the signal as one sample-row longer than it is and
+    // let the (never read) tail stay virtual: the last frame ends at sample F*L - 1.
+    const int64_t start = 0, len = n + L;
+    rc = spb_batch_create(ctx, pl, &start, &len, 1, &b);
+  }
+  const int K = nfft / 2 + 1;
+  float *d_out = rc ? nullptr : (float *)scratch(ctx, 1, (size_t)F * K * 4);
+  if (!rc && !d_out) rc = SPB_ERR_CUDA;
+  if (!rc) {
+    FeatArgs a;
+    fill_feat_args(a, b, d_sig, n, mode == 0 ? FEAT_POWER : FEAT_MAG, d_out, nullptr);
+    rc = run_features(ctx, a);
+  }
+  if (!rc) rc = download_as_f64(ctx, d_out, (size_t)F * K, out);
+  cudaStreamSynchronize(ctx->stream);
+  spb_batch_destroy(b);
+  spb_plan_destroy(pl);
+  return rc;
+}
+
+int spb_mfe(spb_context *ctx, const spb_plan *plan, const void *sig, int32_t dtype, int64_t n,
+            double *feat, double *energy) {
+  if (!plan) return fail(ctx, SPB_ERR_INVALID, "spb_mfe: NULL plan");
+  return single_signal(ctx, plan, sig, dtype, n, FEAT_MFE, plan->p.num_filters, feat, energy);
+}
+
+int spb_lmfe(spb_context *ctx, const spb_plan *plan, const void *sig, int32_t dtype, int64_t n,
+             double *feat) {
+  if (!plan) return fail(ctx, SPB_ERR_INVALID, "spb_lmfe: NULL plan");
+  return single_signal(ctx, plan, sig, dtype, n, FEAT_LMFE, plan->p.num_filters, feat, nullptr);
+}
+
+int spb_mfcc(spb_context *ctx, const spb_plan *plan, const void *sig, int32_t dtype, int64_t n,
+             double *ceps) {
+  if (!plan) return fail(ctx, SPB_ERR_INVALID, "spb_mfcc: NULL plan");
+  SPB_REQUIRE(ctx, plan->p.num_cepstral >= 1, "spb_mfcc: plan has num_cepstral == 0");
+  return single_signal(ctx, plan, sig, dtype, n, FEAT_MFCC, plan->p.num_cepstral, ceps, nullptr);
+}
+
+// ------------------------------------------------------------------ float64 helpers
+static int f64_roundtrip(spb_context *ctx, const double *in, size_t n_in, double **d_in, size_t n_out,
+                         double **d_out) {
+  *d_in = (double *)scratch(ctx, 0, std::max(n_in, (size_t)1) * 8);
+  *d_out = (double *)scratch(ctx, 1, std::max(n_out, (size_t)1) * 8);
+  if (!*d_in || !*d_out) return SPB_ERR_CUDA;
+  SPB_CUDA(ctx, cudaMemcpyAsync(*d_in, in, n_in * 8, cudaMemcpyHostToDevice, ctx->stream));
+  return SPB_OK;
+}
+
+int spb_delta_cube(spb_context *ctx, const double *feat, int64_t F, int32_t cols, double *out) {
+  SPB_REQUIRE(ctx, ctx != nullptr, "spb_delta_cube: NULL context");
+  SPB_REQUIRE(ctx, F >= 0 && cols >= 1, "spb_delta_cube: bad shape");
+  if (F == 0) return SPB_OK;
+  SPB_REQUIRE(ctx, feat && out, "spb_delta_cube: NULL buffer");
+  SPB_CUDA(ctx, cudaSetDevice(ctx->device));
+  double *d_in, *d_out;
+  const size_t n = (size_t)F * cols;
+  int rc = f64_roundtrip(ctx, feat, n, &d_in, n * 3, &d_out);
+  if (rc) return rc;
+  rc = launch_delta_cube_f64(ctx, d_in, F, cols, d_out);
+  if (rc) return rc;
+  SPB_CUDA(ctx, cudaMemcpyAsync(out, d_out, n * 3 * 8, cudaMemcpyDeviceToHost, ctx->stream));
+  SPB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  return SPB_OK;
+}
+
+int spb_derivative(spb_context *ctx, const double *feat, int64_t F, int32_t cols, int32_t dw,
+                   double *out) {
+  SPB_REQUIRE(ctx, ctx != nullptr, "spb_derivative: NULL context");
+  SPB_REQUIRE(ctx, F >= 0 && cols >= 1 && dw >= 1, "spb_derivative: bad shape or DeltaWindows");
+  if (F == 0) return SPB_OK;
+  SPB_REQUIRE(ctx, feat && out, "spb_derivative: NULL buffer");
+  SPB_CUDA(ctx, cudaSetDevice(ctx->device));
+  double *d_in, *d_out;
+  const size_t n = (size_t)F * cols;
+  int rc = f64_roundtrip(ctx, feat, n, &d_in, n, &d_out);
+  if (rc) return rc;
+  rc = launch_derivative_f64(ctx, d_in, F, cols, dw, d_out);
+  if (rc) return rc;
+  SPB_CUDA(ctx, cudaMemcpyAsync(out, d_out, n * 8, cudaMemcpyDeviceToHost, ctx->stream));
+  SPB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  return SPB_OK;
+}
+
+int spb_cmvn(spb_context *ctx, const double *vec, int64_t rows, int32_t cols, int32_t varnorm,
+             double *out) {
+  SPB_REQUIRE(ctx, ctx != nullptr, "spb_cmvn: NULL context");
+  SPB_REQUIRE(ctx, rows >= 0 && cols >= 0, "spb_cmvn: bad shape");
+  if (rows == 0 || cols == 0) return SPB_OK;
+  SPB_REQUIRE(ctx, vec && out, "spb_cmvn: NULL buffer");
+  SPB_CUDA(ctx, cudaSetDevice(ctx->device));
+  double *d_in, *d_out;
+  const size_t n = (size_t)rows * cols;
+  int rc = f64_roundtrip(ctx, vec, n, &d_in, n, &d_out);
+  if (rc) return rc;
+  rc = launch_cmvn_f64(ctx, d_in, rows, cols, varnorm, d_out);
+  if (rc) return rc;
+  SPB_CUDA(ctx, cudaMemcpyAsync(out, d_out, n * 8, cudaMemcpyDeviceToHost, ctx->stream));
+  SPB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  return SPB_OK;
+}
+
+int spb_cmvnw(spb_context *ctx, const double *vec, int64_t rows, int32_t cols, int32_t win,
+              int32_t varnorm, float *out) {
+  SPB_REQUIRE(ctx, ctx != nullptr, "spb_cmvnw: NULL context");
+  SPB_REQUIRE(ctx, win > 0 && (win & 1), "Windows size must be odd!");
+  SPB_REQUIRE(ctx, rows >= 0 && cols >= 0, "spb_cmvnw: bad shape");
+  SPB_REQUIRE(ctx, rows < ((int64_t)1 << 30), "spb_cmvnw: too many rows");
+  if (rows == 0 || cols == 0) return SPB_OK;
+  SPB_REQUIRE(ctx, vec && out, "spb_cmvnw: NULL buffer");
+  SPB_CUDA(ctx, cudaSetDevice(ctx->device));
+  // column chunk that fits shared memory
+  int cc = cols;
+  while (cc > 1 && !cmvnw_supported(cc, win)) cc = (cc + 1) / 2;
+  if (!cmvnw_supported(cc, win)) return fail(ctx, SPB_ERR_UNSUPPORTED, "cmvnw: win_size too large for shared memory");
+  const size_t n = (size_t)rows * cols;
+  double *d_f64 = (double *)scratch(ctx, 5, n * 8);
+  float *d_in = (float *)scratch(ctx, 0, n * 4);
+  float *d_out = (float *)scratch(ctx, 1, n * 4);
+  float *d_ms = (float *)scratch(ctx, 3, n * 4);
+  if (!d_f64 || !d_in || !d_out || !d_ms) return SPB_ERR_CUDA;
+  SPB_CUDA(ctx, cudaMemcpyAsync(d_f64, vec, n * 8, cudaMemcpyHostToDevice, ctx->stream));
+  int rc = launch_convert(ctx, d_f64, SPB_F64, d_in, SPB_F32, (int64_t)n);
+  if (rc) return rc;
+  // one "utterance" of `rows` rows
+  const int R = cmvnw_tile_rows(cc, win);
+  const int64_t ntiles = (rows + R - 1) / R;
+  const int32_t nfr = (int32_t)rows;
+  const int64_t offs[2] = {0, rows};
+  const int64_t toff[2] = {0, ntiles};
+  int32_t *d_nfr = (int32_t *)scratch(ctx, 4, 64 + (size_t)ntiles * sizeof(int2));
+  if (!d_nfr) return SPB_ERR_CUDA;
+  int64_t *d_offs = (int64_t *)((char *)d_nfr + 16);
+  int64_t *d_toff = (int64_t *)((char *)d_nfr + 32);
+  int2 *d_tiles = (int2 *)((char *)d_nfr + 64);
+  SPB_CUDA(ctx, cudaMemcpyAsync(d_nfr, &nfr, 4, cudaMemcpyHostToDevice, ctx->stream));
+  SPB_CUDA(ctx, cudaMemcpyAsync(d_offs, offs, 16, cudaMemcpyHostToDevice, ctx->stream));
+  SPB_CUDA(ctx, cudaMemcpyAsync(d_toff, toff, 16, cudaMemcpyHostToDevice, ctx->stream));
+  rc = launch_build_tiles(ctx, d_nfr, d_toff, 1, R, d_tiles);
+  if (rc) return rc;
+  for (int c0 = 0; c0 < cols; c0 += cc) {
+    const int w = std::min(cc, cols - c0);
+    rc = launch_cmvnw_f32(ctx, d_in + c0, d_ms + c0, d_out + c0, d_nfr, d_offs, d_tiles, ntiles, R,
+                          w, cols, win, varnorm);
+    if (rc) return rc;
+  }
+  SPB_CUDA(ctx, cudaMemcpyAsync(out, d_out, n * 4, cudaMemcpyDeviceToHost, ctx->stream));
+  SPB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  return SPB_OK;
+}
+
+// ------------------------------------------------------------------ batch entry points
+int spb_lmfe_cmvnw_batch_dev(spb_context *ctx, const spb_batch *b, const float *d_samples,
+                             int64_t arena_len, float *d_out) {
+  int rc = check_batch(ctx, b, arena_len, d_samples, d_out);
+  if (rc) return rc;
+  SPB_CUDA(ctx, cudaSetDevice(ctx->device));
+  return run_lmfe_cmvnw(ctx, b, d_samples, arena_len, d_out);
+}
+
+int spb_lmfe_batch_dev(spb_context *ctx, const spb_batch *b, const float *d_samples,
+                       int64_t arena_len, float *d_out) {
+  int rc = check_batch(ctx, b, arena_len, d_samples, d_out);
+  if (rc) return rc;
+  SPB_CUDA(ctx, cudaSetDevice(ctx->device));
+  return run_simple_mode(ctx, b, d_samples, arena_len, FEAT_LMFE, d_out, nullptr);
+}
+
+int spb_mfcc_delta_batch_dev(spb_context *ctx, const spb_batch *b, const float *d_samples,
+                             int64_t arena_len, float *d_out) {
+  int rc = check_batch(ctx, b, arena_len, d_samples, d_out);
+  if (rc) return rc;
+  SPB_REQUIRE(ctx, b->plan->p.num_cepstral >= 1, "mfcc_delta: plan has num_cepstral == 0");
+  SPB_CUDA(ctx, cudaSetDevice(ctx->device));
+  return run_simple_mode(ctx, b, d_samples, arena_len, FEAT_MFCC_DELTA, d_out, nullptr);
+}
+
+static int host_batch(spb_context *ctx, const spb_batch *b, const float *samples, int64_t arena_len,
+                      float *out, int which) {
+  int rc = check_batch(ctx, b, arena_len, samples, out);
+  if (rc) return rc;
+  SPB_CUDA(ctx, cudaSetDevice(ctx->device));
+  if (b->total_frames == 0) return SPB_OK;
+  const int width = (which == 0) ? b->plan->p.num_filters : b->plan->p.num_cepstral * 3;
+  float *d_samples = (float *)scratch(ctx, 0, (size_t)arena_len * 4);
+  float *d_out = (float *)scratch(ctx, 1, (size_t)b->total_frames * width * 4);
+  if (!d_samples || !d_out) return SPB_ERR_CUDA;
+  SPB_CUDA(ctx, cudaMemcpyAsync(d_samples, samples, (size_t)arena_len * 4, cudaMemcpyHostToDevice, ctx->stream));
+  rc = (which == 0) ? run_lmfe_cmvnw(ctx, b, d_samples, arena_len, d_out)
+                    : run_simple_mode(ctx, b, d_samples, arena_len, FEAT_MFCC_DELTA, d_out, nullptr);
+  if (rc) return rc;
+  SPB_CUDA(ctx, cudaMemcpyAsync(out, d_out, (size_t)b->total_frames * width * 4, cudaMemcpyDeviceToHost, ctx->stream));
+  SPB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  return SPB_OK;
+}
+
+int spb_lmfe_cmvnw_batch(spb_context *ctx, const spb_batch *b, const float *samples,
+                         int64_t arena_len, float *out) {
+  return host_batch(ctx, b, samples, arena_len, out, 0);
+}
+
+int spb_mfcc_delta_batch(spb_context *ctx, const spb_batch *b, const float *samples,
+                         int64_t arena_len, float *out) {
+  if (b && b->plan->p.num_cepstral < 1) return fail(ctx, SPB_ERR_INVALID, "mfcc_delta: plan has num_cepstral == 0");
+  return host_batch(ctx, b, samples, arena_len, out, 1);
+}
+
+}  // extern "C"

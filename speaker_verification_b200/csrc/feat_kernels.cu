@@ -1,0 +1,518 @@
+// K1/K2: fused framing -> real FFT -> |X|^2 -> mel -> log -> (DCT, c0, deltas).
+//
+// Replaces, per frame, the numpy pipeline of
+//   speech_feature_extraction/speechpy/processing.py:123-138 (frame gather)
+//   processing.py:158-159,174                              (rfft, |.|^2/NFFT)
+//   feature.py:202-217,256                                 (energy, mel, zero_handling, log)
+//   feature.py:146-152                                     (DCT-II ortho, c0 <- ln energy)
+//   processing.py:216-236 via feature.py:272-278           (delta cube, as written)
+//
+// Two kernels share the output stage:
+//   * features_fast512: NFFT = 512, 16 lanes per frame, 256-point complex FFT as
+//     16 x 16 register FFTs with one swizzled shared-memory exchange, real-FFT
+//     untangle through 16-lane shuffles; 32-frame tiles, persistent CTAs.
+//   * features_generic: any power-of-two NFFT in [32, 4096], one warp per frame,
+//     radix-2 in shared memory.  Used for NFFT != 512 and as an on-device cross-check.
+#include <math.h>
+
+#include "fft_math.cuh"
+#include "spb_internal.cuh"
+
+namespace spb {
+
+static constexpr float kEpsF64AsF32 = 2.220446049250313e-16f;  // functions.py:62
+
+struct FeatParams {
+  const float *samples;
+  const int64_t *starts;
+  const int32_t *nframes;
+  const int64_t *frame_offsets;
+  const int2 *tiles;
+  long long num_tiles;
+  int L, S, K;
+  int M, C, dc_elim;
+  const int32_t *band_lo, *band_n, *band_off;
+  const float *band_w;
+  int band_total;
+  const float *dct;
+  int mode;
+  float *out;
+  float *energy;
+  const float2 *twA;
+  const float2 *twB;
+  const float2 *tw;
+  int nfft, log2nc;
+  int need_energy;
+};
+
+// ------------------------------------------------------------------------------------
+// Output stage shared by both kernels.  s_p: [nf][pstride] UNSCALED |X|^2 rows (bins
+// 0..pbins-1), s_en: per-frame energy (already scaled, zero-handled) or unused.
+// Called by the whole CTA after a __syncthreads().  s_a / s_b: scratch of TILE*(41|..).
+// ------------------------------------------------------------------------------------
+template <int TILE>
+__device__ __forceinline__ void output_stage(const FeatParams &p, const float *s_p, int pstride,
+                                             const float *s_en, float *s_a, float *s_b,
+                                             const float *s_bw, const int *s_bmeta,
+                                             const float *s_dct, int nf, long long row0) {
+  const int tid = threadIdx.x;
+  const int nthreads = blockDim.x;
+  const float scale = 1.0f / (float)p.nfft;  // |X|^2 / NFFT  (processing.py:174)
+  if (p.mode == FEAT_POWER || p.mode == FEAT_MAG) {
+    // rows are contiguous in global memory: (row0 + f) * K + k
+    const int total = nf * p.K;
+    float *dst = p.out + row0 * p.K;
+    for (int i = tid; i < total; i += nthreads) {
+      int f = i / p.K, k = i - f * p.K;
+      float v = s_p[f * pstride + k];
+      dst[i] = (p.mode == FEAT_POWER) ? v * scale : sqrtf(v);
+    }
+    return;
+  }
+  const int M = p.M;
+  const int astride = M + 1;  // odd-ish padding: lane = frame accesses stay conflict-light
+  // mel energies: thread (frame = tid % TILE, filter slot = tid / TILE)
+  {
+    const int f = tid % TILE;
+    const int slot = tid / TILE;
+    const int nslots = nthreads / TILE;
+    if (f < nf) {
+      const float *prow = s_p + f * pstride;
+      for (int m = slot; m < M; m += nslots) {
+        const int lo = s_bmeta[m], n = s_bmeta[M + m], off = s_bmeta[2 * M + m];
+        float acc = 0.f;
+        for (int k = 0; k < n; ++k) acc = fmaf(s_bw[off + k], prow[lo + k], acc);
+        acc *= scale;
+        if (acc == 0.f) acc = kEpsF64AsF32;  // functions.zero_handling (feature.py:217)
+        s_a[f * astride + m] = (p.mode == FEAT_MFE) ? acc : __logf(acc);
+      }
+    }
+  }
+  __syncthreads();
+  if (p.mode == FEAT_MFE || p.mode == FEAT_LMFE) {
+    const int total = nf * M;
+    float *dst = p.out + row0 * M;
+    for (int i = tid; i < total; i += nthreads) {
+      int f = i / M, m = i - f * M;
+      dst[i] = s_a[f * astride + m];
+    }
+    if (p.mode == FEAT_MFE && p.energy != nullptr) {
+      for (int f = tid; f < nf; f += nthreads) p.energy[row0 + f] = s_en[f];
+    }
+    return;
+  }
+  // MFCC: DCT-II (ortho) of the log-mel row, first C coefficients (feature.py:147)
+  const int C = p.C;
+  const int cstride = C + ((C & 1) ? 0 : 1);
+  {
+    const int f = tid % TILE;
+    const int slot = tid / TILE;
+    const int nslots = nthreads / TILE;
+    if (f < nf) {
+      const float *lrow = s_a + f * astride;
+      for (int c = slot; c < C; c += nslots) {
+        const float *drow = s_dct + c * M;
+        float acc = 0.f;
+        for (int m = 0; m < M; ++m) acc = fmaf(drow[m], lrow[m], acc);
+        if (c == 0 && p.dc_elim) acc = __logf(s_en[f]);  // feature.py:151-152
+        s_b[f * cstride + c] = acc;
+      }
+    }
+  }
+  __syncthreads();
+  if (p.mode == FEAT_MFCC) {
+    const int total = nf * C;
+    float *dst = p.out + row0 * C;
+    for (int i = tid; i < total; i += nthreads) {
+      int f = i / C, c = i - f * C;
+      dst[i] = s_b[f * cstride + c];
+    }
+    return;
+  }
+  // FEAT_MFCC_DELTA: [x, D(x), D(D(x))] interleaved on a new last axis
+  // D(x)[c] = (x[min(c+1,C-1)] + 2 x[min(c+2,C-1)]) / 10   (processing.py:223-236 as written)
+  {
+    const int total = nf * C;
+    float *dst = p.out + row0 * C * 3;
+    for (int i = tid; i < total; i += nthreads) {
+      int f = i / C, c = i - f * C;
+      const float *x = s_b + f * cstride;
+      auto X = [&](int j) { return x[min(j, C - 1)]; };
+      auto D1 = [&](int j) {
+        j = min(j, C - 1);
+        return (X(j + 1) + 2.f * X(j + 2)) / 10.f;
+      };
+      float d0 = x[c];
+      float d1 = D1(c);
+      float d2 = (D1(c + 1) + 2.f * D1(c + 2)) / 10.f;
+      dst[i * 3 + 0] = d0;
+      dst[i * 3 + 1] = d1;
+      dst[i * 3 + 2] = d2;
+    }
+  }
+}
+
+__device__ __forceinline__ void load_plan_to_smem(const FeatParams &p, float *s_bw, int *s_bmeta,
+                                                  float *s_dct) {
+  if (p.mode < FEAT_MFE) return;
+  for (int i = threadIdx.x; i < p.band_total; i += blockDim.x) s_bw[i] = p.band_w[i];
+  for (int i = threadIdx.x; i < p.M; i += blockDim.x) {
+    s_bmeta[i] = p.band_lo[i];
+    s_bmeta[p.M + i] = p.band_n[i];
+    s_bmeta[2 * p.M + i] = p.band_off[i];
+  }
+  if (p.mode >= FEAT_MFCC)
+    for (int i = threadIdx.x; i < p.C * p.M; i += blockDim.x) s_dct[i] = p.dct[i];
+}
+
+// ====================================================================================
+// Fast kernel, NFFT = 512.
+// ====================================================================================
+constexpr int kTile = 32;        // frames per tile
+constexpr int kFastThreads = 256;
+
+template <int NJ, bool FULL>
+__global__ void __launch_bounds__(kFastThreads, 2)
+features_fast512(const FeatParams p) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  constexpr int PBINS = FULL ? 257 : 129;
+  constexpr int PSTRIDE = PBINS;  // == 1 (mod 32): lane = frame column walks are conflict-free
+  const int L = p.L, S = p.S;
+  const int span_max = (kTile - 1) * S + L;
+  // carve shared memory
+  float *s_x = reinterpret_cast<float *>(smem_raw);                 // [span_max (+pad)]
+  int off = ((span_max + 3) & ~3);
+  float2 *s_exch = reinterpret_cast<float2 *>(s_x + off);           // 16 half-warps x 256
+  float *s_p = reinterpret_cast<float *>(s_exch + 16 * 256);        // [kTile][PSTRIDE]
+  float *s_en = s_p + kTile * PSTRIDE;                              // [kTile]
+  float *s_a = s_en + kTile;                                        // [kTile][M+1]
+  float *s_b = s_a + kTile * (p.M + 1);                             // [kTile][C+1]
+  float *s_bw = s_b + kTile * (p.C + 1);                            // [band_total]
+  float *s_dct = s_bw + p.band_total;                               // [C*M]
+  int *s_bmeta = reinterpret_cast<int *>(s_dct + p.C * p.M);        // [3M]
+
+  const int tid = threadIdx.x;
+  const int warp = tid >> 5;
+  const int lane = tid & 31;
+  const int half = lane >> 4;
+  const int l16 = lane & 15;
+  const int hw = warp * 2 + half;  // half-warp id 0..15
+  float2 *my_exch = s_exch + hw * 256;
+
+  load_plan_to_smem(p, s_bw, s_bmeta, s_dct);
+
+  // per-lane twiddles (fixed for the whole kernel)
+  float2 twA[16];  // W256^(l16*k1)
+#pragma unroll
+  for (int k1 = 0; k1 < 16; ++k1) twA[k1] = p.twA[l16 * 16 + k1];
+  float2 twB[8];   // W512^(l16 + 16*k2)
+#pragma unroll
+  for (int k2 = 0; k2 < 8; ++k2) twB[k2] = p.twB[l16 * 9 + k2];
+  const int partner = (16 - l16) & 15;
+  const int nz_complex = (min(L, 512) + 1) >> 1;  // complex inputs that can be non-zero
+  const int Leff = min(L, 512);
+
+  for (long long tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x) {
+    const int2 td = p.tiles[tile];
+    const int utt = td.x, f0 = td.y;
+    const int nf = min(kTile, p.nframes[utt] - f0);
+    const long long gstart = p.starts[utt] + (long long)f0 * S;
+    const int count = (nf - 1) * S + L;
+    const float *src = p.samples + gstart;
+    __syncthreads();  // previous tile's readers of s_x / s_p are done
+    // ---- phase A: stage the tile's samples (each sample is used by L/S frames)
+    if ((gstart & 3) == 0) {
+      const float4 *src4 = reinterpret_cast<const float4 *>(src);
+      float4 *dst4 = reinterpret_cast<float4 *>(s_x);
+      const int n4 = count >> 2;
+      for (int i = tid; i < n4; i += kFastThreads) dst4[i] = __ldg(src4 + i);
+      for (int i = (n4 << 2) + tid; i < count; i += kFastThreads) s_x[i] = __ldg(src + i);
+    } else {
+      for (int i = tid; i < count; i += kFastThreads) s_x[i] = __ldg(src + i);
+    }
+    __syncthreads();
+
+    // ---- phase B: two frames per half-warp
+#pragma unroll 1
+    for (int pass = 0; pass < 2; ++pass) {
+      const int fl = 2 * (warp + 8 * half) + pass;
+      const bool active = fl < nf;
+      const float *xf = s_x + (active ? fl : 0) * S;
+      float2 v[16];
+      // z[m] = x[2m] + i x[2m+1], m = 16 j + l16
+      if (NJ < 16) {
+        // compile-time pruned: every lane has exactly NJ non-zero inputs, S even, L == 32*NJ
+#pragma unroll
+        for (int j = 0; j < 16; ++j) {
+          if (j < NJ) v[j] = *reinterpret_cast<const float2 *>(xf + 32 * j + 2 * l16);
+          else v[j] = c_make(0.f, 0.f);
+        }
+      } else {
+#pragma unroll
+        for (int j = 0; j < 16; ++j) {
+          const int m = 16 * j + l16;
+          float re = (2 * m < Leff) ? xf[2 * m] : 0.f;
+          float im = (2 * m + 1 < Leff) ? xf[2 * m + 1] : 0.f;
+          v[j] = c_make(re, im);
+        }
+      }
+      float sumsq = 0.f;
+      if (p.need_energy) {
+#pragma unroll
+        for (int j = 0; j < 16; ++j)
+          if (j < NJ) sumsq = fmaf(v[j].x, v[j].x, fmaf(v[j].y, v[j].y, sumsq));
+      }
+      // step 1: FFT16 over j  -> index k1, then twiddle W256^(l16*k1)
+      fft16<NJ>(v);
+#pragma unroll
+      for (int k1 = 1; k1 < 16; ++k1) v[k1] = c_mul(v[k1], twA[k1]);
+      __syncwarp();  // previous pass's step-2 loads are complete
+#pragma unroll
+      for (int k1 = 0; k1 < 16; ++k1) my_exch[exch_store_index(k1, l16)] = v[k1];
+      __syncwarp();
+      // step 2: lane = k1 gathers n2 = 0..15
+#pragma unroll
+      for (int c = 0; c < 8; ++c) {
+        const float4 q = *reinterpret_cast<const float4 *>(my_exch + exch_load_chunk_index(l16, c));
+        v[2 * c] = c_make(q.x, q.y);
+        v[2 * c + 1] = c_make(q.z, q.w);
+      }
+      fft16<16>(v);  // v[k2] = Z[l16 + 16 k2]
+      // untangle: partner value Z[256 - k] lives in lane (16 - l16) & 15
+      float *prow = s_p + fl * PSTRIDE;
+#pragma unroll
+      for (int k2 = 0; k2 < 8; ++k2) {
+        // sender slot t = 7 - k2: generic lanes send v[8 + t], lane 0 sends v[(9 + t) & 15]
+        const int t = 7 - k2;
+        const float2 snd = (l16 == 0) ? v[(9 + t) & 15] : v[8 + t];
+        float2 zp;
+        zp.x = __shfl_sync(0xffffffffu, snd.x, partner, 16);
+        zp.y = __shfl_sync(0xffffffffu, snd.y, partner, 16);
+        const float2 zk = v[k2];
+        const float2 A = c_make(zk.x + zp.x, zk.y - zp.y);
+        const float2 B = c_make(zk.y + zp.y, zp.x - zk.x);
+        const float2 WB = c_mul(B, twB[k2]);
+        const float xr = A.x + WB.x, xi = A.y + WB.y;
+        const float pk = 0.25f * fmaf(xr, xr, xi * xi);
+        if (active) prow[l16 + 16 * k2] = pk;
+        if (FULL) {
+          const float yr = A.x - WB.x, yi = A.y - WB.y;
+          const float pm = 0.25f * fmaf(yr, yr, yi * yi);
+          if (active) prow[256 - (l16 + 16 * k2)] = pm;  // k = 0 writes bin 256
+        }
+      }
+      if (l16 == 0) {
+        // bin 128 = Z[128] (its own partner): X = Zr - i Zi  -> |Z|^2
+        const float2 z = v[8];
+        if (active) prow[128] = fmaf(z.x, z.x, z.y * z.y);
+      }
+      if (p.need_energy) {
+        // frame energy = sum_k P[k], all 257 one-sided bins (feature.py:202), via Parseval:
+        // (NFFT*sum x^2 + X0^2 + X256^2) / (2*NFFT), X0 = Zr+Zi, X256 = Zr-Zi of Z[0]
+#pragma unroll
+        for (int o = 8; o >= 1; o >>= 1) sumsq += __shfl_xor_sync(0xffffffffu, sumsq, o, 16);
+        if (l16 == 0 && active) {
+          const float x0 = v[0].x + v[0].y, x256 = v[0].x - v[0].y;
+          float e = (512.f * sumsq + x0 * x0 + x256 * x256) * (1.0f / (2.f * 512.f));
+          if (e == 0.f) e = kEpsF64AsF32;  // feature.py:205
+          s_en[fl] = e;
+        }
+      }
+    }
+    __syncthreads();
+    // ---- phase C
+    const long long row0 = p.frame_offsets[utt] + f0;
+    output_stage<kTile>(p, s_p, PSTRIDE, s_en, s_a, s_b, s_bw, s_bmeta, s_dct, nf, row0);
+  }
+}
+
+// ====================================================================================
+// Generic kernel: one warp per frame, radix-2 DIT on NFFT/2 complex points in smem.
+// ====================================================================================
+constexpr int kGenWarps = 4;
+constexpr int kGenTile = kGenWarps;  // frames per CTA iteration
+
+__global__ void __launch_bounds__(kGenWarps * 32)
+features_generic(const FeatParams p) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  const int nc = p.nfft >> 1;
+  const int K = p.K;
+  const int pstride = K | 1;
+  float2 *s_z = reinterpret_cast<float2 *>(smem_raw);      // [kGenWarps][nc]
+  float *s_p = reinterpret_cast<float *>(s_z + kGenWarps * nc);  // [kGenTile][pstride]
+  float *s_en = s_p + kGenTile * pstride;
+  float *s_a = s_en + kGenTile;
+  float *s_b = s_a + kGenTile * (p.M + 1);
+  float *s_bw = s_b + kGenTile * (p.C + 1);
+  float *s_dct = s_bw + p.band_total;
+  int *s_bmeta = reinterpret_cast<int *>(s_dct + p.C * p.M);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  load_plan_to_smem(p, s_bw, s_bmeta, s_dct);
+  const int Leff = min(p.L, p.nfft);
+  float2 *z = s_z + warp * nc;
+
+  // tiles here are the same 32-frame tiles as the fast kernel; walk them kGenTile frames at a time
+  for (long long tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x) {
+    const int2 td = p.tiles[tile];
+    const int utt = td.x;
+    const int nf_tile = min(kTile, p.nframes[utt] - td.y);
+    for (int fsub = 0; fsub < nf_tile; fsub += kGenTile) {
+      const int f0 = td.y + fsub;
+      const int nf = min(kGenTile, nf_tile - fsub);
+      __syncthreads();
+      if (warp < nf) {
+        const float *x = p.samples + p.starts[utt] + (long long)(f0 + warp) * p.S;
+        // bit-reversed load of z[m] = x[2m] + i x[2m+1]
+        float sumsq = 0.f;
+        for (int m = lane; m < nc; m += 32) {
+          float re = (2 * m < Leff) ? __ldg(x + 2 * m) : 0.f;
+          float im = (2 * m + 1 < Leff) ? __ldg(x + 2 * m + 1) : 0.f;
+          sumsq = fmaf(re, re, fmaf(im, im, sumsq));
+          const int r = __brev((unsigned)m) >> (32 - p.log2nc);
+          z[r] = c_make(re, im);
+        }
+        __syncwarp();
+        for (int s = 0; s < p.log2nc; ++s) {
+          const int hlf = 1 << s;
+          const int tw_step = (p.nfft >> 1) >> s;  // W_{2*hlf}^pos = tw[pos * nfft/(2*hlf)]
+          for (int b = lane; b < (nc >> 1); b += 32) {
+            const int pos = b & (hlf - 1);
+            const int i = ((b >> s) << (s + 1)) + pos;
+            const int j = i + hlf;
+            const float2 w = p.tw[pos * tw_step];
+            const float2 u = z[i];
+            const float2 t = c_mul(z[j], w);
+            z[i] = c_add(u, t);
+            z[j] = c_sub(u, t);
+          }
+          __syncwarp();
+        }
+        // untangle: X[k] = E + W^k O ; bins 0..nc
+        float *prow = s_p + warp * pstride;
+        for (int k = lane; k <= (nc >> 1); k += 32) {
+          const float2 zk = z[k];
+          const float2 zp = z[(nc - k) & (nc - 1)];
+          const float2 A = c_make(zk.x + zp.x, zk.y - zp.y);
+          const float2 B = c_make(zk.y + zp.y, zp.x - zk.x);
+          const float2 w = p.tw[k];
+          const float2 WB = c_mul(B, w);
+          const float xr = A.x + WB.x, xi = A.y + WB.y;
+          const float yr = A.x - WB.x, yi = A.y - WB.y;
+          prow[k] = 0.25f * fmaf(xr, xr, xi * xi);
+          prow[nc - k] = 0.25f * fmaf(yr, yr, yi * yi);
+        }
+        if (p.need_energy) {
+          for (int o = 16; o >= 1; o >>= 1) sumsq += __shfl_xor_sync(0xffffffffu, sumsq, o);
+          if (lane == 0) {
+            const float x0 = z[0].x + z[0].y, xn = z[0].x - z[0].y;
+            const float nf_ = (float)p.nfft;
+            float e = (nf_ * sumsq + x0 * x0 + xn * xn) / (2.f * nf_);
+            if (e == 0.f) e = kEpsF64AsF32;
+            s_en[warp] = e;
+          }
+        }
+      }
+      __syncthreads();
+      const long long row0 = p.frame_offsets[utt] + f0;
+      output_stage<kGenTile>(p, s_p, pstride, s_en, s_a, s_b, s_bw, s_bmeta, s_dct, nf, row0);
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------
+static FeatParams make_params(const FeatArgs &a, const FftTables &t) {
+  FeatParams p;
+  p.samples = a.samples;
+  p.starts = a.starts;
+  p.nframes = a.nframes;
+  p.frame_offsets = a.frame_offsets;
+  p.tiles = a.tiles;
+  p.num_tiles = a.num_tiles;
+  p.L = a.L; p.S = a.S; p.K = a.K;
+  p.M = a.M; p.C = a.C; p.dc_elim = a.dc_elim;
+  p.band_lo = a.band_lo; p.band_n = a.band_n; p.band_off = a.band_off;
+  p.band_w = a.band_w; p.band_total = a.band_total;
+  p.dct = a.dct;
+  p.mode = a.mode;
+  p.out = a.out;
+  p.energy = a.energy;
+  p.twA = t.d_twA; p.twB = t.d_twB; p.tw = t.d_tw;
+  p.nfft = a.nfft;
+  int lg = 0;
+  while ((1 << lg) < (a.nfft >> 1)) ++lg;
+  p.log2nc = lg;
+  p.need_energy = (a.mode == FEAT_MFE && a.energy != nullptr) ||
+                  (a.mode >= FEAT_MFCC && a.dc_elim);
+  return p;
+}
+
+static size_t plan_smem_bytes(const FeatArgs &a, int tile) {
+  size_t floats = (size_t)tile                                   // s_en
+                  + (size_t)tile * (a.M + 1) + (size_t)tile * (a.C + 1)
+                  + (size_t)a.band_total + (size_t)a.C * a.M + 3 * (size_t)a.M;
+  return floats * 4;
+}
+
+bool fast512_supported(const FeatArgs &a) {
+  if (a.nfft != 512) return false;
+  if (a.tile_frames != kTile) return false;
+  if (a.L < 1 || a.S < 1) return false;
+  size_t span = (size_t)(kTile - 1) * a.S + a.L;
+  if (span * 4 > 96 * 1024) return false;  // absurd strides: let the generic kernel take it
+  return true;
+}
+
+template <int NJ, bool FULL>
+static int launch_fast(spb_context *ctx, const FeatParams &p, const FeatArgs &a) {
+  const int span_max = (kTile - 1) * a.S + a.L;
+  size_t smem = (size_t)((span_max + 3) & ~3) * 4 + 16 * 256 * sizeof(float2) +
+                (size_t)kTile * (FULL ? 257 : 129) * 4 + plan_smem_bytes(a, kTile);
+  auto kern = features_fast512<NJ, FULL>;
+  SPB_CUDA(ctx, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  int per_sm = 0;
+  SPB_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, kFastThreads, smem));
+  if (per_sm < 1) return fail(ctx, SPB_ERR_INVALID, "fast512: kernel does not fit on an SM");
+  long long grid = (long long)ctx->sm_count * per_sm;
+  if (grid > a.num_tiles) grid = a.num_tiles;
+  if (grid < 1) return SPB_OK;
+  kern<<<(unsigned)grid, kFastThreads, smem, ctx->stream>>>(p);
+  SPB_LAUNCH_CHECK(ctx, "features_fast512");
+  return SPB_OK;
+}
+
+int launch_features_fast512(spb_context *ctx, const FeatArgs &a, const FftTables &t) {
+  FeatParams p = make_params(a, t);
+  // FULL spectrum is needed for power/magnitude output; feature modes only read the
+  // bins the filterbank touches (speechpy's (K+1) bin mapping never exceeds bin 128,
+  // a custom bank that does selects the FULL variant).
+  const bool full = (a.mode == FEAT_POWER || a.mode == FEAT_MAG) || a.max_bin > 128;
+  const FeatArgs &aa = a;
+  const bool pruned320 = (a.L == 320 && (a.S % 2 == 0));
+  if (full) {
+    return pruned320 ? launch_fast<10, true>(ctx, p, aa) : launch_fast<16, true>(ctx, p, aa);
+  }
+  return pruned320 ? launch_fast<10, false>(ctx, p, aa) : launch_fast<16, false>(ctx, p, aa);
+}
+
+int launch_features_generic(spb_context *ctx, const FeatArgs &a, const FftTables &t) {
+  FeatParams p = make_params(a, t);
+  const FeatArgs &aa = a;
+  const int nc = a.nfft >> 1;
+  size_t smem = (size_t)kGenWarps * nc * sizeof(float2) + (size_t)kGenTile * (a.K | 1) * 4 +
+                plan_smem_bytes(aa, kGenTile);
+  SPB_CUDA(ctx, cudaFuncSetAttribute(features_generic,
+                                     cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  int per_sm = 0;
+  SPB_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, features_generic,
+                                                              kGenWarps * 32, smem));
+  if (per_sm < 1) return fail(ctx, SPB_ERR_INVALID, "generic fft kernel does not fit on an SM");
+  long long grid = (long long)ctx->sm_count * per_sm;
+  if (grid > a.num_tiles) grid = a.num_tiles;
+  if (grid < 1) return SPB_OK;
+  features_generic<<<(unsigned)grid, kGenWarps * 32, smem, ctx->stream>>>(p);
+  SPB_LAUNCH_CHECK(ctx, "features_generic");
+  return SPB_OK;
+}
+
+}  // namespace spb

@@ -1,0 +1,151 @@
+// Small element-wise kernels: float64 frame gather (stack_frames), the reference's
+// "derivative" operator and delta cube, dtype conversion, tile-table construction.
+#include "spb_internal.cuh"
+
+namespace spb {
+
+// speech_feature_extraction/speechpy/processing.py:123-138: frames = signal[idx] * window,
+// idx[f, j] = j + f*S.  Samples at or beyond N are the zero padding of processing.py:108-110.
+__global__ void stack_frames_kernel(const double *__restrict__ sig, long long n, int L, int S,
+                                    const double *__restrict__ window, long long total,
+                                    double *__restrict__ out) {
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const long long f = i / L;
+    const int j = (int)(i - f * L);
+    const long long idx = f * S + j;
+    double v = (idx < n) ? sig[idx] : 0.0;
+    if (window) v *= window[j];
+    out[i] = v;
+  }
+}
+
+int launch_stack_frames_f64(spb_context *ctx, const double *sig, int64_t n, int L, int S,
+                            const double *window, int64_t F, double *out) {
+  const long long total = (long long)F * L;
+  if (total <= 0) return SPB_OK;
+  long long blocks = (total + 255) / 256;
+  if (blocks > (long long)ctx->sm_count * 16) blocks = (long long)ctx->sm_count * 16;
+  stack_frames_kernel<<<(unsigned)blocks, 256, 0, ctx->stream>>>(sig, n, L, S, window, total, out);
+  SPB_LAUNCH_CHECK(ctx, "stack_frames_kernel");
+  return SPB_OK;
+}
+
+// processing.py:216-236 as written: DIF[f, c] = sum_{r=1..D} r * x[f, min(c + r, cols-1)],
+// divided by 2 * sum r^2 (the subtraction on processing.py:232 is a no-op statement).
+__device__ __forceinline__ double deriv_at(const double *row, int c, int cols, int dw, double inv) {
+  double acc = 0.0;
+  for (int r = 1; r <= dw; ++r) acc += (double)r * row[min(c + r, cols - 1)];
+  return acc * inv;
+}
+
+__global__ void derivative_kernel(const double *__restrict__ in, long long rows, int cols, int dw,
+                                  double scale, double *__restrict__ out) {
+  const long long total = rows * cols;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const long long f = i / cols;
+    const int c = (int)(i - f * cols);
+    const double *row = in + f * cols;
+    double acc = 0.0;
+    for (int r = 1; r <= dw; ++r) acc += (double)r * row[min(c + r, cols - 1)];
+    out[i] = acc / scale;
+  }
+}
+
+int launch_derivative_f64(spb_context *ctx, const double *in, int64_t rows, int cols, int dw,
+                          double *out) {
+  const long long total = (long long)rows * cols;
+  if (total <= 0) return SPB_OK;
+  double scale = 0.0;
+  for (int r = 1; r <= dw; ++r) scale += 2.0 * r * r;
+  long long blocks = (total + 255) / 256;
+  if (blocks > (long long)ctx->sm_count * 16) blocks = (long long)ctx->sm_count * 16;
+  derivative_kernel<<<(unsigned)blocks, 256, 0, ctx->stream>>>(in, rows, cols, dw, scale, out);
+  SPB_LAUNCH_CHECK(ctx, "derivative_kernel");
+  return SPB_OK;
+}
+
+// feature.py:272-278: cube[f, c, :] = [x, D(x), D(D(x))], DeltaWindows = 2 (scale 10).
+__global__ void delta_cube_kernel(const double *__restrict__ in, long long rows, int cols,
+                                  double *__restrict__ out) {
+  const long long total = rows * cols;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const long long f = i / cols;
+    const int c = (int)(i - f * cols);
+    const double *row = in + f * cols;
+    auto X = [&](int j) { return row[min(j, cols - 1)]; };
+    auto D1 = [&](int j) {
+      j = min(j, cols - 1);
+      return (X(j + 1) + 2.0 * X(j + 2)) / 10.0;
+    };
+    out[i * 3 + 0] = row[c];
+    out[i * 3 + 1] = D1(c);
+    out[i * 3 + 2] = (D1(c + 1) + 2.0 * D1(c + 2)) / 10.0;
+  }
+}
+
+int launch_delta_cube_f64(spb_context *ctx, const double *in, int64_t rows, int cols,
+                          double *out) {
+  const long long total = (long long)rows * cols;
+  if (total <= 0) return SPB_OK;
+  long long blocks = (total + 255) / 256;
+  if (blocks > (long long)ctx->sm_count * 16) blocks = (long long)ctx->sm_count * 16;
+  delta_cube_kernel<<<(unsigned)blocks, 256, 0, ctx->stream>>>(in, rows, cols, out);
+  SPB_LAUNCH_CHECK(ctx, "delta_cube_kernel");
+  return SPB_OK;
+}
+
+// ------------------------------------------------------------------ conversions
+template <typename TI, typename TO>
+__global__ void convert_kernel(const TI *__restrict__ in, TO *__restrict__ out, long long n) {
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n;
+       i += (long long)gridDim.x * blockDim.x)
+    out[i] = (TO)in[i];
+}
+
+int launch_convert(spb_context *ctx, const void *in, int dtype_in, void *out, int dtype_out,
+                   int64_t n) {
+  if (n <= 0) return SPB_OK;
+  long long blocks = (n + 255) / 256;
+  if (blocks > (long long)ctx->sm_count * 16) blocks = (long long)ctx->sm_count * 16;
+  const unsigned g = (unsigned)blocks;
+#define SPB_CVT(TI, TO) \
+  convert_kernel<TI, TO><<<g, 256, 0, ctx->stream>>>((const TI *)in, (TO *)out, n)
+  if (dtype_in == SPB_F64 && dtype_out == SPB_F32) SPB_CVT(double, float);
+  else if (dtype_in == SPB_F32 && dtype_out == SPB_F64) SPB_CVT(float, double);
+  else if (dtype_in == SPB_I16 && dtype_out == SPB_F32) SPB_CVT(int16_t, float);
+  else if (dtype_in == SPB_I32 && dtype_out == SPB_F32) SPB_CVT(int32_t, float);
+  else if (dtype_in == SPB_F32 && dtype_out == SPB_F32) SPB_CVT(float, float);
+  else return fail(ctx, SPB_ERR_INVALID, "unsupported dtype conversion");
+#undef SPB_CVT
+  SPB_LAUNCH_CHECK(ctx, "convert_kernel");
+  return SPB_OK;
+}
+
+// ------------------------------------------------------------------ tile tables
+// tiles[tile_offsets[u] + t] = {u, t * tile} for t < ceil(nframes[u] / tile)
+__global__ void build_tiles_kernel(const int32_t *__restrict__ nframes,
+                                   const int64_t *__restrict__ tile_offsets, long long U, int tile,
+                                   int2 *__restrict__ tiles) {
+  // one warp per utterance
+  const long long w = (blockIdx.x * (long long)blockDim.x + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
+  if (w >= U) return;
+  const int nt = (nframes[w] + tile - 1) / tile;
+  const long long base = tile_offsets[w];
+  for (int t = lane; t < nt; t += 32) tiles[base + t] = make_int2((int)w, t * tile);
+}
+
+int launch_build_tiles(spb_context *ctx, const int32_t *nframes, const int64_t *tile_offsets,
+                       int64_t U, int tile, int2 *tiles) {
+  if (U <= 0) return SPB_OK;
+  const long long threads = U * 32;
+  const unsigned blocks = (unsigned)((threads + 255) / 256);
+  build_tiles_kernel<<<blocks, 256, 0, ctx->stream>>>(nframes, tile_offsets, U, tile, tiles);
+  SPB_LAUNCH_CHECK(ctx, "build_tiles_kernel");
+  return SPB_OK;
+}
+
+}  // namespace spb

@@ -1,0 +1,172 @@
+// Internal declarations shared by the kernels and the C-ABI layer.
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include <map>
+#include <string>
+#include <vector>
+
+#include "speechpy_b200.h"
+
+namespace spb {
+
+// ---------------------------------------------------------------- errors
+void set_global_error(const std::string &msg);
+
+struct DeviceBuffer {
+  void *ptr = nullptr;
+  size_t bytes = 0;
+};
+
+struct FftTables {
+  // generic kernel: tw[k] = exp(-2*pi*i*k/nfft), k < nfft/2
+  float2 *d_tw = nullptr;
+  // fast 512 kernel: twA[l*16+k1] = W256^(l*k1); twB[k1*9+k2] = W512^(k1+16*k2)
+  float2 *d_twA = nullptr;
+  float2 *d_twB = nullptr;
+};
+
+}  // namespace spb
+
+struct spb_context {
+  int device = 0;
+  cudaStream_t stream = nullptr;
+  cudaStream_t copy_stream = nullptr;
+  cudaEvent_t ev_a = nullptr, ev_b = nullptr;
+  int sm_count = 0, cc_major = 0, cc_minor = 0;
+  size_t total_mem = 0;
+  uint64_t launches = 0;
+  std::string last_error;
+  // grow-only device scratch, keyed by role
+  spb::DeviceBuffer scratch[8];
+  // pinned staging (two halves for double buffering)
+  void *pinned[2] = {nullptr, nullptr};
+  size_t pinned_bytes = 0;
+  std::map<int, spb::FftTables> fft_tables;  // by nfft
+  std::vector<spb_plan *> plans;
+};
+
+struct spb_plan {
+  spb_context *ctx = nullptr;
+  spb_feature_params p{};
+  int K = 0;  // nfft/2+1
+  // band-compressed filterbank (float32 on device)
+  int32_t *d_band_lo = nullptr;   // [M] first bin with non-zero weight
+  int32_t *d_band_n = nullptr;    // [M] number of bins in the band
+  int32_t *d_band_off = nullptr;  // [M] offset into d_band_w
+  float *d_band_w = nullptr;      // [sum band_n]
+  int band_total = 0;
+  int max_bin = -1;               // largest bin index carrying weight
+  float *d_dct = nullptr;         // [C][M] orthonormal DCT-II rows
+  std::vector<int32_t> h_band_lo, h_band_n, h_band_off;
+};
+
+namespace spb {
+// a run of whole utterances whose intermediates fit in L2
+struct BatchChunk {
+  int64_t u0, u1;        // utterances [u0, u1)
+  int64_t tile0, tile1;  // fft tiles
+  int64_t cm0, cm1;      // cmvnw tiles
+  int64_t row0, row1;    // output rows
+};
+}  // namespace spb
+
+struct spb_batch {
+  spb_context *ctx = nullptr;
+  const spb_plan *plan = nullptr;
+  int64_t U = 0;
+  int64_t total_frames = 0;
+  int64_t total_tiles = 0;       // fft tiles
+  int64_t total_cm_tiles = 0;    // cmvnw tiles
+  int tile_frames = 0;
+  int cm_tile_rows = 0;
+  std::vector<int64_t> h_frame_offsets;  // [U+1]
+  int64_t max_end = 0;                   // max(starts+lengths): arena must be at least this long
+  int64_t *d_starts = nullptr;           // [U]
+  int32_t *d_nframes = nullptr;          // [U]
+  int64_t *d_frame_offsets = nullptr;    // [U+1]
+  int2 *d_tiles = nullptr;               // [total_tiles] {utt, first frame}
+  int2 *d_cm_tiles = nullptr;            // [total_cm_tiles] {utt, first row}
+  std::vector<spb::BatchChunk> chunks;
+  int64_t max_chunk_rows = 0;
+};
+
+namespace spb {
+
+int fail(spb_context *ctx, int code, const std::string &msg);
+int cuda_fail(spb_context *ctx, cudaError_t e, const char *what);
+// returns device pointer of at least `bytes` (grow-only), or nullptr (error set)
+void *scratch(spb_context *ctx, int slot, size_t bytes);
+int get_fft_tables(spb_context *ctx, int nfft, FftTables *out);
+
+#define SPB_CUDA(ctx, call)                                        \
+  do {                                                             \
+    cudaError_t e__ = (call);                                      \
+    if (e__ != cudaSuccess) return spb::cuda_fail(ctx, e__, #call); \
+  } while (0)
+
+#define SPB_LAUNCH_CHECK(ctx, name)                                  \
+  do {                                                               \
+    (ctx)->launches++;                                               \
+    cudaError_t e__ = cudaGetLastError();                            \
+    if (e__ != cudaSuccess) return spb::cuda_fail(ctx, e__, name);   \
+  } while (0)
+
+// ------------------------------------------------------------ kernel entry points
+enum FeatMode { FEAT_POWER = 0, FEAT_MAG = 1, FEAT_MFE = 2, FEAT_LMFE = 3, FEAT_MFCC = 4,
+                FEAT_MFCC_DELTA = 5 };
+
+struct FeatArgs {
+  const float *samples;      // arena
+  int64_t arena_len;
+  const int64_t *starts;     // [U]
+  const int32_t *nframes;    // [U]
+  const int64_t *frame_offsets;  // [U+1]
+  const int2 *tiles;         // [num_tiles]
+  int64_t num_tiles;
+  int tile_frames;
+  int L, S, nfft, K;
+  int M, C, dc_elim;
+  const int32_t *band_lo, *band_n, *band_off;
+  const float *band_w;
+  int band_total;
+  int max_bin;               // largest bin with non-zero weight
+  const float *dct;          // [C][M]
+  int mode;
+  float *out;                // power/mag: [frames][K]; mfe/lmfe: [frames][M]; mfcc: [frames][C]; delta: [frames][C][3]
+  float *energy;             // [frames] or nullptr (mfe only)
+};
+
+int launch_features_generic(spb_context *ctx, const FeatArgs &a, const FftTables &t);
+bool fast512_supported(const FeatArgs &a);
+int launch_features_fast512(spb_context *ctx, const FeatArgs &a, const FftTables &t);
+
+int launch_cmvnw_f32(spb_context *ctx, const float *in, float *scratch_ms, float *out,
+                     const int32_t *nframes, const int64_t *frame_offsets, const int2 *tiles,
+                     int64_t num_tiles, int tile_rows, int cols, int ld, int win, int varnorm);
+int cmvnw_tile_rows(int cols, int win);
+bool cmvnw_supported(int cols, int win);
+int launch_cmvn_f64(spb_context *ctx, const double *in, int64_t rows, int cols, int varnorm,
+                    double *out);
+int launch_stack_frames_f64(spb_context *ctx, const double *sig, int64_t n, int L, int S,
+                            const double *window, int64_t F, double *out);
+int launch_derivative_f64(spb_context *ctx, const double *in, int64_t rows, int cols, int dw,
+                          double *out);
+int launch_delta_cube_f64(spb_context *ctx, const double *in, int64_t rows, int cols,
+                          double *out);
+int launch_convert(spb_context *ctx, const void *in, int dtype_in, void *out, int dtype_out,
+                   int64_t n);
+int launch_build_tiles(spb_context *ctx, const int32_t *nframes, const int64_t *tile_offsets,
+                       int64_t U, int tile, int2 *tiles);
+
+int launch_cosine_scores(spb_context *ctx, const float *d_E, int64_t m, const float *d_T,
+                         int64_t n, int d, float *d_S);
+int launch_trial_gather(spb_context *ctx, const float *d_S, int64_t m, int64_t n,
+                        const int32_t *ti, const int32_t *tj, int64_t nt, float *out);
+int launch_argmax_rows(spb_context *ctx, const float *d_S, int64_t m, int64_t n, int32_t *out);
+int run_eer(spb_context *ctx, const float *d_scores, const int32_t *d_labels, int64_t n,
+            double *eer, double *auc);
+
+}  // namespace spb
