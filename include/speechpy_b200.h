@@ -73,6 +73,12 @@ SPB_API int spb_device_info(spb_context *ctx, int32_t *sm_count, int32_t *cc_maj
                     int32_t *cc_minor, uint64_t *total_mem);
 /* Number of kernels this context has launched so far (bench.py's gpu_launches). */
 SPB_API int spb_launch_count(spb_context *ctx, uint64_t *count);
+/* Per-kernel device timing: when enabled, every launch of the three hot kernels is
+ * bracketed by CUDA events on the context's stream.  spb_timing_read synchronises,
+ * sums the elapsed times recorded since the last read and clears them.
+ * kernel: 0 = features (framing+FFT+mel+log), 1 = cmvnw stage 1, 2 = cmvnw stage 2. */
+SPB_API int spb_timing_enable(spb_context *ctx, int32_t on);
+SPB_API int spb_timing_read(spb_context *ctx, int32_t kernel, double *total_ms, uint64_t *launches);
 /* Pinned host memory, so callers can hand page-locked buffers to the host API. */
 SPB_API int spb_host_alloc(void **ptr, size_t bytes);
 SPB_API int spb_host_free(void *ptr);

@@ -37,6 +37,8 @@ PROTOTYPES = {
     "spb_stream": (C.c_int, [c_vp, C.POINTER(c_u64)]),
     "spb_device_info": (C.c_int, [c_vp, C.POINTER(c_i32), C.POINTER(c_i32), C.POINTER(c_i32), C.POINTER(c_u64)]),
     "spb_launch_count": (C.c_int, [c_vp, C.POINTER(c_u64)]),
+    "spb_timing_enable": (C.c_int, [c_vp, c_i32]),
+    "spb_timing_read": (C.c_int, [c_vp, c_i32, C.POINTER(C.c_double), C.POINTER(c_u64)]),
     "spb_host_alloc": (C.c_int, [C.POINTER(c_vp), C.c_size_t]),
     "spb_host_free": (C.c_int, [c_vp]),
     "spb_num_frames": (C.c_int, [c_i64, c_i32, c_i32, c_i32, C.POINTER(c_i64)]),
@@ -69,7 +71,7 @@ PROTOTYPES = {
 }
 
 _lib = None
-_lock = threading.Lock()
+_lock = threading.RLock()
 _contexts: dict = {}
 
 
@@ -155,6 +157,14 @@ class Context:
         n = c_u64()
         check(self.lib.spb_launch_count(self.handle, C.byref(n)), self.handle)
         return n.value
+
+    def timing_enable(self, on: bool):
+        check(self.lib.spb_timing_enable(self.handle, 1 if on else 0), self.handle)
+
+    def timing_read(self, kernel: int):
+        ms, n = C.c_double(), c_u64()
+        check(self.lib.spb_timing_read(self.handle, kernel, C.byref(ms), C.byref(n)), self.handle)
+        return ms.value, n.value
 
     def stream(self) -> int:
         s = c_u64()

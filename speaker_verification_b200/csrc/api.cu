@@ -46,6 +46,28 @@ void *scratch(spb_context *ctx, int slot, size_t bytes) {
   return b.ptr;
 }
 
+static size_t timing_event(spb_context *ctx) {
+  if (ctx->ev_used == ctx->ev_pool.size()) {
+    cudaEvent_t e;
+    if (cudaEventCreate(&e) != cudaSuccess) return (size_t)-1;
+    ctx->ev_pool.push_back(e);
+  }
+  const size_t i = ctx->ev_used++;
+  cudaEventRecord(ctx->ev_pool[i], ctx->stream);
+  return i;
+}
+
+size_t timing_begin(spb_context *ctx) {
+  if (!ctx->timing) return (size_t)-1;
+  return timing_event(ctx);
+}
+
+void timing_end(spb_context *ctx, int kernel, size_t begin_idx) {
+  if (!ctx->timing || begin_idx == (size_t)-1) return;
+  const size_t e = timing_event(ctx);
+  if (e != (size_t)-1) ctx->ev_pairs[kernel].push_back({begin_idx, e});
+}
+
 static bool is_pow2(int v) { return v > 0 && (v & (v - 1)) == 0; }
 
 int get_fft_tables(spb_context *ctx, int nfft, FftTables *out) {
@@ -159,6 +181,7 @@ int spb_destroy(spb_context *ctx) {
     if (b.ptr) cudaFree(b.ptr);
   for (int i = 0; i < 2; ++i)
     if (ctx->pinned[i]) cudaFreeHost(ctx->pinned[i]);
+  for (auto e : ctx->ev_pool) cudaEventDestroy(e);
   for (auto &kv : ctx->fft_tables) {
     if (kv.second.d_tw) cudaFree(kv.second.d_tw);
     if (kv.second.d_twA) cudaFree(kv.second.d_twA);
@@ -202,6 +225,36 @@ int spb_device_info(spb_context *ctx, int32_t *sm_count, int32_t *cc_major, int3
 int spb_launch_count(spb_context *ctx, uint64_t *count) {
   SPB_REQUIRE(ctx, ctx && count, "spb_launch_count: NULL argument");
   *count = ctx->launches;
+  return SPB_OK;
+}
+
+int spb_timing_enable(spb_context *ctx, int32_t on) {
+  SPB_REQUIRE(ctx, ctx != nullptr, "spb_timing_enable: NULL context");
+  SPB_CUDA(ctx, cudaSetDevice(ctx->device));
+  SPB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  ctx->timing = on != 0;
+  ctx->ev_used = 0;
+  for (auto &v : ctx->ev_pairs) v.clear();
+  return SPB_OK;
+}
+
+int spb_timing_read(spb_context *ctx, int32_t kernel, double *total_ms, uint64_t *launches) {
+  SPB_REQUIRE(ctx, ctx && total_ms && launches, "spb_timing_read: NULL argument");
+  SPB_REQUIRE(ctx, kernel >= 0 && kernel < 3, "spb_timing_read: kernel must be 0, 1 or 2");
+  SPB_CUDA(ctx, cudaSetDevice(ctx->device));
+  SPB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  double tot = 0.0;
+  for (auto &pr : ctx->ev_pairs[kernel]) {
+    float ms = 0.f;
+    SPB_CUDA(ctx, cudaEventElapsedTime(&ms, ctx->ev_pool[pr.first], ctx->ev_pool[pr.second]));
+    tot += ms;
+  }
+  *total_ms = tot;
+  *launches = ctx->ev_pairs[kernel].size();
+  ctx->ev_pairs[kernel].clear();
+  bool all_empty = true;
+  for (auto &v : ctx->ev_pairs) all_empty = all_empty && v.empty();
+  if (all_empty) ctx->ev_used = 0;
   return SPB_OK;
 }
 
@@ -518,8 +571,11 @@ static int run_features(spb_context *ctx, FeatArgs &a) {
   FftTables t;
   int rc = get_fft_tables(ctx, a.nfft, &t);
   if (rc) return rc;
-  if (!g_force_generic && fast512_supported(a)) return launch_features_fast512(ctx, a, t);
-  return launch_features_generic(ctx, a, t);
+  const size_t tb = timing_begin(ctx);
+  rc = (!g_force_generic && fast512_supported(a)) ? launch_features_fast512(ctx, a, t)
+                                                  : launch_features_generic(ctx, a, t);
+  timing_end(ctx, 0, tb);
+  return rc;
 }
 
 static int check_batch(spb_context *ctx, const spb_batch *b, int64_t arena_len, const void *in,

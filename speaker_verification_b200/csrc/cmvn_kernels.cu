@@ -195,7 +195,9 @@ int launch_cmvnw_f32(spb_context *ctx, const float *in, float *scratch_ms, float
     if (grid > num_tiles) grid = num_tiles;
     p.in = (stage == 1) ? in : scratch_ms;
     p.out = (stage == 1) ? (varnorm ? scratch_ms : out) : out;
+    const size_t tb = timing_begin(ctx);
     kern<<<(unsigned)grid, kCmThreads, smem, ctx->stream>>>(p);
+    timing_end(ctx, stage, tb);
     SPB_LAUNCH_CHECK(ctx, "cmvnw_kernel");
   }
   return SPB_OK;

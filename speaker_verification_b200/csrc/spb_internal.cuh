@@ -46,6 +46,11 @@ struct spb_context {
   size_t pinned_bytes = 0;
   std::map<int, spb::FftTables> fft_tables;  // by nfft
   std::vector<spb_plan *> plans;
+  // optional per-kernel timing (spb_timing_enable)
+  bool timing = false;
+  std::vector<cudaEvent_t> ev_pool;
+  size_t ev_used = 0;
+  std::vector<std::pair<size_t, size_t>> ev_pairs[3];  // indices into ev_pool
 };
 
 struct spb_plan {
@@ -96,6 +101,9 @@ struct spb_batch {
 namespace spb {
 
 int fail(spb_context *ctx, int code, const std::string &msg);
+// timing helpers: begin returns an index to pass to end (or SIZE_MAX when disabled)
+size_t timing_begin(spb_context *ctx);
+void timing_end(spb_context *ctx, int kernel, size_t begin_idx);
 int cuda_fail(spb_context *ctx, cudaError_t e, const char *what);
 // returns device pointer of at least `bytes` (grow-only), or nullptr (error set)
 void *scratch(spb_context *ctx, int slot, size_t bytes);

@@ -1,0 +1,93 @@
+"""Ragged-batch entry points (host and device pointers) against the oracle."""
+import numpy as np
+import pytest
+
+from oracle import speechpy_oracle as o
+from speaker_verification_b200 import batch, synth
+
+pytestmark = pytest.mark.gpu
+FS = 16000
+TOL = 1e-4
+
+
+def _signals(seed, lengths):
+    return [synth.audio(seed + i, int(n), np.float32) for i, n in enumerate(lengths)]
+
+
+def test_lmfe_cmvnw_ragged_batch(sp):
+    lengths = [64000, 480, 35000, 320, 100321, 8000, 479, 20000, 70000]
+    sigs = _signals(300, lengths)
+    arena, starts, lens = batch.pack(sigs)
+    fb = batch.FeatureBatch(starts, lens)
+    out = fb.lmfe_cmvnw(arena)
+    assert out.dtype == np.float32 and out.shape == (fb.total_frames, 40)
+    parts = fb.split(out)
+    for s, got in zip(sigs, parts):
+        lm = o.lmfe(s, FS)
+        assert got.shape == lm.shape
+        if lm.shape[0]:
+            ref = o.cmvnw_vectorised(lm, 301, True)
+            assert np.max(np.abs(got - ref)) < TOL
+    fb.close()
+
+
+def test_unaligned_starts(sp):
+    sigs = _signals(400, [5000, 7001, 6002, 9003])
+    lens = np.array([len(s) for s in sigs], dtype=np.int64)
+    starts = np.array([1, 5003, 12007, 18010], dtype=np.int64)
+    arena = np.zeros(28000, dtype=np.float32)
+    for s, st in zip(sigs, starts):
+        arena[st:st + len(s)] = s
+    fb = batch.FeatureBatch(starts, lens, variance_normalization=False)
+    out = fb.split(fb.lmfe_cmvnw(arena))
+    for s, got in zip(sigs, out):
+        assert np.max(np.abs(got - o.cmvnw(o.lmfe(s, FS), 301, False))) < TOL
+    fb.close()
+
+
+def test_mfcc_delta_batch(sp):
+    sigs = _signals(500, [128000, 16000, 640, 48000])
+    arena, starts, lens = batch.pack(sigs)
+    fb = batch.FeatureBatch(starts, lens)
+    out = fb.mfcc_delta(arena)
+    assert out.shape == (fb.total_frames, 13, 3)
+    for s, got in zip(sigs, fb.split(out)):
+        ref = o.extract_derivative_feature(o.mfcc(s, FS))
+        assert np.max(np.abs(got - ref)) < TOL
+    fb.close()
+
+
+def test_device_pointer_path_and_launch_count(sp):
+    import torch
+    from speaker_verification_b200 import _lib
+    lengths = synth.cfg3_lengths(64, seed=3)
+    arena, starts, lens = synth.ragged_corpus(lengths, seed=33)
+    fb = batch.FeatureBatch(starts, lens)
+    d_in = torch.from_numpy(arena).cuda()
+    d_out = torch.empty((fb.total_frames, 40), dtype=torch.float32, device="cuda")
+    torch.cuda.synchronize()
+    n0 = fb.ctx.launch_count()
+    fb.lmfe_cmvnw_dev(d_in.data_ptr(), d_in.numel(), d_out.data_ptr())
+    fb.ctx.sync()
+    assert fb.ctx.launch_count() - n0 >= 3
+    got = d_out.cpu().numpy()
+    host = fb.lmfe_cmvnw(arena)
+    assert np.array_equal(got, host)  # same kernels, same order: bit-identical
+    for u in (0, 17, 63):
+        s = arena[starts[u]:starts[u] + lens[u]]
+        ref = o.cmvnw_vectorised(o.lmfe(s, FS), 301, True)
+        assert np.max(np.abs(got[fb.frame_offsets[u]:fb.frame_offsets[u + 1]] - ref)) < TOL
+    # property at size: every utterance's columns are ~zero-mean locally => global column means small
+    assert np.all(np.isfinite(got))
+    fb.close()
+
+
+def test_batch_errors(sp):
+    with pytest.raises(ValueError):
+        batch.FeatureBatch(np.array([0]), np.array([100]))
+    with pytest.raises(AssertionError):
+        batch.FeatureBatch(np.array([0]), np.array([4000]), win_size=300)
+    fb = batch.FeatureBatch(np.array([0]), np.array([4000]))
+    with pytest.raises(AssertionError):
+        fb.lmfe_cmvnw(np.zeros(100, dtype=np.float32))
+    fb.close()

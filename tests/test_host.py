@@ -1,0 +1,157 @@
+"""CPU-side checks: the library builds, exports every symbol the header declares,
+fails loudly without a GPU, and the host logic (filterbank, geometry, sharding,
+import shims) matches the reference's behaviour.  No compute calls."""
+import ctypes
+import os
+import re
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+
+from conftest import ROOT, golden
+
+
+def header_symbols():
+    text = open(os.path.join(ROOT, "include", "speechpy_b200.h")).read()
+    return sorted(set(re.findall(r"SPB_API\s+(?:const\s+char\s*\*|int)\s*(spb_\w+)\s*\(", text)))
+
+
+def test_library_exports_every_declared_symbol(lib_built):
+    lib = ctypes.CDLL(lib_built)
+    names = header_symbols()
+    assert len(names) >= 35
+    for n in names:
+        assert hasattr(lib, n), n
+    from speaker_verification_b200 import _lib
+    assert sorted(_lib.PROTOTYPES) == names  # the ctypes table mirrors the header one to one
+    assert lib.spb_version() == 100
+
+
+def test_host_integer_math_matches_reference_table(lib_built):
+    from speaker_verification_b200 import _lib
+    lib = _lib.load()
+    g = golden("frame_geometry.npz")
+    for L, S, n, f_nopad, f_pad in g["table"]:
+        for zp, want in ((0, f_nopad), (1, f_pad)):
+            F = _lib.c_i64()
+            rc = lib.spb_num_frames(int(n), int(L), int(S), zp, ctypes.byref(F))
+            if want < 0:
+                assert rc == _lib.SPB_ERR_NEGATIVE_DIM
+                assert b"negative dimensions" in lib.spb_last_error(None)
+            else:
+                assert rc == 0 and F.value == want
+
+
+def test_no_cpu_fallback(lib_built):
+    """Without a CUDA device the product path must raise, not compute."""
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("a GPU is present")
+    code = ("import sys; sys.path.insert(0, %r)\n"
+            "import numpy as np, speaker_verification_b200 as p; p.install_dropin()\n"
+            "import speechpy\n"
+            "try:\n"
+            "    speechpy.feature.lmfe(np.zeros(4000), 16000)\n"
+            "except RuntimeError as e:\n"
+            "    print('RAISED', e)\n" % ROOT)
+    out = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True).stdout
+    assert "RAISED" in out and "no CPU fallback" in out
+
+
+def test_product_does_not_import_oracle():
+    pkg = os.path.join(ROOT, "speaker_verification_b200")
+    for dirpath, _, files in os.walk(pkg):
+        for f in files:
+            if f.endswith((".py", ".cu", ".cuh")):
+                text = open(os.path.join(dirpath, f)).read()
+                assert "oracle" not in text.replace("# oracle", ""), os.path.join(dirpath, f)
+
+
+def test_filterbank_host_bit_exact():
+    import speaker_verification_b200 as pkg
+    pkg.install_dropin()
+    from speechpy import feature
+    g = golden("filterbanks.npz")
+    for i in range(int(g["count"])):
+        m, k, f, lo, hi = (int(v) for v in g[f"params_{i}"])
+        lo = None if lo < 0 else lo
+        hi = None if hi < 0 else hi
+        bank = feature.filterbanks(m, k, f, lo, hi)
+        assert bank.dtype == np.float64 and np.array_equal(bank, g[f"bank_{i}"])
+    with pytest.raises(AssertionError):
+        feature.filterbanks(40, 257, 16000, 0, 9000)
+    with pytest.raises(AssertionError):
+        feature.filterbanks(40, 257, 16000, -5, 8000)
+
+
+def test_import_spellings_and_api_surface():
+    """Every import spelling the reference uses and every name
+    speech_feature_extraction/tests/test_speechpy.py:24-51 checks."""
+    import speaker_verification_b200 as pkg
+    pkg.install_dropin()
+    import speech_feature_extraction.speechpy as speech2
+    import speech_feature_extraction.speechpy.feature as speech
+    import speechpy
+    from speechpy import feature, functions, processing
+    assert speech.lmfe is feature.lmfe or speech.lmfe.__name__ == "lmfe"
+    assert hasattr(speech2.feature, "extract_derivative_feature") and hasattr(speech2.processing, "cmvn")
+    for n in ("preemphasis", "stack_frames", "fft_spectrum", "power_spectrum", "log_power_spectrum",
+              "derivative_extraction", "cmvn", "cmvnw"):
+        assert hasattr(processing, n) and hasattr(speechpy.processing, n)
+    for n in ("filterbanks", "mfcc", "mfe", "lmfe", "extract_derivative_feature"):
+        assert hasattr(feature, n)
+    for n in ("frequency_to_mel", "mel_to_frequency", "triangle", "zero_handling"):
+        assert hasattr(functions, n)
+    import inspect
+    sig = inspect.signature(feature.mfcc)
+    assert list(sig.parameters) == ["signal", "sampling_frequency", "frame_length", "frame_stride",
+                                    "num_cepstral", "num_filters", "fft_length", "low_frequency",
+                                    "high_frequency", "dc_elimination"]
+    d = {k: v.default for k, v in sig.parameters.items()}
+    assert (d["frame_length"], d["frame_stride"], d["num_cepstral"], d["num_filters"], d["fft_length"],
+            d["low_frequency"], d["high_frequency"], d["dc_elimination"]) == (0.020, 0.01, 13, 40, 512, 0, None, True)
+    sig = inspect.signature(processing.stack_frames)
+    assert sig.parameters["frame_stride"].default == 0.020 and sig.parameters["zero_padding"].default is True
+    assert inspect.signature(processing.cmvnw).parameters["win_size"].default == 301
+    # argument validation that needs no device
+    with pytest.raises(AssertionError):
+        processing.stack_frames(np.zeros((4, 4)), 16000)
+    with pytest.raises(AssertionError):
+        processing.cmvnw(np.zeros((4, 4)), win_size=300)
+    with pytest.raises(AssertionError):
+        processing.cmvnw(np.zeros((4, 4)), win_size=301.0)
+    with pytest.raises(ValueError):
+        processing.stack_frames(np.zeros(100), 16000, 0.02, 0.01)
+    pre = processing.preemphasis(np.arange(5.0), cof=0.98)
+    assert np.allclose(pre, np.arange(5.0) - 0.98 * np.roll(np.arange(5.0), 1))
+
+
+def test_pack_and_shard_balance():
+    from speaker_verification_b200 import batch, synth
+    lengths = synth.cfg3_lengths(20000, seed=3)
+    assert lengths.min() >= 64000 and lengths.max() <= 320000
+    for ws in (2, 4, 8):
+        shards = batch.shard_indices_fast(lengths, ws)
+        allidx = np.sort(np.concatenate(shards))
+        assert np.array_equal(allidx, np.arange(len(lengths)))
+        loads = np.array([lengths[s].sum() for s in shards])
+        assert (loads.max() - loads.min()) <= lengths.max()
+    shards = batch.shard_indices(lengths[:500], 4)
+    loads = np.array([lengths[:500][s].sum() for s in shards])
+    assert (loads.max() - loads.min()) <= lengths.max()
+    sigs = [np.arange(n, dtype=np.float32) for n in (5, 8, 3)]
+    arena, starts, lens = batch.pack(sigs)
+    assert list(starts) == [0, 8, 16] and list(lens) == [5, 8, 3] and arena.shape[0] == 20
+    assert np.array_equal(arena[8:16], sigs[1]) and arena[5] == 0
+
+
+def test_host_fft_emulation(tmp_path):
+    """The __host__ __device__ FFT building blocks, emulated lane by lane on the CPU."""
+    exe = str(tmp_path / "host_fft_check")
+    subprocess.check_call(["nvcc", "-O1", "-Wno-deprecated-gpu-targets", "-I",
+                           os.path.join(ROOT, "speaker_verification_b200", "csrc"), "-o", exe,
+                           os.path.join(ROOT, "tests", "host", "host_fft_check.cu")])
+    out = subprocess.run([exe], capture_output=True, text=True)
+    assert out.returncode == 0 and "OK" in out.stdout, out.stdout
