@@ -68,6 +68,26 @@ void timing_end(spb_context *ctx, int kernel, size_t begin_idx) {
   if (e != (size_t)-1) ctx->ev_pairs[kernel].push_back({begin_idx, e});
 }
 
+int configure_kernel(spb_context *ctx, const void *func, int threads, size_t smem, int *per_sm) {
+  auto key = std::make_pair(func, smem);
+  auto it = ctx->kernel_cfg.find(key);
+  if (it != ctx->kernel_cfg.end()) {
+    *per_sm = it->second;
+    return SPB_OK;
+  }
+  // the attribute is a per-function maximum: only ever raise it
+  size_t &cur_max = ctx->kernel_smem_max[func];
+  if (smem > cur_max) {
+    SPB_CUDA(ctx, cudaFuncSetAttribute(func, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    cur_max = smem;
+  }
+  int n = 0;
+  SPB_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, func, threads, smem));
+  ctx->kernel_cfg[key] = n;
+  *per_sm = n;
+  return SPB_OK;
+}
+
 static bool is_pow2(int v) { return v > 0 && (v & (v - 1)) == 0; }
 
 int get_fft_tables(spb_context *ctx, int nfft, FftTables *out) {
@@ -350,8 +370,11 @@ int spb_plan_create(spb_context *ctx, const spb_feature_params *params, const do
     pl->h_band_off[m] = (int)w.size();
     if (lo >= 0) {
       pl->h_band_lo[m] = lo;
-      pl->h_band_n[m] = hi - lo + 1;
-      for (int k = lo; k <= hi; ++k) w.push_back((float)filterbank[(size_t)m * K + k]);
+      // taps zero-padded to a multiple of four: the kernels read four weights per load
+      const int n4 = (hi - lo + 1 + 3) & ~3;
+      pl->h_band_n[m] = n4;
+      for (int k = lo; k < lo + n4; ++k)
+        w.push_back(k <= hi ? (float)filterbank[(size_t)m * K + k] : 0.f);
       pl->max_bin = std::max(pl->max_bin, hi);
     }
   }

@@ -44,7 +44,25 @@ struct CmParams {
   float eps;
 };
 
-template <int STAGE>
+// Vector helpers: VEC columns per thread (1 or 2).
+template <int VEC> struct CmVec;
+template <> struct CmVec<1> {
+  static __device__ __forceinline__ void load(const float *p, float (&v)[1]) { v[0] = *p; }
+  static __device__ __forceinline__ void store(float *p, const float (&v)[1]) { *p = v[0]; }
+};
+template <> struct CmVec<2> {
+  static __device__ __forceinline__ void load(const float *p, float (&v)[2]) {
+    const float2 t = *reinterpret_cast<const float2 *>(p);
+    v[0] = t.x; v[1] = t.y;
+  }
+  static __device__ __forceinline__ void store(float *p, const float (&v)[2]) {
+    *reinterpret_cast<float2 *>(p) = make_float2(v[0], v[1]);
+  }
+};
+
+// Thread layout: column group g = tid % ncg (VEC adjacent columns), row block b = tid / ncg;
+// every index below is derived from (g, b) with adds only -- no per-element division.
+template <int STAGE, int VEC>
 __global__ void __launch_bounds__(kCmThreads)
 cmvnw_kernel(const CmParams p) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -58,7 +76,17 @@ cmvnw_kernel(const CmParams p) {
   double *bs1 = reinterpret_cast<double *>(smem_raw + s_bytes);         // [nblk_max][cols]
   double *bs2 = bs1 + (size_t)nblk_max * cols;                          // stage 2 only
   const int tid = threadIdx.x;
+  const int warp = tid >> 5, lane = tid & 31;
+  constexpr int kWarps = kCmThreads / 32;
+  const int ncg = cols / VEC;                 // column groups
+  const int nbpt = kCmThreads / ncg;          // row blocks handled per sweep
+  const int g = tid % ncg, b0 = tid / ncg;    // once per thread
+  const bool worker = b0 < nbpt;
+  const int c0 = g * VEC;
   const double inv_win = 1.0 / (double)win;
+  const bool vec4 = ((cols & 3) == 0) && ((ld & 3) == 0) &&
+                    ((((size_t)p.in) & 15) == 0);
+  const int n4 = cols >> 2;
 
   for (long long tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x) {
     const int2 td = p.tiles[tile];
@@ -68,82 +96,127 @@ cmvnw_kernel(const CmParams p) {
     const int nrows = min(R, F - r0);
     const int rows_needed = nrows + win - 1;
     __syncthreads();
-    // ---- stage the rows [r0-h, r0+nrows+h) with symmetric reflection at the ends
-    const long long first = (long long)r0 - h;
-    if (first >= 0 && first + rows_needed <= F && ld == cols) {
-      const float *src = p.in + (base + first) * cols;
-      const int total = rows_needed * cols;
-      if ((((size_t)src) & 15) == 0) {
-        const float4 *s4 = reinterpret_cast<const float4 *>(src);
-        float4 *d4 = reinterpret_cast<float4 *>(s);
-        const int n4 = total >> 2;
-        for (int i = tid; i < n4; i += kCmThreads) d4[i] = __ldg(s4 + i);
-        for (int i = (n4 << 2) + tid; i < total; i += kCmThreads) s[i] = __ldg(src + i);
-      } else {
-        for (int i = tid; i < total; i += kCmThreads) s[i] = __ldg(src + i);
+    // ---- stage rows [r0-h, r0+nrows+h), symmetric reflection at the utterance ends
+    const int first = r0 - h;
+    const bool interior = first >= 0 && first + rows_needed <= F;
+    if (interior && ld == cols && vec4) {
+      const float4 *s4 = reinterpret_cast<const float4 *>(p.in + (base + first) * cols);
+      float4 *d4 = reinterpret_cast<float4 *>(s);
+      const int total4 = (rows_needed * cols) >> 2;
+      for (int i = tid; i < total4; i += kCmThreads) d4[i] = __ldg(s4 + i);
+    } else if (vec4 && n4 <= 32) {
+      // rows_per_pass rows per warp iteration, one float4 per lane
+      const int rpp = 32 / n4;
+      const int lr = lane / n4, lc = lane - lr * n4;
+      const int period = 2 * F;
+      if (lr < rpp) {
+        for (int t = warp * rpp + lr; t < rows_needed; t += kWarps * rpp) {
+          int m = (first + t) % period;
+          if (m < 0) m += period;
+          const int srow = (m < F) ? m : (period - 1 - m);
+          const float4 v = __ldg(reinterpret_cast<const float4 *>(p.in + (base + srow) * ld) + lc);
+          reinterpret_cast<float4 *>(s + (size_t)t * cols)[lc] = v;
+        }
       }
     } else {
-      const int total = rows_needed * cols;
-      for (int i = tid; i < total; i += kCmThreads) {
-        const int t = i / cols, c = i - t * cols;
-        const int srow = reflect_row(first + t, F);
-        s[i] = __ldg(p.in + (base + srow) * ld + c);
+      const int period = 2 * F;
+      for (int t = warp; t < rows_needed; t += kWarps) {
+        int m = (first + t) % period;
+        if (m < 0) m += period;
+        const int srow = (m < F) ? m : (period - 1 - m);
+        const float *src = p.in + (base + srow) * ld;
+        for (int c = lane; c < cols; c += 32) s[(size_t)t * cols + c] = __ldg(src + c);
       }
     }
     __syncthreads();
-    // ---- block sums
+    // ---- float64 sums of kCmG-row blocks
     const int nblk_out = (nrows + kCmG - 1) / kCmG;
     const int nblk = nblk_out + nb - 1;  // every block lies inside rows_needed
-    for (int i = tid; i < nblk * cols; i += kCmThreads) {
-      const int k = i / cols, c = i - k * cols;
-      const float *col = s + (size_t)k * kCmG * cols + c;
-      double a1 = 0.0, a2 = 0.0;
+    if (worker) {
+      for (int k = b0; k < nblk; k += nbpt) {
+        const float *col = s + (size_t)k * kCmG * cols + c0;
+        double a1[VEC], a2[VEC];
 #pragma unroll
-      for (int r = 0; r < kCmG; ++r) {
-        const double v = (double)col[r * cols];
-        a1 += v;
-        if (STAGE == 2) a2 = fma(v, v, a2);
+        for (int v = 0; v < VEC; ++v) a1[v] = a2[v] = 0.0;
+#pragma unroll
+        for (int r = 0; r < kCmG; ++r) {
+          float x[VEC];
+          CmVec<VEC>::load(col + r * cols, x);
+#pragma unroll
+          for (int v = 0; v < VEC; ++v) {
+            const double d = (double)x[v];
+            a1[v] += d;
+            if (STAGE == 2) a2[v] = fma(d, d, a2[v]);
+          }
+        }
+#pragma unroll
+        for (int v = 0; v < VEC; ++v) {
+          bs1[k * cols + c0 + v] = a1[v];
+          if (STAGE == 2) bs2[k * cols + c0 + v] = a2[v];
+        }
       }
-      bs1[i] = a1;
-      if (STAGE == 2) bs2[i] = a2;
     }
     __syncthreads();
-    // ---- window sums: first row of each block from block sums, then slide
-    for (int i = tid; i < nblk_out * cols; i += kCmThreads) {
-      const int b = i / cols, c = i - b * cols;
-      double w1 = 0.0, w2 = 0.0;
-      for (int j = 0; j < nb; ++j) {
-        w1 += bs1[(b + j) * cols + c];
-        if (STAGE == 2) w2 += bs2[(b + j) * cols + c];
-      }
-      const float *col = s + c;
-      const int tail0 = (b + nb) * kCmG;
-      for (int r = 0; r < rem; ++r) {
-        const double v = (double)col[(size_t)(tail0 + r) * cols];
-        w1 += v;
-        if (STAGE == 2) w2 = fma(v, v, w2);
-      }
-      const int q0 = b * kCmG;
-      const int q1 = min(q0 + kCmG, nrows);
-      float *dst = p.out + (base + r0) * ld + c;
-      for (int q = q0; q < q1; ++q) {
-        const float xc = col[(size_t)(q + h) * cols];
-        if (STAGE == 1) {
-          // processing.py:304-307: float32(vec[i] - mean(window))
-          dst[(size_t)q * ld] = (float)((double)xc - w1 * inv_win);
-        } else {
-          // processing.py:318-322: ms / (std(window) + eps), population std
-          const double mean = w1 * inv_win;
-          double var = fma(-mean, mean, w2 * inv_win);
-          var = var > 0.0 ? var : 0.0;
-          const float sd = sqrtf((float)var);
-          dst[(size_t)q * ld] = xc / (sd + p.eps);
+    // ---- window sums: first row of each block from block sums, then slide down the block
+    if (worker) {
+      for (int b = b0; b < nblk_out; b += nbpt) {
+        double w1[VEC], w2[VEC];
+#pragma unroll
+        for (int v = 0; v < VEC; ++v) w1[v] = w2[v] = 0.0;
+        for (int j = 0; j < nb; ++j) {
+#pragma unroll
+          for (int v = 0; v < VEC; ++v) {
+            w1[v] += bs1[(b + j) * cols + c0 + v];
+            if (STAGE == 2) w2[v] += bs2[(b + j) * cols + c0 + v];
+          }
         }
-        if (q + 1 < q1) {
-          const double vin = (double)col[(size_t)(q + win) * cols];
-          const double vout = (double)col[(size_t)q * cols];
-          w1 += vin - vout;
-          if (STAGE == 2) w2 += fma(vin, vin, -vout * vout);
+        const float *col = s + c0;
+        const int tail0 = (b + nb) * kCmG;
+        for (int r = 0; r < rem; ++r) {
+          float x[VEC];
+          CmVec<VEC>::load(col + (size_t)(tail0 + r) * cols, x);
+#pragma unroll
+          for (int v = 0; v < VEC; ++v) {
+            const double d = (double)x[v];
+            w1[v] += d;
+            if (STAGE == 2) w2[v] = fma(d, d, w2[v]);
+          }
+        }
+        const int q0 = b * kCmG;
+        const int q1 = min(q0 + kCmG, nrows);
+        float *dst = p.out + (base + r0 + q0) * ld + c0;
+        const float *pc = col + (size_t)(q0 + h) * cols;   // centre row
+        const float *pin = col + (size_t)(q0 + win) * cols;  // row entering the window
+        const float *pout = col + (size_t)q0 * cols;         // row leaving the window
+        for (int q = q0; q < q1; ++q) {
+          float xc[VEC], o[VEC];
+          CmVec<VEC>::load(pc, xc);
+#pragma unroll
+          for (int v = 0; v < VEC; ++v) {
+            if (STAGE == 1) {
+              // processing.py:304-307: float32(vec[i] - mean(window))
+              o[v] = (float)((double)xc[v] - w1[v] * inv_win);
+            } else {
+              // processing.py:318-322: ms / (std(window) + eps), population std
+              const double mean = w1[v] * inv_win;
+              double var = fma(-mean, mean, w2[v] * inv_win);
+              var = var > 0.0 ? var : 0.0;
+              o[v] = xc[v] / (sqrtf((float)var) + p.eps);
+            }
+          }
+          CmVec<VEC>::store(dst, o);
+          if (q + 1 < q1) {
+            float xi[VEC], xo[VEC];
+            CmVec<VEC>::load(pin, xi);
+            CmVec<VEC>::load(pout, xo);
+#pragma unroll
+            for (int v = 0; v < VEC; ++v) {
+              const double vin = (double)xi[v], vout = (double)xo[v];
+              w1[v] += vin - vout;
+              if (STAGE == 2) w2[v] += fma(vin, vin, -vout * vout);
+            }
+          }
+          dst += ld; pc += cols; pin += cols; pout += cols;
         }
       }
     }
@@ -167,7 +240,7 @@ int cmvnw_tile_rows(int cols, int win) {
 }
 
 bool cmvnw_supported(int cols, int win) {
-  return cm_smem_bytes(kCmG, cols, win) <= 200 * 1024;
+  return cols <= kCmThreads && cm_smem_bytes(kCmG, cols, win) <= 200 * 1024;
 }
 
 int launch_cmvnw_f32(spb_context *ctx, const float *in, float *scratch_ms, float *out,
@@ -186,10 +259,14 @@ int launch_cmvnw_f32(spb_context *ctx, const float *in, float *scratch_ms, float
   p.eps = 9.313225746154785e-10f;  // 2^-30 (processing.py:292)
   const size_t smem = cm_smem_bytes(tile_rows, cols, win);
   for (int stage = 1; stage <= (varnorm ? 2 : 1); ++stage) {
-    auto kern = (stage == 1) ? cmvnw_kernel<1> : cmvnw_kernel<2>;
-    SPB_CUDA(ctx, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    // two columns per thread need 8-byte aligned rows in global and shared memory
+    const bool v2 = (cols % 2 == 0) && (ld % 2 == 0) && ((((size_t)in) & 7) == 0) &&
+                    ((((size_t)out) & 7) == 0) && (!scratch_ms || (((size_t)scratch_ms) & 7) == 0);
+    auto kern = (stage == 1) ? (v2 ? cmvnw_kernel<1, 2> : cmvnw_kernel<1, 1>)
+                             : (v2 ? cmvnw_kernel<2, 2> : cmvnw_kernel<2, 1>);
     int per_sm = 0;
-    SPB_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, kCmThreads, smem));
+    int rc = configure_kernel(ctx, (const void *)kern, kCmThreads, smem, &per_sm);
+    if (rc) return rc;
     if (per_sm < 1) return fail(ctx, SPB_ERR_UNSUPPORTED, "cmvnw: window x columns too large for shared memory");
     long long grid = (long long)ctx->sm_count * per_sm;
     if (grid > num_tiles) grid = num_tiles;

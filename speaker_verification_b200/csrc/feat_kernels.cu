@@ -50,6 +50,9 @@ struct FeatParams {
 // 0..pbins-1), s_en: per-frame energy (already scaled, zero-handled) or unused.
 // Called by the whole CTA after a __syncthreads().  s_a / s_b: scratch of TILE*(41|..).
 // ------------------------------------------------------------------------------------
+// Band weights are zero-padded to multiples of four (offsets too), so the inner loop is a
+// 128-bit broadcast load of four weights + four FFMAs; P rows carry >= 3 zeroed pad bins
+// after the last real bin so the padded taps read finite values.
 template <int TILE>
 __device__ __forceinline__ void output_stage(const FeatParams &p, const float *s_p, int pstride,
                                              const float *s_en, float *s_a, float *s_b,
@@ -60,12 +63,15 @@ __device__ __forceinline__ void output_stage(const FeatParams &p, const float *s
   const float scale = 1.0f / (float)p.nfft;  // |X|^2 / NFFT  (processing.py:174)
   if (p.mode == FEAT_POWER || p.mode == FEAT_MAG) {
     // rows are contiguous in global memory: (row0 + f) * K + k
-    const int total = nf * p.K;
-    float *dst = p.out + row0 * p.K;
-    for (int i = tid; i < total; i += nthreads) {
-      int f = i / p.K, k = i - f * p.K;
-      float v = s_p[f * pstride + k];
-      dst[i] = (p.mode == FEAT_POWER) ? v * scale : sqrtf(v);
+    const int K = p.K;
+    float *dst = p.out + row0 * K;
+    int f = tid / K, k = tid - f * K;
+    const int df = nthreads / K, dk = nthreads - df * K;
+    while (f < nf) {
+      const float v = s_p[f * pstride + k];
+      dst[f * K + k] = (p.mode == FEAT_POWER) ? v * scale : sqrtf(v);
+      k += dk; f += df;
+      if (k >= K) { k -= K; ++f; }
     }
     return;
   }
@@ -80,8 +86,16 @@ __device__ __forceinline__ void output_stage(const FeatParams &p, const float *s
       const float *prow = s_p + f * pstride;
       for (int m = slot; m < M; m += nslots) {
         const int lo = s_bmeta[m], n = s_bmeta[M + m], off = s_bmeta[2 * M + m];
+        const float4 *w4 = reinterpret_cast<const float4 *>(s_bw + off);
+        const float *pr = prow + lo;
         float acc = 0.f;
-        for (int k = 0; k < n; ++k) acc = fmaf(s_bw[off + k], prow[lo + k], acc);
+        for (int k = 0; k < n; k += 4) {
+          const float4 w = w4[k >> 2];
+          acc = fmaf(w.x, pr[k], acc);
+          acc = fmaf(w.y, pr[k + 1], acc);
+          acc = fmaf(w.z, pr[k + 2], acc);
+          acc = fmaf(w.w, pr[k + 3], acc);
+        }
         acc *= scale;
         if (acc == 0.f) acc = kEpsF64AsF32;  // functions.zero_handling (feature.py:217)
         s_a[f * astride + m] = (p.mode == FEAT_MFE) ? acc : __logf(acc);
@@ -90,14 +104,16 @@ __device__ __forceinline__ void output_stage(const FeatParams &p, const float *s
   }
   __syncthreads();
   if (p.mode == FEAT_MFE || p.mode == FEAT_LMFE) {
-    const int total = nf * M;
     float *dst = p.out + row0 * M;
-    for (int i = tid; i < total; i += nthreads) {
-      int f = i / M, m = i - f * M;
-      dst[i] = s_a[f * astride + m];
+    int f = tid / M, m = tid - f * M;
+    const int df = nthreads / M, dm = nthreads - df * M;
+    while (f < nf) {
+      dst[f * M + m] = s_a[f * astride + m];
+      m += dm; f += df;
+      if (m >= M) { m -= M; ++f; }
     }
     if (p.mode == FEAT_MFE && p.energy != nullptr) {
-      for (int f = tid; f < nf; f += nthreads) p.energy[row0 + f] = s_en[f];
+      for (int ff = tid; ff < nf; ff += nthreads) p.energy[row0 + ff] = s_en[ff];
     }
     return;
   }
@@ -120,34 +136,34 @@ __device__ __forceinline__ void output_stage(const FeatParams &p, const float *s
     }
   }
   __syncthreads();
+  int f = tid / C, c = tid - f * C;
+  const int df = nthreads / C, dc = nthreads - df * C;
   if (p.mode == FEAT_MFCC) {
-    const int total = nf * C;
     float *dst = p.out + row0 * C;
-    for (int i = tid; i < total; i += nthreads) {
-      int f = i / C, c = i - f * C;
-      dst[i] = s_b[f * cstride + c];
+    while (f < nf) {
+      dst[f * C + c] = s_b[f * cstride + c];
+      c += dc; f += df;
+      if (c >= C) { c -= C; ++f; }
     }
     return;
   }
   // FEAT_MFCC_DELTA: [x, D(x), D(D(x))] interleaved on a new last axis
   // D(x)[c] = (x[min(c+1,C-1)] + 2 x[min(c+2,C-1)]) / 10   (processing.py:223-236 as written)
   {
-    const int total = nf * C;
     float *dst = p.out + row0 * C * 3;
-    for (int i = tid; i < total; i += nthreads) {
-      int f = i / C, c = i - f * C;
+    while (f < nf) {
       const float *x = s_b + f * cstride;
       auto X = [&](int j) { return x[min(j, C - 1)]; };
       auto D1 = [&](int j) {
         j = min(j, C - 1);
         return (X(j + 1) + 2.f * X(j + 2)) / 10.f;
       };
-      float d0 = x[c];
-      float d1 = D1(c);
-      float d2 = (D1(c + 1) + 2.f * D1(c + 2)) / 10.f;
-      dst[i * 3 + 0] = d0;
-      dst[i * 3 + 1] = d1;
-      dst[i * 3 + 2] = d2;
+      float *o = dst + (f * C + c) * 3;
+      o[0] = x[c];
+      o[1] = D1(c);
+      o[2] = (D1(c + 1) + 2.f * D1(c + 2)) / 10.f;
+      c += dc; f += df;
+      if (c >= C) { c -= C; ++f; }
     }
   }
 }
@@ -165,6 +181,14 @@ __device__ __forceinline__ void load_plan_to_smem(const FeatParams &p, float *s_
     for (int i = threadIdx.x; i < p.C * p.M; i += blockDim.x) s_dct[i] = p.dct[i];
 }
 
+__device__ __forceinline__ void cp_async16(void *smem_dst, const void *gsrc) {
+  const unsigned d = (unsigned)__cvta_generic_to_shared(smem_dst);
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(d), "l"(gsrc) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;\n" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;\n" ::"n"(N) : "memory"); }
+
 // ====================================================================================
 // Fast kernel, NFFT = 512.
 // ====================================================================================
@@ -176,19 +200,21 @@ __global__ void __launch_bounds__(kFastThreads, 2)
 features_fast512(const FeatParams p) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   constexpr int PBINS = FULL ? 257 : 129;
-  constexpr int PSTRIDE = PBINS;  // == 1 (mod 32): lane = frame column walks are conflict-free
+  // 4 zeroed pad bins (padded band taps); stride == 5 (mod 32): conflict-free both for the
+  // half-warp row writes (rows 16 apart land 16 banks apart) and the lane = frame column reads
+  constexpr int PSTRIDE = PBINS + 4;
   const int L = p.L, S = p.S;
   const int span_max = (kTile - 1) * S + L;
   // carve shared memory
-  float *s_x = reinterpret_cast<float *>(smem_raw);                 // [span_max (+pad)]
-  int off = ((span_max + 3) & ~3);
-  float2 *s_exch = reinterpret_cast<float2 *>(s_x + off);           // 16 half-warps x 256
+  const int xoff = ((span_max + 3) & ~3);
+  float *s_xbuf = reinterpret_cast<float *>(smem_raw);              // 2 x [xoff] sample stages
+  float2 *s_exch = reinterpret_cast<float2 *>(s_xbuf + 2 * xoff);   // 16 half-warps x 256
   float *s_p = reinterpret_cast<float *>(s_exch + 16 * 256);        // [kTile][PSTRIDE]
-  float *s_en = s_p + kTile * PSTRIDE;                              // [kTile]
+  float *s_bw = s_p + kTile * PSTRIDE;                              // [band_total] (16 B aligned)
+  float *s_en = s_bw + p.band_total;                                // [kTile]
   float *s_a = s_en + kTile;                                        // [kTile][M+1]
   float *s_b = s_a + kTile * (p.M + 1);                             // [kTile][C+1]
-  float *s_bw = s_b + kTile * (p.C + 1);                            // [band_total]
-  float *s_dct = s_bw + p.band_total;                               // [C*M]
+  float *s_dct = s_b + kTile * (p.C + 1);                           // [C*M]
   int *s_bmeta = reinterpret_cast<int *>(s_dct + p.C * p.M);        // [3M]
 
   const int tid = threadIdx.x;
@@ -200,6 +226,8 @@ features_fast512(const FeatParams p) {
   float2 *my_exch = s_exch + hw * 256;
 
   load_plan_to_smem(p, s_bw, s_bmeta, s_dct);
+  for (int i = tid; i < kTile * 4; i += kFastThreads)
+    s_p[(i >> 2) * PSTRIDE + PBINS + (i & 3)] = 0.f;
 
   // per-lane twiddles (fixed for the whole kernel)
   float2 twA[16];  // W256^(l16*k1)
@@ -209,28 +237,44 @@ features_fast512(const FeatParams p) {
 #pragma unroll
   for (int k2 = 0; k2 < 8; ++k2) twB[k2] = p.twB[l16 * 9 + k2];
   const int partner = (16 - l16) & 15;
-  const int nz_complex = (min(L, 512) + 1) >> 1;  // complex inputs that can be non-zero
   const int Leff = min(L, 512);
 
-  for (long long tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x) {
-    const int2 td = p.tiles[tile];
-    const int utt = td.x, f0 = td.y;
-    const int nf = min(kTile, p.nframes[utt] - f0);
+  // Stage a tile's samples into s_xbuf[b]: 16-byte cp.async when the tile starts on a
+  // 16-byte boundary (batches packed by batch.pack do), plain loads otherwise.  Each sample
+  // is fetched from HBM once and used by L/S frames.
+  auto stage = [&](long long t, int b, int &utt, int &f0, int &nf) {
+    const int2 td = p.tiles[t];
+    utt = td.x;
+    f0 = td.y;
+    nf = min(kTile, p.nframes[utt] - f0);
     const long long gstart = p.starts[utt] + (long long)f0 * S;
     const int count = (nf - 1) * S + L;
     const float *src = p.samples + gstart;
-    __syncthreads();  // previous tile's readers of s_x / s_p are done
-    // ---- phase A: stage the tile's samples (each sample is used by L/S frames)
+    float *dst = s_xbuf + b * xoff;
     if ((gstart & 3) == 0) {
-      const float4 *src4 = reinterpret_cast<const float4 *>(src);
-      float4 *dst4 = reinterpret_cast<float4 *>(s_x);
       const int n4 = count >> 2;
-      for (int i = tid; i < n4; i += kFastThreads) dst4[i] = __ldg(src4 + i);
-      for (int i = (n4 << 2) + tid; i < count; i += kFastThreads) s_x[i] = __ldg(src + i);
+      for (int i = tid; i < n4; i += kFastThreads) cp_async16(dst + 4 * i, src + 4 * i);
+      for (int i = (n4 << 2) + tid; i < count; i += kFastThreads) dst[i] = __ldg(src + i);
     } else {
-      for (int i = tid; i < count; i += kFastThreads) s_x[i] = __ldg(src + i);
+      for (int i = tid; i < count; i += kFastThreads) dst[i] = __ldg(src + i);
     }
-    __syncthreads();
+  };
+
+  long long tile = blockIdx.x;
+  int buf = 0;
+  int utt = 0, f0 = 0, nf = 0;
+  if (tile < p.num_tiles) stage(tile, 0, utt, f0, nf);
+  cp_async_commit();
+  for (; tile < p.num_tiles; buf ^= 1) {
+    const long long next = tile + gridDim.x;
+    int n_utt = 0, n_f0 = 0, n_nf = 0;
+    // prefetch the next tile while this one is transformed (its buffer was last read in
+    // phase B of the previous iteration, which every thread has left)
+    if (next < p.num_tiles) stage(next, buf ^ 1, n_utt, n_f0, n_nf);
+    cp_async_commit();
+    cp_async_wait<1>();
+    __syncthreads();  // samples of this tile visible; previous tile's phase C is finished
+    const float *s_x = s_xbuf + buf * xoff;
 
     // ---- phase B: two frames per half-warp
 #pragma unroll 1
@@ -323,7 +367,10 @@ features_fast512(const FeatParams p) {
     // ---- phase C
     const long long row0 = p.frame_offsets[utt] + f0;
     output_stage<kTile>(p, s_p, PSTRIDE, s_en, s_a, s_b, s_bw, s_bmeta, s_dct, nf, row0);
+    tile = next;
+    utt = n_utt; f0 = n_f0; nf = n_nf;
   }
+  cp_async_wait<0>();
 }
 
 // ====================================================================================
@@ -337,18 +384,20 @@ features_generic(const FeatParams p) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const int nc = p.nfft >> 1;
   const int K = p.K;
-  const int pstride = K | 1;
+  const int pstride = (K + 4) | 1;  // >= 4 zeroed pad bins after the last real bin
   float2 *s_z = reinterpret_cast<float2 *>(smem_raw);      // [kGenWarps][nc]
   float *s_p = reinterpret_cast<float *>(s_z + kGenWarps * nc);  // [kGenTile][pstride]
-  float *s_en = s_p + kGenTile * pstride;
+  float *s_bw = s_p + kGenTile * pstride;                  // 16 B aligned (kGenTile == 4)
+  float *s_en = s_bw + p.band_total;
   float *s_a = s_en + kGenTile;
   float *s_b = s_a + kGenTile * (p.M + 1);
-  float *s_bw = s_b + kGenTile * (p.C + 1);
-  float *s_dct = s_bw + p.band_total;
+  float *s_dct = s_b + kGenTile * (p.C + 1);
   int *s_bmeta = reinterpret_cast<int *>(s_dct + p.C * p.M);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   load_plan_to_smem(p, s_bw, s_bmeta, s_dct);
+  for (int i = threadIdx.x; i < kGenTile * (pstride - K); i += blockDim.x)
+    s_p[(i / (pstride - K)) * pstride + K + i % (pstride - K)] = 0.f;
   const int Leff = min(p.L, p.nfft);
   float2 *z = s_z + warp * nc;
 
@@ -459,19 +508,19 @@ bool fast512_supported(const FeatArgs &a) {
   if (a.tile_frames != kTile) return false;
   if (a.L < 1 || a.S < 1) return false;
   size_t span = (size_t)(kTile - 1) * a.S + a.L;
-  if (span * 4 > 96 * 1024) return false;  // absurd strides: let the generic kernel take it
+  if (span * 4 > 44 * 1024) return false;  // long strides / frames: the generic kernel takes it
   return true;
 }
 
 template <int NJ, bool FULL>
 static int launch_fast(spb_context *ctx, const FeatParams &p, const FeatArgs &a) {
   const int span_max = (kTile - 1) * a.S + a.L;
-  size_t smem = (size_t)((span_max + 3) & ~3) * 4 + 16 * 256 * sizeof(float2) +
-                (size_t)kTile * (FULL ? 257 : 129) * 4 + plan_smem_bytes(a, kTile);
+  size_t smem = 2 * (size_t)((span_max + 3) & ~3) * 4 + 16 * 256 * sizeof(float2) +
+                (size_t)kTile * ((FULL ? 257 : 129) + 4) * 4 + plan_smem_bytes(a, kTile);
   auto kern = features_fast512<NJ, FULL>;
-  SPB_CUDA(ctx, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   int per_sm = 0;
-  SPB_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, kFastThreads, smem));
+  int rc = configure_kernel(ctx, (const void *)kern, kFastThreads, smem, &per_sm);
+  if (rc) return rc;
   if (per_sm < 1) return fail(ctx, SPB_ERR_INVALID, "fast512: kernel does not fit on an SM");
   long long grid = (long long)ctx->sm_count * per_sm;
   if (grid > a.num_tiles) grid = a.num_tiles;
@@ -499,13 +548,11 @@ int launch_features_generic(spb_context *ctx, const FeatArgs &a, const FftTables
   FeatParams p = make_params(a, t);
   const FeatArgs &aa = a;
   const int nc = a.nfft >> 1;
-  size_t smem = (size_t)kGenWarps * nc * sizeof(float2) + (size_t)kGenTile * (a.K | 1) * 4 +
+  size_t smem = (size_t)kGenWarps * nc * sizeof(float2) + (size_t)kGenTile * ((a.K + 4) | 1) * 4 +
                 plan_smem_bytes(aa, kGenTile);
-  SPB_CUDA(ctx, cudaFuncSetAttribute(features_generic,
-                                     cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   int per_sm = 0;
-  SPB_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, features_generic,
-                                                              kGenWarps * 32, smem));
+  int rc = configure_kernel(ctx, (const void *)features_generic, kGenWarps * 32, smem, &per_sm);
+  if (rc) return rc;
   if (per_sm < 1) return fail(ctx, SPB_ERR_INVALID, "generic fft kernel does not fit on an SM");
   long long grid = (long long)ctx->sm_count * per_sm;
   if (grid > a.num_tiles) grid = a.num_tiles;

@@ -46,6 +46,9 @@ struct spb_context {
   size_t pinned_bytes = 0;
   std::map<int, spb::FftTables> fft_tables;  // by nfft
   std::vector<spb_plan *> plans;
+  // (kernel function, dynamic smem) -> resident CTAs per SM, set up once per context
+  std::map<std::pair<const void *, size_t>, int> kernel_cfg;
+  std::map<const void *, size_t> kernel_smem_max;
   // optional per-kernel timing (spb_timing_enable)
   bool timing = false;
   std::vector<cudaEvent_t> ev_pool;
@@ -108,6 +111,8 @@ int cuda_fail(spb_context *ctx, cudaError_t e, const char *what);
 // returns device pointer of at least `bytes` (grow-only), or nullptr (error set)
 void *scratch(spb_context *ctx, int slot, size_t bytes);
 int get_fft_tables(spb_context *ctx, int nfft, FftTables *out);
+// opt in to `smem` bytes of dynamic shared memory and query occupancy, cached per context
+int configure_kernel(spb_context *ctx, const void *func, int threads, size_t smem, int *per_sm);
 
 #define SPB_CUDA(ctx, call)                                        \
   do {                                                             \
