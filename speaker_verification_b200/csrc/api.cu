@@ -260,7 +260,7 @@ int spb_timing_enable(spb_context *ctx, int32_t on) {
 
 int spb_timing_read(spb_context *ctx, int32_t kernel, double *total_ms, uint64_t *launches) {
   SPB_REQUIRE(ctx, ctx && total_ms && launches, "spb_timing_read: NULL argument");
-  SPB_REQUIRE(ctx, kernel >= 0 && kernel < 3, "spb_timing_read: kernel must be 0, 1 or 2");
+  SPB_REQUIRE(ctx, kernel >= 0 && kernel < 4, "spb_timing_read: kernel must be 0..3");
   SPB_CUDA(ctx, cudaSetDevice(ctx->device));
   SPB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
   double tot = 0.0;

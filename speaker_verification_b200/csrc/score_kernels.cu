@@ -1,40 +1,692 @@
-// Scoring path (cosine score matrix on tcgen05, trial gather, EER) -- placeholder until
-// the tensor-core kernel lands; the entry points fail loudly rather than fall back.
+// K4/K5: scoring path -- cosine score matrix on the tcgen05 tensor cores, trial gather,
+// row argmax, ROC -> EER / AUC.
+//
+// Replaces
+//   evaluation.py:76-77   one sklearn cosine_similarity(1xd, 1xd) call per (utterance, speaker)
+//   evaluation.py:79      argmax over the similarity vector
+//   evaluation.py:47-52   roc_curve + roc_auc_score + brentq(1 - x - interp1d(fpr, tpr)(x))
+//
+// Cosine matrix.  S = normalize(E) . normalize(T)^T (sklearn semantics: zero rows stay zero).
+//   prologue  : one warp per row: 1/|x| in fp32, x^ = x/|x|, split x^ = hi + lo with hi rounded
+//               to TF32 (cvt.rna) and lo = tf32(x^ - hi); rows padded with zeros to a multiple
+//               of 32 columns.  hi/lo live in context scratch (4 x 10 MB at 4874 x 512).
+//   GEMM      : persistent, warp-specialised, one CTA per SM.  Per 128 x 256 output tile and
+//               32-column k-block, TMA (SWIZZLE_128B) stages A_hi, A_lo (128 x 32) and B_hi, B_lo
+//               (256 x 32) once and one elected thread issues three groups of four
+//               tcgen05.mma.kind::tf32 (M128 N256 K8): lo.hi + hi.lo + hi.hi, all accumulating
+//               in the same fp32 TMEM tile -- the 3xTF32 split the 1e-5 tolerance needs
+//               (single-pass TF32 is ~7e-4 relative on 512-d embeddings).  Two TMEM accumulators
+//               (2 x 256 columns) let the epilogue of tile i overlap the MMAs of tile i+1.
+//   epilogue  : 4 warps, tcgen05.ld 32x32b.x32 -> registers -> padded smem transpose ->
+//               row-contiguous 128-byte global stores (the row pitch 4n bytes is in general not
+//               a multiple of 16, so a TMA store of S is not possible).
+#include <cuda.h>
+#include <math.h>
+
+#include <cub/cub.cuh>
+
 #include "spb_internal.cuh"
 
 namespace spb {
-int launch_cosine_scores(spb_context *ctx, const float *, int64_t, const float *, int64_t, int, float *) {
-  return fail(ctx, SPB_ERR_UNSUPPORTED, "cosine scores: kernel not built yet");
+
+// ------------------------------------------------------------------------------------
+// small PTX wrappers
+// ------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void *p) {
+  return (uint32_t)__cvta_generic_to_shared(p);
 }
-int launch_trial_gather(spb_context *ctx, const float *, int64_t, int64_t, const int32_t *, const int32_t *, int64_t, float *) {
-  return fail(ctx, SPB_ERR_UNSUPPORTED, "trial gather: kernel not built yet");
+__device__ __forceinline__ void mbar_init(uint64_t *bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
 }
-int launch_argmax_rows(spb_context *ctx, const float *, int64_t, int64_t, int32_t *) {
-  return fail(ctx, SPB_ERR_UNSUPPORTED, "argmax: kernel not built yet");
+__device__ __forceinline__ void mbar_expect_tx(uint64_t *bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes)
+               : "memory");
 }
-int run_eer(spb_context *ctx, const float *, const int32_t *, int64_t, double *, double *) {
-  return fail(ctx, SPB_ERR_UNSUPPORTED, "eer: kernel not built yet");
+__device__ __forceinline__ void mbar_arrive(uint64_t *bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
+__device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity) {
+  const uint32_t a = smem_u32(bar);
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      "WAIT_LOOP:\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+      "@p bra WAIT_DONE;\n\t"
+      "bra WAIT_LOOP;\n\t"
+      "WAIT_DONE:\n\t"
+      "}" ::"r"(a), "r"(parity)
+      : "memory");
+}
+__device__ __forceinline__ bool elect_one() {
+  uint32_t pred;
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      "elect.sync _|p, 0xffffffff;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t"
+      "}"
+      : "=r"(pred));
+  return pred != 0;
+}
+__device__ __forceinline__ void tma_load_2d(const CUtensorMap *map, uint64_t *bar, void *dst, int c0,
+                                            int c1) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+      ::"r"(smem_u32(dst)), "l"(map), "r"(smem_u32(bar)), "r"(c0), "r"(c1)
+      : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_commit(uint64_t *bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar))
+               : "memory");
+}
+// D[tmem] (+)= A[smem] * B[smem]^T, TF32 inputs, fp32 accumulate
+__device__ __forceinline__ void umma_tf32(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc,
+                                          uint32_t accumulate) {
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t"
+      "}" ::"r"(tmem_d), "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&v)[32]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+      "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+      : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
+        "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]),
+        "=r"(v[16]), "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]),
+        "=r"(v[24]), "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
+      : "r"(taddr)
+      : "memory");
+  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+
+// K-major operand tile in shared memory, rows of 128 bytes, SWIZZLE_128B (what TMA wrote):
+// start address >> 4, LBO = 1 (unused for swizzled K-major), SBO = 1024 B between 8-row
+// groups, descriptor version 1 (sm_100), layout type 2 (SWIZZLE_128B).
+__device__ __forceinline__ uint64_t umma_desc_sw128(const void *smem) {
+  uint64_t d = 0;
+  d |= (uint64_t)((smem_u32(smem) & 0x3FFFF) >> 4);
+  d |= (uint64_t)1 << 16;
+  d |= (uint64_t)(1024 >> 4) << 32;
+  d |= (uint64_t)1 << 46;
+  d |= (uint64_t)2 << 61;
+  return d;
+}
+
+// ------------------------------------------------------------------------------------
+// prologue: normalise + TF32 hi/lo split, one warp per row
+// ------------------------------------------------------------------------------------
+__device__ __forceinline__ float tf32_round(float x) {
+  uint32_t r;
+  asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(x));
+  return __uint_as_float(r);
+}
+
+__global__ void __launch_bounds__(256)
+normalize_split_kernel(const float *__restrict__ X, long long rows, int d, int dp,
+                       float *__restrict__ hi, float *__restrict__ lo) {
+  const int lane = threadIdx.x & 31;
+  const long long row = (long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (row >= rows) return;
+  const float *x = X + row * d;
+  float ss = 0.f;
+  for (int c = lane; c < d; c += 32) {
+    const float v = __ldg(x + c);
+    ss = fmaf(v, v, ss);
+  }
+#pragma unroll
+  for (int o = 16; o >= 1; o >>= 1) ss += __shfl_xor_sync(0xffffffffu, ss, o);
+  // sklearn normalize(): zero-norm rows are divided by 1 (they stay zero)
+  const float nrm = sqrtf(ss);
+  const float inv = (nrm == 0.f) ? 1.f : 1.f / nrm;
+  for (int c = lane; c < dp; c += 32) {
+    const float v = (c < d) ? __ldg(x + c) * inv : 0.f;
+    const float h = tf32_round(v);
+    hi[row * dp + c] = h;
+    lo[row * dp + c] = tf32_round(v - h);
+  }
+}
+
+// ------------------------------------------------------------------------------------
+// cosine GEMM
+// ------------------------------------------------------------------------------------
+constexpr int kBM = 128, kBN = 256, kBK = 32;  // kBK floats == one 128-byte swizzle row
+constexpr int kStages = 2;
+constexpr int kUmmaK = 8;                      // tf32
+constexpr int kGemmThreads = 192;              // warp 0 TMA, warp 1 MMA, warps 2..5 epilogue
+constexpr uint32_t kABytes = kBM * kBK * 4;    // 16 KB
+constexpr uint32_t kBBytes = kBN * kBK * 4;    // 32 KB
+constexpr uint32_t kStageBytes = 2 * kABytes + 2 * kBBytes;  // 96 KB
+constexpr int kEpiPitch = 33;
+constexpr uint32_t kEpiBytes = 4 * 32 * kEpiPitch * 4;
+constexpr uint32_t kGemmSmem = 1024 /* alignment slack */ + kStages * kStageBytes + kEpiBytes + 128;
+// instruction descriptor: D = F32 (bits 4-5 = 1), A = B = TF32 (bits 7-9, 10-12 = 2), both
+// K-major, N >> 3 at bit 17, M >> 4 at bit 24
+constexpr uint32_t kIdesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(kBN >> 3) << 17) |
+                            ((uint32_t)(kBM >> 4) << 24);
+
+struct GemmParams {
+  float *S;
+  long long m, n;
+  int kblocks;
+  int tiles_m, tiles_n;
+};
+
+__global__ void __launch_bounds__(kGemmThreads, 1)
+cosine_gemm_kernel(const __grid_constant__ CUtensorMap map_ehi, const __grid_constant__ CUtensorMap map_elo,
+                   const __grid_constant__ CUtensorMap map_thi, const __grid_constant__ CUtensorMap map_tlo,
+                   const GemmParams p) {
+  extern __shared__ unsigned char smem_raw[];
+  unsigned char *base = reinterpret_cast<unsigned char *>(
+      ((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);  // SWIZZLE_128B wants 1024-byte alignment
+  float *s_epi = reinterpret_cast<float *>(base + kStages * kStageBytes);
+  uint64_t *bars = reinterpret_cast<uint64_t *>(base + kStages * kStageBytes + kEpiBytes);
+  uint64_t *full = bars;                 // [kStages]
+  uint64_t *empty = bars + kStages;      // [kStages]
+  uint64_t *acc_full = bars + 2 * kStages;       // [2]
+  uint64_t *acc_empty = bars + 2 * kStages + 2;  // [2]
+  uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + 2 * kStages + 4);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const long long num_tiles = (long long)p.tiles_m * p.tiles_n;
+
+  if (warp == 0 && lane == 0) {
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&map_ehi) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&map_elo) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&map_thi) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&map_tlo) : "memory");
+    for (int s = 0; s < kStages; ++s) {
+      mbar_init(&full[s], 1);
+      mbar_init(&empty[s], 1);
+    }
+    for (int a = 0; a < 2; ++a) {
+      mbar_init(&acc_full[a], 1);
+      mbar_init(&acc_empty[a], 4);  // one arrival per epilogue warp
+    }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 1) {
+    // 512 TMEM columns: two 128 x 256 fp32 accumulators (one CTA per SM, so no contention)
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)),
+                 "r"(512u)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // ===== TMA producer =====
+    if (elect_one()) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (long long t = blockIdx.x; t < num_tiles; t += gridDim.x) {
+        const int tm = (int)(t % p.tiles_m), tn = (int)(t / p.tiles_m);
+        for (int kb = 0; kb < p.kblocks; ++kb) {
+          mbar_wait(&empty[stage], phase ^ 1);
+          unsigned char *st = base + stage * kStageBytes;
+          mbar_expect_tx(&full[stage], kStageBytes);
+          tma_load_2d(&map_ehi, &full[stage], st, kb * kBK, tm * kBM);
+          tma_load_2d(&map_elo, &full[stage], st + kABytes, kb * kBK, tm * kBM);
+          tma_load_2d(&map_thi, &full[stage], st + 2 * kABytes, kb * kBK, tn * kBN);
+          tma_load_2d(&map_tlo, &full[stage], st + 2 * kABytes + kBBytes, kb * kBK, tn * kBN);
+          if (++stage == kStages) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===== MMA issuer: one elected thread =====
+    if (elect_one()) {
+      int stage = 0;
+      uint32_t phase = 0;
+      long long it = 0;
+      for (long long t = blockIdx.x; t < num_tiles; t += gridDim.x, ++it) {
+        const uint32_t acc = (uint32_t)(it & 1);
+        const uint32_t acc_phase = (uint32_t)((it >> 1) & 1);
+        mbar_wait(&acc_empty[acc], acc_phase ^ 1);  // epilogue has drained this accumulator
+        tc_fence_after();
+        const uint32_t tmem_d = tmem_base + acc * kBN;
+        for (int kb = 0; kb < p.kblocks; ++kb) {
+          mbar_wait(&full[stage], phase);
+          tc_fence_after();
+          unsigned char *st = base + stage * kStageBytes;
+          const uint64_t a_hi = umma_desc_sw128(st);
+          const uint64_t a_lo = umma_desc_sw128(st + kABytes);
+          const uint64_t b_hi = umma_desc_sw128(st + 2 * kABytes);
+          const uint64_t b_lo = umma_desc_sw128(st + 2 * kABytes + kBBytes);
+          // small terms first: lo.hi, hi.lo, then hi.hi
+#pragma unroll
+          for (int k = 0; k < kBK / kUmmaK; ++k) {
+            const uint64_t adv = (uint64_t)((k * kUmmaK * 4) >> 4);  // 32 bytes along K per step
+            umma_tf32(tmem_d, a_lo + adv, b_hi + adv, kIdesc, (kb | k) != 0);
+          }
+#pragma unroll
+          for (int k = 0; k < kBK / kUmmaK; ++k) {
+            const uint64_t adv = (uint64_t)((k * kUmmaK * 4) >> 4);
+            umma_tf32(tmem_d, a_hi + adv, b_lo + adv, kIdesc, 1u);
+          }
+#pragma unroll
+          for (int k = 0; k < kBK / kUmmaK; ++k) {
+            const uint64_t adv = (uint64_t)((k * kUmmaK * 4) >> 4);
+            umma_tf32(tmem_d, a_hi + adv, b_hi + adv, kIdesc, 1u);
+          }
+          tc_commit(&empty[stage]);  // frees the smem stage when these MMAs retire
+          if (++stage == kStages) { stage = 0; phase ^= 1; }
+        }
+        tc_commit(&acc_full[acc]);   // accumulator complete -> epilogue
+      }
+    }
+  } else {
+    // ===== epilogue: warps 2..5, TMEM lane quadrant = warp % 4 =====
+    const int quad = warp & 3;
+    float *my = s_epi + (warp - 2) * 32 * kEpiPitch;
+    long long it = 0;
+    for (long long t = blockIdx.x; t < num_tiles; t += gridDim.x, ++it) {
+      const int tm = (int)(t % p.tiles_m), tn = (int)(t / p.tiles_m);
+      const uint32_t acc = (uint32_t)(it & 1);
+      const uint32_t acc_phase = (uint32_t)((it >> 1) & 1);
+      mbar_wait(&acc_full[acc], acc_phase);
+      tc_fence_after();
+      const long long row_base = (long long)tm * kBM + quad * 32;
+      const long long col_base = (long long)tn * kBN;
+      const uint32_t taddr = tmem_base + ((uint32_t)(quad * 32) << 16) + acc * kBN;
+#pragma unroll 1
+      for (int ch = 0; ch < kBN / 32; ++ch) {
+        uint32_t v[32];
+        tmem_ld32(taddr + ch * 32, v);
+        // lane = row of the quadrant; transpose through smem so stores run along columns
+        __syncwarp();
+#pragma unroll
+        for (int j = 0; j < 32; ++j) my[lane * kEpiPitch + j] = __uint_as_float(v[j]);
+        __syncwarp();
+        const long long col = col_base + ch * 32 + lane;
+        if (col < p.n) {
+#pragma unroll 8
+          for (int r = 0; r < 32; ++r) {
+            const long long row = row_base + r;
+            if (row < p.m) p.S[row * p.n + col] = my[r * kEpiPitch + lane];
+          }
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&acc_empty[acc]);
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512u) : "memory");
+  }
+}
+
+// ------------------------------------------------------------------------------------
+// host side of the cosine GEMM
+// ------------------------------------------------------------------------------------
+typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *,
+                                  const cuuint64_t *, const cuuint32_t *, const cuuint32_t *,
+                                  CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion,
+                                  CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn get_encode_fn(spb_context *ctx) {
+  static EncodeTiledFn fn = nullptr;
+  if (fn) return fn;
+  void *p = nullptr;
+  cudaDriverEntryPointQueryResult q;
+  cudaError_t e = cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q);
+  if (e != cudaSuccess || q != cudaDriverEntryPointSuccess || !p) {
+    cudaGetLastError();
+    fail(ctx, SPB_ERR_CUDA, "cuTensorMapEncodeTiled is not available from the driver");
+    return nullptr;
+  }
+  fn = (EncodeTiledFn)p;
+  return fn;
+}
+
+// (rows, dp) row-major fp32, box = (kBK columns, box_rows), SWIZZLE_128B, OOB rows read as 0
+static int make_operand_map(spb_context *ctx, CUtensorMap *map, const float *ptr, long long rows, int dp,
+                            int box_rows) {
+  EncodeTiledFn enc = get_encode_fn(ctx);
+  if (!enc) return SPB_ERR_CUDA;
+  cuuint64_t dims[2] = {(cuuint64_t)dp, (cuuint64_t)rows};
+  cuuint64_t strides[1] = {(cuuint64_t)dp * 4};
+  cuuint32_t box[2] = {(cuuint32_t)kBK, (cuuint32_t)box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = enc(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, (void *)ptr, dims, strides, box, estr,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) return fail(ctx, SPB_ERR_CUDA, "cuTensorMapEncodeTiled failed (" + std::to_string((int)r) + ")");
+  return SPB_OK;
+}
+
+int launch_cosine_scores(spb_context *ctx, const float *d_E, int64_t m, const float *d_T, int64_t n, int d,
+                         float *d_S) {
+  if (m == 0 || n == 0) return SPB_OK;
+  const int dp = (d + kBK - 1) / kBK * kBK;
+  const size_t e_elems = (size_t)m * dp, t_elems = (size_t)n * dp;
+  // slot 6: [E_hi | E_lo | T_hi | T_lo], each block 1 KB aligned
+  auto al = [](size_t x) { return (x + 255) & ~(size_t)255; };
+  float *buf = (float *)scratch(ctx, 6, (2 * al(e_elems) + 2 * al(t_elems)) * 4);
+  if (!buf) return SPB_ERR_CUDA;
+  float *e_hi = buf, *e_lo = e_hi + al(e_elems), *t_hi = e_lo + al(e_elems), *t_lo = t_hi + al(t_elems);
+  const int rows_per_block = 256 / 32;
+  normalize_split_kernel<<<(unsigned)((m + rows_per_block - 1) / rows_per_block), 256, 0, ctx->stream>>>(
+      d_E, m, d, dp, e_hi, e_lo);
+  SPB_LAUNCH_CHECK(ctx, "normalize_split_kernel(E)");
+  normalize_split_kernel<<<(unsigned)((n + rows_per_block - 1) / rows_per_block), 256, 0, ctx->stream>>>(
+      d_T, n, d, dp, t_hi, t_lo);
+  SPB_LAUNCH_CHECK(ctx, "normalize_split_kernel(T)");
+  CUtensorMap m_ehi, m_elo, m_thi, m_tlo;
+  int rc;
+  if ((rc = make_operand_map(ctx, &m_ehi, e_hi, m, dp, kBM)) || (rc = make_operand_map(ctx, &m_elo, e_lo, m, dp, kBM)) ||
+      (rc = make_operand_map(ctx, &m_thi, t_hi, n, dp, kBN)) || (rc = make_operand_map(ctx, &m_tlo, t_lo, n, dp, kBN)))
+    return rc;
+  GemmParams p;
+  p.S = d_S;
+  p.m = m;
+  p.n = n;
+  p.kblocks = dp / kBK;
+  p.tiles_m = (int)((m + kBM - 1) / kBM);
+  p.tiles_n = (int)((n + kBN - 1) / kBN);
+  static bool attr_set = false;
+  if (!attr_set) {
+    SPB_CUDA(ctx, cudaFuncSetAttribute(cosine_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kGemmSmem));
+    attr_set = true;
+  }
+  long long grid = std::min<long long>((long long)p.tiles_m * p.tiles_n, ctx->sm_count);
+  const size_t tb = timing_begin(ctx);
+  cosine_gemm_kernel<<<(unsigned)grid, kGemmThreads, kGemmSmem, ctx->stream>>>(m_ehi, m_elo, m_thi, m_tlo, p);
+  timing_end(ctx, 3, tb);
+  SPB_LAUNCH_CHECK(ctx, "cosine_gemm_kernel");
+  return SPB_OK;
+}
+
+// ------------------------------------------------------------------------------------
+// trial gather and row argmax
+// ------------------------------------------------------------------------------------
+__global__ void trial_gather_kernel(const float *__restrict__ S, long long m, long long n,
+                                    const int32_t *__restrict__ ti, const int32_t *__restrict__ tj,
+                                    long long nt, float *__restrict__ out, int *__restrict__ bad) {
+  const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= nt) return;
+  const long long i = ti[t], j = tj[t];
+  if (i < 0 || i >= m || j < 0 || j >= n) {
+    *bad = 1;
+    out[t] = 0.f;
+    return;
+  }
+  out[t] = __ldg(S + i * n + j);
+}
+
+int launch_trial_gather(spb_context *ctx, const float *d_S, int64_t m, int64_t n, const int32_t *ti,
+                        const int32_t *tj, int64_t nt, float *out) {
+  if (nt <= 0) return SPB_OK;
+  int *d_bad = (int *)scratch(ctx, 7, 64);
+  if (!d_bad) return SPB_ERR_CUDA;
+  SPB_CUDA(ctx, cudaMemsetAsync(d_bad, 0, 4, ctx->stream));
+  trial_gather_kernel<<<(unsigned)((nt + 255) / 256), 256, 0, ctx->stream>>>(d_S, m, n, ti, tj, nt, out, d_bad);
+  SPB_LAUNCH_CHECK(ctx, "trial_gather_kernel");
+  int bad = 0;
+  SPB_CUDA(ctx, cudaMemcpyAsync(&bad, d_bad, 4, cudaMemcpyDeviceToHost, ctx->stream));
+  SPB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  if (bad) return fail(ctx, SPB_ERR_INVALID, "trial index out of range");
+  return SPB_OK;
+}
+
+// first index of the row maximum (np.argmax, evaluation.py:79); one warp per row
+__global__ void __launch_bounds__(256)
+argmax_rows_kernel(const float *__restrict__ S, long long m, long long n, int32_t *__restrict__ out) {
+  const int lane = threadIdx.x & 31;
+  const long long row = (long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (row >= m) return;
+  const float *s = S + row * n;
+  float best = -INFINITY;
+  long long bi = n;  // larger than any valid index
+  for (long long c = lane; c < n; c += 32) {
+    const float v = __ldg(s + c);
+    if (v > best || (bi == n)) { best = v; bi = c; }
+  }
+#pragma unroll
+  for (int o = 16; o >= 1; o >>= 1) {
+    const float ov = __shfl_xor_sync(0xffffffffu, best, o);
+    const long long oi = __shfl_xor_sync(0xffffffffu, bi, o);
+    if (oi < n && (bi == n || ov > best || (ov == best && oi < bi))) { best = ov; bi = oi; }
+  }
+  if (lane == 0) out[row] = (int32_t)bi;
+}
+
+int launch_argmax_rows(spb_context *ctx, const float *d_S, int64_t m, int64_t n, int32_t *out) {
+  if (m <= 0) return SPB_OK;
+  if (n <= 0) return fail(ctx, SPB_ERR_INVALID, "attempt to get argmax of an empty sequence");
+  argmax_rows_kernel<<<(unsigned)((m + 7) / 8), 256, 0, ctx->stream>>>(d_S, m, n, out);
+  SPB_LAUNCH_CHECK(ctx, "argmax_rows_kernel");
+  return SPB_OK;
+}
+
+// ------------------------------------------------------------------------------------
+// EER / AUC (evaluation.py:47-52)
+//   sort (score, label) by descending score; ROC vertices sit at the last element of every
+//   run of equal scores (sklearn _binary_clf_curve); tp = inclusive sum of labels,
+//   fp = index + 1 - tp.  drop_intermediate only removes collinear vertices, so the
+//   piecewise-linear curve -- and with it brentq's root and the trapezoid area -- is the same
+//   without it.  All counting is integer; g = 1 - fpr - tpr is compared through
+//   P*N - fp*P - tp*N (exact in int64).  The vertex before the first g <= 0 vertex comes
+//   from a max-scan of (group start index, tp before the group) packed in 64 bits.
+// ------------------------------------------------------------------------------------
+struct MaxU64 {
+  __device__ __forceinline__ unsigned long long operator()(unsigned long long a, unsigned long long b) const {
+    return a > b ? a : b;
+  }
+};
+
+__global__ void group_start_kernel(const float *__restrict__ s, const int32_t *__restrict__ lab,
+                                   const int32_t *__restrict__ tp, long long n,
+                                   unsigned long long *__restrict__ marks) {
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const bool start = (i == 0) || (s[i - 1] != s[i]);
+  const unsigned long long tp_before = (unsigned long long)(tp[i] - (lab[i] != 0 ? 1 : 0));
+  marks[i] = start ? (((unsigned long long)i << 32) | tp_before) : 0ull;
+}
+
+struct EerAccum {
+  unsigned long long first_v;   // smallest group-end index with g <= 0
+  unsigned long long auc2;      // sum (fp_i - fp_prev) * (tp_i + tp_prev)  == 2 * P * N * AUC
+};
+
+__global__ void __launch_bounds__(256)
+roc_vertex_kernel(const float *__restrict__ s, const int32_t *__restrict__ tp,
+                  const unsigned long long *__restrict__ gs, long long n, long long P, long long N,
+                  EerAccum *__restrict__ acc) {
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  unsigned long long area = 0;
+  if (i < n) {
+    const bool end = (i == n - 1) || (s[i] != s[i + 1]);
+    if (end) {
+      const long long tpi = tp[i], fpi = i + 1 - tpi;
+      const long long start = (long long)(gs[i] >> 32), tpp = (long long)(gs[i] & 0xffffffffull);
+      const long long fpp = start - tpp;
+      area = (unsigned long long)(fpi - fpp) * (unsigned long long)(tpi + tpp);
+      const long long g = P * N - fpi * P - tpi * N;
+      if (g <= 0) atomicMin(&acc->first_v, (unsigned long long)i);
+    }
+  }
+  typedef cub::BlockReduce<unsigned long long, 256> Reduce;
+  __shared__ typename Reduce::TempStorage tmp;
+  const unsigned long long tot = Reduce(tmp).Sum(area);
+  if (threadIdx.x == 0 && tot) atomicAdd(&acc->auc2, tot);
+}
+
+__global__ void eer_solve_kernel(const int32_t *__restrict__ tp, const unsigned long long *__restrict__ gs,
+                                 long long P, long long N, const EerAccum *__restrict__ acc,
+                                 double *__restrict__ out) {
+  const long long v = (long long)acc->first_v;
+  const long long tpv = tp[v], fpv = v + 1 - tpv;
+  const long long start = (long long)(gs[v] >> 32), tpu = (long long)(gs[v] & 0xffffffffull);
+  const long long fpu = start - tpu;
+  const double fpr_v = (double)fpv / (double)N, tpr_v = (double)tpv / (double)P;
+  const double fpr_u = (double)fpu / (double)N, tpr_u = (double)tpu / (double)P;
+  double eer;
+  if (P * N - fpv * P - tpv * N == 0) {
+    eer = fpr_v;
+  } else {
+    const double dx = fpr_v - fpr_u, dy = tpr_v - tpr_u;
+    eer = (fpv == fpu) ? fpr_u : fpr_u + (1.0 - fpr_u - tpr_u) * dx / (dx + dy);
+  }
+  out[0] = eer;
+  out[1] = (double)acc->auc2 / (2.0 * (double)P * (double)N);
+}
+
+int run_eer(spb_context *ctx, const float *d_scores, const int32_t *d_labels, int64_t n, double *eer,
+            double *auc) {
+  if (n <= 0) return fail(ctx, SPB_ERR_INVALID, "eer: no trials");
+  if (n >= ((int64_t)1 << 31) - 1) return fail(ctx, SPB_ERR_INVALID, "eer: too many trials");
+  const int in = (int)n;
+  size_t sort_bytes = 0, sum_bytes = 0, max_bytes = 0;
+  cub::DeviceRadixSort::SortPairsDescending(nullptr, sort_bytes, (const float *)nullptr, (float *)nullptr,
+                                            (const int32_t *)nullptr, (int32_t *)nullptr, in, 0, 32, ctx->stream);
+  cub::DeviceScan::InclusiveSum(nullptr, sum_bytes, (const int32_t *)nullptr, (int32_t *)nullptr, in, ctx->stream);
+  cub::DeviceScan::InclusiveScan(nullptr, max_bytes, (const unsigned long long *)nullptr,
+                                 (unsigned long long *)nullptr, MaxU64(), in, ctx->stream);
+  const size_t tmp_bytes = std::max(sort_bytes, std::max(sum_bytes, max_bytes));
+  auto al = [](size_t x) { return (x + 255) & ~(size_t)255; };
+  const size_t off_s = 0, off_l = off_s + al((size_t)n * 4), off_tp = off_l + al((size_t)n * 4),
+               off_marks = off_tp + al((size_t)n * 4), off_gs = off_marks + al((size_t)n * 8),
+               off_acc = off_gs + al((size_t)n * 8), off_out = off_acc + 256, off_tmp = off_out + 256;
+  unsigned char *buf = (unsigned char *)scratch(ctx, 7, off_tmp + al(tmp_bytes));
+  if (!buf) return SPB_ERR_CUDA;
+  float *s = (float *)(buf + off_s);
+  int32_t *lab = (int32_t *)(buf + off_l), *tp = (int32_t *)(buf + off_tp);
+  unsigned long long *marks = (unsigned long long *)(buf + off_marks), *gs = (unsigned long long *)(buf + off_gs);
+  EerAccum *acc = (EerAccum *)(buf + off_acc);
+  double *d_out = (double *)(buf + off_out);
+  void *tmp = buf + off_tmp;
+  size_t tb = tmp_bytes;
+  SPB_CUDA(ctx, cub::DeviceRadixSort::SortPairsDescending(tmp, tb, d_scores, s, d_labels, lab, in, 0, 32, ctx->stream));
+  ctx->launches += 1;
+  tb = tmp_bytes;
+  SPB_CUDA(ctx, cub::DeviceScan::InclusiveSum(tmp, tb, lab, tp, in, ctx->stream));
+  ctx->launches += 1;
+  int32_t P32 = 0;
+  SPB_CUDA(ctx, cudaMemcpyAsync(&P32, tp + (n - 1), 4, cudaMemcpyDeviceToHost, ctx->stream));
+  const unsigned blocks = (unsigned)((n + 255) / 256);
+  group_start_kernel<<<blocks, 256, 0, ctx->stream>>>(s, lab, tp, n, marks);
+  SPB_LAUNCH_CHECK(ctx, "group_start_kernel");
+  tb = tmp_bytes;
+  SPB_CUDA(ctx, cub::DeviceScan::InclusiveScan(tmp, tb, marks, gs, MaxU64(), in, ctx->stream));
+  ctx->launches += 1;
+  SPB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  const long long P = P32, N = n - P32;
+  // sklearn: roc_auc_score raises ValueError when only one class is present
+  if (P == 0 || N == 0) return fail(ctx, SPB_ERR_INVALID, "Only one class present in y_true. ROC AUC score is not defined in that case.");
+  const EerAccum init = {~0ull, 0ull};
+  SPB_CUDA(ctx, cudaMemcpyAsync(acc, &init, sizeof(init), cudaMemcpyHostToDevice, ctx->stream));
+  roc_vertex_kernel<<<blocks, 256, 0, ctx->stream>>>(s, tp, gs, n, P, N, acc);
+  SPB_LAUNCH_CHECK(ctx, "roc_vertex_kernel");
+  eer_solve_kernel<<<1, 1, 0, ctx->stream>>>(tp, gs, P, N, acc, d_out);
+  SPB_LAUNCH_CHECK(ctx, "eer_solve_kernel");
+  double h_out[2] = {0, 0};
+  SPB_CUDA(ctx, cudaMemcpyAsync(h_out, d_out, 16, cudaMemcpyDeviceToHost, ctx->stream));
+  SPB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  if (eer) *eer = h_out[0];
+  if (auc) *auc = h_out[1];
+  return SPB_OK;
+}
+
 }  // namespace spb
 
 using namespace spb;
-extern "C" {
-int spb_cosine_scores(spb_context *ctx, const float *, int64_t, const float *, int64_t, int32_t, float *) {
-  return fail(ctx, SPB_ERR_UNSUPPORTED, "cosine scores: kernel not built yet");
+
+#define SPB_REQ(ctx, cond, msg) \
+  do {                          \
+    if (!(cond)) return fail(ctx, SPB_ERR_INVALID, msg); \
+  } while (0)
+
+static int check_scores_args(spb_context *ctx, const void *E, int64_t m, const void *T, int64_t n, int32_t d,
+                             const void *S) {
+  SPB_REQ(ctx, ctx != nullptr, "cosine scores: NULL context");
+  SPB_REQ(ctx, m >= 0 && n >= 0 && d >= 1, "cosine scores: bad shape");
+  SPB_REQ(ctx, d <= 65536, "cosine scores: embedding dimension too large");
+  if (m > 0 && n > 0) SPB_REQ(ctx, E && T && S, "cosine scores: NULL buffer");
+  return SPB_OK;
 }
-int spb_cosine_scores_dev(spb_context *ctx, const float *E, int64_t m, const float *T, int64_t n, int32_t d, float *S) {
+
+extern "C" {
+
+int spb_cosine_scores_dev(spb_context *ctx, const float *E, int64_t m, const float *T, int64_t n, int32_t d,
+                          float *S) {
+  int rc = check_scores_args(ctx, E, m, T, n, d, S);
+  if (rc) return rc;
+  SPB_CUDA(ctx, cudaSetDevice(ctx->device));
   return launch_cosine_scores(ctx, E, m, T, n, d, S);
 }
-int spb_trial_scores_dev(spb_context *ctx, const float *S, int64_t m, int64_t n, const int32_t *ti, const int32_t *tj, int64_t nt, float *out) {
+
+int spb_cosine_scores(spb_context *ctx, const float *E, int64_t m, const float *T, int64_t n, int32_t d,
+                      float *S) {
+  int rc = check_scores_args(ctx, E, m, T, n, d, S);
+  if (rc) return rc;
+  if (m == 0 || n == 0) return SPB_OK;
+  SPB_CUDA(ctx, cudaSetDevice(ctx->device));
+  float *d_E = (float *)scratch(ctx, 0, (size_t)m * d * 4);
+  float *d_T = (float *)scratch(ctx, 5, (size_t)n * d * 4);
+  float *d_S = (float *)scratch(ctx, 1, (size_t)m * n * 4);
+  if (!d_E || !d_T || !d_S) return SPB_ERR_CUDA;
+  SPB_CUDA(ctx, cudaMemcpyAsync(d_E, E, (size_t)m * d * 4, cudaMemcpyHostToDevice, ctx->stream));
+  SPB_CUDA(ctx, cudaMemcpyAsync(d_T, T, (size_t)n * d * 4, cudaMemcpyHostToDevice, ctx->stream));
+  rc = launch_cosine_scores(ctx, d_E, m, d_T, n, d, d_S);
+  if (rc) return rc;
+  SPB_CUDA(ctx, cudaMemcpyAsync(S, d_S, (size_t)m * n * 4, cudaMemcpyDeviceToHost, ctx->stream));
+  SPB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  return SPB_OK;
+}
+
+int spb_trial_scores_dev(spb_context *ctx, const float *S, int64_t m, int64_t n, const int32_t *ti,
+                         const int32_t *tj, int64_t nt, float *out) {
+  SPB_REQ(ctx, ctx != nullptr, "trial scores: NULL context");
+  SPB_REQ(ctx, m >= 0 && n >= 0 && nt >= 0, "trial scores: bad shape");
+  if (nt == 0) return SPB_OK;
+  SPB_REQ(ctx, S && ti && tj && out, "trial scores: NULL buffer");
+  SPB_CUDA(ctx, cudaSetDevice(ctx->device));
   return launch_trial_gather(ctx, S, m, n, ti, tj, nt, out);
 }
+
 int spb_argmax_rows_dev(spb_context *ctx, const float *S, int64_t m, int64_t n, int32_t *out) {
+  SPB_REQ(ctx, ctx != nullptr, "argmax: NULL context");
+  SPB_REQ(ctx, m >= 0 && n >= 0, "argmax: bad shape");
+  if (m == 0) return SPB_OK;
+  SPB_REQ(ctx, S && out, "argmax: NULL buffer");
+  SPB_CUDA(ctx, cudaSetDevice(ctx->device));
   return launch_argmax_rows(ctx, S, m, n, out);
 }
-int spb_eer(spb_context *ctx, const float *, const int32_t *, int64_t, double *, double *) {
-  return fail(ctx, SPB_ERR_UNSUPPORTED, "eer: kernel not built yet");
-}
+
 int spb_eer_dev(spb_context *ctx, const float *s, const int32_t *l, int64_t n, double *eer, double *auc) {
+  SPB_REQ(ctx, ctx != nullptr, "eer: NULL context");
+  SPB_REQ(ctx, n > 0 && s && l, "eer: no trials or NULL buffer");
+  SPB_CUDA(ctx, cudaSetDevice(ctx->device));
   return run_eer(ctx, s, l, n, eer, auc);
 }
+
+int spb_eer(spb_context *ctx, const float *s, const int32_t *l, int64_t n, double *eer, double *auc) {
+  SPB_REQ(ctx, ctx != nullptr, "eer: NULL context");
+  SPB_REQ(ctx, n > 0 && s && l, "eer: no trials or NULL buffer");
+  SPB_CUDA(ctx, cudaSetDevice(ctx->device));
+  float *d_s = (float *)scratch(ctx, 0, (size_t)n * 4);
+  int32_t *d_l = (int32_t *)scratch(ctx, 1, (size_t)n * 4);
+  if (!d_s || !d_l) return SPB_ERR_CUDA;
+  SPB_CUDA(ctx, cudaMemcpyAsync(d_s, s, (size_t)n * 4, cudaMemcpyHostToDevice, ctx->stream));
+  SPB_CUDA(ctx, cudaMemcpyAsync(d_l, l, (size_t)n * 4, cudaMemcpyHostToDevice, ctx->stream));
+  return run_eer(ctx, d_s, d_l, n, eer, auc);
 }
+
+}  // extern "C"

@@ -53,7 +53,7 @@ struct spb_context {
   bool timing = false;
   std::vector<cudaEvent_t> ev_pool;
   size_t ev_used = 0;
-  std::vector<std::pair<size_t, size_t>> ev_pairs[3];  // indices into ev_pool
+  std::vector<std::pair<size_t, size_t>> ev_pairs[4];  // indices into ev_pool
 };
 
 struct spb_plan {
