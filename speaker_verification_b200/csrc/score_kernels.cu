@@ -15,9 +15,11 @@
 //               (256 x 32) once and one elected thread issues three groups of four
 //               tcgen05.mma.kind::tf32 (M128 N256 K8): lo.hi + hi.lo + hi.hi, all accumulating
 //               in the same fp32 TMEM tile -- the 3xTF32 split the 1e-5 tolerance needs
-//               (single-pass TF32 is ~7e-4 relative on 512-d embeddings).  Two TMEM accumulators
-//               (2 x 256 columns) let the epilogue of tile i overlap the MMAs of tile i+1.
-//   epilogue  : 4 warps, tcgen05.ld 32x32b.x32 -> registers -> padded smem transpose ->
+//               (single-pass TF32 is ~7e-4 relative on 512-d embeddings).  TMEM accumulation
+//               truncates, so a chain is cut every 4 k-blocks: chunks alternate between two
+//               TMEM accumulators (2 x 256 columns) and are summed by the epilogue warps.
+//   epilogue  : 8 warps, tcgen05.ld 32x32b.x32 of every chunk -> fp32 register accumulators
+//               (round-to-nearest adds) -> at the end of a tile padded smem transpose ->
 //               row-contiguous 128-byte global stores (the row pitch 4n bytes is in general not
 //               a multiple of 16, so a TMA store of S is not possible).
 #include <cuda.h>
@@ -160,12 +162,13 @@ normalize_split_kernel(const float *__restrict__ X, long long rows, int d, int d
 constexpr int kBM = 128, kBN = 256, kBK = 32;  // kBK floats == one 128-byte swizzle row
 constexpr int kStages = 2;
 constexpr int kUmmaK = 8;                      // tf32
-constexpr int kGemmThreads = 192;              // warp 0 TMA, warp 1 MMA, warps 2..5 epilogue
+constexpr int kGemmThreads = 320;              // warp 0 TMA, warp 1 MMA, warps 2..9 epilogue
+constexpr int kMaxChunkKB = 4;                 // at most this many k-blocks accumulate in TMEM before a drain
 constexpr uint32_t kABytes = kBM * kBK * 4;    // 16 KB
 constexpr uint32_t kBBytes = kBN * kBK * 4;    // 32 KB
 constexpr uint32_t kStageBytes = 2 * kABytes + 2 * kBBytes;  // 96 KB
 constexpr int kEpiPitch = 33;
-constexpr uint32_t kEpiBytes = 4 * 32 * kEpiPitch * 4;
+constexpr uint32_t kEpiBytes = 8 * 32 * kEpiPitch * 4;
 constexpr uint32_t kGemmSmem = 1024 /* alignment slack */ + kStages * kStageBytes + kEpiBytes + 128;
 // instruction descriptor: D = F32 (bits 4-5 = 1), A = B = TF32 (bits 7-9, 10-12 = 2), both
 // K-major, N >> 3 at bit 17, M >> 4 at bit 24
@@ -176,6 +179,7 @@ struct GemmParams {
   float *S;
   long long m, n;
   int kblocks;
+  int chunk_kb;  // k-blocks per TMEM accumulation chain (1..kMaxChunkKB)
   int tiles_m, tiles_n;
 };
 
@@ -209,7 +213,7 @@ cosine_gemm_kernel(const __grid_constant__ CUtensorMap map_ehi, const __grid_con
     }
     for (int a = 0; a < 2; ++a) {
       mbar_init(&acc_full[a], 1);
-      mbar_init(&acc_empty[a], 4);  // one arrival per epilogue warp
+      mbar_init(&acc_empty[a], 8);  // one arrival per epilogue warp
     }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
@@ -246,68 +250,89 @@ cosine_gemm_kernel(const __grid_constant__ CUtensorMap map_ehi, const __grid_con
     }
   } else if (warp == 1) {
     // ===== MMA issuer: one elected thread =====
+    // The tensor core adds into the fp32 TMEM accumulator with truncation (measured: a 192-MMA
+    // chain loses ~1e-6 absolute, always towards zero), so a chain is cut after chunk_kb
+    // k-blocks: each chunk starts a fresh accumulator (alternating between the two TMEM
+    // buffers) and the epilogue warps sum the chunks in registers with round-to-nearest adds.
     if (elect_one()) {
       int stage = 0;
       uint32_t phase = 0;
-      long long it = 0;
-      for (long long t = blockIdx.x; t < num_tiles; t += gridDim.x, ++it) {
-        const uint32_t acc = (uint32_t)(it & 1);
-        const uint32_t acc_phase = (uint32_t)((it >> 1) & 1);
-        mbar_wait(&acc_empty[acc], acc_phase ^ 1);  // epilogue has drained this accumulator
-        tc_fence_after();
-        const uint32_t tmem_d = tmem_base + acc * kBN;
-        for (int kb = 0; kb < p.kblocks; ++kb) {
-          mbar_wait(&full[stage], phase);
+      long long cit = 0;  // chunk counter across tiles
+      for (long long t = blockIdx.x; t < num_tiles; t += gridDim.x) {
+        for (int kb0 = 0; kb0 < p.kblocks; kb0 += p.chunk_kb, ++cit) {
+          const uint32_t acc = (uint32_t)(cit & 1);
+          const uint32_t acc_phase = (uint32_t)((cit >> 1) & 1);
+          mbar_wait(&acc_empty[acc], acc_phase ^ 1);  // epilogue has drained this accumulator
           tc_fence_after();
-          unsigned char *st = base + stage * kStageBytes;
-          const uint64_t a_hi = umma_desc_sw128(st);
-          const uint64_t a_lo = umma_desc_sw128(st + kABytes);
-          const uint64_t b_hi = umma_desc_sw128(st + 2 * kABytes);
-          const uint64_t b_lo = umma_desc_sw128(st + 2 * kABytes + kBBytes);
-          // small terms first: lo.hi, hi.lo, then hi.hi
+          const uint32_t tmem_d = tmem_base + acc * kBN;
+          const int kb1 = min(kb0 + p.chunk_kb, p.kblocks);
+          for (int kb = kb0; kb < kb1; ++kb) {
+            mbar_wait(&full[stage], phase);
+            tc_fence_after();
+            unsigned char *st = base + stage * kStageBytes;
+            const uint64_t a_hi = umma_desc_sw128(st);
+            const uint64_t a_lo = umma_desc_sw128(st + kABytes);
+            const uint64_t b_hi = umma_desc_sw128(st + 2 * kABytes);
+            const uint64_t b_lo = umma_desc_sw128(st + 2 * kABytes + kBBytes);
+            // small terms first: lo.hi, hi.lo, then hi.hi
 #pragma unroll
-          for (int k = 0; k < kBK / kUmmaK; ++k) {
-            const uint64_t adv = (uint64_t)((k * kUmmaK * 4) >> 4);  // 32 bytes along K per step
-            umma_tf32(tmem_d, a_lo + adv, b_hi + adv, kIdesc, (kb | k) != 0);
-          }
+            for (int k = 0; k < kBK / kUmmaK; ++k) {
+              const uint64_t adv = (uint64_t)((k * kUmmaK * 4) >> 4);  // 32 bytes along K per step
+              umma_tf32(tmem_d, a_lo + adv, b_hi + adv, kIdesc, (kb != kb0 || k != 0) ? 1u : 0u);
+            }
 #pragma unroll
-          for (int k = 0; k < kBK / kUmmaK; ++k) {
-            const uint64_t adv = (uint64_t)((k * kUmmaK * 4) >> 4);
-            umma_tf32(tmem_d, a_hi + adv, b_lo + adv, kIdesc, 1u);
-          }
+            for (int k = 0; k < kBK / kUmmaK; ++k) {
+              const uint64_t adv = (uint64_t)((k * kUmmaK * 4) >> 4);
+              umma_tf32(tmem_d, a_hi + adv, b_lo + adv, kIdesc, 1u);
+            }
 #pragma unroll
-          for (int k = 0; k < kBK / kUmmaK; ++k) {
-            const uint64_t adv = (uint64_t)((k * kUmmaK * 4) >> 4);
-            umma_tf32(tmem_d, a_hi + adv, b_hi + adv, kIdesc, 1u);
+            for (int k = 0; k < kBK / kUmmaK; ++k) {
+              const uint64_t adv = (uint64_t)((k * kUmmaK * 4) >> 4);
+              umma_tf32(tmem_d, a_hi + adv, b_hi + adv, kIdesc, 1u);
+            }
+            tc_commit(&empty[stage]);  // frees the smem stage when these MMAs retire
+            if (++stage == kStages) { stage = 0; phase ^= 1; }
           }
-          tc_commit(&empty[stage]);  // frees the smem stage when these MMAs retire
-          if (++stage == kStages) { stage = 0; phase ^= 1; }
+          tc_commit(&acc_full[acc]);   // chunk complete -> epilogue
         }
-        tc_commit(&acc_full[acc]);   // accumulator complete -> epilogue
       }
     }
   } else {
-    // ===== epilogue: warps 2..5, TMEM lane quadrant = warp % 4 =====
+    // ===== epilogue: warps 2..9.  TMEM lane quadrant = warp % 4, column half = (warp-2)/4 =====
     const int quad = warp & 3;
+    const int half = (warp - 2) >> 2;
     float *my = s_epi + (warp - 2) * 32 * kEpiPitch;
-    long long it = 0;
-    for (long long t = blockIdx.x; t < num_tiles; t += gridDim.x, ++it) {
+    long long cit = 0;
+    for (long long t = blockIdx.x; t < num_tiles; t += gridDim.x) {
       const int tm = (int)(t % p.tiles_m), tn = (int)(t / p.tiles_m);
-      const uint32_t acc = (uint32_t)(it & 1);
-      const uint32_t acc_phase = (uint32_t)((it >> 1) & 1);
-      mbar_wait(&acc_full[acc], acc_phase);
-      tc_fence_after();
+      float accr[128];
+#pragma unroll
+      for (int j = 0; j < 128; ++j) accr[j] = 0.f;
+      for (int kb0 = 0; kb0 < p.kblocks; kb0 += p.chunk_kb, ++cit) {
+        const uint32_t acc = (uint32_t)(cit & 1);
+        const uint32_t acc_phase = (uint32_t)((cit >> 1) & 1);
+        mbar_wait(&acc_full[acc], acc_phase);
+        tc_fence_after();
+        const uint32_t taddr = tmem_base + ((uint32_t)(quad * 32) << 16) + acc * kBN + half * 128;
+#pragma unroll
+        for (int ch = 0; ch < 4; ++ch) {
+          uint32_t v[32];
+          tmem_ld32(taddr + ch * 32, v);
+#pragma unroll
+          for (int j = 0; j < 32; ++j) accr[ch * 32 + j] += __uint_as_float(v[j]);
+        }
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&acc_empty[acc]);
+      }
+      // write-out: lane = row of the quadrant; transpose through smem so stores run along columns
       const long long row_base = (long long)tm * kBM + quad * 32;
-      const long long col_base = (long long)tn * kBN;
-      const uint32_t taddr = tmem_base + ((uint32_t)(quad * 32) << 16) + acc * kBN;
-#pragma unroll 1
-      for (int ch = 0; ch < kBN / 32; ++ch) {
-        uint32_t v[32];
-        tmem_ld32(taddr + ch * 32, v);
-        // lane = row of the quadrant; transpose through smem so stores run along columns
+      const long long col_base = (long long)tn * kBN + half * 128;
+#pragma unroll
+      for (int ch = 0; ch < 4; ++ch) {
         __syncwarp();
 #pragma unroll
-        for (int j = 0; j < 32; ++j) my[lane * kEpiPitch + j] = __uint_as_float(v[j]);
+        for (int j = 0; j < 32; ++j) my[lane * kEpiPitch + j] = accr[ch * 32 + j];
         __syncwarp();
         const long long col = col_base + ch * 32 + lane;
         if (col < p.n) {
@@ -318,9 +343,6 @@ cosine_gemm_kernel(const __grid_constant__ CUtensorMap map_ehi, const __grid_con
           }
         }
       }
-      tc_fence_before();
-      __syncwarp();
-      if (lane == 0) mbar_arrive(&acc_empty[acc]);
     }
   }
   tc_fence_before();
@@ -397,6 +419,8 @@ int launch_cosine_scores(spb_context *ctx, const float *d_E, int64_t m, const fl
   p.m = m;
   p.n = n;
   p.kblocks = dp / kBK;
+  // short chains for small d (precision), up to 4 k-blocks (48 MMAs) for large d (drain bandwidth)
+  p.chunk_kb = std::max(1, std::min(kMaxChunkKB, p.kblocks / 4));
   p.tiles_m = (int)((m + kBM - 1) / kBM);
   p.tiles_n = (int)((n + kBN - 1) / kBN);
   static bool attr_set = false;
