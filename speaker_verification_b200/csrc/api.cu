@@ -138,6 +138,15 @@ static bool frame_count(int64_t n, int L, int S, int zero_padding, int64_t *F) {
   return f >= 0.0;
 }
 
+void append_big_tiles(std::vector<int4> &v, int utt, int64_t F, int rmax) {
+  if (F <= 0) return;
+  const int64_t nt = (F + rmax - 1) / rmax;
+  int64_t r = (F + nt - 1) / nt;
+  r = (r + 29) / 30 * 30;  // multiple of the 30-row block
+  if (r > rmax) r = rmax;
+  for (int64_t r0 = 0; r0 < F; r0 += r) v.push_back(make_int4(utt, (int)r0, (int)std::min<int64_t>(r, F - r0), 0));
+}
+
 }  // namespace spb
 
 using namespace spb;
@@ -446,7 +455,8 @@ int spb_batch_create(spb_context *ctx, const spb_plan *plan, const int64_t *star
   std::vector<int64_t> tile_off(U + 1, 0), cm_off(U + 1, 0);
   b->h_frame_offsets.assign(U + 1, 0);
   spb_batch &ch = *b;
-  BatchChunk cur{0, 0, 0, 0, 0, 0, 0, 0};
+  BatchChunk cur;
+  cur.u0 = cur.u1 = cur.tile0 = cur.tile1 = cur.cm0 = cur.cm1 = cur.row0 = cur.row1 = 0;
   for (int64_t u = 0; u < U; ++u) {
     int64_t F;
     if (starts[u] < 0 || lengths[u] < 0) {
@@ -474,7 +484,14 @@ int spb_batch_create(spb_context *ctx, const spb_plan *plan, const int64_t *star
       cur.row1 = b->h_frame_offsets[u];
       ch.chunks.push_back(cur);
       ch.max_chunk_rows = std::max(ch.max_chunk_rows, cur.row1 - cur.row0);
-      cur = BatchChunk{u, u, tile_off[u], tile_off[u], cm_off[u], cm_off[u], cur.row1, cur.row1};
+      {
+        BatchChunk nx;
+        nx.u0 = nx.u1 = u;
+        nx.tile0 = nx.tile1 = tile_off[u];
+        nx.cm0 = nx.cm1 = cm_off[u];
+        nx.row0 = nx.row1 = cur.row1;
+        cur = nx;
+      }
     }
   }
   cur.u1 = U;
@@ -488,6 +505,18 @@ int spb_batch_create(spb_context *ctx, const spb_plan *plan, const int64_t *star
   b->total_frames = b->h_frame_offsets[U];
   b->total_tiles = tile_off[U];
   b->total_cm_tiles = cm_off[U];
+  // large-tile cmvnw table: balanced tiles per utterance, longest first inside each chunk
+  std::vector<int4> big;
+  b->big_rmax = (win > 0) ? cmvnw_big_rmax(plan->p.num_filters, win) : 0;
+  if (b->big_rmax > 0) {
+    for (BatchChunk &c : ch.chunks) {
+      c.big0 = (int64_t)big.size();
+      for (int64_t u = c.u0; u < c.u1; ++u) append_big_tiles(big, (int)u, nframes[u], b->big_rmax);
+      c.big1 = (int64_t)big.size();
+      std::stable_sort(big.begin() + c.big0, big.begin() + c.big1,
+                       [](const int4 &x, const int4 &y) { return x.z > y.z; });
+    }
+  }
   auto cleanup = [&](cudaError_t e, const char *what) {
     spb_batch_destroy(b);
     return cuda_fail(ctx, e, what);
@@ -500,6 +529,7 @@ int spb_batch_create(spb_context *ctx, const spb_plan *plan, const int64_t *star
       (e = cudaMalloc(&b->d_frame_offsets, (u_bytes + 1) * 8)) != cudaSuccess ||
       (e = cudaMalloc(&b->d_tiles, (size_t)std::max<int64_t>(b->total_tiles, 1) * sizeof(int2))) != cudaSuccess ||
       (e = cudaMalloc(&b->d_cm_tiles, (size_t)std::max<int64_t>(b->total_cm_tiles, 1) * sizeof(int2))) != cudaSuccess ||
+      (e = cudaMalloc(&b->d_big_tiles, std::max<size_t>(big.size(), 1) * sizeof(int4))) != cudaSuccess ||
       (e = cudaMalloc(&d_tile_off, (u_bytes + 1) * 8)) != cudaSuccess ||
       (e = cudaMalloc(&d_cm_off, (u_bytes + 1) * 8)) != cudaSuccess)
     return cleanup(e, "cudaMalloc(batch)");
@@ -510,6 +540,9 @@ int spb_batch_create(spb_context *ctx, const spb_plan *plan, const int64_t *star
         (e = cudaMemcpyAsync(d_tile_off, tile_off.data(), (size_t)(U + 1) * 8, cudaMemcpyHostToDevice, ctx->stream)) != cudaSuccess ||
         (e = cudaMemcpyAsync(d_cm_off, cm_off.data(), (size_t)(U + 1) * 8, cudaMemcpyHostToDevice, ctx->stream)) != cudaSuccess)
       return cleanup(e, "cudaMemcpyAsync(batch)");
+    if (!big.empty() &&
+        (e = cudaMemcpyAsync(b->d_big_tiles, big.data(), big.size() * sizeof(int4), cudaMemcpyHostToDevice, ctx->stream)) != cudaSuccess)
+      return cleanup(e, "cudaMemcpyAsync(big tiles)");
     int rc = launch_build_tiles(ctx, b->d_nframes, d_tile_off, U, kFftTile, b->d_tiles);
     if (!rc && b->cm_tile_rows)
       rc = launch_build_tiles(ctx, b->d_nframes, d_cm_off, U, b->cm_tile_rows, b->d_cm_tiles);
@@ -535,6 +568,7 @@ int spb_batch_destroy(spb_batch *b) {
   cudaFree(b->d_frame_offsets);
   cudaFree(b->d_tiles);
   cudaFree(b->d_cm_tiles);
+  cudaFree(b->d_big_tiles);
   delete b;
   return SPB_OK;
 }
@@ -588,6 +622,7 @@ static void fill_feat_args(FeatArgs &a, const spb_batch *b, const float *d_sampl
 
 // force_generic: 0 auto, 1 generic kernel (used by tests to cross-check the fast path)
 static int g_force_generic = 0;
+static int g_force_small_cmvnw = 0;
 
 static int run_features(spb_context *ctx, FeatArgs &a) {
   if (a.num_tiles <= 0) return SPB_OK;
@@ -636,9 +671,14 @@ static int run_lmfe_cmvnw(spb_context *ctx, const spb_batch *b, const float *d_s
     int rc = run_features(ctx, a);
     if (rc) return rc;
     float *ms_biased = d_ms ? d_ms - (ptrdiff_t)c.row0 * M : nullptr;
-    rc = launch_cmvnw_f32(ctx, lmfe_biased, ms_biased, d_out, b->d_nframes, b->d_frame_offsets,
-                          b->d_cm_tiles + c.cm0, c.cm1 - c.cm0, b->cm_tile_rows, M, M, win,
-                          pl->p.cmvn_variance);
+    if (b->big_rmax > 0 && !g_force_small_cmvnw && (((size_t)d_out) & 15) == 0)
+      rc = launch_cmvnw_big(ctx, lmfe_biased, ms_biased, d_out, b->d_nframes, b->d_frame_offsets,
+                            b->d_big_tiles + c.big0, c.big1 - c.big0, b->big_rmax, M, M, win,
+                            pl->p.cmvn_variance);
+    else
+      rc = launch_cmvnw_f32(ctx, lmfe_biased, ms_biased, d_out, b->d_nframes, b->d_frame_offsets,
+                            b->d_cm_tiles + c.cm0, c.cm1 - c.cm0, b->cm_tile_rows, M, M, win,
+                            pl->p.cmvn_variance);
     if (rc) return rc;
   }
   return SPB_OK;
@@ -719,7 +759,8 @@ extern "C" {
 
 // test hook (not in the public header): route every feature launch through the generic kernel
 SPB_API int spb_debug_force_generic(int on) {
-  g_force_generic = on;
+  g_force_generic = on & 1;
+  g_force_small_cmvnw = (on >> 1) & 1;  // bit 1: small-tile cmvnw kernels (cross-check)
   return SPB_OK;
 }
 
@@ -871,11 +912,28 @@ int spb_cmvnw(spb_context *ctx, const double *vec, int64_t rows, int32_t cols, i
   SPB_CUDA(ctx, cudaMemcpyAsync(d_f64, vec, n * 8, cudaMemcpyHostToDevice, ctx->stream));
   int rc = launch_convert(ctx, d_f64, SPB_F64, d_in, SPB_F32, (int64_t)n);
   if (rc) return rc;
+  const int32_t nfr = (int32_t)rows;
+  const int64_t offs[2] = {0, rows};
+  const int big_rmax = g_force_small_cmvnw ? 0 : cmvnw_big_rmax(cols, win);
+  if (big_rmax > 0) {
+    // large-tile kernels over all columns at once
+    std::vector<int4> tiles;
+    append_big_tiles(tiles, 0, rows, big_rmax);
+    unsigned char *meta = (unsigned char *)scratch(ctx, 4, 64 + tiles.size() * sizeof(int4));
+    if (!meta) return SPB_ERR_CUDA;
+    SPB_CUDA(ctx, cudaMemcpyAsync(meta, &nfr, 4, cudaMemcpyHostToDevice, ctx->stream));
+    SPB_CUDA(ctx, cudaMemcpyAsync(meta + 16, offs, 16, cudaMemcpyHostToDevice, ctx->stream));
+    SPB_CUDA(ctx, cudaMemcpyAsync(meta + 64, tiles.data(), tiles.size() * sizeof(int4), cudaMemcpyHostToDevice, ctx->stream));
+    rc = launch_cmvnw_big(ctx, d_in, d_ms, d_out, (const int32_t *)meta, (const int64_t *)(meta + 16),
+                          (const int4 *)(meta + 64), (int64_t)tiles.size(), big_rmax, cols, cols, win, varnorm);
+    if (rc) return rc;
+    SPB_CUDA(ctx, cudaMemcpyAsync(out, d_out, n * 4, cudaMemcpyDeviceToHost, ctx->stream));
+    SPB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return SPB_OK;
+  }
   // one "utterance" of `rows` rows
   const int R = cmvnw_tile_rows(cc, win);
   const int64_t ntiles = (rows + R - 1) / R;
-  const int32_t nfr = (int32_t)rows;
-  const int64_t offs[2] = {0, rows};
   const int64_t toff[2] = {0, ntiles};
   int32_t *d_nfr = (int32_t *)scratch(ctx, 4, 64 + (size_t)ntiles * sizeof(int2));
   if (!d_nfr) return SPB_ERR_CUDA;

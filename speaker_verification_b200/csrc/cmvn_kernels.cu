@@ -17,12 +17,26 @@
 // for chunked batches) and needs the same halo of ms, which is why the two stages are
 // separate launches rather than one kernel with a 2h halo (that would recompute stage
 // 1 for (R+2h)/R times the rows).
+#include <algorithm>
+
+#include "ptx_helpers.cuh"
 #include "spb_internal.cuh"
 
 namespace spb {
 
 constexpr int kCmG = 15;          // rows per block sum
 constexpr int kCmThreads = 320;
+
+// 32-bit variant with the common single-reflection cases first
+__device__ __forceinline__ int reflect_row32(int t, int F) {
+  if (t >= 0 && t < F) return t;
+  if (t < 0 && t >= -F) return -1 - t;
+  if (t >= F && t < 2 * F) return 2 * F - 1 - t;
+  const int period = 2 * F;
+  int m = t % period;
+  if (m < 0) m += period;
+  return (m < F) ? m : (period - 1 - m);
+}
 
 __device__ __forceinline__ int reflect_row(long long t, int F) {
   // np.pad(..., 'symmetric'): ... x1 x0 | x0 x1 ... x(F-1) | x(F-1) x(F-2) ...
@@ -276,6 +290,265 @@ int launch_cmvnw_f32(spb_context *ctx, const float *in, float *scratch_ms, float
     kern<<<(unsigned)grid, kCmThreads, smem, ctx->stream>>>(p);
     timing_end(ctx, stage, tb);
     SPB_LAUNCH_CHECK(ctx, "cmvnw_kernel");
+  }
+  return SPB_OK;
+}
+
+// ====================================================================================
+// cmvnw, large-tile variant (the batch hot path).
+//
+// Same arithmetic as cmvnw_kernel above, restructured for instruction count:
+//   * one CTA per SM, 640 threads, tiles of up to ~960 rows (+ win-1 halo rows) so that most
+//     utterances are a single tile whose halo is pure reflection (halo factor ~1.3, was 1.9);
+//     tiles are balanced per utterance and listed longest-first, CTAs pull them from an
+//     atomic counter;
+//   * interior rows staged with flat 16-byte loads, only the <= win-1 halo rows pay the
+//     reflection arithmetic;
+//   * 30-row block sums (win = 10 blocks + 1 row at 301), column pair per thread, COLS as a
+//     template constant so every shared-memory offset is an immediate; the slide loop is
+//     unrolled by two;
+//   * stage 2 uses sqrt.approx / rcp.approx (2 ulp; the reference computes np.std in float32).
+// ====================================================================================
+constexpr int kBigG = 30;
+constexpr int kBigThreads = 640;
+
+struct CmBigParams {
+  const float *in;
+  float *out;
+  const int32_t *nframes;
+  const int64_t *frame_offsets;
+  const int4 *tiles;   // {utt, first row, rows, 0}
+  int num_tiles;
+  int *counter;        // dynamic tile scheduler
+  int cols, win, ld, rmax;
+  float eps;
+};
+
+template <int STAGE, int COLS>
+__global__ void __launch_bounds__(kBigThreads, 1)
+cmvnw_big_kernel(const CmBigParams p) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  const int cols = COLS ? COLS : p.cols;
+  const int win = p.win, ld = p.ld;
+  const int h = (win - 1) >> 1;
+  const int rows_ext_max = p.rmax + win - 1;
+  const int nb = win / kBigG, rem = win - nb * kBigG;
+  const int nblk_max = (rows_ext_max + kBigG - 1) / kBigG + 1;
+  float *s = reinterpret_cast<float *>(smem_raw);
+  const size_t s_bytes = ((size_t)rows_ext_max * cols * 4 + 15) & ~(size_t)15;
+  double *bs1 = reinterpret_cast<double *>(smem_raw + s_bytes);
+  double *bs2 = bs1 + (size_t)nblk_max * cols;
+  __shared__ int s_tile;
+  __shared__ __align__(8) uint64_t s_bar;
+  const int tid = threadIdx.x;
+  const int warp = tid >> 5, lane = tid & 31;
+  constexpr int kWarps = kBigThreads / 32;
+  if (tid == 0) {
+    mbar_init(&s_bar, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  uint32_t bar_phase = 0;
+  const int ncg = cols >> 1;
+  const int nbpt = kBigThreads / ncg;
+  const int g = tid % ncg, b0 = tid / ncg;
+  const bool worker = b0 < nbpt;
+  const int c0 = 2 * g;
+  const double inv_win = 1.0 / (double)win;
+  const int n4 = cols >> 2;  // cols % 4 == 0 (checked by the launcher)
+
+  for (;;) {
+    __syncthreads();  // previous tile fully consumed (smem and s_tile)
+    if (tid == 0) s_tile = atomicAdd(p.counter, 1);
+    __syncthreads();
+    const int tile = s_tile;
+    if (tile >= p.num_tiles) break;
+    const int4 td = p.tiles[tile];
+    const int utt = td.x, r0 = td.y, nrows = td.z;
+    const int F = p.nframes[utt];
+    const long long base = p.frame_offsets[utt];
+    const int rows_needed = nrows + win - 1;
+    const int first = r0 - h;
+    // ---- stage: ext row e <-> utterance row first + e; interior = [e_lo, e_hi)
+    const int e_lo = max(0, -first), e_hi = min(rows_needed, F - first);
+    if (e_hi > e_lo) {
+      if (ld == cols) {
+        // interior rows are one contiguous block in global memory: TMA bulk copies issued by
+        // one thread (<= 64 KB each), completion on an mbarrier; the other threads go straight
+        // to the halo rows
+        if (tid == 0) {
+          const char *src = reinterpret_cast<const char *>(p.in + (base + first + e_lo) * (long long)cols);
+          char *dst = reinterpret_cast<char *>(s + (size_t)e_lo * cols);
+          const uint32_t total = (uint32_t)(e_hi - e_lo) * (uint32_t)cols * 4u;
+          // order earlier generic-proxy accesses of this buffer before the async-proxy writes
+          asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+          mbar_expect_tx(&s_bar, total);
+          for (uint32_t off = 0; off < total; off += 65536u)
+            bulk_load(dst + off, src + off, min(65536u, total - off), &s_bar);
+        }
+      } else {
+        for (int i = tid; i < (e_hi - e_lo) * n4; i += kBigThreads) {
+          const int r = i / n4, c = i - r * n4;
+          reinterpret_cast<float4 *>(s + (size_t)(e_lo + r) * cols)[c] =
+              __ldg(reinterpret_cast<const float4 *>(p.in + (base + first + e_lo + r) * (long long)ld) + c);
+        }
+      }
+    }
+    {
+      // halo rows: [0, e_lo) and [e_hi, rows_needed), symmetric reflection (np.pad 'symmetric')
+      const int nh_lo = max(e_lo, 0), nh = nh_lo + max(rows_needed - max(e_hi, e_lo), 0);
+      const int rpp = 32 / n4 > 0 ? 32 / n4 : 1;
+      const int lr = lane / n4, lc = lane - lr * n4;
+      if (n4 <= 32 && lr < rpp) {
+        for (int k = warp * rpp + lr; k < nh; k += kWarps * rpp) {
+          const int e = (k < nh_lo) ? k : max(e_hi, e_lo) + (k - nh_lo);
+          const int srow = reflect_row32(first + e, F);
+          reinterpret_cast<float4 *>(s + (size_t)e * cols)[lc] =
+              __ldg(reinterpret_cast<const float4 *>(p.in + (base + srow) * (long long)ld) + lc);
+        }
+      } else if (n4 > 32) {
+        for (int k = warp; k < nh; k += kWarps) {
+          const int e = (k < nh_lo) ? k : max(e_hi, e_lo) + (k - nh_lo);
+          const int srow = reflect_row32(first + e, F);
+          for (int c = lane; c < n4; c += 32)
+            reinterpret_cast<float4 *>(s + (size_t)e * cols)[c] =
+                __ldg(reinterpret_cast<const float4 *>(p.in + (base + srow) * (long long)ld) + c);
+        }
+      }
+    }
+    if (ld == cols && e_hi > e_lo) {
+      mbar_wait(&s_bar, bar_phase);  // bulk copy landed (async-proxy writes visible after the wait)
+      bar_phase ^= 1;
+    }
+    __syncthreads();
+    // ---- float64 sums of 30-row blocks
+    const int nblk_out = (nrows + kBigG - 1) / kBigG;
+    const int nblk = nblk_out + nb - 1;
+    if (worker) {
+      for (int k = b0; k < nblk; k += nbpt) {
+        const float *col = s + (size_t)k * kBigG * cols + c0;
+        double a1x = 0.0, a1y = 0.0, a2x = 0.0, a2y = 0.0;
+#pragma unroll 10
+        for (int r = 0; r < kBigG; ++r) {
+          const float2 x = *reinterpret_cast<const float2 *>(col + r * cols);
+          const double dx = (double)x.x, dy = (double)x.y;
+          a1x += dx; a1y += dy;
+          if (STAGE == 2) { a2x = fma(dx, dx, a2x); a2y = fma(dy, dy, a2y); }
+        }
+        *reinterpret_cast<double2 *>(bs1 + k * cols + c0) = make_double2(a1x, a1y);
+        if (STAGE == 2) *reinterpret_cast<double2 *>(bs2 + k * cols + c0) = make_double2(a2x, a2y);
+      }
+    }
+    __syncthreads();
+    // ---- window sums: first row of each block from block sums, then slide
+    if (worker) {
+      for (int b = b0; b < nblk_out; b += nbpt) {
+        double w1x = 0.0, w1y = 0.0, w2x = 0.0, w2y = 0.0;
+        for (int j = 0; j < nb; ++j) {
+          const double2 t1 = *reinterpret_cast<const double2 *>(bs1 + (b + j) * cols + c0);
+          w1x += t1.x; w1y += t1.y;
+          if (STAGE == 2) {
+            const double2 t2 = *reinterpret_cast<const double2 *>(bs2 + (b + j) * cols + c0);
+            w2x += t2.x; w2y += t2.y;
+          }
+        }
+        const float *col = s + c0;
+        const int tail0 = (b + nb) * kBigG;
+        for (int r = 0; r < rem; ++r) {
+          const float2 x = *reinterpret_cast<const float2 *>(col + (size_t)(tail0 + r) * cols);
+          const double dx = (double)x.x, dy = (double)x.y;
+          w1x += dx; w1y += dy;
+          if (STAGE == 2) { w2x = fma(dx, dx, w2x); w2y = fma(dy, dy, w2y); }
+        }
+        const int q0 = b * kBigG;
+        const int q1 = min(q0 + kBigG, nrows);
+        float *dst = p.out + (base + r0 + q0) * (long long)ld + c0;
+        const float *pc = col + (size_t)(q0 + h) * cols;     // centre row
+        const float *pin = col + (size_t)(q0 + win) * cols;  // row entering the window
+        const float *pout = col + (size_t)q0 * cols;         // row leaving the window
+#pragma unroll 2
+        for (int q = q0; q < q1; ++q) {
+          const float2 xc = *reinterpret_cast<const float2 *>(pc);
+          float2 o;
+          if (STAGE == 1) {
+            // processing.py:304-307: float32(vec[i] - mean(window))
+            // (x is float32 here; subtracting the float32-rounded float64 mean differs from
+            // the reference's float64 subtraction by <= 1 ulp of the result)
+            o.x = xc.x - (float)(w1x * inv_win);
+            o.y = xc.y - (float)(w1y * inv_win);
+          } else {
+            // processing.py:318-322: ms / (std(window) + eps), population std
+            const double mx = w1x * inv_win, my = w1y * inv_win;
+            const float vx = (float)fma(-mx, mx, w2x * inv_win), vy = (float)fma(-my, my, w2y * inv_win);
+            float sx, sy;
+            asm("sqrt.approx.f32 %0, %1;" : "=f"(sx) : "f"(fmaxf(vx, 0.f)));
+            asm("sqrt.approx.f32 %0, %1;" : "=f"(sy) : "f"(fmaxf(vy, 0.f)));
+            o.x = __fdividef(xc.x, sx + p.eps);
+            o.y = __fdividef(xc.y, sy + p.eps);
+          }
+          *reinterpret_cast<float2 *>(dst) = o;
+          if (q + 1 < q1) {
+            const float2 xi = *reinterpret_cast<const float2 *>(pin);
+            const float2 xo = *reinterpret_cast<const float2 *>(pout);
+            const double ix = (double)xi.x, iy = (double)xi.y, ox = (double)xo.x, oy = (double)xo.y;
+            w1x += ix - ox; w1y += iy - oy;
+            if (STAGE == 2) { w2x += fma(ix, ix, -ox * ox); w2y += fma(iy, iy, -oy * oy); }
+          }
+          dst += ld; pc += cols; pin += cols; pout += cols;
+        }
+      }
+    }
+  }
+}
+
+static size_t cm_big_smem_bytes(int rmax, int cols, int win) {
+  const int rows_ext = rmax + win - 1;
+  const int nblk = (rows_ext + kBigG - 1) / kBigG + 1;
+  const size_t s_bytes = ((size_t)rows_ext * cols * 4 + 15) & ~(size_t)15;
+  return s_bytes + 2 * (size_t)nblk * cols * 8;
+}
+
+// Largest tile (multiple of 30 rows, at most 960) that fits one CTA per SM; 0 = unsupported.
+int cmvnw_big_rmax(int cols, int win) {
+  if (cols < 4 || (cols & 3) || cols / 2 > kBigThreads || win < kBigG) return 0;
+  int best = 0;
+  for (int r = kBigG; r <= 960; r += kBigG)
+    if (cm_big_smem_bytes(r, cols, win) <= 226 * 1024) best = r;
+  return best >= 4 * kBigG ? best : 0;
+}
+
+int launch_cmvnw_big(spb_context *ctx, const float *in, float *scratch_ms, float *out,
+                     const int32_t *nframes, const int64_t *frame_offsets, const int4 *tiles,
+                     int64_t num_tiles, int rmax, int cols, int ld, int win, int varnorm) {
+  if (num_tiles <= 0) return SPB_OK;
+  int *counters = (int *)scratch(ctx, 7, 256);
+  if (!counters) return SPB_ERR_CUDA;
+  SPB_CUDA(ctx, cudaMemsetAsync(counters, 0, 8, ctx->stream));
+  CmBigParams p;
+  p.nframes = nframes;
+  p.frame_offsets = frame_offsets;
+  p.tiles = tiles;
+  p.num_tiles = (int)num_tiles;
+  p.cols = cols;
+  p.ld = ld;
+  p.win = win;
+  p.rmax = rmax;
+  p.eps = 9.313225746154785e-10f;  // 2^-30 (processing.py:292)
+  const size_t smem = cm_big_smem_bytes(rmax, cols, win);
+  for (int stage = 1; stage <= (varnorm ? 2 : 1); ++stage) {
+    auto kern = (cols == 40) ? (stage == 1 ? cmvnw_big_kernel<1, 40> : cmvnw_big_kernel<2, 40>)
+                             : (stage == 1 ? cmvnw_big_kernel<1, 0> : cmvnw_big_kernel<2, 0>);
+    int per_sm = 0;
+    int rc = configure_kernel(ctx, (const void *)kern, kBigThreads, smem, &per_sm);
+    if (rc) return rc;
+    if (per_sm < 1) return fail(ctx, SPB_ERR_UNSUPPORTED, "cmvnw: tile does not fit in shared memory");
+    long long grid = std::min<long long>(ctx->sm_count, num_tiles);
+    p.in = (stage == 1) ? in : scratch_ms;
+    p.out = (stage == 1) ? (varnorm ? scratch_ms : out) : out;
+    p.counter = counters + (stage - 1);
+    const size_t tb = timing_begin(ctx);
+    kern<<<(unsigned)grid, kBigThreads, smem, ctx->stream>>>(p);
+    timing_end(ctx, stage, tb);
+    SPB_LAUNCH_CHECK(ctx, "cmvnw_big_kernel");
   }
   return SPB_OK;
 }

@@ -78,6 +78,7 @@ struct BatchChunk {
   int64_t tile0, tile1;  // fft tiles
   int64_t cm0, cm1;      // cmvnw tiles
   int64_t row0, row1;    // output rows
+  int64_t big0 = 0, big1 = 0;  // large-tile cmvnw tiles
 };
 }  // namespace spb
 
@@ -97,6 +98,8 @@ struct spb_batch {
   int64_t *d_frame_offsets = nullptr;    // [U+1]
   int2 *d_tiles = nullptr;               // [total_tiles] {utt, first frame}
   int2 *d_cm_tiles = nullptr;            // [total_cm_tiles] {utt, first row}
+  int4 *d_big_tiles = nullptr;           // large-tile cmvnw: {utt, first row, rows, 0}, longest first per chunk
+  int big_rmax = 0;                      // 0: large-tile path not usable for this plan
   std::vector<spb::BatchChunk> chunks;
   int64_t max_chunk_rows = 0;
 };
@@ -160,6 +163,12 @@ int launch_cmvnw_f32(spb_context *ctx, const float *in, float *scratch_ms, float
                      const int32_t *nframes, const int64_t *frame_offsets, const int2 *tiles,
                      int64_t num_tiles, int tile_rows, int cols, int ld, int win, int varnorm);
 int cmvnw_tile_rows(int cols, int win);
+int cmvnw_big_rmax(int cols, int win);
+int launch_cmvnw_big(spb_context *ctx, const float *in, float *scratch_ms, float *out,
+                     const int32_t *nframes, const int64_t *frame_offsets, const int4 *tiles,
+                     int64_t num_tiles, int rmax, int cols, int ld, int win, int varnorm);
+// balanced tiles of one utterance of F rows: appends {utt, r0, rows, 0}
+void append_big_tiles(std::vector<int4> &v, int utt, int64_t F, int rmax);
 bool cmvnw_supported(int cols, int win);
 int launch_cmvn_f64(spb_context *ctx, const double *in, int64_t rows, int cols, int varnorm,
                     double *out);

@@ -91,3 +91,35 @@ def test_batch_errors(sp):
     with pytest.raises(AssertionError):
         fb.lmfe_cmvnw(np.zeros(100, dtype=np.float32))
     fb.close()
+
+
+def test_large_tile_cmvnw_matches_small_tile_kernels(sp):
+    """The batch path runs the large-tile cmvnw kernels; bit 1 of the debug hook routes the
+    same call through the small-tile kernels (independent tiling, block size, sqrt/div)."""
+    import ctypes
+    from speaker_verification_b200 import _lib
+    raw = ctypes.CDLL(_lib.LIB_PATH)
+    # multi-tile (> 960 frames), exactly-one-tile, short (< 150 frames: repeated reflection), tiny
+    lengths = [320000, 154000, 153920, 100321, 20000, 1000, 480, 800, 235000]
+    sigs = _signals(700, lengths)
+    arena, starts, lens = batch.pack(sigs)
+    for vn in (True, False):
+        fb = batch.FeatureBatch(starts, lens, variance_normalization=vn)
+        big = fb.lmfe_cmvnw(arena)
+        raw.spb_debug_force_generic(2)
+        try:
+            small = fb.lmfe_cmvnw(arena)
+        finally:
+            raw.spb_debug_force_generic(0)
+        assert np.max(np.abs(big - small)) < 2e-5
+        for s, got in zip(sigs, fb.split(big)):
+            lm = o.lmfe(s, FS)
+            if lm.shape[0]:
+                assert np.max(np.abs(got - o.cmvnw_vectorised(lm, 301, vn))) < TOL
+        fb.close()
+    # public API, other window sizes / widths through both kernel families
+    rng = np.random.Generator(np.random.Philox(5))
+    for rows, cols, win in [(2500, 40, 301), (700, 24, 101), (64, 40, 31), (5, 8, 301), (1500, 13, 301)]:
+        v = rng.standard_normal((rows, cols)) * 3 + 1
+        got = sp.processing.cmvnw(v, win, True)
+        assert np.max(np.abs(got - o.cmvnw_vectorised(v, win, True))) < TOL, (rows, cols, win)
