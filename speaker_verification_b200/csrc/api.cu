@@ -388,6 +388,88 @@ int spb_plan_create(spb_context *ctx, const spb_feature_params *params, const do
     }
   }
   pl->band_total = (int)w.size();
+  // ---- segment form (see spb_plan): validated against the dense bank, else left empty
+  std::vector<float4> seg_rd;
+  std::vector<int4> seg_ranges;
+  if (M >= 1) {
+    std::vector<int> mid(M, -1);
+    for (int m = 0; m < M; ++m) {
+      double best = 0.0;
+      for (int k = 0; k < K; ++k)
+        if (filterbank[(size_t)m * K + k] > best) { best = filterbank[(size_t)m * K + k]; mid[m] = k; }
+    }
+    int kmin = K, kmax = -1;
+    std::vector<int> seg(K, -1);
+    std::vector<float> rw(K, 0.f), dw(K, 0.f);
+    bool ok = true;
+    for (int k = 0; k < K && ok; ++k) {
+      int cnt = 0, jmax = -1;
+      for (int m = 0; m < M; ++m)
+        if (filterbank[(size_t)m * K + k] != 0.0) { ++cnt; jmax = m; }
+      if (cnt == 0) continue;
+      if (cnt > 2) { ok = false; break; }
+      kmin = std::min(kmin, k);
+      kmax = std::max(kmax, k);
+      if (cnt == 2) {
+        if (filterbank[(size_t)(jmax - 1) * K + k] == 0.0) { ok = false; break; }
+        seg[k] = jmax;
+        rw[k] = (float)filterbank[(size_t)jmax * K + k];
+        dw[k] = (float)filterbank[(size_t)(jmax - 1) * K + k];
+      } else if (k <= mid[jmax]) {
+        seg[k] = jmax;
+        rw[k] = (float)filterbank[(size_t)jmax * K + k];
+      } else {
+        seg[k] = jmax + 1;
+        dw[k] = (float)filterbank[(size_t)jmax * K + k];
+      }
+    }
+    if (ok && kmax >= kmin) {
+      // bins without weight inside the range inherit the previous segment; segments must run
+      // 0, 1, ..., M without gaps
+      int prev = 0;
+      for (int k = kmin; k <= kmax && ok; ++k) {
+        if (seg[k] < 0) seg[k] = prev;
+        if (seg[k] != prev && seg[k] != prev + 1) ok = false;
+        if (k == kmin && seg[k] != 0) ok = false;
+        prev = seg[k];
+      }
+      if (ok && prev != M) ok = false;
+      // exact reconstruction of the fp32 bank
+      for (int m = 0; m < M && ok; ++m)
+        for (int k = 0; k < K && ok; ++k) {
+          float wgt = 0.f;
+          if (k >= kmin && k <= kmax) {
+            if (seg[k] == m) wgt = rw[k];
+            else if (seg[k] == m + 1) wgt = dw[k];
+          }
+          if (wgt != (float)filterbank[(size_t)m * K + k]) ok = false;
+        }
+    } else {
+      ok = false;
+    }
+    if (ok) {
+      const int nb = kmax - kmin + 1;
+      seg_rd.resize(nb);
+      for (int k = kmin; k <= kmax; ++k) {
+        const bool end = (k == kmax) || (seg[k + 1] != seg[k]);
+        seg_rd[k - kmin] = make_float4(rw[k], dw[k], end ? 1.f : 0.f, 0.f);
+      }
+      // eight warp ranges of whole segments, balanced by bin count
+      seg_ranges.assign(8, make_int4(kmax + 1, kmax + 1, M + 1, 0));
+      int k = kmin;
+      for (int wv = 0; wv < 8 && k <= kmax; ++wv) {
+        const int remaining_w = 8 - wv;
+        const int target = (kmax + 1 - k + remaining_w - 1) / remaining_w;
+        int e = k;
+        while (e <= kmax && ((e - k) < target || seg_rd[e - 1 - kmin].z == 0.f)) ++e;  // stop after a segment end
+        if (wv == 7) e = kmax + 1;
+        seg_ranges[wv] = make_int4(k, e, seg[k], 0);
+        k = e;
+      }
+      pl->seg_kmin = kmin;
+      pl->seg_nbins = nb;
+    }
+  }
   std::vector<float> dct((size_t)C * M);
   const double pi = 3.14159265358979323846264338327950288;
   for (int c = 0; c < C; ++c) {
@@ -405,6 +487,8 @@ int spb_plan_create(spb_context *ctx, const spb_feature_params *params, const do
       (e = up((void **)&pl->d_band_n, pl->h_band_n.data(), (size_t)M * 4)) != cudaSuccess ||
       (e = up((void **)&pl->d_band_off, pl->h_band_off.data(), (size_t)M * 4)) != cudaSuccess ||
       (e = up((void **)&pl->d_band_w, w.data(), w.size() * 4)) != cudaSuccess ||
+      (e = up((void **)&pl->d_seg_rd, seg_rd.data(), seg_rd.size() * sizeof(float4))) != cudaSuccess ||
+      (e = up((void **)&pl->d_seg_ranges, seg_ranges.data(), seg_ranges.size() * sizeof(int4))) != cudaSuccess ||
       (e = up((void **)&pl->d_dct, dct.data(), dct.size() * 4)) != cudaSuccess) {
     spb_plan_destroy(pl);
     return cuda_fail(ctx, e, "plan upload");
@@ -426,6 +510,8 @@ int spb_plan_destroy(spb_plan *pl) {
   cudaFree(pl->d_band_n);
   cudaFree(pl->d_band_off);
   cudaFree(pl->d_band_w);
+  cudaFree(pl->d_seg_rd);
+  cudaFree(pl->d_seg_ranges);
   cudaFree(pl->d_dct);
   delete pl;
   return SPB_OK;
@@ -614,6 +700,10 @@ static void fill_feat_args(FeatArgs &a, const spb_batch *b, const float *d_sampl
   a.band_w = pl->d_band_w;
   a.band_total = pl->band_total;
   a.max_bin = pl->max_bin;
+  a.seg_rd = pl->seg_nbins > 0 ? pl->d_seg_rd : nullptr;
+  a.seg_ranges = pl->d_seg_ranges;
+  a.seg_kmin = pl->seg_kmin;
+  a.seg_nbins = pl->seg_nbins;
   a.dct = pl->d_dct;
   a.mode = mode;
   a.out = d_out;

@@ -16,6 +16,7 @@
 #include <math.h>
 
 #include "fft_math.cuh"
+#include "ptx_helpers.cuh"
 #include "spb_internal.cuh"
 
 namespace spb {
@@ -35,6 +36,9 @@ struct FeatParams {
   const float *band_w;
   int band_total;
   const float *dct;
+  const float4 *seg_rd;
+  const int4 *seg_ranges;
+  int seg_kmin, seg_nbins;
   int mode;
   float *out;
   float *energy;
@@ -53,11 +57,19 @@ struct FeatParams {
 // Band weights are zero-padded to multiples of four (offsets too), so the inner loop is a
 // 128-bit broadcast load of four weights + four FFMAs; P rows carry >= 3 zeroed pad bins
 // after the last real bin so the padded taps read finite values.
-template <int TILE>
+__device__ __forceinline__ int tid0_div(int a, int b) { return a / b; }
+
+struct FmIndex {  // tid -> (frame, filter) walk over a [frames][M] tile, hoisted out of the tile loop
+  int f0, m0, df, dm;
+};
+
+template <int TILE, bool SEG>
 __device__ __forceinline__ void output_stage(const FeatParams &p, const float *s_p, int pstride,
                                              const float *s_en, float *s_a, float *s_b,
                                              const float *s_bw, const int *s_bmeta,
-                                             const float *s_dct, int nf, long long row0) {
+                                             const float *s_dct, int nf, long long row0,
+                                             const float4 *s_rd, const int4 *s_wr,
+                                             float *s_U, float *s_D, const FmIndex fm) {
   const int tid = threadIdx.x;
   const int nthreads = blockDim.x;
   const float scale = 1.0f / (float)p.nfft;  // |X|^2 / NFFT  (processing.py:174)
@@ -77,6 +89,56 @@ __device__ __forceinline__ void output_stage(const FeatParams &p, const float *s
   }
   const int M = p.M;
   const int astride = M + 1;  // odd-ish padding: lane = frame accesses stay conflict-light
+  if (SEG) {
+    // Segment form (triangular bank): lane = frame, each warp walks its run of whole
+    // segments once; bin k feeds the rising sum of filter seg and the falling sum of filter
+    // seg-1.  U[f][j] = rising sum of filter j, D[f][j] = falling sum of filter j-1.
+    const int lane = tid & 31, warp = tid >> 5;
+    const int upitch = (M + 2) | 1;
+    const int4 wr = s_wr[warp];
+    if (lane < nf) {
+      const float *pp = s_p + lane * pstride + wr.x;
+      const float4 *rd = s_rd + (wr.x - p.seg_kmin);
+      float *pu = s_U + lane * upitch + wr.z;
+      float *pd = s_D + lane * upitch + wr.z;
+      float up = 0.f, dn = 0.f;
+      const int n = wr.y - wr.x;
+#pragma unroll 4
+      for (int i = 0; i < n; ++i) {
+        const float4 c = rd[i];
+        const float pv = pp[i];
+        up = fmaf(c.x, pv, up);
+        dn = fmaf(c.y, pv, dn);
+        if (c.z != 0.f) {
+          *pu++ = up;
+          *pd++ = dn;
+          up = dn = 0.f;
+        }
+      }
+    }
+    __syncthreads();
+    const bool direct = (p.mode == FEAT_MFE || p.mode == FEAT_LMFE);
+    float *dst = p.out + row0 * M + tid;   // tile rows are contiguous in global memory
+    int f = fm.f0, m = fm.m0;
+    const float *pu = s_U + f * upitch + m;
+    const float *pd = s_D + f * upitch + m + 1;
+    float *pa = s_a + f * astride + m;
+    const int ustep = fm.df * upitch + fm.dm, astep = fm.df * astride + fm.dm;
+    while (f < nf) {
+      float acc = (*pu + *pd) * scale;
+      if (acc == 0.f) acc = kEpsF64AsF32;  // functions.zero_handling (feature.py:217)
+      const float v = (p.mode == FEAT_MFE) ? acc : __logf(acc);
+      if (direct) *dst = v; else *pa = v;
+      m += fm.dm; f += fm.df;
+      pu += ustep; pd += ustep; pa += astep; dst += nthreads;
+      if (m >= M) { m -= M; ++f; pu += upitch - M; pd += upitch - M; pa += astride - M; }
+    }
+    if (direct) {
+      if (p.mode == FEAT_MFE && p.energy != nullptr)
+        for (int ff = tid; ff < nf; ff += nthreads) p.energy[row0 + ff] = s_en[ff];
+      return;
+    }
+  } else {
   // mel energies: thread (frame = tid % TILE, filter slot = tid / TILE)
   {
     const int f = tid % TILE;
@@ -101,6 +163,7 @@ __device__ __forceinline__ void output_stage(const FeatParams &p, const float *s
         s_a[f * astride + m] = (p.mode == FEAT_MFE) ? acc : __logf(acc);
       }
     }
+  }
   }
   __syncthreads();
   if (p.mode == FEAT_MFE || p.mode == FEAT_LMFE) {
@@ -216,6 +279,24 @@ features_fast512(const FeatParams p) {
   float *s_b = s_a + kTile * (p.M + 1);                             // [kTile][C+1]
   float *s_dct = s_b + kTile * (p.C + 1);                           // [C*M]
   int *s_bmeta = reinterpret_cast<int *>(s_dct + p.C * p.M);        // [3M]
+  // segment form of the bank (16-byte aligned: everything before it is a multiple of 4 floats
+  // once padded)
+  const int used_floats = (int)(reinterpret_cast<float *>(s_bmeta + 3 * p.M) - reinterpret_cast<float *>(smem_raw));
+  float4 *s_rd = reinterpret_cast<float4 *>(reinterpret_cast<float *>(smem_raw) + ((used_floats + 3) & ~3));
+  int4 *s_wr = reinterpret_cast<int4 *>(s_rd + p.seg_nbins);
+  // U / D alias the FFT exchange buffer (32 KB), which is idle during the output stage
+  float *s_U = reinterpret_cast<float *>(s_exch);                   // [kTile][(M+2)|1]
+  float *s_D = s_U + kTile * ((p.M + 2) | 1);
+  FmIndex fm;
+  {
+    const int Mq = p.M > 0 ? p.M : 1;
+    fm.f0 = tid0_div(threadIdx.x, Mq);
+    fm.m0 = threadIdx.x - fm.f0 * Mq;
+    fm.df = kFastThreads / Mq;
+    fm.dm = kFastThreads - fm.df * Mq;
+  }
+  const bool use_seg = p.seg_rd != nullptr && p.mode >= FEAT_MFE &&
+                       2 * kTile * ((p.M + 2) | 1) * 4 <= 16 * 256 * (int)sizeof(float2);
 
   const int tid = threadIdx.x;
   const int warp = tid >> 5;
@@ -226,6 +307,10 @@ features_fast512(const FeatParams p) {
   float2 *my_exch = s_exch + hw * 256;
 
   load_plan_to_smem(p, s_bw, s_bmeta, s_dct);
+  if (use_seg) {
+    for (int i = tid; i < p.seg_nbins; i += kFastThreads) s_rd[i] = p.seg_rd[i];
+    if (tid < 8) s_wr[tid] = p.seg_ranges[tid];
+  }
   for (int i = tid; i < kTile * 4; i += kFastThreads)
     s_p[(i >> 2) * PSTRIDE + PBINS + (i & 3)] = 0.f;
 
@@ -239,10 +324,18 @@ features_fast512(const FeatParams p) {
   const int partner = (16 - l16) & 15;
   const int Leff = min(L, 512);
 
-  // Stage a tile's samples into s_xbuf[b]: 16-byte cp.async when the tile starts on a
-  // 16-byte boundary (batches packed by batch.pack do), plain loads otherwise.  Each sample
-  // is fetched from HBM once and used by L/S frames.
-  auto stage = [&](long long t, int b, int &utt, int &f0, int &nf) {
+  // Stage a tile's samples into s_xbuf[b]: one TMA bulk copy issued by thread 0 when the tile
+  // starts on a 16-byte boundary (batches packed by batch.pack do), plain loads otherwise.
+  // Each sample is fetched from HBM once and used by L/S frames.
+  __shared__ __align__(8) uint64_t s_full[2];
+  if (tid == 0) {
+    mbar_init(&s_full[0], 1);
+    mbar_init(&s_full[1], 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncthreads();
+  uint32_t ph0 = 0, ph1 = 0;
+  auto stage = [&](long long t, int b, int &utt, int &f0, int &nf, bool &bulk) {
     const int2 td = p.tiles[t];
     utt = td.x;
     f0 = td.y;
@@ -251,9 +344,14 @@ features_fast512(const FeatParams p) {
     const int count = (nf - 1) * S + L;
     const float *src = p.samples + gstart;
     float *dst = s_xbuf + b * xoff;
-    if ((gstart & 3) == 0) {
+    bulk = ((gstart & 3) == 0) && count >= 4;
+    if (bulk) {
       const int n4 = count >> 2;
-      for (int i = tid; i < n4; i += kFastThreads) cp_async16(dst + 4 * i, src + 4 * i);
+      if (tid == 0) {
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        mbar_expect_tx(&s_full[b], (uint32_t)n4 * 16u);
+        bulk_load(dst, src, (uint32_t)n4 * 16u, &s_full[b]);
+      }
       for (int i = (n4 << 2) + tid; i < count; i += kFastThreads) dst[i] = __ldg(src + i);
     } else {
       for (int i = tid; i < count; i += kFastThreads) dst[i] = __ldg(src + i);
@@ -263,16 +361,19 @@ features_fast512(const FeatParams p) {
   long long tile = blockIdx.x;
   int buf = 0;
   int utt = 0, f0 = 0, nf = 0;
-  if (tile < p.num_tiles) stage(tile, 0, utt, f0, nf);
-  cp_async_commit();
+  bool bulk = false;
+  if (tile < p.num_tiles) stage(tile, 0, utt, f0, nf, bulk);
   for (; tile < p.num_tiles; buf ^= 1) {
     const long long next = tile + gridDim.x;
     int n_utt = 0, n_f0 = 0, n_nf = 0;
+    bool n_bulk = false;
     // prefetch the next tile while this one is transformed (its buffer was last read in
     // phase B of the previous iteration, which every thread has left)
-    if (next < p.num_tiles) stage(next, buf ^ 1, n_utt, n_f0, n_nf);
-    cp_async_commit();
-    cp_async_wait<1>();
+    if (next < p.num_tiles) stage(next, buf ^ 1, n_utt, n_f0, n_nf, n_bulk);
+    if (bulk) {
+      if (buf == 0) { mbar_wait(&s_full[0], ph0); ph0 ^= 1; }
+      else { mbar_wait(&s_full[1], ph1); ph1 ^= 1; }
+    }
     __syncthreads();  // samples of this tile visible; previous tile's phase C is finished
     const float *s_x = s_xbuf + buf * xoff;
 
@@ -366,11 +467,15 @@ features_fast512(const FeatParams p) {
     __syncthreads();
     // ---- phase C
     const long long row0 = p.frame_offsets[utt] + f0;
-    output_stage<kTile>(p, s_p, PSTRIDE, s_en, s_a, s_b, s_bw, s_bmeta, s_dct, nf, row0);
+    if (use_seg)
+      output_stage<kTile, true>(p, s_p, PSTRIDE, s_en, s_a, s_b, s_bw, s_bmeta, s_dct, nf, row0, s_rd, s_wr,
+                                s_U, s_D, fm);
+    else
+      output_stage<kTile, false>(p, s_p, PSTRIDE, s_en, s_a, s_b, s_bw, s_bmeta, s_dct, nf, row0, s_rd, s_wr,
+                                 s_U, s_D, fm);
     tile = next;
-    utt = n_utt; f0 = n_f0; nf = n_nf;
+    utt = n_utt; f0 = n_f0; nf = n_nf; bulk = n_bulk;
   }
-  cp_async_wait<0>();
 }
 
 // ====================================================================================
@@ -464,7 +569,8 @@ features_generic(const FeatParams p) {
       }
       __syncthreads();
       const long long row0 = p.frame_offsets[utt] + f0;
-      output_stage<kGenTile>(p, s_p, pstride, s_en, s_a, s_b, s_bw, s_bmeta, s_dct, nf, row0);
+      output_stage<kGenTile, false>(p, s_p, pstride, s_en, s_a, s_b, s_bw, s_bmeta, s_dct, nf, row0, nullptr,
+                                    nullptr, nullptr, nullptr, FmIndex{0, 0, 0, 0});
     }
   }
 }
@@ -483,6 +589,10 @@ static FeatParams make_params(const FeatArgs &a, const FftTables &t) {
   p.band_lo = a.band_lo; p.band_n = a.band_n; p.band_off = a.band_off;
   p.band_w = a.band_w; p.band_total = a.band_total;
   p.dct = a.dct;
+  p.seg_rd = a.seg_rd;
+  p.seg_ranges = a.seg_ranges;
+  p.seg_kmin = a.seg_kmin;
+  p.seg_nbins = a.seg_nbins;
   p.mode = a.mode;
   p.out = a.out;
   p.energy = a.energy;
@@ -516,7 +626,8 @@ template <int NJ, bool FULL>
 static int launch_fast(spb_context *ctx, const FeatParams &p, const FeatArgs &a) {
   const int span_max = (kTile - 1) * a.S + a.L;
   size_t smem = 2 * (size_t)((span_max + 3) & ~3) * 4 + 16 * 256 * sizeof(float2) +
-                (size_t)kTile * ((FULL ? 257 : 129) + 4) * 4 + plan_smem_bytes(a, kTile);
+                (size_t)kTile * ((FULL ? 257 : 129) + 4) * 4 + plan_smem_bytes(a, kTile) +
+                16 + (size_t)a.seg_nbins * 16 + 8 * 16;
   auto kern = features_fast512<NJ, FULL>;
   int per_sm = 0;
   int rc = configure_kernel(ctx, (const void *)kern, kFastThreads, smem, &per_sm);

@@ -68,6 +68,13 @@ struct spb_plan {
   int band_total = 0;
   int max_bin = -1;               // largest bin index carrying weight
   float *d_dct = nullptr;         // [C][M] orthonormal DCT-II rows
+  // segment form of a triangular bank (every bin feeds at most the rising side of filter j and
+  // the falling side of filter j-1): per bin {rise weight, fall weight, end-of-segment flag, 0},
+  // bins [seg_kmin, seg_kmin + seg_nbins); 8 warp ranges {first bin, end bin, first segment, 0}.
+  // seg_nbins == 0: the bank does not have that structure (generic taps are used).
+  float4 *d_seg_rd = nullptr;
+  int4 *d_seg_ranges = nullptr;
+  int seg_kmin = 0, seg_nbins = 0;
   std::vector<int32_t> h_band_lo, h_band_n, h_band_off;
 };
 
@@ -150,6 +157,9 @@ struct FeatArgs {
   int band_total;
   int max_bin;               // largest bin with non-zero weight
   const float *dct;          // [C][M]
+  const float4 *seg_rd;      // segment form of the bank (or nullptr)
+  const int4 *seg_ranges;
+  int seg_kmin, seg_nbins;
   int mode;
   float *out;                // power/mag: [frames][K]; mfe/lmfe: [frames][M]; mfcc: [frames][C]; delta: [frames][C][3]
   float *energy;             // [frames] or nullptr (mfe only)
