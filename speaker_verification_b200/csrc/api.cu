@@ -614,6 +614,7 @@ int spb_batch_create(spb_context *ctx, const spb_plan *plan, const int64_t *star
       (e = cudaMalloc(&b->d_nframes, u_bytes * 4)) != cudaSuccess ||
       (e = cudaMalloc(&b->d_frame_offsets, (u_bytes + 1) * 8)) != cudaSuccess ||
       (e = cudaMalloc(&b->d_tiles, (size_t)std::max<int64_t>(b->total_tiles, 1) * sizeof(int2))) != cudaSuccess ||
+      (e = cudaMalloc(&b->d_ftiles, (size_t)std::max<int64_t>(b->total_tiles, 1) * sizeof(FftTile))) != cudaSuccess ||
       (e = cudaMalloc(&b->d_cm_tiles, (size_t)std::max<int64_t>(b->total_cm_tiles, 1) * sizeof(int2))) != cudaSuccess ||
       (e = cudaMalloc(&b->d_big_tiles, std::max<size_t>(big.size(), 1) * sizeof(int4))) != cudaSuccess ||
       (e = cudaMalloc(&d_tile_off, (u_bytes + 1) * 8)) != cudaSuccess ||
@@ -630,6 +631,9 @@ int spb_batch_create(spb_context *ctx, const spb_plan *plan, const int64_t *star
         (e = cudaMemcpyAsync(b->d_big_tiles, big.data(), big.size() * sizeof(int4), cudaMemcpyHostToDevice, ctx->stream)) != cudaSuccess)
       return cleanup(e, "cudaMemcpyAsync(big tiles)");
     int rc = launch_build_tiles(ctx, b->d_nframes, d_tile_off, U, kFftTile, b->d_tiles);
+    if (!rc)
+      rc = launch_build_fft_tiles(ctx, b->d_nframes, d_tile_off, b->d_starts, b->d_frame_offsets, U, kFftTile, S,
+                                  b->d_ftiles);
     if (!rc && b->cm_tile_rows)
       rc = launch_build_tiles(ctx, b->d_nframes, d_cm_off, U, b->cm_tile_rows, b->d_cm_tiles);
     if (rc) {
@@ -653,6 +657,7 @@ int spb_batch_destroy(spb_batch *b) {
   cudaFree(b->d_nframes);
   cudaFree(b->d_frame_offsets);
   cudaFree(b->d_tiles);
+  cudaFree(b->d_ftiles);
   cudaFree(b->d_cm_tiles);
   cudaFree(b->d_big_tiles);
   delete b;
@@ -685,6 +690,7 @@ static void fill_feat_args(FeatArgs &a, const spb_batch *b, const float *d_sampl
   a.nframes = b->d_nframes;
   a.frame_offsets = b->d_frame_offsets;
   a.tiles = b->d_tiles;
+  a.ftiles = b->d_ftiles;
   a.num_tiles = b->total_tiles;
   a.tile_frames = b->tile_frames;
   a.L = pl->p.frame_len;
@@ -757,6 +763,7 @@ static int run_lmfe_cmvnw(spb_context *ctx, const spb_batch *b, const float *d_s
     float *lmfe_biased = d_lmfe - (ptrdiff_t)c.row0 * M;
     fill_feat_args(a, b, d_samples, arena_len, FEAT_LMFE, lmfe_biased, nullptr);
     a.tiles = b->d_tiles + c.tile0;
+    a.ftiles = b->d_ftiles + c.tile0;
     a.num_tiles = c.tile1 - c.tile0;
     int rc = run_features(ctx, a);
     if (rc) return rc;

@@ -16,6 +16,7 @@
 #include <math.h>
 
 #include "fft_math.cuh"
+#include "fft_math2.cuh"
 #include "ptx_helpers.cuh"
 #include "spb_internal.cuh"
 
@@ -29,6 +30,7 @@ struct FeatParams {
   const int32_t *nframes;
   const int64_t *frame_offsets;
   const int2 *tiles;
+  const FftTile *ftiles;
   long long num_tiles;
   int L, S, K;
   int M, C, dc_elim;
@@ -63,7 +65,7 @@ struct FmIndex {  // tid -> (frame, filter) walk over a [frames][M] tile, hoiste
   int f0, m0, df, dm;
 };
 
-template <int TILE, bool SEG>
+template <int TILE, bool SEG, int MODE_CT = -1>
 __device__ __forceinline__ void output_stage(const FeatParams &p, const float *s_p, int pstride,
                                              const float *s_en, float *s_a, float *s_b,
                                              const float *s_bw, const int *s_bmeta,
@@ -117,24 +119,27 @@ __device__ __forceinline__ void output_stage(const FeatParams &p, const float *s
       }
     }
     __syncthreads();
-    const bool direct = (p.mode == FEAT_MFE || p.mode == FEAT_LMFE);
-    float *dst = p.out + row0 * M + tid;   // tile rows are contiguous in global memory
-    int f = fm.f0, m = fm.m0;
-    const float *pu = s_U + f * upitch + m;
-    const float *pd = s_D + f * upitch + m + 1;
-    float *pa = s_a + f * astride + m;
-    const int ustep = fm.df * upitch + fm.dm, astep = fm.df * astride + fm.dm;
-    while (f < nf) {
-      float acc = (*pu + *pd) * scale;
-      if (acc == 0.f) acc = kEpsF64AsF32;  // functions.zero_handling (feature.py:217)
-      const float v = (p.mode == FEAT_MFE) ? acc : __logf(acc);
-      if (direct) *dst = v; else *pa = v;
-      m += fm.dm; f += fm.df;
-      pu += ustep; pd += ustep; pa += astep; dst += nthreads;
-      if (m >= M) { m -= M; ++f; pu += upitch - M; pd += upitch - M; pa += astride - M; }
+    // thread = (filter m fixed, frames f0, f0 + rpp, ...): rpp = threads / M whole rows per sweep
+    const int mode = (MODE_CT >= 0) ? MODE_CT : p.mode;
+    const bool direct = (mode == FEAT_MFE || mode == FEAT_LMFE);
+    const int rpp = fm.df;
+    if (fm.f0 < rpp) {
+      const int m = fm.m0;
+      const float *pu = s_U + fm.f0 * upitch + m;
+      const float *pd = s_D + fm.f0 * upitch + m + 1;
+      float *pa = s_a + fm.f0 * astride + m;
+      float *dst = p.out + (row0 + fm.f0) * M + m;  // tile rows are contiguous in global memory
+      const int ustep = rpp * upitch, astep = rpp * astride, dstep = rpp * M;
+      for (int f = fm.f0; f < nf; f += rpp) {
+        float acc = (*pu + *pd) * scale;
+        if (acc == 0.f) acc = kEpsF64AsF32;  // functions.zero_handling (feature.py:217)
+        const float v = (mode == FEAT_MFE) ? acc : __logf(acc);
+        if (direct) *dst = v; else *pa = v;
+        pu += ustep; pd += ustep; pa += astep; dst += dstep;
+      }
     }
     if (direct) {
-      if (p.mode == FEAT_MFE && p.energy != nullptr)
+      if (mode == FEAT_MFE && p.energy != nullptr)
         for (int ff = tid; ff < nf; ff += nthreads) p.energy[row0 + ff] = s_en[ff];
       return;
     }
@@ -273,7 +278,7 @@ features_fast512(const FeatParams p) {
   float *s_xbuf = reinterpret_cast<float *>(smem_raw);              // 2 x [xoff] sample stages
   float2 *s_exch = reinterpret_cast<float2 *>(s_xbuf + 2 * xoff);   // 16 half-warps x 256
   float *s_p = reinterpret_cast<float *>(s_exch + 16 * 256);        // [kTile][PSTRIDE]
-  float *s_bw = s_p + kTile * PSTRIDE;                              // [band_total] (16 B aligned)
+  float *s_bw = s_p + kTile * PSTRIDE;                                 // [band_total] (16 B aligned)
   float *s_en = s_bw + p.band_total;                                // [kTile]
   float *s_a = s_en + kTile;                                        // [kTile][M+1]
   float *s_b = s_a + kTile * (p.M + 1);                             // [kTile][C+1]
@@ -284,6 +289,8 @@ features_fast512(const FeatParams p) {
   const int used_floats = (int)(reinterpret_cast<float *>(s_bmeta + 3 * p.M) - reinterpret_cast<float *>(smem_raw));
   float4 *s_rd = reinterpret_cast<float4 *>(reinterpret_cast<float *>(smem_raw) + ((used_floats + 3) & ~3));
   int4 *s_wr = reinterpret_cast<int4 *>(s_rd + p.seg_nbins);
+  float2 *s_twA = reinterpret_cast<float2 *>(s_wr + 8);            // [256]
+  float2 *s_twB = s_twA + 256;                                      // [128]
   // U / D alias the FFT exchange buffer (32 KB), which is idle during the output stage
   float *s_U = reinterpret_cast<float *>(s_exch);                   // [kTile][(M+2)|1]
   float *s_D = s_U + kTile * ((p.M + 2) | 1);
@@ -314,13 +321,10 @@ features_fast512(const FeatParams p) {
   for (int i = tid; i < kTile * 4; i += kFastThreads)
     s_p[(i >> 2) * PSTRIDE + PBINS + (i & 3)] = 0.f;
 
-  // per-lane twiddles (fixed for the whole kernel)
-  float2 twA[16];  // W256^(l16*k1)
-#pragma unroll
-  for (int k1 = 0; k1 < 16; ++k1) twA[k1] = p.twA[l16 * 16 + k1];
-  float2 twB[8];   // W512^(l16 + 16*k2)
-#pragma unroll
-  for (int k2 = 0; k2 < 8; ++k2) twB[k2] = p.twB[l16 * 9 + k2];
+  // twiddle tables in shared memory, lane-major so a half-warp reads consecutive float2:
+  // s_twA[k1*16 + l] = W256^(l*k1), s_twB[k2*16 + l] = W512^(l + 16*k2)
+  for (int i = tid; i < 256; i += kFastThreads) s_twA[i] = p.twA[(i & 15) * 16 + (i >> 4)];
+  for (int i = tid; i < 128; i += kFastThreads) s_twB[i] = p.twB[(i & 15) * 9 + (i >> 4)];
   const int partner = (16 - l16) & 15;
   const int Leff = min(L, 512);
 
@@ -335,12 +339,13 @@ features_fast512(const FeatParams p) {
   }
   __syncthreads();
   uint32_t ph0 = 0, ph1 = 0;
-  auto stage = [&](long long t, int b, int &utt, int &f0, int &nf, bool &bulk) {
-    const int2 td = p.tiles[t];
-    utt = td.x;
-    f0 = td.y;
-    nf = min(kTile, p.nframes[utt] - f0);
-    const long long gstart = p.starts[utt] + (long long)f0 * S;
+  auto stage = [&](long long t, int b, long long &row0, int &nf, bool &bulk) {
+    // one 32-byte descriptor per tile (two 16-byte loads, no dependent chain)
+    const int4 d0 = __ldg(reinterpret_cast<const int4 *>(p.ftiles + t));
+    const longlong2 d1 = __ldg(reinterpret_cast<const longlong2 *>(p.ftiles + t) + 1);
+    nf = d0.z;
+    const long long gstart = d1.x;
+    row0 = d1.y;
     const int count = (nf - 1) * S + L;
     const float *src = p.samples + gstart;
     float *dst = s_xbuf + b * xoff;
@@ -360,16 +365,18 @@ features_fast512(const FeatParams p) {
 
   long long tile = blockIdx.x;
   int buf = 0;
-  int utt = 0, f0 = 0, nf = 0;
+  long long row0 = 0;
+  int nf = 0;
   bool bulk = false;
-  if (tile < p.num_tiles) stage(tile, 0, utt, f0, nf, bulk);
+  if (tile < p.num_tiles) stage(tile, 0, row0, nf, bulk);
   for (; tile < p.num_tiles; buf ^= 1) {
     const long long next = tile + gridDim.x;
-    int n_utt = 0, n_f0 = 0, n_nf = 0;
+    long long n_row0 = 0;
+    int n_nf = 0;
     bool n_bulk = false;
     // prefetch the next tile while this one is transformed (its buffer was last read in
     // phase B of the previous iteration, which every thread has left)
-    if (next < p.num_tiles) stage(next, buf ^ 1, n_utt, n_f0, n_nf, n_bulk);
+    if (next < p.num_tiles) stage(next, buf ^ 1, n_row0, n_nf, n_bulk);
     if (bulk) {
       if (buf == 0) { mbar_wait(&s_full[0], ph0); ph0 ^= 1; }
       else { mbar_wait(&s_full[1], ph1); ph1 ^= 1; }
@@ -377,104 +384,135 @@ features_fast512(const FeatParams p) {
     __syncthreads();  // samples of this tile visible; previous tile's phase C is finished
     const float *s_x = s_xbuf + buf * xoff;
 
-    // ---- phase B: two frames per half-warp
-#pragma unroll 1
-    for (int pass = 0; pass < 2; ++pass) {
-      const int fl = 2 * (warp + 8 * half) + pass;
-      const bool active = fl < nf;
-      const float *xf = s_x + (active ? fl : 0) * S;
-      float2 v[16];
+    // ---- phase B: each half-warp transforms two frames at once (packed fp32, fft_math2.cuh)
+    {
+      const int flA = 2 * (warp + 8 * half), flB = flA + 1;
+      const bool actA = flA < nf, actB = flB < nf;
+      const float *xa = s_x + (actA ? flA : 0) * S;
+      const float *xb = s_x + (actB ? flB : 0) * S;
+      C2 v[16];
       // z[m] = x[2m] + i x[2m+1], m = 16 j + l16
       if (NJ < 16) {
         // compile-time pruned: every lane has exactly NJ non-zero inputs, S even, L == 32*NJ
 #pragma unroll
         for (int j = 0; j < 16; ++j) {
-          if (j < NJ) v[j] = *reinterpret_cast<const float2 *>(xf + 32 * j + 2 * l16);
-          else v[j] = c_make(0.f, 0.f);
+          if (j < NJ) {
+            // one 64-bit load per frame (a half-warp reads 128 contiguous bytes), then pair up
+            const float2 za = *reinterpret_cast<const float2 *>(xa + 32 * j + 2 * l16);
+            const float2 zb = *reinterpret_cast<const float2 *>(xb + 32 * j + 2 * l16);
+            v[j] = c2_make(p_make(za.x, zb.x), p_make(za.y, zb.y));
+          } else {
+            v[j] = c2_zero();
+          }
         }
       } else {
 #pragma unroll
         for (int j = 0; j < 16; ++j) {
           const int m = 16 * j + l16;
-          float re = (2 * m < Leff) ? xf[2 * m] : 0.f;
-          float im = (2 * m + 1 < Leff) ? xf[2 * m + 1] : 0.f;
-          v[j] = c_make(re, im);
+          const bool r_ok = 2 * m < Leff, i_ok = 2 * m + 1 < Leff;
+          v[j] = c2_make(p_make(r_ok ? xa[2 * m] : 0.f, r_ok ? xb[2 * m] : 0.f),
+                         p_make(i_ok ? xa[2 * m + 1] : 0.f, i_ok ? xb[2 * m + 1] : 0.f));
         }
       }
-      float sumsq = 0.f;
+      float2 sumsq = p_bc(0.f);
       if (p.need_energy) {
 #pragma unroll
         for (int j = 0; j < 16; ++j)
-          if (j < NJ) sumsq = fmaf(v[j].x, v[j].x, fmaf(v[j].y, v[j].y, sumsq));
+          if (j < NJ) sumsq = p_fma(v[j].re, v[j].re, p_fma(v[j].im, v[j].im, sumsq));
       }
-      // step 1: FFT16 over j  -> index k1, then twiddle W256^(l16*k1)
-      fft16<NJ>(v);
+      // step 1: FFT16 over j -> index k1, then twiddle W256^(l16*k1) (table in shared memory)
+      fft16_2<NJ>(v);
 #pragma unroll
-      for (int k1 = 1; k1 < 16; ++k1) v[k1] = c_mul(v[k1], twA[k1]);
-      __syncwarp();  // previous pass's step-2 loads are complete
+      for (int k1 = 1; k1 < 16; ++k1) v[k1] = c2_mul(v[k1], s_twA[k1 * 16 + l16]);
+      // exchange within the half-warp, real parts then imaginary parts through the same 2 KB
+      float2 *ex = my_exch;
 #pragma unroll
-      for (int k1 = 0; k1 < 16; ++k1) my_exch[exch_store_index(k1, l16)] = v[k1];
+      for (int k1 = 0; k1 < 16; ++k1) ex[exch_store_index(k1, l16)] = v[k1].re;
       __syncwarp();
-      // step 2: lane = k1 gathers n2 = 0..15
 #pragma unroll
       for (int c = 0; c < 8; ++c) {
-        const float4 q = *reinterpret_cast<const float4 *>(my_exch + exch_load_chunk_index(l16, c));
-        v[2 * c] = c_make(q.x, q.y);
-        v[2 * c + 1] = c_make(q.z, q.w);
+        const float4 q = *reinterpret_cast<const float4 *>(ex + exch_load_chunk_index(l16, c));
+        v[2 * c].re = make_float2(q.x, q.y);
+        v[2 * c + 1].re = make_float2(q.z, q.w);
       }
-      fft16<16>(v);  // v[k2] = Z[l16 + 16 k2]
+      __syncwarp();
+#pragma unroll
+      for (int k1 = 0; k1 < 16; ++k1) ex[exch_store_index(k1, l16)] = v[k1].im;
+      __syncwarp();
+#pragma unroll
+      for (int c = 0; c < 8; ++c) {
+        const float4 q = *reinterpret_cast<const float4 *>(ex + exch_load_chunk_index(l16, c));
+        v[2 * c].im = make_float2(q.x, q.y);
+        v[2 * c + 1].im = make_float2(q.z, q.w);
+      }
+      // step 2: lane = k1 holds n2 = 0..15
+      fft16_2<16>(v);  // v[k2] = Z[l16 + 16 k2]
       // untangle: partner value Z[256 - k] lives in lane (16 - l16) & 15
-      float *prow = s_p + fl * PSTRIDE;
+      float *prA = s_p + flA * PSTRIDE, *prB = prA + PSTRIDE;
 #pragma unroll
       for (int k2 = 0; k2 < 8; ++k2) {
         // sender slot t = 7 - k2: generic lanes send v[8 + t], lane 0 sends v[(9 + t) & 15]
         const int t = 7 - k2;
-        const float2 snd = (l16 == 0) ? v[(9 + t) & 15] : v[8 + t];
-        float2 zp;
-        zp.x = __shfl_sync(0xffffffffu, snd.x, partner, 16);
-        zp.y = __shfl_sync(0xffffffffu, snd.y, partner, 16);
-        const float2 zk = v[k2];
-        const float2 A = c_make(zk.x + zp.x, zk.y - zp.y);
-        const float2 B = c_make(zk.y + zp.y, zp.x - zk.x);
-        const float2 WB = c_mul(B, twB[k2]);
-        const float xr = A.x + WB.x, xi = A.y + WB.y;
-        const float pk = 0.25f * fmaf(xr, xr, xi * xi);
-        if (active) prow[l16 + 16 * k2] = pk;
+        const C2 snd = (l16 == 0) ? v[(9 + t) & 15] : v[8 + t];
+        C2 zp;
+        zp.re.x = __shfl_sync(0xffffffffu, snd.re.x, partner, 16);
+        zp.re.y = __shfl_sync(0xffffffffu, snd.re.y, partner, 16);
+        zp.im.x = __shfl_sync(0xffffffffu, snd.im.x, partner, 16);
+        zp.im.y = __shfl_sync(0xffffffffu, snd.im.y, partner, 16);
+        const C2 zk = v[k2];
+        const C2 A = c2_make(p_add(zk.re, zp.re), p_sub(zk.im, zp.im));
+        const C2 B = c2_make(p_add(zk.im, zp.im), p_sub(zp.re, zk.re));
+        const C2 WB = c2_mul(B, s_twB[k2 * 16 + l16]);
+        const float2 xr = p_add(A.re, WB.re), xi = p_add(A.im, WB.im);
+        const float2 pk = p_muls(p_fma(xr, xr, p_mul(xi, xi)), 0.25f);
+        if (actA) prA[l16 + 16 * k2] = pk.x;
+        if (actB) prB[l16 + 16 * k2] = pk.y;
         if (FULL) {
-          const float yr = A.x - WB.x, yi = A.y - WB.y;
-          const float pm = 0.25f * fmaf(yr, yr, yi * yi);
-          if (active) prow[256 - (l16 + 16 * k2)] = pm;  // k = 0 writes bin 256
+          const float2 yr = p_sub(A.re, WB.re), yi = p_sub(A.im, WB.im);
+          const float2 pm = p_muls(p_fma(yr, yr, p_mul(yi, yi)), 0.25f);
+          if (actA) prA[256 - (l16 + 16 * k2)] = pm.x;  // k = 0 writes bin 256
+          if (actB) prB[256 - (l16 + 16 * k2)] = pm.y;
         }
       }
       if (l16 == 0) {
         // bin 128 = Z[128] (its own partner): X = Zr - i Zi  -> |Z|^2
-        const float2 z = v[8];
-        if (active) prow[128] = fmaf(z.x, z.x, z.y * z.y);
+        const C2 z = v[8];
+        const float2 pz = p_fma(z.re, z.re, p_mul(z.im, z.im));
+        if (actA) prA[128] = pz.x;
+        if (actB) prB[128] = pz.y;
       }
       if (p.need_energy) {
         // frame energy = sum_k P[k], all 257 one-sided bins (feature.py:202), via Parseval:
         // (NFFT*sum x^2 + X0^2 + X256^2) / (2*NFFT), X0 = Zr+Zi, X256 = Zr-Zi of Z[0]
 #pragma unroll
-        for (int o = 8; o >= 1; o >>= 1) sumsq += __shfl_xor_sync(0xffffffffu, sumsq, o, 16);
-        if (l16 == 0 && active) {
-          const float x0 = v[0].x + v[0].y, x256 = v[0].x - v[0].y;
-          float e = (512.f * sumsq + x0 * x0 + x256 * x256) * (1.0f / (2.f * 512.f));
-          if (e == 0.f) e = kEpsF64AsF32;  // feature.py:205
-          s_en[fl] = e;
+        for (int o = 8; o >= 1; o >>= 1) {
+          sumsq.x += __shfl_xor_sync(0xffffffffu, sumsq.x, o, 16);
+          sumsq.y += __shfl_xor_sync(0xffffffffu, sumsq.y, o, 16);
+        }
+        if (l16 == 0) {
+          const float2 x0 = p_add(v[0].re, v[0].im), x256 = p_sub(v[0].re, v[0].im);
+          float ea = (512.f * sumsq.x + x0.x * x0.x + x256.x * x256.x) * (1.0f / (2.f * 512.f));
+          float eb = (512.f * sumsq.y + x0.y * x0.y + x256.y * x256.y) * (1.0f / (2.f * 512.f));
+          if (ea == 0.f) ea = kEpsF64AsF32;  // feature.py:205
+          if (eb == 0.f) eb = kEpsF64AsF32;
+          if (actA) s_en[flA] = ea;
+          if (actB) s_en[flB] = eb;
         }
       }
     }
     __syncthreads();
     // ---- phase C
-    const long long row0 = p.frame_offsets[utt] + f0;
-    if (use_seg)
+    if (use_seg && p.mode == FEAT_LMFE)
+      output_stage<kTile, true, FEAT_LMFE>(p, s_p, PSTRIDE, s_en, s_a, s_b, s_bw, s_bmeta, s_dct, nf, row0, s_rd,
+                                           s_wr, s_U, s_D, fm);
+    else if (use_seg)
       output_stage<kTile, true>(p, s_p, PSTRIDE, s_en, s_a, s_b, s_bw, s_bmeta, s_dct, nf, row0, s_rd, s_wr,
                                 s_U, s_D, fm);
     else
       output_stage<kTile, false>(p, s_p, PSTRIDE, s_en, s_a, s_b, s_bw, s_bmeta, s_dct, nf, row0, s_rd, s_wr,
                                  s_U, s_D, fm);
     tile = next;
-    utt = n_utt; f0 = n_f0; nf = n_nf; bulk = n_bulk;
+    row0 = n_row0; nf = n_nf; bulk = n_bulk;
   }
 }
 
@@ -583,6 +621,7 @@ static FeatParams make_params(const FeatArgs &a, const FftTables &t) {
   p.nframes = a.nframes;
   p.frame_offsets = a.frame_offsets;
   p.tiles = a.tiles;
+  p.ftiles = a.ftiles;
   p.num_tiles = a.num_tiles;
   p.L = a.L; p.S = a.S; p.K = a.K;
   p.M = a.M; p.C = a.C; p.dc_elim = a.dc_elim;
@@ -627,7 +666,7 @@ static int launch_fast(spb_context *ctx, const FeatParams &p, const FeatArgs &a)
   const int span_max = (kTile - 1) * a.S + a.L;
   size_t smem = 2 * (size_t)((span_max + 3) & ~3) * 4 + 16 * 256 * sizeof(float2) +
                 (size_t)kTile * ((FULL ? 257 : 129) + 4) * 4 + plan_smem_bytes(a, kTile) +
-                16 + (size_t)a.seg_nbins * 16 + 8 * 16;
+                16 + (size_t)a.seg_nbins * 16 + 8 * 16 + (256 + 128) * sizeof(float2);
   auto kern = features_fast512<NJ, FULL>;
   int per_sm = 0;
   int rc = configure_kernel(ctx, (const void *)kern, kFastThreads, smem, &per_sm);

@@ -148,4 +148,39 @@ int launch_build_tiles(spb_context *ctx, const int32_t *nframes, const int64_t *
   return SPB_OK;
 }
 
+__global__ void build_fft_tiles_kernel(const int32_t *__restrict__ nframes,
+                                       const int64_t *__restrict__ tile_offsets,
+                                       const int64_t *__restrict__ starts,
+                                       const int64_t *__restrict__ frame_offsets, long long U, int tile,
+                                       int stride, FftTile *__restrict__ tiles) {
+  const long long w = (blockIdx.x * (long long)blockDim.x + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
+  if (w >= U) return;
+  const int F = nframes[w];
+  const int nt = (F + tile - 1) / tile;
+  const long long base = tile_offsets[w];
+  for (int t = lane; t < nt; t += 32) {
+    FftTile d;
+    d.utt = (int)w;
+    d.f0 = t * tile;
+    d.nf = min(tile, F - d.f0);
+    d.pad = 0;
+    d.gstart = starts[w] + (long long)d.f0 * stride;
+    d.row0 = frame_offsets[w] + d.f0;
+    tiles[base + t] = d;
+  }
+}
+
+int launch_build_fft_tiles(spb_context *ctx, const int32_t *nframes, const int64_t *tile_offsets,
+                           const int64_t *starts, const int64_t *frame_offsets, int64_t U, int tile,
+                           int stride, FftTile *tiles) {
+  if (U <= 0) return SPB_OK;
+  const long long threads = U * 32;
+  const unsigned blocks = (unsigned)((threads + 255) / 256);
+  build_fft_tiles_kernel<<<blocks, 256, 0, ctx->stream>>>(nframes, tile_offsets, starts, frame_offsets, U, tile,
+                                                          stride, tiles);
+  SPB_LAUNCH_CHECK(ctx, "build_fft_tiles_kernel");
+  return SPB_OK;
+}
+
 }  // namespace spb

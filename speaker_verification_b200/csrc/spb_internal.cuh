@@ -79,6 +79,14 @@ struct spb_plan {
 };
 
 namespace spb {
+// everything the FFT kernel needs to know about one 32-frame tile (one 32-byte load, no
+// dependent descriptor chain)
+struct __align__(16) FftTile {
+  int utt, f0, nf, pad;
+  long long gstart;  // first sample of the tile in the arena
+  long long row0;    // first output row of the tile
+};
+
 // a run of whole utterances whose intermediates fit in L2
 struct BatchChunk {
   int64_t u0, u1;        // utterances [u0, u1)
@@ -104,6 +112,7 @@ struct spb_batch {
   int32_t *d_nframes = nullptr;          // [U]
   int64_t *d_frame_offsets = nullptr;    // [U+1]
   int2 *d_tiles = nullptr;               // [total_tiles] {utt, first frame}
+  spb::FftTile *d_ftiles = nullptr;      // [total_tiles] full descriptors for the fast kernel
   int2 *d_cm_tiles = nullptr;            // [total_cm_tiles] {utt, first row}
   int4 *d_big_tiles = nullptr;           // large-tile cmvnw: {utt, first row, rows, 0}, longest first per chunk
   int big_rmax = 0;                      // 0: large-tile path not usable for this plan
@@ -148,6 +157,7 @@ struct FeatArgs {
   const int32_t *nframes;    // [U]
   const int64_t *frame_offsets;  // [U+1]
   const int2 *tiles;         // [num_tiles]
+  const FftTile *ftiles;     // [num_tiles] or nullptr
   int64_t num_tiles;
   int tile_frames;
   int L, S, nfft, K;
@@ -192,6 +202,9 @@ int launch_convert(spb_context *ctx, const void *in, int dtype_in, void *out, in
                    int64_t n);
 int launch_build_tiles(spb_context *ctx, const int32_t *nframes, const int64_t *tile_offsets,
                        int64_t U, int tile, int2 *tiles);
+int launch_build_fft_tiles(spb_context *ctx, const int32_t *nframes, const int64_t *tile_offsets,
+                           const int64_t *starts, const int64_t *frame_offsets, int64_t U, int tile,
+                           int stride, FftTile *tiles);
 
 int launch_cosine_scores(spb_context *ctx, const float *d_E, int64_t m, const float *d_T,
                          int64_t n, int d, float *d_S);
