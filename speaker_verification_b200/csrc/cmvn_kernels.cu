@@ -465,35 +465,56 @@ cmvnw_big_kernel(const CmBigParams p) {
         const float *pc = col + (size_t)(q0 + h) * cols;     // centre row
         const float *pin = col + (size_t)(q0 + win) * cols;  // row entering the window
         const float *pout = col + (size_t)q0 * cols;         // row leaving the window
+        // The float64 window sums anchor the first row of the block; inside the block
+        // (<= 29 steps) the window moves by float32 deltas D = sum(x_in - x_out), which costs no
+        // conversions.  Error of D: <= 30 * 2^-24 * |D| on the SUM, i.e. ~1e-7 * |x| on the mean.
+        // mean = mh + (ml + D/win) with mh + ml the float64 mean split in two floats, so
+        // x - mean is formed as (x - mh) - (ml + D/win): exact to 1 ulp of the RESULT even when
+        // |mean| >> |x - mean| (processing.py:304-307 subtracts in float64).
+        const float inv_w = (float)inv_win;
+        const double m0x = w1x * inv_win, m0y = w1y * inv_win;
+        const float mhx = (float)m0x, mhy = (float)m0y;
+        const float mlx = (float)(m0x - (double)mhx), mly = (float)(m0y - (double)mhy);
+        float Dx = 0.f, Dy = 0.f;
+        if (STAGE == 1) {
 #pragma unroll 2
-        for (int q = q0; q < q1; ++q) {
-          const float2 xc = *reinterpret_cast<const float2 *>(pc);
-          float2 o;
-          if (STAGE == 1) {
-            // processing.py:304-307: float32(vec[i] - mean(window))
-            // (x is float32 here; subtracting the float32-rounded float64 mean differs from
-            // the reference's float64 subtraction by <= 1 ulp of the result)
-            o.x = xc.x - (float)(w1x * inv_win);
-            o.y = xc.y - (float)(w1y * inv_win);
-          } else {
-            // processing.py:318-322: ms / (std(window) + eps), population std
-            const double mx = w1x * inv_win, my = w1y * inv_win;
-            const float vx = (float)fma(-mx, mx, w2x * inv_win), vy = (float)fma(-my, my, w2y * inv_win);
+          for (int q = q0; q < q1; ++q) {
+            const float2 xc = *reinterpret_cast<const float2 *>(pc);
+            float2 o;
+            o.x = (xc.x - mhx) - fmaf(Dx, inv_w, mlx);
+            o.y = (xc.y - mhy) - fmaf(Dy, inv_w, mly);
+            *reinterpret_cast<float2 *>(dst) = o;
+            const float2 xi = *reinterpret_cast<const float2 *>(pin);
+            const float2 xo = *reinterpret_cast<const float2 *>(pout);
+            Dx += xi.x - xo.x;
+            Dy += xi.y - xo.y;
+            dst += ld; pc += cols; pin += cols; pout += cols;
+          }
+        } else {
+          // processing.py:318-322: ms / (std(window) + eps), population std; the input is the
+          // mean-subtracted signal, so E[x^2] >> mean^2 and float32 is enough for the variance
+          const float e0x = (float)(w2x * inv_win), e0y = (float)(w2y * inv_win);
+          float Qx = 0.f, Qy = 0.f;
+#pragma unroll 2
+          for (int q = q0; q < q1; ++q) {
+            const float2 xc = *reinterpret_cast<const float2 *>(pc);
+            const float mx = mhx + fmaf(Dx, inv_w, mlx), my = mhy + fmaf(Dy, inv_w, mly);
+            const float vx = fmaf(-mx, mx, fmaf(Qx, inv_w, e0x)), vy = fmaf(-my, my, fmaf(Qy, inv_w, e0y));
             float sx, sy;
             asm("sqrt.approx.f32 %0, %1;" : "=f"(sx) : "f"(fmaxf(vx, 0.f)));
             asm("sqrt.approx.f32 %0, %1;" : "=f"(sy) : "f"(fmaxf(vy, 0.f)));
+            float2 o;
             o.x = __fdividef(xc.x, sx + p.eps);
             o.y = __fdividef(xc.y, sy + p.eps);
-          }
-          *reinterpret_cast<float2 *>(dst) = o;
-          if (q + 1 < q1) {
+            *reinterpret_cast<float2 *>(dst) = o;
             const float2 xi = *reinterpret_cast<const float2 *>(pin);
             const float2 xo = *reinterpret_cast<const float2 *>(pout);
-            const double ix = (double)xi.x, iy = (double)xi.y, ox = (double)xo.x, oy = (double)xo.y;
-            w1x += ix - ox; w1y += iy - oy;
-            if (STAGE == 2) { w2x += fma(ix, ix, -ox * ox); w2y += fma(iy, iy, -oy * oy); }
+            Dx += xi.x - xo.x;
+            Dy += xi.y - xo.y;
+            Qx += fmaf(xi.x, xi.x, -xo.x * xo.x);
+            Qy += fmaf(xi.y, xi.y, -xo.y * xo.y);
+            dst += ld; pc += cols; pin += cols; pout += cols;
           }
-          dst += ld; pc += cols; pin += cols; pout += cols;
         }
       }
     }
