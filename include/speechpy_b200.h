@@ -73,10 +73,11 @@ SPB_API int spb_device_info(spb_context *ctx, int32_t *sm_count, int32_t *cc_maj
                     int32_t *cc_minor, uint64_t *total_mem);
 /* Number of kernels this context has launched so far (bench.py's gpu_launches). */
 SPB_API int spb_launch_count(spb_context *ctx, uint64_t *count);
-/* Per-kernel device timing: when enabled, every launch of the three hot kernels is
+/* Per-kernel device timing: when enabled, every launch of the hot kernels is
  * bracketed by CUDA events on the context's stream.  spb_timing_read synchronises,
  * sums the elapsed times recorded since the last read and clears them.
- * kernel: 0 = features (framing+FFT+mel+log), 1 = cmvnw stage 1, 2 = cmvnw stage 2. */
+ * kernel: 0 = features (framing+FFT+mel+log), 1 = cmvnw stage 1, 2 = cmvnw stage 2,
+ * 3 = cosine GEMM. */
 SPB_API int spb_timing_enable(spb_context *ctx, int32_t on);
 SPB_API int spb_timing_read(spb_context *ctx, int32_t kernel, double *total_ms, uint64_t *launches);
 /* Pinned host memory, so callers can hand page-locked buffers to the host API. */
@@ -182,12 +183,23 @@ SPB_API int spb_lmfe_batch_dev(spb_context *ctx, const spb_batch *batch, const f
  * d_out (total_frames, C, 3) float32. */
 SPB_API int spb_mfcc_delta_batch_dev(spb_context *ctx, const spb_batch *batch,
                              const float *d_samples, int64_t arena_len, float *d_out);
-/* Host-pointer variants: copy the arena in, run, copy the result out (chunked
- * through the context's pinned staging unless the buffers are already pinned). */
+/* Host-pointer variants, pipelined over chunks of whole utterances: the host->device copy
+ * of chunk k+1, the kernels of chunk k and the device->host copy of chunk k-1 run on three
+ * streams, so a call costs about max(H2D, compute, D2H).  Pinned buffers (spb_host_alloc)
+ * give full PCIe rate; pageable buffers work but copy synchronously. */
 SPB_API int spb_lmfe_cmvnw_batch(spb_context *ctx, const spb_batch *batch, const float *samples,
                          int64_t arena_len, float *out);
 SPB_API int spb_mfcc_delta_batch(spb_context *ctx, const spb_batch *batch, const float *samples,
                          int64_t arena_len, float *out);
+/* Same, with the sample arena in any spb_dtype.  SPB_I16 is what
+ * scipy.io.wavfile.read hands the reference (load_data.py:58-70) before
+ * `signal.astype(float)` (feature.py:182): the PCM arena crosses PCIe at 2 bytes per
+ * sample and is widened on the device (exact: every int16/int32<2^24 is a float32).
+ * starts/lengths/arena_len are in samples. */
+SPB_API int spb_lmfe_cmvnw_batch_dtype(spb_context *ctx, const spb_batch *batch, const void *samples,
+                               int dtype, int64_t arena_len, float *out);
+SPB_API int spb_mfcc_delta_batch_dtype(spb_context *ctx, const spb_batch *batch, const void *samples,
+                               int dtype, int64_t arena_len, float *out);
 
 /* ------------------------------------------------------- a10  cosine scores
  * evaluation.py:76-77 over all (enrolment, test) pairs at once:

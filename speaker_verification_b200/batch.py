@@ -20,8 +20,22 @@ from .speechpy import feature as _feature
 from .speechpy import processing as _processing
 
 
-def pack(signals, align: int = 4):
-    """Concatenate 1-D signals into one float32 arena.
+_ARENA_DTYPES = {np.dtype(np.float32): _lib.F32, np.dtype(np.float64): _lib.F64,
+                 np.dtype(np.int16): _lib.I16, np.dtype(np.int32): _lib.I32}
+
+
+def _as_arena(arena):
+    """Contiguous arena in a dtype the library ingests + its spb_dtype code.  int16 PCM
+    (what ``scipy.io.wavfile.read`` returns, load_data.py:58) stays int16: it crosses PCIe
+    at 2 bytes per sample and is widened on the device like ``signal.astype(float)``."""
+    arena = np.ascontiguousarray(arena)
+    if arena.dtype not in _ARENA_DTYPES:
+        arena = arena.astype(np.float32)
+    return arena, _ARENA_DTYPES[arena.dtype]
+
+
+def pack(signals, align: int = 4, dtype=np.float32):
+    """Concatenate 1-D signals into one arena of ``dtype`` (float32, or int16 for PCM).
 
     Returns (arena, starts, lengths).  Every utterance starts on a multiple of
     ``align`` samples so the kernels can stage tiles with 128-bit loads.
@@ -31,7 +45,7 @@ def pack(signals, align: int = 4):
     starts = np.zeros(len(signals), dtype=np.int64)
     if len(signals) > 1:
         np.cumsum(padded[:-1], out=starts[1:])
-    arena = np.zeros(int(padded.sum()), dtype=np.float32)
+    arena = np.zeros(int(padded.sum()), dtype=dtype)
     for s, st, n in zip(signals, starts, lengths):
         arena[st:st + n] = s
     return arena, starts, lengths
@@ -129,20 +143,20 @@ class FeatureBatch:
     def lmfe_cmvnw(self, arena: np.ndarray, out: np.ndarray | None = None) -> np.ndarray:
         """lmfe + cmvnw of every utterance: (total_frames, num_filters) float32; rows of
         utterance u are frame_offsets[u]:frame_offsets[u+1]."""
-        arena = np.ascontiguousarray(arena, dtype=np.float32)
+        arena, code = _as_arena(arena)
         if out is None:
             out = np.empty((self.total_frames, self.num_filters), dtype=np.float32)
-        _lib.check(self.ctx.lib.spb_lmfe_cmvnw_batch(self.ctx.handle, self.handle, _lib.ptr(arena),
-                                                     arena.shape[0], _lib.ptr(out)), self.ctx.handle)
+        _lib.check(self.ctx.lib.spb_lmfe_cmvnw_batch_dtype(self.ctx.handle, self.handle, _lib.ptr(arena), code,
+                                                           arena.shape[0], _lib.ptr(out)), self.ctx.handle)
         return out
 
     def mfcc_delta(self, arena: np.ndarray, out: np.ndarray | None = None) -> np.ndarray:
         """mfcc + extract_derivative_feature: (total_frames, num_cepstral, 3) float32."""
-        arena = np.ascontiguousarray(arena, dtype=np.float32)
+        arena, code = _as_arena(arena)
         if out is None:
             out = np.empty((self.total_frames, self.num_cepstral, 3), dtype=np.float32)
-        _lib.check(self.ctx.lib.spb_mfcc_delta_batch(self.ctx.handle, self.handle, _lib.ptr(arena),
-                                                     arena.shape[0], _lib.ptr(out)), self.ctx.handle)
+        _lib.check(self.ctx.lib.spb_mfcc_delta_batch_dtype(self.ctx.handle, self.handle, _lib.ptr(arena), code,
+                                                           arena.shape[0], _lib.ptr(out)), self.ctx.handle)
         return out
 
     # ---- device-pointer entry points (asynchronous on ctx.stream()) -----------------

@@ -192,6 +192,7 @@ int spb_init(int device, spb_context **out) {
   }
   if ((e = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking)) != cudaSuccess ||
       (e = cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking)) != cudaSuccess ||
+      (e = cudaStreamCreateWithFlags(&ctx->out_stream, cudaStreamNonBlocking)) != cudaSuccess ||
       (e = cudaEventCreateWithFlags(&ctx->ev_a, cudaEventDisableTiming)) != cudaSuccess ||
       (e = cudaEventCreateWithFlags(&ctx->ev_b, cudaEventDisableTiming)) != cudaSuccess) {
     delete ctx;
@@ -206,11 +207,13 @@ int spb_destroy(spb_context *ctx) {
   cudaSetDevice(ctx->device);
   cudaStreamSynchronize(ctx->stream);
   cudaStreamSynchronize(ctx->copy_stream);
+  cudaStreamSynchronize(ctx->out_stream);
   for (auto &b : ctx->scratch)
     if (b.ptr) cudaFree(b.ptr);
   for (int i = 0; i < 2; ++i)
     if (ctx->pinned[i]) cudaFreeHost(ctx->pinned[i]);
   for (auto e : ctx->ev_pool) cudaEventDestroy(e);
+  for (auto e : ctx->pipe_events) cudaEventDestroy(e);
   for (auto &kv : ctx->fft_tables) {
     if (kv.second.d_tw) cudaFree(kv.second.d_tw);
     if (kv.second.d_twA) cudaFree(kv.second.d_twA);
@@ -220,6 +223,7 @@ int spb_destroy(spb_context *ctx) {
   cudaEventDestroy(ctx->ev_b);
   cudaStreamDestroy(ctx->stream);
   cudaStreamDestroy(ctx->copy_stream);
+  cudaStreamDestroy(ctx->out_stream);
   delete ctx;
   return SPB_OK;
 }
@@ -590,6 +594,15 @@ int spb_batch_create(spb_context *ctx, const spb_plan *plan, const int64_t *star
   }
   b->total_frames = b->h_frame_offsets[U];
   b->total_tiles = tile_off[U];
+  for (BatchChunk &c : ch.chunks) {
+    c.s_lo = INT64_MAX;
+    c.s_hi = 0;
+    for (int64_t u = c.u0; u < c.u1; ++u) {
+      c.s_lo = std::min(c.s_lo, starts[u]);
+      c.s_hi = std::max(c.s_hi, starts[u] + lengths[u]);
+    }
+    b->chunk_span_total += c.s_hi - c.s_lo;
+  }
   b->total_cm_tiles = cm_off[U];
   // large-tile cmvnw table: balanced tiles per utterance, longest first inside each chunk
   std::vector<int4> big;
@@ -743,39 +756,51 @@ static int check_batch(spb_context *ctx, const spb_batch *b, int64_t arena_len, 
 
 // lmfe -> cmvnw over chunks of whole utterances; the lmfe and mean-subtracted
 // intermediates of a chunk live in two chunk-sized scratch buffers that stay in L2.
-static int run_lmfe_cmvnw(spb_context *ctx, const spb_batch *b, const float *d_samples,
-                          int64_t arena_len, float *d_out) {
+static int lmfe_cmvnw_chunk(spb_context *ctx, const spb_batch *b, const BatchChunk &c,
+                            const float *d_samples, int64_t arena_len, float *d_lmfe, float *d_ms,
+                            float *d_out) {
+  const spb_plan *pl = b->plan;
+  const int M = pl->p.num_filters, win = pl->p.cmvn_window;
+  FeatArgs a;
+  // rows are addressed by their global index; bias the scratch pointers so that row
+  // c.row0 lands at the start of the chunk buffer
+  float *lmfe_biased = d_lmfe - (ptrdiff_t)c.row0 * M;
+  fill_feat_args(a, b, d_samples, arena_len, FEAT_LMFE, lmfe_biased, nullptr);
+  a.tiles = b->d_tiles + c.tile0;
+  a.ftiles = b->d_ftiles + c.tile0;
+  a.num_tiles = c.tile1 - c.tile0;
+  int rc = run_features(ctx, a);
+  if (rc) return rc;
+  float *ms_biased = d_ms ? d_ms - (ptrdiff_t)c.row0 * M : nullptr;
+  if (b->big_rmax > 0 && !g_force_small_cmvnw && (((size_t)d_out) & 15) == 0)
+    return launch_cmvnw_big(ctx, lmfe_biased, ms_biased, d_out, b->d_nframes, b->d_frame_offsets,
+                            b->d_big_tiles + c.big0, c.big1 - c.big0, b->big_rmax, M, M, win,
+                            pl->p.cmvn_variance);
+  return launch_cmvnw_f32(ctx, lmfe_biased, ms_biased, d_out, b->d_nframes, b->d_frame_offsets,
+                          b->d_cm_tiles + c.cm0, c.cm1 - c.cm0, b->cm_tile_rows, M, M, win,
+                          pl->p.cmvn_variance);
+}
+
+static int lmfe_cmvnw_prepare(spb_context *ctx, const spb_batch *b, float **d_lmfe, float **d_ms) {
   const spb_plan *pl = b->plan;
   const int M = pl->p.num_filters, win = pl->p.cmvn_window;
   SPB_REQUIRE(ctx, win > 0 && (win & 1), "lmfe_cmvnw: plan has no (odd) cmvn_window");
   SPB_REQUIRE(ctx, M >= 1, "lmfe_cmvnw: plan has no filterbank");
   if (!cmvnw_supported(M, win)) return fail(ctx, SPB_ERR_UNSUPPORTED, "cmvnw: window x columns too large for shared memory");
-  const spb_batch &ch = *b;
-  if (ch.chunks.empty()) return SPB_OK;
-  const size_t chunk_bytes = (size_t)ch.max_chunk_rows * M * 4;
-  float *d_lmfe = (float *)scratch(ctx, 2, chunk_bytes);
-  float *d_ms = pl->p.cmvn_variance ? (float *)scratch(ctx, 3, chunk_bytes) : nullptr;
-  if (!d_lmfe || (pl->p.cmvn_variance && !d_ms)) return SPB_ERR_CUDA;
-  for (const BatchChunk &c : ch.chunks) {
-    FeatArgs a;
-    // rows are addressed by their global index; bias the scratch pointers so that row
-    // c.row0 lands at the start of the chunk buffer
-    float *lmfe_biased = d_lmfe - (ptrdiff_t)c.row0 * M;
-    fill_feat_args(a, b, d_samples, arena_len, FEAT_LMFE, lmfe_biased, nullptr);
-    a.tiles = b->d_tiles + c.tile0;
-    a.ftiles = b->d_ftiles + c.tile0;
-    a.num_tiles = c.tile1 - c.tile0;
-    int rc = run_features(ctx, a);
-    if (rc) return rc;
-    float *ms_biased = d_ms ? d_ms - (ptrdiff_t)c.row0 * M : nullptr;
-    if (b->big_rmax > 0 && !g_force_small_cmvnw && (((size_t)d_out) & 15) == 0)
-      rc = launch_cmvnw_big(ctx, lmfe_biased, ms_biased, d_out, b->d_nframes, b->d_frame_offsets,
-                            b->d_big_tiles + c.big0, c.big1 - c.big0, b->big_rmax, M, M, win,
-                            pl->p.cmvn_variance);
-    else
-      rc = launch_cmvnw_f32(ctx, lmfe_biased, ms_biased, d_out, b->d_nframes, b->d_frame_offsets,
-                            b->d_cm_tiles + c.cm0, c.cm1 - c.cm0, b->cm_tile_rows, M, M, win,
-                            pl->p.cmvn_variance);
+  const size_t chunk_bytes = (size_t)std::max<int64_t>(b->max_chunk_rows, 1) * M * 4;
+  *d_lmfe = (float *)scratch(ctx, 2, chunk_bytes);
+  *d_ms = pl->p.cmvn_variance ? (float *)scratch(ctx, 3, chunk_bytes) : nullptr;
+  if (!*d_lmfe || (pl->p.cmvn_variance && !*d_ms)) return SPB_ERR_CUDA;
+  return SPB_OK;
+}
+
+static int run_lmfe_cmvnw(spb_context *ctx, const spb_batch *b, const float *d_samples,
+                          int64_t arena_len, float *d_out) {
+  float *d_lmfe, *d_ms;
+  int rc = lmfe_cmvnw_prepare(ctx, b, &d_lmfe, &d_ms);
+  if (rc) return rc;
+  for (const BatchChunk &c : b->chunks) {
+    rc = lmfe_cmvnw_chunk(ctx, b, c, d_samples, arena_len, d_lmfe, d_ms, d_out);
     if (rc) return rc;
   }
   return SPB_OK;
@@ -1079,34 +1104,102 @@ int spb_mfcc_delta_batch_dev(spb_context *ctx, const spb_batch *b, const float *
   return run_simple_mode(ctx, b, d_samples, arena_len, FEAT_MFCC_DELTA, d_out, nullptr);
 }
 
-static int host_batch(spb_context *ctx, const spb_batch *b, const float *samples, int64_t arena_len,
-                      float *out, int which) {
+// Host-buffer batch calls, pipelined over the batch's chunks (runs of whole utterances):
+//   copy_stream : H2D of chunk k+1's sample span (raw dtype)
+//   stream      : [convert to float32] + kernels of chunk k
+//   out_stream  : D2H of chunk k-1's feature rows
+// so a call costs about max(H2D, compute, D2H) instead of their sum (PCIe is full duplex).
+// `samples` may be float32, int16 (what scipy.io.wavfile hands load_data.py:58-70), int32 or
+// float64; non-float32 input is widened on the device exactly like signal.astype(float).
+static int host_batch(spb_context *ctx, const spb_batch *b, const void *samples, int dtype,
+                      int64_t arena_len, float *out, int which) {
   int rc = check_batch(ctx, b, arena_len, samples, out);
   if (rc) return rc;
+  SPB_REQUIRE(ctx, dtype == SPB_F32 || dtype == SPB_F64 || dtype == SPB_I16 || dtype == SPB_I32,
+              "batch call: unsupported sample dtype");
   SPB_CUDA(ctx, cudaSetDevice(ctx->device));
   if (b->total_frames == 0) return SPB_OK;
+  const size_t esz = (dtype == SPB_F64) ? 8 : (dtype == SPB_I16 ? 2 : 4);
   const int width = (which == 0) ? b->plan->p.num_filters : b->plan->p.num_cepstral * 3;
   float *d_samples = (float *)scratch(ctx, 0, (size_t)arena_len * 4);
   float *d_out = (float *)scratch(ctx, 1, (size_t)b->total_frames * width * 4);
-  if (!d_samples || !d_out) return SPB_ERR_CUDA;
-  SPB_CUDA(ctx, cudaMemcpyAsync(d_samples, samples, (size_t)arena_len * 4, cudaMemcpyHostToDevice, ctx->stream));
-  rc = (which == 0) ? run_lmfe_cmvnw(ctx, b, d_samples, arena_len, d_out)
-                    : run_simple_mode(ctx, b, d_samples, arena_len, FEAT_MFCC_DELTA, d_out, nullptr);
-  if (rc) return rc;
-  SPB_CUDA(ctx, cudaMemcpyAsync(out, d_out, (size_t)b->total_frames * width * 4, cudaMemcpyDeviceToHost, ctx->stream));
+  char *d_raw = (dtype == SPB_F32) ? (char *)d_samples : (char *)scratch(ctx, 5, (size_t)arena_len * esz);
+  if (!d_samples || !d_out || !d_raw) return SPB_ERR_CUDA;
+  float *d_lmfe = nullptr, *d_ms = nullptr;
+  if (which == 0 && (rc = lmfe_cmvnw_prepare(ctx, b, &d_lmfe, &d_ms))) return rc;
+  const size_t nch = b->chunks.size();
+  // chunk spans overlap when utterances are not packed in order: then copy the arena once
+  const bool piecewise = b->chunk_span_total <= arena_len + arena_len / 4;
+  while (ctx->pipe_events.size() < 2 * nch + 1) {
+    cudaEvent_t e;
+    SPB_CUDA(ctx, cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+    ctx->pipe_events.push_back(e);
+  }
+  // the copy streams must not overtake earlier work on the compute stream that uses the scratch
+  cudaEvent_t ev_start = ctx->pipe_events[2 * nch];
+  SPB_CUDA(ctx, cudaEventRecord(ev_start, ctx->stream));
+  SPB_CUDA(ctx, cudaStreamWaitEvent(ctx->copy_stream, ev_start, 0));
+  SPB_CUDA(ctx, cudaStreamWaitEvent(ctx->out_stream, ev_start, 0));
+  if (!piecewise) {
+    SPB_CUDA(ctx, cudaMemcpyAsync(d_raw, samples, (size_t)arena_len * esz, cudaMemcpyHostToDevice, ctx->copy_stream));
+    SPB_CUDA(ctx, cudaEventRecord(ctx->pipe_events[0], ctx->copy_stream));
+    SPB_CUDA(ctx, cudaStreamWaitEvent(ctx->stream, ctx->pipe_events[0], 0));
+    if (dtype != SPB_F32 && (rc = launch_convert(ctx, d_raw, dtype, d_samples, SPB_F32, arena_len))) return rc;
+  }
+  for (size_t k = 0; k < nch; ++k) {
+    const BatchChunk &c = b->chunks[k];
+    cudaEvent_t ev_in = ctx->pipe_events[2 * k], ev_done = ctx->pipe_events[2 * k + 1];
+    if (piecewise) {
+      const int64_t n = c.s_hi - c.s_lo;
+      SPB_CUDA(ctx, cudaMemcpyAsync(d_raw + (size_t)c.s_lo * esz, (const char *)samples + (size_t)c.s_lo * esz,
+                                    (size_t)n * esz, cudaMemcpyHostToDevice, ctx->copy_stream));
+      SPB_CUDA(ctx, cudaEventRecord(ev_in, ctx->copy_stream));
+      SPB_CUDA(ctx, cudaStreamWaitEvent(ctx->stream, ev_in, 0));
+      if (dtype != SPB_F32 &&
+          (rc = launch_convert(ctx, d_raw + (size_t)c.s_lo * esz, dtype, d_samples + c.s_lo, SPB_F32, n)))
+        return rc;
+    }
+    if (which == 0) {
+      rc = lmfe_cmvnw_chunk(ctx, b, c, d_samples, arena_len, d_lmfe, d_ms, d_out);
+    } else {
+      FeatArgs a;
+      fill_feat_args(a, b, d_samples, arena_len, FEAT_MFCC_DELTA, d_out, nullptr);
+      a.tiles = b->d_tiles + c.tile0;
+      a.ftiles = b->d_ftiles + c.tile0;
+      a.num_tiles = c.tile1 - c.tile0;
+      rc = run_features(ctx, a);
+    }
+    if (rc) return rc;
+    SPB_CUDA(ctx, cudaEventRecord(ev_done, ctx->stream));
+    SPB_CUDA(ctx, cudaStreamWaitEvent(ctx->out_stream, ev_done, 0));
+    SPB_CUDA(ctx, cudaMemcpyAsync(out + (size_t)c.row0 * width, d_out + (size_t)c.row0 * width,
+                                  (size_t)(c.row1 - c.row0) * width * 4, cudaMemcpyDeviceToHost, ctx->out_stream));
+  }
+  SPB_CUDA(ctx, cudaStreamSynchronize(ctx->out_stream));
   SPB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
   return SPB_OK;
 }
 
 int spb_lmfe_cmvnw_batch(spb_context *ctx, const spb_batch *b, const float *samples,
                          int64_t arena_len, float *out) {
-  return host_batch(ctx, b, samples, arena_len, out, 0);
+  return host_batch(ctx, b, samples, SPB_F32, arena_len, out, 0);
+}
+
+int spb_lmfe_cmvnw_batch_dtype(spb_context *ctx, const spb_batch *b, const void *samples, int dtype,
+                               int64_t arena_len, float *out) {
+  return host_batch(ctx, b, samples, dtype, arena_len, out, 0);
 }
 
 int spb_mfcc_delta_batch(spb_context *ctx, const spb_batch *b, const float *samples,
                          int64_t arena_len, float *out) {
   if (b && b->plan->p.num_cepstral < 1) return fail(ctx, SPB_ERR_INVALID, "mfcc_delta: plan has num_cepstral == 0");
-  return host_batch(ctx, b, samples, arena_len, out, 1);
+  return host_batch(ctx, b, samples, SPB_F32, arena_len, out, 1);
+}
+
+int spb_mfcc_delta_batch_dtype(spb_context *ctx, const spb_batch *b, const void *samples, int dtype,
+                               int64_t arena_len, float *out) {
+  if (b && b->plan->p.num_cepstral < 1) return fail(ctx, SPB_ERR_INVALID, "mfcc_delta: plan has num_cepstral == 0");
+  return host_batch(ctx, b, samples, dtype, arena_len, out, 1);
 }
 
 }  // extern "C"

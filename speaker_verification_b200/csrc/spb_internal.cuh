@@ -33,7 +33,9 @@ struct FftTables {
 struct spb_context {
   int device = 0;
   cudaStream_t stream = nullptr;
-  cudaStream_t copy_stream = nullptr;
+  cudaStream_t copy_stream = nullptr;  // host->device leg of the pipelined host batch calls
+  cudaStream_t out_stream = nullptr;   // device->host leg
+  std::vector<cudaEvent_t> pipe_events;  // per-chunk events of the pipelined host batch calls
   cudaEvent_t ev_a = nullptr, ev_b = nullptr;
   int sm_count = 0, cc_major = 0, cc_minor = 0;
   size_t total_mem = 0;
@@ -94,6 +96,7 @@ struct BatchChunk {
   int64_t cm0, cm1;      // cmvnw tiles
   int64_t row0, row1;    // output rows
   int64_t big0 = 0, big1 = 0;  // large-tile cmvnw tiles
+  int64_t s_lo = 0, s_hi = 0;  // sample span [min start, max end) of the chunk's utterances
 };
 }  // namespace spb
 
@@ -118,6 +121,7 @@ struct spb_batch {
   int big_rmax = 0;                      // 0: large-tile path not usable for this plan
   std::vector<spb::BatchChunk> chunks;
   int64_t max_chunk_rows = 0;
+  int64_t chunk_span_total = 0;  // sum of the chunks' sample spans (== arena use when utterances are packed in order)
 };
 
 namespace spb {

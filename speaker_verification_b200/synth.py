@@ -19,6 +19,13 @@ def audio(seed: int, num_samples: int, dtype=np.float32, sigma: float = 0.1) -> 
     return (sigma * rng.standard_normal(num_samples)).astype(dtype)
 
 
+def pcm16(seed: int, num_samples: int, sigma: float = 0.1) -> np.ndarray:
+    """One utterance of 16-bit PCM noise, round(N(0, sigma) * 32768) clipped to int16: the
+    dtype ``scipy.io.wavfile.read`` hands the reference (load_data.py:58)."""
+    x = audio(seed, num_samples, np.float64, sigma) * 32768.0
+    return np.clip(np.round(x), -32768, 32767).astype(np.int16)
+
+
 def cfg3_lengths(num_utterances: int, seed: int = 3) -> np.ndarray:
     """VoxCeleb1-dev-shaped durations: clip(lognormal(ln 7.2 s, 0.5), 4 s, 20 s)
     in whole samples (int64)."""

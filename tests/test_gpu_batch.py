@@ -123,3 +123,68 @@ def test_large_tile_cmvnw_matches_small_tile_kernels(sp):
         v = rng.standard_normal((rows, cols)) * 3 + 1
         got = sp.processing.cmvnw(v, win, True)
         assert np.max(np.abs(got - o.cmvnw_vectorised(v, win, True))) < TOL, (rows, cols, win)
+
+
+def test_int16_pcm_arena_matches_astype_float(sp):
+    """load_data.py:58-70 hands lmfe the int16 array scipy.io.wavfile returns; the batch call
+    ingests the PCM arena as int16 and must equal the reference on signal.astype(float)."""
+    rng = np.random.Generator(np.random.Philox(11))
+    lengths = [48000, 16001, 480, 320, 99999]
+    sigs = [np.clip(np.round(rng.standard_normal(n) * 3000), -32768, 32767).astype(np.int16) for n in lengths]
+    arena, starts, lens = batch.pack(sigs, dtype=np.int16)
+    assert arena.dtype == np.int16
+    fb = batch.FeatureBatch(starts, lens)
+    got16 = fb.lmfe_cmvnw(arena)
+    got32 = fb.lmfe_cmvnw(arena.astype(np.float32))
+    got64 = fb.lmfe_cmvnw(arena.astype(np.float64))
+    assert np.array_equal(got16, got32) and np.array_equal(got16, got64)  # widening is exact
+    for s, got in zip(sigs, fb.split(got16)):
+        lm = o.lmfe(s.astype(float), FS)
+        if lm.shape[0] == 1:
+            # one frame: every window is 301 copies of the row, the true result is 0.  The
+            # reference returns its float64 summation noise (~1e-13 at |lmfe| ~ 16) divided by
+            # (0 + 2^-30), i.e. O(1e-4) garbage; the device result is exactly 0.
+            assert np.max(np.abs(got)) == 0 and np.max(np.abs(o.cmvnw_vectorised(lm, 301, True))) < 1e-3
+        elif lm.shape[0]:
+            assert np.max(np.abs(got - o.cmvnw_vectorised(lm, 301, True))) < TOL
+    mf = fb.mfcc_delta(arena)
+    for s, got in zip(sigs, fb.split(mf)):
+        if not got.size:
+            continue
+        ref = o.extract_derivative_feature(o.mfcc(s.astype(float), FS))
+        assert np.max(np.abs(got - ref)) < 2e-4  # |values| ~ 20x larger than for N(0, 0.1) audio
+    fb.close()
+
+
+def test_pipelined_host_path_many_chunks(sp):
+    """Host-buffer calls overlap H2D / kernels / D2H chunk by chunk (chunks = runs of whole
+    utterances of at most 192 Ki frames).  ~80 min of audio = 3 chunks; result must equal the
+    device-pointer path bit for bit, for float32 and int16 arenas, and the oracle on samples."""
+    import torch
+    rng = np.random.Generator(np.random.Philox(12))
+    lengths = rng.integers(64000, 320000, size=400)
+    pcm = [np.clip(np.round(rng.standard_normal(int(n)) * 2000), -32768, 32767).astype(np.int16) for n in lengths]
+    arena16, starts, lens = batch.pack(pcm, dtype=np.int16)
+    arena32 = arena16.astype(np.float32)
+    fb = batch.FeatureBatch(starts, lens)
+    assert fb.total_frames > 2 * 192 * 1024
+    host32 = fb.lmfe_cmvnw(arena32)
+    host16 = fb.lmfe_cmvnw(arena16)
+    d_arena = torch.from_numpy(arena32).cuda()
+    d_out = torch.empty((fb.total_frames, 40), dtype=torch.float32, device="cuda")
+    torch.cuda.synchronize()
+    fb.lmfe_cmvnw_dev(d_arena.data_ptr(), d_arena.numel(), d_out.data_ptr())
+    fb.ctx.sync()
+    dev = d_out.cpu().numpy()
+    assert np.array_equal(host32, dev) and np.array_equal(host16, dev)
+    parts = fb.split(host16)
+    for u in (0, 97, 250, 399):
+        ref = o.cmvnw_vectorised(o.lmfe(pcm[u].astype(float), FS), 301, True)
+        assert np.max(np.abs(parts[u] - ref)) < TOL
+    # utterances not packed in order (chunk spans overlap): whole-arena copy fallback
+    perm = rng.permutation(len(lens))
+    fb2 = batch.FeatureBatch(starts[perm], lens[perm])
+    out2 = fb2.split(fb2.lmfe_cmvnw(arena16))
+    for k in (0, 11, 200):
+        assert np.array_equal(out2[k], parts[perm[k]])
+    fb.close(); fb2.close()
