@@ -99,7 +99,7 @@ def _cpu_worker(args):
     os.environ["OMP_NUM_THREADS"] = "1"
     from oracle import speechpy_oracle as o
     from speaker_verification_b200 import synth
-    x = synth.pcm16(seed, int(n))  # int16, widened by lmfe's signal.astype(float) (feature.py:182)
+    x = synth.pcm16(seed, int(n)).astype(np.float32) * np.float32(1.0 / 32768.0)  # == librosa.load of a PCM16 wav
     out = o.cmvnw(o.lmfe(x, FS), WIN, True)
     return out.shape[0]
 
@@ -149,7 +149,8 @@ def run_reference(args, rank, world):
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * t_total / args.steps,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
-        "data": "synthetic 16 kHz audio, 16-bit PCM values round(N(0,0.1)*32768), Philox-seeded",
+        "data": "synthetic 16 kHz audio, 16-bit PCM round(N(0,0.1)*32768) scaled by 1/32768 to float32 (what "
+                "librosa.load returns), Philox-seeded",
         "config": workload_config(per_step, args.gpus),
         "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
@@ -176,8 +177,8 @@ def make_device_corpus(torch, lengths, seed, device):
     gen.manual_seed(seed)
     chunk = 1 << 28
     for s in range(0, total, chunk):
-        # 16-bit PCM values (what scipy.io.wavfile hands the reference, load_data.py:58) held as float32
-        arena[s:s + chunk].normal_(0.0, 0.1 * 32768.0, generator=gen).round_().clamp_(-32768.0, 32767.0)
+        # 16-bit PCM values / 32768: the float32 audio librosa.load (utils.py:170-173) decodes from a wav
+        arena[s:s + chunk].normal_(0.0, 0.1 * 32768.0, generator=gen).round_().clamp_(-32768.0, 32767.0).mul_(1.0 / 32768.0)
     return arena, starts
 
 
@@ -257,14 +258,16 @@ def run_ours(args, rank, world, local_rank):
 
     def e2e_leg(host_dtype):
         h_in = torch.empty(e_end, dtype=host_dtype, pin_memory=True)
-        h_in.copy_(arena[:e_end])  # exact: the corpus is PCM-valued
+        pcm = host_dtype == torch.int16
+        h_in.copy_(arena[:e_end] * 32768.0 if pcm else arena[:e_end])  # exact: the corpus is PCM / 32768
+        scale = batch.PCM16_SCALE if pcm else 1.0
         a_np, o_np = h_in.numpy(), h_out.numpy()
         for _ in range(2):
-            fbe.lmfe_cmvnw(a_np, o_np)
+            fbe.lmfe_cmvnw(a_np, o_np, sample_scale=scale)
         barrier()
         t0 = time.perf_counter()
         for _ in range(e_steps):
-            fbe.lmfe_cmvnw(a_np, o_np)
+            fbe.lmfe_cmvnw(a_np, o_np, sample_scale=scale)
         torch.cuda.synchronize()
         dt = time.perf_counter() - t0
         te = torch.tensor([dt], dtype=torch.float64, device=device)
@@ -286,14 +289,14 @@ def run_ours(args, rank, world, local_rank):
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms_max / args.steps, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f32 (f64 window accumulators in cmvnw)",
-            "data": "synthetic 16 kHz audio, 16-bit PCM values round(N(0,0.1)*32768) generated on device "
-                    "(torch Philox), random lengths seeded",
+            "data": "synthetic 16 kHz audio, 16-bit PCM round(N(0,0.1)*32768) scaled by 1/32768 to float32 (what "
+                    "librosa.load returns), generated on device (torch Philox), random lengths seeded",
             "config": workload_config(U, world),
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(e_end * 2),
                     "d2h_bytes_per_step": int(fbe.total_frames * M * 4),
                     "sample": f"first {Ue} utterances of the corpus ({e_audio_h:.2f} audio-h) per step, "
-                              f"{e_steps} steps, pinned host buffers, int16 PCM arena in (the dtype wavfile.read "
-                              f"hands the reference), float32 features out, spb_lmfe_cmvnw_batch_dtype "
+                              f"{e_steps} steps, pinned host buffers, int16 PCM arena in (the wav payload; scaled by "
+                              f"1/32768 on the device like librosa.load), float32 features out, spb_lmfe_cmvnw_batch_dtype "
                               f"(H2D / kernels / D2H pipelined over chunks)",
                     "float32_arena_value": e2e_f32, "float32_arena_h2d_bytes_per_step": int(e_end * 4),
                     "matches_device_path": same},

@@ -191,15 +191,17 @@ SPB_API int spb_lmfe_cmvnw_batch(spb_context *ctx, const spb_batch *batch, const
                          int64_t arena_len, float *out);
 SPB_API int spb_mfcc_delta_batch(spb_context *ctx, const spb_batch *batch, const float *samples,
                          int64_t arena_len, float *out);
-/* Same, with the sample arena in any spb_dtype.  SPB_I16 is what
- * scipy.io.wavfile.read hands the reference (load_data.py:58-70) before
- * `signal.astype(float)` (feature.py:182): the PCM arena crosses PCIe at 2 bytes per
- * sample and is widened on the device (exact: every int16/int32<2^24 is a float32).
- * starts/lengths/arena_len are in samples. */
+/* Same, with the sample arena in any spb_dtype (wav ingest).  The device
+ * computes x = float(sample) * sample_scale before framing:
+ *   sample_scale = 1            `signal.astype(float)` (feature.py:182) of an integer array;
+ *   SPB_I16, 1.0/32768          the float32 array librosa.load (utils.py:170-173 load_wav,
+ *                               called at load_data.py:53) decodes from a PCM16 wav.
+ * The PCM arena crosses PCIe at 2 bytes per sample; widening and power-of-two scaling are
+ * exact in float32.  starts/lengths/arena_len are in samples. */
 SPB_API int spb_lmfe_cmvnw_batch_dtype(spb_context *ctx, const spb_batch *batch, const void *samples,
-                               int dtype, int64_t arena_len, float *out);
+                               int dtype, double sample_scale, int64_t arena_len, float *out);
 SPB_API int spb_mfcc_delta_batch_dtype(spb_context *ctx, const spb_batch *batch, const void *samples,
-                               int dtype, int64_t arena_len, float *out);
+                               int dtype, double sample_scale, int64_t arena_len, float *out);
 
 /* ------------------------------------------------------- a10  cosine scores
  * evaluation.py:76-77 over all (enrolment, test) pairs at once:

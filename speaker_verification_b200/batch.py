@@ -20,14 +20,15 @@ from .speechpy import feature as _feature
 from .speechpy import processing as _processing
 
 
+PCM16_SCALE = 1.0 / 32768.0  # librosa / soundfile scaling of 16-bit PCM to [-1, 1)
+
 _ARENA_DTYPES = {np.dtype(np.float32): _lib.F32, np.dtype(np.float64): _lib.F64,
                  np.dtype(np.int16): _lib.I16, np.dtype(np.int32): _lib.I32}
 
 
 def _as_arena(arena):
-    """Contiguous arena in a dtype the library ingests + its spb_dtype code.  int16 PCM
-    (what ``scipy.io.wavfile.read`` returns, load_data.py:58) stays int16: it crosses PCIe
-    at 2 bytes per sample and is widened on the device like ``signal.astype(float)``."""
+    """Contiguous arena in a dtype the library ingests + its spb_dtype code.  int16 PCM stays
+    int16: it crosses PCIe at 2 bytes per sample and is widened (and scaled) on the device."""
     arena = np.ascontiguousarray(arena)
     if arena.dtype not in _ARENA_DTYPES:
         arena = arena.astype(np.float32)
@@ -140,23 +141,32 @@ class FeatureBatch:
             pass
 
     # ---- host (numpy) entry points -------------------------------------------------
-    def lmfe_cmvnw(self, arena: np.ndarray, out: np.ndarray | None = None) -> np.ndarray:
+    def lmfe_cmvnw(self, arena: np.ndarray, out: np.ndarray | None = None,
+                   sample_scale: float = 1.0) -> np.ndarray:
         """lmfe + cmvnw of every utterance: (total_frames, num_filters) float32; rows of
-        utterance u are frame_offsets[u]:frame_offsets[u+1]."""
+        utterance u are frame_offsets[u]:frame_offsets[u+1].
+
+        ``arena`` may be float32, float64, int16 or int32; the device computes
+        ``float(sample) * sample_scale``.  ``sample_scale=1`` is ``signal.astype(float)``
+        (feature.py:182); an int16 PCM arena with ``sample_scale=PCM16_SCALE`` (1/32768) is the
+        float32 audio ``librosa.load`` returns in the reference's ``load_wav`` (utils.py:170-173)."""
         arena, code = _as_arena(arena)
         if out is None:
             out = np.empty((self.total_frames, self.num_filters), dtype=np.float32)
         _lib.check(self.ctx.lib.spb_lmfe_cmvnw_batch_dtype(self.ctx.handle, self.handle, _lib.ptr(arena), code,
-                                                           arena.shape[0], _lib.ptr(out)), self.ctx.handle)
+                                                           float(sample_scale), arena.shape[0], _lib.ptr(out)),
+                   self.ctx.handle)
         return out
 
-    def mfcc_delta(self, arena: np.ndarray, out: np.ndarray | None = None) -> np.ndarray:
+    def mfcc_delta(self, arena: np.ndarray, out: np.ndarray | None = None,
+                   sample_scale: float = 1.0) -> np.ndarray:
         """mfcc + extract_derivative_feature: (total_frames, num_cepstral, 3) float32."""
         arena, code = _as_arena(arena)
         if out is None:
             out = np.empty((self.total_frames, self.num_cepstral, 3), dtype=np.float32)
         _lib.check(self.ctx.lib.spb_mfcc_delta_batch_dtype(self.ctx.handle, self.handle, _lib.ptr(arena), code,
-                                                           arena.shape[0], _lib.ptr(out)), self.ctx.handle)
+                                                           float(sample_scale), arena.shape[0], _lib.ptr(out)),
+                   self.ctx.handle)
         return out
 
     # ---- device-pointer entry points (asynchronous on ctx.stream()) -----------------

@@ -1109,10 +1109,13 @@ int spb_mfcc_delta_batch_dev(spb_context *ctx, const spb_batch *b, const float *
 //   stream      : [convert to float32] + kernels of chunk k
 //   out_stream  : D2H of chunk k-1's feature rows
 // so a call costs about max(H2D, compute, D2H) instead of their sum (PCIe is full duplex).
-// `samples` may be float32, int16 (what scipy.io.wavfile hands load_data.py:58-70), int32 or
-// float64; non-float32 input is widened on the device exactly like signal.astype(float).
+// `samples` may be float32, int16 PCM, int32 or float64; x = float(sample) * scale on the
+// device: scale 1 is signal.astype(float) (feature.py:182), int16 with scale 1/32768 is the
+// float32 array librosa.load (utils.py:170-173 load_wav) decodes from a PCM16 file.
 static int host_batch(spb_context *ctx, const spb_batch *b, const void *samples, int dtype,
-                      int64_t arena_len, float *out, int which) {
+                      double scale_d, int64_t arena_len, float *out, int which) {
+  const float scale = (float)scale_d;
+  SPB_REQUIRE(ctx, scale_d == scale_d && scale != 0.f, "batch call: sample_scale must be a non-zero number");
   int rc = check_batch(ctx, b, arena_len, samples, out);
   if (rc) return rc;
   SPB_REQUIRE(ctx, dtype == SPB_F32 || dtype == SPB_F64 || dtype == SPB_I16 || dtype == SPB_I32,
@@ -1128,6 +1131,7 @@ static int host_batch(spb_context *ctx, const spb_batch *b, const void *samples,
   float *d_lmfe = nullptr, *d_ms = nullptr;
   if (which == 0 && (rc = lmfe_cmvnw_prepare(ctx, b, &d_lmfe, &d_ms))) return rc;
   const size_t nch = b->chunks.size();
+  const bool ingest = dtype != SPB_F32 || scale != 1.0f;  // float32 with scale 1 is used as uploaded
   // chunk spans overlap when utterances are not packed in order: then copy the arena once
   const bool piecewise = b->chunk_span_total <= arena_len + arena_len / 4;
   while (ctx->pipe_events.size() < 2 * nch + 1) {
@@ -1144,7 +1148,7 @@ static int host_batch(spb_context *ctx, const spb_batch *b, const void *samples,
     SPB_CUDA(ctx, cudaMemcpyAsync(d_raw, samples, (size_t)arena_len * esz, cudaMemcpyHostToDevice, ctx->copy_stream));
     SPB_CUDA(ctx, cudaEventRecord(ctx->pipe_events[0], ctx->copy_stream));
     SPB_CUDA(ctx, cudaStreamWaitEvent(ctx->stream, ctx->pipe_events[0], 0));
-    if (dtype != SPB_F32 && (rc = launch_convert(ctx, d_raw, dtype, d_samples, SPB_F32, arena_len))) return rc;
+    if (ingest && (rc = launch_ingest(ctx, d_raw, dtype, d_samples, arena_len, scale))) return rc;
   }
   for (size_t k = 0; k < nch; ++k) {
     const BatchChunk &c = b->chunks[k];
@@ -1155,8 +1159,7 @@ static int host_batch(spb_context *ctx, const spb_batch *b, const void *samples,
                                     (size_t)n * esz, cudaMemcpyHostToDevice, ctx->copy_stream));
       SPB_CUDA(ctx, cudaEventRecord(ev_in, ctx->copy_stream));
       SPB_CUDA(ctx, cudaStreamWaitEvent(ctx->stream, ev_in, 0));
-      if (dtype != SPB_F32 &&
-          (rc = launch_convert(ctx, d_raw + (size_t)c.s_lo * esz, dtype, d_samples + c.s_lo, SPB_F32, n)))
+      if (ingest && (rc = launch_ingest(ctx, d_raw + (size_t)c.s_lo * esz, dtype, d_samples + c.s_lo, n, scale)))
         return rc;
     }
     if (which == 0) {
@@ -1182,24 +1185,24 @@ static int host_batch(spb_context *ctx, const spb_batch *b, const void *samples,
 
 int spb_lmfe_cmvnw_batch(spb_context *ctx, const spb_batch *b, const float *samples,
                          int64_t arena_len, float *out) {
-  return host_batch(ctx, b, samples, SPB_F32, arena_len, out, 0);
+  return host_batch(ctx, b, samples, SPB_F32, 1.0, arena_len, out, 0);
 }
 
 int spb_lmfe_cmvnw_batch_dtype(spb_context *ctx, const spb_batch *b, const void *samples, int dtype,
-                               int64_t arena_len, float *out) {
-  return host_batch(ctx, b, samples, dtype, arena_len, out, 0);
+                               double sample_scale, int64_t arena_len, float *out) {
+  return host_batch(ctx, b, samples, dtype, sample_scale, arena_len, out, 0);
 }
 
 int spb_mfcc_delta_batch(spb_context *ctx, const spb_batch *b, const float *samples,
                          int64_t arena_len, float *out) {
   if (b && b->plan->p.num_cepstral < 1) return fail(ctx, SPB_ERR_INVALID, "mfcc_delta: plan has num_cepstral == 0");
-  return host_batch(ctx, b, samples, SPB_F32, arena_len, out, 1);
+  return host_batch(ctx, b, samples, SPB_F32, 1.0, arena_len, out, 1);
 }
 
 int spb_mfcc_delta_batch_dtype(spb_context *ctx, const spb_batch *b, const void *samples, int dtype,
-                               int64_t arena_len, float *out) {
+                               double sample_scale, int64_t arena_len, float *out) {
   if (b && b->plan->p.num_cepstral < 1) return fail(ctx, SPB_ERR_INVALID, "mfcc_delta: plan has num_cepstral == 0");
-  return host_batch(ctx, b, samples, dtype, arena_len, out, 1);
+  return host_batch(ctx, b, samples, dtype, sample_scale, arena_len, out, 1);
 }
 
 }  // extern "C"

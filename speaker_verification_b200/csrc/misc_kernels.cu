@@ -124,6 +124,62 @@ int launch_convert(spb_context *ctx, const void *in, int dtype_in, void *out, in
   return SPB_OK;
 }
 
+// ------------------------------------------------------------------ sample ingest
+// out[i] = float(in[i]) * scale: raw PCM / integer / float64 arenas widened on the device.
+// scale = 1 is `signal.astype(float)` (feature.py:182); scale = 1/32768 on int16 is what
+// librosa.load (utils.py:170-173) produces from a PCM16 file.  Power-of-two scales are exact.
+template <typename TI>
+__global__ void ingest_kernel(const TI *__restrict__ in, float *__restrict__ out, long long n,
+                              float scale) {
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n;
+       i += (long long)gridDim.x * blockDim.x)
+    out[i] = (float)in[i] * scale;
+}
+
+// int16: 8 samples (16 B) in, two float4 out per thread and step; both pointers 16-byte aligned
+__global__ void ingest_i16x8_kernel(const int4 *__restrict__ in, float4 *__restrict__ out,
+                                    long long n8, float scale) {
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n8;
+       i += (long long)gridDim.x * blockDim.x) {
+    const int4 v = __ldg(in + i);
+    float4 a, b;
+    a.x = (float)(short)(v.x & 0xffff) * scale;
+    a.y = (float)(v.x >> 16) * scale;
+    a.z = (float)(short)(v.y & 0xffff) * scale;
+    a.w = (float)(v.y >> 16) * scale;
+    b.x = (float)(short)(v.z & 0xffff) * scale;
+    b.y = (float)(v.z >> 16) * scale;
+    b.z = (float)(short)(v.w & 0xffff) * scale;
+    b.w = (float)(v.w >> 16) * scale;
+    out[2 * i] = a;
+    out[2 * i + 1] = b;
+  }
+}
+
+int launch_ingest(spb_context *ctx, const void *in, int dtype_in, float *out, int64_t n, float scale) {
+  if (n <= 0) return SPB_OK;
+  const long long cap = (long long)ctx->sm_count * 16;
+  if (dtype_in == SPB_I16 && (((size_t)in | (size_t)out) & 15) == 0 && n >= 8) {
+    const long long n8 = n / 8;
+    const unsigned g = (unsigned)std::min<long long>((n8 + 255) / 256, cap);
+    ingest_i16x8_kernel<<<g, 256, 0, ctx->stream>>>((const int4 *)in, (float4 *)out, n8, scale);
+    SPB_LAUNCH_CHECK(ctx, "ingest_i16x8_kernel");
+    const long long done = n8 * 8;
+    if (done == n) return SPB_OK;
+    ingest_kernel<int16_t><<<1, 32, 0, ctx->stream>>>((const int16_t *)in + done, out + done, n - done, scale);
+    SPB_LAUNCH_CHECK(ctx, "ingest_kernel");
+    return SPB_OK;
+  }
+  const unsigned g = (unsigned)std::min<long long>((n + 255) / 256, cap);
+  if (dtype_in == SPB_I16) ingest_kernel<int16_t><<<g, 256, 0, ctx->stream>>>((const int16_t *)in, out, n, scale);
+  else if (dtype_in == SPB_I32) ingest_kernel<int32_t><<<g, 256, 0, ctx->stream>>>((const int32_t *)in, out, n, scale);
+  else if (dtype_in == SPB_F64) ingest_kernel<double><<<g, 256, 0, ctx->stream>>>((const double *)in, out, n, scale);
+  else if (dtype_in == SPB_F32) ingest_kernel<float><<<g, 256, 0, ctx->stream>>>((const float *)in, out, n, scale);
+  else return fail(ctx, SPB_ERR_INVALID, "unsupported sample dtype");
+  SPB_LAUNCH_CHECK(ctx, "ingest_kernel");
+  return SPB_OK;
+}
+
 // ------------------------------------------------------------------ tile tables
 // tiles[tile_offsets[u] + t] = {u, t * tile} for t < ceil(nframes[u] / tile)
 __global__ void build_tiles_kernel(const int32_t *__restrict__ nframes,

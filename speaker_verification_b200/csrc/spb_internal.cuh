@@ -204,6 +204,7 @@ int launch_delta_cube_f64(spb_context *ctx, const double *in, int64_t rows, int 
                           double *out);
 int launch_convert(spb_context *ctx, const void *in, int dtype_in, void *out, int dtype_out,
                    int64_t n);
+int launch_ingest(spb_context *ctx, const void *in, int dtype_in, float *out, int64_t n, float scale);
 int launch_build_tiles(spb_context *ctx, const int32_t *nframes, const int64_t *tile_offsets,
                        int64_t U, int tile, int2 *tiles);
 int launch_build_fft_tiles(spb_context *ctx, const int32_t *nframes, const int64_t *tile_offsets,

@@ -20,8 +20,9 @@ def audio(seed: int, num_samples: int, dtype=np.float32, sigma: float = 0.1) -> 
 
 
 def pcm16(seed: int, num_samples: int, sigma: float = 0.1) -> np.ndarray:
-    """One utterance of 16-bit PCM noise, round(N(0, sigma) * 32768) clipped to int16: the
-    dtype ``scipy.io.wavfile.read`` hands the reference (load_data.py:58)."""
+    """One utterance of 16-bit PCM noise, round(N(0, sigma) * 32768) clipped to int16 (what a
+    VoxCeleb wav holds; ``librosa.load`` in the reference's ``load_wav``, utils.py:170-173,
+    decodes it to ``pcm / 32768`` float32)."""
     x = audio(seed, num_samples, np.float64, sigma) * 32768.0
     return np.clip(np.round(x), -32768, 32767).astype(np.int16)
 

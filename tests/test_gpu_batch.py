@@ -126,8 +126,9 @@ def test_large_tile_cmvnw_matches_small_tile_kernels(sp):
 
 
 def test_int16_pcm_arena_matches_astype_float(sp):
-    """load_data.py:58-70 hands lmfe the int16 array scipy.io.wavfile returns; the batch call
-    ingests the PCM arena as int16 and must equal the reference on signal.astype(float)."""
+    """An int16 array handed to lmfe is widened by signal.astype(float) (feature.py:182); the
+    batch call ingests the PCM arena as int16 (sample_scale 1) and must equal that.  With
+    sample_scale 1/32768 it must equal the float32 audio librosa.load returns (utils.py:170-173)."""
     rng = np.random.Generator(np.random.Philox(11))
     lengths = [48000, 16001, 480, 320, 99999]
     sigs = [np.clip(np.round(rng.standard_normal(n) * 3000), -32768, 32767).astype(np.int16) for n in lengths]
@@ -146,6 +147,14 @@ def test_int16_pcm_arena_matches_astype_float(sp):
             # (0 + 2^-30), i.e. O(1e-4) garbage; the device result is exactly 0.
             assert np.max(np.abs(got)) == 0 and np.max(np.abs(o.cmvnw_vectorised(lm, 301, True))) < 1e-3
         elif lm.shape[0]:
+            assert np.max(np.abs(got - o.cmvnw_vectorised(lm, 301, True))) < TOL
+    # librosa-style ingest: int16 * 2^-15 on the device == float32 arena scaled on the host
+    scaled = arena.astype(np.float32) * np.float32(batch.PCM16_SCALE)
+    got_l = fb.lmfe_cmvnw(arena, sample_scale=batch.PCM16_SCALE)
+    assert np.array_equal(got_l, fb.lmfe_cmvnw(scaled))
+    for s, got in zip(sigs, fb.split(got_l)):
+        lm = o.lmfe(s.astype(np.float32) * np.float32(batch.PCM16_SCALE), FS)
+        if lm.shape[0] > 1:
             assert np.max(np.abs(got - o.cmvnw_vectorised(lm, 301, True))) < TOL
     mf = fb.mfcc_delta(arena)
     for s, got in zip(sigs, fb.split(mf)):
