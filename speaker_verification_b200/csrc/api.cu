@@ -523,7 +523,16 @@ int spb_plan_destroy(spb_plan *pl) {
 
 // ------------------------------------------------------------------ batches
 static constexpr int kFftTile = 32;
-static constexpr int64_t kChunkRows = 192 * 1024;  // ~30 MB of 40-wide fp32 rows: L2-resident
+static constexpr int64_t kChunkRowsDefault = 192 * 1024;  // pipeline unit of the host-pointer calls (~30 MB of rows)
+static constexpr int64_t kGroupRowsDefault = 4 * 1024 * 1024;  // launch unit of the device-pointer calls
+// tuning knobs (read when a batch is created): SPB_CHUNK_ROWS, SPB_GROUP_ROWS, SPB_BIG_RMAX
+static int64_t env_int(const char *name, int64_t dflt) {
+  const char *v = getenv(name);
+  if (!v || !*v) return dflt;
+  char *end = nullptr;
+  const long long x = strtoll(v, &end, 10);
+  return (end && *end == 0 && x > 0) ? (int64_t)x : dflt;
+}
 
 int spb_batch_create(spb_context *ctx, const spb_plan *plan, const int64_t *starts,
                      const int64_t *lengths, int64_t U, spb_batch **out) {
@@ -540,6 +549,7 @@ int spb_batch_create(spb_context *ctx, const spb_plan *plan, const int64_t *star
   b->U = U;
   b->tile_frames = kFftTile;
   const int win = plan->p.cmvn_window;
+  const int64_t chunk_rows = env_int("SPB_CHUNK_ROWS", kChunkRowsDefault);
   b->cm_tile_rows = (win > 0) ? cmvnw_tile_rows(plan->p.num_filters, win) : 0;
   std::vector<int32_t> nframes(U);
   std::vector<int64_t> tile_off(U + 1, 0), cm_off(U + 1, 0);
@@ -567,7 +577,7 @@ int spb_batch_create(spb_context *ctx, const spb_plan *plan, const int64_t *star
     cm_off[u + 1] = cm_off[u] + (b->cm_tile_rows ? (F + b->cm_tile_rows - 1) / b->cm_tile_rows : 0);
     b->max_end = std::max(b->max_end, starts[u] + lengths[u]);
     // chunking by whole utterances
-    if (b->h_frame_offsets[u + 1] - cur.row0 > kChunkRows && u > cur.u0) {
+    if (b->h_frame_offsets[u + 1] - cur.row0 > chunk_rows && u > cur.u0) {
       cur.u1 = u;
       cur.tile1 = tile_off[u];
       cur.cm1 = cm_off[u];
@@ -607,10 +617,43 @@ int spb_batch_create(spb_context *ctx, const spb_plan *plan, const int64_t *star
   // large-tile cmvnw table: balanced tiles per utterance, longest first inside each chunk
   std::vector<int4> big;
   b->big_rmax = (win > 0) ? cmvnw_big_rmax(plan->p.num_filters, win) : 0;
+  const int tile_target = (int)std::min<int64_t>(b->big_rmax, std::max<int64_t>(30, env_int("SPB_BIG_RMAX", b->big_rmax) / 30 * 30));
   if (b->big_rmax > 0) {
     for (BatchChunk &c : ch.chunks) {
       c.big0 = (int64_t)big.size();
-      for (int64_t u = c.u0; u < c.u1; ++u) append_big_tiles(big, (int)u, nframes[u], b->big_rmax);
+      for (int64_t u = c.u0; u < c.u1; ++u) append_big_tiles(big, (int)u, nframes[u], tile_target);
+      c.big1 = (int64_t)big.size();
+      std::stable_sort(big.begin() + c.big0, big.begin() + c.big1,
+                       [](const int4 &x, const int4 &y) { return x.z > y.z; });
+    }
+  }
+  // launch groups of the device-pointer path: runs of chunks of up to group_rows rows.  A launch
+  // over ~200 Ki rows is only ~2 tiles per SM for the cmvnw kernels and pays a full tail per
+  // kernel; measured, large groups win although their intermediates no longer fit L2.
+  {
+    const int64_t group_rows = env_int("SPB_GROUP_ROWS", kGroupRowsDefault);
+    BatchChunk g;
+    bool open = false;
+    for (const BatchChunk &c : ch.chunks) {
+      if (open && c.row1 - g.row0 > group_rows) {
+        b->groups.push_back(g);
+        open = false;
+      }
+      if (!open) {
+        g = c;
+        open = true;
+      } else {
+        g.u1 = c.u1; g.tile1 = c.tile1; g.cm1 = c.cm1; g.row1 = c.row1;
+        g.s_lo = std::min(g.s_lo, c.s_lo);
+        g.s_hi = std::max(g.s_hi, c.s_hi);
+      }
+    }
+    if (open) b->groups.push_back(g);
+    for (BatchChunk &c : b->groups) {
+      b->max_group_rows = std::max(b->max_group_rows, c.row1 - c.row0);
+      if (b->big_rmax <= 0) continue;
+      c.big0 = (int64_t)big.size();  // group tables follow the chunk tables in d_big_tiles
+      for (int64_t u = c.u0; u < c.u1; ++u) append_big_tiles(big, (int)u, nframes[u], tile_target);
       c.big1 = (int64_t)big.size();
       std::stable_sort(big.begin() + c.big0, big.begin() + c.big1,
                        [](const int4 &x, const int4 &y) { return x.z > y.z; });
@@ -781,13 +824,13 @@ static int lmfe_cmvnw_chunk(spb_context *ctx, const spb_batch *b, const BatchChu
                           pl->p.cmvn_variance);
 }
 
-static int lmfe_cmvnw_prepare(spb_context *ctx, const spb_batch *b, float **d_lmfe, float **d_ms) {
+static int lmfe_cmvnw_prepare(spb_context *ctx, const spb_batch *b, int64_t max_rows, float **d_lmfe, float **d_ms) {
   const spb_plan *pl = b->plan;
   const int M = pl->p.num_filters, win = pl->p.cmvn_window;
   SPB_REQUIRE(ctx, win > 0 && (win & 1), "lmfe_cmvnw: plan has no (odd) cmvn_window");
   SPB_REQUIRE(ctx, M >= 1, "lmfe_cmvnw: plan has no filterbank");
   if (!cmvnw_supported(M, win)) return fail(ctx, SPB_ERR_UNSUPPORTED, "cmvnw: window x columns too large for shared memory");
-  const size_t chunk_bytes = (size_t)std::max<int64_t>(b->max_chunk_rows, 1) * M * 4;
+  const size_t chunk_bytes = (size_t)std::max<int64_t>(max_rows, 1) * M * 4;
   *d_lmfe = (float *)scratch(ctx, 2, chunk_bytes);
   *d_ms = pl->p.cmvn_variance ? (float *)scratch(ctx, 3, chunk_bytes) : nullptr;
   if (!*d_lmfe || (pl->p.cmvn_variance && !*d_ms)) return SPB_ERR_CUDA;
@@ -797,9 +840,9 @@ static int lmfe_cmvnw_prepare(spb_context *ctx, const spb_batch *b, float **d_lm
 static int run_lmfe_cmvnw(spb_context *ctx, const spb_batch *b, const float *d_samples,
                           int64_t arena_len, float *d_out) {
   float *d_lmfe, *d_ms;
-  int rc = lmfe_cmvnw_prepare(ctx, b, &d_lmfe, &d_ms);
+  int rc = lmfe_cmvnw_prepare(ctx, b, b->max_group_rows, &d_lmfe, &d_ms);
   if (rc) return rc;
-  for (const BatchChunk &c : b->chunks) {
+  for (const BatchChunk &c : b->groups) {
     rc = lmfe_cmvnw_chunk(ctx, b, c, d_samples, arena_len, d_lmfe, d_ms, d_out);
     if (rc) return rc;
   }
@@ -1129,7 +1172,7 @@ static int host_batch(spb_context *ctx, const spb_batch *b, const void *samples,
   char *d_raw = (dtype == SPB_F32) ? (char *)d_samples : (char *)scratch(ctx, 5, (size_t)arena_len * esz);
   if (!d_samples || !d_out || !d_raw) return SPB_ERR_CUDA;
   float *d_lmfe = nullptr, *d_ms = nullptr;
-  if (which == 0 && (rc = lmfe_cmvnw_prepare(ctx, b, &d_lmfe, &d_ms))) return rc;
+  if (which == 0 && (rc = lmfe_cmvnw_prepare(ctx, b, b->max_chunk_rows, &d_lmfe, &d_ms))) return rc;
   const size_t nch = b->chunks.size();
   const bool ingest = dtype != SPB_F32 || scale != 1.0f;  // float32 with scale 1 is used as uploaded
   // chunk spans overlap when utterances are not packed in order: then copy the arena once

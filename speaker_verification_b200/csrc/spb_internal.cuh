@@ -119,7 +119,9 @@ struct spb_batch {
   int2 *d_cm_tiles = nullptr;            // [total_cm_tiles] {utt, first row}
   int4 *d_big_tiles = nullptr;           // large-tile cmvnw: {utt, first row, rows, 0}, longest first per chunk
   int big_rmax = 0;                      // 0: large-tile path not usable for this plan
-  std::vector<spb::BatchChunk> chunks;
+  std::vector<spb::BatchChunk> chunks;   // pipeline units of the host-pointer calls
+  std::vector<spb::BatchChunk> groups;   // launch units of the device-pointer calls (runs of chunks)
+  int64_t max_group_rows = 0;
   int64_t max_chunk_rows = 0;
   int64_t chunk_span_total = 0;  // sum of the chunks' sample spans (== arena use when utterances are packed in order)
 };
