@@ -101,10 +101,19 @@ SPB_API int spb_stack_frames(spb_context *ctx, const double *sig, int64_t num_sa
  * sfe/speechpy/processing.py:142-159, 162-174.  frames is (F, L) row-major
  * float64; rows are zero-padded (L < nfft) or truncated (L > nfft) to nfft as
  * numpy's rfft(n=) does.  out is (F, nfft/2+1) float64.
- * mode 0: |X|^2/nfft   mode 1: |X|.   nfft must be a power of two in [32, 4096]
- * (SPB_ERR_UNSUPPORTED otherwise). */
+ * mode 0: |X|^2/nfft   mode 1: |X|
+ * mode 2: log_power_spectrum(normalize=False) = 10 log10(max(P, 1e-20)) (processing.py:177-198)
+ * mode 3: the same minus its global maximum (normalize=True).
+ * nfft must be a power of two in [32, 4096] (SPB_ERR_UNSUPPORTED otherwise). */
 SPB_API int spb_power_spectrum(spb_context *ctx, const double *frames, int64_t num_frames,
                        int32_t frame_len, int32_t nfft, int32_t mode, double *out);
+
+/* ------------------------------------------------- 8f-2  preemphasis
+ * sfe/speechpy/processing.py:45-58: out[i] = sig[i] - cof * sig[(i - shift) mod n]
+ * (np.roll is circular: sample 0 uses the last sample).  Computed in the dtype numpy
+ * uses: float32 in -> float32 out; float64 / int16 / int32 in -> float64 out. */
+SPB_API int spb_preemphasis(spb_context *ctx, const void *sig, int32_t dtype, int64_t n, int64_t shift,
+                    double cof, void *out);
 
 /* -------------------------------------------------------------- feature plan
  * Everything mfe / lmfe / mfcc need that does not depend on the signal.  The
@@ -229,6 +238,16 @@ SPB_API int spb_eer(spb_context *ctx, const float *scores, const int32_t *labels
             double *eer, double *auc);
 SPB_API int spb_eer_dev(spb_context *ctx, const float *d_scores, const int32_t *d_labels,
                 int64_t n, double *eer, double *auc);
+
+/* ROC curve export: sklearn.metrics.roc_curve(label, score, pos_label=1) as
+ * called at evaluation.py:48 (drop_intermediate=True; first point (0, 0, +inf)).
+ * fpr / tpr / thresholds: caller-allocated HOST arrays of `capacity` doubles (n + 1 always
+ * suffices; thresholds may be NULL); *count receives the number of points (also when the
+ * capacity is too small, which returns SPB_ERR_INVALID).  _dev: scores/labels on the device. */
+SPB_API int spb_roc_curve(spb_context *ctx, const float *scores, const int32_t *labels, int64_t n,
+                  double *fpr, double *tpr, double *thresholds, int64_t capacity, int64_t *count);
+SPB_API int spb_roc_curve_dev(spb_context *ctx, const float *d_scores, const int32_t *d_labels, int64_t n,
+                      double *fpr, double *tpr, double *thresholds, int64_t capacity, int64_t *count);
 
 #ifdef __cplusplus
 }

@@ -303,6 +303,18 @@ def main():
         assert abs(e3 - eer) < 1e-9 and abs(a3 - auc) < 1e-12, (name, e3, eer, a3, auc)
         sc[f"eer_{name}"] = np.float64(eer)
         sc[f"auc_{name}"] = np.float64(auc)
+        # ROC curve as the reference's get_eer_auc returns it, on the float32 scores the scorer emits
+        from sklearn.metrics import roc_curve as sk_roc_curve
+        s32 = np.asarray(s, dtype=np.float32)
+        _, _, fpr32, tpr32 = rev.get_eer_auc(lab, s32)
+        _, _, thr32 = sk_roc_curve(lab, s32, pos_label=1)
+        f3, t3, th3 = so.roc_curve_restated(lab, s32)
+        assert np.array_equal(f3, fpr32) and np.array_equal(t3, tpr32), name
+        assert np.array_equal(th3[1:], thr32[1:].astype(np.float64)) and np.isinf(thr32[0]), name
+        f4, t4, _ = so.roc_curve_restated(lab, s)
+        assert np.array_equal(f4, fpr) and np.array_equal(t4, tpr), name
+        sc[f"fpr_{name}"] = fpr32
+        sc[f"tpr_{name}"] = tpr32
         if name in ("ties", "tiny", "perfect"):
             sc[f"label_{name}"] = lab
             sc[f"score_{name}"] = s

@@ -105,6 +105,29 @@ def roc_points_restated(label, score):
     return fps, tps, int(fps[-1]), int(tps[-1])
 
 
+def roc_curve_restated(label, score):
+    """``sklearn.metrics.roc_curve(label, score, pos_label=1)`` (evaluation.py:48) restated:
+    vertices of ``_binary_clf_curve``; with more than two of them, ``drop_intermediate`` keeps
+    the first, the last and every vertex where the second difference of fps or of tps is
+    non-zero; then ``(0, 0, inf)`` is prepended.  Returns (fpr, tpr, thresholds) float64."""
+    label = np.asarray(label)
+    score = np.asarray(score)
+    order = np.argsort(score, kind='mergesort')[::-1]
+    s = score[order]
+    y = (label[order] == 1).astype(np.int64)
+    last_of_run = np.r_[np.nonzero(np.diff(s))[0], y.size - 1]
+    tps = np.cumsum(y)[last_of_run]
+    fps = 1 + last_of_run - tps
+    thr = s[last_of_run].astype(np.float64)
+    if fps.size > 2:
+        keep = np.r_[True, np.logical_or(np.diff(fps, 2), np.diff(tps, 2)), True]
+        fps, tps, thr = fps[keep], tps[keep], thr[keep]
+    tps = np.r_[0, tps]
+    fps = np.r_[0, fps]
+    thr = np.r_[np.inf, thr]
+    return fps / float(fps[-1]), tps / float(tps[-1]), thr
+
+
 def eer_auc_restated(label, score):
     """EER = root of 1 - x - tpr(x) on the piecewise-linear ROC; AUC = trapezoid.
 

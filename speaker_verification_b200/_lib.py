@@ -53,6 +53,7 @@ PROTOTYPES = {
     "spb_derivative": (C.c_int, [c_vp, c_vp, c_i64, c_i32, c_i32, c_vp]),
     "spb_cmvn": (C.c_int, [c_vp, c_vp, c_i64, c_i32, c_i32, c_vp]),
     "spb_cmvnw": (C.c_int, [c_vp, c_vp, c_i64, c_i32, c_i32, c_i32, c_vp]),
+    "spb_preemphasis": (C.c_int, [c_vp, c_vp, c_i32, c_i64, c_i64, C.c_double, c_vp]),
     "spb_batch_create": (C.c_int, [c_vp, c_vp, c_vp, c_vp, c_i64, C.POINTER(c_vp)]),
     "spb_batch_destroy": (C.c_int, [c_vp]),
     "spb_batch_total_frames": (C.c_int, [c_vp, C.POINTER(c_i64)]),
@@ -70,6 +71,8 @@ PROTOTYPES = {
     "spb_argmax_rows_dev": (C.c_int, [c_vp, c_vp, c_i64, c_i64, c_vp]),
     "spb_eer": (C.c_int, [c_vp, c_vp, c_vp, c_i64, C.POINTER(C.c_double), C.POINTER(C.c_double)]),
     "spb_eer_dev": (C.c_int, [c_vp, c_vp, c_vp, c_i64, C.POINTER(C.c_double), C.POINTER(C.c_double)]),
+    "spb_roc_curve": (C.c_int, [c_vp, c_vp, c_vp, c_i64, c_vp, c_vp, c_vp, c_i64, C.POINTER(c_i64)]),
+    "spb_roc_curve_dev": (C.c_int, [c_vp, c_vp, c_vp, c_i64, c_vp, c_vp, c_vp, c_i64, C.POINTER(c_i64)]),
 }
 
 _lib = None

@@ -933,7 +933,7 @@ int spb_power_spectrum(spb_context *ctx, const double *frames, int64_t F, int32_
                        int32_t mode, double *out) {
   SPB_REQUIRE(ctx, ctx != nullptr, "spb_power_spectrum: NULL context");
   SPB_REQUIRE(ctx, F >= 0 && L >= 1, "spb_power_spectrum: bad shape");
-  SPB_REQUIRE(ctx, mode == 0 || mode == 1, "spb_power_spectrum: mode must be 0 or 1");
+  SPB_REQUIRE(ctx, mode >= 0 && mode <= 3, "spb_power_spectrum: mode must be 0..3");
   if (!(is_pow2(nfft) && nfft >= 32 && nfft <= 4096))
     return fail(ctx, SPB_ERR_UNSUPPORTED, "fft_points must be a power of two in [32, 4096]");
   if (F == 0) return SPB_OK;
@@ -963,10 +963,22 @@ int spb_power_spectrum(spb_context *ctx, const double *frames, int64_t F, int32_
   if (!rc && !d_out) rc = SPB_ERR_CUDA;
   if (!rc) {
     FeatArgs a;
-    fill_feat_args(a, b, d_sig, n, mode == 0 ? FEAT_POWER : FEAT_MAG, d_out, nullptr);
+    fill_feat_args(a, b, d_sig, n, mode == 1 ? FEAT_MAG : FEAT_POWER, d_out, nullptr);
     rc = run_features(ctx, a);
   }
-  if (!rc) rc = download_as_f64(ctx, d_out, (size_t)F * K, out);
+  if (!rc && mode >= 2) {  // log power spectrum: float64 epilogue on the device
+    double *d_log = (double *)scratch(ctx, 4, (size_t)F * K * 8 + 256);
+    if (!d_log) rc = SPB_ERR_CUDA;
+    unsigned int *d_max = d_log ? (unsigned int *)((char *)d_log + (size_t)F * K * 8) : nullptr;
+    if (!rc) rc = launch_log_power(ctx, d_out, (long long)F * K, mode == 3, d_max, d_log);
+    if (!rc) {
+      cudaError_t e = cudaMemcpyAsync(out, d_log, (size_t)F * K * 8, cudaMemcpyDeviceToHost, ctx->stream);
+      if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+      if (e != cudaSuccess) rc = cuda_fail(ctx, e, "log power D2H");
+    }
+  } else if (!rc) {
+    rc = download_as_f64(ctx, d_out, (size_t)F * K, out);
+  }
   cudaStreamSynchronize(ctx->stream);
   spb_batch_destroy(b);
   spb_plan_destroy(pl);
@@ -1246,6 +1258,28 @@ int spb_mfcc_delta_batch_dtype(spb_context *ctx, const spb_batch *b, const void 
                                double sample_scale, int64_t arena_len, float *out) {
   if (b && b->plan->p.num_cepstral < 1) return fail(ctx, SPB_ERR_INVALID, "mfcc_delta: plan has num_cepstral == 0");
   return host_batch(ctx, b, samples, dtype, sample_scale, arena_len, out, 1);
+}
+
+int spb_preemphasis(spb_context *ctx, const void *sig, int32_t dtype, int64_t n, int64_t shift, double cof,
+                    void *out) {
+  SPB_REQUIRE(ctx, ctx != nullptr, "spb_preemphasis: NULL context");
+  SPB_REQUIRE(ctx, n >= 0, "spb_preemphasis: negative length");
+  SPB_REQUIRE(ctx, dtype == SPB_F32 || dtype == SPB_F64 || dtype == SPB_I16 || dtype == SPB_I32,
+              "spb_preemphasis: unsupported dtype");
+  if (n == 0) return SPB_OK;
+  SPB_REQUIRE(ctx, sig && out, "spb_preemphasis: NULL buffer");
+  SPB_CUDA(ctx, cudaSetDevice(ctx->device));
+  const size_t esz_in = (dtype == SPB_F64) ? 8 : (dtype == SPB_I16 ? 2 : 4);
+  const size_t esz_out = (dtype == SPB_F32) ? 4 : 8;
+  void *d_in = scratch(ctx, 0, (size_t)n * esz_in);
+  void *d_out = scratch(ctx, 1, (size_t)n * esz_out);
+  if (!d_in || !d_out) return SPB_ERR_CUDA;
+  SPB_CUDA(ctx, cudaMemcpyAsync(d_in, sig, (size_t)n * esz_in, cudaMemcpyHostToDevice, ctx->stream));
+  int rc = launch_preemphasis(ctx, d_in, dtype, n, shift, cof, d_out);
+  if (rc) return rc;
+  SPB_CUDA(ctx, cudaMemcpyAsync(out, d_out, (size_t)n * esz_out, cudaMemcpyDeviceToHost, ctx->stream));
+  SPB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  return SPB_OK;
 }
 
 }  // extern "C"

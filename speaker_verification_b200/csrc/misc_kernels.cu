@@ -180,6 +180,80 @@ int launch_ingest(spb_context *ctx, const void *in, int dtype_in, float *out, in
   return SPB_OK;
 }
 
+// ------------------------------------------------------------------ preemphasis (8f-2)
+// processing.py:45-58: signal - cof * np.roll(signal, shift): rolled[i] = signal[(i - shift) mod n]
+// (circular: sample 0 uses the last sample).  Two separately rounded operations like numpy
+// (no FMA contraction), in the dtype numpy computes in: float32 for a float32 signal, float64
+// for float64 and integer signals.
+template <typename TI, typename TO>
+__global__ void preemphasis_kernel(const TI *__restrict__ x, long long n, long long shift, TO cof,
+                                   TO *__restrict__ out) {
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n;
+       i += (long long)gridDim.x * blockDim.x) {
+    long long j = i - shift;
+    if (j < 0) j += n;
+    const TO a = (TO)x[i], b = (TO)x[j];
+    if (sizeof(TO) == 4) out[i] = (TO)__fsub_rn((float)a, __fmul_rn((float)cof, (float)b));
+    else out[i] = (TO)__dsub_rn((double)a, __dmul_rn((double)cof, (double)b));
+  }
+}
+
+int launch_preemphasis(spb_context *ctx, const void *in, int dtype, long long n, long long shift, double cof,
+                       void *out) {
+  if (n <= 0) return SPB_OK;
+  shift %= n;
+  if (shift < 0) shift += n;
+  const unsigned g = (unsigned)std::min<long long>((n + 255) / 256, (long long)ctx->sm_count * 16);
+  if (dtype == SPB_F32) preemphasis_kernel<float, float><<<g, 256, 0, ctx->stream>>>((const float *)in, n, shift, (float)cof, (float *)out);
+  else if (dtype == SPB_F64) preemphasis_kernel<double, double><<<g, 256, 0, ctx->stream>>>((const double *)in, n, shift, cof, (double *)out);
+  else if (dtype == SPB_I16) preemphasis_kernel<int16_t, double><<<g, 256, 0, ctx->stream>>>((const int16_t *)in, n, shift, cof, (double *)out);
+  else if (dtype == SPB_I32) preemphasis_kernel<int32_t, double><<<g, 256, 0, ctx->stream>>>((const int32_t *)in, n, shift, cof, (double *)out);
+  else return fail(ctx, SPB_ERR_INVALID, "preemphasis: unsupported dtype");
+  SPB_LAUNCH_CHECK(ctx, "preemphasis_kernel");
+  return SPB_OK;
+}
+
+// ------------------------------------------------------------------ log power spectrum (8f-2)
+// processing.py:177-198: 10 * log10(max(P, 1e-20)), minus the global maximum when normalised.
+// log10 is monotonic, so the maximum of the logs is the log of the maximum power.
+__global__ void max_f32_kernel(const float *__restrict__ p, long long n, unsigned int *__restrict__ out_bits) {
+  float m = 0.f;  // powers are >= 0
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n;
+       i += (long long)gridDim.x * blockDim.x)
+    m = fmaxf(m, p[i]);
+  for (int o = 16; o; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
+  if ((threadIdx.x & 31) == 0) atomicMax(out_bits, __float_as_uint(m));  // non-negative floats order like uints
+}
+
+__global__ void log_power_kernel(const float *__restrict__ p, long long n, const unsigned int *__restrict__ max_bits,
+                                 double *__restrict__ out) {
+  double sub = 0.0;
+  if (max_bits) {
+    const double pm = (double)__uint_as_float(*max_bits);
+    sub = __dmul_rn(10.0, log10(pm <= 1e-20 ? 1e-20 : pm));
+  }
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n;
+       i += (long long)gridDim.x * blockDim.x) {
+    const double v = (double)p[i];
+    out[i] = __dsub_rn(__dmul_rn(10.0, log10(v <= 1e-20 ? 1e-20 : v)), sub);  // no FMA: the maximum maps to exactly 0
+  }
+}
+
+int launch_log_power(spb_context *ctx, const float *p, long long n, int normalize, unsigned int *d_max_bits,
+                     double *out) {
+  if (n <= 0) return SPB_OK;
+  const unsigned g = (unsigned)std::min<long long>((n + 255) / 256, (long long)ctx->sm_count * 16);
+  if (normalize) {
+    cudaError_t e = cudaMemsetAsync(d_max_bits, 0, 4, ctx->stream);
+    if (e != cudaSuccess) return cuda_fail(ctx, e, "cudaMemsetAsync(log power max)");
+    max_f32_kernel<<<g, 256, 0, ctx->stream>>>(p, n, d_max_bits);
+    SPB_LAUNCH_CHECK(ctx, "max_f32_kernel");
+  }
+  log_power_kernel<<<g, 256, 0, ctx->stream>>>(p, n, normalize ? d_max_bits : nullptr, out);
+  SPB_LAUNCH_CHECK(ctx, "log_power_kernel");
+  return SPB_OK;
+}
+
 // ------------------------------------------------------------------ tile tables
 // tiles[tile_offsets[u] + t] = {u, t * tile} for t < ceil(nframes[u] / tile)
 __global__ void build_tiles_kernel(const int32_t *__restrict__ nframes,

@@ -551,6 +551,114 @@ int run_eer(spb_context *ctx, const float *d_scores, const int32_t *d_labels, in
   return SPB_OK;
 }
 
+// ------------------------------------------------------------------ ROC curve export
+// sklearn.metrics.roc_curve(label, score, pos_label=1) as evaluation.py:48 calls it
+// (drop_intermediate=True): vertices at the last element of every run of equal scores in
+// descending order; a vertex is dropped when the second differences of BOTH count sequences
+// are zero (collinear), first and last are kept; then (fpr, tpr, threshold) = (0, 0, +inf) is
+// prepended.  Counts are integers, so the kept set is exact; fpr = fp / N, tpr = tp / P in
+// float64 like sklearn's float division.
+__global__ void roc_end_flags_kernel(const float *__restrict__ s, long long n, unsigned char *__restrict__ flags) {
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) flags[i] = (i == n - 1) || (s[i] != s[i + 1]);
+}
+
+__global__ void roc_keep_kernel(const int32_t *__restrict__ vidx, const int32_t *__restrict__ tp, int V,
+                                unsigned char *__restrict__ keep) {
+  const int v = blockIdx.x * blockDim.x + threadIdx.x;
+  if (v >= V) return;
+  if (v == 0 || v == V - 1) {
+    keep[v] = 1;
+    return;
+  }
+  const long long i0 = vidx[v - 1], i1 = vidx[v], i2 = vidx[v + 1];
+  const long long t0 = tp[i0], t1 = tp[i1], t2 = tp[i2];
+  const long long f0 = i0 + 1 - t0, f1 = i1 + 1 - t1, f2 = i2 + 1 - t2;
+  keep[v] = ((f2 - 2 * f1 + f0) != 0) || ((t2 - 2 * t1 + t0) != 0);
+}
+
+__global__ void roc_emit_kernel(const int32_t *__restrict__ kidx, const float *__restrict__ s,
+                                const int32_t *__restrict__ tp, int Kc, double P, double N,
+                                double *__restrict__ fpr, double *__restrict__ tpr, double *__restrict__ thr) {
+  const int k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k > Kc) return;
+  if (k == 0) {
+    fpr[0] = 0.0;
+    tpr[0] = 0.0;
+    thr[0] = __longlong_as_double(0x7ff0000000000000ll);  // +inf (sklearn >= 1.3)
+    return;
+  }
+  const long long i = kidx[k - 1];
+  const long long t = tp[i], f = i + 1 - t;
+  fpr[k] = (double)f / N;
+  tpr[k] = (double)t / P;
+  thr[k] = (double)s[i];
+}
+
+int run_roc_curve(spb_context *ctx, const float *d_scores, const int32_t *d_labels, int64_t n,
+                  double *h_fpr, double *h_tpr, double *h_thr, int64_t capacity, int64_t *count) {
+  if (n <= 0) return fail(ctx, SPB_ERR_INVALID, "roc_curve: no trials");
+  if (n >= ((int64_t)1 << 31) - 1) return fail(ctx, SPB_ERR_INVALID, "roc_curve: too many trials");
+  const int in = (int)n;
+  size_t sort_bytes = 0, sum_bytes = 0, sel_bytes = 0;
+  cub::DeviceRadixSort::SortPairsDescending(nullptr, sort_bytes, (const float *)nullptr, (float *)nullptr,
+                                            (const int32_t *)nullptr, (int32_t *)nullptr, in, 0, 32, ctx->stream);
+  cub::DeviceScan::InclusiveSum(nullptr, sum_bytes, (const int32_t *)nullptr, (int32_t *)nullptr, in, ctx->stream);
+  cub::DeviceSelect::Flagged(nullptr, sel_bytes, cub::CountingInputIterator<int32_t>(0), (const unsigned char *)nullptr,
+                             (int32_t *)nullptr, (int32_t *)nullptr, in, ctx->stream);
+  const size_t tmp_bytes = std::max(sort_bytes, std::max(sum_bytes, sel_bytes));
+  auto al = [](size_t x) { return (x + 255) & ~(size_t)255; };
+  const size_t n4 = al((size_t)n * 4), n8 = al(((size_t)n + 1) * 8);
+  const size_t off_s = 0, off_l = off_s + n4, off_tp = off_l + n4, off_vidx = off_tp + n4, off_kidx = off_vidx + n4,
+               off_flags = off_kidx + n4, off_cnt = off_flags + al((size_t)n), off_fpr = off_cnt + 256,
+               off_tpr = off_fpr + n8, off_thr = off_tpr + n8, off_tmp = off_thr + n8;
+  unsigned char *buf = (unsigned char *)scratch(ctx, 7, off_tmp + al(tmp_bytes));
+  if (!buf) return SPB_ERR_CUDA;
+  float *s = (float *)(buf + off_s);
+  int32_t *lab = (int32_t *)(buf + off_l), *tp = (int32_t *)(buf + off_tp);
+  int32_t *vidx = (int32_t *)(buf + off_vidx), *kidx = (int32_t *)(buf + off_kidx);
+  unsigned char *flags = buf + off_flags;
+  int32_t *d_cnt = (int32_t *)(buf + off_cnt);
+  double *fpr = (double *)(buf + off_fpr), *tpr = (double *)(buf + off_tpr), *thr = (double *)(buf + off_thr);
+  void *tmp = buf + off_tmp;
+  size_t tb = tmp_bytes;
+  SPB_CUDA(ctx, cub::DeviceRadixSort::SortPairsDescending(tmp, tb, d_scores, s, d_labels, lab, in, 0, 32, ctx->stream));
+  tb = tmp_bytes;
+  SPB_CUDA(ctx, cub::DeviceScan::InclusiveSum(tmp, tb, lab, tp, in, ctx->stream));
+  ctx->launches += 2;
+  const unsigned blocks = (unsigned)((n + 255) / 256);
+  roc_end_flags_kernel<<<blocks, 256, 0, ctx->stream>>>(s, n, flags);
+  SPB_LAUNCH_CHECK(ctx, "roc_end_flags_kernel");
+  tb = tmp_bytes;
+  SPB_CUDA(ctx, cub::DeviceSelect::Flagged(tmp, tb, cub::CountingInputIterator<int32_t>(0), flags, vidx, d_cnt, in, ctx->stream));
+  ctx->launches += 1;
+  int32_t h[2] = {0, 0};  // V, P
+  SPB_CUDA(ctx, cudaMemcpyAsync(&h[0], d_cnt, 4, cudaMemcpyDeviceToHost, ctx->stream));
+  SPB_CUDA(ctx, cudaMemcpyAsync(&h[1], tp + (n - 1), 4, cudaMemcpyDeviceToHost, ctx->stream));
+  SPB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  const int V = h[0];
+  const long long P = h[1], N = n - P;
+  if (P == 0 || N == 0) return fail(ctx, SPB_ERR_INVALID, "Only one class present in y_true. ROC AUC score is not defined in that case.");
+  roc_keep_kernel<<<(unsigned)((V + 255) / 256), 256, 0, ctx->stream>>>(vidx, tp, V, flags);
+  SPB_LAUNCH_CHECK(ctx, "roc_keep_kernel");
+  tb = tmp_bytes;
+  SPB_CUDA(ctx, cub::DeviceSelect::Flagged(tmp, tb, vidx, flags, kidx, d_cnt, V, ctx->stream));
+  ctx->launches += 1;
+  int32_t Kc = 0;
+  SPB_CUDA(ctx, cudaMemcpyAsync(&Kc, d_cnt, 4, cudaMemcpyDeviceToHost, ctx->stream));
+  SPB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  if (count) *count = (int64_t)Kc + 1;
+  if ((int64_t)Kc + 1 > capacity) return fail(ctx, SPB_ERR_INVALID, "roc_curve: output capacity too small (n + 1 always suffices)");
+  roc_emit_kernel<<<(unsigned)((Kc + 1 + 255) / 256), 256, 0, ctx->stream>>>(kidx, s, tp, Kc, (double)P, (double)N, fpr, tpr, thr);
+  SPB_LAUNCH_CHECK(ctx, "roc_emit_kernel");
+  const size_t ob = ((size_t)Kc + 1) * 8;
+  if (h_fpr) SPB_CUDA(ctx, cudaMemcpyAsync(h_fpr, fpr, ob, cudaMemcpyDeviceToHost, ctx->stream));
+  if (h_tpr) SPB_CUDA(ctx, cudaMemcpyAsync(h_tpr, tpr, ob, cudaMemcpyDeviceToHost, ctx->stream));
+  if (h_thr) SPB_CUDA(ctx, cudaMemcpyAsync(h_thr, thr, ob, cudaMemcpyDeviceToHost, ctx->stream));
+  SPB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  return SPB_OK;
+}
+
 }  // namespace spb
 
 using namespace spb;
@@ -634,6 +742,29 @@ int spb_eer(spb_context *ctx, const float *s, const int32_t *l, int64_t n, doubl
   SPB_CUDA(ctx, cudaMemcpyAsync(d_s, s, (size_t)n * 4, cudaMemcpyHostToDevice, ctx->stream));
   SPB_CUDA(ctx, cudaMemcpyAsync(d_l, l, (size_t)n * 4, cudaMemcpyHostToDevice, ctx->stream));
   return run_eer(ctx, d_s, d_l, n, eer, auc);
+}
+
+int spb_roc_curve_dev(spb_context *ctx, const float *s, const int32_t *l, int64_t n, double *fpr, double *tpr,
+                      double *thresholds, int64_t capacity, int64_t *count) {
+  SPB_REQ(ctx, ctx != nullptr, "roc_curve: NULL context");
+  SPB_REQ(ctx, n > 0 && s && l, "roc_curve: no trials or NULL buffer");
+  SPB_REQ(ctx, capacity >= 0 && count, "roc_curve: bad capacity or NULL count");
+  SPB_CUDA(ctx, cudaSetDevice(ctx->device));
+  return run_roc_curve(ctx, s, l, n, fpr, tpr, thresholds, capacity, count);
+}
+
+int spb_roc_curve(spb_context *ctx, const float *s, const int32_t *l, int64_t n, double *fpr, double *tpr,
+                  double *thresholds, int64_t capacity, int64_t *count) {
+  SPB_REQ(ctx, ctx != nullptr, "roc_curve: NULL context");
+  SPB_REQ(ctx, n > 0 && s && l, "roc_curve: no trials or NULL buffer");
+  SPB_REQ(ctx, capacity >= 0 && count, "roc_curve: bad capacity or NULL count");
+  SPB_CUDA(ctx, cudaSetDevice(ctx->device));
+  float *d_s = (float *)scratch(ctx, 0, (size_t)n * 4);
+  int32_t *d_l = (int32_t *)scratch(ctx, 1, (size_t)n * 4);
+  if (!d_s || !d_l) return SPB_ERR_CUDA;
+  SPB_CUDA(ctx, cudaMemcpyAsync(d_s, s, (size_t)n * 4, cudaMemcpyHostToDevice, ctx->stream));
+  SPB_CUDA(ctx, cudaMemcpyAsync(d_l, l, (size_t)n * 4, cudaMemcpyHostToDevice, ctx->stream));
+  return run_roc_curve(ctx, d_s, d_l, n, fpr, tpr, thresholds, capacity, count);
 }
 
 }  // extern "C"

@@ -206,6 +206,10 @@ int launch_delta_cube_f64(spb_context *ctx, const double *in, int64_t rows, int 
                           double *out);
 int launch_convert(spb_context *ctx, const void *in, int dtype_in, void *out, int dtype_out,
                    int64_t n);
+int launch_preemphasis(spb_context *ctx, const void *in, int dtype, long long n, long long shift, double cof,
+                       void *out);
+int launch_log_power(spb_context *ctx, const float *p, long long n, int normalize, unsigned int *d_max_bits,
+                     double *out);
 int launch_ingest(spb_context *ctx, const void *in, int dtype_in, float *out, int64_t n, float scale);
 int launch_build_tiles(spb_context *ctx, const int32_t *nframes, const int64_t *tile_offsets,
                        int64_t U, int tile, int2 *tiles);

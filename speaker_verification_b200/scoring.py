@@ -55,10 +55,7 @@ def cosine_similarity(X, Y=None):
     return cosine_scores(X, Y)
 
 
-def get_eer_auc(label, distance, device=None):
-    """evaluation.py:47-52.  Returns ``(eer, auc, fpr, tpr)`` like the reference; the
-    curve itself is only used for plotting there (out of scope), so ``fpr`` and ``tpr``
-    are returned as ``None``."""
+def _labels_scores(label, distance):
     label = np.asarray(label)
     distance = np.asarray(distance)
     if label.shape != distance.shape or label.ndim != 1:
@@ -66,12 +63,36 @@ def get_eer_auc(label, distance, device=None):
     lab = np.ascontiguousarray(label == 1, dtype=np.int32)  # pos_label=1 (evaluation.py:48)
     if lab.size == 0 or lab.min() == lab.max():
         raise ValueError("Only one class present in y_true. ROC AUC score is not defined in that case.")
-    s = _f32c(distance)
+    return lab, _f32c(distance)
+
+
+def roc_curve(label, distance, device=None):
+    """``sklearn.metrics.roc_curve(label, distance, pos_label=1)`` as called at
+    evaluation.py:48: ``(fpr, tpr, thresholds)`` float64 arrays, collinear vertices dropped,
+    first point ``(0, 0, inf)``.  Scores are ranked as float32 (the dtype the scorer emits)."""
+    lab, s = _labels_scores(label, distance)
+    ctx = _lib.context(device)
+    cap = lab.size + 1
+    fpr, tpr, thr = (np.empty(cap, dtype=np.float64) for _ in range(3))
+    count = C.c_int64()
+    _lib.check(ctx.lib.spb_roc_curve(ctx.handle, _lib.ptr(s), _lib.ptr(lab), lab.size, _lib.ptr(fpr),
+                                     _lib.ptr(tpr), _lib.ptr(thr), cap, C.byref(count)), ctx.handle)
+    k = count.value
+    return fpr[:k].copy(), tpr[:k].copy(), thr[:k].copy()
+
+
+def get_eer_auc(label, distance, device=None, curve=True):
+    """evaluation.py:47-52: returns ``(eer, auc, fpr, tpr)`` like the reference.  ``curve=False``
+    skips the ROC export (the reference only plots it) and returns ``None`` for fpr / tpr."""
+    lab, s = _labels_scores(label, distance)
     ctx = _lib.context(device)
     eer, auc = C.c_double(), C.c_double()
     _lib.check(ctx.lib.spb_eer(ctx.handle, _lib.ptr(s), _lib.ptr(lab), lab.size, C.byref(eer), C.byref(auc)),
                ctx.handle)
-    return eer.value, auc.value, None, None
+    if not curve:
+        return eer.value, auc.value, None, None
+    fpr, tpr, _ = roc_curve(lab, s, device=device)
+    return eer.value, auc.value, fpr, tpr
 
 
 def k_fold_eer_auc(label, scores, k=1, verbose=True, device=None):
@@ -83,7 +104,7 @@ def k_fold_eer_auc(label, scores, k=1, verbose=True, device=None):
     eers, aucs = np.zeros((k, 1)), np.zeros((k, 1))
     for split_num in range(k):
         a, b = split_num * step, (split_num + 1) * step
-        eers[split_num], aucs[split_num], _, _ = get_eer_auc(label[a:b], scores[a:b], device=device)
+        eers[split_num], aucs[split_num], _, _ = get_eer_auc(label[a:b], scores[a:b], device=device, curve=False)
     if verbose:
         print("EER=", np.mean(eers) * 100)
         print("AUC=", np.mean(aucs) * 100)

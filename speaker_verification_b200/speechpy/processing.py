@@ -21,13 +21,24 @@ def round_half_up(number):
     return int(decimal.Decimal(number).quantize(decimal.Decimal('1'), rounding=decimal.ROUND_HALF_UP))
 
 
-def preemphasis(signal, shift=1, cof=0.98):
-    """signal - cof * roll(signal, shift), circular (processing.py:45-58).
+_PRE_DTYPES = {np.dtype(np.float32): _lib.F32, np.dtype(np.float64): _lib.F64,
+               np.dtype(np.int16): _lib.I16, np.dtype(np.int32): _lib.I32}
 
-    Not on the accelerated path: mfe/lmfe/mfcc never
-    call it; it is a two-term host expression kept for API compatibility.
-    """
-    return signal - cof * np.roll(signal, shift)
+
+def preemphasis(signal, shift=1, cof=0.98):
+    """signal - cof * np.roll(signal, shift), circular (processing.py:45-58), on the device
+    (``spb_preemphasis``).  Result dtype as numpy gives it: float32 for a float32 signal,
+    float64 for float64 and integer signals; any shape (np.roll flattens when axis is None)."""
+    signal = np.asarray(signal)
+    x = np.ascontiguousarray(signal)
+    if x.dtype not in _PRE_DTYPES:
+        x = x.astype(np.float32 if x.dtype == np.float16 else np.float64)
+    out = np.empty(x.shape, dtype=np.float32 if x.dtype == np.float32 else np.float64)
+    if x.size:
+        ctx = _lib.context()
+        _lib.check(ctx.lib.spb_preemphasis(ctx.handle, _lib.ptr(x), _PRE_DTYPES[x.dtype], x.size, int(shift),
+                                           float(cof), _lib.ptr(out)), ctx.handle)
+    return out
 
 
 def _geometry(length_signal, sampling_frequency, frame_length, frame_stride):
@@ -97,14 +108,8 @@ def power_spectrum(frames, fft_points=512):
 
 def log_power_spectrum(frames, fft_points=512, normalize=True):
     """10 log10(max(P, 1e-20)), minus the global maximum when ``normalize``
-    (processing.py:177-198).  P comes from the GPU; the two-line epilogue is host numpy
-    (SURVEY.md section 8f, row f2)."""
-    power_spec = power_spectrum(frames, fft_points)
-    power_spec[power_spec <= 1e-20] = 1e-20
-    log_power_spec = 10 * np.log10(power_spec)
-    if normalize:
-        return log_power_spec - np.max(log_power_spec)
-    return log_power_spec
+    (processing.py:177-198); power spectrum and float64 log epilogue both on the device."""
+    return _spectrum(frames, fft_points, 3 if normalize else 2)
 
 
 def derivative_extraction(feat, DeltaWindows):

@@ -66,6 +66,36 @@ def test_power_spectrum(sp):
         sp.processing.power_spectrum(fr, 500)
 
 
+def test_preemphasis_and_log_power_spectrum_on_device(sp):
+    """SURVEY 8f-2 (processing.py:45-58, 177-198): both run on the device; preemphasis is
+    bit-exact in numpy's dtype (two separately rounded operations), for any shift."""
+    g = golden("stack_frames_hamming.npz")
+    sig = synth.audio(11, 4000, np.float64)
+    assert np.array_equal(sp.processing.preemphasis(sig, 1, 0.98), g["preemphasis"])
+    rng = np.random.Generator(np.random.Philox(21))
+    for x in (rng.standard_normal(10007), rng.standard_normal(513).astype(np.float32),
+              rng.integers(-32768, 32767, 9999).astype(np.int16), rng.integers(-10**6, 10**6, 777).astype(np.int32),
+              rng.standard_normal((7, 33))):
+        for shift, cof in ((1, 0.98), (3, 0.5), (-2, 0.97), (x.size + 5, 0.9), (0, 1.0)):
+            ref = o.preemphasis(x, shift, cof)
+            got = sp.processing.preemphasis(x, shift, cof)
+            assert got.dtype == ref.dtype and got.shape == ref.shape and np.array_equal(got, ref), (x.dtype, shift)
+    assert sp.processing.preemphasis(np.zeros(0)).shape == (0,)
+    # log power spectrum: float32 FFT, float64 log epilogue
+    fr = o.stack_frames(synth.audio(1, 48000, np.float64), FS, 0.020, 0.010, zero_padding=False)
+    for normalize in (False, True):
+        ref = o.log_power_spectrum(fr, 512, normalize)
+        got = sp.processing.log_power_spectrum(fr, 512, normalize)
+        assert got.shape == ref.shape and got.dtype == np.float64
+        p_ref = o.power_spectrum(fr, 512)
+        strong = p_ref >= 1e-4 * p_ref.max(axis=1, keepdims=True)
+        assert np.max(np.abs(got - ref)[strong]) < 1e-3          # dB, bins within 40 dB of the row maximum
+        assert np.max(np.abs(got - ref)) < 0.05                  # every bin
+    assert np.max(sp.processing.log_power_spectrum(fr, 512, True)) == 0.0
+    silent = sp.processing.log_power_spectrum(np.zeros((3, 320)), 512, False)
+    assert np.all(silent == -200.0)                              # floor 1e-20 -> -200 dB
+
+
 def test_generic_kernel_matches_fast(sp):
     """Route the same call through the generic radix-2 kernel: two independent FFTs."""
     from speaker_verification_b200 import _lib

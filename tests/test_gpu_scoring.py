@@ -70,6 +70,38 @@ def test_eer_auc_goldens(lib_built, name):
     assert abs(auc - float(g[f"auc_{name}"])) < 1e-12
 
 
+@pytest.mark.parametrize("name", ["ties", "tiny", "perfect"])
+def test_roc_curve_goldens(lib_built, name):
+    """get_eer_auc returns (eer, auc, fpr, tpr) like evaluation.py:47-52; the curve must be the
+    reference's point for point (integer counts -> bit-exact float64 ratios)."""
+    g = golden("scoring.npz")
+    lab, s = g[f"label_{name}"], g[f"score_{name}"]
+    _, _, fpr, tpr = scoring.get_eer_auc(lab, s)
+    assert fpr.dtype == np.float64 and np.array_equal(fpr, g[f"fpr_{name}"]) and np.array_equal(tpr, g[f"tpr_{name}"])
+    f2, t2, thr = scoring.roc_curve(lab, s)
+    fo, to, tho = so.roc_curve_restated(lab, s.astype(np.float32))
+    assert np.array_equal(f2, fo) and np.array_equal(t2, to) and np.array_equal(thr, tho)
+
+
+def test_roc_curve_large_with_ties_and_cfg5(lib_built):
+    from sklearn.metrics import roc_curve as sk_roc_curve
+    g = golden("scoring.npz")
+    rng = np.random.Generator(np.random.Philox(9))
+    s = np.round(rng.standard_normal(200_000), 2).astype(np.float32)
+    lab = (rng.random(200_000) < 0.1 + 0.3 * (s > 0.3)).astype(np.int32)
+    fpr, tpr, thr = scoring.roc_curve(lab, s)
+    f_sk, t_sk, th_sk = sk_roc_curve(lab, s, pos_label=1)
+    assert np.array_equal(fpr, f_sk) and np.array_equal(tpr, t_sk)
+    assert np.isinf(thr[0]) and np.array_equal(thr[1:], th_sk[1:].astype(np.float64))
+    # config 5 trial scores (float32 of the float64 golden scores)
+    ti, tj, lab5 = so.synth_trials(4874, 4874, 37720, seed=5)
+    f5, t5, _ = scoring.roc_curve(lab5, g["cfg5_trial_scores_f64"].astype(np.float32))
+    assert np.array_equal(f5, g["fpr_cfg5"]) and np.array_equal(t5, g["tpr_cfg5"])
+    # two points only / all scores equal
+    f, t, th = scoring.roc_curve(np.array([1, 0, 1, 0, 0]), np.zeros(5))
+    assert f.tolist() == [0.0, 1.0] and t.tolist() == [0.0, 1.0] and th[1] == 0.0
+
+
 def test_eer_edge_cases(lib_built):
     with pytest.raises(ValueError):
         scoring.get_eer_auc(np.ones(5, np.int32), np.arange(5.0))

@@ -136,10 +136,16 @@ def test_scoring_oracle():
         assert eer == float(g[f"eer_{name}"]) and auc == float(g[f"auc_{name}"])
         e2, a2 = so.eer_auc_restated(lab, s)
         assert abs(e2 - eer) < 1e-9 and abs(a2 - auc) < 1e-12
+        # ROC curve export: restatement == the curve the reference's get_eer_auc returned
+        f, t, thr = so.roc_curve_restated(lab, s.astype(np.float32))
+        assert np.array_equal(f, g[f"fpr_{name}"]) and np.array_equal(t, g[f"tpr_{name}"])
+        assert np.isinf(thr[0]) and np.all(np.diff(thr) < 0)
     ti, tj, lab = so.synth_trials(4874, 4874, 37720, seed=5)
     s = g["cfg5_trial_scores_f64"]
     eer, auc, _, _ = so.get_eer_auc(lab, s)
     assert eer == float(g["eer_cfg5"]) and auc == float(g["auc_cfg5"])
     e2, a2 = so.eer_auc_restated(lab, s)
     assert abs(e2 - eer) < 1e-9 and abs(a2 - auc) < 1e-12
+    f, t, _ = so.roc_curve_restated(lab, s.astype(np.float32))
+    assert np.array_equal(f, g["fpr_cfg5"]) and np.array_equal(t, g["tpr_cfg5"])
     assert 0.005 < eer < 0.45  # the synthetic trial set is neither trivial nor random
