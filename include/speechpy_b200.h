@@ -212,6 +212,24 @@ SPB_API int spb_lmfe_cmvnw_batch_dtype(spb_context *ctx, const spb_batch *batch,
 SPB_API int spb_mfcc_delta_batch_dtype(spb_context *ctx, const spb_batch *batch, const void *samples,
                                int dtype, double sample_scale, int64_t arena_len, float *out);
 
+/* ------------------------------------------------- 8f-1  training feature cubes
+ * utils.py:325-397, the DataLoader transforms that follow lmfe (train.py:194-210):
+ *   CMVN        : derivative != 0 -> extract_derivative_feature (F, M, 3);
+ *                 normalize  != 0 -> each (F, M) channel <- cmvn(channel, True) over the utterance
+ *   FeatureCube : out[u][ch][k][t][c] = feature_u[crop_starts[u*num_crops + k] + t][c][ch]
+ * out: (U, channels, num_crops, crop_frames, M) float32, channels = derivative ? 3 : 1
+ * (utterance u's slice is the reference's FeatureCube3C / FeatureCube[None] output).
+ * crop_starts: HOST int32 [U * num_crops], each in [0, F_u - crop_frames] -- the reference
+ * draws them with np.random.randint(F - frames, size=crops) (utils.py:373); the caller owns
+ * the RNG.  The log-mel features never leave the device. */
+SPB_API int spb_feature_cubes_batch_dev(spb_context *ctx, const spb_batch *batch, const float *d_samples,
+                                int64_t arena_len, int32_t derivative, int32_t normalize,
+                                const int32_t *crop_starts, int32_t num_crops, int32_t crop_frames,
+                                float *d_out);
+SPB_API int spb_feature_cubes_batch(spb_context *ctx, const spb_batch *batch, const void *samples, int32_t dtype,
+                            double sample_scale, int64_t arena_len, int32_t derivative, int32_t normalize,
+                            const int32_t *crop_starts, int32_t num_crops, int32_t crop_frames, float *out);
+
 /* ------------------------------------------------------- a10  cosine scores
  * evaluation.py:76-77 over all (enrolment, test) pairs at once:
  * S[i, j] = <E_i, T_j> / (|E_i| |T_j|); zero-norm rows give 0 (sklearn).

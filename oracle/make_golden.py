@@ -275,6 +275,27 @@ def main():
                         cube=rf.extract_derivative_feature(v), x1=v1,
                         cube1=rf.extract_derivative_feature(v1))
 
+    # ------------------------------------------- 8f-1: CMVN / FeatureCube transforms (utils.py:325-397)
+    rutils = sys.modules["utils"]  # the reference's utils, imported by `from utils import *` in evaluation.py
+    sig_c = synth.audio(21, 40000, np.float64)
+    lm = rf.lmfe(sig_c, 16000, frame_length=0.020, frame_stride=0.010, num_filters=40, fft_length=512)
+    cubes = {"seed": 21, "n": 40000}
+    for deriv in (False, True):
+        for norm in (False, True):
+            rutils.c.DERIVATIVE, rutils.c.NORMALIZE = deriv, norm
+            smp = rutils.CMVN()({"feature": lm.copy(), "label": 3})
+            same(smp["feature"], o.cmvn_transform(lm.copy(), deriv, norm), 0.0, "CMVN transform")
+            np.random.seed(77)
+            cube_cls = rutils.FeatureCube3C((80, 40, 20, 3)) if deriv else rutils.FeatureCube((80, 40, 20))
+            ref_cube = cube_cls({"feature": smp["feature"], "label": 3})["feature"]
+            np.random.seed(77)
+            idx = np.random.randint(lm.shape[0] - 80, size=20)
+            same(ref_cube, o.feature_cube(smp["feature"], idx, 80), 0.0, "FeatureCube")
+            cubes[f"idx_d{int(deriv)}n{int(norm)}"] = idx
+            cubes[f"cube_d{int(deriv)}n{int(norm)}"] = ref_cube[:, :3]  # first 3 crops (small file)
+    rutils.c.DERIVATIVE, rutils.c.NORMALIZE = False, False
+    np.savez_compressed(os.path.join(out_dir, "feature_cubes.npz"), **cubes)
+
     # --------------------------------------------------------------- scoring
     sc = {}
     E, T = so.synth_embeddings(97, 113, 64, seed=5)

@@ -313,3 +313,35 @@ def cmvnw_vectorised(vec, win_size=301, variance_normalization=False):
         sd = np.std(w.astype(np.float64), axis=-1)
         out[s:e] = centred[s:e] / (sd + CMVN_EPS)
     return out
+
+
+# ----------------------------------------------------------------------------
+# the DataLoader transforms that follow lmfe (utils.py:325-397)
+# ----------------------------------------------------------------------------
+def cmvn_transform(feature, derivative, normalize):
+    """``utils.CMVN.__call__`` (utils.py:383-397) with c.DERIVATIVE / c.NORMALIZE as arguments."""
+    if derivative:
+        feature = extract_derivative_feature(feature)
+        if normalize:
+            for k in range(3):
+                feature[:, :, k] = cmvn(feature[:, :, k], variance_normalization=True)
+    elif normalize:
+        feature = cmvn(feature, variance_normalization=True)
+    return feature
+
+
+def feature_cube(feature, idx, num_frames):
+    """``utils.FeatureCube.__call__`` (utils.py:354-373, feature (F, M)) and
+    ``FeatureCube3C.__call__`` (utils.py:335-350, feature (F, M, 3)) with the random crop
+    starts ``idx`` given: float32 (1, crops, frames, M) / (3, crops, frames, M)."""
+    idx = np.asarray(idx)
+    if feature.ndim == 3:
+        f = feature.transpose(2, 0, 1)
+        cube = np.zeros((f.shape[0], len(idx), num_frames, f.shape[2]), dtype=np.float32)
+        for num, index in enumerate(idx):
+            cube[:, num, :, :] = f[:, index:index + num_frames, :]
+        return cube
+    cube = np.zeros((len(idx), num_frames, feature.shape[1]), dtype=np.float32)
+    for num, index in enumerate(idx):
+        cube[num, :, :] = feature[index:index + num_frames, :]
+    return cube[None, :, :, :]

@@ -65,6 +65,9 @@ PROTOTYPES = {
     "spb_mfcc_delta_batch": (C.c_int, [c_vp, c_vp, c_vp, c_i64, c_vp]),
     "spb_lmfe_cmvnw_batch_dtype": (C.c_int, [c_vp, c_vp, c_vp, c_i32, C.c_double, c_i64, c_vp]),
     "spb_mfcc_delta_batch_dtype": (C.c_int, [c_vp, c_vp, c_vp, c_i32, C.c_double, c_i64, c_vp]),
+    "spb_feature_cubes_batch_dev": (C.c_int, [c_vp, c_vp, c_vp, c_i64, c_i32, c_i32, c_vp, c_i32, c_i32, c_vp]),
+    "spb_feature_cubes_batch": (C.c_int, [c_vp, c_vp, c_vp, c_i32, C.c_double, c_i64, c_i32, c_i32, c_vp, c_i32,
+                                          c_i32, c_vp]),
     "spb_cosine_scores": (C.c_int, [c_vp, c_vp, c_i64, c_vp, c_i64, c_i32, c_vp]),
     "spb_cosine_scores_dev": (C.c_int, [c_vp, c_vp, c_i64, c_vp, c_i64, c_i32, c_vp]),
     "spb_trial_scores_dev": (C.c_int, [c_vp, c_vp, c_i64, c_i64, c_vp, c_vp, c_i64, c_vp]),

@@ -169,6 +169,45 @@ class FeatureBatch:
                    self.ctx.handle)
         return out
 
+    # ---- training cubes (utils.CMVN + utils.FeatureCube / FeatureCube3C, utils.py:325-397) ----
+    def draw_crop_starts(self, num_crops: int = 20, crop_frames: int = 80, rng=None) -> np.ndarray:
+        """(U, num_crops) int32 crop starts, drawn like ``FeatureCube.__call__`` does per
+        utterance: ``np.random.randint(F - crop_frames, size=num_crops)`` (utils.py:373), in
+        utterance order, from the global numpy RNG unless ``rng`` (a RandomState) is given."""
+        rnd = np.random if rng is None else rng
+        F = np.diff(self.frame_offsets)
+        return np.stack([rnd.randint(int(f) - crop_frames, size=num_crops) for f in F]).astype(np.int32)
+
+    def feature_cubes(self, arena: np.ndarray, crop_starts=None, num_crops: int = 20, crop_frames: int = 80,
+                      derivative: bool = False, normalize: bool = False, sample_scale: float = 1.0,
+                      out: np.ndarray | None = None) -> np.ndarray:
+        """lmfe -> [Delta, Delta-Delta] -> [per-utterance cmvn] -> random crops, all on the
+        device: (U, channels, num_crops, crop_frames, num_filters) float32, channels = 3 if
+        ``derivative`` else 1; slice ``[u]`` is what the reference's transform pipeline
+        ``Compose([CMVN(), FeatureCube(...)])`` (train.py:194-210) yields for utterance u."""
+        arena, code = _as_arena(arena)
+        if crop_starts is None:
+            crop_starts = self.draw_crop_starts(num_crops, crop_frames)
+        crops = np.ascontiguousarray(crop_starts, dtype=np.int32).reshape(len(self.starts), -1)
+        num_crops = crops.shape[1]
+        shape = (len(self.starts), 3 if derivative else 1, num_crops, crop_frames, self.num_filters)
+        if out is None:
+            out = np.empty(shape, dtype=np.float32)
+        assert out.shape == shape and out.dtype == np.float32 and out.flags.c_contiguous
+        _lib.check(self.ctx.lib.spb_feature_cubes_batch(
+            self.ctx.handle, self.handle, _lib.ptr(arena), code, float(sample_scale), arena.shape[0],
+            int(bool(derivative)), int(bool(normalize)), _lib.ptr(crops), num_crops, int(crop_frames),
+            _lib.ptr(out)), self.ctx.handle)
+        return out
+
+    def feature_cubes_dev(self, d_samples: int, arena_len: int, d_out: int, crop_starts, crop_frames: int = 80,
+                          derivative: bool = False, normalize: bool = False):
+        """Device-pointer variant (float32 arena in, cubes out; ``crop_starts`` host int32 (U, crops))."""
+        crops = np.ascontiguousarray(crop_starts, dtype=np.int32).reshape(len(self.starts), -1)
+        _lib.check(self.ctx.lib.spb_feature_cubes_batch_dev(
+            self.ctx.handle, self.handle, d_samples, arena_len, int(bool(derivative)), int(bool(normalize)),
+            _lib.ptr(crops), crops.shape[1], int(crop_frames), d_out), self.ctx.handle)
+
     # ---- device-pointer entry points (asynchronous on ctx.stream()) -----------------
     def lmfe_cmvnw_dev(self, d_samples: int, arena_len: int, d_out: int):
         _lib.check(self.ctx.lib.spb_lmfe_cmvnw_batch_dev(self.ctx.handle, self.handle, d_samples,

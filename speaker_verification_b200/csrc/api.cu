@@ -1282,4 +1282,79 @@ int spb_preemphasis(spb_context *ctx, const void *sig, int32_t dtype, int64_t n,
   return SPB_OK;
 }
 
+// ------------------------------------------------------------------ 8f-1 feature cubes
+static int run_feature_cubes(spb_context *ctx, const spb_batch *b, const float *d_samples, int64_t arena_len,
+                             int derivative, int normalize, const int32_t *crop_starts, int num_crops,
+                             int crop_frames, float *d_out) {
+  const int M = b->plan->p.num_filters;
+  SPB_REQUIRE(ctx, M >= 1, "feature cubes: plan has no filterbank");
+  SPB_REQUIRE(ctx, num_crops >= 1 && crop_frames >= 1 && crop_starts, "feature cubes: bad crop arguments");
+  for (int64_t u = 0; u < b->U; ++u) {
+    const int64_t F = b->h_frame_offsets[u + 1] - b->h_frame_offsets[u];
+    for (int k = 0; k < num_crops; ++k) {
+      const int64_t st = crop_starts[u * num_crops + k];
+      // np.random.randint(F - frames) yields [0, F - frames) and needs F > frames (utils.py:373)
+      SPB_REQUIRE(ctx, st >= 0 && st + crop_frames <= F, "feature cubes: crop outside its utterance");
+    }
+  }
+  const int channels = derivative ? 3 : 1;
+  float *d_lmfe = (float *)scratch(ctx, 2, (size_t)std::max<int64_t>(b->total_frames, 1) * M * 4);
+  int32_t *d_crops = (int32_t *)scratch(ctx, 4, (size_t)b->U * num_crops * 4);
+  double2 *d_stats = normalize ? (double2 *)scratch(ctx, 3, (size_t)b->U * channels * M * sizeof(double2)) : nullptr;
+  if (!d_lmfe || !d_crops || (normalize && !d_stats)) return SPB_ERR_CUDA;
+  SPB_CUDA(ctx, cudaMemcpyAsync(d_crops, crop_starts, (size_t)b->U * num_crops * 4, cudaMemcpyHostToDevice, ctx->stream));
+  int rc = run_simple_mode(ctx, b, d_samples, arena_len, FEAT_LMFE, d_lmfe, nullptr);
+  if (rc) return rc;
+  rc = launch_feature_cubes(ctx, d_lmfe, b->d_frame_offsets, b->U, M, channels, normalize, d_crops, num_crops,
+                            crop_frames, d_stats, d_out);
+  if (rc) return rc;
+  // crop_starts is caller memory (pageable): finish its upload before returning
+  SPB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  return SPB_OK;
+}
+
+int spb_feature_cubes_batch_dev(spb_context *ctx, const spb_batch *b, const float *d_samples, int64_t arena_len,
+                                int32_t derivative, int32_t normalize, const int32_t *crop_starts,
+                                int32_t num_crops, int32_t crop_frames, float *d_out) {
+  int rc = check_batch(ctx, b, arena_len, d_samples, d_out);
+  if (rc) return rc;
+  if (b->U == 0) return SPB_OK;
+  SPB_CUDA(ctx, cudaSetDevice(ctx->device));
+  return run_feature_cubes(ctx, b, d_samples, arena_len, derivative, normalize, crop_starts, num_crops,
+                           crop_frames, d_out);
+}
+
+int spb_feature_cubes_batch(spb_context *ctx, const spb_batch *b, const void *samples, int32_t dtype,
+                            double sample_scale, int64_t arena_len, int32_t derivative, int32_t normalize,
+                            const int32_t *crop_starts, int32_t num_crops, int32_t crop_frames, float *out) {
+  int rc = check_batch(ctx, b, arena_len, samples, out);
+  if (rc) return rc;
+  SPB_REQUIRE(ctx, dtype == SPB_F32 || dtype == SPB_F64 || dtype == SPB_I16 || dtype == SPB_I32,
+              "feature cubes: unsupported sample dtype");
+  if (b->U == 0) return SPB_OK;
+  SPB_REQUIRE(ctx, num_crops >= 1 && crop_frames >= 1, "feature cubes: bad crop arguments");
+  SPB_CUDA(ctx, cudaSetDevice(ctx->device));
+  const size_t esz = (dtype == SPB_F64) ? 8 : (dtype == SPB_I16 ? 2 : 4);
+  const float scale = (float)sample_scale;
+  const int M = b->plan->p.num_filters, channels = derivative ? 3 : 1;
+  const size_t out_elems = (size_t)b->U * channels * num_crops * crop_frames * M;
+  float *d_samples = (float *)scratch(ctx, 0, (size_t)std::max<int64_t>(arena_len, 1) * 4);
+  float *d_out = (float *)scratch(ctx, 1, out_elems * 4);
+  if (!d_samples || !d_out) return SPB_ERR_CUDA;
+  if (dtype == SPB_F32 && scale == 1.0f) {
+    SPB_CUDA(ctx, cudaMemcpyAsync(d_samples, samples, (size_t)arena_len * 4, cudaMemcpyHostToDevice, ctx->stream));
+  } else {
+    void *d_raw = scratch(ctx, 5, (size_t)std::max<int64_t>(arena_len, 1) * esz);
+    if (!d_raw) return SPB_ERR_CUDA;
+    SPB_CUDA(ctx, cudaMemcpyAsync(d_raw, samples, (size_t)arena_len * esz, cudaMemcpyHostToDevice, ctx->stream));
+    if ((rc = launch_ingest(ctx, d_raw, dtype, d_samples, arena_len, scale))) return rc;
+  }
+  rc = run_feature_cubes(ctx, b, d_samples, arena_len, derivative, normalize, crop_starts, num_crops, crop_frames,
+                         d_out);
+  if (rc) return rc;
+  SPB_CUDA(ctx, cudaMemcpyAsync(out, d_out, out_elems * 4, cudaMemcpyDeviceToHost, ctx->stream));
+  SPB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  return SPB_OK;
+}
+
 }  // extern "C"

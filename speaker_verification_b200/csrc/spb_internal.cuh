@@ -210,6 +210,9 @@ int launch_preemphasis(spb_context *ctx, const void *in, int dtype, long long n,
                        void *out);
 int launch_log_power(spb_context *ctx, const float *p, long long n, int normalize, unsigned int *d_max_bits,
                      double *out);
+int launch_feature_cubes(spb_context *ctx, const float *d_lmfe, const int64_t *d_frame_offsets, int64_t U, int M,
+                         int channels, int normalize, const int32_t *d_crop_starts, int num_crops,
+                         int crop_frames, double2 *d_stats, float *d_out);
 int launch_ingest(spb_context *ctx, const void *in, int dtype_in, float *out, int64_t n, float scale);
 int launch_build_tiles(spb_context *ctx, const int32_t *nframes, const int64_t *tile_offsets,
                        int64_t U, int tile, int2 *tiles);

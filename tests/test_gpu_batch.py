@@ -197,3 +197,49 @@ def test_pipelined_host_path_many_chunks(sp):
     for k in (0, 11, 200):
         assert np.array_equal(out2[k], parts[perm[k]])
     fb.close(); fb2.close()
+
+
+def test_feature_cubes_match_reference_transforms(sp):
+    """utils.CMVN + FeatureCube / FeatureCube3C (utils.py:325-397) on the device.
+    Golden = the reference's transforms run on the reference's float64 lmfe with seeded
+    np.random crops; tolerance 1e-4 (float32 lmfe; normalised values are O(1))."""
+    from conftest import golden
+    g = golden("feature_cubes.npz")
+    sig = synth.audio(int(g["seed"]), int(g["n"]), np.float64)
+    others = _signals(900, [30000, 16160, 52345])
+    sigs = [others[0], sig.astype(np.float32), others[1], others[2]]
+    arena, starts, lens = batch.pack(sigs)
+    fb = batch.FeatureBatch(starts, lens)
+    F = np.diff(fb.frame_offsets)
+    rs = np.random.RandomState(5)
+    for deriv in (False, True):
+        for norm in (False, True):
+            tag = f"d{int(deriv)}n{int(norm)}"
+            crops = np.stack([rs.randint(int(f) - 80, size=20) for f in F]).astype(np.int32)
+            crops[1] = g[f"idx_{tag}"]
+            out = fb.feature_cubes(arena, crops, derivative=deriv, normalize=norm)
+            assert out.shape == (4, 3 if deriv else 1, 20, 80, 40) and out.dtype == np.float32
+            assert np.max(np.abs(out[1][:, :3] - g[f"cube_{tag}"])) < TOL, tag
+            for u, s in enumerate(sigs):      # every utterance against the oracle transforms
+                feat = o.cmvn_transform(o.lmfe(s, FS), deriv, norm)
+                assert np.max(np.abs(out[u] - o.feature_cube(feat, crops[u], 80))) < TOL, (tag, u)
+    # reference-style RNG use: np.random.seed + one randint call per utterance, in order
+    np.random.seed(123)
+    auto = fb.draw_crop_starts()
+    np.random.seed(123)
+    assert np.array_equal(auto, np.stack([np.random.randint(int(f) - 80, size=20) for f in F]))
+    # last admissible start is F - 80; one past it is rejected
+    edge = np.tile((F - 80).astype(np.int32)[:, None], (1, 2))
+    fb.feature_cubes(arena, edge)
+    edge[2, 1] += 1
+    with pytest.raises(Exception):
+        fb.feature_cubes(arena, edge)
+    # int16 PCM arena with the librosa scale gives the same cubes as the scaled float arena
+    pcm = [synth.pcm16(40 + i, n) for i, n in enumerate([30000, 40000])]
+    a16, st, ln = batch.pack(pcm, dtype=np.int16)
+    fb2 = batch.FeatureBatch(st, ln)
+    cr = fb2.draw_crop_starts(4, 80, rng=np.random.RandomState(1))
+    c16 = fb2.feature_cubes(a16, cr, derivative=True, normalize=True, sample_scale=batch.PCM16_SCALE)
+    c32 = fb2.feature_cubes(a16.astype(np.float32) * np.float32(batch.PCM16_SCALE), cr, derivative=True, normalize=True)
+    assert np.array_equal(c16, c32)
+    fb.close(); fb2.close()

@@ -149,3 +149,16 @@ def test_scoring_oracle():
     f, t, _ = so.roc_curve_restated(lab, s.astype(np.float32))
     assert np.array_equal(f, g["fpr_cfg5"]) and np.array_equal(t, g["tpr_cfg5"])
     assert 0.005 < eer < 0.45  # the synthetic trial set is neither trivial nor random
+
+
+def test_cmvn_transform_and_feature_cubes_oracle():
+    """SURVEY 8f-1 oracle (utils.py:325-397) against the cubes the reference's transforms produced."""
+    g = golden("feature_cubes.npz")
+    from speaker_verification_b200 import synth
+    lm = o.lmfe(synth.audio(int(g["seed"]), int(g["n"]), np.float64), 16000)
+    for deriv in (False, True):
+        for norm in (False, True):
+            tag = f"d{int(deriv)}n{int(norm)}"
+            cube = o.feature_cube(o.cmvn_transform(lm.copy(), deriv, norm), g[f"idx_{tag}"], 80)
+            assert cube.shape == (3 if deriv else 1, 20, 80, 40) and cube.dtype == np.float32
+            assert np.array_equal(cube[:, :3], g[f"cube_{tag}"])
