@@ -397,10 +397,11 @@ features_fast512(const FeatParams p) {
 #pragma unroll
         for (int j = 0; j < 16; ++j) {
           if (j < NJ) {
-            // one 64-bit load per frame (a half-warp reads 128 contiguous bytes), then pair up
-            const float2 za = *reinterpret_cast<const float2 *>(xa + 32 * j + 2 * l16);
-            const float2 zb = *reinterpret_cast<const float2 *>(xb + 32 * j + 2 * l16);
-            v[j] = c2_make(p_make(za.x, zb.x), p_make(za.y, zb.y));
+            // four 32-bit loads straight into the halves of the two register pairs (A.re, B.re),
+            // (A.im, B.im): 64-bit loads per frame would need four MOVs per sample pair to
+            // transpose (and ptxas re-materialises those at every use)
+            const int o = 32 * j + 2 * l16;
+            v[j] = c2_make(p_make(xa[o], xb[o]), p_make(xa[o + 1], xb[o + 1]));
           } else {
             v[j] = c2_zero();
           }
