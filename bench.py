@@ -197,6 +197,16 @@ def run_ours(args, rank, world, local_rank):
                         "sample": f"{len(ls)} cfg3-shaped utterances ({ls.sum() / FS / 3600:.3f} audio-h), "
                                   f"oracle port of speechpy lmfe+cmvnw, one process per core, {dt:.1f} s wall"}
 
+    # pin this rank to the CPUs next to its GPU so that the pinned host buffers of the e2e leg
+    # are first-touched on the GPU's NUMA node (matters when several ranks share the host)
+    numa = "unset"
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        pynvml.nvmlDeviceSetCpuAffinity(pynvml.nvmlDeviceGetHandleByIndex(local_rank))
+        numa = f"{len(os.sched_getaffinity(0))} cpus near gpu {local_rank}"
+    except Exception as e:  # not fatal: the bench still runs, just without NUMA placement
+        numa = f"unavailable:{type(e).__name__}"
     import torch
     import torch.distributed as dist
     from speaker_verification_b200 import _lib, batch
@@ -298,6 +308,7 @@ def run_ours(args, rank, world, local_rank):
                               f"{e_steps} steps, pinned host buffers, int16 PCM arena in (the wav payload; scaled by "
                               f"1/32768 on the device like librosa.load), float32 features out, spb_lmfe_cmvnw_batch_dtype "
                               f"(H2D / kernels / D2H pipelined over chunks)",
+                    "host_affinity": numa,
                     "float32_arena_value": e2e_f32, "float32_arena_h2d_bytes_per_step": int(e_end * 4),
                     "matches_device_path": same},
             "gpu_launches": int(launches),
