@@ -6,7 +6,7 @@
 //   FeatureCube[3C]  : idx = np.random.randint(F - frames, size=crops);
 //                      cube[ch, k, t, c] = feature[idx[k] + t, c, ch]                  float32
 // Here: one stats kernel (per utterance, channel and column: mean and population std of the
-// mean-subtracted values, float64 accumulators, two passes like numpy) and one gather kernel
+// mean-subtracted values, float64 accumulators) and one gather kernel
 // that derives Delta / Delta-Delta on the fly, normalises and writes the crops.  The random
 // crop starts are drawn on the host (the reference uses the global numpy RNG) and passed in.
 #include <algorithm>
@@ -31,69 +31,83 @@ __device__ __forceinline__ float channel_value(const float *row, int c, int ch, 
 
 constexpr int kStatSlices = 4;
 
-// grid = utterances; block = (M * channels) x kStatSlices threads.  stats[u][ch][c] = {mean, std}
+// grid = utterances; block = kStatSlices x (M * channels) threads.  stats[u][ch][c] = {mean, 1/(std+eps)}.
+// One pass: every slice stages its row in shared memory (one coalesced 4*M-byte read per row),
+// the M * channels threads of the slice derive their channel value from it and accumulate
+// sum(v - p) and sum((v - p)^2) in float64 around the pivot p = value in the utterance's first
+// row (keeps the single-pass variance free of cancellation).  mean = p + S1/F,
+// var = S2/F - (S1/F)^2 == the population variance of the mean-subtracted column that
+// cmvn (processing.py:257-266) takes.
 __global__ void cube_stats_kernel(const float *__restrict__ lmfe, const int64_t *__restrict__ frame_offsets,
                                   int M, int channels, double2 *__restrict__ stats) {
-  extern __shared__ double s_red[];  // [kStatSlices][M * channels]
-  const int u = blockIdx.x;
+  extern __shared__ double s_red[];                         // [2][kStatSlices][cols]
   const int cols = M * channels;
+  float *s_row = reinterpret_cast<float *>(s_red + 2 * kStatSlices * cols);  // [kStatSlices + 1][M]
+  const int u = blockIdx.x;
   const int j = threadIdx.x % cols, slice = threadIdx.x / cols;
   const int ch = j / M, c = j % M;
   const long long r0 = frame_offsets[u], F = frame_offsets[u + 1] - r0;
   const float *base = lmfe + r0 * M;
-  double sum = 0.0;
-  for (long long f = slice; f < F; f += kStatSlices) sum += (double)channel_value(base + f * M, c, ch, M);
-  s_red[slice * cols + j] = sum;
+  float *row = s_row + slice * M, *row0 = s_row + kStatSlices * M;
+  if (threadIdx.x < M) row0[threadIdx.x] = F > 0 ? base[threadIdx.x] : 0.f;
   __syncthreads();
-  double tot = 0.0;
-  for (int s = 0; s < kStatSlices; ++s) tot += s_red[s * cols + j];
-  const double mean = F > 0 ? tot / (double)F : 0.0;
-  __syncthreads();
-  // cmvn: std of the mean-subtracted FLOAT64 values (processing.py:257-266); np.std subtracts
-  // their (round-off sized) mean again, which is reproduced by the two accumulators below
+  const double pivot = (double)channel_value(row0, c, ch, M);
   double s1 = 0.0, s2 = 0.0;
-  for (long long f = slice; f < F; f += kStatSlices) {
-    const double d = (double)channel_value(base + f * M, c, ch, M) - mean;
-    s1 += d;
-    s2 += d * d;
+  for (long long f0 = 0; f0 < F; f0 += kStatSlices) {
+    const long long f = f0 + slice;
+    if (j < M && f < F) row[j] = base[f * M + j];
+    __syncthreads();
+    if (f < F) {
+      const double d = (double)channel_value(row, c, ch, M) - pivot;
+      s1 += d;
+      s2 += d * d;
+    }
+    __syncthreads();
   }
   s_red[slice * cols + j] = s1;
-  __syncthreads();
-  double t1 = 0.0;
-  for (int s = 0; s < kStatSlices; ++s) t1 += s_red[s * cols + j];
-  __syncthreads();
-  s_red[slice * cols + j] = s2;
+  s_red[(kStatSlices + slice) * cols + j] = s2;
   __syncthreads();
   if (slice == 0) {
-    double t2 = 0.0;
-    for (int s = 0; s < kStatSlices; ++s) t2 += s_red[s * cols + j];
-    double var = 0.0;
+    double t1 = 0.0, t2 = 0.0;
+    for (int s = 0; s < kStatSlices; ++s) {
+      t1 += s_red[s * cols + j];
+      t2 += s_red[(kStatSlices + s) * cols + j];
+    }
+    double mean = 0.0, var = 0.0;
     if (F > 0) {
       const double m1 = t1 / (double)F;
+      mean = pivot + m1;
       var = t2 / (double)F - m1 * m1;
       if (var < 0.0) var = 0.0;
     }
-    stats[((long long)u * channels + ch) * M + c] = make_double2(mean, sqrt(var));
+    // {mean, 1 / (std + 2^-30)} (processing.py:253, 266)
+    stats[((long long)u * channels + ch) * M + c] = make_double2(mean, 1.0 / (sqrt(var) + 9.313225746154785e-10));
   }
 }
 
-// grid = (crops, utterances); out[u][ch][k][t][c]
+// grid = (crops, utterances); out[u][ch][k][t][c].  The crop's rows are staged in shared memory
+// once (coalesced), every channel is derived from the staged rows and stored coalesced.
 __global__ void cube_gather_kernel(const float *__restrict__ lmfe, const int64_t *__restrict__ frame_offsets,
                                    const int32_t *__restrict__ crop_starts, const double2 *__restrict__ stats,
                                    int M, int channels, int num_crops, int crop_frames, float *__restrict__ out) {
+  extern __shared__ float s_crop[];  // [crop_frames][M]
   const int k = blockIdx.x, u = blockIdx.y;
   const long long r0 = frame_offsets[u] + crop_starts[(long long)u * num_crops + k];
   const int per_ch = crop_frames * M;
-  const double eps = 9.313225746154785e-10;  // 2^-30 (processing.py:253)
-  for (int i = threadIdx.x; i < per_ch * channels; i += blockDim.x) {
-    const int ch = i / per_ch, rem = i % per_ch;
-    const int t = rem / M, c = rem % M;
-    float v = channel_value(lmfe + (r0 + t) * M, c, ch, M);
-    if (stats) {
-      const double2 ms = stats[((long long)u * channels + ch) * M + c];
-      v = (float)(((double)v - ms.x) / (ms.y + eps));
+  const float *src = lmfe + r0 * M;
+  for (int i = threadIdx.x; i < per_ch; i += blockDim.x) s_crop[i] = src[i];
+  __syncthreads();
+  for (int i = threadIdx.x; i < per_ch; i += blockDim.x) {
+    const int t = i / M, c = i - t * M;
+    const float *row = s_crop + t * M;
+    for (int ch = 0; ch < channels; ++ch) {
+      float v = channel_value(row, c, ch, M);
+      if (stats) {
+        const double2 ms = stats[((long long)u * channels + ch) * M + c];
+        v = (v - (float)ms.x) * (float)ms.y;  // float32 like the cube; |error| ~1e-6 of an O(1) value
+      }
+      out[(((long long)u * channels + ch) * num_crops + k) * per_ch + i] = v;
     }
-    out[((((long long)u * channels + ch) * num_crops + k) * crop_frames + t) * M + c] = v;
   }
 }
 
@@ -104,13 +118,17 @@ int launch_feature_cubes(spb_context *ctx, const float *d_lmfe, const int64_t *d
   const int cols = M * channels;
   if (cols * kStatSlices > 1024) return fail(ctx, SPB_ERR_UNSUPPORTED, "feature cubes: num_filters * channels > 256");
   if (U > 65535) return fail(ctx, SPB_ERR_UNSUPPORTED, "feature cubes: more than 65535 utterances per call");
+  if ((size_t)crop_frames * M * sizeof(float) > 48 * 1024)
+    return fail(ctx, SPB_ERR_UNSUPPORTED, "feature cubes: crop_frames * num_filters > 12288");
   if (normalize) {
-    cube_stats_kernel<<<(unsigned)U, cols * kStatSlices, (size_t)kStatSlices * cols * sizeof(double), ctx->stream>>>(
+    cube_stats_kernel<<<(unsigned)U, cols * kStatSlices,
+                        (size_t)2 * kStatSlices * cols * sizeof(double) + (size_t)(kStatSlices + 1) * M * sizeof(float),
+                        ctx->stream>>>(
         d_lmfe, d_frame_offsets, M, channels, d_stats);
     SPB_LAUNCH_CHECK(ctx, "cube_stats_kernel");
   }
   dim3 grid((unsigned)num_crops, (unsigned)U);
-  cube_gather_kernel<<<grid, 256, 0, ctx->stream>>>(d_lmfe, d_frame_offsets, d_crop_starts,
+  cube_gather_kernel<<<grid, 256, (size_t)crop_frames * M * sizeof(float), ctx->stream>>>(d_lmfe, d_frame_offsets, d_crop_starts,
                                                      normalize ? d_stats : nullptr, M, channels, num_crops,
                                                      crop_frames, d_out);
   SPB_LAUNCH_CHECK(ctx, "cube_gather_kernel");
