@@ -316,7 +316,14 @@ def run_ours(args, rank, world, local_rank):
             "roofline": {
                 "bound": "hbm", "kernel": "features_fast512 (framing+FFT512+|X|^2+mel+log)",
                 "achieved": achieved, "peak": peak, "unit": "GB/s",
-                "frac": (achieved / peak) if achieved else None, "traffic": None,
+                "frac": (achieved / peak) if achieved else None,
+                # ncu --set full (profiles/r01d_ncu_full_summary.csv, 4000-utterance launch): dram read
+                # 2.088 GB + write 0.506 GB for 2.607 GB algorithmic (samples read once, rows written
+                # once) -> 0.995 B of DRAM traffic per algorithmic byte; scaled to this run's launches
+                "traffic": 0.995 * alg_bytes / max(feat_n // max(args.steps, 1), 1),
+                "traffic_source": "ncu dram__bytes_read.sum + dram__bytes_write.sum of features_fast512 in "
+                                  "profiles/r01d_ncu_full_summary.csv (0.995 x algorithmic bytes), per launch",
+                "achieved_per_launch_bytes": alg_bytes / max(feat_n // max(args.steps, 1), 1),
                 "peak_source": peak_src,
                 "algorithmic_bytes_per_step": alg_bytes,
                 "kernel_ms_per_step": {"features": feat_ms / args.steps,
