@@ -243,3 +243,47 @@ def test_feature_cubes_match_reference_transforms(sp):
     c32 = fb2.feature_cubes(a16.astype(np.float32) * np.float32(batch.PCM16_SCALE), cr, derivative=True, normalize=True)
     assert np.array_equal(c16, c32)
     fb.close(); fb2.close()
+
+
+def test_full_size_properties_cfg3_scale(sp):
+    """Size-independent properties at benchmark scale (20 000 cfg3-shaped utterances, 45 audio-h,
+    10 GB arena generated on the device, several launch groups):
+      * independence - an utterance inside the big batch == the same utterance featurised alone,
+        bit for bit (first / last utterance of the batch and of launch groups, longest, shortest);
+      * gain invariance - scaling the audio by 2^-3 (exact in float32) moves lmfe by a constant
+        that cmvnw removes: outputs agree to 2e-5;
+      * oracle spot checks on the same utterances (1e-4)."""
+    import torch
+    lengths = synth.cfg3_lengths(20000, seed=3)
+    starts = np.zeros(len(lengths), dtype=np.int64)
+    np.cumsum((lengths[:-1] + 3) // 4 * 4, out=starts[1:])
+    total = int(starts[-1] + lengths[-1])
+    gen = torch.Generator(device="cuda")
+    gen.manual_seed(99)
+    arena = torch.empty(total, dtype=torch.float32, device="cuda")
+    for s in range(0, total, 1 << 28):
+        arena[s:s + (1 << 28)].normal_(0.0, 0.1, generator=gen)
+    fb = batch.FeatureBatch(starts, lengths)
+    assert fb.total_frames > 3 * 4 * 1024 * 1024          # more than three 4 Mi-row launch groups
+    out = torch.empty((fb.total_frames, 40), dtype=torch.float32, device="cuda")
+    torch.cuda.synchronize()
+    fb.lmfe_cmvnw_dev(arena.data_ptr(), total, out.data_ptr())
+    fb.ctx.sync()
+    assert bool(torch.isfinite(out).all())
+    fo = fb.frame_offsets
+    group_edge = int(np.searchsorted(fo, 4 * 1024 * 1024))  # utterance straddling the first group boundary
+    picks = sorted({0, len(lengths) - 1, group_edge - 1, group_edge, int(np.argmax(lengths)), int(np.argmin(lengths)), 7777})
+    for u in picks:
+        x = arena[starts[u]:starts[u] + lengths[u]].cpu().numpy()
+        alone = batch.lmfe_cmvnw([x])[0]
+        got = out[fo[u]:fo[u + 1]].cpu().numpy()
+        assert np.array_equal(got, alone), u
+        ref = o.cmvnw_vectorised(o.lmfe(x, FS), 301, True)
+        assert np.max(np.abs(got - ref)) < TOL, u
+    arena.mul_(0.125)
+    out2 = torch.empty_like(out)
+    torch.cuda.synchronize()
+    fb.lmfe_cmvnw_dev(arena.data_ptr(), total, out2.data_ptr())
+    fb.ctx.sync()
+    assert float((out - out2).abs().max()) < 2e-5
+    fb.close()
