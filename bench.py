@@ -290,6 +290,48 @@ def run_ours(args, rank, world, local_rank):
     # sanity: device path and host path agree bit for bit on the shared prefix
     same = bool(torch.equal(out[:fbe.total_frames].cpu(), h_out))
 
+    # ---- config 5 beside it (rank 0): the cosine score matrix on the tensor cores + EER
+    scoring_line = None
+    if rank == 0:
+        from speaker_verification_b200 import scoring
+        gen = torch.Generator(device=device)
+        gen.manual_seed(5)
+        m5 = n5 = 4874
+        d5 = 512
+        E5 = torch.randn((m5, d5), generator=gen, device=device)
+        T5 = torch.randn((n5, d5), generator=gen, device=device)
+        S5 = torch.empty((m5, n5), dtype=torch.float32, device=device)
+        for _ in range(3):
+            scoring.cosine_scores_dev(E5, T5, S5)
+        ctx.timing_enable(True)
+        for _ in range(10):
+            scoring.cosine_scores_dev(E5, T5, S5)
+        g_ms, g_n = ctx.timing_read(3)
+        ctx.timing_enable(False)
+        ti5 = torch.randint(0, m5, (37720,), generator=gen, device=device, dtype=torch.int64).to(torch.int32)
+        tj5 = torch.randint(0, n5, (37720,), generator=gen, device=device, dtype=torch.int64).to(torch.int32)
+        lab5 = (torch.rand(37720, generator=gen, device=device) < 0.5).to(torch.int32)
+        tr5 = scoring.trial_scores_dev(S5, ti5, tj5) + 0.05 * lab5
+        scoring.eer_auc_dev(tr5, lab5)
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        eer5, auc5 = scoring.eer_auc_dev(tr5, lab5)
+        eer_ms = (time.perf_counter() - t0) * 1e3
+        per = g_ms / max(g_n, 1) / 1e3
+        flops = 2.0 * m5 * n5 * d5
+        tf_peak = None
+        try:
+            with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as fh:
+                tf_peak = float(json.load(fh)["bf16_tflops"]) / 2.0  # TF32 runs at half the bf16 rate
+        except Exception:
+            pass
+        scoring_line = {"workload": "cfg5: cosine scores 4874 x 4874 x 512 (3xTF32 on tcgen05) + EER of 37720 trials",
+                        "gemm_us": per * 1e6, "useful_tflops": flops / per / 1e12,
+                        "issued_tf32_tflops": 3 * flops / per / 1e12,
+                        "tensor_frac_of_measured_bf16_over_2": (3 * flops / per / 1e12 / tf_peak) if tf_peak else None,
+                        "eer_call_ms": eer_ms, "eer": eer5, "auc": auc5}
+        del E5, T5, S5
+
     if rank == 0:
         peak, peak_src = peaks()
         feat_ms, feat_n = k_ms[0]
@@ -337,6 +379,8 @@ def run_ours(args, rank, world, local_rank):
             },
             "audio_hours_per_step_per_gpu": audio_h,
         }
+        if scoring_line is not None:
+            line["scoring"] = scoring_line
         if cpu_baseline is not None:
             line["cpu_baseline"] = cpu_baseline
         print(json.dumps(line), flush=True)
