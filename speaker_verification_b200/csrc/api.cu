@@ -797,8 +797,9 @@ static int check_batch(spb_context *ctx, const spb_batch *b, int64_t arena_len, 
   return SPB_OK;
 }
 
-// lmfe -> cmvnw over chunks of whole utterances; the lmfe and mean-subtracted
-// intermediates of a chunk live in two chunk-sized scratch buffers that stay in L2.
+// lmfe -> cmvnw of one run of whole utterances (a chunk of the host-pointer pipeline or a launch
+// group of the device-pointer path); the lmfe and mean-subtracted intermediates of the run live
+// in two scratch buffers sized for the largest run.
 static int lmfe_cmvnw_chunk(spb_context *ctx, const spb_batch *b, const BatchChunk &c,
                             const float *d_samples, int64_t arena_len, float *d_lmfe, float *d_ms,
                             float *d_out) {
