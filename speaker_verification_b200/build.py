@@ -25,7 +25,7 @@ SOURCES = ["api.cu", "feat_kernels.cu", "cmvn_kernels.cu", "misc_kernels.cu", "c
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
     "-Xcompiler", "-fPIC", "-Xcompiler", "-fvisibility=hidden",
-    "--expt-relaxed-constexpr", "-Wno-deprecated-gpu-targets",
+    "--expt-relaxed-constexpr", "-Wno-deprecated-gpu-targets", *os.environ.get("SPB_EXTRA_NVCC", "").split(),
 ]
 
 

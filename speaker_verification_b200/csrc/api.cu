@@ -522,7 +522,7 @@ int spb_plan_destroy(spb_plan *pl) {
 }
 
 // ------------------------------------------------------------------ batches
-static constexpr int kFftTile = 32;
+static constexpr int kFftTile = spb::kFftTileFrames;
 static constexpr int64_t kChunkRowsDefault = 192 * 1024;  // pipeline unit of the host-pointer calls (~30 MB of rows)
 static constexpr int64_t kGroupRowsDefault = 4 * 1024 * 1024;  // launch unit of the device-pointer calls
 // tuning knobs (read when a batch is created): SPB_CHUNK_ROWS, SPB_GROUP_ROWS, SPB_BIG_RMAX

@@ -95,9 +95,11 @@ __device__ __forceinline__ void output_stage(const FeatParams &p, const float *s
     // Segment form (triangular bank): lane = frame, each warp walks its run of whole
     // segments once; bin k feeds the rising sum of filter seg and the falling sum of filter
     // seg-1.  U[f][j] = rising sum of filter j, D[f][j] = falling sum of filter j-1.
-    const int lane = tid & 31, warp = tid >> 5;
+    // TILE consecutive threads (a warp, or a half-warp for 16-frame tiles) = the frames of the
+    // tile; each such group walks one of the 8 bin ranges
+    const int lane = tid % TILE, range = tid / TILE;
     const int upitch = (M + 2) | 1;
-    const int4 wr = s_wr[warp];
+    const int4 wr = s_wr[range];
     if (lane < nf) {
       const float *pp = s_p + lane * pstride + wr.x;
       const float4 *rd = s_rd + (wr.x - p.seg_kmin);
@@ -260,11 +262,12 @@ __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_gr
 // ====================================================================================
 // Fast kernel, NFFT = 512.
 // ====================================================================================
-constexpr int kTile = 32;        // frames per tile
-constexpr int kFastThreads = 256;
+constexpr int kNW = kFftWarps;            // warps per CTA
+constexpr int kTile = kFftTileFrames;     // frames per tile (two per half-warp)
+constexpr int kFastThreads = 32 * kNW;
 
 template <int NJ, bool FULL>
-__global__ void __launch_bounds__(kFastThreads, 2)
+__global__ void __launch_bounds__(kFastThreads, 16 / kNW)
 features_fast512(const FeatParams p) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   constexpr int PBINS = FULL ? 257 : 129;
@@ -277,7 +280,7 @@ features_fast512(const FeatParams p) {
   const int xoff = ((span_max + 3) & ~3);
   float *s_xbuf = reinterpret_cast<float *>(smem_raw);              // 2 x [xoff] sample stages
   float2 *s_exch = reinterpret_cast<float2 *>(s_xbuf + 2 * xoff);   // 16 half-warps x 256
-  float *s_p = reinterpret_cast<float *>(s_exch + 16 * 256);        // [kTile][PSTRIDE]
+  float *s_p = reinterpret_cast<float *>(s_exch + 2 * kNW * 256);        // [kTile][PSTRIDE]
   float *s_bw = s_p + kTile * PSTRIDE;                                 // [band_total] (16 B aligned)
   float *s_en = s_bw + p.band_total;                                // [kTile]
   float *s_a = s_en + kTile;                                        // [kTile][M+1]
@@ -303,7 +306,7 @@ features_fast512(const FeatParams p) {
     fm.dm = kFastThreads - fm.df * Mq;
   }
   const bool use_seg = p.seg_rd != nullptr && p.mode >= FEAT_MFE &&
-                       2 * kTile * ((p.M + 2) | 1) * 4 <= 16 * 256 * (int)sizeof(float2);
+                       2 * kTile * ((p.M + 2) | 1) * 4 <= 2 * kNW * 256 * (int)sizeof(float2);
 
   const int tid = threadIdx.x;
   const int warp = tid >> 5;
@@ -386,7 +389,7 @@ features_fast512(const FeatParams p) {
 
     // ---- phase B: each half-warp transforms two frames at once (packed fp32, fft_math2.cuh)
     {
-      const int flA = 2 * (warp + 8 * half), flB = flA + 1;
+      const int flA = 2 * (warp + kNW * half), flB = flA + 1;
       const bool actA = flA < nf, actB = flB < nf;
       const float *xa = s_x + (actA ? flA : 0) * S;
       const float *xb = s_x + (actB ? flB : 0) * S;
@@ -665,7 +668,7 @@ bool fast512_supported(const FeatArgs &a) {
 template <int NJ, bool FULL>
 static int launch_fast(spb_context *ctx, const FeatParams &p, const FeatArgs &a) {
   const int span_max = (kTile - 1) * a.S + a.L;
-  size_t smem = 2 * (size_t)((span_max + 3) & ~3) * 4 + 16 * 256 * sizeof(float2) +
+  size_t smem = 2 * (size_t)((span_max + 3) & ~3) * 4 + 2 * kNW * 256 * sizeof(float2) +
                 (size_t)kTile * ((FULL ? 257 : 129) + 4) * 4 + plan_smem_bytes(a, kTile) +
                 16 + (size_t)a.seg_nbins * 16 + 8 * 16 + (256 + 128) * sizeof(float2);
   auto kern = features_fast512<NJ, FULL>;

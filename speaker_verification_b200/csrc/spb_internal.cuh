@@ -10,7 +10,13 @@
 
 #include "speechpy_b200.h"
 
+#ifndef SPB_FFT_NW
+#define SPB_FFT_NW 8   // warps per CTA of the NFFT-512 feature kernel; a tile is 4 frames per warp
+#endif
+
 namespace spb {
+constexpr int kFftWarps = SPB_FFT_NW;
+constexpr int kFftTileFrames = 4 * kFftWarps;
 
 // ---------------------------------------------------------------- errors
 void set_global_error(const std::string &msg);
