@@ -89,24 +89,28 @@ __global__ void cube_stats_kernel(const float *__restrict__ lmfe, const int64_t 
 // once (coalesced), every channel is derived from the staged rows and stored coalesced.
 __global__ void cube_gather_kernel(const float *__restrict__ lmfe, const int64_t *__restrict__ frame_offsets,
                                    const int32_t *__restrict__ crop_starts, const double2 *__restrict__ stats,
-                                   int M, int channels, int num_crops, int crop_frames, float *__restrict__ out) {
+                                   long long U, int M, int channels, int num_crops, int crop_frames,
+                                   float *__restrict__ out) {
   extern __shared__ float s_crop[];  // [crop_frames][M]
-  const int k = blockIdx.x, u = blockIdx.y;
-  const long long r0 = frame_offsets[u] + crop_starts[(long long)u * num_crops + k];
+  const int k = blockIdx.x;
   const int per_ch = crop_frames * M;
-  const float *src = lmfe + r0 * M;
-  for (int i = threadIdx.x; i < per_ch; i += blockDim.x) s_crop[i] = src[i];
-  __syncthreads();
-  for (int i = threadIdx.x; i < per_ch; i += blockDim.x) {
-    const int t = i / M, c = i - t * M;
-    const float *row = s_crop + t * M;
-    for (int ch = 0; ch < channels; ++ch) {
-      float v = channel_value(row, c, ch, M);
-      if (stats) {
-        const double2 ms = stats[((long long)u * channels + ch) * M + c];
-        v = (v - (float)ms.x) * (float)ms.y;  // float32 like the cube; |error| ~1e-6 of an O(1) value
+  for (long long u = blockIdx.y; u < U; u += gridDim.y) {  // gridDim.y <= 65535
+    const long long r0 = frame_offsets[u] + crop_starts[u * num_crops + k];
+    const float *src = lmfe + r0 * M;
+    __syncthreads();  // previous utterance's crop fully consumed
+    for (int i = threadIdx.x; i < per_ch; i += blockDim.x) s_crop[i] = src[i];
+    __syncthreads();
+    for (int i = threadIdx.x; i < per_ch; i += blockDim.x) {
+      const int t = i / M, c = i - t * M;
+      const float *row = s_crop + t * M;
+      for (int ch = 0; ch < channels; ++ch) {
+        float v = channel_value(row, c, ch, M);
+        if (stats) {
+          const double2 ms = stats[(u * channels + ch) * M + c];
+          v = (v - (float)ms.x) * (float)ms.y;  // float32 like the cube; |error| ~1e-6 of an O(1) value
+        }
+        out[((u * channels + ch) * num_crops + k) * per_ch + i] = v;
       }
-      out[(((long long)u * channels + ch) * num_crops + k) * per_ch + i] = v;
     }
   }
 }
@@ -117,7 +121,6 @@ int launch_feature_cubes(spb_context *ctx, const float *d_lmfe, const int64_t *d
   if (U <= 0 || num_crops <= 0) return SPB_OK;
   const int cols = M * channels;
   if (cols * kStatSlices > 1024) return fail(ctx, SPB_ERR_UNSUPPORTED, "feature cubes: num_filters * channels > 256");
-  if (U > 65535) return fail(ctx, SPB_ERR_UNSUPPORTED, "feature cubes: more than 65535 utterances per call");
   if ((size_t)crop_frames * M * sizeof(float) > 48 * 1024)
     return fail(ctx, SPB_ERR_UNSUPPORTED, "feature cubes: crop_frames * num_filters > 12288");
   if (normalize) {
@@ -127,9 +130,10 @@ int launch_feature_cubes(spb_context *ctx, const float *d_lmfe, const int64_t *d
         d_lmfe, d_frame_offsets, M, channels, d_stats);
     SPB_LAUNCH_CHECK(ctx, "cube_stats_kernel");
   }
-  dim3 grid((unsigned)num_crops, (unsigned)U);
+  if (num_crops > 65535 * 32) return fail(ctx, SPB_ERR_UNSUPPORTED, "feature cubes: too many crops per utterance");
+  dim3 grid((unsigned)num_crops, (unsigned)std::min<int64_t>(U, 65535));
   cube_gather_kernel<<<grid, 256, (size_t)crop_frames * M * sizeof(float), ctx->stream>>>(d_lmfe, d_frame_offsets, d_crop_starts,
-                                                     normalize ? d_stats : nullptr, M, channels, num_crops,
+                                                     normalize ? d_stats : nullptr, (long long)U, M, channels, num_crops,
                                                      crop_frames, d_out);
   SPB_LAUNCH_CHECK(ctx, "cube_gather_kernel");
   return SPB_OK;

@@ -287,3 +287,25 @@ def test_full_size_properties_cfg3_scale(sp):
     fb.ctx.sync()
     assert float((out - out2).abs().max()) < 2e-5
     fb.close()
+
+
+def test_feature_cubes_many_utterances(sp):
+    """More utterances than a CUDA grid dimension (65535): the gather kernel strides over them."""
+    import torch
+    U, n = 70000, 13440                      # 82 frames each
+    starts = np.arange(U, dtype=np.int64) * n
+    lens = np.full(U, n, dtype=np.int64)
+    gen = torch.Generator(device="cuda")
+    gen.manual_seed(3)
+    arena = torch.empty(U * n, dtype=torch.float32, device="cuda").normal_(0.0, 0.1, generator=gen)
+    fb = batch.FeatureBatch(starts, lens)
+    crops = np.random.RandomState(2).randint(82 - 80, size=(U, 2)).astype(np.int32)
+    out = torch.empty((U, 3, 2, 80, 40), dtype=torch.float32, device="cuda")
+    torch.cuda.synchronize()
+    fb.feature_cubes_dev(arena.data_ptr(), arena.numel(), out.data_ptr(), crops, derivative=True, normalize=True)
+    fb.ctx.sync()
+    for u in (0, 65534, 65535, 65536, U - 1):
+        x = arena[u * n:(u + 1) * n].cpu().numpy()
+        feat = o.cmvn_transform(o.lmfe(x, FS), True, True)
+        assert np.max(np.abs(out[u].cpu().numpy() - o.feature_cube(feat, crops[u], 80))) < TOL, u
+    fb.close()
