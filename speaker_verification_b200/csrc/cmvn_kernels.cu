@@ -338,7 +338,8 @@ cmvnw_big_kernel(const CmBigParams p) {
   const size_t s_bytes = ((size_t)rows_ext_max * cols * 4 + 15) & ~(size_t)15;
   double *bs1 = reinterpret_cast<double *>(smem_raw + s_bytes);
   double *bs2 = bs1 + (size_t)nblk_max * cols;
-  __shared__ int s_tile;
+  __shared__ int4 s_desc[2];
+  __shared__ long long s_base[2];
   __shared__ __align__(8) uint64_t s_bar;
   const int tid = threadIdx.x;
   const int warp = tid >> 5, lane = tid & 31;
@@ -356,16 +357,30 @@ cmvnw_big_kernel(const CmBigParams p) {
   const double inv_win = 1.0 / (double)win;
   const int n4 = cols >> 2;  // cols % 4 == 0 (checked by the launcher)
 
-  for (;;) {
-    __syncthreads();  // previous tile fully consumed (smem and s_tile)
-    if (tid == 0) s_tile = atomicAdd(p.counter, 1);
-    __syncthreads();
-    const int tile = s_tile;
-    if (tile >= p.num_tiles) break;
-    const int4 td = p.tiles[tile];
+  // Tile descriptors are fetched one tile ahead by a single thread (atomic ticket + three dependent
+  // global loads, ~2 us of latency) while the CTA works on the current tile.
+  auto fetch_desc = [&](int slot) {
+    const int t = atomicAdd(p.counter, 1);
+    int4 d = make_int4(-1, 0, 0, 0);
+    long long b = 0;
+    if (t < p.num_tiles) {
+      const int4 td = p.tiles[t];
+      d = make_int4(td.x, td.y, td.z, p.nframes[td.x]);
+      b = p.frame_offsets[td.x];
+    }
+    s_desc[slot] = d;
+    s_base[slot] = b;
+  };
+  if (tid == 0) fetch_desc(0);
+  for (int slot = 0;; slot ^= 1) {
+    __syncthreads();  // previous tile fully consumed; descriptor `slot` published
+    const int4 td = s_desc[slot];
+    if (td.x < 0) break;
+    if (tid == kBigThreads - 1) fetch_desc(slot ^ 1);  // overlaps with this tile's work
     const int utt = td.x, r0 = td.y, nrows = td.z;
-    const int F = p.nframes[utt];
-    const long long base = p.frame_offsets[utt];
+    const int F = td.w;
+    const long long base = s_base[slot];
+    (void)utt;
     const int rows_needed = nrows + win - 1;
     const int first = r0 - h;
     // ---- stage: ext row e <-> utterance row first + e; interior = [e_lo, e_hi)
