@@ -342,10 +342,18 @@ features_fast512(const FeatParams p) {
   }
   __syncthreads();
   uint32_t ph0 = 0, ph1 = 0;
-  auto stage = [&](long long t, int b, long long &row0, int &nf, bool &bulk) {
-    // one 32-byte descriptor per tile (two 16-byte loads, no dependent chain)
-    const int4 d0 = __ldg(reinterpret_cast<const int4 *>(p.ftiles + t));
-    const longlong2 d1 = __ldg(reinterpret_cast<const longlong2 *>(p.ftiles + t) + 1);
+  // 32-byte tile descriptors travel through a two-slot shared-memory ring, filled two tiles ahead
+  // by thread 0 with cp.async (no register dependency, so nobody stalls on the L2 round trip)
+  __shared__ __align__(16) int4 s_fd[2][2];
+  auto fetch_desc = [&](long long t, int slot) {  // thread 0 only
+    const int4 *src = reinterpret_cast<const int4 *>(p.ftiles + t);
+    cp_async16(&s_fd[slot][0], src);
+    cp_async16(&s_fd[slot][1], src + 1);
+    cp_async_commit();
+  };
+  auto stage = [&](int slot, int b, long long &row0, int &nf, bool &bulk) {
+    const int4 d0 = s_fd[slot][0];
+    const longlong2 d1 = *reinterpret_cast<const longlong2 *>(&s_fd[slot][1]);
     nf = d0.z;
     const long long gstart = d1.x;
     row0 = d1.y;
@@ -371,15 +379,25 @@ features_fast512(const FeatParams p) {
   long long row0 = 0;
   int nf = 0;
   bool bulk = false;
-  if (tile < p.num_tiles) stage(tile, 0, row0, nf, bulk);
-  for (; tile < p.num_tiles; buf ^= 1) {
+  if (tid == 0) {
+    if (tile < p.num_tiles) fetch_desc(tile, 0);
+    if (tile + gridDim.x < p.num_tiles) fetch_desc(tile + gridDim.x, 1);
+    cp_async_wait<0>();
+  }
+  __syncthreads();
+  if (tile < p.num_tiles) stage(0, 0, row0, nf, bulk);
+  for (; tile < p.num_tiles; buf ^= 1) {  // descriptor of the tile in sample buffer b sits in ring slot b
     const long long next = tile + gridDim.x;
     long long n_row0 = 0;
     int n_nf = 0;
     bool n_bulk = false;
     // prefetch the next tile while this one is transformed (its buffer was last read in
     // phase B of the previous iteration, which every thread has left)
-    if (next < p.num_tiles) stage(next, buf ^ 1, n_row0, n_nf, n_bulk);
+    if (next < p.num_tiles) stage(buf ^ 1, buf ^ 1, n_row0, n_nf, n_bulk);
+    // slot `buf` (this tile's descriptor, consumed an iteration ago) takes the tile after next;
+    // thread 0 waits for it just before the barrier that ends phase B
+    const bool refill = tid == 0 && next + gridDim.x < p.num_tiles;
+    if (refill) fetch_desc(next + gridDim.x, buf);
     if (bulk) {
       if (buf == 0) { mbar_wait(&s_full[0], ph0); ph0 ^= 1; }
       else { mbar_wait(&s_full[1], ph1); ph1 ^= 1; }
@@ -504,6 +522,7 @@ features_fast512(const FeatParams p) {
         }
       }
     }
+    if (refill) cp_async_wait<0>();
     __syncthreads();
     // ---- phase C
     if (use_seg && p.mode == FEAT_LMFE)
