@@ -370,6 +370,15 @@ cmvnw_big_kernel(const CmBigParams p) {
     }
     s_desc[slot] = d;
     s_base[slot] = b;
+    if (d.x >= 0 && ld == cols) {
+      // pull the next tile's rows (interior and non-reflected halo) into L2 while this tile is
+      // being processed: its bulk copies then stream from L2 instead of waiting on HBM
+      const int h2 = (win - 1) >> 1;
+      const int lo = max(d.y - h2, 0), hi = min(d.y + d.z + h2, d.w);
+      const char *src = reinterpret_cast<const char *>(p.in + (b + lo) * (long long)cols);
+      const uint32_t total = (uint32_t)(hi - lo) * (uint32_t)cols * 4u;
+      for (uint32_t off = 0; off < total; off += 65536u) bulk_prefetch_l2(src + off, min(65536u, total - off));
+    }
   };
   if (tid == 0) fetch_desc(0);
   for (int slot = 0;; slot ^= 1) {

@@ -93,4 +93,9 @@ __device__ __forceinline__ void bulk_load(void *dst, const void *src, uint32_t b
                : "memory");
 }
 
+// Ask the TMA engine to pull [src, src + bytes) into L2 (bytes and src multiples of 16).
+__device__ __forceinline__ void bulk_prefetch_l2(const void *src, uint32_t bytes) {
+  asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(src), "r"(bytes) : "memory");
+}
+
 }  // namespace spb
