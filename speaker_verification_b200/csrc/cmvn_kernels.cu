@@ -423,11 +423,26 @@ cmvnw_big_kernel(const CmBigParams p) {
       const int rpp = 32 / n4 > 0 ? 32 / n4 : 1;
       const int lr = lane / n4, lc = lane - lr * n4;
       if (n4 <= 32 && lr < rpp) {
-        for (int k = warp * rpp + lr; k < nh; k += kWarps * rpp) {
-          const int e = (k < nh_lo) ? k : max(e_hi, e_lo) + (k - nh_lo);
-          const int srow = reflect_row32(first + e, F);
-          reinterpret_cast<float4 *>(s + (size_t)e * cols)[lc] =
-              __ldg(reinterpret_cast<const float4 *>(p.in + (base + srow) * (long long)ld) + lc);
+        // batches of six rows per thread: all loads of a batch are issued before the first store,
+        // so their L2 latencies overlap instead of adding up
+        constexpr int kHB = 6;
+        for (int k0 = warp * rpp + lr; k0 < nh; k0 += kHB * kWarps * rpp) {
+          float4 v[kHB];
+          int ee[kHB];
+#pragma unroll
+          for (int i = 0; i < kHB; ++i) {
+            const int k = k0 + i * kWarps * rpp;
+            ee[i] = -1;
+            if (k < nh) {
+              const int e = (k < nh_lo) ? k : max(e_hi, e_lo) + (k - nh_lo);
+              const int srow = reflect_row32(first + e, F);
+              ee[i] = e;
+              v[i] = __ldg(reinterpret_cast<const float4 *>(p.in + (base + srow) * (long long)ld) + lc);
+            }
+          }
+#pragma unroll
+          for (int i = 0; i < kHB; ++i)
+            if (ee[i] >= 0) reinterpret_cast<float4 *>(s + (size_t)ee[i] * cols)[lc] = v[i];
         }
       } else if (n4 > 32) {
         for (int k = warp; k < nh; k += kWarps) {
