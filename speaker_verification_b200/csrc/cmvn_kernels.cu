@@ -324,6 +324,17 @@ struct CmBigParams {
   float eps;
 };
 
+// float -> double with integer instructions: exact for normal numbers; zero and denormals come
+// out as +-2^-127-sized values (far below anything these sums resolve); inf / nan map to huge
+// finite values of the same sign.  F2F.F64.F32 runs on the 16-lane XU pipe, which bounds the
+// block-sum phase (2 conversions x 640 threads per row = 80 clocks); doing every other
+// conversion on the integer pipe lets the two pipes work in parallel.
+__device__ __forceinline__ double f2d_alu(float f) {
+  const unsigned u = __float_as_uint(f);
+  const unsigned hi = (((u & 0x7fffffffu) >> 3) + 0x38000000u) | (u & 0x80000000u);
+  return __hiloint2double((int)hi, (int)(u << 29));
+}
+
 template <int STAGE, int COLS>
 __global__ void __launch_bounds__(kBigThreads, 1)
 cmvnw_big_kernel(const CmBigParams p) {
@@ -469,7 +480,7 @@ cmvnw_big_kernel(const CmBigParams p) {
 #pragma unroll 10
         for (int r = 0; r < kBigG; ++r) {
           const float2 x = *reinterpret_cast<const float2 *>(col + r * cols);
-          const double dx = (double)x.x, dy = (double)x.y;
+          const double dx = (double)x.x, dy = f2d_alu(x.y);  // one conversion per pipe (XU / integer)
           a1x += dx; a1y += dy;
           if (STAGE == 2) { a2x = fma(dx, dx, a2x); a2y = fma(dy, dy, a2y); }
         }
