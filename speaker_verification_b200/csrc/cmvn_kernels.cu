@@ -214,7 +214,7 @@ cmvnw_kernel(const CmParams p) {
               // processing.py:318-322: ms / (std(window) + eps), population std
               const double mean = w1[v] * inv_win;
               double var = fma(-mean, mean, w2[v] * inv_win);
-              var = var > 0.0 ? var : 0.0;
+              var = var < 0.0 ? 0.0 : var;  // select, not fmax: a NaN variance must stay NaN
               o[v] = xc[v] / (sqrtf((float)var) + p.eps);
             }
           }
@@ -325,13 +325,14 @@ struct CmBigParams {
 };
 
 // float -> double with integer instructions: exact for normal numbers; zero and denormals come
-// out as +-2^-127-sized values (far below anything these sums resolve); inf / nan map to huge
-// finite values of the same sign.  F2F.F64.F32 runs on the 16-lane XU pipe, which bounds the
+// out as +-2^-127-sized values (far below anything these sums resolve); inf / nan stay inf / nan.  F2F.F64.F32 runs on the 16-lane XU pipe, which bounds the
 // block-sum phase (2 conversions x 640 threads per row = 80 clocks); doing every other
 // conversion on the integer pipe lets the two pipes work in parallel.
 __device__ __forceinline__ double f2d_alu(float f) {
   const unsigned u = __float_as_uint(f);
-  const unsigned hi = (((u & 0x7fffffffu) >> 3) + 0x38000000u) | (u & 0x80000000u);
+  const unsigned a = u & 0x7fffffffu;
+  unsigned hi = ((a >> 3) + 0x38000000u) | (u & 0x80000000u);
+  if (a >= 0x7f800000u) hi |= 0x7ff00000u;  // inf / nan keep their class (one predicated LOP3)
   return __hiloint2double((int)hi, (int)(u << 29));
 }
 
@@ -551,8 +552,10 @@ cmvnw_big_kernel(const CmBigParams p) {
             const float mx = mhx + fmaf(Dx, inv_w, mlx), my = mhy + fmaf(Dy, inv_w, mly);
             const float vx = fmaf(-mx, mx, fmaf(Qx, inv_w, e0x)), vy = fmaf(-my, my, fmaf(Qy, inv_w, e0y));
             float sx, sy;
-            asm("sqrt.approx.f32 %0, %1;" : "=f"(sx) : "f"(fmaxf(vx, 0.f)));
-            asm("sqrt.approx.f32 %0, %1;" : "=f"(sy) : "f"(fmaxf(vy, 0.f)));
+            // clamp rounding-negative variances with a select: fmaxf would swallow a NaN variance
+            // (a NaN anywhere in the window must poison the row, processing.py:318-322)
+            asm("sqrt.approx.f32 %0, %1;" : "=f"(sx) : "f"(vx < 0.f ? 0.f : vx));
+            asm("sqrt.approx.f32 %0, %1;" : "=f"(sy) : "f"(vy < 0.f ? 0.f : vy));
             float2 o;
             o.x = __fdividef(xc.x, sx + p.eps);
             o.y = __fdividef(xc.y, sy + p.eps);

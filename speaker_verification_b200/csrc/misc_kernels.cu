@@ -218,10 +218,15 @@ int launch_preemphasis(spb_context *ctx, const void *in, int dtype, long long n,
 // log10 is monotonic, so the maximum of the logs is the log of the maximum power.
 __global__ void max_f32_kernel(const float *__restrict__ p, long long n, unsigned int *__restrict__ out_bits) {
   float m = 0.f;  // powers are >= 0
+  bool bad = false;  // np.max propagates NaN (processing.py:196); fmaxf would drop it
   for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n;
-       i += (long long)gridDim.x * blockDim.x)
-    m = fmaxf(m, p[i]);
+       i += (long long)gridDim.x * blockDim.x) {
+    const float v = p[i];
+    bad |= (v != v);
+    m = fmaxf(m, v);
+  }
   for (int o = 16; o; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
+  if (__any_sync(0xffffffffu, bad)) m = __uint_as_float(0x7fc00000u);  // orders above every finite value as uint
   if ((threadIdx.x & 31) == 0) atomicMax(out_bits, __float_as_uint(m));  // non-negative floats order like uints
 }
 

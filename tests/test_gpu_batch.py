@@ -309,3 +309,30 @@ def test_feature_cubes_many_utterances(sp):
         feat = o.cmvn_transform(o.lmfe(x, FS), True, True)
         assert np.max(np.abs(out[u].cpu().numpy() - o.feature_cube(feat, crops[u], 80))) < TOL, u
     fb.close()
+
+
+def test_nan_samples_poison_the_window_like_the_reference(sp):
+    """A NaN sample makes its frames NaN and, through the window mean / std, every cmvnw row whose
+    window touches them (processing.py:302-322) -- in every column (the block sums convert half of
+    the columns with integer instructions, and the variance clamp is a select: both keep NaN).
+    Known deviation: the sliding sums are re-anchored every 30 rows (15 in the small-tile kernels),
+    so a NaN that has left the window can poison up to 29 further rows; never fewer rows than the
+    reference."""
+    x = synth.audio(5, 64000, np.float32)
+    x[32000] = np.nan
+    arena, starts, lens = batch.pack([x])
+    lm = o.lmfe(x, FS)
+    assert np.isnan(lm).any(axis=1).sum() == 2
+    for vn in (True, False):
+        ref = o.cmvnw_vectorised(lm, 301, vn)
+        fb = batch.FeatureBatch(starts, lens, variance_normalization=vn)
+        for got in (fb.lmfe_cmvnw(arena), sp.processing.cmvnw(lm, 301, vn)):  # large- / small-tile kernels
+            gn, rn = np.isnan(got), np.isnan(ref)
+            assert np.all(gn[rn])                                     # every reference NaN is a NaN here
+            extra = (gn & ~rn).any(axis=1)
+            assert extra.sum() <= 29 and (not extra.any() or np.flatnonzero(extra).min() > np.flatnonzero(rn.any(axis=1)).max())
+            ok = ~gn
+            if ok.any():
+                assert np.max(np.abs(got[ok] - ref[ok])) < TOL
+        fb.close()
+    assert np.isnan(o.cmvnw_vectorised(lm, 301, True)).all()          # variance mode: +-300 rows cover this utterance
