@@ -782,8 +782,9 @@ static int run_features(spb_context *ctx, FeatArgs &a) {
   int rc = get_fft_tables(ctx, a.nfft, &t);
   if (rc) return rc;
   const size_t tb = timing_begin(ctx);
-  rc = (!g_force_generic && fast512_supported(a)) ? launch_features_fast512(ctx, a, t)
-                                                  : launch_features_generic(ctx, a, t);
+  if (!g_force_generic && fast512_supported(a)) rc = launch_features_fast512(ctx, a, t);
+  else if (!g_force_generic && fast1024_supported(a)) rc = launch_features_fast1024(ctx, a, t);
+  else rc = launch_features_generic(ctx, a, t);
   timing_end(ctx, 0, tb);
   return rc;
 }

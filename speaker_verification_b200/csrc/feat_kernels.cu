@@ -99,8 +99,8 @@ __device__ __forceinline__ void output_stage(const FeatParams &p, const float *s
     // tile; each such group walks one of the 8 bin ranges
     const int lane = tid % TILE, range = tid / TILE;
     const int upitch = (M + 2) | 1;
-    const int4 wr = s_wr[range];
-    if (lane < nf) {
+    const int4 wr = s_wr[range < 8 ? range : 0];
+    if (range < 8 && lane < nf) {
       const float *pp = s_p + lane * pstride + wr.x;
       const float4 *rd = s_rd + (wr.x - p.seg_kmin);
       float *pu = s_U + lane * upitch + wr.z;
@@ -540,6 +540,239 @@ features_fast512(const FeatParams p) {
 }
 
 // ====================================================================================
+// Fast kernel, NFFT = 1024: the reference's own call (load_data.py:64-70 with constants.py:
+// FRAME_LEN 0.025 -> L = 400, FRAME_STEP 0.01, NUM_FFT 1024, NUM_COEF 40).
+//
+// Same pipeline as features_fast512 (TMA-staged sample tiles, descriptor ring, P rows in shared
+// memory, segment-form mel, direct stores); the transform is one frame per WARP:
+//   z[n] = x[2n] + i x[2n+1], n = 32 j + l (l = lane): 16-point register FFT over j (inputs
+//   j >= NZ are zero: L <= 448 -> NZ = 7), twiddle W512^(l k1), exchange through shared memory
+//   so that lane (k1, b) holds the 16 values l = 2a + b, 16-point FFT over a, and one radix-2
+//   step across the two half-warps (shuffle) -> lane (k1, s) holds Z[k1 + 16 q + 256 s].
+//   Real-FFT untangle for bins 0..256 (speechpy's (K+1) bin mapping stops at bin 256 here): the
+//   lower half-warp owns them, partners Z[512 - k] come from the upper half by shuffles with
+//   static register indices.  Index algebra checked against numpy in tests/host.
+// 16 warps per CTA (two passes per 32-frame tile), one CTA per SM.
+// ====================================================================================
+constexpr int kF1kWarps = 16;
+constexpr int kF1kThreads = 32 * kF1kWarps;
+constexpr int kF1kRS = 34;  // exchange row stride (float2): the 16 rows a read touches spread over all banks
+
+template <int NZ>
+__global__ void __launch_bounds__(kF1kThreads, 1)
+features_fast1024(const FeatParams p) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  constexpr int PBINS = 257;
+  constexpr int PSTRIDE = PBINS + 4;  // 261 == 5 (mod 32): lane = frame column reads are conflict-free
+  const int L = p.L, S = p.S;
+  const int span_max = (kTile - 1) * S + L;
+  const int xoff = ((span_max + 3) & ~3);
+  float *s_xbuf = reinterpret_cast<float *>(smem_raw);                      // 2 x [xoff]
+  float2 *s_exch = reinterpret_cast<float2 *>(s_xbuf + 2 * xoff);           // [kF1kWarps][16][kF1kRS]
+  float *s_p = reinterpret_cast<float *>(s_exch + kF1kWarps * 16 * kF1kRS); // [kTile][PSTRIDE]
+  float *s_bw = s_p + kTile * PSTRIDE;
+  float *s_en = s_bw + p.band_total;
+  float *s_a = s_en + kTile;
+  float *s_b = s_a + kTile * (p.M + 1);
+  float *s_dct = s_b + kTile * (p.C + 1);
+  int *s_bmeta = reinterpret_cast<int *>(s_dct + p.C * p.M);
+  const int used_floats = (int)(reinterpret_cast<float *>(s_bmeta + 3 * p.M) - reinterpret_cast<float *>(smem_raw));
+  float4 *s_rd = reinterpret_cast<float4 *>(reinterpret_cast<float *>(smem_raw) + ((used_floats + 3) & ~3));
+  int4 *s_wr = reinterpret_cast<int4 *>(s_rd + p.seg_nbins);
+  float2 *s_tw1 = reinterpret_cast<float2 *>(s_wr + 8);  // [16][32]  W512^(l k1) at k1 * 32 + l
+  float2 *s_tw2 = s_tw1 + 512;                           // [16][16]  W1024^(k1 + 16 q) at q * 16 + k1
+  float2 *s_tw3 = s_tw2 + 256;                           // [16]      W32^q
+  float *s_U = reinterpret_cast<float *>(s_exch);        // [kTile][(M+2)|1], aliases the exchange buffer
+  float *s_D = s_U + kTile * ((p.M + 2) | 1);
+  FmIndex fm;
+  {
+    const int Mq = p.M > 0 ? p.M : 1;
+    fm.f0 = tid0_div(threadIdx.x, Mq);
+    fm.m0 = threadIdx.x - fm.f0 * Mq;
+    fm.df = kF1kThreads / Mq;
+    fm.dm = kF1kThreads - fm.df * Mq;
+  }
+  const bool use_seg = p.seg_rd != nullptr && p.mode >= FEAT_MFE &&
+                       2 * kTile * ((p.M + 2) | 1) * 4 <= kF1kWarps * 16 * kF1kRS * (int)sizeof(float2);
+  const int tid = threadIdx.x;
+  const int warp = tid >> 5;
+  const int lane = tid & 31;
+  const int k1r = lane & 15, hb = lane >> 4;
+  float2 *my_exch = s_exch + warp * 16 * kF1kRS;
+
+  load_plan_to_smem(p, s_bw, s_bmeta, s_dct);
+  if (use_seg) {
+    for (int i = tid; i < p.seg_nbins; i += kF1kThreads) s_rd[i] = p.seg_rd[i];
+    if (tid < 8) s_wr[tid] = p.seg_ranges[tid];
+  }
+  for (int i = tid; i < kTile * 4; i += kF1kThreads) s_p[(i >> 2) * PSTRIDE + PBINS + (i & 3)] = 0.f;
+  // twiddles (float64 sincospi once per CTA; the kernel is persistent)
+  for (int i = tid; i < 512 + 256 + 16; i += kF1kThreads) {
+    double ang;  // in units of pi
+    if (i < 512) ang = -(double)((i & 31) * (i >> 5)) / 256.0;
+    else if (i < 768) ang = -(double)(((i - 512) & 15) + 16 * ((i - 512) >> 4)) / 512.0;
+    else ang = -(double)(i - 768) / 16.0;
+    double sn, cs;
+    sincospi(ang, &sn, &cs);
+    s_tw1[i] = make_float2((float)cs, (float)sn);  // the three tables are contiguous
+  }
+  const int Leff = min(L, 1024);
+
+  __shared__ __align__(8) uint64_t s_full[2];
+  if (tid == 0) {
+    mbar_init(&s_full[0], 1);
+    mbar_init(&s_full[1], 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncthreads();
+  uint32_t ph0 = 0, ph1 = 0;
+  __shared__ __align__(16) int4 s_fd[2][2];
+  auto fetch_desc = [&](long long t, int slot) {  // thread 0 only
+    const int4 *src = reinterpret_cast<const int4 *>(p.ftiles + t);
+    cp_async16(&s_fd[slot][0], src);
+    cp_async16(&s_fd[slot][1], src + 1);
+    cp_async_commit();
+  };
+  auto stage = [&](int slot, int b, long long &row0, int &nf, bool &bulk) {
+    const int4 d0 = s_fd[slot][0];
+    const longlong2 d1 = *reinterpret_cast<const longlong2 *>(&s_fd[slot][1]);
+    nf = d0.z;
+    const long long gstart = d1.x;
+    row0 = d1.y;
+    const int count = (nf - 1) * S + L;
+    const float *src = p.samples + gstart;
+    float *dst = s_xbuf + b * xoff;
+    bulk = ((gstart & 3) == 0) && count >= 4;
+    if (bulk) {
+      const int n4 = count >> 2;
+      if (tid == 0) {
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        mbar_expect_tx(&s_full[b], (uint32_t)n4 * 16u);
+        bulk_load(dst, src, (uint32_t)n4 * 16u, &s_full[b]);
+      }
+      for (int i = (n4 << 2) + tid; i < count; i += kF1kThreads) dst[i] = __ldg(src + i);
+    } else {
+      for (int i = tid; i < count; i += kF1kThreads) dst[i] = __ldg(src + i);
+    }
+  };
+
+  long long tile = blockIdx.x;
+  int buf = 0;
+  long long row0 = 0;
+  int nf = 0;
+  bool bulk = false;
+  if (tid == 0) {
+    if (tile < p.num_tiles) fetch_desc(tile, 0);
+    if (tile + gridDim.x < p.num_tiles) fetch_desc(tile + gridDim.x, 1);
+    cp_async_wait<0>();
+  }
+  __syncthreads();
+  if (tile < p.num_tiles) stage(0, 0, row0, nf, bulk);
+  for (; tile < p.num_tiles; buf ^= 1) {
+    const long long next = tile + gridDim.x;
+    long long n_row0 = 0;
+    int n_nf = 0;
+    bool n_bulk = false;
+    if (next < p.num_tiles) stage(buf ^ 1, buf ^ 1, n_row0, n_nf, n_bulk);
+    const bool refill = tid == 0 && next + gridDim.x < p.num_tiles;
+    if (refill) fetch_desc(next + gridDim.x, buf);
+    if (bulk) {
+      if (buf == 0) { mbar_wait(&s_full[0], ph0); ph0 ^= 1; }
+      else { mbar_wait(&s_full[1], ph1); ph1 ^= 1; }
+    }
+    __syncthreads();  // samples of this tile visible; previous tile's phase C is finished
+    const float *s_x = s_xbuf + buf * xoff;
+
+    // ---- phase B: one frame per warp and pass
+    for (int pass = 0; pass < kTile / kF1kWarps; ++pass) {
+      const int fl = pass * kF1kWarps + warp;
+      if (fl >= nf) continue;  // warp-uniform
+      const float *xf = s_x + fl * S;
+      float2 v[16];
+#pragma unroll
+      for (int j = 0; j < 16; ++j) {
+        if (j < NZ) {
+          const int o = 64 * j + 2 * lane;
+          v[j] = c_make(o < Leff ? xf[o] : 0.f, o + 1 < Leff ? xf[o + 1] : 0.f);
+        } else {
+          v[j] = c_make(0.f, 0.f);
+        }
+      }
+      float sumsq = 0.f;
+      if (p.need_energy) {
+#pragma unroll
+        for (int j = 0; j < 16; ++j)
+          if (j < NZ) sumsq = fmaf(v[j].x, v[j].x, fmaf(v[j].y, v[j].y, sumsq));
+      }
+      fft16<NZ>(v);  // over j -> k1
+#pragma unroll
+      for (int k1 = 1; k1 < 16; ++k1) v[k1] = c_mul(v[k1], s_tw1[k1 * 32 + lane]);
+      __syncwarp();  // the previous pass's reads of my_exch are done
+#pragma unroll
+      for (int k1 = 0; k1 < 16; ++k1) my_exch[k1 * kF1kRS + lane] = v[k1];
+      __syncwarp();
+#pragma unroll
+      for (int a = 0; a < 16; ++a) v[a] = my_exch[k1r * kF1kRS + 2 * a + hb];
+      fft16<16>(v);  // over a -> q
+      if (hb) {
+#pragma unroll
+        for (int q = 1; q < 16; ++q) v[q] = c_mul(v[q], s_tw3[q]);
+      }
+#pragma unroll
+      for (int q = 0; q < 16; ++q) {
+        float2 o;
+        o.x = __shfl_xor_sync(0xffffffffu, v[q].x, 16);
+        o.y = __shfl_xor_sync(0xffffffffu, v[q].y, 16);
+        v[q] = hb ? c_sub(o, v[q]) : c_add(v[q], o);  // lane (k1, s): Z[k1 + 16 q + 256 s]
+      }
+      // untangle: X[k] = (A + W1024^k B) / 2, A = Z[k] + conj Z[512-k], B = -i (Z[k] - conj Z[512-k])
+      const int src = ((16 - k1r) & 15) + 16;
+      float2 prev = v[0];  // k1 == 0, q == 0: the partner of Z[0] is Z[512] = Z[0]
+      float *prow = s_p + fl * PSTRIDE;
+#pragma unroll
+      for (int q = 0; q < 16; ++q) {
+        float2 r;
+        r.x = __shfl_sync(0xffffffffu, v[15 - q].x, src);
+        r.y = __shfl_sync(0xffffffffu, v[15 - q].y, src);
+        const float2 zp = (k1r == 0) ? prev : r;  // lane k1 == 0 wants element 16 - q: last round's value
+        prev = r;
+        const float2 zk = v[q];
+        const float2 A = c_make(zk.x + zp.x, zk.y - zp.y);
+        const float2 B = c_make(zk.y + zp.y, zp.x - zk.x);
+        const float2 WB = c_mul(B, s_tw2[q * 16 + k1r]);
+        const float xr = A.x + WB.x, xi = A.y + WB.y;
+        if (hb == 0) prow[k1r + 16 * q] = 0.25f * fmaf(xr, xr, xi * xi);
+      }
+      if (lane == 16) prow[256] = fmaf(v[0].x, v[0].x, v[0].y * v[0].y);  // Z[256] is its own partner
+      if (p.need_energy) {
+        // frame energy = sum of the one-sided power spectrum, via Parseval (feature.py:202)
+        for (int o = 16; o >= 1; o >>= 1) sumsq += __shfl_xor_sync(0xffffffffu, sumsq, o);
+        if (lane == 0) {
+          const float x0 = v[0].x + v[0].y, xn = v[0].x - v[0].y;
+          float e = (1024.f * sumsq + x0 * x0 + xn * xn) * (1.0f / 2048.f);
+          if (e == 0.f) e = kEpsF64AsF32;  // feature.py:205
+          s_en[fl] = e;
+        }
+      }
+    }
+    if (refill) cp_async_wait<0>();
+    __syncthreads();
+    // ---- phase C
+    if (use_seg && p.mode == FEAT_LMFE)
+      output_stage<kTile, true, FEAT_LMFE>(p, s_p, PSTRIDE, s_en, s_a, s_b, s_bw, s_bmeta, s_dct, nf, row0, s_rd,
+                                           s_wr, s_U, s_D, fm);
+    else if (use_seg)
+      output_stage<kTile, true>(p, s_p, PSTRIDE, s_en, s_a, s_b, s_bw, s_bmeta, s_dct, nf, row0, s_rd, s_wr,
+                                s_U, s_D, fm);
+    else
+      output_stage<kTile, false>(p, s_p, PSTRIDE, s_en, s_a, s_b, s_bw, s_bmeta, s_dct, nf, row0, s_rd, s_wr,
+                                 s_U, s_D, fm);
+    tile = next;
+    row0 = n_row0; nf = n_nf; bulk = n_bulk;
+  }
+}
+
+// ====================================================================================
 // Generic kernel: one warp per frame, radix-2 DIT on NFFT/2 complex points in smem.
 // ====================================================================================
 constexpr int kGenWarps = 4;
@@ -715,6 +948,34 @@ int launch_features_fast512(spb_context *ctx, const FeatArgs &a, const FftTables
     return pruned320 ? launch_fast<10, true>(ctx, p, aa) : launch_fast<16, true>(ctx, p, aa);
   }
   return pruned320 ? launch_fast<10, false>(ctx, p, aa) : launch_fast<16, false>(ctx, p, aa);
+}
+
+bool fast1024_supported(const FeatArgs &a) {
+  if (a.nfft != 1024 || a.tile_frames != kTile) return false;
+  if (a.mode < FEAT_MFE || a.max_bin > 256) return false;  // spectrum outputs need all 513 bins: generic kernel
+  if (a.L < 1 || a.S < 1) return false;
+  size_t span = (size_t)(kTile - 1) * a.S + a.L;
+  if (span * 4 > 44 * 1024) return false;
+  return true;
+}
+
+int launch_features_fast1024(spb_context *ctx, const FeatArgs &a, const FftTables &t) {
+  FeatParams p = make_params(a, t);
+  const int span_max = (kTile - 1) * a.S + a.L;
+  size_t smem = 2 * (size_t)((span_max + 3) & ~3) * 4 + (size_t)kF1kWarps * 16 * kF1kRS * sizeof(float2) +
+                (size_t)kTile * (257 + 4) * 4 + plan_smem_bytes(a, kTile) + 16 + (size_t)a.seg_nbins * 16 + 8 * 16 +
+                (512 + 256 + 16) * sizeof(float2);
+  auto kern = (a.L <= 448) ? features_fast1024<7> : features_fast1024<16>;
+  int per_sm = 0;
+  int rc = configure_kernel(ctx, (const void *)kern, kF1kThreads, smem, &per_sm);
+  if (rc) return rc;
+  if (per_sm < 1) return fail(ctx, SPB_ERR_INVALID, "fast1024: kernel does not fit on an SM");
+  long long grid = (long long)ctx->sm_count * per_sm;
+  if (grid > a.num_tiles) grid = a.num_tiles;
+  if (grid < 1) return SPB_OK;
+  kern<<<(unsigned)grid, kF1kThreads, smem, ctx->stream>>>(p);
+  SPB_LAUNCH_CHECK(ctx, "features_fast1024");
+  return SPB_OK;
 }
 
 int launch_features_generic(spb_context *ctx, const FeatArgs &a, const FftTables &t) {

@@ -190,6 +190,8 @@ struct FeatArgs {
 int launch_features_generic(spb_context *ctx, const FeatArgs &a, const FftTables &t);
 bool fast512_supported(const FeatArgs &a);
 int launch_features_fast512(spb_context *ctx, const FeatArgs &a, const FftTables &t);
+bool fast1024_supported(const FeatArgs &a);
+int launch_features_fast1024(spb_context *ctx, const FeatArgs &a, const FftTables &t);
 
 int launch_cmvnw_f32(spb_context *ctx, const float *in, float *scratch_ms, float *out,
                      const int32_t *nframes, const int64_t *frame_offsets, const int2 *tiles,

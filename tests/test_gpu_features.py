@@ -12,6 +12,13 @@ from speaker_verification_b200 import synth
 
 pytestmark = pytest.mark.gpu
 FS = 16000
+
+
+def _lib_path():
+    from speaker_verification_b200 import _lib
+    _lib.load()
+    return _lib.LIB_PATH
+
 TOL = 1e-4
 
 
@@ -112,6 +119,44 @@ def test_generic_kernel_matches_fast(sp):
     assert maxabs(fast, gen) < 2e-5
     assert maxabs(fast, o.lmfe(x, FS)) < TOL
     assert maxabs(mf_gen, o.mfcc(x, FS)) < TOL
+
+
+@pytest.mark.parametrize("fl,fs_,nf", [(0.025, 0.010, 40), (0.032, 0.0125, 40), (0.0250625, 0.0100625, 24), (0.064, 0.016, 40)])
+def test_fast1024_kernel_matches_generic_and_oracle(sp, fl, fs_, nf):
+    """NFFT 1024 (the reference's own call, load_data.py:64-70 + constants.py) runs the warp-per-frame
+    register FFT kernel; the generic radix-2 kernel is an independent second implementation.
+    Cases: L = 400 / S = 160 (pruned inputs), L = 512 / S = 200 (unpruned), odd L = 401 and odd
+    S = 161 (unaligned frame starts), L = 1024 (no zero padding)."""
+    raw = ctypes.CDLL(_lib_path())
+    x = synth.audio(31, 50000, np.float32)
+    kw = dict(frame_length=fl, frame_stride=fs_, num_filters=nf, fft_length=1024)
+    fast_mfe, fast_en = sp.feature.mfe(x, FS, **kw)
+    fast_l = sp.feature.lmfe(x, FS, **kw)
+    fast_c = sp.feature.mfcc(x, FS, frame_length=fl, frame_stride=fs_, num_filters=nf, fft_length=1024)
+    raw.spb_debug_force_generic(1)
+    try:
+        gen_mfe, gen_en = sp.feature.mfe(x, FS, **kw)
+        gen_l = sp.feature.lmfe(x, FS, **kw)
+    finally:
+        raw.spb_debug_force_generic(0)
+    assert fast_l.shape == gen_l.shape and fast_l.shape[0] > 100
+    assert maxabs(fast_l, gen_l) < 2e-5
+    assert np.max(np.abs(fast_mfe - gen_mfe) / np.maximum(gen_mfe, 1e-30)) < 2e-5
+    assert np.max(np.abs(fast_en - gen_en) / gen_en) < 2e-5
+    ref_mfe, ref_en = o.mfe(x, FS, **kw)
+    assert maxabs(fast_l, o.lmfe(x, FS, **kw)) < TOL
+    assert np.max(np.abs(fast_en - ref_en) / ref_en) < 1e-5
+    assert maxabs(fast_c, o.mfcc(x, FS, frame_length=fl, frame_stride=fs_, num_filters=nf, fft_length=1024)) < TOL
+    # ragged batch through the same kernel (TMA-staged tiles, partial last tiles)
+    from speaker_verification_b200 import batch
+    sigs = [synth.audio(70 + i, n, np.float32) for i, n in enumerate((40000, 1700, 16000, 99999))]
+    arena, starts, lens = batch.pack(sigs)
+    fb = batch.FeatureBatch(starts, lens, **kw)
+    for sgn, got in zip(sigs, fb.split(fb.lmfe_cmvnw(arena))):
+        lm = o.lmfe(sgn, FS, **kw)
+        if lm.shape[0] > 1:
+            assert maxabs(got, o.cmvnw_vectorised(lm, 301, True)) < TOL
+    fb.close()
 
 
 @pytest.mark.parametrize("name,kw", [

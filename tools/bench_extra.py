@@ -75,3 +75,12 @@ out = torch.empty((fb.total_frames, 40), dtype=torch.float32, device=dev)
 ms = timed(lambda: fb.lmfe_cmvnw_dev(arena.data_ptr(), arena.numel(), out.data_ptr()), fb.ctx)
 assert bool(torch.isfinite(out).all())
 report("cfg4 lmfe+cmvnw, 1024 x 60 s", ms, lengths.sum() / FS / 3600, 4 * lengths.sum() + 160 * fb.total_frames)
+del out, arena
+fb.close()
+# ---- the repo's own call (load_data.py:64-70 with constants.py): 25 ms frames, NFFT 1024, lmfe only
+arena, starts, lengths = corpus(4874, 128000)
+fb = batch.FeatureBatch(starts, lengths, frame_length=0.025, frame_stride=0.01, num_filters=40, fft_length=1024)
+out = torch.empty((fb.total_frames, 40), dtype=torch.float32, device=dev)
+ms = timed(lambda: fb.lmfe_dev(arena.data_ptr(), arena.numel(), out.data_ptr()), fb.ctx)
+assert bool(torch.isfinite(out).all())
+report("repo call lmfe(25 ms, NFFT 1024), 4874 x 8 s", ms, lengths.sum() / FS / 3600, 4 * lengths.sum() + 160 * fb.total_frames)
