@@ -551,7 +551,7 @@ features_fast512(const FeatParams p) {
 //   step across the two half-warps (shuffle) -> lane (k1, s) holds Z[k1 + 16 q + 256 s].
 //   Real-FFT untangle for bins 0..256 (speechpy's (K+1) bin mapping stops at bin 256 here): the
 //   lower half-warp owns them, partners Z[512 - k] come from the upper half by shuffles with
-//   static register indices.  Index algebra checked against numpy in tests/host.
+//   static register indices.  Index algebra: tests/test_host.py::test_fast1024_index_algebra.
 // 16 warps per CTA (two passes per 32-frame tile), one CTA per SM.
 // ====================================================================================
 constexpr int kF1kWarps = 16;

@@ -153,3 +153,67 @@ def test_host_fft_emulation(tmp_path):
                            os.path.join(ROOT, "tests", "host", "host_fft_check.cu")])
     out = subprocess.run([exe], capture_output=True, text=True)
     assert out.returncode == 0 and "OK" in out.stdout, out.stdout
+
+
+def test_fast1024_index_algebra():
+    """numpy model of features_fast1024's data movement (csrc/feat_kernels.cu): lane l holds
+    z[32 j + l]; FFT16 over j, twiddle W512^(l k1), exchange to lanes (k1, b) holding l = 2a + b,
+    FFT16 over a, radix-2 across the half-warps, untangle of bins 0..256 with partners fetched
+    from lane ((16 - k1) & 15) + 16 (element 15 - q; lane k1 = 0 uses the previous round's value)."""
+    rng = np.random.default_rng(0)
+    L = 400
+    x = rng.standard_normal(L)
+    xx = np.zeros(1024); xx[:L] = x
+    z = xx[0::2] + 1j * xx[1::2]                      # 512 complex
+    W = lambda N, e: np.exp(-2j * np.pi * e / N)
+    # stage 1: lane l holds v[j] = z[32 j + l]
+    V = np.zeros((32, 16), complex)                   # [l][k1]
+    for l in range(32):
+        v = np.array([z[32 * j + l] for j in range(16)])
+        V[l] = np.fft.fft(v)                          # over j -> k1
+        V[l] *= W(512, l * np.arange(16))
+    # exchange: lane m=(k1,b) gets y[a] = V[2a+b][k1]
+    Zs = np.zeros((32, 16), complex)                  # lane (k1 + 16 s) element q -> Z[k1 + 16 q + 256 s]
+    Y = np.zeros((32, 16), complex)
+    for m in range(32):
+        k1, b = m & 15, m >> 4
+        y = np.array([V[2 * a + b][k1] for a in range(16)])
+        Y[m] = np.fft.fft(y)
+        if b == 1:
+            Y[m] *= W(32, np.arange(16))
+    for m in range(32):
+        k1, b = m & 15, m >> 4
+        other = Y[m ^ 16]
+        Zs[m] = Y[m] + other if b == 0 else other - Y[m]
+    Zref = np.fft.fft(z)
+    for m in range(32):
+        k1, s = m & 15, m >> 4
+        for q in range(16):
+            assert abs(Zs[m][q] - Zref[k1 + 16 * q + 256 * s]) < 1e-9
+    # untangle on lanes s = 0
+    Xref = np.fft.rfft(xx)
+    P = np.zeros(257)
+    recv_prev = None
+    for q in range(16):
+        recv = [Zs[((16 - (m & 15)) & 15) + 16][15 - q] for m in range(32)]   # shfl of element 15-q from lane partner
+        for m in range(16):
+            k1 = m
+            k = k1 + 16 * q
+            if k1 == 0:
+                zp = Zs[0][0] if q == 0 else recv_prev[0]
+            else:
+                zp = recv[m]
+            zk = Zs[m][q]
+            A = complex(zk.real + zp.real, zk.imag - zp.imag)
+            B = complex(zk.imag + zp.imag, zp.real - zk.real)
+            w = W(1024, k)
+            X2 = A + B * w
+            assert abs(X2 / 2 - Xref[k]) < 1e-9, (k, X2 / 2, Xref[k])
+            P[k] = 0.25 * abs(X2) ** 2
+        recv_prev = recv
+    z256 = Zs[16][0]
+    P[256] = z256.real ** 2 + z256.imag ** 2
+    assert np.allclose(P, np.abs(Xref[:257]) ** 2)
+    x0 = Zs[0][0].real + Zs[0][0].imag; xn = Zs[0][0].real - Zs[0][0].imag
+    assert abs(x0 - Xref[0].real) < 1e-9 and abs(xn - Xref[512].real) < 1e-9
+
