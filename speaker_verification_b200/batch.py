@@ -234,3 +234,70 @@ def lmfe_cmvnw(signals, **kw):
         return [a.copy() for a in fb.split(fb.lmfe_cmvnw(arena))]
     finally:
         fb.close()
+
+
+class CubeCollate:
+    """``collate_fn`` for a DataLoader whose dataset yields raw ``(signal, label)`` pairs (or
+    ``{'signal': ..., 'label': ...}`` dicts): ONE ragged batch call per mini-batch instead of the
+    reference's per-utterance chain ``speech.lmfe`` (load_data.py:61-68) ->
+    ``Compose([CMVN(), FeatureCube(cube_shape), ToTensor()])`` (train.py:194-210).
+
+    Returns ``(features, labels)`` like the reference's loader does (train.py:76):
+    ``features`` is (B, channels, num_crops, crop_frames, num_filters) float32 and ``labels``
+    int64 (utils.ToTensor, utils.py:400-408).  With ``as_torch=True`` both are torch tensors
+    and ``features`` is produced directly in device memory, so ``train_input.cuda()``
+    (train.py:78) becomes a no-op; with ``as_torch=False`` they are numpy arrays.
+
+    The defaults are the reference's training call: 25 ms frames, 10 ms stride, 40 filters,
+    NFFT 1024 (load_data.py:61-68) and cube_shape (80, 40, 20) (train.py:199,204).  Crop starts
+    come from the global numpy RNG in utterance order, as ``FeatureCube.__call__`` draws them
+    (utils.py:373), unless ``rng`` is given.
+    """
+
+    def __init__(self, cube_shape=(80, 40, 20), derivative: bool = False, normalize: bool = False,
+                 sampling_frequency=16000, frame_length=0.025, frame_stride=0.01, num_filters=None,
+                 fft_length=1024, sample_scale: float = 1.0, as_torch: bool = True, rng=None, device=None):
+        self.crop_frames, self.num_filters, self.num_crops = (int(v) for v in cube_shape[:3])
+        if num_filters is not None:
+            assert int(num_filters) == self.num_filters, "cube_shape[1] is the number of filters"
+        self.derivative, self.normalize = bool(derivative), bool(normalize)
+        self.kw = dict(sampling_frequency=sampling_frequency, frame_length=frame_length,
+                       frame_stride=frame_stride, num_filters=self.num_filters, fft_length=fft_length,
+                       device=device)
+        self.sample_scale, self.as_torch, self.rng = float(sample_scale), bool(as_torch), rng
+
+    @staticmethod
+    def _unpack(sample):
+        if isinstance(sample, dict):
+            return sample["signal"], sample["label"]
+        return sample[0], sample[1]
+
+    def __call__(self, samples):
+        signals, labels = zip(*(self._unpack(s) for s in samples))
+        signals = [np.asarray(s).reshape(-1) for s in signals]
+        pcm = all(s.dtype == np.int16 for s in signals)
+        arena, starts, lengths = pack(signals, dtype=np.int16 if pcm else np.float32)
+        fb = FeatureBatch(starts, lengths, **self.kw)
+        try:
+            if int(np.diff(fb.frame_offsets).min()) <= self.crop_frames:
+                # np.random.randint(F - crop_frames) raises for F <= crop_frames (utils.py:373)
+                raise ValueError("utterance shorter than crop_frames + 1 frames")
+            crops = fb.draw_crop_starts(self.num_crops, self.crop_frames, self.rng)
+            labels = np.asarray(labels, dtype=np.int64)
+            if not self.as_torch:
+                return fb.feature_cubes(arena, crops, crop_frames=self.crop_frames, derivative=self.derivative,
+                                        normalize=self.normalize, sample_scale=self.sample_scale), labels
+            import torch
+            dev = torch.device("cuda", fb.ctx.device)
+            d_in = torch.from_numpy(arena).to(dev)
+            if d_in.dtype != torch.float32 or self.sample_scale != 1.0:
+                d_in = d_in.to(torch.float32).mul_(self.sample_scale)  # exact for power-of-two scales
+            out = torch.empty((len(signals), 3 if self.derivative else 1, self.num_crops, self.crop_frames,
+                               self.num_filters), dtype=torch.float32, device=dev)
+            torch.cuda.current_stream(dev).synchronize()
+            fb.feature_cubes_dev(d_in.data_ptr(), d_in.numel(), out.data_ptr(), crops, self.crop_frames,
+                                 self.derivative, self.normalize)
+            fb.ctx.sync()
+            return out, torch.from_numpy(labels)
+        finally:
+            fb.close()

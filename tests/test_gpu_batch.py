@@ -245,6 +245,42 @@ def test_feature_cubes_match_reference_transforms(sp):
     fb.close(); fb2.close()
 
 
+def test_cube_collate_is_the_reference_loader_batch(sp):
+    """one collate call == the reference's per-utterance chain
+    speech.lmfe(25 ms, NFFT 1024) -> CMVN -> FeatureCube[3C] -> ToTensor stacked by the
+    DataLoader (load_data.py:61-68, train.py:194-226), with the reference's RNG use."""
+    import torch
+    lengths = [48000, 20000, 33333, 16400 + 400]
+    sigs = _signals(1200, lengths)
+    labels = [3, 0, 7, 3]
+    for deriv, norm in ((False, False), (True, True)):
+        coll = batch.CubeCollate((80, 40, 20), derivative=deriv, normalize=norm)
+        np.random.seed(99)
+        feats, lab = coll([{"signal": s, "label": l} for s, l in zip(sigs, labels)])
+        assert feats.is_cuda and feats.dtype == torch.float32 and lab.dtype == torch.int64
+        assert tuple(feats.shape) == (4, 3 if deriv else 1, 20, 80, 40) and lab.tolist() == labels
+        np.random.seed(99)
+        for u, s in enumerate(sigs):
+            lm = o.lmfe(s, FS, frame_length=0.025, frame_stride=0.01, num_filters=40, fft_length=1024)
+            idx = np.random.randint(lm.shape[0] - 80, size=20)
+            ref = o.feature_cube(o.cmvn_transform(lm, deriv, norm), idx, 80)
+            assert np.max(np.abs(feats[u].cpu().numpy() - ref)) < TOL, (deriv, norm, u)
+        # numpy flavour, tuple samples, same RNG state -> same cubes
+        np.random.seed(99)
+        f2, l2 = batch.CubeCollate((80, 40, 20), derivative=deriv, normalize=norm, as_torch=False)(
+            list(zip(sigs, labels)))
+        assert np.array_equal(f2, feats.cpu().numpy()) and l2.dtype == np.int64
+    # int16 PCM with the librosa scale == the scaled float signals
+    pcm = [synth.pcm16(70 + i, n) for i, n in enumerate([30000, 25000])]
+    rs = np.random.RandomState(4)
+    a, _ = batch.CubeCollate(sample_scale=batch.PCM16_SCALE, rng=rs)([(p, 1) for p in pcm])
+    rs = np.random.RandomState(4)
+    b, _ = batch.CubeCollate(rng=rs)([(p.astype(np.float32) * np.float32(batch.PCM16_SCALE), 1) for p in pcm])
+    assert torch.equal(a, b)
+    with pytest.raises(ValueError):  # 80 frames or fewer: the reference's randint raises too
+        batch.CubeCollate()([(sigs[0][:8000], 0)])
+
+
 def test_full_size_properties_cfg3_scale(sp):
     """Size-independent properties at benchmark scale (20 000 cfg3-shaped utterances, 45 audio-h,
     10 GB arena generated on the device, several launch groups):
