@@ -499,6 +499,7 @@ int spb_plan_create(spb_context *ctx, const spb_feature_params *params, const do
   }
   FftTables t;
   int rc = get_fft_tables(ctx, q.nfft, &t);
+  if (!rc && pl->seg_nbins > 0) rc = build_tc_plan(ctx, pl, seg_rd.data());
   if (rc) {
     spb_plan_destroy(pl);
     return rc;
@@ -517,6 +518,10 @@ int spb_plan_destroy(spb_plan *pl) {
   cudaFree(pl->d_seg_rd);
   cudaFree(pl->d_seg_ranges);
   cudaFree(pl->d_dct);
+  cudaFree(pl->d_tc_whi);
+  cudaFree(pl->d_tc_wlo);
+  if (pl->ctx && pl->ctx->tc_const_plan == pl) pl->ctx->tc_const_plan = nullptr;
+  cudaFree(pl->d_tc_flag);
   delete pl;
   return SPB_OK;
 }
@@ -627,6 +632,31 @@ int spb_batch_create(spb_context *ctx, const spb_plan *plan, const int64_t *star
                        [](const int4 &x, const int4 &y) { return x.z > y.z; });
     }
   }
+  // tensor-core feature kernel: groups of 32 hops (31 frames), 4 per tile, each chunk padded to
+  // whole tiles; needs 16-byte aligned utterance starts
+  std::vector<TcGroup> tcg;
+  bool tc_use = plan->tc_ok;
+  for (int64_t u = 0; u < U && tc_use; ++u) tc_use = (starts[u] & 3) == 0;
+  if (tc_use) {
+    for (BatchChunk &c : ch.chunks) {
+      c.tc0 = (int64_t)tcg.size();
+      for (int64_t u = c.u0; u < c.u1; ++u)
+        for (int64_t f0 = 0; f0 < nframes[u]; f0 += kTcGroupFrames) {
+          TcGroup g;
+          g.gstart = starts[u] + f0 * S;
+          g.row0 = b->h_frame_offsets[u] + f0;
+          g.nf = (int)std::min<int64_t>(kTcGroupFrames, nframes[u] - f0);
+          g.pad[0] = g.pad[1] = g.pad[2] = 0;
+          tcg.push_back(g);
+        }
+      while (tcg.size() & 3) {
+        TcGroup g;
+        g.gstart = 0; g.row0 = 0; g.nf = 0; g.pad[0] = g.pad[1] = g.pad[2] = 0;
+        tcg.push_back(g);
+      }
+      c.tc1 = (int64_t)tcg.size();
+    }
+  }
   // launch groups of the device-pointer path: runs of chunks of up to group_rows rows.  A launch
   // over ~200 Ki rows is only ~2 tiles per SM for the cmvnw kernels and pays a full tail per
   // kernel; measured, large groups win although their intermediates no longer fit L2.
@@ -643,7 +673,7 @@ int spb_batch_create(spb_context *ctx, const spb_plan *plan, const int64_t *star
         g = c;
         open = true;
       } else {
-        g.u1 = c.u1; g.tile1 = c.tile1; g.cm1 = c.cm1; g.row1 = c.row1;
+        g.u1 = c.u1; g.tile1 = c.tile1; g.cm1 = c.cm1; g.row1 = c.row1; g.tc1 = c.tc1;
         g.s_lo = std::min(g.s_lo, c.s_lo);
         g.s_hi = std::max(g.s_hi, c.s_hi);
       }
@@ -673,6 +703,7 @@ int spb_batch_create(spb_context *ctx, const spb_plan *plan, const int64_t *star
       (e = cudaMalloc(&b->d_ftiles, (size_t)std::max<int64_t>(b->total_tiles, 1) * sizeof(FftTile))) != cudaSuccess ||
       (e = cudaMalloc(&b->d_cm_tiles, (size_t)std::max<int64_t>(b->total_cm_tiles, 1) * sizeof(int2))) != cudaSuccess ||
       (e = cudaMalloc(&b->d_big_tiles, std::max<size_t>(big.size(), 1) * sizeof(int4))) != cudaSuccess ||
+      (!tcg.empty() && (e = cudaMalloc(&b->d_tc_groups, tcg.size() * sizeof(TcGroup))) != cudaSuccess) ||
       (e = cudaMalloc(&d_tile_off, (u_bytes + 1) * 8)) != cudaSuccess ||
       (e = cudaMalloc(&d_cm_off, (u_bytes + 1) * 8)) != cudaSuccess)
     return cleanup(e, "cudaMalloc(batch)");
@@ -683,6 +714,9 @@ int spb_batch_create(spb_context *ctx, const spb_plan *plan, const int64_t *star
         (e = cudaMemcpyAsync(d_tile_off, tile_off.data(), (size_t)(U + 1) * 8, cudaMemcpyHostToDevice, ctx->stream)) != cudaSuccess ||
         (e = cudaMemcpyAsync(d_cm_off, cm_off.data(), (size_t)(U + 1) * 8, cudaMemcpyHostToDevice, ctx->stream)) != cudaSuccess)
       return cleanup(e, "cudaMemcpyAsync(batch)");
+    if (!tcg.empty() &&
+        (e = cudaMemcpyAsync(b->d_tc_groups, tcg.data(), tcg.size() * sizeof(TcGroup), cudaMemcpyHostToDevice, ctx->stream)) != cudaSuccess)
+      return cleanup(e, "cudaMemcpyAsync(tc groups)");
     if (!big.empty() &&
         (e = cudaMemcpyAsync(b->d_big_tiles, big.data(), big.size() * sizeof(int4), cudaMemcpyHostToDevice, ctx->stream)) != cudaSuccess)
       return cleanup(e, "cudaMemcpyAsync(big tiles)");
@@ -714,6 +748,7 @@ int spb_batch_destroy(spb_batch *b) {
   cudaFree(b->d_frame_offsets);
   cudaFree(b->d_tiles);
   cudaFree(b->d_ftiles);
+  cudaFree(b->d_tc_groups);
   cudaFree(b->d_cm_tiles);
   cudaFree(b->d_big_tiles);
   delete b;
@@ -747,6 +782,10 @@ static void fill_feat_args(FeatArgs &a, const spb_batch *b, const float *d_sampl
   a.frame_offsets = b->d_frame_offsets;
   a.tiles = b->d_tiles;
   a.ftiles = b->d_ftiles;
+  a.plan = pl;
+  a.tc_groups = nullptr;  // set per launch range (chunk / group)
+  a.num_tc_groups = 0;
+  a.run_if = nullptr;
   a.num_tiles = b->total_tiles;
   a.tile_frames = b->tile_frames;
   a.L = pl->p.frame_len;
@@ -775,6 +814,16 @@ static void fill_feat_args(FeatArgs &a, const spb_batch *b, const float *d_sampl
 // force_generic: 0 auto, 1 generic kernel (used by tests to cross-check the fast path)
 static int g_force_generic = 0;
 static int g_force_small_cmvnw = 0;
+static int g_no_tc = 0;
+// tensor-core feature kernel: SPB_TC=0 disables it (read once)
+static bool tc_enabled() {
+  static int v = -1;
+  if (v < 0) {
+    const char *e = getenv("SPB_TC");
+    v = (e && e[0] == '0') ? 0 : 1;
+  }
+  return v != 0;
+}
 
 static int run_features(spb_context *ctx, FeatArgs &a) {
   if (a.num_tiles <= 0) return SPB_OK;
@@ -782,7 +831,17 @@ static int run_features(spb_context *ctx, FeatArgs &a) {
   int rc = get_fft_tables(ctx, a.nfft, &t);
   if (rc) return rc;
   const size_t tb = timing_begin(ctx);
-  if (!g_force_generic && fast512_supported(a)) rc = launch_features_fast512(ctx, a, t);
+  if (!g_force_generic && !g_no_tc && tc_enabled() && features_tc_supported(a) && fast512_supported(a)) {
+    // tensor-core kernel; samples it cannot split (|x| >= 2, NaN, inf) raise the plan's flag
+    // and the guarded CUDA-core kernel redoes the launch
+    SPB_CUDA(ctx, cudaMemsetAsync(a.plan->d_tc_flag, 0, 4, ctx->stream));
+    rc = launch_features_tc(ctx, a);
+    if (!rc) {
+      a.run_if = a.plan->d_tc_flag;
+      rc = launch_features_fast512(ctx, a, t);
+      a.run_if = nullptr;
+    }
+  } else if (!g_force_generic && fast512_supported(a)) rc = launch_features_fast512(ctx, a, t);
   else if (!g_force_generic && fast1024_supported(a)) rc = launch_features_fast1024(ctx, a, t);
   else rc = launch_features_generic(ctx, a, t);
   timing_end(ctx, 0, tb);
@@ -814,6 +873,10 @@ static int lmfe_cmvnw_chunk(spb_context *ctx, const spb_batch *b, const BatchChu
   a.tiles = b->d_tiles + c.tile0;
   a.ftiles = b->d_ftiles + c.tile0;
   a.num_tiles = c.tile1 - c.tile0;
+  if (b->d_tc_groups) {
+    a.tc_groups = b->d_tc_groups + c.tc0;
+    a.num_tc_groups = c.tc1 - c.tc0;
+  }
   int rc = run_features(ctx, a);
   if (rc) return rc;
   float *ms_biased = d_ms ? d_ms - (ptrdiff_t)c.row0 * M : nullptr;
@@ -855,6 +918,10 @@ static int run_simple_mode(spb_context *ctx, const spb_batch *b, const float *d_
                            int64_t arena_len, int mode, float *d_out, float *d_energy) {
   FeatArgs a;
   fill_feat_args(a, b, d_samples, arena_len, mode, d_out, d_energy);
+  if (b->d_tc_groups && !b->chunks.empty()) {
+    a.tc_groups = b->d_tc_groups;
+    a.num_tc_groups = b->chunks.back().tc1;
+  }
   return run_features(ctx, a);
 }
 
@@ -928,6 +995,7 @@ extern "C" {
 SPB_API int spb_debug_force_generic(int on) {
   g_force_generic = on & 1;
   g_force_small_cmvnw = (on >> 1) & 1;  // bit 1: small-tile cmvnw kernels (cross-check)
+  g_no_tc = (on >> 2) & 1;              // bit 2: CUDA-core FFT kernel instead of the tensor-core one
   return SPB_OK;
 }
 

@@ -49,6 +49,7 @@ struct FeatParams {
   const float2 *tw;
   int nfft, log2nc;
   int need_energy;
+  const int *run_if;  // fast512: when set, the launch is a no-op unless *run_if != 0
 };
 
 // ------------------------------------------------------------------------------------
@@ -270,6 +271,7 @@ template <int NJ, bool FULL>
 __global__ void __launch_bounds__(kFastThreads, 16 / kNW)
 features_fast512(const FeatParams p) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
+  if (p.run_if != nullptr && *p.run_if == 0) return;  // fallback launch of the tensor-core path
   constexpr int PBINS = FULL ? 257 : 129;
   // 4 zeroed pad bins (padded band taps); stride == 5 (mod 32): conflict-free both for the
   // half-warp row writes (rows 16 apart land 16 banks apart) and the lane = frame column reads
@@ -878,6 +880,7 @@ static FeatParams make_params(const FeatArgs &a, const FftTables &t) {
   p.frame_offsets = a.frame_offsets;
   p.tiles = a.tiles;
   p.ftiles = a.ftiles;
+  p.run_if = a.run_if;
   p.num_tiles = a.num_tiles;
   p.L = a.L; p.S = a.S; p.K = a.K;
   p.M = a.M; p.C = a.C; p.dc_elim = a.dc_elim;

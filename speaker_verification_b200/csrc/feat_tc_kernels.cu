@@ -1,0 +1,523 @@
+// Tensor-core variant of the lmfe feature kernel (stack_frames + |rfft|^2/NFFT + mel + log):
+// the transform runs on tcgen05 as a hop-block DFT.
+//
+// Replaces, for the batch paths at L == 2 S (speechpy defaults: 20 ms frames, 10 ms stride):
+//   processing.py:93-139   stack_frames        frame f = hops f and f+1 (a hop = S samples)
+//   processing.py:158-174  |rfft|^2 / NFFT     X_f[k] = A_f[k] + e^{-2 pi i S k / NFFT} A_{f+1}[k]
+//   feature.py:199-217     P . fb^T, zero_handling, log
+//
+// A_h[k] = sum_{n<S} x[hS+n] e^{-2 pi i k n / NFFT} is ONE dense product per hop, shared by the
+// two frames the hop belongs to: rows = hops (the sample arena itself, viewed S samples per
+// row), columns = (cos, -sin) of the bins the filterbank reads (speechpy's (K+1) bin mapping
+// stops at bin 128; up to 124 bins = 248 columns), K = S = 160.
+//
+// fp32 accuracy from fp16 tensor cores: x 2^15 = xh + xl, W = Wh + Wl (fp16 each; for int16
+// PCM audio the sample split is exact).  Per tile the 20 small products xl.Wh, xh.Wl go first
+// into the empty fp32 TMEM accumulator, then the 10 xh.Wh products: TMEM accumulation
+// truncates, and only those last 10 additions happen at full magnitude (measured: the
+// interleaved order is 3.5x noisier).  |x| >= 2 (or NaN/inf) cannot be split this way: the
+// converter raises a flag and the launcher's guarded CUDA-core FFT kernel redoes the launch.
+//
+// One persistent CTA per SM, 17 warps:
+//   warps 0..7   epilogue: quadrant q = warp % 4 owns hop rows 32q..32q+31 (31 frames), the
+//                two warps of a quadrant split the filterbank segments; tcgen05.ld, neighbour
+//                hop by shuffle, complex MAC, |X|^2, segment-form mel sums (weights are
+//                immediate constant-bank operands), log, staged 128-bit stores
+//   warp  8      MMA issuer (one elected thread), M128 N256 K16 kind::f16, two TMEM accumulators
+//   warps 9..16  converters: 128-bit sample loads five k-steps ahead, split, st.shared into the
+//                no-swizzle K-major operand buffers (xh: whole tile, xl: ring of 3 k-steps)
+// The DFT matrix (2 x 77.5 KB) stays resident in shared memory.
+#include <cuda.h>
+#include <cuda_fp16.h>
+#include <math.h>
+#include <stdlib.h>
+
+#include <vector>
+
+#include "ptx_helpers.cuh"
+#include "spb_internal.cuh"
+
+namespace spb {
+
+constexpr int kTcHop = 160;                       // samples per hop row == K of the product
+constexpr int kTcKSteps = kTcHop / 16;            // 10 MMA k-steps
+constexpr int kTcRows = 128;                      // hop rows per tile (MMA M)
+constexpr int kTcN = 256;                         // MMA N
+constexpr int kTcNAlloc = 248;                    // stored columns: (re, im) of up to 124 bins
+constexpr int kTcMaxBins = kTcNAlloc / 2;
+constexpr int kTcLoSlots = 3;                     // xl ring depth (k-steps)
+constexpr int kTcAhead = 5;                       // converter load distance (k-steps)
+constexpr int kTcOutPitch = 40;                   // staging rows: up to 40 filters
+constexpr uint32_t kTcBLbo = kTcNAlloc * 16;             // 3 968 B between the k-chunks of W
+constexpr uint32_t kTcBMat = (kTcHop / 8) * kTcBLbo;     // 79 360 B: [k/8][col][8 halves]
+constexpr uint32_t kTcAMat = 2 * kTcRows * 16;           // 4 096 B per k-step: [2][row][8 halves]
+constexpr uint32_t kTcOffHi = 2 * kTcBMat;               // xh: 10 k-steps
+constexpr uint32_t kTcOffLo = kTcOffHi + kTcKSteps * kTcAMat;
+constexpr uint32_t kTcOffOut = kTcOffLo + kTcLoSlots * kTcAMat;
+constexpr uint32_t kTcOutBytes = 4 * kTcGroupFrames * kTcOutPitch * 4;
+constexpr uint32_t kTcOffBars = kTcOffOut + kTcOutBytes;
+constexpr uint32_t kTcSmem = kTcOffBars + 256;
+static_assert(kTcSmem <= 232448, "features_tc: shared memory budget");
+constexpr int kTcEpiWarps = 8, kTcMmaWarp = 8, kTcCvtWarp0 = 9, kTcCvtWarps = 8;
+constexpr int kTcThreads = (kTcCvtWarp0 + kTcCvtWarps) * 32;
+constexpr float kTcInScale = 32768.f;             // 2^15
+// D = F32 (bit 4), A = B = F16 (0), K-major both, N >> 3 at bit 17, M >> 4 at bit 24
+constexpr uint32_t kTcIdesc = (1u << 4) | ((uint32_t)(kTcN >> 3) << 17) | ((uint32_t)(kTcRows >> 4) << 24);
+static constexpr float kTcEps = 2.220446049250313e-16f;  // functions.py:62
+
+// per bin {rise weight, fall weight, cos, sin of the hop rotation}, one table per epilogue half
+// (bins outside a half's segments carry zero weights).  Constant bank: the unrolled epilogue
+// uses the entries as immediate operands.
+struct TcConst {
+  float4 tab[2][128];
+};
+__constant__ TcConst c_tc;
+
+struct TcHalf {
+  uint32_t endmask[4];  // bit b: bin b closes a segment of this half
+  int ch_begin, ch_end; // 16-bin chunks [begin, end) this half reads
+  int seg0;             // index of the first segment it walks
+  int out_lo;           // filters below this index belong to the other half
+};
+
+struct TcParams {
+  const float *samples;
+  const TcGroup *groups;     // 4 per tile
+  long long num_tiles;
+  const __half *w_hi, *w_lo; // DFT matrix in the shared-memory layout (kTcBMat bytes each)
+  TcHalf half[2];
+  int M;
+  float scale;               // 1 / (NFFT * 2^30)
+  int mfe;                   // 1: no log
+  float *out;
+  int *flag;                 // set when a sample cannot be split (|x| >= 2, NaN, inf)
+  int dbg;                   // SPB_TC_DBG phase knobs (timing experiments only)
+};
+
+// K-major operand without swizzle: core matrix = 8 rows x 16 bytes stored contiguously,
+// SBO = 128 B between 8-row groups, LBO = distance between the two core matrices of a k-step.
+__device__ __forceinline__ uint64_t umma_desc_plain(uint32_t saddr, uint32_t lbo) {
+  uint64_t d = 0;
+  d |= (uint64_t)((saddr & 0x3FFFF) >> 4);
+  d |= (uint64_t)(lbo >> 4) << 16;
+  d |= (uint64_t)(128 >> 4) << 32;
+  d |= (uint64_t)1 << 46;
+  return d;
+}
+__device__ __forceinline__ void umma_f16(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc,
+                                         uint32_t accumulate) {
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t"
+      "}" ::"r"(tmem_d), "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+__device__ __forceinline__ void fence_async_smem() {
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+}
+__device__ __forceinline__ void named_bar_sync(int id, int threads) {
+  asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(threads) : "memory");
+}
+__device__ __forceinline__ void tmem_ld32_nowait(uint32_t taddr, uint32_t (&v)[32]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+      "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+      : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
+        "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]),
+        "=r"(v[16]), "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]),
+        "=r"(v[24]), "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
+      : "r"(taddr)
+      : "memory");
+}
+__device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+
+// four scaled samples -> fp16 hi and lo halves (two 32-bit words each)
+__device__ __forceinline__ void split4(const float4 x, uint2 &hi, uint2 &lo, bool &bad) {
+  const float a = x.x * kTcInScale, b = x.y * kTcInScale, c = x.z * kTcInScale, d = x.w * kTcInScale;
+  const float m = fmaxf(fmaxf(fabsf(a), fabsf(b)), fmaxf(fabsf(c), fabsf(d)));
+  bad |= !(m < 65504.f) || (a != a) || (b != b) || (c != c) || (d != d);
+  const __half2 h0 = __floats2half2_rn(a, b), h1 = __floats2half2_rn(c, d);
+  const float2 f0 = __half22float2(h0), f1 = __half22float2(h1);
+  const __half2 l0 = __floats2half2_rn(a - f0.x, b - f0.y), l1 = __floats2half2_rn(c - f1.x, d - f1.y);
+  hi.x = *reinterpret_cast<const uint32_t *>(&h0);
+  hi.y = *reinterpret_cast<const uint32_t *>(&h1);
+  lo.x = *reinterpret_cast<const uint32_t *>(&l0);
+  lo.y = *reinterpret_cast<const uint32_t *>(&l1);
+}
+
+// One tile of one epilogue warp: lane = hop row of the quadrant, frame = hops (lane, lane + 1).
+// The chunk loop is NOT unrolled: the straight-line version (123 bins x ~40 instructions, twice)
+// ran at the instruction-fetch rate (ncu: stall_no_inst on every line).
+__device__ __forceinline__ void tc_epilogue_tile(const TcParams &p, const int half, const uint32_t taddr, float *my,
+                                                 const int lane) {
+  const int M = p.M;
+  const int ch_begin = half ? p.half[1].ch_begin : p.half[0].ch_begin;
+  const int ch_end = half ? p.half[1].ch_end : p.half[0].ch_end;
+  const int out_lo = half ? p.half[1].out_lo : p.half[0].out_lo;
+  const uint32_t m0 = half ? p.half[1].endmask[0] : p.half[0].endmask[0];
+  const uint32_t m1 = half ? p.half[1].endmask[1] : p.half[0].endmask[1];
+  const uint32_t m2 = half ? p.half[1].endmask[2] : p.half[0].endmask[2];
+  const uint32_t m3 = half ? p.half[1].endmask[3] : p.half[0].endmask[3];
+  float rise = 0.f, fall = 0.f, prev_u = 0.f;
+  int seg = half ? p.half[1].seg0 : p.half[0].seg0;
+#pragma unroll 1
+  for (int ch = ch_begin; ch < ch_end; ++ch) {
+    uint32_t v[32];
+    tmem_ld32_nowait(taddr + ch * 32, v);
+    const uint32_t mw = (ch < 4) ? ((ch < 2) ? m0 : m1) : ((ch < 6) ? m2 : m3);
+    const uint32_t mask = mw >> ((ch & 1) * 16);
+    const float4 *tb = &c_tc.tab[half][ch * 16];
+    tmem_ld_wait();
+#pragma unroll
+    for (int j = 0; j < 16; ++j) {
+      const float4 w = tb[j];
+      const float a_re = __uint_as_float(v[2 * j]), a_im = __uint_as_float(v[2 * j + 1]);
+      const float b_re = __shfl_down_sync(0xffffffffu, a_re, 1);
+      const float b_im = __shfl_down_sync(0xffffffffu, a_im, 1);
+      const float xr = fmaf(-w.w, b_im, fmaf(w.z, b_re, a_re));
+      const float xi = fmaf(w.w, b_re, fmaf(w.z, b_im, a_im));
+      const float pw = fmaf(xr, xr, xi * xi);
+      rise = fmaf(w.x, pw, rise);
+      fall = fmaf(w.y, pw, fall);
+      if ((mask >> j) & 1u) {
+        const int o = seg - 1;
+        if (o >= out_lo && lane < kTcGroupFrames) {
+          float a = (prev_u + fall) * p.scale;
+          if (a == 0.f) a = kTcEps;  // functions.zero_handling (feature.py:217)
+          my[lane * M + o] = p.mfe ? a : __logf(a);
+        }
+        prev_u = rise;
+        rise = 0.f;
+        fall = 0.f;
+        ++seg;
+      }
+    }
+  }
+}
+
+__global__ void __launch_bounds__(kTcThreads, 1) features_tc_kernel(const TcParams p) {
+  extern __shared__ __align__(128) unsigned char tc_smem[];
+  unsigned char *base = tc_smem;
+  float *s_out = reinterpret_cast<float *>(base + kTcOffOut);
+  uint64_t *bars = reinterpret_cast<uint64_t *>(base + kTcOffBars);
+  uint64_t *full = bars;                         // [10] k-step s of the tile converted (8 converter warps)
+  uint64_t *hi_empty = bars + 10;                // [10] xh of k-step s consumed (tcgen05.commit)
+  uint64_t *lo_empty = bars + 20;                // [3]  xl ring slot consumed
+  uint64_t *acc_full = bars + 23;                // [2]
+  uint64_t *acc_empty = bars + 25;               // [2] 8 epilogue warps
+  uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + 27);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const uint32_t sbase = smem_u32(base);
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < kTcKSteps; ++s) {
+      mbar_init(&full[s], kTcCvtWarps);
+      mbar_init(&hi_empty[s], 1);
+    }
+    for (int s = 0; s < kTcLoSlots; ++s) mbar_init(&lo_empty[s], 1);
+    for (int a = 0; a < 2; ++a) {
+      mbar_init(&acc_full[a], 1);
+      mbar_init(&acc_empty[a], kTcEpiWarps);
+    }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == kTcMmaWarp) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)),
+                 "r"(512u)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  {  // resident DFT matrix
+    const uint4 *gh = reinterpret_cast<const uint4 *>(p.w_hi);
+    const uint4 *gl = reinterpret_cast<const uint4 *>(p.w_lo);
+    uint4 *sh = reinterpret_cast<uint4 *>(base);
+    uint4 *sl = reinterpret_cast<uint4 *>(base + kTcBMat);
+    for (uint32_t i = threadIdx.x; i < kTcBMat / 16; i += kTcThreads) {
+      sh[i] = __ldg(gh + i);
+      sl[i] = __ldg(gl + i);
+    }
+    fence_async_smem();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp >= kTcCvtWarp0) {
+    // ===== converters =====
+    const int c = (warp - kTcCvtWarp0) * 32 + lane;  // 0..255
+    const int q = c & 3;                             // which 4 samples of the 16 of a k-step
+    const int rA = c >> 2, rB = 64 + (c >> 2);       // the two hop rows this thread feeds
+    const uint32_t dA = (uint32_t)((q >> 1) * (kTcRows * 16) + rA * 16 + (q & 1) * 8);
+    const uint32_t dB = (uint32_t)((q >> 1) * (kTcRows * 16) + rB * 16 + (q & 1) * 8);
+    bool bad = false;
+    const float4 zero4 = make_float4(0.f, 0.f, 0.f, 0.f);
+    auto row_ptr = [&](long long t, int r) -> const float * {
+      if (t >= p.num_tiles) return nullptr;
+      const TcGroup g = p.groups[t * 4 + (r >> 5)];
+      const int i = r & 31;
+      return (g.nf > 0 && i <= g.nf) ? p.samples + g.gstart + (long long)i * kTcHop + q * 4 : nullptr;
+    };
+    long long t = blockIdx.x;
+    const float *pA = row_ptr(t, rA), *pB = row_ptr(t, rB);
+    float4 bufA[kTcAhead], bufB[kTcAhead];
+#pragma unroll
+    for (int s = 0; s < kTcAhead; ++s) {
+      bufA[s] = pA ? __ldg(reinterpret_cast<const float4 *>(pA + s * 16)) : zero4;
+      bufB[s] = pB ? __ldg(reinterpret_cast<const float4 *>(pB + s * 16)) : zero4;
+    }
+    uint32_t gs = 0, it = 0;  // k-steps, tiles produced so far
+    for (; t < p.num_tiles; t += gridDim.x, ++it) {
+      const float *nA = row_ptr(t + gridDim.x, rA), *nB = row_ptr(t + gridDim.x, rB);
+#pragma unroll
+      for (int s = 0; s < kTcKSteps; ++s, ++gs) {
+        const float4 xa = bufA[s % kTcAhead], xb = bufB[s % kTcAhead];
+        if (s + kTcAhead < kTcKSteps) {
+          bufA[s % kTcAhead] = pA ? __ldg(reinterpret_cast<const float4 *>(pA + (s + kTcAhead) * 16)) : zero4;
+          bufB[s % kTcAhead] = pB ? __ldg(reinterpret_cast<const float4 *>(pB + (s + kTcAhead) * 16)) : zero4;
+        } else {
+          bufA[s % kTcAhead] = nA ? __ldg(reinterpret_cast<const float4 *>(nA + (s + kTcAhead - kTcKSteps) * 16)) : zero4;
+          bufB[s % kTcAhead] = nB ? __ldg(reinterpret_cast<const float4 *>(nB + (s + kTcAhead - kTcKSteps) * 16)) : zero4;
+        }
+        uint2 ha, la, hb, lb;
+        split4(xa, ha, la, bad);
+        split4(xb, hb, lb, bad);
+        const uint32_t slot = gs % kTcLoSlots;
+        mbar_wait(&hi_empty[s], (it & 1) ^ 1);
+        mbar_wait(&lo_empty[slot], ((gs / kTcLoSlots) & 1) ^ 1);
+        unsigned char *sh = base + kTcOffHi + s * kTcAMat;
+        unsigned char *sl = base + kTcOffLo + slot * kTcAMat;
+        *reinterpret_cast<uint2 *>(sh + dA) = ha;
+        *reinterpret_cast<uint2 *>(sl + dA) = la;
+        *reinterpret_cast<uint2 *>(sh + dB) = hb;
+        *reinterpret_cast<uint2 *>(sl + dB) = lb;
+        fence_async_smem();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&full[s]);
+      }
+      pA = nA;
+      pB = nB;
+    }
+    if (bad) *p.flag = 1;
+  } else if (warp == kTcMmaWarp) {
+    // ===== MMA issuer =====
+    if (elect_one()) {
+      const uint32_t b_hi = sbase, b_lo = sbase + kTcBMat;
+      uint32_t gs = 0, it = 0;
+      for (long long t = blockIdx.x; t < p.num_tiles; t += gridDim.x, ++it) {
+        const uint32_t acc = it & 1;
+        mbar_wait(&acc_empty[acc], ((it >> 1) & 1) ^ 1);
+        tc_fence_after();
+        const uint32_t tmem_d = tmem_base + acc * kTcN;
+        // small terms first, into the empty accumulator
+#pragma unroll
+        for (int s = 0; s < kTcKSteps; ++s, ++gs) {
+          const uint32_t slot = gs % kTcLoSlots;
+          mbar_wait(&full[s], it & 1);
+          tc_fence_after();
+          const uint64_t da_hi = umma_desc_plain(sbase + kTcOffHi + s * kTcAMat, kTcRows * 16);
+          const uint64_t da_lo = umma_desc_plain(sbase + kTcOffLo + slot * kTcAMat, kTcRows * 16);
+          const uint64_t db_hi = umma_desc_plain(b_hi + s * 2 * kTcBLbo, kTcBLbo);
+          const uint64_t db_lo = umma_desc_plain(b_lo + s * 2 * kTcBLbo, kTcBLbo);
+          umma_f16(tmem_d, da_lo, db_hi, kTcIdesc, s ? 1u : 0u);
+          umma_f16(tmem_d, da_hi, db_lo, kTcIdesc, 1u);
+          tc_commit(&lo_empty[slot]);
+        }
+#pragma unroll
+        for (int s = 0; s < kTcKSteps; ++s) {
+          const uint64_t da_hi = umma_desc_plain(sbase + kTcOffHi + s * kTcAMat, kTcRows * 16);
+          const uint64_t db_hi = umma_desc_plain(b_hi + s * 2 * kTcBLbo, kTcBLbo);
+          umma_f16(tmem_d, da_hi, db_hi, kTcIdesc, 1u);
+          tc_commit(&hi_empty[s]);
+        }
+        tc_commit(&acc_full[acc]);
+      }
+    }
+  } else {
+    // ===== epilogue: quadrant q = hop rows 32q..32q+31 = group q of the tile; two warps per quadrant =====
+    const int quad = warp & 3, half = warp >> 2;
+    float *my = s_out + quad * kTcGroupFrames * kTcOutPitch;
+    const int M = p.M;
+    const bool vec_ok = ((M & 3) == 0) && ((reinterpret_cast<uintptr_t>(p.out) & 15) == 0);
+    uint32_t it = 0;
+    for (long long t = blockIdx.x; t < p.num_tiles; t += gridDim.x, ++it) {
+      const TcGroup g = p.groups[t * 4 + quad];
+      const uint32_t acc = it & 1;
+      mbar_wait(&acc_full[acc], (it >> 1) & 1);
+      tc_fence_after();
+      const uint32_t taddr = tmem_base + ((uint32_t)(quad * 32) << 16) + acc * kTcN;
+      if (!(p.dbg & 1)) {
+        tc_epilogue_tile(p, half, taddr, my, lane);
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&acc_empty[acc]);
+      named_bar_sync(1 + quad, 64);  // both halves of the quadrant have staged their filters
+      if (g.nf > 0) {
+        // rows of a group are contiguous in the output and in the staging buffer (pitch M)
+        float *dst = p.out + g.row0 * M;
+        const int total = g.nf * M;
+        if (vec_ok) {
+          const float4 *s4 = reinterpret_cast<const float4 *>(my);
+          float4 *d4 = reinterpret_cast<float4 *>(dst);
+          for (int i = half * 32 + lane; i < (total >> 2); i += 64) d4[i] = s4[i];
+        } else {
+          for (int i = half * 32 + lane; i < total; i += 64) dst[i] = my[i];
+        }
+      }
+      named_bar_sync(1 + quad, 64);  // staging free for the next tile
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == kTcMmaWarp) {
+    tc_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512u) : "memory");
+  }
+}
+
+// ------------------------------------------------------------------------------------ host
+// Plan side: DFT matrix (fp16 hi/lo, shared-memory layout), per-half bin tables and ranges.
+// Covered shape: NFFT 512, stride 160, frame 320, a segment-form bank over <= 124 bins and
+// <= 40 filters.
+int build_tc_plan(spb_context *ctx, spb_plan *pl, const float4 *seg_rd) {
+  pl->tc_ok = false;
+  const spb_feature_params &q = pl->p;
+  if (q.nfft != 512 || q.frame_stride != kTcHop || q.frame_len != 2 * kTcHop) return SPB_OK;
+  if (pl->seg_nbins < 1 || pl->seg_nbins > kTcMaxBins || q.num_filters < 1 || q.num_filters > kTcOutPitch) return SPB_OK;
+  const int nb = pl->seg_nbins, kmin = pl->seg_kmin, M = q.num_filters;
+  const double two_pi = 6.283185307179586476925286766559;
+  std::vector<__half> hi((size_t)kTcBMat / 2), lo((size_t)kTcBMat / 2);
+  for (int n = 0; n < kTcHop; ++n)
+    for (int col = 0; col < kTcNAlloc; ++col) {
+      double w = 0.0;
+      const int j = col >> 1;
+      if (j < nb) {
+        const int r = (int)(((long long)(kmin + j) * n) % q.nfft);
+        const double ang = two_pi * (double)r / (double)q.nfft;
+        w = (col & 1) ? -sin(ang) : cos(ang);
+      }
+      const __half h = __float2half_rn((float)w);
+      const __half l = __float2half_rn((float)(w - (double)__half2float(h)));
+      const size_t idx = (size_t)(n >> 3) * (kTcNAlloc * 8) + (size_t)col * 8 + (n & 7);
+      hi[idx] = h;
+      lo[idx] = l;
+    }
+  // segments: seg_first[s] / seg_last[s] bins of segment s = 0..M
+  std::vector<int> seg_first, seg_last;
+  {
+    int first = 0;
+    for (int j = 0; j < nb; ++j)
+      if (seg_rd[j].z != 0.f) {
+        seg_first.push_back(first);
+        seg_last.push_back(j);
+        first = j + 1;
+      }
+  }
+  if ((int)seg_first.size() != M + 1) return SPB_OK;  // not the structure the epilogue walks
+  // split the segments between the two warps of a quadrant: half 1 starts at a chunk boundary cb
+  // with the first segment s1 that begins at or after it; half 0 walks segments 0..s1 (filters
+  // 0..s1-1), half 1 segments s1..M (filters s1..M-1).  Pick the cb with the best balance.
+  const int nch = (nb + 15) / 16;
+  int best_s1 = -1;
+  long best_cost = -1;
+  for (int cb = 1; cb < nch; ++cb) {
+    int s1 = -1;
+    for (int s = 1; s <= M - 1; ++s)
+      if (seg_first[s] >= cb * 16) { s1 = s; break; }
+    if (s1 < 0) continue;
+    const long c0 = (long)(seg_last[s1] / 16 + 1) * 16 * 13 + (long)(s1 + 1) * 10;
+    const long c1 = (long)(nch - seg_first[s1] / 16) * 16 * 13 + (long)(M + 1 - s1) * 10;
+    const long cost = std::max(c0, c1);
+    if (best_cost < 0 || cost < best_cost) { best_cost = cost; best_s1 = s1; }
+  }
+  pl->h_tc_tab.assign(2 * 128 * 4, 0.f);
+  for (int hf = 0; hf < 2; ++hf)
+    for (int i = 0; i < 4; ++i) pl->tc_endmask[hf][i] = 0;
+  int lo_bin[2] = {0, nb}, hi_bin[2] = {nb - 1, nb - 1};  // bins carrying weight per half
+  if (best_s1 > 0) {
+    hi_bin[0] = seg_last[best_s1];
+    lo_bin[1] = seg_first[best_s1];
+    pl->tc_half[0][0] = 0; pl->tc_half[0][1] = seg_last[best_s1] / 16 + 1; pl->tc_half[0][2] = 0; pl->tc_half[0][3] = 0;
+    pl->tc_half[1][0] = seg_first[best_s1] / 16; pl->tc_half[1][1] = nch; pl->tc_half[1][2] = best_s1; pl->tc_half[1][3] = best_s1;
+  } else {
+    pl->tc_half[0][0] = 0; pl->tc_half[0][1] = nch; pl->tc_half[0][2] = 0; pl->tc_half[0][3] = 0;
+    pl->tc_half[1][0] = 0; pl->tc_half[1][1] = 0; pl->tc_half[1][2] = 0; pl->tc_half[1][3] = M;
+  }
+  for (int hf = 0; hf < 2; ++hf)
+    for (int j = 0; j < nb; ++j) {
+      const int r = (int)(((long long)(kmin + j) * q.frame_stride) % q.nfft);
+      const double ang = two_pi * (double)r / (double)q.nfft;
+      // X_f = A_f + (cos - i sin) A_{f+1}
+      float *e = &pl->h_tc_tab[((size_t)hf * 128 + j) * 4];
+      const bool in = (j >= lo_bin[hf] && j <= hi_bin[hf]);
+      e[0] = in ? seg_rd[j].x : 0.f;
+      e[1] = in ? seg_rd[j].y : 0.f;
+      e[2] = (float)cos(ang);
+      e[3] = (float)-sin(ang);
+      if (in && seg_rd[j].z != 0.f) pl->tc_endmask[hf][j >> 5] |= 1u << (j & 31);
+    }
+  cudaError_t e;
+  if ((e = cudaMalloc(&pl->d_tc_whi, kTcBMat)) != cudaSuccess || (e = cudaMalloc(&pl->d_tc_wlo, kTcBMat)) != cudaSuccess ||
+      (e = cudaMalloc(&pl->d_tc_flag, 64)) != cudaSuccess)
+    return cuda_fail(ctx, e, "cudaMalloc(tc plan)");
+  if ((e = cudaMemcpy(pl->d_tc_whi, hi.data(), kTcBMat, cudaMemcpyHostToDevice)) != cudaSuccess ||
+      (e = cudaMemcpy(pl->d_tc_wlo, lo.data(), kTcBMat, cudaMemcpyHostToDevice)) != cudaSuccess ||
+      (e = cudaMemset(pl->d_tc_flag, 0, 64)) != cudaSuccess)
+    return cuda_fail(ctx, e, "cudaMemcpy(tc plan)");
+  pl->tc_ok = true;
+  return SPB_OK;
+}
+
+bool features_tc_supported(const FeatArgs &a) {
+  return a.plan && a.plan->tc_ok && a.tc_groups && a.num_tc_groups > 0 && (a.num_tc_groups % 4) == 0 &&
+         (a.mode == FEAT_LMFE || (a.mode == FEAT_MFE && a.energy == nullptr));
+}
+
+int launch_features_tc(spb_context *ctx, const FeatArgs &a) {
+  const spb_plan *pl = a.plan;
+  TcParams p;
+  p.samples = a.samples;
+  p.groups = a.tc_groups;
+  p.num_tiles = a.num_tc_groups / 4;
+  p.w_hi = (const __half *)pl->d_tc_whi;
+  p.w_lo = (const __half *)pl->d_tc_wlo;
+  for (int hf = 0; hf < 2; ++hf) {
+    for (int i = 0; i < 4; ++i) p.half[hf].endmask[i] = pl->tc_endmask[hf][i];
+    p.half[hf].ch_begin = pl->tc_half[hf][0];
+    p.half[hf].ch_end = pl->tc_half[hf][1];
+    p.half[hf].seg0 = pl->tc_half[hf][2];
+    p.half[hf].out_lo = pl->tc_half[hf][3];
+  }
+  p.M = a.M;
+  p.scale = (float)(1.0 / ((double)a.nfft * 1073741824.0));
+  p.mfe = (a.mode == FEAT_MFE) ? 1 : 0;
+  p.out = a.out;
+  p.flag = pl->d_tc_flag;
+  {
+    const char *e = getenv("SPB_TC_DBG");
+    p.dbg = e ? atoi(e) : 0;
+  }
+  if (ctx->tc_const_plan != pl) {
+    // the copy is stream-ordered and reads h_tc_tab (pageable) before returning
+    SPB_CUDA(ctx, cudaMemcpyToSymbolAsync(c_tc, pl->h_tc_tab.data(), sizeof(TcConst), 0, cudaMemcpyHostToDevice, ctx->stream));
+    ctx->tc_const_plan = pl;
+  }
+  int per_sm = 0;
+  int rc = configure_kernel(ctx, (const void *)features_tc_kernel, kTcThreads, kTcSmem, &per_sm);
+  if (rc) return rc;
+  if (per_sm < 1) return fail(ctx, SPB_ERR_INVALID, "features_tc: kernel does not fit on an SM");
+  long long grid = ctx->sm_count;
+  if (grid > p.num_tiles) grid = p.num_tiles;
+  if (grid < 1) return SPB_OK;
+  features_tc_kernel<<<(unsigned)grid, kTcThreads, kTcSmem, ctx->stream>>>(p);
+  SPB_LAUNCH_CHECK(ctx, "features_tc");
+  return SPB_OK;
+}
+
+}  // namespace spb

@@ -17,6 +17,7 @@
 namespace spb {
 constexpr int kFftWarps = SPB_FFT_NW;
 constexpr int kFftTileFrames = 4 * kFftWarps;
+constexpr int kTcGroupFrames = 31;   // tensor-core feature kernel: 32 hop rows -> 31 frames
 
 // ---------------------------------------------------------------- errors
 void set_global_error(const std::string &msg);
@@ -53,6 +54,7 @@ struct spb_context {
   void *pinned[2] = {nullptr, nullptr};
   size_t pinned_bytes = 0;
   std::map<int, spb::FftTables> fft_tables;  // by nfft
+  const spb_plan *tc_const_plan = nullptr;   // plan whose tables sit in the tensor-core kernel's constant bank
   std::vector<spb_plan *> plans;
   // (kernel function, dynamic smem) -> resident CTAs per SM, set up once per context
   std::map<std::pair<const void *, size_t>, int> kernel_cfg;
@@ -84,6 +86,14 @@ struct spb_plan {
   int4 *d_seg_ranges = nullptr;
   int seg_kmin = 0, seg_nbins = 0;
   std::vector<int32_t> h_band_lo, h_band_n, h_band_off;
+  // tensor-core hop-DFT kernel (feat_tc_kernels.cu): fp16 hi/lo DFT matrix in its shared-memory
+  // layout, per-bin {rise, fall, cos, sin}; tc_ok == false: plan shape not covered
+  bool tc_ok = false;
+  void *d_tc_whi = nullptr, *d_tc_wlo = nullptr;
+  std::vector<float> h_tc_tab;        // [2][128][4]: per epilogue half {rise, fall, cos, sin}
+  uint32_t tc_endmask[2][4] = {{0, 0, 0, 0}, {0, 0, 0, 0}};
+  int tc_half[2][4] = {{0, 0, 0, 0}, {0, 0, 0, 0}};  // {first chunk, end chunk, first segment, first filter}
+  int *d_tc_flag = nullptr;
 };
 
 namespace spb {
@@ -95,6 +105,14 @@ struct __align__(16) FftTile {
   long long row0;    // first output row of the tile
 };
 
+// tensor-core feature kernel: 32 consecutive hops of one utterance (31 frames); 4 per tile
+struct __align__(16) TcGroup {
+  long long gstart;  // first sample of the group's first hop in the arena
+  long long row0;    // first output row
+  int nf;            // frames (0: padding group)
+  int pad[3];
+};
+
 // a run of whole utterances whose intermediates fit in L2
 struct BatchChunk {
   int64_t u0, u1;        // utterances [u0, u1)
@@ -103,6 +121,7 @@ struct BatchChunk {
   int64_t row0, row1;    // output rows
   int64_t big0 = 0, big1 = 0;  // large-tile cmvnw tiles
   int64_t s_lo = 0, s_hi = 0;  // sample span [min start, max end) of the chunk's utterances
+  int64_t tc0 = 0, tc1 = 0;    // TcGroup range (multiples of 4)
 };
 }  // namespace spb
 
@@ -123,6 +142,7 @@ struct spb_batch {
   int2 *d_tiles = nullptr;               // [total_tiles] {utt, first frame}
   spb::FftTile *d_ftiles = nullptr;      // [total_tiles] full descriptors for the fast kernel
   int2 *d_cm_tiles = nullptr;            // [total_cm_tiles] {utt, first row}
+  spb::TcGroup *d_tc_groups = nullptr;    // tensor-core feature kernel tiles (nullptr: not usable)
   int4 *d_big_tiles = nullptr;           // large-tile cmvnw: {utt, first row, rows, 0}, longest first per chunk
   int big_rmax = 0;                      // 0: large-tile path not usable for this plan
   std::vector<spb::BatchChunk> chunks;   // pipeline units of the host-pointer calls
@@ -170,6 +190,10 @@ struct FeatArgs {
   const int64_t *frame_offsets;  // [U+1]
   const int2 *tiles;         // [num_tiles]
   const FftTile *ftiles;     // [num_tiles] or nullptr
+  const TcGroup *tc_groups = nullptr;  // tensor-core kernel: groups of this launch (4 per tile) or nullptr
+  int64_t num_tc_groups = 0;
+  const spb_plan *plan = nullptr;
+  const int *run_if = nullptr;         // fast512: run only when *run_if != 0
   int64_t num_tiles;
   int tile_frames;
   int L, S, nfft, K;
@@ -190,6 +214,9 @@ struct FeatArgs {
 int launch_features_generic(spb_context *ctx, const FeatArgs &a, const FftTables &t);
 bool fast512_supported(const FeatArgs &a);
 int launch_features_fast512(spb_context *ctx, const FeatArgs &a, const FftTables &t);
+bool features_tc_supported(const FeatArgs &a);
+int launch_features_tc(spb_context *ctx, const FeatArgs &a);
+int build_tc_plan(spb_context *ctx, spb_plan *pl, const float4 *seg_rd);  // seg_rd: host copy, seg_nbins entries
 bool fast1024_supported(const FeatArgs &a);
 int launch_features_fast1024(spb_context *ctx, const FeatArgs &a, const FftTables &t);
 
