@@ -88,6 +88,7 @@ struct TcParams {
   TcHalf half[2];
   int M;
   float scale;               // 1 / (NFFT * 2^30)
+  float ln_scale;            // ln(scale)
   int mfe;                   // 1: no log
   float *out;
   int *flag;                 // set when a sample cannot be split (|x| >= 2, NaN, inf)
@@ -135,10 +136,9 @@ __device__ __forceinline__ void tmem_ld32_nowait(uint32_t taddr, uint32_t (&v)[3
 __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 
 // four scaled samples -> fp16 hi and lo halves (two 32-bit words each)
-__device__ __forceinline__ void split4(const float4 x, uint2 &hi, uint2 &lo, bool &bad) {
+// bad: bit 15 / 31 set when a half came out as inf or NaN (|x| >= 2, NaN, inf)
+__device__ __forceinline__ void split4(const float4 x, uint2 &hi, uint2 &lo, uint32_t &bad) {
   const float a = x.x * kTcInScale, b = x.y * kTcInScale, c = x.z * kTcInScale, d = x.w * kTcInScale;
-  const float m = fmaxf(fmaxf(fabsf(a), fabsf(b)), fmaxf(fabsf(c), fabsf(d)));
-  bad |= !(m < 65504.f) || (a != a) || (b != b) || (c != c) || (d != d);
   const __half2 h0 = __floats2half2_rn(a, b), h1 = __floats2half2_rn(c, d);
   const float2 f0 = __half22float2(h0), f1 = __half22float2(h1);
   const __half2 l0 = __floats2half2_rn(a - f0.x, b - f0.y), l1 = __floats2half2_rn(c - f1.x, d - f1.y);
@@ -146,23 +146,41 @@ __device__ __forceinline__ void split4(const float4 x, uint2 &hi, uint2 &lo, boo
   hi.y = *reinterpret_cast<const uint32_t *>(&h1);
   lo.x = *reinterpret_cast<const uint32_t *>(&l0);
   lo.y = *reinterpret_cast<const uint32_t *>(&l1);
+  bad |= ((hi.x & 0x7fff7fffu) + 0x04000400u) | ((hi.y & 0x7fff7fffu) + 0x04000400u);
 }
+
+// cos / sin of 2 pi m / 16: the hop rotation e^{-2 pi i S k / NFFT} = e^{-2 pi i (5k mod 16) / 16}
+// at S = 160, NFFT = 512 has period 16 in k, so with kmin mod 16 known at compile time it is an
+// immediate operand of the unrolled bin loop.
+__device__ constexpr float kCos16[16] = {1.f, 0.92387953251128674f, 0.70710678118654752f, 0.38268343236508977f,
+                                         0.f, -0.38268343236508977f, -0.70710678118654752f, -0.92387953251128674f,
+                                         -1.f, -0.92387953251128674f, -0.70710678118654752f, -0.38268343236508977f,
+                                         0.f, 0.38268343236508977f, 0.70710678118654752f, 0.92387953251128674f};
+__device__ constexpr float kSin16[16] = {0.f, 0.38268343236508977f, 0.70710678118654752f, 0.92387953251128674f,
+                                         1.f, 0.92387953251128674f, 0.70710678118654752f, 0.38268343236508977f,
+                                         0.f, -0.38268343236508977f, -0.70710678118654752f, -0.92387953251128674f,
+                                         -1.f, -0.92387953251128674f, -0.70710678118654752f, -0.38268343236508977f};
 
 // One tile of one epilogue warp: lane = hop row of the quadrant, frame = hops (lane, lane + 1).
 // The chunk loop is NOT unrolled: the straight-line version (123 bins x ~40 instructions, twice)
 // ran at the instruction-fetch rate (ncu: stall_no_inst on every line).
+// KM = kmin mod 16 (rotation as immediates) or -1 (rotation from the table).
+template <int KM>
 __device__ __forceinline__ void tc_epilogue_tile(const TcParams &p, const int half, const uint32_t taddr, float *my,
                                                  const int lane) {
-  const int M = p.M;
   const int ch_begin = half ? p.half[1].ch_begin : p.half[0].ch_begin;
   const int ch_end = half ? p.half[1].ch_end : p.half[0].ch_end;
-  const int out_lo = half ? p.half[1].out_lo : p.half[0].out_lo;
   const uint32_t m0 = half ? p.half[1].endmask[0] : p.half[0].endmask[0];
   const uint32_t m1 = half ? p.half[1].endmask[1] : p.half[0].endmask[1];
   const uint32_t m2 = half ? p.half[1].endmask[2] : p.half[0].endmask[2];
   const uint32_t m3 = half ? p.half[1].endmask[3] : p.half[0].endmask[3];
   float rise = 0.f, fall = 0.f, prev_u = 0.f;
-  int seg = half ? p.half[1].seg0 : p.half[0].seg0;
+  // the first flush of a half only latches U of its first segment (filter j = U[j] + D[j+1])
+  int skip = 1;
+  const bool lane_ok = lane < kTcGroupFrames;
+  float *pout = my + lane * p.M + (half ? p.half[1].out_lo : 0);
+  const float ln_scale = p.ln_scale, scale = p.scale;
+  const bool mfe = p.mfe != 0;
 #pragma unroll 1
   for (int ch = ch_begin; ch < ch_end; ++ch) {
     uint32_t v[32];
@@ -173,31 +191,45 @@ __device__ __forceinline__ void tc_epilogue_tile(const TcParams &p, const int ha
     tmem_ld_wait();
 #pragma unroll
     for (int j = 0; j < 16; ++j) {
-      const float4 w = tb[j];
+      float wr, wf, cr, ci;
+      if (KM >= 0) {
+        const float2 w = *reinterpret_cast<const float2 *>(&tb[j]);
+        wr = w.x; wf = w.y;
+        cr = kCos16[(5 * (KM + j)) & 15];
+        ci = -kSin16[(5 * (KM + j)) & 15];
+      } else {
+        const float4 w = tb[j];
+        wr = w.x; wf = w.y; cr = w.z; ci = w.w;
+      }
       const float a_re = __uint_as_float(v[2 * j]), a_im = __uint_as_float(v[2 * j + 1]);
       const float b_re = __shfl_down_sync(0xffffffffu, a_re, 1);
       const float b_im = __shfl_down_sync(0xffffffffu, a_im, 1);
-      const float xr = fmaf(-w.w, b_im, fmaf(w.z, b_re, a_re));
-      const float xi = fmaf(w.w, b_re, fmaf(w.z, b_im, a_im));
+      const float xr = fmaf(-ci, b_im, fmaf(cr, b_re, a_re));
+      const float xi = fmaf(ci, b_re, fmaf(cr, b_im, a_im));
       const float pw = fmaf(xr, xr, xi * xi);
-      rise = fmaf(w.x, pw, rise);
-      fall = fmaf(w.y, pw, fall);
+      rise = fmaf(wr, pw, rise);
+      fall = fmaf(wf, pw, fall);
       if ((mask >> j) & 1u) {
-        const int o = seg - 1;
-        if (o >= out_lo && lane < kTcGroupFrames) {
-          float a = (prev_u + fall) * p.scale;
-          if (a == 0.f) a = kTcEps;  // functions.zero_handling (feature.py:217)
-          my[lane * M + o] = p.mfe ? a : __logf(a);
+        if (skip == 0) {
+          const float a = prev_u + fall;  // unscaled (x 2^30 NFFT): never denormal for real input
+          float lg;
+          asm("lg2.approx.ftz.f32 %0, %1;" : "=f"(lg) : "f"(a));
+          // functions.zero_handling (feature.py:217): exact zero -> eps
+          float r = mfe ? a * scale : fmaf(lg, 0.69314718055994531f, ln_scale);
+          if (a == 0.f) r = mfe ? kTcEps : -36.04365338911715f;
+          if (lane_ok) *pout = r;
+          ++pout;
         }
+        skip = 0;
         prev_u = rise;
         rise = 0.f;
         fall = 0.f;
-        ++seg;
       }
     }
   }
 }
 
+template <int KM>
 __global__ void __launch_bounds__(kTcThreads, 1) features_tc_kernel(const TcParams p) {
   extern __shared__ __align__(128) unsigned char tc_smem[];
   unsigned char *base = tc_smem;
@@ -255,13 +287,13 @@ __global__ void __launch_bounds__(kTcThreads, 1) features_tc_kernel(const TcPara
     const int rA = c >> 2, rB = 64 + (c >> 2);       // the two hop rows this thread feeds
     const uint32_t dA = (uint32_t)((q >> 1) * (kTcRows * 16) + rA * 16 + (q & 1) * 8);
     const uint32_t dB = (uint32_t)((q >> 1) * (kTcRows * 16) + rB * 16 + (q & 1) * 8);
-    bool bad = false;
+    uint32_t bad = 0;
     const float4 zero4 = make_float4(0.f, 0.f, 0.f, 0.f);
     auto row_ptr = [&](long long t, int r) -> const float * {
       if (t >= p.num_tiles) return nullptr;
       const TcGroup g = p.groups[t * 4 + (r >> 5)];
       const int i = r & 31;
-      return (g.nf > 0 && i <= g.nf) ? p.samples + g.gstart + (long long)i * kTcHop + q * 4 : nullptr;
+      return (g.nf > 0 && i <= g.nf && !(p.dbg & 64)) ? p.samples + g.gstart + (long long)i * kTcHop + q * 4 : nullptr;
     };
     long long t = blockIdx.x;
     const float *pA = row_ptr(t, rA), *pB = row_ptr(t, rB);
@@ -274,6 +306,14 @@ __global__ void __launch_bounds__(kTcThreads, 1) features_tc_kernel(const TcPara
     uint32_t gs = 0, it = 0;  // k-steps, tiles produced so far
     for (; t < p.num_tiles; t += gridDim.x, ++it) {
       const float *nA = row_ptr(t + gridDim.x, rA), *nB = row_ptr(t + gridDim.x, rB);
+      if (c < 4 && !(p.dbg & 32)) {
+        // pull the samples of the tile after next into L2 with the TMA engine (one 20 KB run per group)
+        const long long tp = t + 2 * (long long)gridDim.x;
+        if (tp < p.num_tiles) {
+          const TcGroup g = p.groups[tp * 4 + c];
+          if (g.nf > 0) bulk_prefetch_l2(p.samples + g.gstart, (uint32_t)(g.nf + 1) * (kTcHop * 4));
+        }
+      }
 #pragma unroll
       for (int s = 0; s < kTcKSteps; ++s, ++gs) {
         const float4 xa = bufA[s % kTcAhead], xb = bufB[s % kTcAhead];
@@ -292,18 +332,20 @@ __global__ void __launch_bounds__(kTcThreads, 1) features_tc_kernel(const TcPara
         mbar_wait(&lo_empty[slot], ((gs / kTcLoSlots) & 1) ^ 1);
         unsigned char *sh = base + kTcOffHi + s * kTcAMat;
         unsigned char *sl = base + kTcOffLo + slot * kTcAMat;
-        *reinterpret_cast<uint2 *>(sh + dA) = ha;
-        *reinterpret_cast<uint2 *>(sl + dA) = la;
-        *reinterpret_cast<uint2 *>(sh + dB) = hb;
-        *reinterpret_cast<uint2 *>(sl + dB) = lb;
-        fence_async_smem();
+        if (!(p.dbg & 2)) {
+          *reinterpret_cast<uint2 *>(sh + dA) = ha;
+          *reinterpret_cast<uint2 *>(sl + dA) = la;
+          *reinterpret_cast<uint2 *>(sh + dB) = hb;
+          *reinterpret_cast<uint2 *>(sl + dB) = lb;
+        }
+        if (!(p.dbg & 8)) fence_async_smem();
         __syncwarp();
         if (lane == 0) mbar_arrive(&full[s]);
       }
       pA = nA;
       pB = nB;
     }
-    if (bad) *p.flag = 1;
+    if (bad & 0x80008000u) *p.flag = 1;
   } else if (warp == kTcMmaWarp) {
     // ===== MMA issuer =====
     if (elect_one()) {
@@ -324,15 +366,17 @@ __global__ void __launch_bounds__(kTcThreads, 1) features_tc_kernel(const TcPara
           const uint64_t da_lo = umma_desc_plain(sbase + kTcOffLo + slot * kTcAMat, kTcRows * 16);
           const uint64_t db_hi = umma_desc_plain(b_hi + s * 2 * kTcBLbo, kTcBLbo);
           const uint64_t db_lo = umma_desc_plain(b_lo + s * 2 * kTcBLbo, kTcBLbo);
-          umma_f16(tmem_d, da_lo, db_hi, kTcIdesc, s ? 1u : 0u);
-          umma_f16(tmem_d, da_hi, db_lo, kTcIdesc, 1u);
+          if (!(p.dbg & 4)) {
+            umma_f16(tmem_d, da_lo, db_hi, kTcIdesc, s ? 1u : 0u);
+            umma_f16(tmem_d, da_hi, db_lo, kTcIdesc, 1u);
+          }
           tc_commit(&lo_empty[slot]);
         }
 #pragma unroll
         for (int s = 0; s < kTcKSteps; ++s) {
           const uint64_t da_hi = umma_desc_plain(sbase + kTcOffHi + s * kTcAMat, kTcRows * 16);
           const uint64_t db_hi = umma_desc_plain(b_hi + s * 2 * kTcBLbo, kTcBLbo);
-          umma_f16(tmem_d, da_hi, db_hi, kTcIdesc, 1u);
+          if (!(p.dbg & 4)) umma_f16(tmem_d, da_hi, db_hi, kTcIdesc, 1u);
           tc_commit(&hi_empty[s]);
         }
         tc_commit(&acc_full[acc]);
@@ -352,7 +396,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) features_tc_kernel(const TcPara
       tc_fence_after();
       const uint32_t taddr = tmem_base + ((uint32_t)(quad * 32) << 16) + acc * kTcN;
       if (!(p.dbg & 1)) {
-        tc_epilogue_tile(p, half, taddr, my, lane);
+        tc_epilogue_tile<KM>(p, half, taddr, my, lane);
       }
       tc_fence_before();
       __syncwarp();
@@ -496,6 +540,7 @@ int launch_features_tc(spb_context *ctx, const FeatArgs &a) {
   }
   p.M = a.M;
   p.scale = (float)(1.0 / ((double)a.nfft * 1073741824.0));
+  p.ln_scale = (float)log(1.0 / ((double)a.nfft * 1073741824.0));
   p.mfe = (a.mode == FEAT_MFE) ? 1 : 0;
   p.out = a.out;
   p.flag = pl->d_tc_flag;
@@ -509,13 +554,15 @@ int launch_features_tc(spb_context *ctx, const FeatArgs &a) {
     ctx->tc_const_plan = pl;
   }
   int per_sm = 0;
-  int rc = configure_kernel(ctx, (const void *)features_tc_kernel, kTcThreads, kTcSmem, &per_sm);
+  const bool km5 = (pl->seg_kmin & 15) == 5;  // the speechpy default bank starts at bin 5
+  auto kern = km5 ? features_tc_kernel<5> : features_tc_kernel<-1>;
+  int rc = configure_kernel(ctx, (const void *)kern, kTcThreads, kTcSmem, &per_sm);
   if (rc) return rc;
   if (per_sm < 1) return fail(ctx, SPB_ERR_INVALID, "features_tc: kernel does not fit on an SM");
   long long grid = ctx->sm_count;
   if (grid > p.num_tiles) grid = p.num_tiles;
   if (grid < 1) return SPB_OK;
-  features_tc_kernel<<<(unsigned)grid, kTcThreads, kTcSmem, ctx->stream>>>(p);
+  kern<<<(unsigned)grid, kTcThreads, kTcSmem, ctx->stream>>>(p);
   SPB_LAUNCH_CHECK(ctx, "features_tc");
   return SPB_OK;
 }
