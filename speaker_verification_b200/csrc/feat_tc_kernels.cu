@@ -45,17 +45,15 @@ constexpr int kTcRows = 128;                      // hop rows per tile (MMA M)
 constexpr int kTcN = 256;                         // MMA N
 constexpr int kTcNAlloc = 248;                    // stored columns: (re, im) of up to 124 bins
 constexpr int kTcMaxBins = kTcNAlloc / 2;
-constexpr int kTcLoSlots = 3;                     // xl ring depth (k-steps)
+constexpr int kTcLoSlots = 7;                     // xl ring depth (k-steps)
 constexpr int kTcAhead = 5;                       // converter load distance (k-steps)
-constexpr int kTcOutPitch = 40;                   // staging rows: up to 40 filters
+constexpr int kTcOutPitch = 40;                   // at most this many filters
 constexpr uint32_t kTcBLbo = kTcNAlloc * 16;             // 3 968 B between the k-chunks of W
 constexpr uint32_t kTcBMat = (kTcHop / 8) * kTcBLbo;     // 79 360 B: [k/8][col][8 halves]
 constexpr uint32_t kTcAMat = 2 * kTcRows * 16;           // 4 096 B per k-step: [2][row][8 halves]
 constexpr uint32_t kTcOffHi = 2 * kTcBMat;               // xh: 10 k-steps
 constexpr uint32_t kTcOffLo = kTcOffHi + kTcKSteps * kTcAMat;
-constexpr uint32_t kTcOffOut = kTcOffLo + kTcLoSlots * kTcAMat;
-constexpr uint32_t kTcOutBytes = 4 * kTcGroupFrames * kTcOutPitch * 4;
-constexpr uint32_t kTcOffBars = kTcOffOut + kTcOutBytes;
+constexpr uint32_t kTcOffBars = kTcOffLo + kTcLoSlots * kTcAMat;
 constexpr uint32_t kTcSmem = kTcOffBars + 256;
 static_assert(kTcSmem <= 232448, "features_tc: shared memory budget");
 constexpr int kTcEpiWarps = 8, kTcMmaWarp = 8, kTcCvtWarp0 = 9, kTcCvtWarps = 8;
@@ -90,6 +88,7 @@ struct TcParams {
   float scale;               // 1 / (NFFT * 2^30)
   float ln_scale;            // ln(scale)
   int mfe;                   // 1: no log
+  int vec4;                  // both halves emit multiples of four filters and rows are 16-byte aligned
   float *out;
   int *flag;                 // set when a sample cannot be split (|x| >= 2, NaN, inf)
   int dbg;                   // SPB_TC_DBG phase knobs (timing experiments only)
@@ -166,8 +165,8 @@ __device__ constexpr float kSin16[16] = {0.f, 0.38268343236508977f, 0.7071067811
 // ran at the instruction-fetch rate (ncu: stall_no_inst on every line).
 // KM = kmin mod 16 (rotation as immediates) or -1 (rotation from the table).
 template <int KM>
-__device__ __forceinline__ void tc_epilogue_tile(const TcParams &p, const int half, const uint32_t taddr, float *my,
-                                                 const int lane) {
+__device__ __forceinline__ void tc_epilogue_tile(const TcParams &p, const int half, const uint32_t taddr,
+                                                 float *pout, const bool row_ok) {
   const int ch_begin = half ? p.half[1].ch_begin : p.half[0].ch_begin;
   const int ch_end = half ? p.half[1].ch_end : p.half[0].ch_end;
   const uint32_t m0 = half ? p.half[1].endmask[0] : p.half[0].endmask[0];
@@ -177,38 +176,45 @@ __device__ __forceinline__ void tc_epilogue_tile(const TcParams &p, const int ha
   float rise = 0.f, fall = 0.f, prev_u = 0.f;
   // the first flush of a half only latches U of its first segment (filter j = U[j] + D[j+1])
   int skip = 1;
-  const bool lane_ok = lane < kTcGroupFrames;
-  float *pout = my + lane * p.M + (half ? p.half[1].out_lo : 0);
+  // outputs leave in runs of four filters (one 16-byte store per lane; the rows of a warp are
+  // 4 M bytes apart, L2 merges the sectors) when the half's filter range allows it
+  const bool vec4 = p.vec4 != 0;
+  float o0 = 0.f, o1 = 0.f, o2 = 0.f;
+  int cnt = 0;
   const float ln_scale = p.ln_scale, scale = p.scale;
   const bool mfe = p.mfe != 0;
 #pragma unroll 1
   for (int ch = ch_begin; ch < ch_end; ++ch) {
     uint32_t v[32];
-    tmem_ld32_nowait(taddr + ch * 32, v);
+    tmem_ld32(taddr + ch * 32, v);  // load + wait::ld in one asm: v must not be read before the wait
     const uint32_t mw = (ch < 4) ? ((ch < 2) ? m0 : m1) : ((ch < 6) ? m2 : m3);
     const uint32_t mask = mw >> ((ch & 1) * 16);
     const float4 *tb = &c_tc.tab[half][ch * 16];
-    tmem_ld_wait();
+    // pass A, branch-free so the 16 bins overlap: X = A_own + c A_next, |X|^2
+    float pw[16];
 #pragma unroll
     for (int j = 0; j < 16; ++j) {
-      float wr, wf, cr, ci;
+      float cr, ci;
       if (KM >= 0) {
-        const float2 w = *reinterpret_cast<const float2 *>(&tb[j]);
-        wr = w.x; wf = w.y;
         cr = kCos16[(5 * (KM + j)) & 15];
         ci = -kSin16[(5 * (KM + j)) & 15];
       } else {
-        const float4 w = tb[j];
-        wr = w.x; wf = w.y; cr = w.z; ci = w.w;
+        cr = tb[j].z;
+        ci = tb[j].w;
       }
       const float a_re = __uint_as_float(v[2 * j]), a_im = __uint_as_float(v[2 * j + 1]);
       const float b_re = __shfl_down_sync(0xffffffffu, a_re, 1);
       const float b_im = __shfl_down_sync(0xffffffffu, a_im, 1);
       const float xr = fmaf(-ci, b_im, fmaf(cr, b_re, a_re));
       const float xi = fmaf(ci, b_re, fmaf(cr, b_im, a_im));
-      const float pw = fmaf(xr, xr, xi * xi);
-      rise = fmaf(wr, pw, rise);
-      fall = fmaf(wf, pw, fall);
+      pw[j] = fmaf(xr, xr, xi * xi);
+    }
+    // pass B: segment sums, a flush where the mask says a segment ends
+#pragma unroll
+    for (int j = 0; j < 16; ++j) {
+      const float2 w = *reinterpret_cast<const float2 *>(&tb[j]);
+      rise = fmaf(w.x, pw[j], rise);
+      fall = fmaf(w.y, pw[j], fall);
       if ((mask >> j) & 1u) {
         if (skip == 0) {
           const float a = prev_u + fall;  // unscaled (x 2^30 NFFT): never denormal for real input
@@ -217,8 +223,17 @@ __device__ __forceinline__ void tc_epilogue_tile(const TcParams &p, const int ha
           // functions.zero_handling (feature.py:217): exact zero -> eps
           float r = mfe ? a * scale : fmaf(lg, 0.69314718055994531f, ln_scale);
           if (a == 0.f) r = mfe ? kTcEps : -36.04365338911715f;
-          if (lane_ok) *pout = r;
-          ++pout;
+          if (vec4) {
+            if ((cnt & 3) == 3) {
+              if (row_ok) *reinterpret_cast<float4 *>(pout) = make_float4(o0, o1, o2, r);
+              pout += 4;
+            }
+            o0 = o1; o1 = o2; o2 = r;
+            ++cnt;
+          } else {
+            if (row_ok) *pout = r;
+            ++pout;
+          }
         }
         skip = 0;
         prev_u = rise;
@@ -233,14 +248,14 @@ template <int KM>
 __global__ void __launch_bounds__(kTcThreads, 1) features_tc_kernel(const TcParams p) {
   extern __shared__ __align__(128) unsigned char tc_smem[];
   unsigned char *base = tc_smem;
-  float *s_out = reinterpret_cast<float *>(base + kTcOffOut);
   uint64_t *bars = reinterpret_cast<uint64_t *>(base + kTcOffBars);
   uint64_t *full = bars;                         // [10] k-step s of the tile converted (8 converter warps)
   uint64_t *hi_empty = bars + 10;                // [10] xh of k-step s consumed (tcgen05.commit)
   uint64_t *lo_empty = bars + 20;                // [3]  xl ring slot consumed
-  uint64_t *acc_full = bars + 23;                // [2]
-  uint64_t *acc_empty = bars + 25;               // [2] 8 epilogue warps
-  uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + 27);
+  uint64_t *acc_full = bars + 20 + kTcLoSlots;   // [2]
+  uint64_t *acc_empty = acc_full + 2;            // [2] 8 epilogue warps
+  uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(acc_empty + 2);
+  static_assert((20 + kTcLoSlots + 4) * 8 + 4 <= 256, "barrier block");
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -291,7 +306,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) features_tc_kernel(const TcPara
     const float4 zero4 = make_float4(0.f, 0.f, 0.f, 0.f);
     auto row_ptr = [&](long long t, int r) -> const float * {
       if (t >= p.num_tiles) return nullptr;
-      const TcGroup g = p.groups[t * 4 + (r >> 5)];
+      const TcGroup g = p.groups[((p.dbg & 128) ? (long long)blockIdx.x : t) * 4 + (r >> 5)];
       const int i = r & 31;
       return (g.nf > 0 && i <= g.nf && !(p.dbg & 64)) ? p.samples + g.gstart + (long long)i * kTcHop + q * 4 : nullptr;
     };
@@ -327,8 +342,11 @@ __global__ void __launch_bounds__(kTcThreads, 1) features_tc_kernel(const TcPara
         uint2 ha, la, hb, lb;
         split4(xa, ha, la, bad);
         split4(xb, hb, lb, bad);
+        // keep the conversion ahead of the waits (the compiler otherwise sinks it below them and
+        // every k-step pays wait + conversion latency in series)
+        asm volatile("" ::"r"(ha.x), "r"(ha.y), "r"(la.x), "r"(la.y), "r"(hb.x), "r"(hb.y), "r"(lb.x), "r"(lb.y));
         const uint32_t slot = gs % kTcLoSlots;
-        mbar_wait(&hi_empty[s], (it & 1) ^ 1);
+        if (s == 0 || s == kTcKSteps / 2) mbar_wait(&hi_empty[s ? 1 : 0], (it & 1) ^ 1);
         mbar_wait(&lo_empty[slot], ((gs / kTcLoSlots) & 1) ^ 1);
         unsigned char *sh = base + kTcOffHi + s * kTcAMat;
         unsigned char *sl = base + kTcOffLo + slot * kTcAMat;
@@ -372,22 +390,23 @@ __global__ void __launch_bounds__(kTcThreads, 1) features_tc_kernel(const TcPara
           }
           tc_commit(&lo_empty[slot]);
         }
+        // xh k-steps are handed back in two batches (a tcgen05.commit per MMA costs more than it hides)
 #pragma unroll
         for (int s = 0; s < kTcKSteps; ++s) {
           const uint64_t da_hi = umma_desc_plain(sbase + kTcOffHi + s * kTcAMat, kTcRows * 16);
           const uint64_t db_hi = umma_desc_plain(b_hi + s * 2 * kTcBLbo, kTcBLbo);
           if (!(p.dbg & 4)) umma_f16(tmem_d, da_hi, db_hi, kTcIdesc, 1u);
-          tc_commit(&hi_empty[s]);
+          if (s == kTcKSteps / 2 - 1) tc_commit(&hi_empty[0]);
         }
+        tc_commit(&hi_empty[1]);
         tc_commit(&acc_full[acc]);
       }
     }
   } else {
     // ===== epilogue: quadrant q = hop rows 32q..32q+31 = group q of the tile; two warps per quadrant =====
     const int quad = warp & 3, half = warp >> 2;
-    float *my = s_out + quad * kTcGroupFrames * kTcOutPitch;
     const int M = p.M;
-    const bool vec_ok = ((M & 3) == 0) && ((reinterpret_cast<uintptr_t>(p.out) & 15) == 0);
+    const int col0 = half ? p.half[1].out_lo : 0;
     uint32_t it = 0;
     for (long long t = blockIdx.x; t < p.num_tiles; t += gridDim.x, ++it) {
       const TcGroup g = p.groups[t * 4 + quad];
@@ -395,26 +414,10 @@ __global__ void __launch_bounds__(kTcThreads, 1) features_tc_kernel(const TcPara
       mbar_wait(&acc_full[acc], (it >> 1) & 1);
       tc_fence_after();
       const uint32_t taddr = tmem_base + ((uint32_t)(quad * 32) << 16) + acc * kTcN;
-      if (!(p.dbg & 1)) {
-        tc_epilogue_tile<KM>(p, half, taddr, my, lane);
-      }
+      if (!(p.dbg & 1)) tc_epilogue_tile<KM>(p, half, taddr, p.out + (g.row0 + lane) * M + col0, lane < g.nf);
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(&acc_empty[acc]);
-      named_bar_sync(1 + quad, 64);  // both halves of the quadrant have staged their filters
-      if (g.nf > 0) {
-        // rows of a group are contiguous in the output and in the staging buffer (pitch M)
-        float *dst = p.out + g.row0 * M;
-        const int total = g.nf * M;
-        if (vec_ok) {
-          const float4 *s4 = reinterpret_cast<const float4 *>(my);
-          float4 *d4 = reinterpret_cast<float4 *>(dst);
-          for (int i = half * 32 + lane; i < (total >> 2); i += 64) d4[i] = s4[i];
-        } else {
-          for (int i = half * 32 + lane; i < total; i += 64) dst[i] = my[i];
-        }
-      }
-      named_bar_sync(1 + quad, 64);  // staging free for the next tile
     }
   }
   tc_fence_before();
@@ -464,22 +467,21 @@ int build_tc_plan(spb_context *ctx, spb_plan *pl, const float4 *seg_rd) {
       }
   }
   if ((int)seg_first.size() != M + 1) return SPB_OK;  // not the structure the epilogue walks
-  // split the segments between the two warps of a quadrant: half 1 starts at a chunk boundary cb
-  // with the first segment s1 that begins at or after it; half 0 walks segments 0..s1 (filters
-  // 0..s1-1), half 1 segments s1..M (filters s1..M-1).  Pick the cb with the best balance.
+  // split the segments between the two warps of a quadrant: half 0 walks segments 0..s1 (filters
+  // 0..s1-1), half 1 segments s1..M (filters s1..M-1; bins before segment s1 carry zero weights).
+  // Pick the s1 with the best balance, a multiple of four when M is (16-byte output stores).
   const int nch = (nb + 15) / 16;
+  const bool want4 = (M % 4) == 0;
   int best_s1 = -1;
   long best_cost = -1;
-  for (int cb = 1; cb < nch; ++cb) {
-    int s1 = -1;
-    for (int s = 1; s <= M - 1; ++s)
-      if (seg_first[s] >= cb * 16) { s1 = s; break; }
-    if (s1 < 0) continue;
+  for (int s1 = 1; s1 <= M - 1; ++s1) {
+    if (want4 && (s1 % 4) != 0) continue;
     const long c0 = (long)(seg_last[s1] / 16 + 1) * 16 * 13 + (long)(s1 + 1) * 10;
     const long c1 = (long)(nch - seg_first[s1] / 16) * 16 * 13 + (long)(M + 1 - s1) * 10;
     const long cost = std::max(c0, c1);
     if (best_cost < 0 || cost < best_cost) { best_cost = cost; best_s1 = s1; }
   }
+  pl->tc_vec4 = want4;
   pl->h_tc_tab.assign(2 * 128 * 4, 0.f);
   for (int hf = 0; hf < 2; ++hf)
     for (int i = 0; i < 4; ++i) pl->tc_endmask[hf][i] = 0;
@@ -542,6 +544,7 @@ int launch_features_tc(spb_context *ctx, const FeatArgs &a) {
   p.scale = (float)(1.0 / ((double)a.nfft * 1073741824.0));
   p.ln_scale = (float)log(1.0 / ((double)a.nfft * 1073741824.0));
   p.mfe = (a.mode == FEAT_MFE) ? 1 : 0;
+  p.vec4 = (pl->tc_vec4 && (reinterpret_cast<uintptr_t>(a.out) & 15) == 0) ? 1 : 0;
   p.out = a.out;
   p.flag = pl->d_tc_flag;
   {

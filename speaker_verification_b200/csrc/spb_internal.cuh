@@ -93,6 +93,7 @@ struct spb_plan {
   std::vector<float> h_tc_tab;        // [2][128][4]: per epilogue half {rise, fall, cos, sin}
   uint32_t tc_endmask[2][4] = {{0, 0, 0, 0}, {0, 0, 0, 0}};
   int tc_half[2][4] = {{0, 0, 0, 0}, {0, 0, 0, 0}};  // {first chunk, end chunk, first segment, first filter}
+  bool tc_vec4 = false;               // filter ranges of both halves are multiples of four
   int *d_tc_flag = nullptr;
 };
 
