@@ -91,6 +91,7 @@ struct TcParams {
   int vec4;                  // both halves emit multiples of four filters and rows are 16-byte aligned
   float *out;
   int *flag;                 // set when a sample cannot be split (|x| >= 2, NaN, inf)
+  const float *zeros;        // 1 KB of zeros: the hop rows past the end of a group read these
   int dbg;                   // SPB_TC_DBG phase knobs (timing experiments only)
 };
 
@@ -116,6 +117,21 @@ __device__ __forceinline__ void umma_f16(uint32_t tmem_d, uint64_t desc_a, uint6
 }
 __device__ __forceinline__ void fence_async_smem() {
   asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+}
+// mbarrier wait that lets the hardware park the warp (suspend-time hint) instead of spinning:
+// 17 warps polling barriers took ~1/3 of the issue slots of the kernel
+__device__ __forceinline__ void mbar_wait_park(uint64_t *bar, uint32_t parity) {
+  const uint32_t a = smem_u32(bar);
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      "PARK_LOOP:\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1, %2;\n\t"
+      "@p bra PARK_DONE;\n\t"
+      "bra PARK_LOOP;\n\t"
+      "PARK_DONE:\n\t"
+      "}" ::"r"(a), "r"(parity), "r"(20000u)
+      : "memory");
 }
 __device__ __forceinline__ void named_bar_sync(int id, int threads) {
   asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(threads) : "memory");
@@ -164,7 +180,8 @@ __device__ constexpr float kSin16[16] = {0.f, 0.38268343236508977f, 0.7071067811
 // The chunk loop is NOT unrolled: the straight-line version (123 bins x ~40 instructions, twice)
 // ran at the instruction-fetch rate (ncu: stall_no_inst on every line).
 // KM = kmin mod 16 (rotation as immediates) or -1 (rotation from the table).
-template <int KM>
+// FAST: log output in 16-byte runs (vec4 && !mfe known at compile time, flush without inner branches).
+template <int KM, bool FAST>
 __device__ __forceinline__ void tc_epilogue_tile(const TcParams &p, const int half, const uint32_t taddr,
                                                  float *pout, const bool row_ok) {
   const int ch_begin = half ? p.half[1].ch_begin : p.half[0].ch_begin;
@@ -178,11 +195,11 @@ __device__ __forceinline__ void tc_epilogue_tile(const TcParams &p, const int ha
   int skip = 1;
   // outputs leave in runs of four filters (one 16-byte store per lane; the rows of a warp are
   // 4 M bytes apart, L2 merges the sectors) when the half's filter range allows it
-  const bool vec4 = p.vec4 != 0;
+  const bool vec4 = FAST || p.vec4 != 0;
   float o0 = 0.f, o1 = 0.f, o2 = 0.f;
   int cnt = 0;
   const float ln_scale = p.ln_scale, scale = p.scale;
-  const bool mfe = p.mfe != 0;
+  const bool mfe = !FAST && p.mfe != 0;
 #pragma unroll 1
   for (int ch = ch_begin; ch < ch_end; ++ch) {
     uint32_t v[32];
@@ -192,8 +209,10 @@ __device__ __forceinline__ void tc_epilogue_tile(const TcParams &p, const int ha
     const float4 *tb = &c_tc.tab[half][ch * 16];
     // pass A, branch-free so the 16 bins overlap: X = A_own + c A_next, |X|^2
     float pw[16];
+    float2 wgt[16];  // weights fetched here too: behind the flush branches every LDC latency is exposed
 #pragma unroll
     for (int j = 0; j < 16; ++j) {
+      wgt[j] = *reinterpret_cast<const float2 *>(&tb[j]);
       float cr, ci;
       if (KM >= 0) {
         cr = kCos16[(5 * (KM + j)) & 15];
@@ -212,10 +231,24 @@ __device__ __forceinline__ void tc_epilogue_tile(const TcParams &p, const int ha
     // pass B: segment sums, a flush where the mask says a segment ends
 #pragma unroll
     for (int j = 0; j < 16; ++j) {
-      const float2 w = *reinterpret_cast<const float2 *>(&tb[j]);
-      rise = fmaf(w.x, pw[j], rise);
-      fall = fmaf(w.y, pw[j], fall);
+      rise = fmaf(wgt[j].x, pw[j], rise);
+      fall = fmaf(wgt[j].y, pw[j], fall);
       if ((mask >> j) & 1u) {
+        if (FAST) {
+          // straight-line flush: one predicated 16-byte store every fourth filter
+          const float a = prev_u + fall;  // unscaled (x 2^30 NFFT): never denormal for real input
+          float lg;
+          asm("lg2.approx.ftz.f32 %0, %1;" : "=f"(lg) : "f"(a));
+          float r = fmaf(lg, 0.69314718055994531f, ln_scale);
+          r = (a == 0.f) ? -36.04365338911715f : r;  // functions.zero_handling (feature.py:217)
+          const bool st = (skip == 0) && ((cnt & 3) == 3);
+          if (st && row_ok) *reinterpret_cast<float4 *>(pout) = make_float4(o0, o1, o2, r);
+          pout += st ? 4 : 0;
+          o0 = skip ? o0 : o1;
+          o1 = skip ? o1 : o2;
+          o2 = skip ? o2 : r;
+          cnt += skip ? 0 : 1;
+        } else
         if (skip == 0) {
           const float a = prev_u + fall;  // unscaled (x 2^30 NFFT): never denormal for real input
           float lg;
@@ -244,7 +277,7 @@ __device__ __forceinline__ void tc_epilogue_tile(const TcParams &p, const int ha
   }
 }
 
-template <int KM>
+template <int KM, bool FAST>
 __global__ void __launch_bounds__(kTcThreads, 1) features_tc_kernel(const TcParams p) {
   extern __shared__ __align__(128) unsigned char tc_smem[];
   unsigned char *base = tc_smem;
@@ -303,22 +336,21 @@ __global__ void __launch_bounds__(kTcThreads, 1) features_tc_kernel(const TcPara
     const uint32_t dA = (uint32_t)((q >> 1) * (kTcRows * 16) + rA * 16 + (q & 1) * 8);
     const uint32_t dB = (uint32_t)((q >> 1) * (kTcRows * 16) + rB * 16 + (q & 1) * 8);
     uint32_t bad = 0;
-    const float4 zero4 = make_float4(0.f, 0.f, 0.f, 0.f);
     auto row_ptr = [&](long long t, int r) -> const float * {
-      if (t >= p.num_tiles) return nullptr;
+      if (t >= p.num_tiles) return p.zeros;
       const TcGroup g = p.groups[((p.dbg & 128) ? (long long)blockIdx.x : t) * 4 + (r >> 5)];
       const int i = r & 31;
-      return (g.nf > 0 && i <= g.nf && !(p.dbg & 64)) ? p.samples + g.gstart + (long long)i * kTcHop + q * 4 : nullptr;
+      return (g.nf > 0 && i <= g.nf && !(p.dbg & 64)) ? p.samples + g.gstart + (long long)i * kTcHop + q * 4 : p.zeros;
     };
     long long t = blockIdx.x;
     const float *pA = row_ptr(t, rA), *pB = row_ptr(t, rB);
     float4 bufA[kTcAhead], bufB[kTcAhead];
 #pragma unroll
     for (int s = 0; s < kTcAhead; ++s) {
-      bufA[s] = pA ? __ldg(reinterpret_cast<const float4 *>(pA + s * 16)) : zero4;
-      bufB[s] = pB ? __ldg(reinterpret_cast<const float4 *>(pB + s * 16)) : zero4;
+      bufA[s] = __ldg(reinterpret_cast<const float4 *>(pA + s * 16));
+      bufB[s] = __ldg(reinterpret_cast<const float4 *>(pB + s * 16));
     }
-    uint32_t gs = 0, it = 0;  // k-steps, tiles produced so far
+    uint32_t it = 0, slot = 0, lo_par = 1;  // tiles produced so far, xl ring slot and its wait parity
     for (; t < p.num_tiles; t += gridDim.x, ++it) {
       const float *nA = row_ptr(t + gridDim.x, rA), *nB = row_ptr(t + gridDim.x, rB);
       if (c < 4 && !(p.dbg & 32)) {
@@ -330,14 +362,14 @@ __global__ void __launch_bounds__(kTcThreads, 1) features_tc_kernel(const TcPara
         }
       }
 #pragma unroll
-      for (int s = 0; s < kTcKSteps; ++s, ++gs) {
+      for (int s = 0; s < kTcKSteps; ++s) {
         const float4 xa = bufA[s % kTcAhead], xb = bufB[s % kTcAhead];
         if (s + kTcAhead < kTcKSteps) {
-          bufA[s % kTcAhead] = pA ? __ldg(reinterpret_cast<const float4 *>(pA + (s + kTcAhead) * 16)) : zero4;
-          bufB[s % kTcAhead] = pB ? __ldg(reinterpret_cast<const float4 *>(pB + (s + kTcAhead) * 16)) : zero4;
+          bufA[s % kTcAhead] = __ldg(reinterpret_cast<const float4 *>(pA + (s + kTcAhead) * 16));
+          bufB[s % kTcAhead] = __ldg(reinterpret_cast<const float4 *>(pB + (s + kTcAhead) * 16));
         } else {
-          bufA[s % kTcAhead] = nA ? __ldg(reinterpret_cast<const float4 *>(nA + (s + kTcAhead - kTcKSteps) * 16)) : zero4;
-          bufB[s % kTcAhead] = nB ? __ldg(reinterpret_cast<const float4 *>(nB + (s + kTcAhead - kTcKSteps) * 16)) : zero4;
+          bufA[s % kTcAhead] = __ldg(reinterpret_cast<const float4 *>(nA + (s + kTcAhead - kTcKSteps) * 16));
+          bufB[s % kTcAhead] = __ldg(reinterpret_cast<const float4 *>(nB + (s + kTcAhead - kTcKSteps) * 16));
         }
         uint2 ha, la, hb, lb;
         split4(xa, ha, la, bad);
@@ -345,9 +377,8 @@ __global__ void __launch_bounds__(kTcThreads, 1) features_tc_kernel(const TcPara
         // keep the conversion ahead of the waits (the compiler otherwise sinks it below them and
         // every k-step pays wait + conversion latency in series)
         asm volatile("" ::"r"(ha.x), "r"(ha.y), "r"(la.x), "r"(la.y), "r"(hb.x), "r"(hb.y), "r"(lb.x), "r"(lb.y));
-        const uint32_t slot = gs % kTcLoSlots;
-        if (s == 0 || s == kTcKSteps / 2) mbar_wait(&hi_empty[s ? 1 : 0], (it & 1) ^ 1);
-        mbar_wait(&lo_empty[slot], ((gs / kTcLoSlots) & 1) ^ 1);
+        if (s == 0 || s == kTcKSteps / 2) mbar_wait_park(&hi_empty[s ? 1 : 0], (it & 1) ^ 1);
+        mbar_wait_park(&lo_empty[slot], lo_par);
         unsigned char *sh = base + kTcOffHi + s * kTcAMat;
         unsigned char *sl = base + kTcOffLo + slot * kTcAMat;
         if (!(p.dbg & 2)) {
@@ -359,6 +390,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) features_tc_kernel(const TcPara
         if (!(p.dbg & 8)) fence_async_smem();
         __syncwarp();
         if (lane == 0) mbar_arrive(&full[s]);
+        if (++slot == kTcLoSlots) { slot = 0; lo_par ^= 1; }
       }
       pA = nA;
       pB = nB;
@@ -371,14 +403,14 @@ __global__ void __launch_bounds__(kTcThreads, 1) features_tc_kernel(const TcPara
       uint32_t gs = 0, it = 0;
       for (long long t = blockIdx.x; t < p.num_tiles; t += gridDim.x, ++it) {
         const uint32_t acc = it & 1;
-        mbar_wait(&acc_empty[acc], ((it >> 1) & 1) ^ 1);
+        mbar_wait_park(&acc_empty[acc], ((it >> 1) & 1) ^ 1);
         tc_fence_after();
         const uint32_t tmem_d = tmem_base + acc * kTcN;
         // small terms first, into the empty accumulator
 #pragma unroll
         for (int s = 0; s < kTcKSteps; ++s, ++gs) {
           const uint32_t slot = gs % kTcLoSlots;
-          mbar_wait(&full[s], it & 1);
+          mbar_wait_park(&full[s], it & 1);
           tc_fence_after();
           const uint64_t da_hi = umma_desc_plain(sbase + kTcOffHi + s * kTcAMat, kTcRows * 16);
           const uint64_t da_lo = umma_desc_plain(sbase + kTcOffLo + slot * kTcAMat, kTcRows * 16);
@@ -411,10 +443,10 @@ __global__ void __launch_bounds__(kTcThreads, 1) features_tc_kernel(const TcPara
     for (long long t = blockIdx.x; t < p.num_tiles; t += gridDim.x, ++it) {
       const TcGroup g = p.groups[t * 4 + quad];
       const uint32_t acc = it & 1;
-      mbar_wait(&acc_full[acc], (it >> 1) & 1);
+      mbar_wait_park(&acc_full[acc], (it >> 1) & 1);
       tc_fence_after();
       const uint32_t taddr = tmem_base + ((uint32_t)(quad * 32) << 16) + acc * kTcN;
-      if (!(p.dbg & 1)) tc_epilogue_tile<KM>(p, half, taddr, p.out + (g.row0 + lane) * M + col0, lane < g.nf);
+      if (!(p.dbg & 1)) tc_epilogue_tile<KM, FAST>(p, half, taddr, p.out + (g.row0 + lane) * M + col0, lane < g.nf);
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(&acc_empty[acc]);
@@ -510,11 +542,11 @@ int build_tc_plan(spb_context *ctx, spb_plan *pl, const float4 *seg_rd) {
     }
   cudaError_t e;
   if ((e = cudaMalloc(&pl->d_tc_whi, kTcBMat)) != cudaSuccess || (e = cudaMalloc(&pl->d_tc_wlo, kTcBMat)) != cudaSuccess ||
-      (e = cudaMalloc(&pl->d_tc_flag, 64)) != cudaSuccess)
+      (e = cudaMalloc(&pl->d_tc_flag, 2048)) != cudaSuccess)
     return cuda_fail(ctx, e, "cudaMalloc(tc plan)");
   if ((e = cudaMemcpy(pl->d_tc_whi, hi.data(), kTcBMat, cudaMemcpyHostToDevice)) != cudaSuccess ||
       (e = cudaMemcpy(pl->d_tc_wlo, lo.data(), kTcBMat, cudaMemcpyHostToDevice)) != cudaSuccess ||
-      (e = cudaMemset(pl->d_tc_flag, 0, 64)) != cudaSuccess)
+      (e = cudaMemset(pl->d_tc_flag, 0, 2048)) != cudaSuccess)
     return cuda_fail(ctx, e, "cudaMemcpy(tc plan)");
   pl->tc_ok = true;
   return SPB_OK;
@@ -547,6 +579,7 @@ int launch_features_tc(spb_context *ctx, const FeatArgs &a) {
   p.vec4 = (pl->tc_vec4 && (reinterpret_cast<uintptr_t>(a.out) & 15) == 0) ? 1 : 0;
   p.out = a.out;
   p.flag = pl->d_tc_flag;
+  p.zeros = reinterpret_cast<const float *>(pl->d_tc_flag) + 64;
   {
     const char *e = getenv("SPB_TC_DBG");
     p.dbg = e ? atoi(e) : 0;
@@ -558,7 +591,8 @@ int launch_features_tc(spb_context *ctx, const FeatArgs &a) {
   }
   int per_sm = 0;
   const bool km5 = (pl->seg_kmin & 15) == 5;  // the speechpy default bank starts at bin 5
-  auto kern = km5 ? features_tc_kernel<5> : features_tc_kernel<-1>;
+  const bool fast = p.vec4 && !p.mfe;
+  auto kern = km5 ? (fast ? features_tc_kernel<5, true> : features_tc_kernel<5, false>) : features_tc_kernel<-1, false>;
   int rc = configure_kernel(ctx, (const void *)kern, kTcThreads, kTcSmem, &per_sm);
   if (rc) return rc;
   if (per_sm < 1) return fail(ctx, SPB_ERR_INVALID, "features_tc: kernel does not fit on an SM");
