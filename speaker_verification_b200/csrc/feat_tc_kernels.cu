@@ -197,7 +197,7 @@ __device__ __forceinline__ void tc_epilogue_tile(const TcParams &p, const int ha
   // 4 M bytes apart, L2 merges the sectors) when the half's filter range allows it
   const bool vec4 = FAST || p.vec4 != 0;
   float o0 = 0.f, o1 = 0.f, o2 = 0.f;
-  int cnt = 0;
+  int cnt = 0, left = 5, q4 = 0;
   const float ln_scale = p.ln_scale, scale = p.scale;
   const bool mfe = !FAST && p.mfe != 0;
 #pragma unroll 1
@@ -235,19 +235,19 @@ __device__ __forceinline__ void tc_epilogue_tile(const TcParams &p, const int ha
       fall = fmaf(wgt[j].y, pw[j], fall);
       if ((mask >> j) & 1u) {
         if (FAST) {
-          // straight-line flush: one predicated 16-byte store every fourth filter
+          // straight-line flush.  `left` counts down to the next 16-byte store; it starts at 5
+          // because the first flush of a half only latches U of its first segment (its value
+          // shifts through o2..o0 and is gone before the first store)
           const float a = prev_u + fall;  // unscaled (x 2^30 NFFT): never denormal for real input
           float lg;
           asm("lg2.approx.ftz.f32 %0, %1;" : "=f"(lg) : "f"(a));
           float r = fmaf(lg, 0.69314718055994531f, ln_scale);
           r = (a == 0.f) ? -36.04365338911715f : r;  // functions.zero_handling (feature.py:217)
-          const bool st = (skip == 0) && ((cnt & 3) == 3);
-          if (st && row_ok) *reinterpret_cast<float4 *>(pout) = make_float4(o0, o1, o2, r);
-          pout += st ? 4 : 0;
-          o0 = skip ? o0 : o1;
-          o1 = skip ? o1 : o2;
-          o2 = skip ? o2 : r;
-          cnt += skip ? 0 : 1;
+          --left;
+          if (left == 0 && row_ok) reinterpret_cast<float4 *>(pout)[q4] = make_float4(o0, o1, o2, r);
+          q4 += (left == 0) ? 1 : 0;
+          left = (left == 0) ? 4 : left;
+          o0 = o1; o1 = o2; o2 = r;
         } else
         if (skip == 0) {
           const float a = prev_u + fall;  // unscaled (x 2^30 NFFT): never denormal for real input
