@@ -356,15 +356,16 @@ def run_ours(args, rank, world, local_rank):
             "gpu_launches": int(launches),
             "clocks": clocks,
             "roofline": {
-                "bound": "hbm", "kernel": "features_fast512 (framing+FFT512+|X|^2+mel+log)",
+                "bound": "hbm", "kernel": "features_tc_kernel (framing + hop-DFT on tcgen05 + |X|^2 + mel + log; "
+                                          "timed with its flag memset and the guarded no-op FFT launch)",
                 "achieved": achieved, "peak": peak, "unit": "GB/s",
                 "frac": (achieved / peak) if achieved else None,
-                # ncu --set full (profiles/r01d_ncu_full_summary.csv, 4000-utterance launch): dram read
-                # 2.088 GB + write 0.506 GB for 2.607 GB algorithmic (samples read once, rows written
-                # once) -> 0.995 B of DRAM traffic per algorithmic byte; scaled to this run's launches
-                "traffic": 0.995 * alg_bytes / max(feat_n // max(args.steps, 1), 1),
-                "traffic_source": "ncu dram__bytes_read.sum + dram__bytes_write.sum of features_fast512 in "
-                                  "profiles/r01d_ncu_full_summary.csv (0.995 x algorithmic bytes), per launch",
+                # ncu --set full (profiles/r01g_ncu_tc_summary.csv, 4874 x 8 s launch): dram read 2.501 GB +
+                # write 0.606 GB for 3.118 GB algorithmic (samples read once, rows written once)
+                # -> 0.997 B of DRAM traffic per algorithmic byte; scaled to this run's launches
+                "traffic": 0.997 * alg_bytes / max(feat_n // max(args.steps, 1), 1),
+                "traffic_source": "ncu dram__bytes_read.sum + dram__bytes_write.sum of features_tc_kernel in "
+                                  "profiles/r01g_ncu_tc_summary.csv (0.997 x algorithmic bytes), per launch",
                 "achieved_per_launch_bytes": alg_bytes / max(feat_n // max(args.steps, 1), 1),
                 "peak_source": peak_src,
                 "algorithmic_bytes_per_step": alg_bytes,

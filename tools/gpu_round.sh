@@ -16,7 +16,7 @@ $SMALL > $O/${TAG}_bench_small.json 2> $O/${TAG}_bench_small.err && \
 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file $O/${TAG}_launches.csv $SMALL > $O/${TAG}_ncu_launches.log 2>&1
 echo "launch list rc=$?"
 $SMALL > /dev/null 2>&1 && \
-ncu --set full --clock-control none --import-source on -k regex:'features_fast512|cmvnw_big_kernel|cosine_gemm' -s 6 -c 6 -o $O/${TAG}_prof -f $SMALL > $O/${TAG}_ncu_full.log 2>&1
+ncu --set full --clock-control none --import-source on -k regex:'features_tc|features_fast512|cmvnw_big_kernel|cosine_gemm' -s 6 -c 6 -o $O/${TAG}_prof -f $SMALL > $O/${TAG}_ncu_full.log 2>&1
 echo "ncu full rc=$?"
 ls -la $O
 python tools/score_bench.py > $O/${TAG}_score_bench.txt 2>&1; echo "score bench rc=$?"
