@@ -133,6 +133,23 @@ __device__ __forceinline__ void mbar_wait_park(uint64_t *bar, uint32_t parity) {
       "}" ::"r"(a), "r"(parity), "r"(20000u)
       : "memory");
 }
+// wait of a warp that is normally AHEAD of its producer (the converters): back off between polls
+__device__ __forceinline__ void mbar_wait_nap(uint64_t *bar, uint32_t parity) {
+  const uint32_t a = smem_u32(bar);
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+      "@p bra NAP_DONE;\n\t"
+      "NAP_LOOP:\n\t"
+      "nanosleep.u32 96;\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+      "@p bra NAP_DONE;\n\t"
+      "bra NAP_LOOP;\n\t"
+      "NAP_DONE:\n\t"
+      "}" ::"r"(a), "r"(parity)
+      : "memory");
+}
 __device__ __forceinline__ void named_bar_sync(int id, int threads) {
   asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(threads) : "memory");
 }
@@ -149,6 +166,16 @@ __device__ __forceinline__ void tmem_ld32_nowait(uint32_t taddr, uint32_t (&v)[3
       : "memory");
 }
 __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+// wait::ld that also "produces" v: nothing may read (or move) the registers of an in-flight load before it
+__device__ __forceinline__ void tmem_ld_wait_dep(uint32_t (&v)[32]) {
+  asm volatile("tcgen05.wait::ld.sync.aligned;"
+               : "+r"(v[0]), "+r"(v[1]), "+r"(v[2]), "+r"(v[3]), "+r"(v[4]), "+r"(v[5]), "+r"(v[6]), "+r"(v[7]),
+                 "+r"(v[8]), "+r"(v[9]), "+r"(v[10]), "+r"(v[11]), "+r"(v[12]), "+r"(v[13]), "+r"(v[14]), "+r"(v[15]),
+                 "+r"(v[16]), "+r"(v[17]), "+r"(v[18]), "+r"(v[19]), "+r"(v[20]), "+r"(v[21]), "+r"(v[22]), "+r"(v[23]),
+                 "+r"(v[24]), "+r"(v[25]), "+r"(v[26]), "+r"(v[27]), "+r"(v[28]), "+r"(v[29]), "+r"(v[30]), "+r"(v[31])
+               :
+               : "memory");
+}
 
 // four scaled samples -> fp16 hi and lo halves (two 32-bit words each)
 // bad: bit 15 / 31 set when a half came out as inf or NaN (|x| >= 2, NaN, inf)
@@ -377,8 +404,8 @@ __global__ void __launch_bounds__(kTcThreads, 1) features_tc_kernel(const TcPara
         // keep the conversion ahead of the waits (the compiler otherwise sinks it below them and
         // every k-step pays wait + conversion latency in series)
         asm volatile("" ::"r"(ha.x), "r"(ha.y), "r"(la.x), "r"(la.y), "r"(hb.x), "r"(hb.y), "r"(lb.x), "r"(lb.y));
-        if (s == 0 || s == kTcKSteps / 2) mbar_wait_park(&hi_empty[s ? 1 : 0], (it & 1) ^ 1);
-        mbar_wait_park(&lo_empty[slot], lo_par);
+        if (s == 0 || s == kTcKSteps / 2) mbar_wait_nap(&hi_empty[s ? 1 : 0], (it & 1) ^ 1);
+        mbar_wait_nap(&lo_empty[slot], lo_par);
         unsigned char *sh = base + kTcOffHi + s * kTcAMat;
         unsigned char *sl = base + kTcOffLo + slot * kTcAMat;
         if (!(p.dbg & 2)) {
