@@ -20,13 +20,15 @@
 //
 // One persistent CTA per SM, 17 warps:
 //   warps 0..7   epilogue: quadrant q = warp % 4 owns hop rows 32q..32q+31 (31 frames), the
-//                two warps of a quadrant split the filterbank segments; tcgen05.ld, neighbour
-//                hop by shuffle, complex MAC, |X|^2, segment-form mel sums (weights are
-//                immediate constant-bank operands), log, staged 128-bit stores
+//                two warps of a quadrant split the filterbank segments; per 16-bin chunk:
+//                tcgen05.ld, a branch-free pass (neighbour hop by shuffle, complex MAC with the
+//                hop rotation as immediates, |X|^2), then the segment-form mel sums with a
+//                flush (lg2, one predicated 16-byte store every fourth filter) where a segment ends
 //   warp  8      MMA issuer (one elected thread), M128 N256 K16 kind::f16, two TMEM accumulators
-//   warps 9..16  converters: 128-bit sample loads five k-steps ahead, split, st.shared into the
-//                no-swizzle K-major operand buffers (xh: whole tile, xl: ring of 3 k-steps)
-// The DFT matrix (2 x 77.5 KB) stays resident in shared memory.
+//   warps 9..16  converters: 128-bit sample loads five k-steps ahead (+ L2 bulk prefetch two tiles
+//                ahead), split, st.shared into the no-swizzle K-major operand buffers
+//                (xh: whole tile, xl: ring of 7 k-steps)
+// The DFT matrix (2 x 77.5 KB) stays resident in shared memory; 223 KB of the 227 KB are in use.
 #include <cuda.h>
 #include <cuda_fp16.h>
 #include <math.h>
@@ -64,8 +66,7 @@ constexpr uint32_t kTcIdesc = (1u << 4) | ((uint32_t)(kTcN >> 3) << 17) | ((uint
 static constexpr float kTcEps = 2.220446049250313e-16f;  // functions.py:62
 
 // per bin {rise weight, fall weight, cos, sin of the hop rotation}, one table per epilogue half
-// (bins outside a half's segments carry zero weights).  Constant bank: the unrolled epilogue
-// uses the entries as immediate operands.
+// (bins outside a half's segments carry zero weights).  Constant bank, indexed by the chunk.
 struct TcConst {
   float4 tab[2][128];
 };
@@ -150,33 +151,6 @@ __device__ __forceinline__ void mbar_wait_nap(uint64_t *bar, uint32_t parity) {
       "}" ::"r"(a), "r"(parity)
       : "memory");
 }
-__device__ __forceinline__ void named_bar_sync(int id, int threads) {
-  asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(threads) : "memory");
-}
-__device__ __forceinline__ void tmem_ld32_nowait(uint32_t taddr, uint32_t (&v)[32]) {
-  asm volatile(
-      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
-      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
-      "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
-      : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
-        "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]),
-        "=r"(v[16]), "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]),
-        "=r"(v[24]), "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
-      : "r"(taddr)
-      : "memory");
-}
-__device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
-// wait::ld that also "produces" v: nothing may read (or move) the registers of an in-flight load before it
-__device__ __forceinline__ void tmem_ld_wait_dep(uint32_t (&v)[32]) {
-  asm volatile("tcgen05.wait::ld.sync.aligned;"
-               : "+r"(v[0]), "+r"(v[1]), "+r"(v[2]), "+r"(v[3]), "+r"(v[4]), "+r"(v[5]), "+r"(v[6]), "+r"(v[7]),
-                 "+r"(v[8]), "+r"(v[9]), "+r"(v[10]), "+r"(v[11]), "+r"(v[12]), "+r"(v[13]), "+r"(v[14]), "+r"(v[15]),
-                 "+r"(v[16]), "+r"(v[17]), "+r"(v[18]), "+r"(v[19]), "+r"(v[20]), "+r"(v[21]), "+r"(v[22]), "+r"(v[23]),
-                 "+r"(v[24]), "+r"(v[25]), "+r"(v[26]), "+r"(v[27]), "+r"(v[28]), "+r"(v[29]), "+r"(v[30]), "+r"(v[31])
-               :
-               : "memory");
-}
-
 // four scaled samples -> fp16 hi and lo halves (two 32-bit words each)
 // bad: bit 15 / 31 set when a half came out as inf or NaN (|x| >= 2, NaN, inf)
 __device__ __forceinline__ void split4(const float4 x, uint2 &hi, uint2 &lo, uint32_t &bad) {
