@@ -520,7 +520,6 @@ int spb_plan_destroy(spb_plan *pl) {
   cudaFree(pl->d_dct);
   cudaFree(pl->d_tc_whi);
   cudaFree(pl->d_tc_wlo);
-  if (pl->ctx && pl->ctx->tc_const_plan == pl) pl->ctx->tc_const_plan = nullptr;
   cudaFree(pl->d_tc_flag);
   delete pl;
   return SPB_OK;

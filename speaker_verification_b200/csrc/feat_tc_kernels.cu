@@ -34,6 +34,8 @@
 #include <math.h>
 #include <stdlib.h>
 
+#include <atomic>
+#include <mutex>
 #include <vector>
 
 #include "ptx_helpers.cuh"
@@ -462,6 +464,15 @@ __global__ void __launch_bounds__(kTcThreads, 1) features_tc_kernel(const TcPara
 }
 
 // ------------------------------------------------------------------------------------ host
+struct TcConstOwner {
+  std::mutex mu;
+  const spb_plan *plan = nullptr;
+  uint64_t serial = 0;          // plans are heap objects: an address can come back with other tables
+  cudaEvent_t last_use = nullptr;
+};
+static TcConstOwner g_tc_owner[64];
+static std::atomic<uint64_t> g_tc_serial{1};
+
 // Plan side: DFT matrix (fp16 hi/lo, shared-memory layout), per-half bin tables and ranges.
 // Covered shape: NFFT 512, stride 160, frame 320, a segment-form bank over <= 124 bins and
 // <= 40 filters.
@@ -549,6 +560,7 @@ int build_tc_plan(spb_context *ctx, spb_plan *pl, const float4 *seg_rd) {
       (e = cudaMemcpy(pl->d_tc_wlo, lo.data(), kTcBMat, cudaMemcpyHostToDevice)) != cudaSuccess ||
       (e = cudaMemset(pl->d_tc_flag, 0, 2048)) != cudaSuccess)
     return cuda_fail(ctx, e, "cudaMemcpy(tc plan)");
+  pl->tc_serial = g_tc_serial.fetch_add(1);
   pl->tc_ok = true;
   return SPB_OK;
 }
@@ -585,10 +597,17 @@ int launch_features_tc(spb_context *ctx, const FeatArgs &a) {
     const char *e = getenv("SPB_TC_DBG");
     p.dbg = e ? atoi(e) : 0;
   }
-  if (ctx->tc_const_plan != pl) {
+  // c_tc is one table per DEVICE, shared by every context (stream) of the process: a new owner
+  // uploads only after the previous owner's last launch (event), under a lock
+  TcConstOwner &own = g_tc_owner[ctx->device & 63];
+  std::lock_guard<std::mutex> lock(own.mu);
+  if (!own.last_use) SPB_CUDA(ctx, cudaEventCreateWithFlags(&own.last_use, cudaEventDisableTiming));
+  if (own.plan != pl || own.serial != pl->tc_serial) {
+    if (own.plan) SPB_CUDA(ctx, cudaStreamWaitEvent(ctx->stream, own.last_use, 0));
     // the copy is stream-ordered and reads h_tc_tab (pageable) before returning
     SPB_CUDA(ctx, cudaMemcpyToSymbolAsync(c_tc, pl->h_tc_tab.data(), sizeof(TcConst), 0, cudaMemcpyHostToDevice, ctx->stream));
-    ctx->tc_const_plan = pl;
+    own.plan = pl;
+    own.serial = pl->tc_serial;
   }
   int per_sm = 0;
   const bool km5 = (pl->seg_kmin & 15) == 5;  // the speechpy default bank starts at bin 5
@@ -602,6 +621,7 @@ int launch_features_tc(spb_context *ctx, const FeatArgs &a) {
   if (grid < 1) return SPB_OK;
   kern<<<(unsigned)grid, kTcThreads, kTcSmem, ctx->stream>>>(p);
   SPB_LAUNCH_CHECK(ctx, "features_tc");
+  SPB_CUDA(ctx, cudaEventRecord(own.last_use, ctx->stream));
   return SPB_OK;
 }
 

@@ -54,7 +54,6 @@ struct spb_context {
   void *pinned[2] = {nullptr, nullptr};
   size_t pinned_bytes = 0;
   std::map<int, spb::FftTables> fft_tables;  // by nfft
-  const spb_plan *tc_const_plan = nullptr;   // plan whose tables sit in the tensor-core kernel's constant bank
   std::vector<spb_plan *> plans;
   // (kernel function, dynamic smem) -> resident CTAs per SM, set up once per context
   std::map<std::pair<const void *, size_t>, int> kernel_cfg;
@@ -94,6 +93,7 @@ struct spb_plan {
   uint32_t tc_endmask[2][4] = {{0, 0, 0, 0}, {0, 0, 0, 0}};
   int tc_half[2][4] = {{0, 0, 0, 0}, {0, 0, 0, 0}};  // {first chunk, end chunk, first segment, first filter}
   bool tc_vec4 = false;               // filter ranges of both halves are multiples of four
+  uint64_t tc_serial = 0;             // identifies these tables in the per-device constant bank
   int *d_tc_flag = nullptr;
 };
 

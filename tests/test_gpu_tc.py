@@ -158,3 +158,21 @@ def test_tc_silence_and_gain(sp):
     assert np.max(np.abs((a - b) - 12 * np.log(2.0))) < 2e-5
     assert np.max(np.abs(b - o.lmfe(quiet, FS))) < TOL
     fb.close()
+
+
+def test_tc_plans_alternate(sp):
+    """The epilogue tables live in one constant bank per device: alternating plans must re-upload."""
+    sigs = [synth.audio(1600 + i, n, np.float32) for i, n in enumerate((30000, 64321))]
+    arena, starts, lens = batch.pack(sigs)
+    fa = batch.FeatureBatch(starts, lens)
+    fb_ = batch.FeatureBatch(starts, lens, num_filters=24, low_frequency=100)
+    a0, _ = _lmfe_dev(fa, arena, True)
+    b0, _ = _lmfe_dev(fb_, arena, True)
+    for _ in range(3):
+        a1, _ = _lmfe_dev(fa, arena, True)
+        b1, _ = _lmfe_dev(fb_, arena, True)
+        assert np.array_equal(a0, a1) and np.array_equal(b0, b1)
+    assert np.max(np.abs(fa.split(a0)[0] - o.lmfe(sigs[0], FS))) < TOL
+    assert np.max(np.abs(fb_.split(b0)[0] - o.lmfe(sigs[0], FS, num_filters=24, low_frequency=100))) < TOL
+    fa.close()
+    fb_.close()
