@@ -913,8 +913,44 @@ static int run_lmfe_cmvnw(spb_context *ctx, const spb_batch *b, const float *d_s
   return SPB_OK;
 }
 
+// mfcc / mfcc+delta through the tensor-core log-mel kernel: lmfe rows of one run of utterances
+// into scratch, then energy + DCT + deltas (mfcc_post_kernel).  Usable when the plan and the batch
+// qualify for the tensor-core kernel.
+static bool mfcc_hybrid_ok(const spb_batch *b, int mode) {
+  return (mode == FEAT_MFCC || mode == FEAT_MFCC_DELTA) && b->d_tc_groups && b->plan->tc_ok && !g_force_generic &&
+         !g_no_tc && tc_enabled() && b->plan->p.num_cepstral >= 1;
+}
+
+static int mfcc_hybrid_chunk(spb_context *ctx, const spb_batch *b, const BatchChunk &c, const float *d_samples,
+                             int64_t arena_len, int mode, float *d_lmfe, float *d_out) {
+  const int M = b->plan->p.num_filters;
+  FeatArgs a;
+  float *lmfe_biased = d_lmfe - (ptrdiff_t)c.row0 * M;  // rows are addressed by their global index
+  fill_feat_args(a, b, d_samples, arena_len, FEAT_LMFE, lmfe_biased, nullptr);
+  a.tiles = b->d_tiles + c.tile0;
+  a.ftiles = b->d_ftiles + c.tile0;
+  a.num_tiles = c.tile1 - c.tile0;
+  a.tc_groups = b->d_tc_groups + c.tc0;
+  a.num_tc_groups = c.tc1 - c.tc0;
+  int rc = run_features(ctx, a);
+  if (rc) return rc;
+  a.mode = mode;
+  a.out = d_out;
+  return launch_mfcc_post(ctx, a, lmfe_biased);
+}
+
 static int run_simple_mode(spb_context *ctx, const spb_batch *b, const float *d_samples,
                            int64_t arena_len, int mode, float *d_out, float *d_energy) {
+  if (d_energy == nullptr && mfcc_hybrid_ok(b, mode)) {
+    const size_t bytes = (size_t)std::max<int64_t>(b->max_group_rows, 1) * b->plan->p.num_filters * 4;
+    float *d_lmfe = (float *)scratch(ctx, 2, bytes);
+    if (!d_lmfe) return SPB_ERR_CUDA;
+    for (const BatchChunk &c : b->groups) {
+      int rc = mfcc_hybrid_chunk(ctx, b, c, d_samples, arena_len, mode, d_lmfe, d_out);
+      if (rc) return rc;
+    }
+    return SPB_OK;
+  }
   FeatArgs a;
   fill_feat_args(a, b, d_samples, arena_len, mode, d_out, d_energy);
   if (b->d_tc_groups && !b->chunks.empty()) {
@@ -1254,6 +1290,11 @@ static int host_batch(spb_context *ctx, const spb_batch *b, const void *samples,
   if (!d_samples || !d_out || !d_raw) return SPB_ERR_CUDA;
   float *d_lmfe = nullptr, *d_ms = nullptr;
   if (which == 0 && (rc = lmfe_cmvnw_prepare(ctx, b, b->max_chunk_rows, &d_lmfe, &d_ms))) return rc;
+  const bool hybrid = which != 0 && mfcc_hybrid_ok(b, FEAT_MFCC_DELTA);
+  if (hybrid) {
+    d_lmfe = (float *)scratch(ctx, 2, (size_t)std::max<int64_t>(b->max_chunk_rows, 1) * b->plan->p.num_filters * 4);
+    if (!d_lmfe) return SPB_ERR_CUDA;
+  }
   const size_t nch = b->chunks.size();
   const bool ingest = dtype != SPB_F32 || scale != 1.0f;  // float32 with scale 1 is used as uploaded
   // chunk spans overlap when utterances are not packed in order: then copy the arena once
@@ -1288,6 +1329,8 @@ static int host_batch(spb_context *ctx, const spb_batch *b, const void *samples,
     }
     if (which == 0) {
       rc = lmfe_cmvnw_chunk(ctx, b, c, d_samples, arena_len, d_lmfe, d_ms, d_out);
+    } else if (hybrid) {
+      rc = mfcc_hybrid_chunk(ctx, b, c, d_samples, arena_len, FEAT_MFCC_DELTA, d_lmfe, d_out);
     } else {
       FeatArgs a;
       fill_feat_args(a, b, d_samples, arena_len, FEAT_MFCC_DELTA, d_out, nullptr);

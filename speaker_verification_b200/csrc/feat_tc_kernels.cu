@@ -625,4 +625,154 @@ int launch_features_tc(spb_context *ctx, const FeatArgs &a) {
   return SPB_OK;
 }
 
+// ------------------------------------------------------------------------------------
+// mfcc (+ delta cube) on top of the tensor-core log-mel rows: frame energy, DCT-II, deltas.
+//   feature.py:202      frame_energies = sum_k P[k] over all one-sided bins, via Parseval:
+//                       (NFFT sum x^2 + X0^2 + X_{NFFT/2}^2) / (2 NFFT); X0 = sum x, X_{NFFT/2} = sum (-1)^n x
+//   feature.py:147-152  dct(type 2, ortho)[:, :C], c0 <- log(energy) when dc_elimination
+//   processing.py:223-236 (as written)  D(x)[c] = (x[min(c+1,C-1)] + 2 x[min(c+2,C-1)]) / 10
+// One warp per group of the tensor-core table (32 hops -> 31 frames): lane = hop for the three
+// sums over its 160 samples (frame = hops lane, lane + 1), lane = frame for the DCT, rows staged
+// in shared memory so the group's output block leaves in coalesced stores.
+struct PostParams {
+  const float *samples;
+  const TcGroup *groups;
+  long long num_groups;
+  const float *lmfe;  // [rows][M], addressed by global row
+  const float *dct;   // [C][M]
+  int M, C, dc_elim, delta, nfft;
+  float *out;         // [rows][C] or [rows][C][3]
+};
+constexpr int kPostWarps = 8;
+
+__global__ void __launch_bounds__(kPostWarps * 32) mfcc_post_kernel(const PostParams p) {
+  extern __shared__ __align__(16) float post_smem[];
+  const int M = p.M, C = p.C;
+  const int pitch = C | 1;
+  float *s_dct = post_smem;                                   // [C][M]
+  float *s_stage = post_smem + ((C * M + 3) & ~3);            // [warps][31][pitch]
+  for (int i = threadIdx.x; i < C * M; i += blockDim.x) s_dct[i] = __ldg(p.dct + i);
+  __syncthreads();
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  float *st = s_stage + warp * kTcGroupFrames * pitch;
+  const int lpitch = M | 1;
+  float *sl = s_stage + kPostWarps * kTcGroupFrames * pitch + warp * kTcGroupFrames * lpitch;  // log-mel rows
+  const float nf2 = (float)p.nfft, inv2n = 1.0f / (2.f * (float)p.nfft);
+  for (long long gi = (long long)blockIdx.x * kPostWarps + warp; gi < p.num_groups; gi += (long long)gridDim.x * kPostWarps) {
+    const TcGroup g = p.groups[gi];
+    if (g.nf <= 0) continue;
+    // per-hop sums.  Four lanes share a hop (8 hops per pass: a request touches 8 lines, not 32 --
+    // with lane = hop the loads ran at the L1 tag rate), quad reduction, then hop h's sums move to lane h
+    float s2 = 0.f, s0 = 0.f, sa = 0.f;
+#pragma unroll
+    for (int ps = 0; ps < 4; ++ps) {
+      const int h = ps * 8 + (lane >> 2);
+      float t2 = 0.f, t0 = 0.f, ta = 0.f;
+      if (h <= g.nf) {
+        const float4 *q = reinterpret_cast<const float4 *>(p.samples + g.gstart + (long long)h * kTcHop) + (lane & 3);
+#pragma unroll
+        for (int i = 0; i < kTcHop / 16; ++i) {
+          const float4 x = __ldg(q + 4 * i);
+          t2 = fmaf(x.x, x.x, fmaf(x.y, x.y, fmaf(x.z, x.z, fmaf(x.w, x.w, t2))));
+          t0 += (x.x + x.y) + (x.z + x.w);
+          ta += (x.x - x.y) + (x.z - x.w);
+        }
+      }
+#pragma unroll
+      for (int o = 1; o <= 2; o <<= 1) {
+        t2 += __shfl_xor_sync(0xffffffffu, t2, o);
+        t0 += __shfl_xor_sync(0xffffffffu, t0, o);
+        ta += __shfl_xor_sync(0xffffffffu, ta, o);
+      }
+      const int src = (lane & 7) * 4;  // hop ps*8 + (lane & 7) sits in lanes 4 (lane & 7) ..
+      const float u2 = __shfl_sync(0xffffffffu, t2, src);
+      const float u0 = __shfl_sync(0xffffffffu, t0, src);
+      const float ua = __shfl_sync(0xffffffffu, ta, src);
+      if ((lane >> 3) == ps) { s2 = u2; s0 = u0; sa = ua; }
+    }
+    const float n2 = __shfl_down_sync(0xffffffffu, s2, 1);
+    const float n0 = __shfl_down_sync(0xffffffffu, s0, 1);
+    const float na = __shfl_down_sync(0xffffffffu, sa, 1);
+    // the group's log-mel rows are one contiguous block: coalesced into shared memory, then lane = frame
+    {
+      const float *lsrc = p.lmfe + g.row0 * M;
+      const int total = g.nf * M;
+      for (int i = lane; i < total; i += 32) {
+        const int f = i / M;
+        sl[f * lpitch + (i - f * M)] = __ldg(lsrc + i);
+      }
+    }
+    __syncwarp();
+    if (lane < g.nf) {
+      const float x0 = s0 + n0, xn = sa + na;  // the hop length is even: the second hop keeps the signs
+      float e = (nf2 * (s2 + n2) + x0 * x0 + xn * xn) * inv2n;
+      if (e == 0.f) e = kTcEps;  // feature.py:205
+      const float *lrow = sl + lane * lpitch;
+      float lm[kTcOutPitch];
+#pragma unroll
+      for (int m = 0; m < kTcOutPitch; ++m) lm[m] = (m < M) ? lrow[m] : 0.f;
+      for (int c = 0; c < C; ++c) {
+        const float *drow = s_dct + c * M;
+        float acc = 0.f;
+#pragma unroll
+        for (int m = 0; m < kTcOutPitch; ++m)
+          if (m < M) acc = fmaf(drow[m], lm[m], acc);
+        if (c == 0 && p.dc_elim) acc = __logf(e);  // feature.py:151-152
+        st[lane * pitch + c] = acc;
+      }
+    }
+    __syncwarp();
+    if (p.delta) {
+      float *dst = p.out + g.row0 * C * 3;
+      const int total = g.nf * C * 3;
+      for (int i = lane; i < total; i += 32) {
+        const int f = i / (3 * C), r = i - f * 3 * C;
+        const int c = r / 3, w = r - c * 3;
+        const float *x = st + f * pitch;
+        auto X = [&](int j) { return x[min(j, C - 1)]; };
+        auto D1 = [&](int j) {
+          j = min(j, C - 1);
+          return (X(j + 1) + 2.f * X(j + 2)) / 10.f;
+        };
+        dst[i] = (w == 0) ? x[c] : ((w == 1) ? D1(c) : (D1(c + 1) + 2.f * D1(c + 2)) / 10.f);
+      }
+    } else {
+      float *dst = p.out + g.row0 * C;
+      const int total = g.nf * C;
+      for (int i = lane; i < total; i += 32) {
+        const int f = i / C;
+        dst[i] = st[f * pitch + (i - f * C)];
+      }
+    }
+    __syncwarp();
+  }
+}
+
+int launch_mfcc_post(spb_context *ctx, const FeatArgs &a, const float *d_lmfe) {
+  if (a.num_tc_groups <= 0) return SPB_OK;
+  PostParams p;
+  p.samples = a.samples;
+  p.groups = a.tc_groups;
+  p.num_groups = a.num_tc_groups;
+  p.lmfe = d_lmfe;
+  p.dct = a.dct;
+  p.M = a.M;
+  p.C = a.C;
+  p.dc_elim = a.dc_elim;
+  p.delta = (a.mode == FEAT_MFCC_DELTA) ? 1 : 0;
+  p.nfft = a.nfft;
+  p.out = a.out;
+  const size_t smem = (size_t)(((a.C * a.M + 3) & ~3) + kPostWarps * kTcGroupFrames * ((a.C | 1) + (a.M | 1))) * sizeof(float);
+  int per_sm = 0;
+  int rc = configure_kernel(ctx, (const void *)mfcc_post_kernel, kPostWarps * 32, smem, &per_sm);
+  if (rc) return rc;
+  if (per_sm < 1) return fail(ctx, SPB_ERR_INVALID, "mfcc_post: kernel does not fit on an SM");
+  long long grid = (p.num_groups + kPostWarps - 1) / kPostWarps;
+  const long long cap = (long long)ctx->sm_count * per_sm;
+  if (grid > cap) grid = cap;
+  mfcc_post_kernel<<<(unsigned)grid, kPostWarps * 32, smem, ctx->stream>>>(p);
+  SPB_LAUNCH_CHECK(ctx, "mfcc_post");
+  return SPB_OK;
+}
+
 }  // namespace spb

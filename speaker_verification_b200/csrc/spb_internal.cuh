@@ -217,6 +217,8 @@ bool fast512_supported(const FeatArgs &a);
 int launch_features_fast512(spb_context *ctx, const FeatArgs &a, const FftTables &t);
 bool features_tc_supported(const FeatArgs &a);
 int launch_features_tc(spb_context *ctx, const FeatArgs &a);
+// mfcc / mfcc+delta rows from log-mel rows (global row addressing) + frame energies from the samples
+int launch_mfcc_post(spb_context *ctx, const FeatArgs &a, const float *d_lmfe);
 int build_tc_plan(spb_context *ctx, spb_plan *pl, const float4 *seg_rd);  // seg_rd: host copy, seg_nbins entries
 bool fast1024_supported(const FeatArgs &a);
 int launch_features_fast1024(spb_context *ctx, const FeatArgs &a, const FftTables &t);

@@ -176,3 +176,46 @@ def test_tc_plans_alternate(sp):
     assert np.max(np.abs(fb_.split(b0)[0] - o.lmfe(sigs[0], FS, num_filters=24, low_frequency=100))) < TOL
     fa.close()
     fb_.close()
+
+
+def _mfcc_delta_dev(fb, arena, tc=True):
+    import torch
+    raw = _raw()
+    d_in = torch.from_numpy(arena).cuda()
+    d_out = torch.full((max(fb.total_frames, 1), fb.num_cepstral, 3), 777.0, dtype=torch.float32, device="cuda")
+    torch.cuda.synchronize()
+    raw.spb_debug_force_generic(0 if tc else 4)
+    try:
+        fb.mfcc_delta_dev(d_in.data_ptr(), d_in.numel(), d_out.data_ptr())
+        fb.ctx.sync()
+    finally:
+        raw.spb_debug_force_generic(0)
+    return d_out.cpu().numpy()[:fb.total_frames]
+
+
+@pytest.mark.parametrize("kw", [
+    dict(),
+    dict(dc_elimination=False),
+    dict(num_filters=26, num_cepstral=20),
+    dict(num_filters=24, low_frequency=100, num_cepstral=24),
+])
+def test_mfcc_delta_through_tensor_core_lmfe(sp, kw):
+    """mfcc + delta cube = tensor-core log-mel rows + mfcc_post_kernel (Parseval frame energy from
+    the samples, DCT-II, deltas) against the FFT kernel's fused epilogue and the oracle."""
+    frames = [1, 31, 32, 62, 63, 124, 125, 798, 0, 1998]
+    sigs = [synth.audio(1700 + i, _frames_to_samples(f), np.float32) for i, f in enumerate(frames)]
+    arena, starts, lens = batch.pack(sigs)
+    fb = batch.FeatureBatch(starts, lens, **kw)
+    tc = _mfcc_delta_dev(fb, arena, True)
+    fft = _mfcc_delta_dev(fb, arena, False)
+    assert not np.any(tc == 777.0)
+    assert np.max(np.abs(tc - fft)) < 5e-5
+    host = fb.mfcc_delta(arena)  # host-pointer (chunked) call takes the same kernels
+    assert np.array_equal(host, tc)
+    okw = {k: v for k, v in kw.items()}
+    for s, got in zip(sigs, fb.split(tc)):
+        ref = o.extract_derivative_feature(o.mfcc(s, FS, **okw)) if len(s) >= 480 else None
+        if ref is not None and ref.shape[0]:
+            assert got.shape == ref.shape
+            assert np.max(np.abs(got - ref)) < TOL
+    fb.close()
