@@ -219,3 +219,76 @@ def test_mfcc_delta_through_tensor_core_lmfe(sp, kw):
             assert got.shape == ref.shape
             assert np.max(np.abs(got - ref)) < TOL
     fb.close()
+
+
+def _device_noise(total, seed):
+    import torch
+    gen = torch.Generator(device="cuda")
+    gen.manual_seed(seed)
+    arena = torch.empty(total, dtype=torch.float32, device="cuda")
+    for s in range(0, total, 1 << 28):
+        arena[s:s + (1 << 28)].normal_(0.0, 0.1, generator=gen)
+    return arena
+
+
+def test_full_size_properties_cfg2(sp):
+    """BASELINE config 2 at full size (4 874 x 8 s, mfcc 13 + delta cube, generated on the device):
+    independence (an utterance alone == inside the batch, bit for bit), oracle spot checks, and gain:
+    audio x 2^-3 moves only c0 = ln(energy) (by 2 ln 2^-3; the DCT rows k > 0 sum to zero and the
+    reference's deltas never read coefficient 0)."""
+    import torch
+    U, N = 4874, 128000
+    starts = np.arange(U, dtype=np.int64) * N
+    lengths = np.full(U, N, dtype=np.int64)
+    arena = _device_noise(U * N, 202)
+    fb = batch.FeatureBatch(starts, lengths)
+    assert fb.total_frames == U * 798
+    out = torch.empty((fb.total_frames, 13, 3), dtype=torch.float32, device="cuda")
+    torch.cuda.synchronize()
+    fb.mfcc_delta_dev(arena.data_ptr(), arena.numel(), out.data_ptr())
+    fb.ctx.sync()
+    assert bool(torch.isfinite(out).all())
+    for u in (0, 2500, U - 1):
+        x = arena[starts[u]:starts[u] + N].cpu().numpy()
+        one = batch.FeatureBatch(np.zeros(1, dtype=np.int64), np.array([N], dtype=np.int64))
+        alone = one.mfcc_delta(x)
+        one.close()
+        got = out[u * 798:(u + 1) * 798].cpu().numpy()
+        assert np.array_equal(got, alone), u
+        ref = o.extract_derivative_feature(o.mfcc(x, FS))
+        assert np.max(np.abs(got - ref)) < TOL, u
+    arena.mul_(0.125)
+    out2 = torch.empty_like(out)
+    torch.cuda.synchronize()
+    fb.mfcc_delta_dev(arena.data_ptr(), arena.numel(), out2.data_ptr())
+    fb.ctx.sync()
+    d = (out2 - out)
+    assert float((d[:, 0, 0] - 2 * np.log(0.125)).abs().max()) < 5e-5
+    d[:, 0, 0] = 0
+    assert float(d.abs().max()) < 5e-5
+    fb.close()
+
+
+def test_full_size_properties_cfg4(sp):
+    """BASELINE config 4 at full size (1 024 x 60 s, lmfe + cmvnw over 5 998-frame utterances: six
+    large cmvnw tiles and 194 tensor-core groups each): independence and oracle spot checks."""
+    import torch
+    U, N = 1024, 960000
+    starts = np.arange(U, dtype=np.int64) * N
+    lengths = np.full(U, N, dtype=np.int64)
+    arena = _device_noise(U * N, 404)
+    fb = batch.FeatureBatch(starts, lengths)
+    assert fb.total_frames == U * 5998
+    out = torch.empty((fb.total_frames, 40), dtype=torch.float32, device="cuda")
+    torch.cuda.synchronize()
+    fb.lmfe_cmvnw_dev(arena.data_ptr(), arena.numel(), out.data_ptr())
+    fb.ctx.sync()
+    assert bool(torch.isfinite(out).all())
+    for u in (0, 700, U - 1):
+        x = arena[starts[u]:starts[u] + N].cpu().numpy()
+        alone = batch.lmfe_cmvnw([x])[0]
+        got = out[u * 5998:(u + 1) * 5998].cpu().numpy()
+        assert np.array_equal(got, alone), u
+        ref = o.cmvnw_vectorised(o.lmfe(x, FS), 301, True)
+        assert np.max(np.abs(got - ref)) < TOL, u
+    fb.close()
