@@ -932,6 +932,10 @@ static int mfcc_hybrid_chunk(spb_context *ctx, const spb_batch *b, const BatchCh
   a.num_tiles = c.tile1 - c.tile0;
   a.tc_groups = b->d_tc_groups + c.tc0;
   a.num_tc_groups = c.tc1 - c.tc0;
+  // per-hop sums for the frame energy come out of the tensor-core kernel's converters (scratch slot 3
+  // is the cmvnw intermediate of the other batch call: never live at the same time)
+  a.tc_hopsum = (float4 *)scratch(ctx, 3, (size_t)std::max<int64_t>(a.num_tc_groups, 1) * 32 * sizeof(float4));
+  if (!a.tc_hopsum) return SPB_ERR_CUDA;
   int rc = run_features(ctx, a);
   if (rc) return rc;
   a.mode = mode;

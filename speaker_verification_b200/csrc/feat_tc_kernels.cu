@@ -95,6 +95,7 @@ struct TcParams {
   float *out;
   int *flag;                 // set when a sample cannot be split (|x| >= 2, NaN, inf)
   const float *zeros;        // 1 KB of zeros: the hop rows past the end of a group read these
+  float4 *hopsum;            // optional [tiles * 128]: per hop row {sum x^2, sum x, sum (-1)^n x, 0} for the mfcc energy
   int dbg;                   // SPB_TC_DBG phase knobs (timing experiments only)
 };
 
@@ -354,8 +355,10 @@ __global__ void __launch_bounds__(kTcThreads, 1) features_tc_kernel(const TcPara
       bufB[s] = __ldg(reinterpret_cast<const float4 *>(pB + s * 16));
     }
     uint32_t it = 0, slot = 0, lo_par = 1;  // tiles produced so far, xl ring slot and its wait parity
+    const bool want_sums = p.hopsum != nullptr;
     for (; t < p.num_tiles; t += gridDim.x, ++it) {
       const float *nA = row_ptr(t + gridDim.x, rA), *nB = row_ptr(t + gridDim.x, rB);
+      float a2 = 0.f, a0 = 0.f, aa = 0.f, b2 = 0.f, b0 = 0.f, ba = 0.f;  // hop sums of rows rA, rB (this lane's samples)
       if (c < 4 && !(p.dbg & 32)) {
         // pull the samples of the tile after next into L2 with the TMA engine (one 20 KB run per group)
         const long long tp = t + 2 * (long long)gridDim.x;
@@ -373,6 +376,15 @@ __global__ void __launch_bounds__(kTcThreads, 1) features_tc_kernel(const TcPara
         } else {
           bufA[s % kTcAhead] = __ldg(reinterpret_cast<const float4 *>(nA + (s + kTcAhead - kTcKSteps) * 16));
           bufB[s % kTcAhead] = __ldg(reinterpret_cast<const float4 *>(nB + (s + kTcAhead - kTcKSteps) * 16));
+        }
+        if (want_sums) {
+          // frame energy of the mfcc path (feature.py:202 by Parseval): the three sums per hop ride along
+          a2 = fmaf(xa.x, xa.x, fmaf(xa.y, xa.y, fmaf(xa.z, xa.z, fmaf(xa.w, xa.w, a2))));
+          a0 += (xa.x + xa.y) + (xa.z + xa.w);
+          aa += (xa.x - xa.y) + (xa.z - xa.w);
+          b2 = fmaf(xb.x, xb.x, fmaf(xb.y, xb.y, fmaf(xb.z, xb.z, fmaf(xb.w, xb.w, b2))));
+          b0 += (xb.x + xb.y) + (xb.z + xb.w);
+          ba += (xb.x - xb.y) + (xb.z - xb.w);
         }
         uint2 ha, la, hb, lb;
         split4(xa, ha, la, bad);
@@ -394,6 +406,21 @@ __global__ void __launch_bounds__(kTcThreads, 1) features_tc_kernel(const TcPara
         __syncwarp();
         if (lane == 0) mbar_arrive(&full[s]);
         if (++slot == kTcLoSlots) { slot = 0; lo_par ^= 1; }
+      }
+      if (want_sums) {
+#pragma unroll
+        for (int o = 1; o <= 2; o <<= 1) {  // the four lanes of a row
+          a2 += __shfl_xor_sync(0xffffffffu, a2, o);
+          a0 += __shfl_xor_sync(0xffffffffu, a0, o);
+          aa += __shfl_xor_sync(0xffffffffu, aa, o);
+          b2 += __shfl_xor_sync(0xffffffffu, b2, o);
+          b0 += __shfl_xor_sync(0xffffffffu, b0, o);
+          ba += __shfl_xor_sync(0xffffffffu, ba, o);
+        }
+        if (q == 0) {
+          p.hopsum[t * kTcRows + rA] = make_float4(a2, a0, aa, 0.f);
+          p.hopsum[t * kTcRows + rB] = make_float4(b2, b0, ba, 0.f);
+        }
       }
       pA = nA;
       pB = nB;
@@ -593,6 +620,7 @@ int launch_features_tc(spb_context *ctx, const FeatArgs &a) {
   p.out = a.out;
   p.flag = pl->d_tc_flag;
   p.zeros = reinterpret_cast<const float *>(pl->d_tc_flag) + 64;
+  p.hopsum = a.tc_hopsum;
   {
     const char *e = getenv("SPB_TC_DBG");
     p.dbg = e ? atoi(e) : 0;
@@ -640,6 +668,7 @@ struct PostParams {
   long long num_groups;
   const float *lmfe;  // [rows][M], addressed by global row
   const float *dct;   // [C][M]
+  const float4 *hopsum;  // [groups * 32] {sum x^2, sum x, sum (-1)^n x} per hop from the tensor-core kernel, or nullptr
   int M, C, dc_elim, delta, nfft;
   float *out;         // [rows][C] or [rows][C][3]
 };
@@ -658,12 +687,19 @@ __global__ void __launch_bounds__(kPostWarps * 32) mfcc_post_kernel(const PostPa
   const int lpitch = M | 1;
   float *sl = s_stage + kPostWarps * kTcGroupFrames * pitch + warp * kTcGroupFrames * lpitch;  // log-mel rows
   const float nf2 = (float)p.nfft, inv2n = 1.0f / (2.f * (float)p.nfft);
+  // element i = lane + 32 k of a row-major [rows][W] block walks (row, col) by a fixed step: no division per element
+  const int m_f0 = lane / M, m_c0 = lane - m_f0 * M, m_df = 32 / M, m_dc = 32 - m_df * M;
+  const int c_f0 = lane / C, c_c0 = lane - c_f0 * C, c_df = 32 / C, c_dc = 32 - c_df * C;
   for (long long gi = (long long)blockIdx.x * kPostWarps + warp; gi < p.num_groups; gi += (long long)gridDim.x * kPostWarps) {
     const TcGroup g = p.groups[gi];
     if (g.nf <= 0) continue;
     // per-hop sums.  Four lanes share a hop (8 hops per pass: a request touches 8 lines, not 32 --
     // with lane = hop the loads ran at the L1 tag rate), quad reduction, then hop h's sums move to lane h
     float s2 = 0.f, s0 = 0.f, sa = 0.f;
+    if (p.hopsum != nullptr) {
+      const float4 hs = __ldg(p.hopsum + gi * 32 + lane);
+      s2 = hs.x; s0 = hs.y; sa = hs.z;
+    } else
 #pragma unroll
     for (int ps = 0; ps < 4; ++ps) {
       const int h = ps * 8 + (lane >> 2);
@@ -697,9 +733,12 @@ __global__ void __launch_bounds__(kPostWarps * 32) mfcc_post_kernel(const PostPa
     {
       const float *lsrc = p.lmfe + g.row0 * M;
       const int total = g.nf * M;
+      int f = m_f0, m = m_c0;
       for (int i = lane; i < total; i += 32) {
-        const int f = i / M;
-        sl[f * lpitch + (i - f * M)] = __ldg(lsrc + i);
+        sl[f * lpitch + m] = __ldg(lsrc + i);
+        f += m_df;
+        m += m_dc;
+        if (m >= M) { m -= M; ++f; }
       }
     }
     __syncwarp();
@@ -714,34 +753,57 @@ __global__ void __launch_bounds__(kPostWarps * 32) mfcc_post_kernel(const PostPa
       for (int c = 0; c < C; ++c) {
         const float *drow = s_dct + c * M;
         float acc = 0.f;
+        if ((M & 3) == 0) {  // rows of the table are 16-byte aligned: broadcast 128-bit loads
+          const float4 *d4 = reinterpret_cast<const float4 *>(drow);
 #pragma unroll
-        for (int m = 0; m < kTcOutPitch; ++m)
-          if (m < M) acc = fmaf(drow[m], lm[m], acc);
+          for (int m4 = 0; m4 < kTcOutPitch / 4; ++m4)
+            if (m4 * 4 < M) {
+              const float4 w = d4[m4];
+              acc = fmaf(w.x, lm[4 * m4], acc);
+              acc = fmaf(w.y, lm[4 * m4 + 1], acc);
+              acc = fmaf(w.z, lm[4 * m4 + 2], acc);
+              acc = fmaf(w.w, lm[4 * m4 + 3], acc);
+            }
+        } else {
+#pragma unroll
+          for (int m = 0; m < kTcOutPitch; ++m)
+            if (m < M) acc = fmaf(drow[m], lm[m], acc);
+        }
         if (c == 0 && p.dc_elim) acc = __logf(e);  // feature.py:151-152
         st[lane * pitch + c] = acc;
       }
     }
     __syncwarp();
     if (p.delta) {
+      // lane = (frame, coefficient): the three channels x, D(x), D(D(x)) are 12 consecutive bytes
       float *dst = p.out + g.row0 * C * 3;
-      const int total = g.nf * C * 3;
+      const int total = g.nf * C;
+      int f = c_f0, c = c_c0;
       for (int i = lane; i < total; i += 32) {
-        const int f = i / (3 * C), r = i - f * 3 * C;
-        const int c = r / 3, w = r - c * 3;
         const float *x = st + f * pitch;
         auto X = [&](int j) { return x[min(j, C - 1)]; };
-        auto D1 = [&](int j) {
-          j = min(j, C - 1);
-          return (X(j + 1) + 2.f * X(j + 2)) / 10.f;
-        };
-        dst[i] = (w == 0) ? x[c] : ((w == 1) ? D1(c) : (D1(c + 1) + 2.f * D1(c + 2)) / 10.f);
+        const float x1 = X(c + 1), x2 = X(c + 2), x3 = X(c + 3), x4 = X(c + 4);
+        // D1(j) = (X(j+1) + 2 X(j+2)) / 10 with j clamped to C-1 (processing.py:223-236 as written)
+        const float d_c = (x1 + 2.f * x2) / 10.f;
+        const float d_c1 = (c + 1 <= C - 1) ? (x2 + 2.f * x3) / 10.f : (X(C) + 2.f * X(C + 1)) / 10.f;
+        const float d_c2 = (c + 2 <= C - 1) ? (x3 + 2.f * x4) / 10.f : (X(C) + 2.f * X(C + 1)) / 10.f;
+        float *o3 = dst + 3 * i;
+        o3[0] = x[c];
+        o3[1] = d_c;
+        o3[2] = (d_c1 + 2.f * d_c2) / 10.f;
+        f += c_df;
+        c += c_dc;
+        if (c >= C) { c -= C; ++f; }
       }
     } else {
       float *dst = p.out + g.row0 * C;
       const int total = g.nf * C;
+      int f = c_f0, c = c_c0;
       for (int i = lane; i < total; i += 32) {
-        const int f = i / C;
-        dst[i] = st[f * pitch + (i - f * C)];
+        dst[i] = st[f * pitch + c];
+        f += c_df;
+        c += c_dc;
+        if (c >= C) { c -= C; ++f; }
       }
     }
     __syncwarp();
@@ -756,6 +818,7 @@ int launch_mfcc_post(spb_context *ctx, const FeatArgs &a, const float *d_lmfe) {
   p.num_groups = a.num_tc_groups;
   p.lmfe = d_lmfe;
   p.dct = a.dct;
+  p.hopsum = a.tc_hopsum;
   p.M = a.M;
   p.C = a.C;
   p.dc_elim = a.dc_elim;

@@ -193,6 +193,7 @@ struct FeatArgs {
   const FftTile *ftiles;     // [num_tiles] or nullptr
   const TcGroup *tc_groups = nullptr;  // tensor-core kernel: groups of this launch (4 per tile) or nullptr
   int64_t num_tc_groups = 0;
+  float4 *tc_hopsum = nullptr;         // tensor-core kernel: per-hop sums out (mfcc energy), [num_tc_groups * 32]
   const spb_plan *plan = nullptr;
   const int *run_if = nullptr;         // fast512: run only when *run_if != 0
   int64_t num_tiles;
