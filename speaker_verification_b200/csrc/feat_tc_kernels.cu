@@ -281,7 +281,7 @@ __device__ __forceinline__ void tc_epilogue_tile(const TcParams &p, const int ha
   }
 }
 
-template <int KM, bool FAST>
+template <int KM, bool FAST, bool SUMS>
 __global__ void __launch_bounds__(kTcThreads, 1) features_tc_kernel(const TcParams p) {
   extern __shared__ __align__(128) unsigned char tc_smem[];
   unsigned char *base = tc_smem;
@@ -355,7 +355,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) features_tc_kernel(const TcPara
       bufB[s] = __ldg(reinterpret_cast<const float4 *>(pB + s * 16));
     }
     uint32_t it = 0, slot = 0, lo_par = 1;  // tiles produced so far, xl ring slot and its wait parity
-    const bool want_sums = p.hopsum != nullptr;
+    constexpr bool want_sums = SUMS;  // compile-time: the lmfe path pays nothing for the mfcc sums
     for (; t < p.num_tiles; t += gridDim.x, ++it) {
       const float *nA = row_ptr(t + gridDim.x, rA), *nB = row_ptr(t + gridDim.x, rB);
       float a2 = 0.f, a0 = 0.f, aa = 0.f, b2 = 0.f, b0 = 0.f, ba = 0.f;  // hop sums of rows rA, rB (this lane's samples)
@@ -640,7 +640,11 @@ int launch_features_tc(spb_context *ctx, const FeatArgs &a) {
   int per_sm = 0;
   const bool km5 = (pl->seg_kmin & 15) == 5;  // the speechpy default bank starts at bin 5
   const bool fast = p.vec4 && !p.mfe;
-  auto kern = km5 ? (fast ? features_tc_kernel<5, true> : features_tc_kernel<5, false>) : features_tc_kernel<-1, false>;
+  const bool sums = p.hopsum != nullptr;
+  auto kern = sums ? (km5 ? (fast ? features_tc_kernel<5, true, true> : features_tc_kernel<5, false, true>)
+                          : features_tc_kernel<-1, false, true>)
+                   : (km5 ? (fast ? features_tc_kernel<5, true, false> : features_tc_kernel<5, false, false>)
+                          : features_tc_kernel<-1, false, false>);
   int rc = configure_kernel(ctx, (const void *)kern, kTcThreads, kTcSmem, &per_sm);
   if (rc) return rc;
   if (per_sm < 1) return fail(ctx, SPB_ERR_INVALID, "features_tc: kernel does not fit on an SM");
