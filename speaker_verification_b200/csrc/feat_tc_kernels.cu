@@ -25,7 +25,7 @@
 //                hop rotation as immediates, |X|^2), then the segment-form mel sums with a
 //                flush (lg2, one predicated 16-byte store every fourth filter) where a segment ends
 //   warp  8      MMA issuer (one elected thread), M128 N256 K16 kind::f16, two TMEM accumulators
-//   warps 9..16  converters: 128-bit sample loads five k-steps ahead (+ L2 bulk prefetch two tiles
+//   warps 9..16  converters: 128-bit sample loads two k-steps ahead (+ L2 bulk prefetch two tiles
 //                ahead), split, st.shared into the no-swizzle K-major operand buffers
 //                (xh: whole tile, xl: ring of 7 k-steps)
 // The DFT matrix (2 x 77.5 KB) stays resident in shared memory; 223 KB of the 227 KB are in use.
@@ -50,7 +50,10 @@ constexpr int kTcN = 256;                         // MMA N
 constexpr int kTcNAlloc = 248;                    // stored columns: (re, im) of up to 124 bins
 constexpr int kTcMaxBins = kTcNAlloc / 2;
 constexpr int kTcLoSlots = 7;                     // xl ring depth (k-steps)
-constexpr int kTcAhead = 5;                       // converter load distance (k-steps)
+#ifndef SPB_TC_AHEAD
+#define SPB_TC_AHEAD 2   // must divide 10.  Measured 1.119 / 1.126 / 1.140 ms at 1 / 2 / 5: the L2 bulk prefetch covers DRAM, registers matter more
+#endif
+constexpr int kTcAhead = SPB_TC_AHEAD;            // converter load distance (k-steps)
 constexpr int kTcOutPitch = 40;                   // at most this many filters
 constexpr uint32_t kTcBLbo = kTcNAlloc * 16;             // 3 968 B between the k-chunks of W
 constexpr uint32_t kTcBMat = (kTcHop / 8) * kTcBLbo;     // 79 360 B: [k/8][col][8 halves]
