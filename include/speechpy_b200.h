@@ -80,6 +80,19 @@ SPB_API int spb_launch_count(spb_context *ctx, uint64_t *count);
  * 3 = cosine GEMM. */
 SPB_API int spb_timing_enable(spb_context *ctx, int32_t on);
 SPB_API int spb_timing_read(spb_context *ctx, int32_t kernel, double *total_ms, uint64_t *launches);
+/* Process-wide kernel selection and guard knobs.  The defaults are the product path; the other
+ * values exist so that tests can cross-check one kernel family against another on the same call
+ * (parity of every variant) and so that the guard can be calibrated.
+ *   "feature_kernel"  0 auto | 1 generic radix-2 FFT kernel | 2 CUDA-core FFT kernels only
+ *   "cmvnw_kernel"    0 auto (single pass) | 1 small-tile two-pass | 2 large-tile two-pass
+ *   "tc_version"      2 (default) | 1: generation of the tensor-core lmfe kernel
+ *   "tc_epilogue"     -1 auto | 0 generic | 1 runs of four filters (when the bank allows) | 2 static
+ *   "redo"            1 (default) | 0: float64 recomputation of low-energy filters (the guard that
+ *                     keeps every log-mel value within 1e-4 of feature.py:216-217,256)
+ *   "tau_tc", "tau_fft"  guard thresholds (fractions of the frame's level)
+ * Unknown names / out-of-range values return SPB_ERR_INVALID. */
+SPB_API int spb_set_option(const char *name, double value);
+SPB_API int spb_get_option(const char *name, double *value);
 /* Pinned host memory, so callers can hand page-locked buffers to the host API. */
 SPB_API int spb_host_alloc(void **ptr, size_t bytes);
 SPB_API int spb_host_free(void *ptr);

@@ -39,6 +39,8 @@ PROTOTYPES = {
     "spb_launch_count": (C.c_int, [c_vp, C.POINTER(c_u64)]),
     "spb_timing_enable": (C.c_int, [c_vp, c_i32]),
     "spb_timing_read": (C.c_int, [c_vp, c_i32, C.POINTER(C.c_double), C.POINTER(c_u64)]),
+    "spb_set_option": (C.c_int, [C.c_char_p, C.c_double]),
+    "spb_get_option": (C.c_int, [C.c_char_p, C.POINTER(C.c_double)]),
     "spb_host_alloc": (C.c_int, [C.POINTER(c_vp), C.c_size_t]),
     "spb_host_free": (C.c_int, [c_vp]),
     "spb_num_frames": (C.c_int, [c_i64, c_i32, c_i32, c_i32, C.POINTER(c_i64)]),
@@ -123,6 +125,36 @@ def check(rc: int, ctx=None):
     if rc == SPB_ERR_UNSUPPORTED:
         raise NotImplementedError(msg)
     raise SpbError(rc, msg)
+
+
+def set_option(name: str, value: float):
+    """spb_set_option: process-wide kernel selection / guard knobs (see the header)."""
+    check(load().spb_set_option(name.encode(), float(value)))
+
+
+def get_option(name: str) -> float:
+    v = C.c_double()
+    check(load().spb_get_option(name.encode(), C.byref(v)))
+    return v.value
+
+
+class options:
+    """Context manager: set options for the duration of a block, then restore them."""
+
+    def __init__(self, **kw):
+        self.kw = kw
+        self.old = {}
+
+    def __enter__(self):
+        for k, v in self.kw.items():
+            self.old[k] = get_option(k)
+            set_option(k, v)
+        return self
+
+    def __exit__(self, *exc):
+        for k, v in self.old.items():
+            set_option(k, v)
+        return False
 
 
 class Context:

@@ -11,6 +11,11 @@ namespace spb {
 
 static thread_local std::string g_last_error;
 
+Options &options() {
+  static Options o;
+  return o;
+}
+
 void set_global_error(const std::string &msg) { g_last_error = msg; }
 
 int fail(spb_context *ctx, int code, const std::string &msg) {
@@ -106,6 +111,15 @@ int get_fft_tables(spb_context *ctx, int nfft, FftTables *out) {
     }
     SPB_CUDA(ctx, cudaMalloc(&t.d_tw, tw.size() * sizeof(float2)));
     SPB_CUDA(ctx, cudaMemcpy(t.d_tw, tw.data(), tw.size() * sizeof(float2), cudaMemcpyHostToDevice));
+  }
+  {
+    std::vector<double2> tw((size_t)nfft);
+    for (int r = 0; r < nfft; ++r) {
+      const double a = two_pi * (double)r / (double)nfft;
+      tw[r] = make_double2(cos(a), -sin(a));
+    }
+    SPB_CUDA(ctx, cudaMalloc(&t.d_tw64, tw.size() * sizeof(double2)));
+    SPB_CUDA(ctx, cudaMemcpy(t.d_tw64, tw.data(), tw.size() * sizeof(double2), cudaMemcpyHostToDevice));
   }
   if (nfft == 512) {
     std::vector<float2> a(16 * 16), b(16 * 9);
@@ -218,6 +232,7 @@ int spb_destroy(spb_context *ctx) {
     if (kv.second.d_tw) cudaFree(kv.second.d_tw);
     if (kv.second.d_twA) cudaFree(kv.second.d_twA);
     if (kv.second.d_twB) cudaFree(kv.second.d_twB);
+    if (kv.second.d_tw64) cudaFree(kv.second.d_tw64);
   }
   cudaEventDestroy(ctx->ev_a);
   cudaEventDestroy(ctx->ev_b);
@@ -497,6 +512,10 @@ int spb_plan_create(spb_context *ctx, const spb_feature_params *params, const do
     spb_plan_destroy(pl);
     return cuda_fail(ctx, e, "plan upload");
   }
+  if ((e = cudaMalloc(&pl->d_tc_flag, 2048)) != cudaSuccess || (e = cudaMemset(pl->d_tc_flag, 0, 2048)) != cudaSuccess) {
+    spb_plan_destroy(pl);
+    return cuda_fail(ctx, e, "plan flags");
+  }
   FftTables t;
   int rc = get_fft_tables(ctx, q.nfft, &t);
   if (!rc && pl->seg_nbins > 0) rc = build_tc_plan(ctx, pl, seg_rd.data());
@@ -520,6 +539,7 @@ int spb_plan_destroy(spb_plan *pl) {
   cudaFree(pl->d_dct);
   cudaFree(pl->d_tc_whi);
   cudaFree(pl->d_tc_wlo);
+  cudaFree(pl->d_tc2_w);
   cudaFree(pl->d_tc_flag);
   delete pl;
   return SPB_OK;
@@ -810,18 +830,33 @@ static void fill_feat_args(FeatArgs &a, const spb_batch *b, const float *d_sampl
   a.energy = d_energy;
 }
 
-// force_generic: 0 auto, 1 generic kernel (used by tests to cross-check the fast path)
-static int g_force_generic = 0;
-static int g_force_small_cmvnw = 0;
-static int g_no_tc = 0;
-// tensor-core feature kernel: SPB_TC=0 disables it (read once)
-static bool tc_enabled() {
-  static int v = -1;
-  if (v < 0) {
-    const char *e = getenv("SPB_TC");
-    v = (e && e[0] == '0') ? 0 : 1;
+// Exactness guard lists of one feature launch: scratch slots 8 (tensor-core kernel) and 9 (FFT kernels)
+// hold the entries, the plan's flag block the counters.  Capacity: a quarter of the launch's rows
+// (noise flags ~1e-4 of the values); what does not fit sets the overflow flag (redo_all_kernel).
+static int setup_redo(spb_context *ctx, FeatArgs &a, int64_t rows, bool tc) {
+  a.redo_tc = RedoList();
+  a.redo_fft = RedoList();
+  const Options &opt = options();
+  if (!opt.redo || !a.plan || a.M < 1 || !(a.mode == FEAT_MFE || a.mode == FEAT_LMFE)) return SPB_OK;
+  const int64_t cap = std::min<int64_t>(std::max<int64_t>(rows / 4, 65536), (int64_t)1 << 26);
+  int *flags = a.plan->d_tc_flag;
+  if (tc) {
+    RedoEntry *e = (RedoEntry *)scratch(ctx, 8, (size_t)cap * sizeof(RedoEntry));
+    if (!e) return SPB_ERR_CUDA;
+    a.redo_tc.entries = e;
+    a.redo_tc.count = flags + 1;
+    a.redo_tc.overflow = flags + 2;
+    a.redo_tc.cap = (int)cap;
+    a.redo_tc.tau = (float)opt.tau_tc;
   }
-  return v != 0;
+  RedoEntry *e = (RedoEntry *)scratch(ctx, 9, (size_t)cap * sizeof(RedoEntry));
+  if (!e) return SPB_ERR_CUDA;
+  a.redo_fft.entries = e;
+  a.redo_fft.count = flags + 3;
+  a.redo_fft.overflow = flags + 4;
+  a.redo_fft.cap = (int)cap;
+  a.redo_fft.tau = (float)opt.tau_fft;
+  return SPB_OK;
 }
 
 static int run_features(spb_context *ctx, FeatArgs &a) {
@@ -829,20 +864,27 @@ static int run_features(spb_context *ctx, FeatArgs &a) {
   FftTables t;
   int rc = get_fft_tables(ctx, a.nfft, &t);
   if (rc) return rc;
+  const Options &opt = options();
+  const bool generic = opt.feature_kernel == 1;
+  const bool use_tc = opt.feature_kernel == 0 && features_tc_supported(a) && fast512_supported(a);
+  const int64_t rows = a.num_tiles * (int64_t)a.tile_frames;
+  if ((rc = setup_redo(ctx, a, rows, use_tc && features_tc_has_guard(a)))) return rc;
   const size_t tb = timing_begin(ctx);
-  if (!g_force_generic && !g_no_tc && tc_enabled() && features_tc_supported(a) && fast512_supported(a)) {
+  if (a.plan) SPB_CUDA(ctx, cudaMemsetAsync(a.plan->d_tc_flag, 0, 32, ctx->stream));  // flag + guard counters
+  if (use_tc) {
     // tensor-core kernel; samples it cannot split (|x| >= 2, NaN, inf) raise the plan's flag
     // and the guarded CUDA-core kernel redoes the launch
-    SPB_CUDA(ctx, cudaMemsetAsync(a.plan->d_tc_flag, 0, 4, ctx->stream));
     rc = launch_features_tc(ctx, a);
     if (!rc) {
       a.run_if = a.plan->d_tc_flag;
       rc = launch_features_fast512(ctx, a, t);
       a.run_if = nullptr;
     }
-  } else if (!g_force_generic && fast512_supported(a)) rc = launch_features_fast512(ctx, a, t);
-  else if (!g_force_generic && fast1024_supported(a)) rc = launch_features_fast1024(ctx, a, t);
+    if (!rc) rc = launch_redo(ctx, a, a.redo_tc, a.plan->d_tc_flag, t);
+  } else if (!generic && fast512_supported(a)) rc = launch_features_fast512(ctx, a, t);
+  else if (!generic && fast1024_supported(a)) rc = launch_features_fast1024(ctx, a, t);
   else rc = launch_features_generic(ctx, a, t);
+  if (!rc) rc = launch_redo(ctx, a, a.redo_fft, nullptr, t);
   timing_end(ctx, 0, tb);
   return rc;
 }
@@ -879,7 +921,7 @@ static int lmfe_cmvnw_chunk(spb_context *ctx, const spb_batch *b, const BatchChu
   int rc = run_features(ctx, a);
   if (rc) return rc;
   float *ms_biased = d_ms ? d_ms - (ptrdiff_t)c.row0 * M : nullptr;
-  if (b->big_rmax > 0 && !g_force_small_cmvnw && (((size_t)d_out) & 15) == 0)
+  if (b->big_rmax > 0 && options().cmvnw_kernel != 1 && (((size_t)d_out) & 15) == 0)
     return launch_cmvnw_big(ctx, lmfe_biased, ms_biased, d_out, b->d_nframes, b->d_frame_offsets,
                             b->d_big_tiles + c.big0, c.big1 - c.big0, b->big_rmax, M, M, win,
                             pl->p.cmvn_variance);
@@ -917,8 +959,8 @@ static int run_lmfe_cmvnw(spb_context *ctx, const spb_batch *b, const float *d_s
 // into scratch, then energy + DCT + deltas (mfcc_post_kernel).  Usable when the plan and the batch
 // qualify for the tensor-core kernel.
 static bool mfcc_hybrid_ok(const spb_batch *b, int mode) {
-  return (mode == FEAT_MFCC || mode == FEAT_MFCC_DELTA) && b->d_tc_groups && b->plan->tc_ok && !g_force_generic &&
-         !g_no_tc && tc_enabled() && b->plan->p.num_cepstral >= 1;
+  return (mode == FEAT_MFCC || mode == FEAT_MFCC_DELTA) && b->d_tc_groups && b->plan->tc_ok &&
+         options().feature_kernel == 0 && b->plan->p.num_cepstral >= 1;
 }
 
 static int mfcc_hybrid_chunk(spb_context *ctx, const spb_batch *b, const BatchChunk &c, const float *d_samples,
@@ -1030,11 +1072,34 @@ static int single_signal(spb_context *ctx, const spb_plan *plan, const void *sig
 
 extern "C" {
 
-// test hook (not in the public header): route every feature launch through the generic kernel
-SPB_API int spb_debug_force_generic(int on) {
-  g_force_generic = on & 1;
-  g_force_small_cmvnw = (on >> 1) & 1;  // bit 1: small-tile cmvnw kernels (cross-check)
-  g_no_tc = (on >> 2) & 1;              // bit 2: CUDA-core FFT kernel instead of the tensor-core one
+int spb_set_option(const char *name, double value) {
+  if (!name) return fail(nullptr, SPB_ERR_INVALID, "spb_set_option: NULL name");
+  Options &o = options();
+  const std::string n(name);
+  const int iv = (int)value;
+  if (n == "feature_kernel" && iv >= 0 && iv <= 2) o.feature_kernel = iv;
+  else if (n == "cmvnw_kernel" && iv >= 0 && iv <= 2) o.cmvnw_kernel = iv;
+  else if (n == "tc_version" && (iv == 1 || iv == 2)) o.tc_version = iv;
+  else if (n == "tc_epilogue" && iv >= -1 && iv <= 2) o.tc_epilogue = iv;
+  else if (n == "redo" && (iv == 0 || iv == 1)) o.redo = iv;
+  else if (n == "tau_tc" && value >= 0.0) o.tau_tc = value;
+  else if (n == "tau_fft" && value >= 0.0) o.tau_fft = value;
+  else return fail(nullptr, SPB_ERR_INVALID, "spb_set_option: unknown option or value out of range: " + n);
+  return SPB_OK;
+}
+
+int spb_get_option(const char *name, double *value) {
+  if (!name || !value) return fail(nullptr, SPB_ERR_INVALID, "spb_get_option: NULL argument");
+  const Options &o = options();
+  const std::string n(name);
+  if (n == "feature_kernel") *value = o.feature_kernel;
+  else if (n == "cmvnw_kernel") *value = o.cmvnw_kernel;
+  else if (n == "tc_version") *value = o.tc_version;
+  else if (n == "tc_epilogue") *value = o.tc_epilogue;
+  else if (n == "redo") *value = o.redo;
+  else if (n == "tau_tc") *value = o.tau_tc;
+  else if (n == "tau_fft") *value = o.tau_fft;
+  else return fail(nullptr, SPB_ERR_INVALID, "spb_get_option: unknown option: " + n);
   return SPB_OK;
 }
 
@@ -1200,7 +1265,7 @@ int spb_cmvnw(spb_context *ctx, const double *vec, int64_t rows, int32_t cols, i
   if (rc) return rc;
   const int32_t nfr = (int32_t)rows;
   const int64_t offs[2] = {0, rows};
-  const int big_rmax = g_force_small_cmvnw ? 0 : cmvnw_big_rmax(cols, win);
+  const int big_rmax = options().cmvnw_kernel == 1 ? 0 : cmvnw_big_rmax(cols, win);
   if (big_rmax > 0) {
     // large-tile kernels over all columns at once
     std::vector<int4> tiles;

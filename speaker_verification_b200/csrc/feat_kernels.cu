@@ -49,6 +49,8 @@ struct FeatParams {
   const float2 *tw;
   int nfft, log2nc;
   int need_energy;
+  int need_level;     // per-frame sum x^2 for the exactness guard (redo.entries != nullptr, mfe / lmfe output)
+  RedoList redo;      // filters below tau x sum x^2 are listed for the float64 redo (redo_kernels.cu)
   const int *run_if;  // fast512: when set, the launch is a no-op unless *run_if != 0
 };
 
@@ -72,7 +74,8 @@ __device__ __forceinline__ void output_stage(const FeatParams &p, const float *s
                                              const float *s_bw, const int *s_bmeta,
                                              const float *s_dct, int nf, long long row0,
                                              const float4 *s_rd, const int4 *s_wr,
-                                             float *s_U, float *s_D, const FmIndex fm) {
+                                             float *s_U, float *s_D, const FmIndex fm,
+                                             const float *s_lvl, const long long gstart) {
   const int tid = threadIdx.x;
   const int nthreads = blockDim.x;
   const float scale = 1.0f / (float)p.nfft;  // |X|^2 / NFFT  (processing.py:174)
@@ -133,8 +136,13 @@ __device__ __forceinline__ void output_stage(const FeatParams &p, const float *s
       float *pa = s_a + fm.f0 * astride + m;
       float *dst = p.out + (row0 + fm.f0) * M + m;  // tile rows are contiguous in global memory
       const int ustep = rpp * upitch, astep = rpp * astride, dstep = rpp * M;
+      const bool guard = direct && p.need_level != 0;
       for (int f = fm.f0; f < nf; f += rpp) {
-        float acc = (*pu + *pd) * scale;
+        const float raw = *pu + *pd;
+        // exactness guard: fp32 cannot resolve a filter this far below the frame's level
+        if (guard && raw < p.redo.tau * s_lvl[f])
+          redo_push(p.redo, gstart + (long long)f * p.S, (row0 + f) * (long long)M + m);
+        float acc = raw * scale;
         if (acc == 0.f) acc = kEpsF64AsF32;  // functions.zero_handling (feature.py:217)
         const float v = (mode == FEAT_MFE) ? acc : __logf(acc);
         if (direct) *dst = v; else *pa = v;
@@ -166,6 +174,8 @@ __device__ __forceinline__ void output_stage(const FeatParams &p, const float *s
           acc = fmaf(w.z, pr[k + 2], acc);
           acc = fmaf(w.w, pr[k + 3], acc);
         }
+        if (p.need_level != 0 && acc < p.redo.tau * s_lvl[f])
+          redo_push(p.redo, gstart + (long long)f * p.S, (row0 + f) * (long long)M + m);
         acc *= scale;
         if (acc == 0.f) acc = kEpsF64AsF32;  // functions.zero_handling (feature.py:217)
         s_a[f * astride + m] = (p.mode == FEAT_MFE) ? acc : __logf(acc);
@@ -285,7 +295,8 @@ features_fast512(const FeatParams p) {
   float *s_p = reinterpret_cast<float *>(s_exch + 2 * kNW * 256);        // [kTile][PSTRIDE]
   float *s_bw = s_p + kTile * PSTRIDE;                                 // [band_total] (16 B aligned)
   float *s_en = s_bw + p.band_total;                                // [kTile]
-  float *s_a = s_en + kTile;                                        // [kTile][M+1]
+  float *s_lvl = s_en + kTile;                                      // [kTile] sum x^2 per frame (exactness guard)
+  float *s_a = s_lvl + kTile;                                       // [kTile][M+1]
   float *s_b = s_a + kTile * (p.M + 1);                             // [kTile][C+1]
   float *s_dct = s_b + kTile * (p.C + 1);                           // [C*M]
   int *s_bmeta = reinterpret_cast<int *>(s_dct + p.C * p.M);        // [3M]
@@ -353,11 +364,12 @@ features_fast512(const FeatParams p) {
     cp_async16(&s_fd[slot][1], src + 1);
     cp_async_commit();
   };
-  auto stage = [&](int slot, int b, long long &row0, int &nf, bool &bulk) {
+  auto stage = [&](int slot, int b, long long &row0, int &nf, bool &bulk, long long &gs) {
     const int4 d0 = s_fd[slot][0];
     const longlong2 d1 = *reinterpret_cast<const longlong2 *>(&s_fd[slot][1]);
     nf = d0.z;
     const long long gstart = d1.x;
+    gs = gstart;
     row0 = d1.y;
     const int count = (nf - 1) * S + L;
     const float *src = p.samples + gstart;
@@ -378,7 +390,7 @@ features_fast512(const FeatParams p) {
 
   long long tile = blockIdx.x;
   int buf = 0;
-  long long row0 = 0;
+  long long row0 = 0, gs = 0;
   int nf = 0;
   bool bulk = false;
   if (tid == 0) {
@@ -387,15 +399,15 @@ features_fast512(const FeatParams p) {
     cp_async_wait<0>();
   }
   __syncthreads();
-  if (tile < p.num_tiles) stage(0, 0, row0, nf, bulk);
+  if (tile < p.num_tiles) stage(0, 0, row0, nf, bulk, gs);
   for (; tile < p.num_tiles; buf ^= 1) {  // descriptor of the tile in sample buffer b sits in ring slot b
     const long long next = tile + gridDim.x;
-    long long n_row0 = 0;
+    long long n_row0 = 0, n_gs = 0;
     int n_nf = 0;
     bool n_bulk = false;
     // prefetch the next tile while this one is transformed (its buffer was last read in
     // phase B of the previous iteration, which every thread has left)
-    if (next < p.num_tiles) stage(buf ^ 1, buf ^ 1, n_row0, n_nf, n_bulk);
+    if (next < p.num_tiles) stage(buf ^ 1, buf ^ 1, n_row0, n_nf, n_bulk, n_gs);
     // slot `buf` (this tile's descriptor, consumed an iteration ago) takes the tile after next;
     // thread 0 waits for it just before the barrier that ends phase B
     const bool refill = tid == 0 && next + gridDim.x < p.num_tiles;
@@ -439,7 +451,7 @@ features_fast512(const FeatParams p) {
         }
       }
       float2 sumsq = p_bc(0.f);
-      if (p.need_energy) {
+      if (p.need_energy || p.need_level) {
 #pragma unroll
         for (int j = 0; j < 16; ++j)
           if (j < NJ) sumsq = p_fma(v[j].re, v[j].re, p_fma(v[j].im, v[j].im, sumsq));
@@ -505,7 +517,7 @@ features_fast512(const FeatParams p) {
         if (actA) prA[128] = pz.x;
         if (actB) prB[128] = pz.y;
       }
-      if (p.need_energy) {
+      if (p.need_energy || p.need_level) {
         // frame energy = sum_k P[k], all 257 one-sided bins (feature.py:202), via Parseval:
         // (NFFT*sum x^2 + X0^2 + X256^2) / (2*NFFT), X0 = Zr+Zi, X256 = Zr-Zi of Z[0]
 #pragma unroll
@@ -513,7 +525,11 @@ features_fast512(const FeatParams p) {
           sumsq.x += __shfl_xor_sync(0xffffffffu, sumsq.x, o, 16);
           sumsq.y += __shfl_xor_sync(0xffffffffu, sumsq.y, o, 16);
         }
-        if (l16 == 0) {
+        if (l16 == 0 && p.need_level) {
+          if (actA) s_lvl[flA] = sumsq.x;
+          if (actB) s_lvl[flB] = sumsq.y;
+        }
+        if (l16 == 0 && p.need_energy) {
           const float2 x0 = p_add(v[0].re, v[0].im), x256 = p_sub(v[0].re, v[0].im);
           float ea = (512.f * sumsq.x + x0.x * x0.x + x256.x * x256.x) * (1.0f / (2.f * 512.f));
           float eb = (512.f * sumsq.y + x0.y * x0.y + x256.y * x256.y) * (1.0f / (2.f * 512.f));
@@ -529,15 +545,15 @@ features_fast512(const FeatParams p) {
     // ---- phase C
     if (use_seg && p.mode == FEAT_LMFE)
       output_stage<kTile, true, FEAT_LMFE>(p, s_p, PSTRIDE, s_en, s_a, s_b, s_bw, s_bmeta, s_dct, nf, row0, s_rd,
-                                           s_wr, s_U, s_D, fm);
+                                           s_wr, s_U, s_D, fm, s_lvl, gs);
     else if (use_seg)
       output_stage<kTile, true>(p, s_p, PSTRIDE, s_en, s_a, s_b, s_bw, s_bmeta, s_dct, nf, row0, s_rd, s_wr,
-                                s_U, s_D, fm);
+                                s_U, s_D, fm, s_lvl, gs);
     else
       output_stage<kTile, false>(p, s_p, PSTRIDE, s_en, s_a, s_b, s_bw, s_bmeta, s_dct, nf, row0, s_rd, s_wr,
-                                 s_U, s_D, fm);
+                                 s_U, s_D, fm, s_lvl, gs);
     tile = next;
-    row0 = n_row0; nf = n_nf; bulk = n_bulk;
+    row0 = n_row0; nf = n_nf; bulk = n_bulk; gs = n_gs;
   }
 }
 
@@ -574,7 +590,8 @@ features_fast1024(const FeatParams p) {
   float *s_p = reinterpret_cast<float *>(s_exch + kF1kWarps * 16 * kF1kRS); // [kTile][PSTRIDE]
   float *s_bw = s_p + kTile * PSTRIDE;
   float *s_en = s_bw + p.band_total;
-  float *s_a = s_en + kTile;
+  float *s_lvl = s_en + kTile;
+  float *s_a = s_lvl + kTile;
   float *s_b = s_a + kTile * (p.M + 1);
   float *s_dct = s_b + kTile * (p.C + 1);
   int *s_bmeta = reinterpret_cast<int *>(s_dct + p.C * p.M);
@@ -635,11 +652,12 @@ features_fast1024(const FeatParams p) {
     cp_async16(&s_fd[slot][1], src + 1);
     cp_async_commit();
   };
-  auto stage = [&](int slot, int b, long long &row0, int &nf, bool &bulk) {
+  auto stage = [&](int slot, int b, long long &row0, int &nf, bool &bulk, long long &gs) {
     const int4 d0 = s_fd[slot][0];
     const longlong2 d1 = *reinterpret_cast<const longlong2 *>(&s_fd[slot][1]);
     nf = d0.z;
     const long long gstart = d1.x;
+    gs = gstart;
     row0 = d1.y;
     const int count = (nf - 1) * S + L;
     const float *src = p.samples + gstart;
@@ -660,7 +678,7 @@ features_fast1024(const FeatParams p) {
 
   long long tile = blockIdx.x;
   int buf = 0;
-  long long row0 = 0;
+  long long row0 = 0, gs = 0;
   int nf = 0;
   bool bulk = false;
   if (tid == 0) {
@@ -669,13 +687,13 @@ features_fast1024(const FeatParams p) {
     cp_async_wait<0>();
   }
   __syncthreads();
-  if (tile < p.num_tiles) stage(0, 0, row0, nf, bulk);
+  if (tile < p.num_tiles) stage(0, 0, row0, nf, bulk, gs);
   for (; tile < p.num_tiles; buf ^= 1) {
     const long long next = tile + gridDim.x;
-    long long n_row0 = 0;
+    long long n_row0 = 0, n_gs = 0;
     int n_nf = 0;
     bool n_bulk = false;
-    if (next < p.num_tiles) stage(buf ^ 1, buf ^ 1, n_row0, n_nf, n_bulk);
+    if (next < p.num_tiles) stage(buf ^ 1, buf ^ 1, n_row0, n_nf, n_bulk, n_gs);
     const bool refill = tid == 0 && next + gridDim.x < p.num_tiles;
     if (refill) fetch_desc(next + gridDim.x, buf);
     if (bulk) {
@@ -701,7 +719,7 @@ features_fast1024(const FeatParams p) {
         }
       }
       float sumsq = 0.f;
-      if (p.need_energy) {
+      if (p.need_energy || p.need_level) {
 #pragma unroll
         for (int j = 0; j < 16; ++j)
           if (j < NZ) sumsq = fmaf(v[j].x, v[j].x, fmaf(v[j].y, v[j].y, sumsq));
@@ -746,10 +764,11 @@ features_fast1024(const FeatParams p) {
         if (hb == 0) prow[k1r + 16 * q] = 0.25f * fmaf(xr, xr, xi * xi);
       }
       if (lane == 16) prow[256] = fmaf(v[0].x, v[0].x, v[0].y * v[0].y);  // Z[256] is its own partner
-      if (p.need_energy) {
+      if (p.need_energy || p.need_level) {
         // frame energy = sum of the one-sided power spectrum, via Parseval (feature.py:202)
         for (int o = 16; o >= 1; o >>= 1) sumsq += __shfl_xor_sync(0xffffffffu, sumsq, o);
-        if (lane == 0) {
+        if (lane == 0 && p.need_level) s_lvl[fl] = sumsq;
+        if (lane == 0 && p.need_energy) {
           const float x0 = v[0].x + v[0].y, xn = v[0].x - v[0].y;
           float e = (1024.f * sumsq + x0 * x0 + xn * xn) * (1.0f / 2048.f);
           if (e == 0.f) e = kEpsF64AsF32;  // feature.py:205
@@ -762,15 +781,15 @@ features_fast1024(const FeatParams p) {
     // ---- phase C
     if (use_seg && p.mode == FEAT_LMFE)
       output_stage<kTile, true, FEAT_LMFE>(p, s_p, PSTRIDE, s_en, s_a, s_b, s_bw, s_bmeta, s_dct, nf, row0, s_rd,
-                                           s_wr, s_U, s_D, fm);
+                                           s_wr, s_U, s_D, fm, s_lvl, gs);
     else if (use_seg)
       output_stage<kTile, true>(p, s_p, PSTRIDE, s_en, s_a, s_b, s_bw, s_bmeta, s_dct, nf, row0, s_rd, s_wr,
-                                s_U, s_D, fm);
+                                s_U, s_D, fm, s_lvl, gs);
     else
       output_stage<kTile, false>(p, s_p, PSTRIDE, s_en, s_a, s_b, s_bw, s_bmeta, s_dct, nf, row0, s_rd, s_wr,
-                                 s_U, s_D, fm);
+                                 s_U, s_D, fm, s_lvl, gs);
     tile = next;
-    row0 = n_row0; nf = n_nf; bulk = n_bulk;
+    row0 = n_row0; nf = n_nf; bulk = n_bulk; gs = n_gs;
   }
 }
 
@@ -790,7 +809,8 @@ features_generic(const FeatParams p) {
   float *s_p = reinterpret_cast<float *>(s_z + kGenWarps * nc);  // [kGenTile][pstride]
   float *s_bw = s_p + kGenTile * pstride;                  // 16 B aligned (kGenTile == 4)
   float *s_en = s_bw + p.band_total;
-  float *s_a = s_en + kGenTile;
+  float *s_lvl = s_en + kGenTile;
+  float *s_a = s_lvl + kGenTile;
   float *s_b = s_a + kGenTile * (p.M + 1);
   float *s_dct = s_b + kGenTile * (p.C + 1);
   int *s_bmeta = reinterpret_cast<int *>(s_dct + p.C * p.M);
@@ -852,9 +872,10 @@ features_generic(const FeatParams p) {
           prow[k] = 0.25f * fmaf(xr, xr, xi * xi);
           prow[nc - k] = 0.25f * fmaf(yr, yr, yi * yi);
         }
-        if (p.need_energy) {
+        if (p.need_energy || p.need_level) {
           for (int o = 16; o >= 1; o >>= 1) sumsq += __shfl_xor_sync(0xffffffffu, sumsq, o);
-          if (lane == 0) {
+          if (lane == 0 && p.need_level) s_lvl[warp] = sumsq;
+          if (lane == 0 && p.need_energy) {
             const float x0 = z[0].x + z[0].y, xn = z[0].x - z[0].y;
             const float nf_ = (float)p.nfft;
             float e = (nf_ * sumsq + x0 * x0 + xn * xn) / (2.f * nf_);
@@ -866,7 +887,8 @@ features_generic(const FeatParams p) {
       __syncthreads();
       const long long row0 = p.frame_offsets[utt] + f0;
       output_stage<kGenTile, false>(p, s_p, pstride, s_en, s_a, s_b, s_bw, s_bmeta, s_dct, nf, row0, nullptr,
-                                    nullptr, nullptr, nullptr, FmIndex{0, 0, 0, 0});
+                                    nullptr, nullptr, nullptr, FmIndex{0, 0, 0, 0}, s_lvl,
+                                    p.starts[utt] + (long long)f0 * p.S);
     }
   }
 }
@@ -901,11 +923,13 @@ static FeatParams make_params(const FeatArgs &a, const FftTables &t) {
   p.log2nc = lg;
   p.need_energy = (a.mode == FEAT_MFE && a.energy != nullptr) ||
                   (a.mode >= FEAT_MFCC && a.dc_elim);
+  p.redo = a.redo_fft;
+  p.need_level = (a.redo_fft.entries != nullptr && (a.mode == FEAT_MFE || a.mode == FEAT_LMFE)) ? 1 : 0;
   return p;
 }
 
 static size_t plan_smem_bytes(const FeatArgs &a, int tile) {
-  size_t floats = (size_t)tile                                   // s_en
+  size_t floats = 2 * (size_t)tile                               // s_en, s_lvl
                   + (size_t)tile * (a.M + 1) + (size_t)tile * (a.C + 1)
                   + (size_t)a.band_total + (size_t)a.C * a.M + 3 * (size_t)a.M;
   return floats * 4;

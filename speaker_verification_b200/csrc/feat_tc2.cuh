@@ -1,0 +1,674 @@
+// features_tc2_kernel: the lmfe kernel of the batch paths (second generation of the hop-block DFT on
+// tcgen05; included at the end of feat_tc_kernels.cu, whose tables / constant bank it shares).
+//
+// Same contract as features_tc_kernel (frame = 2 hops, X_f = A_f + e^{-2 pi i S k / NFFT} A_{f+1}),
+// but every hop is folded about its centre before it reaches the tensor cores:
+//
+//   n = 79.5 +- (m + 1/2), m = 0..79:   s[m] = x[80+m] + x[79-m],   d[m] = x[80+m] - x[79-m]
+//   A_h[k] = e^{-i 79.5 th_k} ( sum_m s[m] cos(th_k (m+1/2))  -  i sum_m d[m] sin(th_k (m+1/2)) )
+//
+// The common phase drops out of |X_f|^2, so the product per hop is TWO real K = 80 contractions
+// (s . C into the "real" accumulator columns, d . (-S) into the "imaginary" ones) instead of one
+// K = 160 contraction against (cos, -sin): half the tensor work and half the resident matrix
+// (4 x 20 KB: C_hi, C_lo, S_hi, S_lo), which frees shared memory for a 9-slot ring of whole
+// k-steps of the A operand (s_hi, s_lo, d_hi, d_lo; 16 KB per slot), i.e. the converters run up to
+// 1.8 tiles ahead of the MMAs and no role waits on another inside a tile.
+//
+// fp32 accuracy from fp16 tensor cores as before: s 2^14 = s_hi + s_lo (exact for 16-bit PCM:
+// 17 bits = 11 + 6), W = W_hi + W_lo; per tile the 20 small products first, then the 10 large ones
+// (TMEM accumulation truncates).  |s 2^14| >= 65520 (|x| >= 2), NaN, inf raise the flag and the
+// guarded CUDA-core FFT kernel redoes the launch.
+//
+// Epilogue: packed fp32 (FFMA2 / FMUL2) over bin PAIRS with the hop rotation and the mel weights
+// as uniform-register operands, one (rise, fall) FFMA2 per bin for the segment-form mel sums.
+// Three flavours of the segment walk:
+//   EPI 2  the speechpy default bank (40 filters, 16 kHz, NFFT 512): segment ends, the split of
+//          the filters between the two warps of a quadrant and the store schedule are
+//          compile-time constants (no per-bin tests, no counters)
+//   EPI 1  any bank whose halves hold multiples of four filters: log output in 16-byte runs
+//   EPI 0  everything else (mfe, odd filter counts)
+//
+// Exactness guard (north_star: |log-mel error| <= 1e-4 on every value): the converters track
+// max |s|, |d| per hop; a filter whose energy is below tau x the frame's level bound
+// 80 (max_f^2 + max_{f+1}^2) >= sum x^2 cannot be trusted in fp32 (absolute error ~1e-7 of the
+// level) and is appended to a list that redo_list_kernel (redo_kernels.cu) recomputes in float64.
+// (Included inside namespace spb.)
+#pragma once
+
+constexpr int kT2K = 80;                        // K of each product (folded hop)
+constexpr int kT2KSteps = kT2K / 16;            // 5 MMA k-steps
+constexpr int kT2N = 128;                       // MMA N: bins (cos block) / bins (sin block)
+constexpr int kT2MaxBins = 128;
+#ifndef SPB_T2_SLOTS
+#define SPB_T2_SLOTS 9
+#endif
+constexpr int kT2Slots = SPB_T2_SLOTS;          // A-operand ring depth (k-steps)
+constexpr uint32_t kT2BLbo = kT2N * 16;                 // 2 048 B between the k-chunks of a W matrix
+constexpr uint32_t kT2BMat = (kT2K / 8) * kT2BLbo;      // 20 480 B: [k/8][col][8 halves]
+constexpr uint32_t kT2APart = 2 * kTcRows * 16;         // 4 096 B: [2][row][8 halves] of one k-step
+constexpr uint32_t kT2SlotBytes = 4 * kT2APart;         // s_hi | s_lo | d_hi | d_lo
+constexpr uint32_t kT2OffA = 4 * kT2BMat;               // C_hi | C_lo | S_hi | S_lo, then the ring
+constexpr uint32_t kT2OffBars = kT2OffA + kT2Slots * kT2SlotBytes;
+constexpr uint32_t kT2OffLvl = kT2OffBars + 256;        // [4][128] per-hop level (max |s|, |d|), by tile & 3
+constexpr uint32_t kT2Smem = kT2OffLvl + 4 * kTcRows * 4;
+static_assert(kT2Smem <= 232448, "features_tc2: shared memory budget");
+static_assert((2 * kT2Slots + 4) * 8 + 4 <= 256, "features_tc2: barrier block");
+constexpr float kT2InScale = 16384.f;           // 2^14: s, d reach 2 |x|
+constexpr uint32_t kT2Idesc = (1u << 4) | ((uint32_t)(kT2N >> 3) << 17) | ((uint32_t)(kTcRows >> 4) << 24);
+
+// ------------------------------------------------------------------------------------------
+// The speechpy default bank at compile time.  Edges = feature.filterbanks(40, 257, 16000, 0|300,
+// 8000) (feature.py:55-82); build_tc_plan compares the runtime tables it derives
+// from the caller's dense bank with these and only then selects the static epilogue.
+// Bins are relative to kmin; segment s = bins (edge[s], edge[s+1]], the last one ends at bin 127.
+// ------------------------------------------------------------------------------------------
+struct T2Static {
+  int M, kmin, nb, s1;
+  int lo[2], hi[2];        // bins each half walks
+  int out_lo[2], nout[2];  // filters each half emits
+  uint32_t endmask[2][4];  // bit b: bin b closes a segment of this half
+};
+
+constexpr T2Static make_t2_static() {
+  constexpr int edges[42] = {4,  5,  6,  7,  8,  9,  10, 12, 13, 14, 16, 17, 19, 20,  22,  24,  26,  28,  30,  32, 35,
+                             37, 40, 42, 45, 49, 52, 55, 59, 63, 67, 71, 75, 80, 85, 90, 96, 102, 108, 114, 121, 128};
+  T2Static t{};
+  t.M = 40;
+  t.kmin = 5;
+  t.nb = 123;
+  t.s1 = 26;  // filters 0..25 | 26..39: balances bins x 7 + flushes x 11 instructions (654 | 690)
+  int first[41] = {}, last[41] = {};
+  for (int s = 0; s <= 40; ++s) {
+    first[s] = edges[s] + 1 - t.kmin;
+    last[s] = (edges[s + 1] < 127 ? edges[s + 1] : 127) - t.kmin;
+  }
+  t.lo[0] = 0;
+  t.hi[0] = last[t.s1];
+  t.lo[1] = first[t.s1];
+  t.hi[1] = t.nb - 1;
+  t.out_lo[0] = 0;
+  t.nout[0] = t.s1;
+  t.out_lo[1] = t.s1;
+  t.nout[1] = t.M - t.s1;
+  for (int h = 0; h < 2; ++h)
+    for (int i = 0; i < 4; ++i) t.endmask[h][i] = 0;
+  for (int s = 0; s <= 40; ++s) {
+    const int b = last[s];
+    if (s <= t.s1) t.endmask[0][b >> 5] |= 1u << (b & 31);
+    if (s >= t.s1) t.endmask[1][b >> 5] |= 1u << (b & 31);
+  }
+  return t;
+}
+constexpr T2Static kT2StaticHost = make_t2_static();
+__device__ constexpr T2Static kT2S = make_t2_static();
+
+struct T2Params {
+  const float *samples;
+  const TcGroup *groups;     // 4 per tile
+  long long num_tiles;
+  const __half *w;           // C_hi | C_lo | S_hi | S_lo in the shared-memory layout (4 x kT2BMat bytes)
+  TcHalf half[2];
+  int M;
+  float scale;               // 1 / (NFFT * 2^28)
+  float ln_scale;            // ln(scale)
+  int mfe;                   // 1: no log
+  float *out;
+  int *flag;                 // set when a sample cannot be split (|x| >= 2, NaN, inf)
+  const float *zeros;        // >= 640 B of zeros: the hop rows past the end of a group read these
+  float4 *hopsum;            // optional [tiles * 128]: per hop row {sum x^2, sum x, sum (-1)^n x, 0} for the mfcc energy
+  RedoList redo;             // low-energy filters to recompute exactly (entries == nullptr: off)
+};
+
+
+// ------------------------------------------------------------------------------------------
+// mbarrier waits with a watchdog: a protocol bug (or a fault elsewhere in the CTA) must end as a
+// launch error, not as a hung GPU.  The clock is read every 4096 polls only.
+// ------------------------------------------------------------------------------------------
+__device__ __forceinline__ bool t2_try_wait(const uint32_t bar_addr, const uint32_t parity, const uint32_t hint_ns) {
+  uint32_t ok;
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t"
+      "}"
+      : "=r"(ok)
+      : "r"(bar_addr), "r"(parity), "r"(hint_ns)
+      : "memory");
+  return ok != 0;
+}
+__device__ __noinline__ void t2_watchdog(unsigned long long &t0) {
+  unsigned long long now;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
+  if (t0 == 0) t0 = now;
+  else if (now - t0 > 4000000000ull) __trap();  // 4 s
+}
+// the hardware may park the warp for up to the hint
+__device__ __forceinline__ void t2_wait_park(uint64_t *bar, const uint32_t parity) {
+  const uint32_t a = smem_u32(bar);
+  uint32_t n = 0;
+  unsigned long long t0 = 0;
+  while (!t2_try_wait(a, parity, 20000u)) {
+    if ((++n & 4095u) == 0) t2_watchdog(t0);
+  }
+}
+// wait of a warp that is normally AHEAD of its producer (the converters): back off between polls
+__device__ __forceinline__ void t2_wait_nap(uint64_t *bar, const uint32_t parity) {
+  const uint32_t a = smem_u32(bar);
+  if (t2_try_wait(a, parity, 0u)) return;
+  uint32_t n = 0;
+  unsigned long long t0 = 0;
+  do {
+    __nanosleep(96);
+    if ((++n & 4095u) == 0) t2_watchdog(t0);
+  } while (!t2_try_wait(a, parity, 0u));
+}
+
+// ------------------------------------------------------------------------------------------
+// converter arithmetic: four forward samples f = x[80+m .. 80+m+3] and the four mirrored ones
+// b = x[76-m .. 79-m] -> s[i] = f[i] + b[3-i], d[i] = f[i] - b[3-i] (scaled by 2^14, one rounding:
+// fma(b, 2^14, f 2^14)), each split into fp16 hi + lo.  mx: running max of the |hi| bit patterns
+// (two 16-bit lanes; >= 0x7c00 means inf / NaN).  Packed fp32 throughout; the mirrored pair is
+// the LO_HI operand swizzle of FFMA2, not a move.
+// ------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t t2_pack_h2(const float lo, const float hi) {
+  const __half2 h = __floats2half2_rn(lo, hi);
+  return *reinterpret_cast<const uint32_t *>(&h);
+}
+
+struct T2Fold {
+  float2 s01, s23, d01, d23;  // scaled s, d of the four m values
+};
+
+__device__ __forceinline__ T2Fold t2_fold_split(const float4 f, const float4 b, uint2 &shi, uint2 &slo, uint2 &dhi,
+                                                uint2 &dlo, uint32_t &mx) {
+  const float2 sc = make_float2(kT2InScale, kT2InScale), nsc = make_float2(-kT2InScale, -kT2InScale);
+  const float2 a01 = __fmul2_rn(make_float2(f.x, f.y), sc), a23 = __fmul2_rn(make_float2(f.z, f.w), sc);
+  T2Fold r;
+  r.s01 = __ffma2_rn(make_float2(b.w, b.z), sc, a01);
+  r.s23 = __ffma2_rn(make_float2(b.y, b.x), sc, a23);
+  r.d01 = __ffma2_rn(make_float2(b.w, b.z), nsc, a01);
+  r.d23 = __ffma2_rn(make_float2(b.y, b.x), nsc, a23);
+  const __half2 hs0 = __floats2half2_rn(r.s01.x, r.s01.y), hs1 = __floats2half2_rn(r.s23.x, r.s23.y);
+  const __half2 hd0 = __floats2half2_rn(r.d01.x, r.d01.y), hd1 = __floats2half2_rn(r.d23.x, r.d23.y);
+  const float2 fs0 = __half22float2(hs0), fs1 = __half22float2(hs1);
+  const float2 fd0 = __half22float2(hd0), fd1 = __half22float2(hd1);
+  shi.x = *reinterpret_cast<const uint32_t *>(&hs0);
+  shi.y = *reinterpret_cast<const uint32_t *>(&hs1);
+  dhi.x = *reinterpret_cast<const uint32_t *>(&hd0);
+  dhi.y = *reinterpret_cast<const uint32_t *>(&hd1);
+  const float2 ls0 = __fadd2_rn(r.s01, make_float2(-fs0.x, -fs0.y)), ls1 = __fadd2_rn(r.s23, make_float2(-fs1.x, -fs1.y));
+  const float2 ld0 = __fadd2_rn(r.d01, make_float2(-fd0.x, -fd0.y)), ld1 = __fadd2_rn(r.d23, make_float2(-fd1.x, -fd1.y));
+  slo.x = t2_pack_h2(ls0.x, ls0.y);
+  slo.y = t2_pack_h2(ls1.x, ls1.y);
+  dlo.x = t2_pack_h2(ld0.x, ld0.y);
+  dlo.y = t2_pack_h2(ld1.x, ld1.y);
+  mx = __vimax3_s16x2(mx, shi.x & 0x7fff7fffu, shi.y & 0x7fff7fffu);
+  mx = __vimax3_s16x2(mx, dhi.x & 0x7fff7fffu, dhi.y & 0x7fff7fffu);
+  return r;
+}
+
+// per-hop sums of the mfcc energy path from the folded values (scaled by 2^14):
+// sum x = sum s, sum (-1)^n x = sum (-1)^m d (n = 80+m and 79-m have opposite parities),
+// sum x^2 = (sum s^2 + d^2) / 2
+__device__ __forceinline__ void t2_hop_sums(const T2Fold &v, float &q2, float &q0, float &qa) {
+  q2 = fmaf(v.s01.x, v.s01.x, fmaf(v.s01.y, v.s01.y, fmaf(v.s23.x, v.s23.x, fmaf(v.s23.y, v.s23.y, q2))));
+  q2 = fmaf(v.d01.x, v.d01.x, fmaf(v.d01.y, v.d01.y, fmaf(v.d23.x, v.d23.x, fmaf(v.d23.y, v.d23.y, q2))));
+  q0 += (v.s01.x + v.s01.y) + (v.s23.x + v.s23.y);
+  qa += (v.d01.x - v.d01.y) + (v.d23.x - v.d23.y);
+}
+
+// fp16 bit pattern (positive) -> float
+__device__ __forceinline__ float t2_level_of(const uint32_t bits16) {
+  return __half2float(__ushort_as_half((unsigned short)bits16));
+}
+
+// log-mel value of one filter from its unscaled energy a (x 2^28 NFFT): feature.py:216-217,256
+__device__ __forceinline__ float t2_log_value(const float a, const float ln_scale) {
+  float lg;
+  asm("lg2.approx.ftz.f32 %0, %1;" : "=f"(lg) : "f"(a));
+  const float r = fmaf(lg, 0.69314718055994531f, ln_scale);
+  return (a == 0.f) ? -36.04365338911715f : r;  // functions.zero_handling: exact zero -> eps
+}
+
+// hop rotation e^{-2 pi i 160 k / 512} = (cos, -sin)(2 pi (5k mod 16) / 16) of the bin pairs (j, j+1), j even, of a
+// 16-bin chunk when kmin = 5 (mod 16)
+struct T2Rot {
+  float2 cr[8], ci[8];
+};
+__constant__ T2Rot c_rot5 = {{{-0.9238795325112868f, 0.7071067811865474f}, {0.38268343236508984f, -1.0f}, {0.38268343236509f, 0.7071067811865476f}, {-0.9238795325112867f, 0.f}, {0.9238795325112867f, -0.7071067811865475f}, {-0.38268343236509034f, 1.0f}, {-0.3826834323650897f, -0.7071067811865477f}, {0.9238795325112865f, 0.f}},
+                             {{0.38268343236508967f, 0.7071067811865477f}, {-0.9238795325112867f, 0.f}, {0.9238795325112866f, -0.7071067811865475f}, {-0.3826834323650899f, 1.0f}, {-0.3826834323650898f, -0.7071067811865476f}, {0.9238795325112865f, 0.f}, {-0.9238795325112867f, 0.7071067811865475f}, {0.3826834323650904f, -1.0f}}};
+
+// |A_own + rot A_next|^2 of one bin pair (j, j + 1) of a 16-bin chunk.  KM = kmin mod 16 (rotation
+// as compile-time constants, period 16 in k at S = 160, NFFT = 512) or -1 (rotation from the table).
+template <int KM>
+__device__ __forceinline__ float2 t2_pair_power(const uint32_t (&vr)[16], const uint32_t (&vi)[16], const int j,
+                                                const float4 *tb) {
+  float2 cr, ci;
+  if (KM == 5) {
+    // from the constant bank, not as immediates: ptxas then parks the 16 pairs in uniform registers
+    // for the whole epilogue instead of re-materialising two UMOVs in front of every FFMA2
+    cr = c_rot5.cr[j >> 1];
+    ci = c_rot5.ci[j >> 1];
+  } else if (KM >= 0) {
+    cr = make_float2(kCos16[(5 * (KM + j)) & 15], kCos16[(5 * (KM + j + 1)) & 15]);
+    ci = make_float2(-kSin16[(5 * (KM + j)) & 15], -kSin16[(5 * (KM + j + 1)) & 15]);
+  } else {
+    cr = make_float2(tb[j].z, tb[j + 1].z);
+    ci = make_float2(tb[j].w, tb[j + 1].w);
+  }
+  const float2 a_re = make_float2(__uint_as_float(vr[j]), __uint_as_float(vr[j + 1]));
+  const float2 a_im = make_float2(__uint_as_float(vi[j]), __uint_as_float(vi[j + 1]));
+  float2 b_re, b_im;
+  b_re.x = __shfl_down_sync(0xffffffffu, a_re.x, 1);
+  b_re.y = __shfl_down_sync(0xffffffffu, a_re.y, 1);
+  b_im.x = __shfl_down_sync(0xffffffffu, a_im.x, 1);
+  b_im.y = __shfl_down_sync(0xffffffffu, a_im.y, 1);
+  float2 xr = __ffma2_rn(cr, b_re, a_re);
+  xr = __ffma2_rn(make_float2(-ci.x, -ci.y), b_im, xr);
+  float2 xi = __ffma2_rn(cr, b_im, a_im);
+  xi = __ffma2_rn(ci, b_re, xi);
+  return __ffma2_rn(xi, xi, __fmul2_rn(xr, xr));
+}
+
+
+// ------------------------------------------------------------------------------------------
+// Epilogue of one tile for one warp, run-time bank (EPI 0 / 1).  lane = hop row of the quadrant,
+// frame = hops (lane, lane + 1).  HALF is a template parameter so that every quantity the segment
+// walk branches on (chunk range, end masks) comes from kernel parameters and the loop counter only:
+// ptxas then keeps them in uniform registers and the per-bin branch is a BRA.U without
+// reconvergence bookkeeping.  The chunk loop is NOT unrolled (instruction cache).
+// thr: tau x level of this lane's frame (negative for rows that are not frames: never flagged).
+// ------------------------------------------------------------------------------------------
+template <int KM, int EPI, int HALF>
+__device__ __forceinline__ void t2_epilogue_dyn(const T2Params &p, const uint32_t taddr, float *pout, const bool row_ok,
+                                                const float thr, const long long soff, const long long oidx0) {
+  constexpr bool FAST = (EPI == 1);
+  const int ch_begin = p.half[HALF].ch_begin, ch_end = p.half[HALF].ch_end;
+  const uint32_t m0 = p.half[HALF].endmask[0], m1 = p.half[HALF].endmask[1];
+  const uint32_t m2 = p.half[HALF].endmask[2], m3 = p.half[HALF].endmask[3];
+  float2 rf = make_float2(0.f, 0.f);  // (rise, fall) sums of the current segment
+  float prev_u = 0.f;
+  // FAST: outputs leave in runs of four filters (one 16-byte store per lane).  `left` counts down to
+  // the next store; it starts at 5 because the first flush of a half only latches U of its first
+  // segment (filter j = U[j] + D[j+1]); that value shifts through o2..o0 and is gone before the
+  // first store.
+  float o0 = 0.f, o1 = 0.f, o2 = 0.f;
+  int left = 5, q4 = 0;
+  int skip = 1;                              // generic flush: the latch-only first flush
+  uint32_t bit = 0x80000000u, fbits = 0u;    // flagged filters; bit 31 absorbs the first flush
+  const float ln_scale = p.ln_scale, scale = p.scale;
+  const bool mfe = !FAST && p.mfe != 0;
+#pragma unroll 1
+  for (int ch = ch_begin; ch < ch_end; ++ch) {
+    uint32_t vr[16], vi[16];
+    tmem_ld16x2(taddr + ch * 16, taddr + kT2N + ch * 16, vr, vi);
+    const uint32_t mw = (ch < 4) ? ((ch < 2) ? m0 : m1) : ((ch < 6) ? m2 : m3);
+    const uint32_t mask = mw >> ((ch & 1) * 16);
+    const float4 *tb = &c_tc.tab[HALF][ch * 16];
+    float pw[16];
+#pragma unroll
+    for (int j = 0; j < 16; j += 2) {
+      const float2 pp = t2_pair_power<KM>(vr, vi, j, tb);
+      pw[j] = pp.x;
+      pw[j + 1] = pp.y;
+    }
+#pragma unroll
+    for (int j = 0; j < 16; ++j) {
+      const float2 w = *reinterpret_cast<const float2 *>(&tb[j]);
+      rf = __ffma2_rn(w, make_float2(pw[j], pw[j]), rf);
+      if ((mask >> j) & 1u) {
+        const float a = prev_u + rf.y;  // unscaled (x 2^28 NFFT): never denormal for real input
+        fbits |= (a < thr) ? bit : 0u;
+        bit = __funnelshift_l(bit, bit, 1);
+        if (FAST) {
+          const float r = t2_log_value(a, ln_scale);
+          --left;
+          if (left == 0 && row_ok) reinterpret_cast<float4 *>(pout)[q4] = make_float4(o0, o1, o2, r);
+          q4 += (left == 0) ? 1 : 0;
+          left = (left == 0) ? 4 : left;
+          o0 = o1; o1 = o2; o2 = r;
+        } else if (skip == 0) {
+          float r = mfe ? a * scale : t2_log_value(a, ln_scale);
+          if (mfe && a == 0.f) r = kTcEps;  // functions.zero_handling (feature.py:217)
+          if (row_ok) *pout = r;
+          ++pout;
+        }
+        skip = 0;
+        prev_u = rf.x;
+        rf = make_float2(0.f, 0.f);
+      }
+    }
+  }
+  fbits &= 0x7fffffffu;
+  if (fbits != 0u && p.redo.entries != nullptr) {
+    while (fbits) {
+      const int f = __ffs((int)fbits) - 1;
+      fbits &= fbits - 1;
+      redo_push(p.redo, soff, oidx0 + f);
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------------
+// Epilogue for the speechpy default bank (EPI 2): everything the walk depends on is a compile-time
+// constant (kT2S), the code is straight-line over the bins this half needs (~650 instructions per
+// half), the filter index of every flush is static: results sit in four named registers until their
+// 16-byte (or, at the split 26 | 14, 8-byte) store.
+// prow: row base (filter 0) of this lane's output row.
+// ------------------------------------------------------------------------------------------
+template <int HALF>
+__device__ __forceinline__ void t2_store_run(float *prow, const float (&ov)[4], const int g0, const int m, const bool row_ok) {
+  const int count = m - g0 + 1;
+  if (!row_ok) return;
+  if (count == 4) {
+    *reinterpret_cast<float4 *>(prow + g0) = make_float4(ov[0], ov[1], ov[2], ov[3]);
+  } else if (count == 2 && (g0 & 1) == 0) {
+    *reinterpret_cast<float2 *>(prow + g0) = make_float2(ov[g0 & 3], ov[(g0 + 1) & 3]);
+  } else {
+    for (int e = g0; e <= m; ++e) prow[e] = ov[e & 3];
+  }
+}
+
+template <int HALF>
+__device__ __forceinline__ void t2_epilogue_static(const T2Params &p, const uint32_t taddr, float *prow, const bool row_ok,
+                                                   const float thr, const long long soff, const long long oidx_row) {
+  constexpr int LO = kT2S.lo[HALF], HI = kT2S.hi[HALF];
+  constexpr int OUT_LO = kT2S.out_lo[HALF], NOUT = kT2S.nout[HALF];
+  constexpr int KM = kT2S.kmin & 15;
+  float2 rf = make_float2(0.f, 0.f);
+  float prev_u = 0.f;
+  float ov[4] = {0.f, 0.f, 0.f, 0.f};
+  uint32_t fbits = 0u;
+  int nfl = 0;  // flushes so far: a compile-time value once the loops below are unrolled
+  const float ln_scale = p.ln_scale;
+#pragma unroll
+  for (int ch = 0; ch < 8; ++ch) {
+    if (ch * 16 + 15 < LO || ch * 16 > HI) continue;
+    uint32_t vr[16], vi[16];
+    tmem_ld16x2(taddr + ch * 16, taddr + kT2N + ch * 16, vr, vi);
+    const float4 *tb = &c_tc.tab[HALF][ch * 16];
+    float pw[16];
+#pragma unroll
+    for (int j = 0; j < 16; j += 2) {
+      const int b = ch * 16 + j;
+      if (b + 1 < LO || b > HI) continue;
+      const float2 pp = t2_pair_power<KM>(vr, vi, j, tb);
+      pw[j] = pp.x;
+      pw[j + 1] = pp.y;
+    }
+#pragma unroll
+    for (int j = 0; j < 16; ++j) {
+      const int b = ch * 16 + j;
+      if (b < LO || b > HI) continue;
+      const float2 w = *reinterpret_cast<const float2 *>(&tb[j]);
+      rf = __ffma2_rn(w, make_float2(pw[j], pw[j]), rf);
+      if ((kT2S.endmask[HALF][b >> 5] >> (b & 31)) & 1u) {
+        if (nfl >= 1) {
+          const int m = OUT_LO + nfl - 1;  // filter this flush completes
+          const float a = prev_u + rf.y;
+          fbits |= (a < thr) ? (1u << (nfl - 1)) : 0u;
+          ov[m & 3] = t2_log_value(a, ln_scale);
+          if ((m & 3) == 3 || nfl == NOUT) {
+            const int g0 = ((m & ~3) > OUT_LO) ? (m & ~3) : OUT_LO;
+            t2_store_run<HALF>(prow, ov, g0, m, row_ok);
+          }
+        }
+        ++nfl;
+        prev_u = rf.x;
+        rf = make_float2(0.f, 0.f);
+      }
+    }
+  }
+  if (fbits != 0u && p.redo.entries != nullptr) {
+    while (fbits) {
+      const int f = __ffs((int)fbits) - 1;
+      fbits &= fbits - 1;
+      redo_push(p.redo, soff, oidx_row + OUT_LO + f);
+    }
+  }
+}
+
+
+// ------------------------------------------------------------------------------------------
+// The kernel.  One persistent CTA per SM, 17 warps:
+//   warps 0..7   epilogue (quadrant = warp % 4 owns hop rows 32q..32q+31 = group q of the tile,
+//                half = warp / 4 owns a range of filters)
+//   warp  8      MMA issuer (one elected thread): per k-step s_lo.C_hi, s_hi.C_lo -> real columns,
+//                d_lo.S_hi, d_hi.S_lo -> imaginary columns; then per k-step s_hi.C_hi, d_hi.S_hi and
+//                a tcgen05.commit that hands the ring slot back; M128 N128 K16 kind::f16
+//   warps 9..16  converters: lane = (k-chunk, row of 8, 8-byte half) so that a half-warp's
+//                st.shared.v2 covers 128 contiguous bytes of the no-swizzle K-major operand
+//                (conflict-free); 128-bit sample loads one k-step ahead + L2 bulk prefetch two
+//                tiles ahead
+// ------------------------------------------------------------------------------------------
+template <int KM, int EPI, bool SUMS>
+__global__ void __launch_bounds__(kTcThreads, 1) features_tc2_kernel(const T2Params p) {
+  extern __shared__ __align__(128) unsigned char tc_smem[];
+  unsigned char *base = tc_smem;
+  uint64_t *bars = reinterpret_cast<uint64_t *>(base + kT2OffBars);
+  uint64_t *full = bars;                          // [slots] k-step converted (8 converter warps)
+  uint64_t *empty = bars + kT2Slots;              // [slots] k-step consumed (tcgen05.commit)
+  uint64_t *acc_full = bars + 2 * kT2Slots;       // [2]
+  uint64_t *acc_empty = acc_full + 2;             // [2] 8 epilogue warps
+  uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(acc_empty + 2);
+  float *lvl = reinterpret_cast<float *>(base + kT2OffLvl);  // [4][128]
+
+  // the shuffle tells ptxas that the warp index is warp-uniform: role branches become uniform branches and
+  // uniform registers (memory descriptors, rotation constants) stay live across them
+  const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0);
+  const int lane = threadIdx.x & 31;
+  const uint32_t sbase = smem_u32(base);
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < kT2Slots; ++s) {
+      mbar_init(&full[s], kTcCvtWarps);
+      mbar_init(&empty[s], 1);
+    }
+    for (int a = 0; a < 2; ++a) {
+      mbar_init(&acc_full[a], 1);
+      mbar_init(&acc_empty[a], kTcEpiWarps);
+    }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == kTcMmaWarp) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)),
+                 "r"(512u)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  {  // resident DFT matrices
+    const uint4 *g = reinterpret_cast<const uint4 *>(p.w);
+    uint4 *s = reinterpret_cast<uint4 *>(base);
+    for (uint32_t i = threadIdx.x; i < 4 * kT2BMat / 16; i += kTcThreads) s[i] = __ldg(g + i);
+    fence_async_smem();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp >= kTcCvtWarp0) {
+    // ===== converters =====
+    const int cw = warp - kTcCvtWarp0;
+    const int kc = lane >> 4, r8 = (lane >> 1) & 7, hf = lane & 1;
+    const int qq = 2 * kc + hf;                    // which 4 of the 16 m values of a k-step
+    const int rA = cw * 8 + r8, rB = rA + 64;      // the two hop rows this thread feeds
+    const uint32_t dA = (uint32_t)(kc * (kTcRows * 16) + rA * 16 + hf * 8);
+    const uint32_t dB = dA + 64 * 16;
+    const int c = (warp - kTcCvtWarp0) * 32 + lane;
+    auto row_ptr = [&](long long t, int r) -> const float * {
+      if (t >= p.num_tiles) return p.zeros;
+      const TcGroup g = p.groups[t * 4 + (r >> 5)];
+      const int i = r & 31;
+      return (g.nf > 0 && i <= g.nf) ? p.samples + g.gstart + (long long)i * kTcHop : p.zeros;
+    };
+    // forward samples of k-step s: x[80 + 16 s + 4 qq ..], mirrored: x[76 - 16 s - 4 qq ..]
+    const int foff = kT2K + 4 * qq, boff = kT2K - 4 - 4 * qq;
+    long long t = blockIdx.x;
+    const float *pA = row_ptr(t, rA), *pB = row_ptr(t, rB);
+    float4 fA = __ldg(reinterpret_cast<const float4 *>(pA + foff)), bA = __ldg(reinterpret_cast<const float4 *>(pA + boff));
+    float4 fB = __ldg(reinterpret_cast<const float4 *>(pB + foff)), bB = __ldg(reinterpret_cast<const float4 *>(pB + boff));
+    uint32_t it = 0, slot = 0, par = 1;  // tiles produced so far, ring slot and its wait parity
+    uint32_t bad = 0;
+    for (; t < p.num_tiles; t += gridDim.x, ++it) {
+      const float *nA = row_ptr(t + gridDim.x, rA), *nB = row_ptr(t + gridDim.x, rB);
+      uint32_t mxA = 0u, mxB = 0u;
+      float a2 = 0.f, a0 = 0.f, aa = 0.f, b2 = 0.f, b0 = 0.f, ba = 0.f;
+      if (c < 4) {
+        // pull the samples of the tile after next into L2 with the TMA engine (one run per group)
+        const long long tp = t + 2 * (long long)gridDim.x;
+        if (tp < p.num_tiles) {
+          const TcGroup g = p.groups[tp * 4 + c];
+          if (g.nf > 0) bulk_prefetch_l2(p.samples + g.gstart, (uint32_t)(g.nf + 1) * (kTcHop * 4));
+        }
+      }
+#pragma unroll
+      for (int s = 0; s < kT2KSteps; ++s) {
+        const float4 cfA = fA, cbA = bA, cfB = fB, cbB = bB;
+        if (s + 1 < kT2KSteps) {
+          fA = __ldg(reinterpret_cast<const float4 *>(pA + foff + 16 * (s + 1)));
+          bA = __ldg(reinterpret_cast<const float4 *>(pA + boff - 16 * (s + 1)));
+          fB = __ldg(reinterpret_cast<const float4 *>(pB + foff + 16 * (s + 1)));
+          bB = __ldg(reinterpret_cast<const float4 *>(pB + boff - 16 * (s + 1)));
+        } else {
+          fA = __ldg(reinterpret_cast<const float4 *>(nA + foff));
+          bA = __ldg(reinterpret_cast<const float4 *>(nA + boff));
+          fB = __ldg(reinterpret_cast<const float4 *>(nB + foff));
+          bB = __ldg(reinterpret_cast<const float4 *>(nB + boff));
+        }
+        uint2 sha, sla, dha, dla, shb, slb, dhb, dlb;
+        const T2Fold va = t2_fold_split(cfA, cbA, sha, sla, dha, dla, mxA);
+        const T2Fold vb = t2_fold_split(cfB, cbB, shb, slb, dhb, dlb, mxB);
+        if (SUMS) {
+          t2_hop_sums(va, a2, a0, aa);
+          t2_hop_sums(vb, b2, b0, ba);
+        }
+        // keep the conversion ahead of the wait (the compiler otherwise sinks it below)
+        asm volatile("" ::"r"(sha.x), "r"(sha.y), "r"(sla.x), "r"(sla.y), "r"(dha.x), "r"(dha.y), "r"(dla.x), "r"(dla.y));
+        asm volatile("" ::"r"(shb.x), "r"(shb.y), "r"(slb.x), "r"(slb.y), "r"(dhb.x), "r"(dhb.y), "r"(dlb.x), "r"(dlb.y));
+        if (s == kT2KSteps - 1) {
+          // per-hop level for the epilogue's exactness guard (and the unsplittable-sample flag): max over
+          // the four lanes of a row, written BEFORE the arrive of the tile's last k-step (the epilogue
+          // reads it after acc_full, which is ordered after every full[] arrive of the tile)
+          mxA = __vmaxu2(mxA, __shfl_xor_sync(0xffffffffu, mxA, 1));
+          mxB = __vmaxu2(mxB, __shfl_xor_sync(0xffffffffu, mxB, 1));
+          mxA = __vmaxu2(mxA, __shfl_xor_sync(0xffffffffu, mxA, 16));
+          mxB = __vmaxu2(mxB, __shfl_xor_sync(0xffffffffu, mxB, 16));
+          const uint32_t ma = max(mxA & 0xffffu, mxA >> 16), mb = max(mxB & 0xffffu, mxB >> 16);
+          bad |= (ma >= 0x7c00u || mb >= 0x7c00u) ? 1u : 0u;
+          if ((lane & 17) == 0) {
+            lvl[(it & 3) * kTcRows + rA] = t2_level_of(ma);
+            lvl[(it & 3) * kTcRows + rB] = t2_level_of(mb);
+          }
+        }
+        t2_wait_nap(&empty[slot], par);
+        unsigned char *sl = base + kT2OffA + slot * kT2SlotBytes;
+        *reinterpret_cast<uint2 *>(sl + dA) = sha;
+        *reinterpret_cast<uint2 *>(sl + kT2APart + dA) = sla;
+        *reinterpret_cast<uint2 *>(sl + 2 * kT2APart + dA) = dha;
+        *reinterpret_cast<uint2 *>(sl + 3 * kT2APart + dA) = dla;
+        *reinterpret_cast<uint2 *>(sl + dB) = shb;
+        *reinterpret_cast<uint2 *>(sl + kT2APart + dB) = slb;
+        *reinterpret_cast<uint2 *>(sl + 2 * kT2APart + dB) = dhb;
+        *reinterpret_cast<uint2 *>(sl + 3 * kT2APart + dB) = dlb;
+        fence_async_smem();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&full[slot]);
+        if (++slot == kT2Slots) { slot = 0; par ^= 1; }
+      }
+      if (SUMS) {
+        // the four lanes of a row: lane bits 0 and 4
+        a2 += __shfl_xor_sync(0xffffffffu, a2, 1); a0 += __shfl_xor_sync(0xffffffffu, a0, 1); aa += __shfl_xor_sync(0xffffffffu, aa, 1);
+        b2 += __shfl_xor_sync(0xffffffffu, b2, 1); b0 += __shfl_xor_sync(0xffffffffu, b0, 1); ba += __shfl_xor_sync(0xffffffffu, ba, 1);
+        a2 += __shfl_xor_sync(0xffffffffu, a2, 16); a0 += __shfl_xor_sync(0xffffffffu, a0, 16); aa += __shfl_xor_sync(0xffffffffu, aa, 16);
+        b2 += __shfl_xor_sync(0xffffffffu, b2, 16); b0 += __shfl_xor_sync(0xffffffffu, b0, 16); ba += __shfl_xor_sync(0xffffffffu, ba, 16);
+        if ((lane & 17) == 0) {
+          constexpr float u1 = 1.0f / kT2InScale, u2 = 0.5f / (kT2InScale * kT2InScale);
+          p.hopsum[t * kTcRows + rA] = make_float4(a2 * u2, a0 * u1, aa * u1, 0.f);
+          p.hopsum[t * kTcRows + rB] = make_float4(b2 * u2, b0 * u1, ba * u1, 0.f);
+        }
+      }
+      pA = nA;
+      pB = nB;
+    }
+    if (bad) *p.flag = 1;
+  } else if (warp == kTcMmaWarp) {
+    // ===== MMA issuer =====
+    if (elect_one()) {
+      const uint32_t w_chi = sbase, w_clo = sbase + kT2BMat, w_shi = sbase + 2 * kT2BMat, w_slo = sbase + 3 * kT2BMat;
+      uint32_t slot = 0, par = 0, it = 0;
+      for (long long t = blockIdx.x; t < p.num_tiles; t += gridDim.x, ++it) {
+        const uint32_t acc = it & 1;
+        t2_wait_park(&acc_empty[acc], ((it >> 1) & 1) ^ 1);
+        tc_fence_after();
+        const uint32_t tm_re = tmem_base + acc * (2 * kT2N), tm_im = tm_re + kT2N;
+        const uint32_t slot0 = slot;
+        // small terms first, into the empty accumulators
+#pragma unroll
+        for (int s = 0; s < kT2KSteps; ++s) {
+          t2_wait_park(&full[slot], par);
+          tc_fence_after();
+          const uint32_t a = sbase + kT2OffA + slot * kT2SlotBytes;
+          const uint64_t d_shi = umma_desc_plain(a, kTcRows * 16), d_slo = umma_desc_plain(a + kT2APart, kTcRows * 16);
+          const uint64_t d_dhi = umma_desc_plain(a + 2 * kT2APart, kTcRows * 16);
+          const uint64_t d_dlo = umma_desc_plain(a + 3 * kT2APart, kTcRows * 16);
+          const uint32_t ko = s * 2 * kT2BLbo;
+          umma_f16(tm_re, d_slo, umma_desc_plain(w_chi + ko, kT2BLbo), kT2Idesc, s ? 1u : 0u);
+          umma_f16(tm_re, d_shi, umma_desc_plain(w_clo + ko, kT2BLbo), kT2Idesc, 1u);
+          umma_f16(tm_im, d_dlo, umma_desc_plain(w_shi + ko, kT2BLbo), kT2Idesc, s ? 1u : 0u);
+          umma_f16(tm_im, d_dhi, umma_desc_plain(w_slo + ko, kT2BLbo), kT2Idesc, 1u);
+          if (++slot == kT2Slots) { slot = 0; par ^= 1; }
+        }
+        // then the large ones; every k-step hands its ring slot back
+        uint32_t sl2 = slot0;
+#pragma unroll
+        for (int s = 0; s < kT2KSteps; ++s) {
+          const uint32_t a = sbase + kT2OffA + sl2 * kT2SlotBytes;
+          const uint32_t ko = s * 2 * kT2BLbo;
+          umma_f16(tm_re, umma_desc_plain(a, kTcRows * 16), umma_desc_plain(w_chi + ko, kT2BLbo), kT2Idesc, 1u);
+          umma_f16(tm_im, umma_desc_plain(a + 2 * kT2APart, kTcRows * 16), umma_desc_plain(w_shi + ko, kT2BLbo), kT2Idesc, 1u);
+          tc_commit(&empty[sl2]);
+          if (++sl2 == kT2Slots) sl2 = 0;
+        }
+        tc_commit(&acc_full[acc]);
+      }
+    }
+  } else {
+    // ===== epilogue =====
+    const int quad = warp & 3, half = warp >> 2;
+    const int M = p.M;
+    uint32_t it = 0;
+    for (long long t = blockIdx.x; t < p.num_tiles; t += gridDim.x, ++it) {
+      const TcGroup g = p.groups[t * 4 + quad];
+      const uint32_t acc = it & 1;
+      t2_wait_park(&acc_full[acc], (it >> 1) & 1);
+      tc_fence_after();
+      const uint32_t taddr = tmem_base + ((uint32_t)(quad * 32) << 16) + acc * (2 * kT2N);
+      const bool row_ok = lane < g.nf;
+      // level bound of this lane's frame: sum x^2 <= 80 (max_f^2 + max_{f+1}^2), in the units of the accumulator
+      const float l0 = lvl[(it & 3) * kTcRows + quad * 32 + lane];
+      const float l1 = lvl[(it & 3) * kTcRows + min(quad * 32 + lane + 1, kTcRows - 1)];
+      const float thr = row_ok ? p.redo.tau * (80.f * fmaf(l0, l0, l1 * l1)) : -1.f;
+      const long long soff = g.gstart + (long long)lane * kTcHop;
+      const long long row = g.row0 + lane;
+      if (EPI == 2) {
+        if (half == 0) t2_epilogue_static<0>(p, taddr, p.out + row * M, row_ok, thr, soff, row * M);
+        else t2_epilogue_static<1>(p, taddr, p.out + row * M, row_ok, thr, soff, row * M);
+      } else {
+        if (half == 0) t2_epilogue_dyn<KM, EPI, 0>(p, taddr, p.out + row * M, row_ok, thr, soff, row * M);
+        else t2_epilogue_dyn<KM, EPI, 1>(p, taddr, p.out + row * M + p.half[1].out_lo, row_ok, thr, soff,
+                                         row * M + p.half[1].out_lo);
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&acc_empty[acc]);
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == kTcMmaWarp) {
+    tc_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512u) : "memory");
+  }
+}

@@ -99,7 +99,6 @@ struct TcParams {
   int *flag;                 // set when a sample cannot be split (|x| >= 2, NaN, inf)
   const float *zeros;        // 1 KB of zeros: the hop rows past the end of a group read these
   float4 *hopsum;            // optional [tiles * 128]: per hop row {sum x^2, sum x, sum (-1)^n x, 0} for the mfcc energy
-  int dbg;                   // SPB_TC_DBG phase knobs (timing experiments only)
 };
 
 // K-major operand without swizzle: core matrix = 8 rows x 16 bytes stored contiguously,
@@ -345,9 +344,9 @@ __global__ void __launch_bounds__(kTcThreads, 1) features_tc_kernel(const TcPara
     uint32_t bad = 0;
     auto row_ptr = [&](long long t, int r) -> const float * {
       if (t >= p.num_tiles) return p.zeros;
-      const TcGroup g = p.groups[((p.dbg & 128) ? (long long)blockIdx.x : t) * 4 + (r >> 5)];
+      const TcGroup g = p.groups[t * 4 + (r >> 5)];
       const int i = r & 31;
-      return (g.nf > 0 && i <= g.nf && !(p.dbg & 64)) ? p.samples + g.gstart + (long long)i * kTcHop + q * 4 : p.zeros;
+      return (g.nf > 0 && i <= g.nf) ? p.samples + g.gstart + (long long)i * kTcHop + q * 4 : p.zeros;
     };
     long long t = blockIdx.x;
     const float *pA = row_ptr(t, rA), *pB = row_ptr(t, rB);
@@ -362,7 +361,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) features_tc_kernel(const TcPara
     for (; t < p.num_tiles; t += gridDim.x, ++it) {
       const float *nA = row_ptr(t + gridDim.x, rA), *nB = row_ptr(t + gridDim.x, rB);
       float a2 = 0.f, a0 = 0.f, aa = 0.f, b2 = 0.f, b0 = 0.f, ba = 0.f;  // hop sums of rows rA, rB (this lane's samples)
-      if (c < 4 && !(p.dbg & 32)) {
+      if (c < 4) {
         // pull the samples of the tile after next into L2 with the TMA engine (one 20 KB run per group)
         const long long tp = t + 2 * (long long)gridDim.x;
         if (tp < p.num_tiles) {
@@ -399,13 +398,11 @@ __global__ void __launch_bounds__(kTcThreads, 1) features_tc_kernel(const TcPara
         mbar_wait_nap(&lo_empty[slot], lo_par);
         unsigned char *sh = base + kTcOffHi + s * kTcAMat;
         unsigned char *sl = base + kTcOffLo + slot * kTcAMat;
-        if (!(p.dbg & 2)) {
-          *reinterpret_cast<uint2 *>(sh + dA) = ha;
-          *reinterpret_cast<uint2 *>(sl + dA) = la;
-          *reinterpret_cast<uint2 *>(sh + dB) = hb;
-          *reinterpret_cast<uint2 *>(sl + dB) = lb;
-        }
-        if (!(p.dbg & 8)) fence_async_smem();
+        *reinterpret_cast<uint2 *>(sh + dA) = ha;
+        *reinterpret_cast<uint2 *>(sl + dA) = la;
+        *reinterpret_cast<uint2 *>(sh + dB) = hb;
+        *reinterpret_cast<uint2 *>(sl + dB) = lb;
+        fence_async_smem();
         __syncwarp();
         if (lane == 0) mbar_arrive(&full[s]);
         if (++slot == kTcLoSlots) { slot = 0; lo_par ^= 1; }
@@ -449,10 +446,8 @@ __global__ void __launch_bounds__(kTcThreads, 1) features_tc_kernel(const TcPara
           const uint64_t da_lo = umma_desc_plain(sbase + kTcOffLo + slot * kTcAMat, kTcRows * 16);
           const uint64_t db_hi = umma_desc_plain(b_hi + s * 2 * kTcBLbo, kTcBLbo);
           const uint64_t db_lo = umma_desc_plain(b_lo + s * 2 * kTcBLbo, kTcBLbo);
-          if (!(p.dbg & 4)) {
-            umma_f16(tmem_d, da_lo, db_hi, kTcIdesc, s ? 1u : 0u);
-            umma_f16(tmem_d, da_hi, db_lo, kTcIdesc, 1u);
-          }
+          umma_f16(tmem_d, da_lo, db_hi, kTcIdesc, s ? 1u : 0u);
+          umma_f16(tmem_d, da_hi, db_lo, kTcIdesc, 1u);
           tc_commit(&lo_empty[slot]);
         }
         // xh k-steps are handed back in two batches (a tcgen05.commit per MMA costs more than it hides)
@@ -460,7 +455,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) features_tc_kernel(const TcPara
         for (int s = 0; s < kTcKSteps; ++s) {
           const uint64_t da_hi = umma_desc_plain(sbase + kTcOffHi + s * kTcAMat, kTcRows * 16);
           const uint64_t db_hi = umma_desc_plain(b_hi + s * 2 * kTcBLbo, kTcBLbo);
-          if (!(p.dbg & 4)) umma_f16(tmem_d, da_hi, db_hi, kTcIdesc, 1u);
+          umma_f16(tmem_d, da_hi, db_hi, kTcIdesc, 1u);
           if (s == kTcKSteps / 2 - 1) tc_commit(&hi_empty[0]);
         }
         tc_commit(&hi_empty[1]);
@@ -479,7 +474,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) features_tc_kernel(const TcPara
       mbar_wait_park(&acc_full[acc], (it >> 1) & 1);
       tc_fence_after();
       const uint32_t taddr = tmem_base + ((uint32_t)(quad * 32) << 16) + acc * kTcN;
-      if (!(p.dbg & 1)) tc_epilogue_tile<KM, FAST>(p, half, taddr, p.out + (g.row0 + lane) * M + col0, lane < g.nf);
+      tc_epilogue_tile<KM, FAST>(p, half, taddr, p.out + (g.row0 + lane) * M + col0, lane < g.nf);
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(&acc_empty[acc]);
@@ -493,11 +488,14 @@ __global__ void __launch_bounds__(kTcThreads, 1) features_tc_kernel(const TcPara
   }
 }
 
+#include "feat_tc2.cuh"
+
 // ------------------------------------------------------------------------------------ host
 struct TcConstOwner {
   std::mutex mu;
   const spb_plan *plan = nullptr;
   uint64_t serial = 0;          // plans are heap objects: an address can come back with other tables
+  int variant = 0;              // 0: the run-time split tables, 1: the static split of the default bank
   cudaEvent_t last_use = nullptr;
 };
 static TcConstOwner g_tc_owner[64];
@@ -556,39 +554,82 @@ int build_tc_plan(spb_context *ctx, spb_plan *pl, const float4 *seg_rd) {
     if (best_cost < 0 || cost < best_cost) { best_cost = cost; best_s1 = s1; }
   }
   pl->tc_vec4 = want4;
-  pl->h_tc_tab.assign(2 * 128 * 4, 0.f);
-  for (int hf = 0; hf < 2; ++hf)
-    for (int i = 0; i < 4; ++i) pl->tc_endmask[hf][i] = 0;
-  int lo_bin[2] = {0, nb}, hi_bin[2] = {nb - 1, nb - 1};  // bins carrying weight per half
-  if (best_s1 > 0) {
-    hi_bin[0] = seg_last[best_s1];
-    lo_bin[1] = seg_first[best_s1];
-    pl->tc_half[0][0] = 0; pl->tc_half[0][1] = seg_last[best_s1] / 16 + 1; pl->tc_half[0][2] = 0; pl->tc_half[0][3] = 0;
-    pl->tc_half[1][0] = seg_first[best_s1] / 16; pl->tc_half[1][1] = nch; pl->tc_half[1][2] = best_s1; pl->tc_half[1][3] = best_s1;
-  } else {
-    pl->tc_half[0][0] = 0; pl->tc_half[0][1] = nch; pl->tc_half[0][2] = 0; pl->tc_half[0][3] = 0;
-    pl->tc_half[1][0] = 0; pl->tc_half[1][1] = 0; pl->tc_half[1][2] = 0; pl->tc_half[1][3] = M;
-  }
-  for (int hf = 0; hf < 2; ++hf)
-    for (int j = 0; j < nb; ++j) {
-      const int r = (int)(((long long)(kmin + j) * q.frame_stride) % q.nfft);
-      const double ang = two_pi * (double)r / (double)q.nfft;
-      // X_f = A_f + (cos - i sin) A_{f+1}
-      float *e = &pl->h_tc_tab[((size_t)hf * 128 + j) * 4];
-      const bool in = (j >= lo_bin[hf] && j <= hi_bin[hf]);
-      e[0] = in ? seg_rd[j].x : 0.f;
-      e[1] = in ? seg_rd[j].y : 0.f;
-      e[2] = (float)cos(ang);
-      e[3] = (float)-sin(ang);
-      if (in && seg_rd[j].z != 0.f) pl->tc_endmask[hf][j >> 5] |= 1u << (j & 31);
+  // tables of one split: per half and bin {rise, fall, cos, sin of the hop rotation}, segment-end masks,
+  // {first chunk, end chunk, first segment, first filter}
+  auto fill_tables = [&](int s1, std::vector<float> &tab, uint32_t (&endmask)[2][4], int (&hf_meta)[2][4],
+                         int (&lo_bin)[2], int (&hi_bin)[2]) {
+    tab.assign(2 * 128 * 4, 0.f);
+    for (int hf = 0; hf < 2; ++hf)
+      for (int i = 0; i < 4; ++i) endmask[hf][i] = 0;
+    lo_bin[0] = 0; lo_bin[1] = nb;
+    hi_bin[0] = nb - 1; hi_bin[1] = nb - 1;
+    if (s1 > 0) {
+      hi_bin[0] = seg_last[s1];
+      lo_bin[1] = seg_first[s1];
+      hf_meta[0][0] = 0; hf_meta[0][1] = seg_last[s1] / 16 + 1; hf_meta[0][2] = 0; hf_meta[0][3] = 0;
+      hf_meta[1][0] = seg_first[s1] / 16; hf_meta[1][1] = nch; hf_meta[1][2] = s1; hf_meta[1][3] = s1;
+    } else {
+      hf_meta[0][0] = 0; hf_meta[0][1] = nch; hf_meta[0][2] = 0; hf_meta[0][3] = 0;
+      hf_meta[1][0] = 0; hf_meta[1][1] = 0; hf_meta[1][2] = 0; hf_meta[1][3] = M;
     }
+    for (int hf = 0; hf < 2; ++hf)
+      for (int j = 0; j < nb; ++j) {
+        const int r = (int)(((long long)(kmin + j) * q.frame_stride) % q.nfft);
+        const double ang = two_pi * (double)r / (double)q.nfft;
+        // X_f = A_f + (cos - i sin) A_{f+1}
+        float *e = &tab[((size_t)hf * 128 + j) * 4];
+        const bool in = (j >= lo_bin[hf] && j <= hi_bin[hf]);
+        e[0] = in ? seg_rd[j].x : 0.f;
+        e[1] = in ? seg_rd[j].y : 0.f;
+        e[2] = (float)cos(ang);
+        e[3] = (float)-sin(ang);
+        if (in && seg_rd[j].z != 0.f) endmask[hf][j >> 5] |= 1u << (j & 31);
+      }
+  };
+  int lo_bin[2], hi_bin[2];
+  fill_tables(best_s1, pl->h_tc_tab, pl->tc_endmask, pl->tc_half, lo_bin, hi_bin);
+  // ---- second-generation kernel (feat_tc2.cuh): folded DFT matrices C = cos, S = -sin of
+  // th_k (m + 1/2) = 2 pi k (2m + 1) / (2 NFFT), m < 80, fp16 hi + lo, [k/8][col][8 halves] each
+  std::vector<__half> w2((size_t)4 * kT2BMat / 2);
+  for (int m = 0; m < kT2K; ++m)
+    for (int col = 0; col < kT2N; ++col) {
+      double c = 0.0, sn = 0.0;
+      if (col < nb) {
+        const long long r = ((long long)(kmin + col) * (2 * m + 1)) % (2LL * q.nfft);
+        const double ang = two_pi * (double)r / (2.0 * (double)q.nfft);
+        c = cos(ang);
+        sn = -sin(ang);
+      }
+      const size_t idx = (size_t)(m >> 3) * (kT2N * 8) + (size_t)col * 8 + (m & 7);
+      const __half ch = __float2half_rn((float)c), sh = __float2half_rn((float)sn);
+      w2[idx] = ch;
+      w2[(size_t)kT2BMat / 2 + idx] = __float2half_rn((float)(c - (double)__half2float(ch)));
+      w2[(size_t)kT2BMat + idx] = sh;
+      w2[(size_t)3 * kT2BMat / 2 + idx] = __float2half_rn((float)(sn - (double)__half2float(sh)));
+    }
+  // the flagged-filter bit set of the epilogue holds 31 filters per half
+  const int n0 = best_s1 > 0 ? best_s1 : M, n1 = best_s1 > 0 ? M - best_s1 : 0;
+  pl->tc2_ok = n0 <= 31 && n1 <= 31;
+  // the speechpy default bank takes the compile-time epilogue: its own split, tables verified here
+  pl->tc2_static = false;
+  {
+    const T2Static &st = kT2StaticHost;
+    if (M == st.M && kmin == st.kmin && nb == st.nb) {
+      int lo_s[2], hi_s[2];
+      fill_tables(st.s1, pl->h_tc_tab_s, pl->tc_endmask_s, pl->tc_half_s, lo_s, hi_s);
+      bool same = lo_s[0] == st.lo[0] && hi_s[0] == st.hi[0] && lo_s[1] == st.lo[1] && hi_s[1] == st.hi[1];
+      for (int hf = 0; hf < 2; ++hf)
+        for (int i = 0; i < 4; ++i) same = same && pl->tc_endmask_s[hf][i] == st.endmask[hf][i];
+      pl->tc2_static = same;
+    }
+  }
   cudaError_t e;
   if ((e = cudaMalloc(&pl->d_tc_whi, kTcBMat)) != cudaSuccess || (e = cudaMalloc(&pl->d_tc_wlo, kTcBMat)) != cudaSuccess ||
-      (e = cudaMalloc(&pl->d_tc_flag, 2048)) != cudaSuccess)
+      (e = cudaMalloc(&pl->d_tc2_w, 4 * kT2BMat)) != cudaSuccess)
     return cuda_fail(ctx, e, "cudaMalloc(tc plan)");
   if ((e = cudaMemcpy(pl->d_tc_whi, hi.data(), kTcBMat, cudaMemcpyHostToDevice)) != cudaSuccess ||
       (e = cudaMemcpy(pl->d_tc_wlo, lo.data(), kTcBMat, cudaMemcpyHostToDevice)) != cudaSuccess ||
-      (e = cudaMemset(pl->d_tc_flag, 0, 2048)) != cudaSuccess)
+      (e = cudaMemcpy(pl->d_tc2_w, w2.data(), 4 * kT2BMat, cudaMemcpyHostToDevice)) != cudaSuccess)
     return cuda_fail(ctx, e, "cudaMemcpy(tc plan)");
   pl->tc_serial = g_tc_serial.fetch_add(1);
   pl->tc_ok = true;
@@ -600,7 +641,7 @@ bool features_tc_supported(const FeatArgs &a) {
          (a.mode == FEAT_LMFE || (a.mode == FEAT_MFE && a.energy == nullptr));
 }
 
-int launch_features_tc(spb_context *ctx, const FeatArgs &a) {
+static int launch_features_tc1(spb_context *ctx, const FeatArgs &a) {
   const spb_plan *pl = a.plan;
   TcParams p;
   p.samples = a.samples;
@@ -624,21 +665,18 @@ int launch_features_tc(spb_context *ctx, const FeatArgs &a) {
   p.flag = pl->d_tc_flag;
   p.zeros = reinterpret_cast<const float *>(pl->d_tc_flag) + 64;
   p.hopsum = a.tc_hopsum;
-  {
-    const char *e = getenv("SPB_TC_DBG");
-    p.dbg = e ? atoi(e) : 0;
-  }
   // c_tc is one table per DEVICE, shared by every context (stream) of the process: a new owner
   // uploads only after the previous owner's last launch (event), under a lock
   TcConstOwner &own = g_tc_owner[ctx->device & 63];
   std::lock_guard<std::mutex> lock(own.mu);
   if (!own.last_use) SPB_CUDA(ctx, cudaEventCreateWithFlags(&own.last_use, cudaEventDisableTiming));
-  if (own.plan != pl || own.serial != pl->tc_serial) {
+  if (own.plan != pl || own.serial != pl->tc_serial || own.variant != 0) {
     if (own.plan) SPB_CUDA(ctx, cudaStreamWaitEvent(ctx->stream, own.last_use, 0));
     // the copy is stream-ordered and reads h_tc_tab (pageable) before returning
     SPB_CUDA(ctx, cudaMemcpyToSymbolAsync(c_tc, pl->h_tc_tab.data(), sizeof(TcConst), 0, cudaMemcpyHostToDevice, ctx->stream));
     own.plan = pl;
     own.serial = pl->tc_serial;
+    own.variant = 0;
   }
   int per_sm = 0;
   const bool km5 = (pl->seg_kmin & 15) == 5;  // the speechpy default bank starts at bin 5
@@ -659,6 +697,79 @@ int launch_features_tc(spb_context *ctx, const FeatArgs &a) {
   SPB_CUDA(ctx, cudaEventRecord(own.last_use, ctx->stream));
   return SPB_OK;
 }
+
+// generation 2 (feat_tc2.cuh)
+static int launch_features_tc2(spb_context *ctx, const FeatArgs &a) {
+  const spb_plan *pl = a.plan;
+  const Options &opt = options();
+  T2Params p;
+  p.samples = a.samples;
+  p.groups = a.tc_groups;
+  p.num_tiles = a.num_tc_groups / 4;
+  p.w = (const __half *)pl->d_tc2_w;
+  p.M = a.M;
+  p.scale = (float)(1.0 / ((double)a.nfft * 268435456.0));       // 2^28: samples are scaled by 2^14
+  p.ln_scale = (float)log(1.0 / ((double)a.nfft * 268435456.0));
+  p.mfe = (a.mode == FEAT_MFE) ? 1 : 0;
+  p.out = a.out;
+  p.flag = pl->d_tc_flag;
+  p.zeros = reinterpret_cast<const float *>(pl->d_tc_flag) + 64;
+  p.hopsum = a.tc_hopsum;
+  p.redo = a.redo_tc;
+  const bool km5 = (pl->seg_kmin & 15) == 5;  // the speechpy default bank starts at bin 5
+  const bool aligned16 = (reinterpret_cast<uintptr_t>(a.out) & 15) == 0;
+  // epilogue flavour: 2 static default bank, 1 runs of four filters, 0 generic
+  const bool legal1 = !p.mfe && km5 && pl->tc_vec4 && aligned16;
+  const bool legal2 = !p.mfe && pl->tc2_static && aligned16;
+  int epi = legal2 ? 2 : (legal1 ? 1 : 0);
+  if (opt.tc_epilogue == 0 || (opt.tc_epilogue == 1 && legal1)) epi = opt.tc_epilogue;  // cross-checks
+  const int variant = (epi == 2) ? 1 : 0;
+  const int (*hm)[4] = variant ? pl->tc_half_s : pl->tc_half;
+  const uint32_t (*em)[4] = variant ? pl->tc_endmask_s : pl->tc_endmask;
+  for (int hf = 0; hf < 2; ++hf) {
+    for (int i = 0; i < 4; ++i) p.half[hf].endmask[i] = em[hf][i];
+    p.half[hf].ch_begin = hm[hf][0];
+    p.half[hf].ch_end = hm[hf][1];
+    p.half[hf].seg0 = hm[hf][2];
+    p.half[hf].out_lo = hm[hf][3];
+  }
+  TcConstOwner &own = g_tc_owner[ctx->device & 63];
+  std::lock_guard<std::mutex> lock(own.mu);
+  if (!own.last_use) SPB_CUDA(ctx, cudaEventCreateWithFlags(&own.last_use, cudaEventDisableTiming));
+  if (own.plan != pl || own.serial != pl->tc_serial || own.variant != variant) {
+    if (own.plan) SPB_CUDA(ctx, cudaStreamWaitEvent(ctx->stream, own.last_use, 0));
+    const std::vector<float> &tab = variant ? pl->h_tc_tab_s : pl->h_tc_tab;
+    SPB_CUDA(ctx, cudaMemcpyToSymbolAsync(c_tc, tab.data(), sizeof(TcConst), 0, cudaMemcpyHostToDevice, ctx->stream));
+    own.plan = pl;
+    own.serial = pl->tc_serial;
+    own.variant = variant;
+  }
+  const bool sums = p.hopsum != nullptr;
+  void (*kern)(const T2Params) = nullptr;
+  if (epi == 2) kern = sums ? features_tc2_kernel<5, 2, true> : features_tc2_kernel<5, 2, false>;
+  else if (epi == 1) kern = sums ? features_tc2_kernel<5, 1, true> : features_tc2_kernel<5, 1, false>;
+  else if (km5) kern = sums ? features_tc2_kernel<5, 0, true> : features_tc2_kernel<5, 0, false>;
+  else kern = sums ? features_tc2_kernel<-1, 0, true> : features_tc2_kernel<-1, 0, false>;
+  int per_sm = 0;
+  int rc = configure_kernel(ctx, (const void *)kern, kTcThreads, kT2Smem, &per_sm);
+  if (rc) return rc;
+  if (per_sm < 1) return fail(ctx, SPB_ERR_INVALID, "features_tc2: kernel does not fit on an SM");
+  long long grid = ctx->sm_count;
+  if (grid > p.num_tiles) grid = p.num_tiles;
+  if (grid < 1) return SPB_OK;
+  kern<<<(unsigned)grid, kTcThreads, kT2Smem, ctx->stream>>>(p);
+  SPB_LAUNCH_CHECK(ctx, "features_tc2");
+  SPB_CUDA(ctx, cudaEventRecord(own.last_use, ctx->stream));
+  return SPB_OK;
+}
+
+int launch_features_tc(spb_context *ctx, const FeatArgs &a) {
+  if (options().tc_version != 1 && a.plan->tc2_ok) return launch_features_tc2(ctx, a);
+  return launch_features_tc1(ctx, a);
+}
+
+// true when launch_features_tc will append to a.redo_tc (generation 2 only)
+bool features_tc_has_guard(const FeatArgs &a) { return options().tc_version != 1 && a.plan && a.plan->tc2_ok; }
 
 // ------------------------------------------------------------------------------------
 // mfcc (+ delta cube) on top of the tensor-core log-mel rows: frame energy, DCT-II, deltas.

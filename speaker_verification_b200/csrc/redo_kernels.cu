@@ -1,0 +1,125 @@
+// Exactness guard of the log-mel kernels (north_star: |log-mel error| <= 1e-4 on EVERY value).
+//
+// The fp32 feature kernels (tensor-core hop DFT, CUDA-core FFTs) carry an absolute error of ~1e-7
+// of the frame's spectral level in X[k]; a filter whose energy happens to be ~1e-5 of the level or
+// less (one or two bins wide, about one value in 1e5 on noise) would show it in the log domain.  Those
+// kernels compare every filter energy with tau x the level of its frame and append the few that
+// fall below to a list; the kernels here recompute exactly those values in float64, straight from
+// the samples, as the reference does (feature.py:199-217,256: |rfft|^2 / NFFT, dot with the bank,
+// zero_handling, log):
+//
+//   redo_list_kernel  one warp per listed (frame, filter): direct DFT of the filter's bins over the
+//                     frame's samples with a float64 twiddle table, float64 mel sum and log
+//   redo_all_kernel   the same for every (frame, filter) of a launch, run only when the list
+//                     overflowed (pathological input: e.g. a pure tone far from most filters)
+#include <math.h>
+
+#include "spb_internal.cuh"
+
+namespace spb {
+
+struct RedoParams {
+  const float *samples;
+  RedoList list;
+  const int *skip_if;        // list kernel: do nothing when *skip_if != 0 (the fallback kernel rewrote the rows)
+  const FftTile *ftiles;     // all kernel: the launch's 32-frame tiles
+  long long num_tiles;
+  int L, S, nfft, M;
+  const int32_t *band_lo, *band_n, *band_off;
+  const float *band_w;
+  const double2 *tw;         // [nfft] (cos, -sin)(2 pi r / nfft)
+  int mfe;                   // 1: energies (no log)
+  float *out;
+};
+
+// one (frame, filter) by a whole warp; every lane returns the value
+__device__ __forceinline__ float redo_value(const RedoParams &p, const float *x, const int m, const int lane) {
+  const int lo = p.band_lo[m], n = p.band_n[m];
+  const float *w = p.band_w + p.band_off[m];
+  const int Leff = min(p.L, p.nfft);  // numpy rfft(n=): rows longer than NFFT are truncated
+  const int mask = p.nfft - 1;
+  double acc = 0.0;
+  for (int t = 0; t < n; ++t) {
+    const double wt = (double)w[t];
+    if (wt == 0.0) continue;  // zero padding of the tap table (warp-uniform)
+    const int k = lo + t;
+    double re = 0.0, im = 0.0;
+    for (int i = lane; i < Leff; i += 32) {
+      const double2 c = p.tw[(int)(((long long)k * i) & mask)];
+      const double v = (double)x[i];
+      re = fma(v, c.x, re);
+      im = fma(v, c.y, im);
+    }
+#pragma unroll
+    for (int o = 16; o >= 1; o >>= 1) {
+      re += __shfl_xor_sync(0xffffffffu, re, o);
+      im += __shfl_xor_sync(0xffffffffu, im, o);
+    }
+    acc = fma(wt, (re * re + im * im) / (double)p.nfft, acc);
+  }
+  if (acc == 0.0) acc = 2.220446049250313e-16;  // functions.zero_handling (functions.py:55-62)
+  return (float)(p.mfe ? acc : log(acc));
+}
+
+__global__ void __launch_bounds__(256) redo_list_kernel(const RedoParams p) {
+  if (p.skip_if != nullptr && *p.skip_if != 0) return;
+  const int total = min(*p.list.count, p.list.cap);
+  const int lane = threadIdx.x & 31;
+  const int wpb = blockDim.x >> 5;
+  for (int e = blockIdx.x * wpb + (threadIdx.x >> 5); e < total; e += gridDim.x * wpb) {
+    const RedoEntry en = p.list.entries[e];
+    const int m = (int)(en.oidx % p.M);
+    const float v = redo_value(p, p.samples + en.soff, m, lane);
+    if (lane == 0) p.out[en.oidx] = v;
+  }
+}
+
+__global__ void __launch_bounds__(256) redo_all_kernel(const RedoParams p) {
+  if (*p.list.overflow == 0) return;
+  const int lane = threadIdx.x & 31;
+  const int wpb = blockDim.x >> 5;
+  const long long units = p.num_tiles * kFftTileFrames * p.M;
+  for (long long u = (long long)blockIdx.x * wpb + (threadIdx.x >> 5); u < units; u += (long long)gridDim.x * wpb) {
+    const long long tf = u / p.M;
+    const int m = (int)(u - tf * p.M);
+    const long long tile = tf / kFftTileFrames;
+    const int f = (int)(tf - tile * kFftTileFrames);
+    const FftTile td = p.ftiles[tile];
+    if (f >= td.nf) continue;
+    const float v = redo_value(p, p.samples + td.gstart + (long long)f * p.S, m, lane);
+    if (lane == 0) p.out[(td.row0 + f) * p.M + m] = v;
+  }
+}
+
+// Runs the guard's second half for one feature launch: the listed values, then (guarded by the
+// overflow flag) everything.  skip_if: device flag that voids the list (tensor-core fallback).
+int launch_redo(spb_context *ctx, const FeatArgs &a, const RedoList &list, const int *skip_if, const FftTables &t) {
+  if (list.entries == nullptr || a.M < 1) return SPB_OK;
+  RedoParams p;
+  p.samples = a.samples;
+  p.list = list;
+  p.skip_if = skip_if;
+  p.ftiles = a.ftiles;
+  p.num_tiles = a.num_tiles;
+  p.L = a.L;
+  p.S = a.S;
+  p.nfft = a.nfft;
+  p.M = a.M;
+  p.band_lo = a.band_lo;
+  p.band_n = a.band_n;
+  p.band_off = a.band_off;
+  p.band_w = a.band_w;
+  p.tw = t.d_tw64;
+  p.mfe = (a.mode == FEAT_MFE) ? 1 : 0;
+  p.out = a.out;
+  const int grid = ctx->sm_count * 4;
+  redo_list_kernel<<<grid, 256, 0, ctx->stream>>>(p);
+  SPB_LAUNCH_CHECK(ctx, "redo_list");
+  if (a.ftiles != nullptr && a.num_tiles > 0) {
+    redo_all_kernel<<<grid, 256, 0, ctx->stream>>>(p);
+    SPB_LAUNCH_CHECK(ctx, "redo_all");
+  }
+  return SPB_OK;
+}
+
+}  // namespace spb

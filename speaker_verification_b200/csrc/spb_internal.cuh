@@ -33,6 +33,8 @@ struct FftTables {
   // fast 512 kernel: twA[l*16+k1] = W256^(l*k1); twB[k1*9+k2] = W512^(k1+16*k2)
   float2 *d_twA = nullptr;
   float2 *d_twB = nullptr;
+  // float64 redo kernels: tw64[r] = (cos, -sin)(2 pi r / nfft), r < nfft
+  double2 *d_tw64 = nullptr;
 };
 
 }  // namespace spb
@@ -49,7 +51,7 @@ struct spb_context {
   uint64_t launches = 0;
   std::string last_error;
   // grow-only device scratch, keyed by role
-  spb::DeviceBuffer scratch[8];
+  spb::DeviceBuffer scratch[12];
   // pinned staging (two halves for double buffering)
   void *pinned[2] = {nullptr, nullptr};
   size_t pinned_bytes = 0;
@@ -94,6 +96,16 @@ struct spb_plan {
   int tc_half[2][4] = {{0, 0, 0, 0}, {0, 0, 0, 0}};  // {first chunk, end chunk, first segment, first filter}
   bool tc_vec4 = false;               // filter ranges of both halves are multiples of four
   uint64_t tc_serial = 0;             // identifies these tables in the per-device constant bank
+  // second-generation tensor-core kernel (feat_tc2.cuh): folded DFT matrices C_hi | C_lo | S_hi | S_lo;
+  // tc2_static: the bank is the speechpy default one and takes the compile-time epilogue with its own
+  // split of the filters (tables *_s)
+  bool tc2_ok = false, tc2_static = false;
+  void *d_tc2_w = nullptr;
+  std::vector<float> h_tc_tab_s;
+  uint32_t tc_endmask_s[2][4] = {{0, 0, 0, 0}, {0, 0, 0, 0}};
+  int tc_half_s[2][4] = {{0, 0, 0, 0}, {0, 0, 0, 0}};
+  // 2 KB per plan: int flags [0] unsplittable sample seen by the tensor-core kernel, [1] / [2] count /
+  // overflow of its redo list, [3] / [4] the same for the CUDA-core FFT kernels; zeros from byte 256 on
   int *d_tc_flag = nullptr;
 };
 
@@ -113,6 +125,31 @@ struct __align__(16) TcGroup {
   int nf;            // frames (0: padding group)
   int pad[3];
 };
+
+// Exactness guard of the log-mel kernels: a filter whose fp32 energy is below tau x the level of
+// its frame is listed here and recomputed in float64 by redo_list_kernel (redo_kernels.cu).
+struct __align__(16) RedoEntry {
+  long long soff;  // first sample of the frame in the arena
+  long long oidx;  // output element index: row * M + filter
+};
+struct RedoList {
+  RedoEntry *entries = nullptr;  // nullptr: guard off
+  int *count = nullptr;          // entries appended so far (may exceed cap)
+  int *overflow = nullptr;       // set when an entry did not fit: the guarded redo_all kernel takes over
+  int cap = 0;
+  float tau = 0.f;               // threshold factor (kernel-specific meaning of the level)
+};
+__device__ __forceinline__ void redo_push(const RedoList &r, long long soff, long long oidx) {
+  const int i = atomicAdd(r.count, 1);
+  if (i < r.cap) {
+    RedoEntry e;
+    e.soff = soff;
+    e.oidx = oidx;
+    r.entries[i] = e;
+  } else {
+    *r.overflow = 1;
+  }
+}
 
 // a run of whole utterances whose intermediates fit in L2
 struct BatchChunk {
@@ -155,6 +192,18 @@ struct spb_batch {
 
 namespace spb {
 
+// process-wide kernel selection / guard knobs behind spb_set_option (declared in the public header)
+struct Options {
+  int feature_kernel = 0;  // 0 auto, 1 generic radix-2 kernel, 2 CUDA-core FFT kernels only (no tensor cores)
+  int cmvnw_kernel = 0;    // 0 auto (single pass), 1 small-tile two-pass, 2 large-tile two-pass
+  int tc_version = 2;      // tensor-core lmfe kernel generation: 2 (folded hop DFT) or 1
+  int tc_epilogue = -1;    // -1 auto, 0 / 1 / 2: force that epilogue flavour of generation 2 where legal
+  int redo = 1;            // float64 recomputation of low-energy filters (the 1e-4 guard)
+  double tau_tc = 2e-5;    // flag when energy < tau x 80 (max_f^2 + max_f+1^2)  (tensor-core kernels)
+  double tau_fft = 1e-4;   // flag when energy < tau x sum x^2 of the frame      (FFT kernels)
+};
+Options &options();
+
 int fail(spb_context *ctx, int code, const std::string &msg);
 // timing helpers: begin returns an index to pass to end (or SIZE_MAX when disabled)
 size_t timing_begin(spb_context *ctx);
@@ -194,6 +243,7 @@ struct FeatArgs {
   const TcGroup *tc_groups = nullptr;  // tensor-core kernel: groups of this launch (4 per tile) or nullptr
   int64_t num_tc_groups = 0;
   float4 *tc_hopsum = nullptr;         // tensor-core kernel: per-hop sums out (mfcc energy), [num_tc_groups * 32]
+  RedoList redo_tc, redo_fft;          // exactness guard lists of the tensor-core / FFT kernels (entries == nullptr: off)
   const spb_plan *plan = nullptr;
   const int *run_if = nullptr;         // fast512: run only when *run_if != 0
   int64_t num_tiles;
@@ -218,6 +268,9 @@ bool fast512_supported(const FeatArgs &a);
 int launch_features_fast512(spb_context *ctx, const FeatArgs &a, const FftTables &t);
 bool features_tc_supported(const FeatArgs &a);
 int launch_features_tc(spb_context *ctx, const FeatArgs &a);
+bool features_tc_has_guard(const FeatArgs &a);
+// float64 recomputation of the values a feature launch listed in `list` (redo_kernels.cu)
+int launch_redo(spb_context *ctx, const FeatArgs &a, const RedoList &list, const int *skip_if, const FftTables &t);
 // mfcc / mfcc+delta rows from log-mel rows (global row addressing) + frame energies from the samples
 int launch_mfcc_post(spb_context *ctx, const FeatArgs &a, const float *d_lmfe);
 int build_tc_plan(spb_context *ctx, spb_plan *pl, const float4 *seg_rd);  // seg_rd: host copy, seg_nbins entries

@@ -96,9 +96,7 @@ def test_batch_errors(sp):
 def test_large_tile_cmvnw_matches_small_tile_kernels(sp):
     """The batch path runs the large-tile cmvnw kernels; bit 1 of the debug hook routes the
     same call through the small-tile kernels (independent tiling, block size, sqrt/div)."""
-    import ctypes
     from speaker_verification_b200 import _lib
-    raw = ctypes.CDLL(_lib.LIB_PATH)
     # multi-tile (> 960 frames), exactly-one-tile, short (< 150 frames: repeated reflection), tiny
     lengths = [320000, 154000, 153920, 100321, 20000, 1000, 480, 800, 235000]
     sigs = _signals(700, lengths)
@@ -106,11 +104,8 @@ def test_large_tile_cmvnw_matches_small_tile_kernels(sp):
     for vn in (True, False):
         fb = batch.FeatureBatch(starts, lens, variance_normalization=vn)
         big = fb.lmfe_cmvnw(arena)
-        raw.spb_debug_force_generic(2)
-        try:
+        with _lib.options(cmvnw_kernel=1):
             small = fb.lmfe_cmvnw(arena)
-        finally:
-            raw.spb_debug_force_generic(0)
         assert np.max(np.abs(big - small)) < 2e-5
         for s, got in zip(sigs, fb.split(big)):
             lm = o.lmfe(s, FS)

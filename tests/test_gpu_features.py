@@ -107,15 +107,11 @@ def test_generic_kernel_matches_fast(sp):
     """Route the same call through the generic radix-2 kernel: two independent FFTs."""
     from speaker_verification_b200 import _lib
     lib = _lib.load()
-    raw = ctypes.CDLL(_lib.LIB_PATH)
     x = synth.audio(12, 20000, np.float32)
     fast = sp.feature.lmfe(x, FS)
-    raw.spb_debug_force_generic(1)
-    try:
+    with _lib.options(feature_kernel=1):
         gen = sp.feature.lmfe(x, FS)
         mf_gen = sp.feature.mfcc(x, FS)
-    finally:
-        raw.spb_debug_force_generic(0)
     assert maxabs(fast, gen) < 2e-5
     assert maxabs(fast, o.lmfe(x, FS)) < TOL
     assert maxabs(mf_gen, o.mfcc(x, FS)) < TOL
@@ -127,18 +123,15 @@ def test_fast1024_kernel_matches_generic_and_oracle(sp, fl, fs_, nf):
     register FFT kernel; the generic radix-2 kernel is an independent second implementation.
     Cases: L = 400 / S = 160 (pruned inputs), L = 512 / S = 200 (unpruned), odd L = 401 and odd
     S = 161 (unaligned frame starts), L = 1024 (no zero padding)."""
-    raw = ctypes.CDLL(_lib_path())
     x = synth.audio(31, 50000, np.float32)
     kw = dict(frame_length=fl, frame_stride=fs_, num_filters=nf, fft_length=1024)
     fast_mfe, fast_en = sp.feature.mfe(x, FS, **kw)
     fast_l = sp.feature.lmfe(x, FS, **kw)
     fast_c = sp.feature.mfcc(x, FS, frame_length=fl, frame_stride=fs_, num_filters=nf, fft_length=1024)
-    raw.spb_debug_force_generic(1)
-    try:
+    from speaker_verification_b200 import _lib
+    with _lib.options(feature_kernel=1):
         gen_mfe, gen_en = sp.feature.mfe(x, FS, **kw)
         gen_l = sp.feature.lmfe(x, FS, **kw)
-    finally:
-        raw.spb_debug_force_generic(0)
     assert fast_l.shape == gen_l.shape and fast_l.shape[0] > 100
     assert maxabs(fast_l, gen_l) < 2e-5
     assert np.max(np.abs(fast_mfe - gen_mfe) / np.maximum(gen_mfe, 1e-30)) < 2e-5

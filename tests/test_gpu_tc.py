@@ -1,7 +1,5 @@
-"""Tensor-core lmfe kernel (csrc/feat_tc_kernels.cu) against the CUDA-core FFT kernel (debug
-bit 2 of spb_debug_force_generic routes the same call through it) and the float64 oracle."""
-import ctypes
-
+"""Tensor-core lmfe kernels (csrc/feat_tc2.cuh, feat_tc_kernels.cu) against the CUDA-core FFT kernel
+(spb_set_option("feature_kernel", 2) routes the same call through it) and the float64 oracle."""
 import numpy as np
 import pytest
 
@@ -13,24 +11,16 @@ FS = 16000
 TOL = 1e-4  # log-mel tolerance of the path (BASELINE.json north_star)
 
 
-def _raw():
-    return ctypes.CDLL(_lib.LIB_PATH)
-
-
-def _lmfe_dev(fb, arena, tc=True):
+def _lmfe_dev(fb, arena, tc=True, **opts):
     import torch
-    raw = _raw()
     d_in = torch.from_numpy(arena).cuda()
     d_out = torch.full((max(fb.total_frames, 1), fb.num_filters), 777.0, dtype=torch.float32, device="cuda")
     torch.cuda.synchronize()
-    raw.spb_debug_force_generic(0 if tc else 4)
-    try:
+    with _lib.options(feature_kernel=0 if tc else 2, **opts):
         n0 = fb.ctx.launch_count()
         fb.lmfe_dev(d_in.data_ptr(), d_in.numel(), d_out.data_ptr())
         fb.ctx.sync()
         launches = fb.ctx.launch_count() - n0
-    finally:
-        raw.spb_debug_force_generic(0)
     return d_out.cpu().numpy()[:fb.total_frames], launches
 
 
@@ -47,7 +37,7 @@ def test_tc_matches_fft_kernel_and_oracle_on_group_boundaries(sp):
     assert fb.total_frames == sum(frames)
     tc, n_tc = _lmfe_dev(fb, arena, True)
     fft, n_fft = _lmfe_dev(fb, arena, False)
-    assert n_tc == n_fft + 1  # tensor-core kernel + the guarded (no-op) FFT launch
+    assert n_tc > n_fft  # tensor-core kernel + the guarded (no-op) FFT launch + its redo pass
     assert not np.any(tc == 777.0)  # every row written
     assert np.max(np.abs(tc - fft)) < 5e-5
     for s, got in zip(sigs, fb.split(tc)):
@@ -59,38 +49,44 @@ def test_tc_matches_fft_kernel_and_oracle_on_group_boundaries(sp):
 
 
 def test_tc_many_tiles_per_cta(sp):
-    """More tiles than SMs: the persistent loop, ring wrap-around and accumulator ping-pong."""
+    """More tiles than SMs: the persistent loop, ring wrap-around and accumulator ping-pong -- and the
+    north_star tolerance on EVERY value: all 4.3 M log-mel values of 128 cfg3-shaped utterances within
+    1e-4 of the float64 oracle (feature.py:216-217,256), no energy mask.  The fp32 kernels alone cannot
+    do that for the rare filter ~1e-5 below its frame's level; the float64 redo of the flagged filters
+    (csrc/redo_kernels.cu) is what closes it, for the tensor-core path and the FFT path alike."""
     lengths = synth.cfg3_lengths(128, seed=21)
     arena, starts, lens = synth.ragged_corpus(lengths, seed=22)
     fb = batch.FeatureBatch(starts, lens)
     assert fb.total_frames > 3 * 148 * 124
+    ref = np.concatenate([o.lmfe(arena[starts[u]:starts[u] + lens[u]], FS) for u in range(len(starts))])
+    assert ref.shape == (fb.total_frames, 40)
     tc, _ = _lmfe_dev(fb, arena, True)
     fft, _ = _lmfe_dev(fb, arena, False)
     assert np.all(np.isfinite(tc))
-    # Both kernels carry an ABSOLUTE error of ~1e-7 of the frame's spectral level in X, so a filter
-    # whose energy happens to be ~1e-6 of the typical one (one or two bins wide, about one value
-    # in a million on noise) shows 1e-4 .. 3e-4 in the log domain -- the CUDA-core FFT kernel
-    # just as the tensor-core one (measured on this batch: 5 resp. 3 of 4.3 M values above 5e-5).
-    # The log-domain tolerance is therefore asserted where the energy is within e^-8 of the
-    # frame's median, the tail is bounded separately.
-    ok = fft > (np.median(fft, axis=1, keepdims=True) - 8.0)
-    d = np.abs(tc - fft)
-    assert ok.mean() > 0.999
-    assert np.max(d[ok]) < 5e-5
-    assert np.max(d) < 1e-3 and np.quantile(d, 0.9999) < 2e-5
-    for u in (0, 40, 127):
-        s = arena[starts[u]:starts[u] + lens[u]]
-        got = tc[fb.frame_offsets[u]:fb.frame_offsets[u + 1]]
-        ref = o.lmfe(s, FS)
-        oku = ref > (np.median(ref, axis=1, keepdims=True) - 8.0)
-        assert np.max(np.abs(got - ref)[oku]) < TOL
-        assert np.max(np.abs(got - ref)) < 1e-3
-    # the whole pipeline on top of it
+    e_tc, e_fft = np.abs(tc - ref), np.abs(fft - ref)
+    assert e_tc.max() < TOL, (e_tc.max(), np.unravel_index(e_tc.argmax(), e_tc.shape))
+    assert e_fft.max() < TOL, (e_fft.max(), np.unravel_index(e_fft.argmax(), e_fft.shape))
+    assert np.quantile(e_tc, 0.9999) < 2e-5
+    # the guard is what does it: the same kernels without the redo pass show the tail (documented in DESIGN.md)
+    raw_tc, _ = _lmfe_dev(fb, arena, True, redo=0)
+    changed = raw_tc != tc
+    assert 0 < changed.sum() < 2e-3 * tc.size       # a few values per 10^4 are recomputed
+    assert np.max(np.abs(tc[changed] - ref[changed])) < 2e-6  # ... exactly (float32 rounding of the float64 value)
+    # every epilogue flavour of the kernel and the previous generation agree
+    for opts in (dict(tc_epilogue=0), dict(tc_epilogue=1), dict(tc_version=1)):
+        alt, _ = _lmfe_dev(fb, arena, True, **opts)
+        e_alt = np.abs(alt - ref)
+        if "tc_version" in opts:
+            assert np.quantile(e_alt, 0.9999) < 2e-5 and e_alt.max() < 1e-3, opts  # generation 1 has no guard
+        else:
+            assert e_alt.max() < TOL, opts
+            assert np.max(np.abs(alt - tc)) < 2e-6, opts
+    # the whole pipeline on top of it: every value of cmvnw(lmfe) for a sample of utterances
     full = fb.lmfe_cmvnw(arena)
-    u = 17
-    s = arena[starts[u]:starts[u] + lens[u]]
-    ref = o.cmvnw_vectorised(o.lmfe(s, FS), 301, True)
-    assert np.max(np.abs(full[fb.frame_offsets[u]:fb.frame_offsets[u + 1]] - ref)) < TOL
+    for u in (3, 17, 64, 127):
+        s = arena[starts[u]:starts[u] + lens[u]]
+        want = o.cmvnw_vectorised(o.lmfe(s, FS), 301, True)
+        assert np.max(np.abs(full[fb.frame_offsets[u]:fb.frame_offsets[u + 1]] - want)) < TOL, u
     fb.close()
 
 
@@ -180,16 +176,12 @@ def test_tc_plans_alternate(sp):
 
 def _mfcc_delta_dev(fb, arena, tc=True):
     import torch
-    raw = _raw()
     d_in = torch.from_numpy(arena).cuda()
     d_out = torch.full((max(fb.total_frames, 1), fb.num_cepstral, 3), 777.0, dtype=torch.float32, device="cuda")
     torch.cuda.synchronize()
-    raw.spb_debug_force_generic(0 if tc else 4)
-    try:
+    with _lib.options(feature_kernel=0 if tc else 2):
         fb.mfcc_delta_dev(d_in.data_ptr(), d_in.numel(), d_out.data_ptr())
         fb.ctx.sync()
-    finally:
-        raw.spb_debug_force_generic(0)
     return d_out.cpu().numpy()[:fb.total_frames]
 
 

@@ -27,6 +27,25 @@ def test_library_exports_every_declared_symbol(lib_built):
     from speaker_verification_b200 import _lib
     assert sorted(_lib.PROTOTYPES) == names  # the ctypes table mirrors the header one to one
     assert lib.spb_version() == 100
+    # ... and nothing undeclared is exported: no test hooks or debug switches outside the header
+    import subprocess
+    out = subprocess.run(["nm", "-D", "--defined-only", lib_built], capture_output=True, text=True, check=True).stdout
+    exported = sorted(line.split()[-1] for line in out.splitlines() if line.split()[-1].startswith("spb_"))
+    assert exported == names
+    blob = open(lib_built, "rb").read()
+    assert b"SPB_TC_DBG" not in blob and b"spb_debug" not in blob
+
+
+def test_options_api(lib_built):
+    """spb_set_option / spb_get_option (declared kernel-selection knobs): round trip, range checks."""
+    from speaker_verification_b200 import _lib
+    assert _lib.get_option("feature_kernel") == 0 and _lib.get_option("redo") == 1
+    with _lib.options(feature_kernel=2, tau_tc=1e-6):
+        assert _lib.get_option("feature_kernel") == 2 and _lib.get_option("tau_tc") == 1e-6
+    assert _lib.get_option("feature_kernel") == 0
+    for bad in (("feature_kernel", 7), ("tc_version", 3), ("no_such_option", 1), ("tau_fft", -1.0)):
+        with pytest.raises(AssertionError):
+            _lib.set_option(*bad)
 
 
 def test_host_integer_math_matches_reference_table(lib_built):

@@ -9,7 +9,6 @@ sys.path.insert(0, ".")
 from oracle import speechpy_oracle as o  # noqa: E402
 from speaker_verification_b200 import _lib, batch, synth  # noqa: E402
 
-raw = ctypes.CDLL(_lib.LIB_PATH)
 lengths = synth.cfg3_lengths(128, seed=21)
 arena, starts, lens = synth.ragged_corpus(lengths, seed=22)
 fb = batch.FeatureBatch(starts, lens)
@@ -18,10 +17,9 @@ d_in = torch.from_numpy(arena).cuda()
 
 def run(tc):
     out = torch.empty((fb.total_frames, 40), dtype=torch.float32, device="cuda")
-    raw.spb_debug_force_generic(0 if tc else 4)
-    fb.lmfe_dev(d_in.data_ptr(), d_in.numel(), out.data_ptr())
-    fb.ctx.sync()
-    raw.spb_debug_force_generic(0)
+    with _lib.options(feature_kernel=0 if tc else 2):
+        fb.lmfe_dev(d_in.data_ptr(), d_in.numel(), out.data_ptr())
+        fb.ctx.sync()
     return out.cpu().numpy()
 
 

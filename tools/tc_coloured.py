@@ -24,10 +24,9 @@ for floor_db in (-20, -40, -60, -80):
     res = {}
     for name, bit in (("tc", 0), ("fft", 4)):
         out = torch.empty((fb.total_frames, 40), dtype=torch.float32, device="cuda")
-        raw.spb_debug_force_generic(bit)
-        fb.lmfe_dev(d_in.data_ptr(), d_in.numel(), out.data_ptr())
-        fb.ctx.sync()
-        raw.spb_debug_force_generic(0)
+        with _lib.options(feature_kernel=2 if bit else 0):
+            fb.lmfe_dev(d_in.data_ptr(), d_in.numel(), out.data_ptr())
+            fb.ctx.sync()
         res[name] = out.cpu().numpy()
     ref = o.lmfe(x, 16000)
     et, ef = np.abs(res["tc"] - ref), np.abs(res["fft"] - ref)
