@@ -3,7 +3,7 @@
 O=gpurun_out/r02a; mkdir -p $O
 nvidia-smi --query-gpu=name,clocks.sm,clocks.max.sm,power.draw --format=csv > $O/smi.txt 2>&1
 timeout -s KILL 300 python -c "
-import numpy as np, sys
+import numpy as np, sys, torch
 sys.path.insert(0,'.')
 from speaker_verification_b200 import _lib, batch, synth
 from oracle import speechpy_oracle as o
@@ -12,8 +12,10 @@ arena, starts, lens = batch.pack([x, synth.audio(2, 100000, np.float32)])
 fb = batch.FeatureBatch(starts, lens)
 ref = np.concatenate([o.lmfe(arena[s:s+n], 16000) for s, n in zip(starts, lens)])
 for opts in (dict(tc_version=1), dict(feature_kernel=2), dict(tc_epilogue=0), dict(tc_epilogue=1), dict(), dict(redo=0)):
+    d_in = torch.from_numpy(arena).cuda(); d_out = torch.zeros((fb.total_frames, 40), device='cuda')
     with _lib.options(**opts):
-        got = fb.lmfe(arena)
+        fb.lmfe_dev(d_in.data_ptr(), d_in.numel(), d_out.data_ptr()); fb.ctx.sync()
+    got = d_out.cpu().numpy()
     print(opts, 'max err', float(np.abs(got-ref).max()), flush=True)
 " > $O/first.log 2>&1
 echo "first rc=$?" >> $O/first.log
