@@ -253,6 +253,23 @@ SPB_API int spb_cosine_scores(spb_context *ctx, const float *E, int64_t m, const
                       int64_t n, int32_t d, float *S);
 SPB_API int spb_cosine_scores_dev(spb_context *ctx, const float *d_E, int64_t m, const float *d_T,
                           int64_t n, int32_t d, float *d_S);
+/* Allocation-free variant of spb_cosine_scores_dev.  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph
+ * capture, tight serving loops, harnesses that forbid it).  Same arguments and results as
+ * spb_cosine_scores_dev, but the normalised TF32 hi/lo split of E and T lives in a static
+ * __device__ array of SPB_NOALLOC_SCRATCH_BYTES (8 MiB) inside the library instead of the
+ * context's grow-only scratch, and the call performs no cudaMalloc / cudaFree / allocating library
+ * routine (the kernel-timing events of spb_timing_enable are not recorded for it).  Limit:
+ * 2 * (pad256(m * dp) + pad256(n * dp)) * 4 bytes <= SPB_NOALLOC_SCRATCH_BYTES with dp = d rounded
+ * up to a multiple of 32 and pad256 rounding up to 256 floats (e.g. m + n <= 2 048 rows at d = 512);
+ * larger problems return SPB_ERR_INVALID with a message naming both sizes.  Every call on a device
+ * shares the one array (each call rewrites all of it that it reads, so nothing has to be cleared):
+ * calls that overlap on the GPU -- different contexts / streams of the same device -- race; calls
+ * on one context are stream-ordered and safe.  The first call on a device resolves the array's
+ * device address (cudaGetSymbolAddress); make it outside a graph capture. */
+#define SPB_NOALLOC_SCRATCH_BYTES (8u << 20)
+SPB_API int spb_cosine_scores_dev_noalloc(spb_context *ctx, const float *d_E, int64_t m, const float *d_T,
+                                  int64_t n, int32_t d, float *d_S);
 /* out[t] = S[trial_i[t], trial_j[t]] gathered from a device score matrix. */
 SPB_API int spb_trial_scores_dev(spb_context *ctx, const float *d_S, int64_t m, int64_t n,
                          const int32_t *d_trial_i, const int32_t *d_trial_j,

@@ -72,6 +72,7 @@ PROTOTYPES = {
                                           c_i32, c_vp]),
     "spb_cosine_scores": (C.c_int, [c_vp, c_vp, c_i64, c_vp, c_i64, c_i32, c_vp]),
     "spb_cosine_scores_dev": (C.c_int, [c_vp, c_vp, c_i64, c_vp, c_i64, c_i32, c_vp]),
+    "spb_cosine_scores_dev_noalloc": (C.c_int, [c_vp, c_vp, c_i64, c_vp, c_i64, c_i32, c_vp]),
     "spb_trial_scores_dev": (C.c_int, [c_vp, c_vp, c_i64, c_i64, c_vp, c_vp, c_i64, c_vp]),
     "spb_argmax_rows_dev": (C.c_int, [c_vp, c_vp, c_i64, c_i64, c_vp]),
     "spb_eer": (C.c_int, [c_vp, c_vp, c_vp, c_i64, C.POINTER(C.c_double), C.POINTER(C.c_double)]),

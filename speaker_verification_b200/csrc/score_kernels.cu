@@ -25,6 +25,9 @@
 #include <cuda.h>
 #include <math.h>
 
+#include <mutex>
+#include <string>
+
 #include <cub/cub.cuh>
 
 #include "ptx_helpers.cuh"
@@ -315,15 +318,20 @@ static int make_operand_map(spb_context *ctx, CUtensorMap *map, const float *ptr
   return SPB_OK;
 }
 
-int launch_cosine_scores(spb_context *ctx, const float *d_E, int64_t m, const float *d_T, int64_t n, int d,
-                         float *d_S) {
-  if (m == 0 || n == 0) return SPB_OK;
+// floats of hi/lo scratch a (m, d) x (n, d) problem needs: [E_hi | E_lo | T_hi | T_lo], each block 1 KB aligned
+static inline size_t split_align(size_t x) { return (x + 255) & ~(size_t)255; }
+static size_t cosine_scratch_floats(int64_t m, int64_t n, int d) {
+  const int dp = (d + kBK - 1) / kBK * kBK;
+  return 2 * split_align((size_t)m * dp) + 2 * split_align((size_t)n * dp);
+}
+
+// prologue + GEMM with the hi/lo split in `buf` (cosine_scratch_floats(m, n, d) floats).  timed: the
+// GEMM launch is bracketed by the context's timing events when timing is on (those are created on demand).
+static int cosine_scores_in(spb_context *ctx, const float *d_E, int64_t m, const float *d_T, int64_t n, int d,
+                            float *d_S, float *buf, bool timed) {
   const int dp = (d + kBK - 1) / kBK * kBK;
   const size_t e_elems = (size_t)m * dp, t_elems = (size_t)n * dp;
-  // slot 6: [E_hi | E_lo | T_hi | T_lo], each block 1 KB aligned
-  auto al = [](size_t x) { return (x + 255) & ~(size_t)255; };
-  float *buf = (float *)scratch(ctx, 6, (2 * al(e_elems) + 2 * al(t_elems)) * 4);
-  if (!buf) return SPB_ERR_CUDA;
+  auto al = split_align;
   float *e_hi = buf, *e_lo = e_hi + al(e_elems), *t_hi = e_lo + al(e_elems), *t_lo = t_hi + al(t_elems);
   const int rows_per_block = 256 / 32;
   normalize_split_kernel<<<(unsigned)((m + rows_per_block - 1) / rows_per_block), 256, 0, ctx->stream>>>(
@@ -352,10 +360,50 @@ int launch_cosine_scores(spb_context *ctx, const float *d_E, int64_t m, const fl
     attr_set = true;
   }
   long long grid = std::min<long long>((long long)p.tiles_m * p.tiles_n, ctx->sm_count);
-  const size_t tb = timing_begin(ctx);
+  const size_t tb = timed ? timing_begin(ctx) : (size_t)-1;
   cosine_gemm_kernel<<<(unsigned)grid, kGemmThreads, kGemmSmem, ctx->stream>>>(m_ehi, m_elo, m_thi, m_tlo, p);
-  timing_end(ctx, 3, tb);
+  if (timed) timing_end(ctx, 3, tb);
   SPB_LAUNCH_CHECK(ctx, "cosine_gemm_kernel");
+  return SPB_OK;
+}
+
+int launch_cosine_scores(spb_context *ctx, const float *d_E, int64_t m, const float *d_T, int64_t n, int d,
+                         float *d_S) {
+  if (m == 0 || n == 0) return SPB_OK;
+  // slot 6 of the context's grow-only scratch
+  float *buf = (float *)scratch(ctx, 6, cosine_scratch_floats(m, n, d) * 4);
+  if (!buf) return SPB_ERR_CUDA;
+  return cosine_scores_in(ctx, d_E, m, d_T, n, d, d_S, buf, true);
+}
+
+// ------------------------------------------------------------------------------------
+// Allocation-free variant (spb_cosine_scores_dev_noalloc).  No counterpart in the reference: added
+// for callers that cannot call cudaMalloc (CUDA graph capture,
+// tight serving loops, harnesses that forbid it).  The hi/lo split lives in a file-scope __device__
+// array of kNoAllocFloats floats (8 MiB) that every GPU which loads the library holds until exit.
+// In host code `g_noalloc_split` is only a stand-in for the symbol: the device address is resolved
+// once per device with cudaGetSymbolAddress (that device current) and cached.
+// ------------------------------------------------------------------------------------
+constexpr size_t kNoAllocFloats = (size_t)2 << 20;  // 2 Mi floats = 8 MiB
+static_assert(kNoAllocFloats * sizeof(float) == SPB_NOALLOC_SCRATCH_BYTES, "header and library disagree on the limit");
+static __device__ __align__(256) float g_noalloc_split[kNoAllocFloats];
+
+static std::mutex g_noalloc_mu;
+static float *g_noalloc_ptr[64] = {};
+
+static int noalloc_scratch(spb_context *ctx, float **out) {
+  if (ctx->device < 0 || ctx->device >= 64) return fail(ctx, SPB_ERR_INVALID, "noalloc: device index out of range");
+  std::lock_guard<std::mutex> lock(g_noalloc_mu);
+  float *ptr = g_noalloc_ptr[ctx->device];
+  if (ptr == nullptr) {
+    // set-up, once per device, with that device current (the caller made it so)
+    void *sym = nullptr;
+    const cudaError_t e = cudaGetSymbolAddress(&sym, g_noalloc_split);
+    if (e != cudaSuccess) return cuda_fail(ctx, e, "cudaGetSymbolAddress(g_noalloc_split)");
+    if (sym == nullptr) return fail(ctx, SPB_ERR_CUDA, "noalloc: the static scratch has no device address");
+    ptr = g_noalloc_ptr[ctx->device] = static_cast<float *>(sym);
+  }
+  *out = ptr;
   return SPB_OK;
 }
 
@@ -685,6 +733,25 @@ int spb_cosine_scores_dev(spb_context *ctx, const float *E, int64_t m, const flo
   if (rc) return rc;
   SPB_CUDA(ctx, cudaSetDevice(ctx->device));
   return launch_cosine_scores(ctx, E, m, T, n, d, S);
+}
+
+int spb_cosine_scores_dev_noalloc(spb_context *ctx, const float *E, int64_t m, const float *T, int64_t n, int32_t d,
+                                  float *S) {
+  int rc = check_scores_args(ctx, E, m, T, n, d, S);
+  if (rc) return rc;
+  if (m == 0 || n == 0) return SPB_OK;
+  const size_t need = cosine_scratch_floats(m, n, d);
+  if (need > kNoAllocFloats)
+    return fail(ctx, SPB_ERR_INVALID,
+                "spb_cosine_scores_dev_noalloc: (m + n) x d needs " + std::to_string(need * 4) +
+                    " bytes of split scratch, the static scratch holds " + std::to_string(kNoAllocFloats * 4) +
+                    " (use spb_cosine_scores_dev)");
+  SPB_CUDA(ctx, cudaSetDevice(ctx->device));
+  float *buf = nullptr;
+  if ((rc = noalloc_scratch(ctx, &buf))) return rc;
+  // every element of the split that the GEMM reads is rewritten by the prologue of this call (zero
+  // padding of the columns included; rows past m / n are zero-filled by TMA): nothing to clear
+  return cosine_scores_in(ctx, E, m, T, n, d, S, buf, false);
 }
 
 int spb_cosine_scores(spb_context *ctx, const float *E, int64_t m, const float *T, int64_t n, int32_t d,
