@@ -288,7 +288,7 @@ int spb_timing_enable(spb_context *ctx, int32_t on) {
 
 int spb_timing_read(spb_context *ctx, int32_t kernel, double *total_ms, uint64_t *launches) {
   SPB_REQUIRE(ctx, ctx && total_ms && launches, "spb_timing_read: NULL argument");
-  SPB_REQUIRE(ctx, kernel >= 0 && kernel < 4, "spb_timing_read: kernel must be 0..3");
+  SPB_REQUIRE(ctx, kernel >= 0 && kernel < 6, "spb_timing_read: kernel must be 0..5");
   SPB_CUDA(ctx, cudaSetDevice(ctx->device));
   SPB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
   double tot = 0.0;
@@ -642,15 +642,28 @@ int spb_batch_create(spb_context *ctx, const spb_plan *plan, const int64_t *star
   std::vector<int4> big;
   b->big_rmax = (win > 0) ? cmvnw_big_rmax(plan->p.num_filters, win) : 0;
   const int tile_target = (int)std::min<int64_t>(b->big_rmax, std::max<int64_t>(30, env_int("SPB_BIG_RMAX", b->big_rmax) / 30 * 30));
-  if (b->big_rmax > 0) {
-    for (BatchChunk &c : ch.chunks) {
-      c.big0 = (int64_t)big.size();
-      for (int64_t u = c.u0; u < c.u1; ++u) append_big_tiles(big, (int)u, nframes[u], tile_target);
-      c.big1 = (int64_t)big.size();
-      std::stable_sort(big.begin() + c.big0, big.begin() + c.big1,
-                       [](const int4 &x, const int4 &y) { return x.z > y.z; });
-    }
-  }
+  // single-pass stream table (+ large tiles for the utterances too short for it), per chunk / group
+  std::vector<int4> streams;
+  const bool stream_ok = b->big_rmax > 0 && cmvnw_stream_supported(plan->p.num_filters, win, plan->p.cmvn_variance);
+  auto add_cmvnw_tables = [&](BatchChunk &c) {
+    if (b->big_rmax <= 0) return;
+    c.big0 = (int64_t)big.size();
+    for (int64_t u = c.u0; u < c.u1; ++u) append_big_tiles(big, (int)u, nframes[u], tile_target);
+    c.big1 = (int64_t)big.size();
+    std::stable_sort(big.begin() + c.big0, big.begin() + c.big1, [](const int4 &x, const int4 &y) { return x.z > y.z; });
+    if (!stream_ok) return;
+    c.st0 = (int64_t)streams.size();
+    for (int64_t u = c.u0; u < c.u1; ++u) append_streams(streams, (int)u, nframes[u]);
+    c.st1 = (int64_t)streams.size();
+    std::stable_sort(streams.begin() + c.st0, streams.begin() + c.st1,
+                     [](const int4 &x, const int4 &y) { return x.z - x.y > y.z - y.y; });
+    c.rt0 = (int64_t)big.size();
+    for (int64_t u = c.u0; u < c.u1; ++u)
+      if (nframes[u] < cmvnw_stream_min_rows()) append_big_tiles(big, (int)u, nframes[u], tile_target);
+    c.rt1 = (int64_t)big.size();
+    if (c.rt1 > c.rt0) b->has_short_utts = true;
+  };
+  for (BatchChunk &c : ch.chunks) add_cmvnw_tables(c);
   // tensor-core feature kernel: groups of 32 hops (31 frames), 4 per tile, each chunk padded to
   // whole tiles; needs 16-byte aligned utterance starts
   std::vector<TcGroup> tcg;
@@ -700,12 +713,7 @@ int spb_batch_create(spb_context *ctx, const spb_plan *plan, const int64_t *star
     if (open) b->groups.push_back(g);
     for (BatchChunk &c : b->groups) {
       b->max_group_rows = std::max(b->max_group_rows, c.row1 - c.row0);
-      if (b->big_rmax <= 0) continue;
-      c.big0 = (int64_t)big.size();  // group tables follow the chunk tables in d_big_tiles
-      for (int64_t u = c.u0; u < c.u1; ++u) append_big_tiles(big, (int)u, nframes[u], tile_target);
-      c.big1 = (int64_t)big.size();
-      std::stable_sort(big.begin() + c.big0, big.begin() + c.big1,
-                       [](const int4 &x, const int4 &y) { return x.z > y.z; });
+      add_cmvnw_tables(c);  // group tables follow the chunk tables in d_big_tiles / d_streams
     }
   }
   auto cleanup = [&](cudaError_t e, const char *what) {
@@ -722,6 +730,7 @@ int spb_batch_create(spb_context *ctx, const spb_plan *plan, const int64_t *star
       (e = cudaMalloc(&b->d_ftiles, (size_t)std::max<int64_t>(b->total_tiles, 1) * sizeof(FftTile))) != cudaSuccess ||
       (e = cudaMalloc(&b->d_cm_tiles, (size_t)std::max<int64_t>(b->total_cm_tiles, 1) * sizeof(int2))) != cudaSuccess ||
       (e = cudaMalloc(&b->d_big_tiles, std::max<size_t>(big.size(), 1) * sizeof(int4))) != cudaSuccess ||
+      (stream_ok && (e = cudaMalloc(&b->d_streams, std::max<size_t>(streams.size(), 1) * sizeof(int4))) != cudaSuccess) ||
       (!tcg.empty() && (e = cudaMalloc(&b->d_tc_groups, tcg.size() * sizeof(TcGroup))) != cudaSuccess) ||
       (e = cudaMalloc(&d_tile_off, (u_bytes + 1) * 8)) != cudaSuccess ||
       (e = cudaMalloc(&d_cm_off, (u_bytes + 1) * 8)) != cudaSuccess)
@@ -739,6 +748,9 @@ int spb_batch_create(spb_context *ctx, const spb_plan *plan, const int64_t *star
     if (!big.empty() &&
         (e = cudaMemcpyAsync(b->d_big_tiles, big.data(), big.size() * sizeof(int4), cudaMemcpyHostToDevice, ctx->stream)) != cudaSuccess)
       return cleanup(e, "cudaMemcpyAsync(big tiles)");
+    if (b->d_streams && !streams.empty() &&
+        (e = cudaMemcpyAsync(b->d_streams, streams.data(), streams.size() * sizeof(int4), cudaMemcpyHostToDevice, ctx->stream)) != cudaSuccess)
+      return cleanup(e, "cudaMemcpyAsync(streams)");
     int rc = launch_build_tiles(ctx, b->d_nframes, d_tile_off, U, kFftTile, b->d_tiles);
     if (!rc)
       rc = launch_build_fft_tiles(ctx, b->d_nframes, d_tile_off, b->d_starts, b->d_frame_offsets, U, kFftTile, S,
@@ -770,6 +782,7 @@ int spb_batch_destroy(spb_batch *b) {
   cudaFree(b->d_tc_groups);
   cudaFree(b->d_cm_tiles);
   cudaFree(b->d_big_tiles);
+  cudaFree(b->d_streams);
   delete b;
   return SPB_OK;
 }
@@ -898,9 +911,13 @@ static int check_batch(spb_context *ctx, const spb_batch *b, int64_t arena_len, 
   return SPB_OK;
 }
 
+static bool cmvnw_single_pass(const spb_batch *b, const float *d_out) {
+  return b->d_streams != nullptr && options().cmvnw_kernel == 3 && (((size_t)d_out) & 15) == 0;
+}
+
 // lmfe -> cmvnw of one run of whole utterances (a chunk of the host-pointer pipeline or a launch
-// group of the device-pointer path); the lmfe and mean-subtracted intermediates of the run live
-// in two scratch buffers sized for the largest run.
+// group of the device-pointer path); the lmfe intermediate of the run (and, for the two-pass cmvnw
+// kernels, the mean-subtracted one) lives in a scratch buffer sized for the largest run.
 static int lmfe_cmvnw_chunk(spb_context *ctx, const spb_batch *b, const BatchChunk &c,
                             const float *d_samples, int64_t arena_len, float *d_lmfe, float *d_ms,
                             float *d_out) {
@@ -921,6 +938,15 @@ static int lmfe_cmvnw_chunk(spb_context *ctx, const spb_batch *b, const BatchChu
   int rc = run_features(ctx, a);
   if (rc) return rc;
   float *ms_biased = d_ms ? d_ms - (ptrdiff_t)c.row0 * M : nullptr;
+  if (cmvnw_single_pass(b, d_out)) {
+    // one streaming pass (cmvn_stream_kernels.cu, opt-in: measured slower than the two passes);
+    // the rare utterance of < 150 rows takes the large-tile kernels
+    rc = launch_cmvnw_stream(ctx, lmfe_biased, d_out, b->d_nframes, b->d_frame_offsets, b->d_streams + c.st0,
+                             c.st1 - c.st0);
+    if (rc || c.rt1 == c.rt0) return rc;
+    return launch_cmvnw_big(ctx, lmfe_biased, ms_biased, d_out, b->d_nframes, b->d_frame_offsets,
+                            b->d_big_tiles + c.rt0, c.rt1 - c.rt0, b->big_rmax, M, M, win, pl->p.cmvn_variance);
+  }
   if (b->big_rmax > 0 && options().cmvnw_kernel != 1 && (((size_t)d_out) & 15) == 0)
     return launch_cmvnw_big(ctx, lmfe_biased, ms_biased, d_out, b->d_nframes, b->d_frame_offsets,
                             b->d_big_tiles + c.big0, c.big1 - c.big0, b->big_rmax, M, M, win,
@@ -930,7 +956,8 @@ static int lmfe_cmvnw_chunk(spb_context *ctx, const spb_batch *b, const BatchChu
                           pl->p.cmvn_variance);
 }
 
-static int lmfe_cmvnw_prepare(spb_context *ctx, const spb_batch *b, int64_t max_rows, float **d_lmfe, float **d_ms) {
+static int lmfe_cmvnw_prepare(spb_context *ctx, const spb_batch *b, int64_t max_rows, const float *d_out, float **d_lmfe,
+                              float **d_ms) {
   const spb_plan *pl = b->plan;
   const int M = pl->p.num_filters, win = pl->p.cmvn_window;
   SPB_REQUIRE(ctx, win > 0 && (win & 1), "lmfe_cmvnw: plan has no (odd) cmvn_window");
@@ -938,15 +965,17 @@ static int lmfe_cmvnw_prepare(spb_context *ctx, const spb_batch *b, int64_t max_
   if (!cmvnw_supported(M, win)) return fail(ctx, SPB_ERR_UNSUPPORTED, "cmvnw: window x columns too large for shared memory");
   const size_t chunk_bytes = (size_t)std::max<int64_t>(max_rows, 1) * M * 4;
   *d_lmfe = (float *)scratch(ctx, 2, chunk_bytes);
-  *d_ms = pl->p.cmvn_variance ? (float *)scratch(ctx, 3, chunk_bytes) : nullptr;
-  if (!*d_lmfe || (pl->p.cmvn_variance && !*d_ms)) return SPB_ERR_CUDA;
+  // the mean-subtracted intermediate exists only for the two-pass kernels
+  const bool need_ms = pl->p.cmvn_variance && (!cmvnw_single_pass(b, d_out) || b->has_short_utts);
+  *d_ms = need_ms ? (float *)scratch(ctx, 3, chunk_bytes) : nullptr;
+  if (!*d_lmfe || (need_ms && !*d_ms)) return SPB_ERR_CUDA;
   return SPB_OK;
 }
 
 static int run_lmfe_cmvnw(spb_context *ctx, const spb_batch *b, const float *d_samples,
                           int64_t arena_len, float *d_out) {
   float *d_lmfe, *d_ms;
-  int rc = lmfe_cmvnw_prepare(ctx, b, b->max_group_rows, &d_lmfe, &d_ms);
+  int rc = lmfe_cmvnw_prepare(ctx, b, b->max_group_rows, d_out, &d_lmfe, &d_ms);
   if (rc) return rc;
   for (const BatchChunk &c : b->groups) {
     rc = lmfe_cmvnw_chunk(ctx, b, c, d_samples, arena_len, d_lmfe, d_ms, d_out);
@@ -1078,7 +1107,7 @@ int spb_set_option(const char *name, double value) {
   const std::string n(name);
   const int iv = (int)value;
   if (n == "feature_kernel" && iv >= 0 && iv <= 2) o.feature_kernel = iv;
-  else if (n == "cmvnw_kernel" && iv >= 0 && iv <= 2) o.cmvnw_kernel = iv;
+  else if (n == "cmvnw_kernel" && iv >= 0 && iv <= 3) o.cmvnw_kernel = iv;
   else if (n == "tc_version" && (iv == 1 || iv == 2)) o.tc_version = iv;
   else if (n == "tc_epilogue" && iv >= -1 && iv <= 2) o.tc_epilogue = iv;
   else if (n == "redo" && (iv == 0 || iv == 1)) o.redo = iv;
@@ -1358,7 +1387,7 @@ static int host_batch(spb_context *ctx, const spb_batch *b, const void *samples,
   char *d_raw = (dtype == SPB_F32) ? (char *)d_samples : (char *)scratch(ctx, 5, (size_t)arena_len * esz);
   if (!d_samples || !d_out || !d_raw) return SPB_ERR_CUDA;
   float *d_lmfe = nullptr, *d_ms = nullptr;
-  if (which == 0 && (rc = lmfe_cmvnw_prepare(ctx, b, b->max_chunk_rows, &d_lmfe, &d_ms))) return rc;
+  if (which == 0 && (rc = lmfe_cmvnw_prepare(ctx, b, b->max_chunk_rows, d_out, &d_lmfe, &d_ms))) return rc;
   const bool hybrid = which != 0 && mfcc_hybrid_ok(b, FEAT_MFCC_DELTA);
   if (hybrid) {
     d_lmfe = (float *)scratch(ctx, 2, (size_t)std::max<int64_t>(b->max_chunk_rows, 1) * b->plan->p.num_filters * 4);

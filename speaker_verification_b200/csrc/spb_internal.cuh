@@ -64,7 +64,7 @@ struct spb_context {
   bool timing = false;
   std::vector<cudaEvent_t> ev_pool;
   size_t ev_used = 0;
-  std::vector<std::pair<size_t, size_t>> ev_pairs[4];  // indices into ev_pool
+  std::vector<std::pair<size_t, size_t>> ev_pairs[6];  // indices into ev_pool
 };
 
 struct spb_plan {
@@ -160,6 +160,8 @@ struct BatchChunk {
   int64_t big0 = 0, big1 = 0;  // large-tile cmvnw tiles
   int64_t s_lo = 0, s_hi = 0;  // sample span [min start, max end) of the chunk's utterances
   int64_t tc0 = 0, tc1 = 0;    // TcGroup range (multiples of 4)
+  int64_t st0 = 0, st1 = 0;    // single-pass cmvnw streams (utterances of >= 150 rows), longest first
+  int64_t rt0 = 0, rt1 = 0;    // large-tile cmvnw tiles of the utterances the stream kernel does not take
 };
 }  // namespace spb
 
@@ -183,6 +185,8 @@ struct spb_batch {
   spb::TcGroup *d_tc_groups = nullptr;    // tensor-core feature kernel tiles (nullptr: not usable)
   int4 *d_big_tiles = nullptr;           // large-tile cmvnw: {utt, first row, rows, 0}, longest first per chunk
   int big_rmax = 0;                      // 0: large-tile path not usable for this plan
+  int4 *d_streams = nullptr;             // single-pass cmvnw: {utt, first row, end row, 0} (nullptr: not usable)
+  bool has_short_utts = false;           // some utterance has fewer rows than the stream kernel takes
   std::vector<spb::BatchChunk> chunks;   // pipeline units of the host-pointer calls
   std::vector<spb::BatchChunk> groups;   // launch units of the device-pointer calls (runs of chunks)
   int64_t max_group_rows = 0;
@@ -195,7 +199,7 @@ namespace spb {
 // process-wide kernel selection / guard knobs behind spb_set_option (declared in the public header)
 struct Options {
   int feature_kernel = 0;  // 0 auto, 1 generic radix-2 kernel, 2 CUDA-core FFT kernels only (no tensor cores)
-  int cmvnw_kernel = 0;    // 0 auto (single pass), 1 small-tile two-pass, 2 large-tile two-pass
+  int cmvnw_kernel = 0;    // 0 auto (large-tile two-pass), 1 small-tile two-pass, 2 large-tile two-pass, 3 single streaming pass
   int tc_version = 2;      // tensor-core lmfe kernel generation: 2 (folded hop DFT) or 1
   int tc_epilogue = -1;    // -1 auto, 0 / 1 / 2: force that epilogue flavour of generation 2 where legal
   int redo = 1;            // float64 recomputation of low-energy filters (the 1e-4 guard)
@@ -285,6 +289,12 @@ int cmvnw_big_rmax(int cols, int win);
 int launch_cmvnw_big(spb_context *ctx, const float *in, float *scratch_ms, float *out,
                      const int32_t *nframes, const int64_t *frame_offsets, const int4 *tiles,
                      int64_t num_tiles, int rmax, int cols, int ld, int win, int varnorm);
+// single-pass streaming cmvnw (cmvn_stream_kernels.cu): window 301, variance normalisation, 40 columns
+bool cmvnw_stream_supported(int cols, int win, int varnorm);
+int cmvnw_stream_min_rows();
+void append_streams(std::vector<int4> &v, int utt, int64_t F);
+int launch_cmvnw_stream(spb_context *ctx, const float *in, float *out, const int32_t *nframes,
+                        const int64_t *frame_offsets, const int4 *streams, int64_t num_streams);
 // balanced tiles of one utterance of F rows: appends {utt, r0, rows, 0}
 void append_big_tiles(std::vector<int4> &v, int utt, int64_t F, int rmax);
 bool cmvnw_supported(int cols, int win);

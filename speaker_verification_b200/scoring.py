@@ -216,7 +216,8 @@ def _cuda_block_scores(E_block, T, ti_local, tj):
     return trial_scores_dev(S, ti_local, tj), S
 
 
-def score_trials_sharded(E_block, row0, m, T, trial_i, trial_j, labels, group=None, block_scores=None):
+def score_trials_sharded(E_block, row0, m, T, trial_i, trial_j, labels, group=None, block_scores=None,
+                         t_resident=False):
     """Score a trial list with the enrolment rows sharded over the ranks of ``group``.
 
     E_block : this rank's rows [row0, row0 + E_block.shape[0]) of the (m, d) enrolment matrix
@@ -228,6 +229,7 @@ def score_trials_sharded(E_block, row0, m, T, trial_i, trial_j, labels, group=No
     Exchange steps: ONE broadcast of T (NCCL over NVLink on GPUs) and one small
     reduce-to-rank-0 of the per-trial score vector, in which every trial is non-zero on
     exactly the rank that owns its row (x + 0 is exact, so the reduction is a gather).
+    ``t_resident=True`` skips the broadcast: every rank already holds T (broadcast once, outside).
     ``block_scores`` replaces the CUDA block computation in CPU (gloo) tests of this
     exchange logic; the product path never passes it.
     """
@@ -235,7 +237,7 @@ def score_trials_sharded(E_block, row0, m, T, trial_i, trial_j, labels, group=No
     import torch.distributed as dist
     rank = dist.get_rank(group) if dist.is_initialized() else 0
     world = dist.get_world_size(group) if dist.is_initialized() else 1
-    if world > 1:
+    if world > 1 and not t_resident:
         dist.broadcast(T, src=dist.get_global_rank(group, 0) if group is not None else 0, group=group)
     rows = E_block.shape[0]
     own = (trial_i >= row0) & (trial_i < row0 + rows)

@@ -342,6 +342,47 @@ def test_feature_cubes_many_utterances(sp):
     fb.close()
 
 
+def test_single_pass_cmvnw_matches_two_pass_kernels_and_oracle(sp):
+    """Option cmvnw_kernel=3: cmvnw as ONE streaming pass (csrc/cmvn_stream_kernels.cu: rings of lmfe and
+    mean-subtracted rows in shared memory, super-steps of 180 rows; reads every row once and writes it
+    once, but measured slower than the two-pass kernels, so it is opt-in).  Lengths chosen around every
+    boundary of its schedule: < 150 rows (stays with the two-pass kernels), 150 / 151 (minimum), the
+    super-step 180, 330 = 180 + 150, ring sizes 525 / 660, many super-steps, and > 3 000 rows (cut into
+    segments that re-derive their context).  Checked against the large-tile two-pass kernels (the
+    default) and, on every value, against processing.cmvnw in float64."""
+    from speaker_verification_b200 import _lib
+    rows = [149, 150, 151, 164, 165, 179, 180, 181, 195, 299, 300, 301, 329, 330, 331, 345, 359, 360, 361,
+            524, 525, 526, 540, 659, 660, 661, 720, 900, 1998, 3000, 3001, 4801, 5998, 1, 31, 7205]
+    lengths = [320 + 160 * r + (7 * i) % 160 for i, r in enumerate(rows)]
+    sigs = _signals(900, lengths)
+    # digital silence inside an utterance: constant log-mel rows -> zero variance, the reference gives 0 / (0 + eps) = 0
+    sigs[28][40000:140000] = 0.0
+    arena, starts, lens = batch.pack(sigs)
+    fb = batch.FeatureBatch(starts, lens)
+    assert [int(f) for f in np.diff(fb.frame_offsets)] == rows
+    two = fb.lmfe_cmvnw(arena)
+    with _lib.options(cmvnw_kernel=3):
+        one = fb.lmfe_cmvnw(arena)
+        # a NaN sample poisons the rows whose windows touch it, as in the two-pass kernels
+        bad = arena.copy()
+        bad[starts[28] + 200000] = np.nan
+        one_nan = fb.split(fb.lmfe_cmvnw(bad))[28]
+    assert np.all(np.isfinite(one))
+    assert np.max(np.abs(one - two)) < 2e-5
+    worst = 0.0
+    for s, got in zip(sigs, fb.split(one)):
+        ref = o.cmvnw_vectorised(o.lmfe(s, FS), 301, True)
+        worst = max(worst, float(np.max(np.abs(got - ref))))
+    assert worst < TOL, worst
+    sil = fb.split(one)[28][400:700]
+    assert np.max(np.abs(sil)) < 1e-5
+    f_nan = 200000 // 160
+    nan_rows = np.flatnonzero(np.isnan(one_nan).any(axis=1))
+    assert nan_rows.min() >= f_nan - 1 - 300 and nan_rows.max() <= f_nan + 300 + 29
+    assert np.isnan(one_nan[f_nan - 290:f_nan + 290]).all()
+    fb.close()
+
+
 def test_nan_samples_poison_the_window_like_the_reference(sp):
     """A NaN sample makes its frames NaN and, through the window mean / std, every cmvnw row whose
     window touches them (processing.py:302-322) -- in every column (the block sums convert half of

@@ -24,8 +24,10 @@ variants = [
     ("tc1", dict(tc_version=1)),
     ("fft512", dict(feature_kernel=2)),
 ]
-if what != "lmfe":
-    variants += [("tc2 + two-pass large-tile cmvnw", dict(cmvnw_kernel=2))]
+if len(sys.argv) > 2 and sys.argv[2] == "one":
+    variants = variants[:1]
+elif what != "lmfe":
+    variants += [("tc2 + single-pass streaming cmvnw", dict(cmvnw_kernel=3))]
 for name, opts in variants:
     with _lib.options(**opts):
         for _ in range(3):
