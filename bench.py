@@ -555,17 +555,19 @@ def bench_scoring(torch, dist, ctx, rank, world, device):
         E_blk = E5[r0:r1].contiguous()
         T_dev = T5 if rank == 0 else torch.zeros_like(T5)
 
+        plan = scoring.ShardedTrials(r0, r1 - r0, ti5, tj5, lab5)  # trial ownership, computed once
+
         def timed(resident):
             res = None
             for _ in range(3):
-                res = scoring.score_trials_sharded(E_blk, r0, m5, T_dev, ti5, tj5, lab5, t_resident=resident)
+                res = plan.score(E_blk, T_dev, t_resident=resident)
             torch.cuda.synchronize()
             dist.barrier()
             torch.cuda.synchronize()
             K = 10
             t0 = time.perf_counter()
             for _ in range(K):
-                res = scoring.score_trials_sharded(E_blk, r0, m5, T_dev, ti5, tj5, lab5, t_resident=resident)
+                res = plan.score(E_blk, T_dev, t_resident=resident)
             torch.cuda.synchronize()
             t = torch.tensor([(time.perf_counter() - t0) / K * 1e3], dtype=torch.float64, device=device)
             dist.all_reduce(t, op=dist.ReduceOp.MAX)

@@ -118,7 +118,9 @@ SPB_API int spb_stack_frames(spb_context *ctx, const double *sig, int64_t num_sa
  * mode 0: |X|^2/nfft   mode 1: |X|
  * mode 2: log_power_spectrum(normalize=False) = 10 log10(max(P, 1e-20)) (processing.py:177-198)
  * mode 3: the same minus its global maximum (normalize=True).
- * nfft must be a power of two in [32, 4096] (SPB_ERR_UNSUPPORTED otherwise). */
+ * nfft must be a power of two in [32, 4096] (SPB_ERR_UNSUPPORTED otherwise).
+ * Deviation from the reference: the transform runs in float32 on the device (frames are narrowed
+ * after upload, the result widened to float64); |error| <= 1e-5 of the row maximum. */
 SPB_API int spb_power_spectrum(spb_context *ctx, const double *frames, int64_t num_frames,
                        int32_t frame_len, int32_t nfft, int32_t mode, double *out);
 
@@ -155,7 +157,11 @@ SPB_API int spb_plan_destroy(spb_plan *plan);
  * sig: num_samples values of `dtype` (converted like signal.astype(float));
  * frames = floor((N-L)/S) (zero_padding=False, feature.py:193).  Outputs are
  * float64: feat (F, M), energy (F) [may be NULL], ceps (F, C).  Exact zeros
- * become float64 eps before the log (functions.py:55-62). */
+ * become float64 eps before the log (functions.py:55-62).
+ * Deviation from the reference: framing, FFT and filterbank run in float32 on the device (the
+ * signal is narrowed after upload, results widened to float64); log-mel / MFCC values are within
+ * 1e-4 of the float64 reference on every value (filters whose energy is too low for float32 are
+ * recomputed in float64, csrc/redo_kernels.cu). */
 SPB_API int spb_mfe(spb_context *ctx, const spb_plan *plan, const void *sig, int32_t dtype,
             int64_t num_samples, double *feat, double *energy);
 SPB_API int spb_lmfe(spb_context *ctx, const spb_plan *plan, const void *sig, int32_t dtype,
@@ -175,7 +181,12 @@ SPB_API int spb_derivative(spb_context *ctx, const double *feat, int64_t num_fra
 
 /* ------------------------------------------------------- a8 / a9  cmvn, cmvnw
  * sfe/speechpy/processing.py:239-271: float64 in, float64 out.
- * sfe/speechpy/processing.py:274-327: float64 in, float32 out; win_size odd. */
+ * sfe/speechpy/processing.py:274-327: float64 in, float32 out; win_size odd.  The window means are
+ * float64 sums of the float64 input and x - mean is rounded to float32 once, as in the reference
+ * (processing.py:302-307), so a large common offset costs no precision; stage 2 (window std of the
+ * float32 rows) runs in float32 with float64 block sums: var = E[x^2] - mean^2 anchored every 30 rows
+ * in float64 and slid with float32 deltas -- within 1e-4 for feature-like data (|x - mean| spanning
+ * <~ 3 decades inside one window); numpy's two-pass float32 std is more accurate beyond that. */
 SPB_API int spb_cmvn(spb_context *ctx, const double *vec, int64_t rows, int32_t cols,
              int32_t variance_normalization, double *out);
 SPB_API int spb_cmvnw(spb_context *ctx, const double *vec, int64_t rows, int32_t cols,

@@ -1285,13 +1285,19 @@ int spb_cmvnw(spb_context *ctx, const double *vec, int64_t rows, int32_t cols, i
   if (!cmvnw_supported(cc, win)) return fail(ctx, SPB_ERR_UNSUPPORTED, "cmvnw: win_size too large for shared memory");
   const size_t n = (size_t)rows * cols;
   double *d_f64 = (double *)scratch(ctx, 5, n * 8);
-  float *d_in = (float *)scratch(ctx, 0, n * 4);
   float *d_out = (float *)scratch(ctx, 1, n * 4);
   float *d_ms = (float *)scratch(ctx, 3, n * 4);
-  if (!d_f64 || !d_in || !d_out || !d_ms) return SPB_ERR_CUDA;
+  if (!d_f64 || !d_out || !d_ms) return SPB_ERR_CUDA;
   SPB_CUDA(ctx, cudaMemcpyAsync(d_f64, vec, n * 8, cudaMemcpyHostToDevice, ctx->stream));
-  int rc = launch_convert(ctx, d_f64, SPB_F64, d_in, SPB_F32, (int64_t)n);
+  // stage 1 in float64 from the float64 input (processing.py:302-307): a large common offset is
+  // subtracted before anything is narrowed; stage 2 on the float32 rows like the reference
+  int rc = launch_cmvnw_stage1_f64(ctx, d_f64, rows, cols, win, varnorm ? d_ms : d_out);
   if (rc) return rc;
+  if (!varnorm) {
+    SPB_CUDA(ctx, cudaMemcpyAsync(out, d_out, n * 4, cudaMemcpyDeviceToHost, ctx->stream));
+    SPB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return SPB_OK;
+  }
   const int32_t nfr = (int32_t)rows;
   const int64_t offs[2] = {0, rows};
   const int big_rmax = options().cmvnw_kernel == 1 ? 0 : cmvnw_big_rmax(cols, win);
@@ -1304,8 +1310,8 @@ int spb_cmvnw(spb_context *ctx, const double *vec, int64_t rows, int32_t cols, i
     SPB_CUDA(ctx, cudaMemcpyAsync(meta, &nfr, 4, cudaMemcpyHostToDevice, ctx->stream));
     SPB_CUDA(ctx, cudaMemcpyAsync(meta + 16, offs, 16, cudaMemcpyHostToDevice, ctx->stream));
     SPB_CUDA(ctx, cudaMemcpyAsync(meta + 64, tiles.data(), tiles.size() * sizeof(int4), cudaMemcpyHostToDevice, ctx->stream));
-    rc = launch_cmvnw_big(ctx, d_in, d_ms, d_out, (const int32_t *)meta, (const int64_t *)(meta + 16),
-                          (const int4 *)(meta + 64), (int64_t)tiles.size(), big_rmax, cols, cols, win, varnorm);
+    rc = launch_cmvnw_big(ctx, nullptr, d_ms, d_out, (const int32_t *)meta, (const int64_t *)(meta + 16),
+                          (const int4 *)(meta + 64), (int64_t)tiles.size(), big_rmax, cols, cols, win, 1, 2);
     if (rc) return rc;
     SPB_CUDA(ctx, cudaMemcpyAsync(out, d_out, n * 4, cudaMemcpyDeviceToHost, ctx->stream));
     SPB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
@@ -1327,8 +1333,8 @@ int spb_cmvnw(spb_context *ctx, const double *vec, int64_t rows, int32_t cols, i
   if (rc) return rc;
   for (int c0 = 0; c0 < cols; c0 += cc) {
     const int w = std::min(cc, cols - c0);
-    rc = launch_cmvnw_f32(ctx, d_in + c0, d_ms + c0, d_out + c0, d_nfr, d_offs, d_tiles, ntiles, R,
-                          w, cols, win, varnorm);
+    rc = launch_cmvnw_f32(ctx, nullptr, d_ms + c0, d_out + c0, d_nfr, d_offs, d_tiles, ntiles, R,
+                          w, cols, win, 1, 2);
     if (rc) return rc;
   }
   SPB_CUDA(ctx, cudaMemcpyAsync(out, d_out, n * 4, cudaMemcpyDeviceToHost, ctx->stream));

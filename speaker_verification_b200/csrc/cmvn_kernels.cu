@@ -259,7 +259,7 @@ bool cmvnw_supported(int cols, int win) {
 
 int launch_cmvnw_f32(spb_context *ctx, const float *in, float *scratch_ms, float *out,
                      const int32_t *nframes, const int64_t *frame_offsets, const int2 *tiles,
-                     int64_t num_tiles, int tile_rows, int cols, int ld, int win, int varnorm) {
+                     int64_t num_tiles, int tile_rows, int cols, int ld, int win, int varnorm, int first_stage) {
   if (num_tiles <= 0) return SPB_OK;
   CmParams p;
   p.nframes = nframes;
@@ -272,7 +272,7 @@ int launch_cmvnw_f32(spb_context *ctx, const float *in, float *scratch_ms, float
   p.win = win;
   p.eps = 9.313225746154785e-10f;  // 2^-30 (processing.py:292)
   const size_t smem = cm_smem_bytes(tile_rows, cols, win);
-  for (int stage = 1; stage <= (varnorm ? 2 : 1); ++stage) {
+  for (int stage = first_stage; stage <= (varnorm ? 2 : 1); ++stage) {
     // two columns per thread need 8-byte aligned rows in global and shared memory
     const bool v2 = (cols % 2 == 0) && (ld % 2 == 0) && ((((size_t)in) & 7) == 0) &&
                     ((((size_t)out) & 7) == 0) && (!scratch_ms || (((size_t)scratch_ms) & 7) == 0);
@@ -592,7 +592,7 @@ int cmvnw_big_rmax(int cols, int win) {
 
 int launch_cmvnw_big(spb_context *ctx, const float *in, float *scratch_ms, float *out,
                      const int32_t *nframes, const int64_t *frame_offsets, const int4 *tiles,
-                     int64_t num_tiles, int rmax, int cols, int ld, int win, int varnorm) {
+                     int64_t num_tiles, int rmax, int cols, int ld, int win, int varnorm, int first_stage) {
   if (num_tiles <= 0) return SPB_OK;
   int *counters = (int *)scratch(ctx, 7, 256);
   if (!counters) return SPB_ERR_CUDA;
@@ -608,7 +608,7 @@ int launch_cmvnw_big(spb_context *ctx, const float *in, float *scratch_ms, float
   p.rmax = rmax;
   p.eps = 9.313225746154785e-10f;  // 2^-30 (processing.py:292)
   const size_t smem = cm_big_smem_bytes(rmax, cols, win);
-  for (int stage = 1; stage <= (varnorm ? 2 : 1); ++stage) {
+  for (int stage = first_stage; stage <= (varnorm ? 2 : 1); ++stage) {
     auto kern = (cols == 40) ? (stage == 1 ? cmvnw_big_kernel<1, 40> : cmvnw_big_kernel<2, 40>)
                              : (stage == 1 ? cmvnw_big_kernel<1, 0> : cmvnw_big_kernel<2, 0>);
     int per_sm = 0;
@@ -624,6 +624,46 @@ int launch_cmvnw_big(spb_context *ctx, const float *in, float *scratch_ms, float
     timing_end(ctx, stage, tb);
     SPB_LAUNCH_CHECK(ctx, "cmvnw_big_kernel");
   }
+  return SPB_OK;
+}
+
+// ------------------------------------------------------------------------------------
+// cmvnw stage 1 on float64 input (the public processing.cmvnw call hands float64): window means in
+// float64 from the float64 values, x - mean in float64, ONE rounding to float32 on the store --
+// exactly processing.py:302-307 (mean_subtracted is a float32 array).  Narrowing the input first
+// would quantise a large common offset (1e4 +- 1e-2) before it is subtracted.  Stage 2 then runs on
+// the float32 rows like the reference.  One thread per (column, chunk of 64 rows): the first window
+// is summed directly, the rest slides; not a hot path (this call is bound by PCIe).
+// ------------------------------------------------------------------------------------
+constexpr int kS1Chunk = 64;
+__global__ void __launch_bounds__(128)
+cmvnw_stage1_f64_kernel(const double *__restrict__ in, long long rows, int cols, int win, float *__restrict__ out) {
+  const int c = blockIdx.y * 32 + threadIdx.x;
+  const long long r0 = ((long long)blockIdx.x * 4 + threadIdx.y) * kS1Chunk;
+  if (c >= cols || r0 >= rows) return;
+  const int F = (int)rows;
+  const int h = (win - 1) >> 1;
+  const double inv = 1.0 / (double)win;
+  double w = 0.0;
+  for (int t = -h; t <= h; ++t) w += in[(long long)reflect_row(r0 + t, F) * cols + c];
+  const long long r1 = r0 + kS1Chunk < rows ? r0 + kS1Chunk : rows;
+  for (long long r = r0; r < r1; ++r) {
+    out[r * cols + c] = (float)(in[r * cols + c] - w * inv);
+    w += in[(long long)reflect_row(r + h + 1, F) * cols + c] - in[(long long)reflect_row(r - h, F) * cols + c];
+    if (w != w || fabs(w) == INFINITY) {
+      // a NaN / inf that slid in never slides out of a running sum: sum the next window directly, so that
+      // exactly the rows whose window holds it are poisoned (as in the reference)
+      w = 0.0;
+      for (int t = -h; t <= h; ++t) w += in[(long long)reflect_row(r + 1 + t, F) * cols + c];
+    }
+  }
+}
+
+int launch_cmvnw_stage1_f64(spb_context *ctx, const double *in, int64_t rows, int cols, int win, float *out) {
+  if (rows <= 0 || cols <= 0) return SPB_OK;
+  const dim3 grid((unsigned)((rows + 4 * kS1Chunk - 1) / (4 * kS1Chunk)), (unsigned)((cols + 31) / 32));
+  cmvnw_stage1_f64_kernel<<<grid, dim3(32, 4), 0, ctx->stream>>>(in, rows, cols, win, out);
+  SPB_LAUNCH_CHECK(ctx, "cmvnw_stage1_f64_kernel");
   return SPB_OK;
 }
 

@@ -283,12 +283,14 @@ int launch_features_fast1024(spb_context *ctx, const FeatArgs &a, const FftTable
 
 int launch_cmvnw_f32(spb_context *ctx, const float *in, float *scratch_ms, float *out,
                      const int32_t *nframes, const int64_t *frame_offsets, const int2 *tiles,
-                     int64_t num_tiles, int tile_rows, int cols, int ld, int win, int varnorm);
+                     int64_t num_tiles, int tile_rows, int cols, int ld, int win, int varnorm, int first_stage = 1);
 int cmvnw_tile_rows(int cols, int win);
 int cmvnw_big_rmax(int cols, int win);
 int launch_cmvnw_big(spb_context *ctx, const float *in, float *scratch_ms, float *out,
                      const int32_t *nframes, const int64_t *frame_offsets, const int4 *tiles,
-                     int64_t num_tiles, int rmax, int cols, int ld, int win, int varnorm);
+                     int64_t num_tiles, int rmax, int cols, int ld, int win, int varnorm, int first_stage = 1);
+// stage 1 of cmvnw from float64 rows (float64 window means, one rounding to float32): the public cmvnw call
+int launch_cmvnw_stage1_f64(spb_context *ctx, const double *in, int64_t rows, int cols, int win, float *out);
 // single-pass streaming cmvnw (cmvn_stream_kernels.cu): window 301, variance normalisation, 40 columns
 bool cmvnw_stream_supported(int cols, int win, int varnorm);
 int cmvnw_stream_min_rows();

@@ -216,6 +216,46 @@ def _cuda_block_scores(E_block, T, ti_local, tj):
     return trial_scores_dev(S, ti_local, tj), S
 
 
+class ShardedTrials:
+    """The per-rank part of a trial list for row-sharded scoring, computed once: which trials this
+    rank's row block [row0, row0 + rows) owns and their local indices.  ``score`` is the per-call
+    work: [broadcast of T] -> normalise + GEMM of the block -> gather -> reduce to rank 0 -> EER."""
+
+    def __init__(self, row0, rows, trial_i, trial_j, labels, group=None):
+        import torch
+        self.row0, self.rows, self.group = int(row0), int(rows), group
+        own = (trial_i >= row0) & (trial_i < row0 + rows)
+        self.idx = torch.nonzero(own).flatten()
+        self.ti_local = (trial_i[self.idx] - row0).to(torch.int32).contiguous()
+        self.tj_local = trial_j[self.idx].to(torch.int32).contiguous()
+        self.num_trials = int(trial_i.numel())
+        self.labels = labels.to(torch.int32).contiguous()
+
+    def score(self, E_block, T, t_resident=False, block_scores=None):
+        import torch
+        import torch.distributed as dist
+        group = self.group
+        on = dist.is_initialized()
+        rank = dist.get_rank(group) if on else 0
+        world = dist.get_world_size(group) if on else 1
+        root = dist.get_global_rank(group, 0) if (on and group is not None) else 0
+        if world > 1 and not t_resident:
+            dist.broadcast(T, src=root, group=group)
+        full = torch.zeros(self.num_trials, dtype=torch.float32, device=E_block.device)
+        if self.rows > 0 and self.idx.numel() > 0:
+            fn = block_scores or _cuda_block_scores
+            picked, _ = fn(E_block, T, self.ti_local, self.tj_local)
+            full[self.idx] = picked
+        if world > 1:
+            dist.reduce(full, dst=root, op=dist.ReduceOp.SUM, group=group)
+        if rank != 0:
+            return None, None, None
+        if block_scores is not None and not full.is_cuda:
+            return None, None, full  # CPU test of the exchange: the caller checks the scores
+        eer, auc = eer_auc_dev(full, self.labels)
+        return eer, auc, full
+
+
 def score_trials_sharded(E_block, row0, m, T, trial_i, trial_j, labels, group=None, block_scores=None,
                          t_resident=False):
     """Score a trial list with the enrolment rows sharded over the ranks of ``group``.
@@ -233,28 +273,5 @@ def score_trials_sharded(E_block, row0, m, T, trial_i, trial_j, labels, group=No
     ``block_scores`` replaces the CUDA block computation in CPU (gloo) tests of this
     exchange logic; the product path never passes it.
     """
-    import torch
-    import torch.distributed as dist
-    rank = dist.get_rank(group) if dist.is_initialized() else 0
-    world = dist.get_world_size(group) if dist.is_initialized() else 1
-    if world > 1 and not t_resident:
-        dist.broadcast(T, src=dist.get_global_rank(group, 0) if group is not None else 0, group=group)
-    rows = E_block.shape[0]
-    own = (trial_i >= row0) & (trial_i < row0 + rows)
-    idx = torch.nonzero(own).flatten()
-    ti_local = (trial_i[idx] - row0).to(torch.int32).contiguous()
-    tj_local = trial_j[idx].to(torch.int32).contiguous()
-    full = torch.zeros(trial_i.numel(), dtype=torch.float32, device=E_block.device)
-    if rows > 0 and idx.numel() > 0:
-        fn = block_scores or _cuda_block_scores
-        picked, _ = fn(E_block, T, ti_local, tj_local)
-        full[idx] = picked
-    if world > 1:
-        dist.reduce(full, dst=dist.get_global_rank(group, 0) if group is not None else 0,
-                    op=dist.ReduceOp.SUM, group=group)
-    if rank != 0:
-        return None, None, None
-    if block_scores is not None and not full.is_cuda:
-        return None, None, full  # CPU test of the exchange: the caller checks the scores
-    eer, auc = eer_auc_dev(full, labels.to(torch.int32).contiguous())
-    return eer, auc, full
+    plan = ShardedTrials(row0, E_block.shape[0], trial_i, trial_j, labels, group)
+    return plan.score(E_block, T, t_resident=t_resident, block_scores=block_scores)

@@ -228,6 +228,25 @@ def test_other_filterbank_shapes(sp):
         assert maxabs(sp.feature.mfcc(x, FS, num_cepstral=12, **kc), o.mfcc(x, FS, num_cepstral=12, **kc)) < TOL, kw
 
 
+def test_cmvnw_large_offset_and_ramp(sp):
+    """processing.cmvnw takes float64 and subtracts the window mean in float64 (processing.py:302-307).
+    Inputs whose offset dwarfs their variation (1e4 +- 1e-2, a ramp of 1e6 with noise on it) lose
+    everything if they are narrowed to float32 before the mean is subtracted."""
+    rng = np.random.Generator(np.random.Philox(91))
+    noise = rng.standard_normal((1200, 40)) * 1e-2
+    ramp = np.linspace(0.0, 1e6, 1200)[:, None] + rng.standard_normal((1200, 40))
+    for v in (1e4 + noise, -3e5 + noise * 10, ramp):
+        # variance mode on the ramp is left out: its mean-subtracted rows span 5 decades inside one window
+        # (6e4 at the reflected edges, 1 inside) and stage 2's one-pass float32 variance (documented in
+        # include/speechpy_b200.h) is then less accurate than numpy's two-pass float32 std
+        for vn in ((False,) if v is ramp else (True, False)):
+            got = sp.processing.cmvnw(v, 301, vn)
+            ref = o.cmvnw_vectorised(v, 301, vn)
+            scale = max(1.0, float(np.abs(ref).max()))
+            assert got.dtype == np.float32
+            assert np.max(np.abs(got - ref)) < 1e-4 * scale, (float(np.abs(got - ref).max()), scale)
+
+
 def test_cmvnw_row_counts(sp):
     g = golden("cmvnw_rows.npz")
     for rows in (1, 2, 5, 149, 150, 151, 299, 300, 301, 302, 400, 1000):
@@ -281,3 +300,23 @@ def test_reference_test_suite_semantics(sp):
     mf = sp.feature.mfcc(signal, sampling_frequency=FS, frame_length=0.020, num_cepstral=13, frame_stride=0.01,
                          num_filters=40, fft_length=512, low_frequency=0, high_frequency=None)
     assert mf.shape[1] == 13
+
+
+def test_reference_test_file_runs_unchanged_against_the_dropin(sp):
+    """sfe/tests/test_speechpy.py ("must pass unchanged"), staged verbatim under
+    oracle/_ref/tests by oracle/make_ref.py, run by pytest in a fresh process in which `speechpy` is the
+    GPU-backed drop-in (install_dropin() before the file's own `from speechpy import ...`)."""
+    import os
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    test_file = os.path.join(root, "oracle", "_ref", "tests", "test_speechpy.py")
+    if not os.path.exists(test_file):
+        pytest.skip("oracle/_ref not staged (python oracle/make_ref.py where /root/reference exists)")
+    code = ("import sys; sys.path.insert(0, %r); import speaker_verification_b200 as p; p.install_dropin(); "
+            "import speechpy, pytest; assert 'speaker_verification_b200' in speechpy.__file__; "
+            "sys.exit(pytest.main(['-q', '-p', 'no:cacheprovider', %r]))" % (root, test_file))
+    r = subprocess.run([sys.executable, "-c", code], cwd=os.path.dirname(test_file), capture_output=True, text=True,
+                       timeout=600)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+    assert " passed" in r.stdout and "failed" not in r.stdout

@@ -162,3 +162,21 @@ def test_cmvn_transform_and_feature_cubes_oracle():
             cube = o.feature_cube(o.cmvn_transform(lm.copy(), deriv, norm), g[f"idx_{tag}"], 80)
             assert cube.shape == (3 if deriv else 1, 20, 80, 40) and cube.dtype == np.float32
             assert np.array_equal(cube[:, :3], g[f"cube_{tag}"])
+
+
+def test_staged_reference_equals_oracle_port():
+    """oracle/_ref (the reference's own files, staged by oracle/make_ref.py; what bench.py's CPU legs
+    time as kind "reference") and the oracle port agree on the benchmarked chain."""
+    import pytest
+    from oracle import ref_loader
+    ref = ref_loader.load()
+    if ref is None:
+        pytest.skip("oracle/_ref not staged (needs /root/reference: python oracle/make_ref.py)")
+    from speaker_verification_b200 import synth
+    x = synth.audio(1, 48000, np.float32)
+    lm_ref = ref.feature.lmfe(x, 16000, frame_length=0.020, frame_stride=0.01, num_filters=40, fft_length=512)
+    lm = o.lmfe(x, 16000)
+    assert lm_ref.shape == lm.shape and np.max(np.abs(lm_ref - lm)) < 1e-12
+    a = ref.processing.cmvnw(lm_ref, 301, True)
+    b = o.cmvnw(lm, 301, True)
+    assert a.dtype == b.dtype == np.float32 and np.array_equal(a, b)
