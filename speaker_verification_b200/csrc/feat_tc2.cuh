@@ -40,18 +40,25 @@ constexpr int kT2KSteps = kT2K / 16;            // 5 MMA k-steps
 constexpr int kT2N = 128;                       // MMA N: bins (cos block) / bins (sin block)
 constexpr int kT2MaxBins = 128;
 #ifndef SPB_T2_SLOTS
-#define SPB_T2_SLOTS 9
+#define SPB_T2_SLOTS 6
+#endif
+#ifndef SPB_T2_STAGE
+#define SPB_T2_STAGE 3
 #endif
 constexpr int kT2Slots = SPB_T2_SLOTS;          // A-operand ring depth (k-steps)
+constexpr int kT2Stage = SPB_T2_STAGE;          // raw-sample staging depth (k-steps of cp.async in flight per converter)
 constexpr uint32_t kT2BLbo = kT2N * 16;                 // 2 048 B between the k-chunks of a W matrix
 constexpr uint32_t kT2BMat = (kT2K / 8) * kT2BLbo;      // 20 480 B: [k/8][col][8 halves]
 constexpr uint32_t kT2APart = 2 * kTcRows * 16;         // 4 096 B: [2][row][8 halves] of one k-step
 constexpr uint32_t kT2SlotBytes = 4 * kT2APart;         // s_hi | s_lo | d_hi | d_lo
 constexpr uint32_t kT2OffA = 4 * kT2BMat;               // C_hi | C_lo | S_hi | S_lo, then the ring
-constexpr uint32_t kT2OffBars = kT2OffA + kT2Slots * kT2SlotBytes;
+constexpr uint32_t kT2OffStage = kT2OffA + kT2Slots * kT2SlotBytes;       // [stage][4 loads][256 converters][16 B]
+constexpr uint32_t kT2StageBytes = 4 * kTcCvtWarps * 32 * 16;              // 16 KB per k-step
+constexpr uint32_t kT2OffBars = kT2OffStage + kT2Stage * kT2StageBytes;
 constexpr uint32_t kT2OffLvl = kT2OffBars + 256;        // [4][128] per-hop level (max |s|, |d|), by tile & 3
 constexpr uint32_t kT2Smem = kT2OffLvl + 4 * kTcRows * 4;
 static_assert(kT2Smem <= 232448, "features_tc2: shared memory budget");
+static_assert(kT2Stage >= 1 && kT2Stage <= kT2KSteps, "features_tc2: staging depth (at most one tile ahead)");
 static_assert((2 * kT2Slots + 4) * 8 + 4 <= 256, "features_tc2: barrier block");
 constexpr float kT2InScale = 16384.f;           // 2^14: s, d reach 2 |x|
 constexpr uint32_t kT2Idesc = (1u << 4) | ((uint32_t)(kT2N >> 3) << 17) | ((uint32_t)(kTcRows >> 4) << 24);
@@ -505,11 +512,27 @@ __global__ void __launch_bounds__(kTcThreads, 1) features_tc2_kernel(const T2Par
     };
     // forward samples of k-step s: x[80 + 16 s + 4 qq ..], mirrored: x[76 - 16 s - 4 qq ..]
     const int foff = kT2K + 4 * qq, boff = kT2K - 4 - 4 * qq;
+    // Raw samples reach the converter through cp.async (LDGSTS) into a private staging area: kT2Stage
+    // k-steps (4 x 16 B each) per thread are in flight at any time without holding registers -- with
+    // plain loads one k-step ahead the converters sat on the load latency (ncu r02l: long_scoreboard
+    // 6.5 warps per issue).  stage[d][j][c]: 16 B per converter thread, a warp covers 512 contiguous
+    // bytes on the way in and on the way out; a thread reads back only what it copied itself, so
+    // cp.async.wait_group is all the synchronisation there is.
+    const uint32_t stg = sbase + kT2OffStage + (uint32_t)c * 16u;
+    auto stage_issue = [&](const uint32_t d, const float *qa, const float *qb, const int st) {
+      const uint32_t a = stg + d * kT2StageBytes;
+      cp_async16(a, qa + foff + 16 * st);
+      cp_async16(a + 4096u, qa + boff - 16 * st);
+      cp_async16(a + 8192u, qb + foff + 16 * st);
+      cp_async16(a + 12288u, qb + boff - 16 * st);
+      cp_async_commit();
+    };
     long long t = blockIdx.x;
     const float *pA = row_ptr(t, rA), *pB = row_ptr(t, rB);
-    float4 fA = __ldg(reinterpret_cast<const float4 *>(pA + foff)), bA = __ldg(reinterpret_cast<const float4 *>(pA + boff));
-    float4 fB = __ldg(reinterpret_cast<const float4 *>(pB + foff)), bB = __ldg(reinterpret_cast<const float4 *>(pB + boff));
+#pragma unroll
+    for (int d = 0; d < kT2Stage; ++d) stage_issue((uint32_t)d, pA, pB, d);
     uint32_t it = 0, slot = 0, par = 1;  // tiles produced so far, ring slot and its wait parity
+    uint32_t sd = 0;                     // staging slot of the k-step about to be converted
     uint32_t bad = 0;
     for (; t < p.num_tiles; t += gridDim.x, ++it) {
       const float *nA = row_ptr(t + gridDim.x, rA), *nB = row_ptr(t + gridDim.x, rB);
@@ -525,18 +548,9 @@ __global__ void __launch_bounds__(kTcThreads, 1) features_tc2_kernel(const T2Par
       }
 #pragma unroll
       for (int s = 0; s < kT2KSteps; ++s) {
-        const float4 cfA = fA, cbA = bA, cfB = fB, cbB = bB;
-        if (s + 1 < kT2KSteps) {
-          fA = __ldg(reinterpret_cast<const float4 *>(pA + foff + 16 * (s + 1)));
-          bA = __ldg(reinterpret_cast<const float4 *>(pA + boff - 16 * (s + 1)));
-          fB = __ldg(reinterpret_cast<const float4 *>(pB + foff + 16 * (s + 1)));
-          bB = __ldg(reinterpret_cast<const float4 *>(pB + boff - 16 * (s + 1)));
-        } else {
-          fA = __ldg(reinterpret_cast<const float4 *>(nA + foff));
-          bA = __ldg(reinterpret_cast<const float4 *>(nA + boff));
-          fB = __ldg(reinterpret_cast<const float4 *>(nB + foff));
-          bB = __ldg(reinterpret_cast<const float4 *>(nB + boff));
-        }
+        cp_async_wait<kT2Stage - 1>();  // the oldest k-step in flight has landed
+        const uint32_t a = stg + sd * kT2StageBytes;
+        const float4 cfA = lds128(a), cbA = lds128(a + 4096u), cfB = lds128(a + 8192u), cbB = lds128(a + 12288u);
         uint2 sha, sla, dha, dla, shb, slb, dhb, dlb;
         const T2Fold va = t2_fold_split(cfA, cbA, sha, sla, dha, dla, mxA);
         const T2Fold vb = t2_fold_split(cfB, cbB, shb, slb, dhb, dlb, mxB);
@@ -547,6 +561,11 @@ __global__ void __launch_bounds__(kTcThreads, 1) features_tc2_kernel(const T2Par
         // keep the conversion ahead of the wait (the compiler otherwise sinks it below)
         asm volatile("" ::"r"(sha.x), "r"(sha.y), "r"(sla.x), "r"(sla.y), "r"(dha.x), "r"(dha.y), "r"(dla.x), "r"(dla.y));
         asm volatile("" ::"r"(shb.x), "r"(shb.y), "r"(slb.x), "r"(slb.y), "r"(dhb.x), "r"(dhb.y), "r"(dlb.x), "r"(dlb.y));
+        // the staged values are in registers (consumed above): refill the slot with the k-step kT2Stage ahead,
+        // which lies in this tile or the next (past the last tile row_ptr hands out the zero block)
+        if (s + kT2Stage < kT2KSteps) stage_issue(sd, pA, pB, s + kT2Stage);
+        else stage_issue(sd, nA, nB, s + kT2Stage - kT2KSteps);
+        sd = (sd + 1 == kT2Stage) ? 0u : sd + 1;
         if (s == kT2KSteps - 1) {
           // per-hop level for the epilogue's exactness guard (and the unsplittable-sample flag): max over
           // the four lanes of a row, written BEFORE the arrive of the tile's last k-step (the epilogue
@@ -592,6 +611,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) features_tc2_kernel(const T2Par
       pA = nA;
       pB = nB;
     }
+    cp_async_wait<0>();  // nothing may still be landing in shared memory when the CTA retires
     if (bad) *p.flag = 1;
   } else if (warp == kTcMmaWarp) {
     // ===== MMA issuer =====

@@ -103,6 +103,21 @@ __device__ __forceinline__ void tmem_ld16x2(uint32_t ta, uint32_t tb, uint32_t (
   asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
 }
 
+// 16-byte asynchronous copy global -> shared (LDGSTS, bypassing L1) and its group bookkeeping
+__device__ __forceinline__ void cp_async16(const uint32_t smem_addr, const void *src) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_addr), "l"(src) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() {
+  asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
+}
+__device__ __forceinline__ float4 lds128(const uint32_t smem_addr) {
+  float4 v;
+  asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(smem_addr));
+  return v;
+}
+
 // 1-D bulk copy global -> shared (TMA engine), completion counted on an mbarrier.
 // dst, src and bytes must be multiples of 16.
 __device__ __forceinline__ void bulk_load(void *dst, const void *src, uint32_t bytes, uint64_t *bar) {
