@@ -336,6 +336,9 @@ __device__ __forceinline__ double f2d_alu(float f) {
   return __hiloint2double((int)hi, (int)(u << 29));
 }
 
+__device__ __forceinline__ float2 big_neg(const float2 a) { return make_float2(-a.x, -a.y); }
+__device__ __forceinline__ float2 big_sub(const float2 a, const float2 b) { return __fadd2_rn(a, big_neg(b)); }
+
 template <int STAGE, int COLS>
 __global__ void __launch_bounds__(kBigThreads, 1)
 cmvnw_big_kernel(const CmBigParams p) {
@@ -526,46 +529,47 @@ cmvnw_big_kernel(const CmBigParams p) {
         const double m0x = w1x * inv_win, m0y = w1y * inv_win;
         const float mhx = (float)m0x, mhy = (float)m0y;
         const float mlx = (float)(m0x - (double)mhx), mly = (float)(m0y - (double)mhy);
-        float Dx = 0.f, Dy = 0.f;
+        // packed fp32 (FADD2 / FFMA2 / FMUL2: one instruction per column pair)
+        const float2 iw = make_float2(inv_w, inv_w);
+        const float2 mh = make_float2(mhx, mhy), ml = make_float2(mlx, mly);
+        float2 D = make_float2(0.f, 0.f);
         if (STAGE == 1) {
 #pragma unroll 2
           for (int q = q0; q < q1; ++q) {
             const float2 xc = *reinterpret_cast<const float2 *>(pc);
-            float2 o;
-            o.x = (xc.x - mhx) - fmaf(Dx, inv_w, mlx);
-            o.y = (xc.y - mhy) - fmaf(Dy, inv_w, mly);
-            *reinterpret_cast<float2 *>(dst) = o;
             const float2 xi = *reinterpret_cast<const float2 *>(pin);
             const float2 xo = *reinterpret_cast<const float2 *>(pout);
-            Dx += xi.x - xo.x;
-            Dy += xi.y - xo.y;
+            *reinterpret_cast<float2 *>(dst) = big_sub(big_sub(xc, mh), __ffma2_rn(D, iw, ml));
+            D = __fadd2_rn(D, big_sub(xi, xo));
             dst += ld; pc += cols; pin += cols; pout += cols;
           }
         } else {
           // processing.py:318-322: ms / (std(window) + eps), population std; the input is the
-          // mean-subtracted signal, so E[x^2] >> mean^2 and float32 is enough for the variance
-          const float e0x = (float)(w2x * inv_win), e0y = (float)(w2y * inv_win);
-          float Qx = 0.f, Qy = 0.f;
+          // mean-subtracted signal, so E[x^2] >> mean^2 and float32 is enough for the variance.
+          // Branch-free: x / (s + eps) = x r / (1 + eps r), r = rsqrt(v); v is clamped from below with a
+          // select (v <= 0 for constant windows must give x / eps; fmaxf would swallow a NaN variance,
+          // which has to poison the row like the reference)
+          const float2 e0 = make_float2((float)(w2x * inv_win), (float)(w2y * inv_win));
+          const float2 neps = make_float2(p.eps, p.eps), one = make_float2(1.f, 1.f);
+          float2 Q = make_float2(0.f, 0.f);
 #pragma unroll 2
           for (int q = q0; q < q1; ++q) {
             const float2 xc = *reinterpret_cast<const float2 *>(pc);
-            const float mx = mhx + fmaf(Dx, inv_w, mlx), my = mhy + fmaf(Dy, inv_w, mly);
-            const float vx = fmaf(-mx, mx, fmaf(Qx, inv_w, e0x)), vy = fmaf(-my, my, fmaf(Qy, inv_w, e0y));
-            float sx, sy;
-            // clamp rounding-negative variances with a select: fmaxf would swallow a NaN variance
-            // (a NaN anywhere in the window must poison the row, processing.py:318-322)
-            asm("sqrt.approx.f32 %0, %1;" : "=f"(sx) : "f"(vx < 0.f ? 0.f : vx));
-            asm("sqrt.approx.f32 %0, %1;" : "=f"(sy) : "f"(vy < 0.f ? 0.f : vy));
-            float2 o;
-            o.x = __fdividef(xc.x, sx + p.eps);
-            o.y = __fdividef(xc.y, sy + p.eps);
-            *reinterpret_cast<float2 *>(dst) = o;
             const float2 xi = *reinterpret_cast<const float2 *>(pin);
             const float2 xo = *reinterpret_cast<const float2 *>(pout);
-            Dx += xi.x - xo.x;
-            Dy += xi.y - xo.y;
-            Qx += fmaf(xi.x, xi.x, -xo.x * xo.x);
-            Qy += fmaf(xi.y, xi.y, -xo.y * xo.y);
+            const float2 m = __fadd2_rn(mh, __ffma2_rn(D, iw, ml));
+            const float2 v = __ffma2_rn(make_float2(-m.x, -m.y), m, __ffma2_rn(Q, iw, e0));
+            const float vx = v.x < 1e-30f ? 1e-30f : v.x, vy = v.y < 1e-30f ? 1e-30f : v.y;
+            float rx, ry, cx, cy;
+            asm("rsqrt.approx.f32 %0, %1;" : "=f"(rx) : "f"(vx));
+            asm("rsqrt.approx.f32 %0, %1;" : "=f"(ry) : "f"(vy));
+            const float2 r = make_float2(rx, ry);
+            const float2 d = __ffma2_rn(r, neps, one);
+            asm("rcp.approx.f32 %0, %1;" : "=f"(cx) : "f"(d.x));
+            asm("rcp.approx.f32 %0, %1;" : "=f"(cy) : "f"(d.y));
+            *reinterpret_cast<float2 *>(dst) = __fmul2_rn(__fmul2_rn(xc, r), make_float2(cx, cy));
+            D = __fadd2_rn(D, big_sub(xi, xo));
+            Q = __fadd2_rn(Q, __ffma2_rn(xi, xi, big_neg(__fmul2_rn(xo, xo))));
             dst += ld; pc += cols; pin += cols; pout += cols;
           }
         }

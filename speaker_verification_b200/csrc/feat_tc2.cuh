@@ -40,10 +40,10 @@ constexpr int kT2KSteps = kT2K / 16;            // 5 MMA k-steps
 constexpr int kT2N = 128;                       // MMA N: bins (cos block) / bins (sin block)
 constexpr int kT2MaxBins = 128;
 #ifndef SPB_T2_SLOTS
-#define SPB_T2_SLOTS 6
+#define SPB_T2_SLOTS 7
 #endif
 #ifndef SPB_T2_STAGE
-#define SPB_T2_STAGE 3
+#define SPB_T2_STAGE 2
 #endif
 constexpr int kT2Slots = SPB_T2_SLOTS;          // A-operand ring depth (k-steps)
 constexpr int kT2Stage = SPB_T2_STAGE;          // raw-sample staging depth (k-steps of cp.async in flight per converter)
@@ -69,11 +69,19 @@ constexpr uint32_t kT2Idesc = (1u << 4) | ((uint32_t)(kT2N >> 3) << 17) | ((uint
 // from the caller's dense bank with these and only then selects the static epilogue.
 // Bins are relative to kmin; segment s = bins (edge[s], edge[s+1]], the last one ends at bin 127.
 // ------------------------------------------------------------------------------------------
+#ifndef SPB_T2_PARTS
+#define SPB_T2_PARTS 2
+#endif
+// warps per TMEM lane quadrant in the static epilogue (each walks a run of segments).  Measured on B200
+// (10.8 audio-h): 2 parts 0.898 ms; 3 parts (21 warps, 80 registers per thread) 0.964 ms.
+constexpr int kT2Parts = SPB_T2_PARTS;
+static_assert(kT2Parts == 2 || kT2Parts == 3, "features_tc2: static epilogue parts");
 struct T2Static {
-  int M, kmin, nb, s1;
-  int lo[2], hi[2];        // bins each half walks
-  int out_lo[2], nout[2];  // filters each half emits
-  uint32_t endmask[2][4];  // bit b: bin b closes a segment of this half
+  int M, kmin, nb;
+  int sp[kT2Parts + 1];          // part p walks segments sp[p] .. sp[p+1] and emits filters sp[p] .. sp[p+1]-1
+  int lo[kT2Parts], hi[kT2Parts];        // bins each part walks
+  int out_lo[kT2Parts], nout[kT2Parts];  // filters each part emits
+  uint32_t endmask[kT2Parts][4];  // bit b: bin b closes a segment of this part
 };
 
 constexpr T2Static make_t2_static() {
@@ -83,26 +91,25 @@ constexpr T2Static make_t2_static() {
   t.M = 40;
   t.kmin = 5;
   t.nb = 123;
-  t.s1 = 26;  // filters 0..25 | 26..39: balances bins x 7 + flushes x 11 instructions (654 | 690)
+  // balance of bins x 7 + flushes x 11 + TMEM loads x 12 instructions per warp: two parts 0..25 | 26..39
+  // (702 | 750), three parts 0..19 | 20..31 | 32..39 (498 | 506 | 511)
+  if (kT2Parts == 2) {
+    t.sp[0] = 0; t.sp[1] = 26; t.sp[kT2Parts] = 40;
+  } else {
+    t.sp[0] = 0; t.sp[1] = 20; t.sp[kT2Parts - 1] = 32; t.sp[kT2Parts] = 40;
+  }
   int first[41] = {}, last[41] = {};
   for (int s = 0; s <= 40; ++s) {
     first[s] = edges[s] + 1 - t.kmin;
     last[s] = (edges[s + 1] < 127 ? edges[s + 1] : 127) - t.kmin;
   }
-  t.lo[0] = 0;
-  t.hi[0] = last[t.s1];
-  t.lo[1] = first[t.s1];
-  t.hi[1] = t.nb - 1;
-  t.out_lo[0] = 0;
-  t.nout[0] = t.s1;
-  t.out_lo[1] = t.s1;
-  t.nout[1] = t.M - t.s1;
-  for (int h = 0; h < 2; ++h)
-    for (int i = 0; i < 4; ++i) t.endmask[h][i] = 0;
-  for (int s = 0; s <= 40; ++s) {
-    const int b = last[s];
-    if (s <= t.s1) t.endmask[0][b >> 5] |= 1u << (b & 31);
-    if (s >= t.s1) t.endmask[1][b >> 5] |= 1u << (b & 31);
+  for (int p = 0; p < kT2Parts; ++p) {
+    t.lo[p] = (p == 0) ? 0 : first[t.sp[p]];
+    t.hi[p] = (p == kT2Parts - 1) ? t.nb - 1 : last[t.sp[p + 1]];
+    t.out_lo[p] = t.sp[p];
+    t.nout[p] = t.sp[p + 1] - t.sp[p];
+    for (int i = 0; i < 4; ++i) t.endmask[p][i] = 0;
+    for (int s = t.sp[p]; s <= t.sp[p + 1]; ++s) t.endmask[p][last[s] >> 5] |= 1u << (last[s] & 31);
   }
   return t;
 }
@@ -394,7 +401,7 @@ __device__ __forceinline__ void t2_epilogue_static(const T2Params &p, const uint
     if (ch * 16 + 15 < LO || ch * 16 > HI) continue;
     uint32_t vr[16], vi[16];
     tmem_ld16x2(taddr + ch * 16, taddr + kT2N + ch * 16, vr, vi);
-    const float4 *tb = &c_tc.tab[HALF][ch * 16];
+    const float4 *tb = &c_tc.tab[0][ch * 16];  // the static variant's table is not masked per part
     float pw[16];
 #pragma unroll
     for (int j = 0; j < 16; j += 2) {
@@ -438,19 +445,30 @@ __device__ __forceinline__ void t2_epilogue_static(const T2Params &p, const uint
 
 
 // ------------------------------------------------------------------------------------------
-// The kernel.  One persistent CTA per SM, 17 warps:
+// The kernel.  One persistent CTA per SM, 17 warps (21 with the static epilogue: three warps per quadrant):
 //   warps 0..7   epilogue (quadrant = warp % 4 owns hop rows 32q..32q+31 = group q of the tile,
-//                half = warp / 4 owns a range of filters)
-//   warp  8      MMA issuer (one elected thread): per k-step s_lo.C_hi, s_hi.C_lo -> real columns,
+//   (0..11)      part = warp / 4 owns a range of filters)
+//   warp  8 (12) MMA issuer (one elected thread): per k-step s_lo.C_hi, s_hi.C_lo -> real columns,
 //                d_lo.S_hi, d_hi.S_lo -> imaginary columns; then per k-step s_hi.C_hi, d_hi.S_hi and
 //                a tcgen05.commit that hands the ring slot back; M128 N128 K16 kind::f16
-//   warps 9..16  converters: lane = (k-chunk, row of 8, 8-byte half) so that a half-warp's
+//   the next 8   converters: lane = (k-chunk, row of 8, 8-byte half) so that a half-warp's
 //                st.shared.v2 covers 128 contiguous bytes of the no-swizzle K-major operand
 //                (conflict-free); 128-bit sample loads one k-step ahead + L2 bulk prefetch two
 //                tiles ahead
 // ------------------------------------------------------------------------------------------
+// warps of a CTA: 4 x parts epilogue warps, the MMA warp, 8 converter warps
+#ifndef SPB_T2_CVT3
+#define SPB_T2_CVT3 4
+#endif
+__host__ __device__ constexpr int t2_epi_warps(const int epi) { return 4 * (epi == 2 ? kT2Parts : 2); }
+// converter warps: 8 (two hop rows per thread), or SPB_T2_CVT3 beside a three-part static epilogue
+__host__ __device__ constexpr int t2_cvt_warps(const int epi) { return (epi == 2 && kT2Parts == 3) ? SPB_T2_CVT3 : kTcCvtWarps; }
+__host__ __device__ constexpr int t2_threads(const int epi) { return (t2_epi_warps(epi) + 1 + t2_cvt_warps(epi)) * 32; }
+
 template <int KM, int EPI, bool SUMS>
-__global__ void __launch_bounds__(kTcThreads, 1) features_tc2_kernel(const T2Params p) {
+__global__ void __launch_bounds__(t2_threads(EPI), 1) features_tc2_kernel(const T2Params p) {
+  constexpr int kEpiW = t2_epi_warps(EPI), kMmaW = kEpiW, kCvt0 = kEpiW + 1, kCvtW = t2_cvt_warps(EPI);
+  constexpr int kThreads = t2_threads(EPI);
   extern __shared__ __align__(128) unsigned char tc_smem[];
   unsigned char *base = tc_smem;
   uint64_t *bars = reinterpret_cast<uint64_t *>(base + kT2OffBars);
@@ -469,16 +487,16 @@ __global__ void __launch_bounds__(kTcThreads, 1) features_tc2_kernel(const T2Par
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < kT2Slots; ++s) {
-      mbar_init(&full[s], kTcCvtWarps);
+      mbar_init(&full[s], kCvtW);
       mbar_init(&empty[s], 1);
     }
     for (int a = 0; a < 2; ++a) {
       mbar_init(&acc_full[a], 1);
-      mbar_init(&acc_empty[a], kTcEpiWarps);
+      mbar_init(&acc_empty[a], kEpiW);
     }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
-  if (warp == kTcMmaWarp) {
+  if (warp == kMmaW) {
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)),
                  "r"(512u)
                  : "memory");
@@ -487,7 +505,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) features_tc2_kernel(const T2Par
   {  // resident DFT matrices
     const uint4 *g = reinterpret_cast<const uint4 *>(p.w);
     uint4 *s = reinterpret_cast<uint4 *>(base);
-    for (uint32_t i = threadIdx.x; i < 4 * kT2BMat / 16; i += kTcThreads) s[i] = __ldg(g + i);
+    for (uint32_t i = threadIdx.x; i < 4 * kT2BMat / 16; i += kThreads) s[i] = __ldg(g + i);
     fence_async_smem();
   }
   tc_fence_before();
@@ -495,15 +513,19 @@ __global__ void __launch_bounds__(kTcThreads, 1) features_tc2_kernel(const T2Par
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
-  if (warp >= kTcCvtWarp0) {
+  if (warp >= kCvt0) {
     // ===== converters =====
-    const int cw = warp - kTcCvtWarp0;
+    // lane = (k-chunk, row of 8, 8-byte half): a half-warp's st.shared.v2 covers 128 contiguous bytes of the
+    // operand; a thread feeds RPT hop rows (r0 + 8 CW j)
+    constexpr int CW = kCvtW, RPT = kTcRows / (CW * 8), NLD = 2 * RPT;
+    constexpr uint32_t kPlane = CW * 32 * 16;      // one 16-byte load of every converter thread
+    static_assert(NLD * kPlane == kT2StageBytes, "features_tc2: staging layout");
+    const int cw = warp - kCvt0;
     const int kc = lane >> 4, r8 = (lane >> 1) & 7, hf = lane & 1;
     const int qq = 2 * kc + hf;                    // which 4 of the 16 m values of a k-step
-    const int rA = cw * 8 + r8, rB = rA + 64;      // the two hop rows this thread feeds
-    const uint32_t dA = (uint32_t)(kc * (kTcRows * 16) + rA * 16 + hf * 8);
-    const uint32_t dB = dA + 64 * 16;
-    const int c = (warp - kTcCvtWarp0) * 32 + lane;
+    const int r0 = cw * 8 + r8;
+    const uint32_t d0 = (uint32_t)(kc * (kTcRows * 16) + r0 * 16 + hf * 8);
+    const int c = cw * 32 + lane;
     auto row_ptr = [&](long long t, int r) -> const float * {
       if (t >= p.num_tiles) return p.zeros;
       const TcGroup g = p.groups[t * 4 + (r >> 5)];
@@ -513,31 +535,37 @@ __global__ void __launch_bounds__(kTcThreads, 1) features_tc2_kernel(const T2Par
     // forward samples of k-step s: x[80 + 16 s + 4 qq ..], mirrored: x[76 - 16 s - 4 qq ..]
     const int foff = kT2K + 4 * qq, boff = kT2K - 4 - 4 * qq;
     // Raw samples reach the converter through cp.async (LDGSTS) into a private staging area: kT2Stage
-    // k-steps (4 x 16 B each) per thread are in flight at any time without holding registers -- with
+    // k-steps (2 RPT x 16 B each) per thread are in flight at any time without holding registers -- with
     // plain loads one k-step ahead the converters sat on the load latency (ncu r02l: long_scoreboard
-    // 6.5 warps per issue).  stage[d][j][c]: 16 B per converter thread, a warp covers 512 contiguous
+    // 6.5 warps per issue).  stage[d][load][c]: 16 B per converter thread, a warp covers 512 contiguous
     // bytes on the way in and on the way out; a thread reads back only what it copied itself, so
     // cp.async.wait_group is all the synchronisation there is.
     const uint32_t stg = sbase + kT2OffStage + (uint32_t)c * 16u;
-    auto stage_issue = [&](const uint32_t d, const float *qa, const float *qb, const int st) {
+    const float *pR[RPT], *nR[RPT];
+    auto stage_issue = [&](const uint32_t d, const float *const (&q)[RPT], const int st) {
       const uint32_t a = stg + d * kT2StageBytes;
-      cp_async16(a, qa + foff + 16 * st);
-      cp_async16(a + 4096u, qa + boff - 16 * st);
-      cp_async16(a + 8192u, qb + foff + 16 * st);
-      cp_async16(a + 12288u, qb + boff - 16 * st);
+#pragma unroll
+      for (int j = 0; j < RPT; ++j) {
+        cp_async16(a + (2 * j) * kPlane, q[j] + foff + 16 * st);
+        cp_async16(a + (2 * j + 1) * kPlane, q[j] + boff - 16 * st);
+      }
       cp_async_commit();
     };
     long long t = blockIdx.x;
-    const float *pA = row_ptr(t, rA), *pB = row_ptr(t, rB);
 #pragma unroll
-    for (int d = 0; d < kT2Stage; ++d) stage_issue((uint32_t)d, pA, pB, d);
+    for (int j = 0; j < RPT; ++j) pR[j] = row_ptr(t, r0 + j * CW * 8);
+#pragma unroll
+    for (int d = 0; d < kT2Stage; ++d) stage_issue((uint32_t)d, pR, d);
     uint32_t it = 0, slot = 0, par = 1;  // tiles produced so far, ring slot and its wait parity
     uint32_t sd = 0;                     // staging slot of the k-step about to be converted
     uint32_t bad = 0;
     for (; t < p.num_tiles; t += gridDim.x, ++it) {
-      const float *nA = row_ptr(t + gridDim.x, rA), *nB = row_ptr(t + gridDim.x, rB);
-      uint32_t mxA = 0u, mxB = 0u;
-      float a2 = 0.f, a0 = 0.f, aa = 0.f, b2 = 0.f, b0 = 0.f, ba = 0.f;
+#pragma unroll
+      for (int j = 0; j < RPT; ++j) nR[j] = row_ptr(t + gridDim.x, r0 + j * CW * 8);
+      uint32_t mx[RPT];
+      float q2[RPT], q0[RPT], qa[RPT];
+#pragma unroll
+      for (int j = 0; j < RPT; ++j) { mx[j] = 0u; q2[j] = 0.f; q0[j] = 0.f; qa[j] = 0.f; }
       if (c < 4) {
         // pull the samples of the tile after next into L2 with the TMA engine (one run per group)
         const long long tp = t + 2 * (long long)gridDim.x;
@@ -550,47 +578,49 @@ __global__ void __launch_bounds__(kTcThreads, 1) features_tc2_kernel(const T2Par
       for (int s = 0; s < kT2KSteps; ++s) {
         cp_async_wait<kT2Stage - 1>();  // the oldest k-step in flight has landed
         const uint32_t a = stg + sd * kT2StageBytes;
-        const float4 cfA = lds128(a), cbA = lds128(a + 4096u), cfB = lds128(a + 8192u), cbB = lds128(a + 12288u);
-        uint2 sha, sla, dha, dla, shb, slb, dhb, dlb;
-        const T2Fold va = t2_fold_split(cfA, cbA, sha, sla, dha, dla, mxA);
-        const T2Fold vb = t2_fold_split(cfB, cbB, shb, slb, dhb, dlb, mxB);
-        if (SUMS) {
-          t2_hop_sums(va, a2, a0, aa);
-          t2_hop_sums(vb, b2, b0, ba);
+        float4 cf[RPT], cb[RPT];
+#pragma unroll
+        for (int j = 0; j < RPT; ++j) {
+          cf[j] = lds128(a + (2 * j) * kPlane);
+          cb[j] = lds128(a + (2 * j + 1) * kPlane);
         }
-        // keep the conversion ahead of the wait (the compiler otherwise sinks it below)
-        asm volatile("" ::"r"(sha.x), "r"(sha.y), "r"(sla.x), "r"(sla.y), "r"(dha.x), "r"(dha.y), "r"(dla.x), "r"(dla.y));
-        asm volatile("" ::"r"(shb.x), "r"(shb.y), "r"(slb.x), "r"(slb.y), "r"(dhb.x), "r"(dhb.y), "r"(dlb.x), "r"(dlb.y));
+        uint2 sh[RPT], sl_[RPT], dh[RPT], dl[RPT];
+#pragma unroll
+        for (int j = 0; j < RPT; ++j) {
+          const T2Fold v = t2_fold_split(cf[j], cb[j], sh[j], sl_[j], dh[j], dl[j], mx[j]);
+          if (SUMS) t2_hop_sums(v, q2[j], q0[j], qa[j]);
+          // keep the conversion ahead of the wait (the compiler otherwise sinks it below)
+          asm volatile("" ::"r"(sh[j].x), "r"(sh[j].y), "r"(sl_[j].x), "r"(sl_[j].y), "r"(dh[j].x), "r"(dh[j].y),
+                       "r"(dl[j].x), "r"(dl[j].y));
+        }
         // the staged values are in registers (consumed above): refill the slot with the k-step kT2Stage ahead,
         // which lies in this tile or the next (past the last tile row_ptr hands out the zero block)
-        if (s + kT2Stage < kT2KSteps) stage_issue(sd, pA, pB, s + kT2Stage);
-        else stage_issue(sd, nA, nB, s + kT2Stage - kT2KSteps);
+        if (s + kT2Stage < kT2KSteps) stage_issue(sd, pR, s + kT2Stage);
+        else stage_issue(sd, nR, s + kT2Stage - kT2KSteps);
         sd = (sd + 1 == kT2Stage) ? 0u : sd + 1;
         if (s == kT2KSteps - 1) {
           // per-hop level for the epilogue's exactness guard (and the unsplittable-sample flag): max over
           // the four lanes of a row, written BEFORE the arrive of the tile's last k-step (the epilogue
           // reads it after acc_full, which is ordered after every full[] arrive of the tile)
-          mxA = __vmaxu2(mxA, __shfl_xor_sync(0xffffffffu, mxA, 1));
-          mxB = __vmaxu2(mxB, __shfl_xor_sync(0xffffffffu, mxB, 1));
-          mxA = __vmaxu2(mxA, __shfl_xor_sync(0xffffffffu, mxA, 16));
-          mxB = __vmaxu2(mxB, __shfl_xor_sync(0xffffffffu, mxB, 16));
-          const uint32_t ma = max(mxA & 0xffffu, mxA >> 16), mb = max(mxB & 0xffffu, mxB >> 16);
-          bad |= (ma >= 0x7c00u || mb >= 0x7c00u) ? 1u : 0u;
-          if ((lane & 17) == 0) {
-            lvl[(it & 3) * kTcRows + rA] = t2_level_of(ma);
-            lvl[(it & 3) * kTcRows + rB] = t2_level_of(mb);
+#pragma unroll
+          for (int j = 0; j < RPT; ++j) {
+            mx[j] = __vmaxu2(mx[j], __shfl_xor_sync(0xffffffffu, mx[j], 1));
+            mx[j] = __vmaxu2(mx[j], __shfl_xor_sync(0xffffffffu, mx[j], 16));
+            const uint32_t m = max(mx[j] & 0xffffu, mx[j] >> 16);
+            bad |= (m >= 0x7c00u) ? 1u : 0u;
+            if ((lane & 17) == 0) lvl[(it & 3) * kTcRows + r0 + j * CW * 8] = t2_level_of(m);
           }
         }
         t2_wait_nap(&empty[slot], par);
         unsigned char *sl = base + kT2OffA + slot * kT2SlotBytes;
-        *reinterpret_cast<uint2 *>(sl + dA) = sha;
-        *reinterpret_cast<uint2 *>(sl + kT2APart + dA) = sla;
-        *reinterpret_cast<uint2 *>(sl + 2 * kT2APart + dA) = dha;
-        *reinterpret_cast<uint2 *>(sl + 3 * kT2APart + dA) = dla;
-        *reinterpret_cast<uint2 *>(sl + dB) = shb;
-        *reinterpret_cast<uint2 *>(sl + kT2APart + dB) = slb;
-        *reinterpret_cast<uint2 *>(sl + 2 * kT2APart + dB) = dhb;
-        *reinterpret_cast<uint2 *>(sl + 3 * kT2APart + dB) = dlb;
+#pragma unroll
+        for (int j = 0; j < RPT; ++j) {
+          const uint32_t d = d0 + (uint32_t)(j * CW * 8 * 16);
+          *reinterpret_cast<uint2 *>(sl + d) = sh[j];
+          *reinterpret_cast<uint2 *>(sl + kT2APart + d) = sl_[j];
+          *reinterpret_cast<uint2 *>(sl + 2 * kT2APart + d) = dh[j];
+          *reinterpret_cast<uint2 *>(sl + 3 * kT2APart + d) = dl[j];
+        }
         fence_async_smem();
         __syncwarp();
         if (lane == 0) mbar_arrive(&full[slot]);
@@ -598,22 +628,20 @@ __global__ void __launch_bounds__(kTcThreads, 1) features_tc2_kernel(const T2Par
       }
       if (SUMS) {
         // the four lanes of a row: lane bits 0 and 4
-        a2 += __shfl_xor_sync(0xffffffffu, a2, 1); a0 += __shfl_xor_sync(0xffffffffu, a0, 1); aa += __shfl_xor_sync(0xffffffffu, aa, 1);
-        b2 += __shfl_xor_sync(0xffffffffu, b2, 1); b0 += __shfl_xor_sync(0xffffffffu, b0, 1); ba += __shfl_xor_sync(0xffffffffu, ba, 1);
-        a2 += __shfl_xor_sync(0xffffffffu, a2, 16); a0 += __shfl_xor_sync(0xffffffffu, a0, 16); aa += __shfl_xor_sync(0xffffffffu, aa, 16);
-        b2 += __shfl_xor_sync(0xffffffffu, b2, 16); b0 += __shfl_xor_sync(0xffffffffu, b0, 16); ba += __shfl_xor_sync(0xffffffffu, ba, 16);
-        if ((lane & 17) == 0) {
-          constexpr float u1 = 1.0f / kT2InScale, u2 = 0.5f / (kT2InScale * kT2InScale);
-          p.hopsum[t * kTcRows + rA] = make_float4(a2 * u2, a0 * u1, aa * u1, 0.f);
-          p.hopsum[t * kTcRows + rB] = make_float4(b2 * u2, b0 * u1, ba * u1, 0.f);
+        constexpr float u1 = 1.0f / kT2InScale, u2 = 0.5f / (kT2InScale * kT2InScale);
+#pragma unroll
+        for (int j = 0; j < RPT; ++j) {
+          q2[j] += __shfl_xor_sync(0xffffffffu, q2[j], 1); q0[j] += __shfl_xor_sync(0xffffffffu, q0[j], 1); qa[j] += __shfl_xor_sync(0xffffffffu, qa[j], 1);
+          q2[j] += __shfl_xor_sync(0xffffffffu, q2[j], 16); q0[j] += __shfl_xor_sync(0xffffffffu, q0[j], 16); qa[j] += __shfl_xor_sync(0xffffffffu, qa[j], 16);
+          if ((lane & 17) == 0) p.hopsum[t * kTcRows + r0 + j * CW * 8] = make_float4(q2[j] * u2, q0[j] * u1, qa[j] * u1, 0.f);
         }
       }
-      pA = nA;
-      pB = nB;
+#pragma unroll
+      for (int j = 0; j < RPT; ++j) pR[j] = nR[j];
     }
     cp_async_wait<0>();  // nothing may still be landing in shared memory when the CTA retires
     if (bad) *p.flag = 1;
-  } else if (warp == kTcMmaWarp) {
+  } else if (warp == kMmaW) {
     // ===== MMA issuer =====
     if (elect_one()) {
       const uint32_t w_chi = sbase, w_clo = sbase + kT2BMat, w_shi = sbase + 2 * kT2BMat, w_slo = sbase + 3 * kT2BMat;
@@ -674,7 +702,8 @@ __global__ void __launch_bounds__(kTcThreads, 1) features_tc2_kernel(const T2Par
       const long long row = g.row0 + lane;
       if (EPI == 2) {
         if (half == 0) t2_epilogue_static<0>(p, taddr, p.out + row * M, row_ok, thr, soff, row * M);
-        else t2_epilogue_static<1>(p, taddr, p.out + row * M, row_ok, thr, soff, row * M);
+        else if (half == 1) t2_epilogue_static<1>(p, taddr, p.out + row * M, row_ok, thr, soff, row * M);
+        else t2_epilogue_static<kT2Parts - 1>(p, taddr, p.out + row * M, row_ok, thr, soff, row * M);
       } else {
         if (half == 0) t2_epilogue_dyn<KM, EPI, 0>(p, taddr, p.out + row * M, row_ok, thr, soff, row * M);
         else t2_epilogue_dyn<KM, EPI, 1>(p, taddr, p.out + row * M + p.half[1].out_lo, row_ok, thr, soff,
@@ -687,7 +716,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) features_tc2_kernel(const T2Par
   }
   tc_fence_before();
   __syncthreads();
-  if (warp == kTcMmaWarp) {
+  if (warp == kMmaW) {
     tc_fence_after();
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512u) : "memory");
   }

@@ -610,16 +610,23 @@ int build_tc_plan(spb_context *ctx, spb_plan *pl, const float4 *seg_rd) {
   // the flagged-filter bit set of the epilogue holds 31 filters per half
   const int n0 = best_s1 > 0 ? best_s1 : M, n1 = best_s1 > 0 ? M - best_s1 : 0;
   pl->tc2_ok = n0 <= 31 && n1 <= 31;
-  // the speechpy default bank takes the compile-time epilogue: its own split, tables verified here
+  // the speechpy default bank takes the compile-time epilogue: its own split (kT2Parts parts), checked here
+  // against the segments derived from the caller's dense bank; its table is the unmasked one
   pl->tc2_static = false;
   {
     const T2Static &st = kT2StaticHost;
     if (M == st.M && kmin == st.kmin && nb == st.nb) {
+      bool same = true;
+      for (int pt = 0; pt < kT2Parts && same; ++pt) {
+        const int lo = (pt == 0) ? 0 : seg_first[st.sp[pt]];
+        const int hi = (pt == kT2Parts - 1) ? nb - 1 : seg_last[st.sp[pt + 1]];
+        uint32_t em[4] = {0, 0, 0, 0};
+        for (int sg = st.sp[pt]; sg <= st.sp[pt + 1]; ++sg) em[seg_last[sg] >> 5] |= 1u << (seg_last[sg] & 31);
+        same = lo == st.lo[pt] && hi == st.hi[pt] && st.out_lo[pt] == st.sp[pt] && st.nout[pt] == st.sp[pt + 1] - st.sp[pt];
+        for (int i = 0; i < 4; ++i) same = same && em[i] == st.endmask[pt][i];
+      }
       int lo_s[2], hi_s[2];
-      fill_tables(st.s1, pl->h_tc_tab_s, pl->tc_endmask_s, pl->tc_half_s, lo_s, hi_s);
-      bool same = lo_s[0] == st.lo[0] && hi_s[0] == st.hi[0] && lo_s[1] == st.lo[1] && hi_s[1] == st.hi[1];
-      for (int hf = 0; hf < 2; ++hf)
-        for (int i = 0; i < 4; ++i) same = same && pl->tc_endmask_s[hf][i] == st.endmask[hf][i];
+      fill_tables(0, pl->h_tc_tab_s, pl->tc_endmask_s, pl->tc_half_s, lo_s, hi_s);  // s1 = 0: half 0 spans every bin
       pl->tc2_static = same;
     }
   }
@@ -751,13 +758,14 @@ static int launch_features_tc2(spb_context *ctx, const FeatArgs &a) {
   else if (km5) kern = sums ? features_tc2_kernel<5, 0, true> : features_tc2_kernel<5, 0, false>;
   else kern = sums ? features_tc2_kernel<-1, 0, true> : features_tc2_kernel<-1, 0, false>;
   int per_sm = 0;
-  int rc = configure_kernel(ctx, (const void *)kern, kTcThreads, kT2Smem, &per_sm);
+  const int threads = t2_threads(epi);
+  int rc = configure_kernel(ctx, (const void *)kern, threads, kT2Smem, &per_sm);
   if (rc) return rc;
   if (per_sm < 1) return fail(ctx, SPB_ERR_INVALID, "features_tc2: kernel does not fit on an SM");
   long long grid = ctx->sm_count;
   if (grid > p.num_tiles) grid = p.num_tiles;
   if (grid < 1) return SPB_OK;
-  kern<<<(unsigned)grid, kTcThreads, kT2Smem, ctx->stream>>>(p);
+  kern<<<(unsigned)grid, threads, kT2Smem, ctx->stream>>>(p);
   SPB_LAUNCH_CHECK(ctx, "features_tc2");
   SPB_CUDA(ctx, cudaEventRecord(own.last_use, ctx->stream));
   return SPB_OK;
