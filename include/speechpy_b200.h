@@ -118,9 +118,9 @@ SPB_API int spb_stack_frames(spb_context *ctx, const double *sig, int64_t num_sa
  * mode 0: |X|^2/nfft   mode 1: |X|
  * mode 2: log_power_spectrum(normalize=False) = 10 log10(max(P, 1e-20)) (processing.py:177-198)
  * mode 3: the same minus its global maximum (normalize=True).
- * nfft must be a power of two in [32, 4096] (SPB_ERR_UNSUPPORTED otherwise).
- * Deviation from the reference: the transform runs in float32 on the device (frames are narrowed
- * after upload, the result widened to float64); |error| <= 1e-5 of the row maximum. */
+ * Any nfft >= 1 (numpy's rfft(n=) takes them all): powers of two in [32, 4096] run the FFT kernels --
+ * deviation from the reference: in float32 on the device (frames are narrowed after upload, the result
+ * widened to float64), |error| <= 1e-5 of the row maximum; every other size runs a direct DFT in float64. */
 SPB_API int spb_power_spectrum(spb_context *ctx, const double *frames, int64_t num_frames,
                        int32_t frame_len, int32_t nfft, int32_t mode, double *out);
 

@@ -637,6 +637,10 @@ int spb_batch_create(spb_context *ctx, const spb_plan *plan, const int64_t *star
     }
     b->chunk_span_total += c.s_hi - c.s_lo;
   }
+  b->chunk_spans_disjoint = true;
+  for (size_t k = 1; k < ch.chunks.size(); ++k)
+    for (size_t j = 0; j < k && b->chunk_spans_disjoint; ++j)
+      if (ch.chunks[k].s_lo < ch.chunks[j].s_hi && ch.chunks[j].s_lo < ch.chunks[k].s_hi) b->chunk_spans_disjoint = false;
   b->total_cm_tiles = cm_off[U];
   // large-tile cmvnw table: balanced tiles per utterance, longest first inside each chunk
   std::vector<int4> big;
@@ -1137,11 +1141,23 @@ int spb_power_spectrum(spb_context *ctx, const double *frames, int64_t F, int32_
   SPB_REQUIRE(ctx, ctx != nullptr, "spb_power_spectrum: NULL context");
   SPB_REQUIRE(ctx, F >= 0 && L >= 1, "spb_power_spectrum: bad shape");
   SPB_REQUIRE(ctx, mode >= 0 && mode <= 3, "spb_power_spectrum: mode must be 0..3");
-  if (!(is_pow2(nfft) && nfft >= 32 && nfft <= 4096))
-    return fail(ctx, SPB_ERR_UNSUPPORTED, "fft_points must be a power of two in [32, 4096]");
+  SPB_REQUIRE(ctx, nfft >= 1, "spb_power_spectrum: fft_points must be positive");
   if (F == 0) return SPB_OK;
   SPB_REQUIRE(ctx, frames && out, "spb_power_spectrum: NULL buffer");
   SPB_CUDA(ctx, cudaSetDevice(ctx->device));
+  if (!(is_pow2(nfft) && nfft >= 32 && nfft <= 4096)) {
+    // any other size (numpy's rfft(n=) takes them all): direct DFT in float64 on the device
+    const int K = nfft / 2 + 1;
+    double *d_fr = (double *)scratch(ctx, 5, (size_t)F * L * 8);
+    double *d_o = (double *)scratch(ctx, 4, (size_t)F * K * 8 + 256);
+    if (!d_fr || !d_o) return SPB_ERR_CUDA;
+    SPB_CUDA(ctx, cudaMemcpyAsync(d_fr, frames, (size_t)F * L * 8, cudaMemcpyHostToDevice, ctx->stream));
+    int rc = launch_spectrum_dft(ctx, d_fr, F, L, nfft, mode, d_o, (double *)((char *)d_o + (size_t)F * K * 8));
+    if (rc) return rc;
+    SPB_CUDA(ctx, cudaMemcpyAsync(out, d_o, (size_t)F * K * 8, cudaMemcpyDeviceToHost, ctx->stream));
+    SPB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return SPB_OK;
+  }
   // (F, L) row-major frames == one signal of F*L samples framed with length L, stride L
   spb_feature_params q{};
   q.frame_len = L;
@@ -1376,8 +1392,28 @@ int spb_mfcc_delta_batch_dev(spb_context *ctx, const spb_batch *b, const float *
 // `samples` may be float32, int16 PCM, int32 or float64; x = float(sample) * scale on the
 // device: scale 1 is signal.astype(float) (feature.py:182), int16 with scale 1/32768 is the
 // float32 array librosa.load (utils.py:170-173 load_wav) decodes from a PCM16 file.
+static int host_batch_run(spb_context *ctx, const spb_batch *b, const void *samples, int dtype,
+                          double scale_d, int64_t arena_len, float *out, int which);
+
+// On an error in the middle of the pipeline, copies into the caller's `out` (and from `samples`) may still
+// be in flight on the copy streams: drain all three before the call returns, so that the caller's buffers
+// and the context's scratch / events are quiescent whatever the outcome.
 static int host_batch(spb_context *ctx, const spb_batch *b, const void *samples, int dtype,
                       double scale_d, int64_t arena_len, float *out, int which) {
+  const int rc = host_batch_run(ctx, b, samples, dtype, scale_d, arena_len, out, which);
+  if (rc != SPB_OK && ctx != nullptr && ctx->stream != nullptr) {
+    const std::string msg = ctx->last_error;  // keep the first error's message
+    cudaStreamSynchronize(ctx->copy_stream);
+    cudaStreamSynchronize(ctx->stream);
+    cudaStreamSynchronize(ctx->out_stream);
+    cudaGetLastError();
+    ctx->last_error = msg;
+  }
+  return rc;
+}
+
+static int host_batch_run(spb_context *ctx, const spb_batch *b, const void *samples, int dtype,
+                          double scale_d, int64_t arena_len, float *out, int which) {
   const float scale = (float)scale_d;
   SPB_REQUIRE(ctx, scale_d == scale_d && scale != 0.f, "batch call: sample_scale must be a non-zero number");
   int rc = check_batch(ctx, b, arena_len, samples, out);
@@ -1401,8 +1437,9 @@ static int host_batch(spb_context *ctx, const spb_batch *b, const void *samples,
   }
   const size_t nch = b->chunks.size();
   const bool ingest = dtype != SPB_F32 || scale != 1.0f;  // float32 with scale 1 is used as uploaded
-  // chunk spans overlap when utterances are not packed in order: then copy the arena once
-  const bool piecewise = b->chunk_span_total <= arena_len + arena_len / 4;
+  // piecewise upload only when the chunks' sample spans are disjoint (utterances packed in order): a span that
+  // overlaps its neighbour's would be rewritten by the next chunk's H2D while this chunk's kernels read it
+  const bool piecewise = b->chunk_spans_disjoint;
   while (ctx->pipe_events.size() < 2 * nch + 1) {
     cudaEvent_t e;
     SPB_CUDA(ctx, cudaEventCreateWithFlags(&e, cudaEventDisableTiming));

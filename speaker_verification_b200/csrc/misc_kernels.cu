@@ -1,5 +1,7 @@
 // Small element-wise kernels: float64 frame gather (stack_frames), the reference's
 // "derivative" operator and delta cube, dtype conversion, tile-table construction.
+#include <algorithm>
+
 #include "spb_internal.cuh"
 
 namespace spb {
@@ -315,6 +317,91 @@ int launch_build_fft_tiles(spb_context *ctx, const int32_t *nframes, const int64
   build_fft_tiles_kernel<<<blocks, 256, 0, ctx->stream>>>(nframes, tile_offsets, starts, frame_offsets, U, tile,
                                                           stride, tiles);
   SPB_LAUNCH_CHECK(ctx, "build_fft_tiles_kernel");
+  return SPB_OK;
+}
+
+// ------------------------------------------------------------------------------------
+// power / magnitude / log-power spectrum for ANY fft_points (numpy's rfft(n=) takes any n): direct DFT
+// in float64 (processing.py:142-198).  Used for the sizes the FFT kernels do not cover (not a power of
+// two, or outside [32, 4096]); one CTA per frame, twiddles e^{-2 pi i r / n} in shared memory,
+// a thread per bin.  O(n^2) per frame: the rare case, not a hot path.
+//   mode 0: |X|^2 / n   1: |X|   2, 3: 10 log10(max(|X|^2 / n, 1e-20)) (3: the caller subtracts the maximum)
+// ------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+spectrum_dft_kernel(const double *__restrict__ frames, long long F, int L, int nfft, int mode, double *__restrict__ out) {
+  extern __shared__ __align__(16) unsigned char dft_smem[];
+  double2 *tw = reinterpret_cast<double2 *>(dft_smem);  // [nfft]
+  double *x = reinterpret_cast<double *>(tw + nfft);     // [Leff]
+  const int Leff = min(L, nfft);                          // rows longer than n are truncated, shorter ones zero-padded
+  const int K = nfft / 2 + 1;
+  for (int r = threadIdx.x; r < nfft; r += blockDim.x) {
+    double sn, cs;
+    sincospi(2.0 * (double)r / (double)nfft, &sn, &cs);
+    tw[r] = make_double2(cs, -sn);
+  }
+  for (long long f = blockIdx.x; f < F; f += gridDim.x) {
+    __syncthreads();
+    for (int n = threadIdx.x; n < Leff; n += blockDim.x) x[n] = frames[f * L + n];
+    __syncthreads();
+    for (int k = threadIdx.x; k < K; k += blockDim.x) {
+      double re = 0.0, im = 0.0;
+      int r = 0;
+      for (int n = 0; n < Leff; ++n) {
+        const double2 w = tw[r];
+        re = fma(x[n], w.x, re);
+        im = fma(x[n], w.y, im);
+        r += k;
+        if (r >= nfft) r -= nfft;
+      }
+      const double p2 = re * re + im * im;
+      double v;
+      if (mode == 1) v = sqrt(p2);
+      else {
+        v = p2 / (double)nfft;
+        if (mode >= 2) v = 10.0 * log10(fmax(v, 1e-20));
+      }
+      out[f * K + k] = v;
+    }
+  }
+}
+
+__global__ void __launch_bounds__(256) subtract_max_f64_kernel(double *__restrict__ v, long long n, const double *__restrict__ mx) {
+  const double m = *mx;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) v[i] -= m;
+}
+__global__ void __launch_bounds__(256) max_f64_kernel(const double *__restrict__ v, long long n, double *__restrict__ mx) {
+  // single CTA: the spectra this path sees are small
+  __shared__ double sm[256];
+  double m = -INFINITY;
+  for (long long i = threadIdx.x; i < n; i += blockDim.x) m = fmax(m, v[i]);
+  sm[threadIdx.x] = m;
+  __syncthreads();
+  for (int o = 128; o >= 1; o >>= 1) {
+    if ((int)threadIdx.x < o) sm[threadIdx.x] = fmax(sm[threadIdx.x], sm[threadIdx.x + o]);
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) *mx = sm[0];
+}
+
+// d_frames (F, L) float64 on the device -> d_out (F, nfft/2+1) float64 on the device; d_tmp: 8 bytes
+int launch_spectrum_dft(spb_context *ctx, const double *d_frames, int64_t F, int L, int nfft, int mode, double *d_out,
+                        double *d_tmp) {
+  if (F <= 0) return SPB_OK;
+  const size_t smem = (size_t)nfft * 16 + (size_t)std::min(L, nfft) * 8;
+  if (smem > 200 * 1024) return fail(ctx, SPB_ERR_UNSUPPORTED, "fft_points too large for the direct-DFT spectrum kernel");
+  int per_sm = 0;
+  int rc = configure_kernel(ctx, (const void *)spectrum_dft_kernel, 256, smem, &per_sm);
+  if (rc) return rc;
+  const long long grid = std::min<long long>(F, (long long)ctx->sm_count * std::max(per_sm, 1));
+  spectrum_dft_kernel<<<(unsigned)grid, 256, smem, ctx->stream>>>(d_frames, F, L, nfft, mode, d_out);
+  SPB_LAUNCH_CHECK(ctx, "spectrum_dft_kernel");
+  if (mode == 3) {
+    const long long n = (long long)F * (nfft / 2 + 1);
+    max_f64_kernel<<<1, 256, 0, ctx->stream>>>(d_out, n, d_tmp);
+    SPB_LAUNCH_CHECK(ctx, "max_f64_kernel");
+    subtract_max_f64_kernel<<<(unsigned)std::min<long long>((n + 255) / 256, 1024), 256, 0, ctx->stream>>>(d_out, n, d_tmp);
+    SPB_LAUNCH_CHECK(ctx, "subtract_max_f64_kernel");
+  }
   return SPB_OK;
 }
 

@@ -191,6 +191,7 @@ struct spb_batch {
   std::vector<spb::BatchChunk> groups;   // launch units of the device-pointer calls (runs of chunks)
   int64_t max_group_rows = 0;
   int64_t max_chunk_rows = 0;
+  bool chunk_spans_disjoint = true;  // no two chunks' sample spans overlap: the host path may upload chunk by chunk
   int64_t chunk_span_total = 0;  // sum of the chunks' sample spans (== arena use when utterances are packed in order)
 };
 
@@ -308,6 +309,8 @@ int launch_derivative_f64(spb_context *ctx, const double *in, int64_t rows, int 
                           double *out);
 int launch_delta_cube_f64(spb_context *ctx, const double *in, int64_t rows, int cols,
                           double *out);
+int launch_spectrum_dft(spb_context *ctx, const double *d_frames, int64_t F, int L, int nfft, int mode, double *d_out,
+                        double *d_tmp);
 int launch_convert(spb_context *ctx, const void *in, int dtype_in, void *out, int dtype_out,
                    int64_t n);
 int launch_preemphasis(spb_context *ctx, const void *in, int dtype, long long n, long long shift, double cof,

@@ -69,8 +69,18 @@ def test_power_spectrum(sp):
             assert np.max(np.abs(p - r)) <= 3e-6 * np.max(r), (nfft, L)
     lp = sp.processing.log_power_spectrum(fr, 512, True)
     assert maxabs(lp[[0, 297]], g["logpower_norm_rows"]) < 1e-3
-    with pytest.raises(NotImplementedError):
-        sp.processing.power_spectrum(fr, 500)
+    # any other fft_points (numpy's rfft(n=) takes them all): direct DFT in float64 on the device
+    for nfft, L in ((500, 320), (400, 400), (300, 320), (16, 320), (8192, 320), (1, 50), (7, 5), (6000, 100)):
+        fr2 = np.ascontiguousarray(fr[:23, :L]) if L <= 320 else np.ascontiguousarray(np.tile(fr[:23], (1, 2))[:, :L])
+        for fn, ofn in ((sp.processing.power_spectrum, o.power_spectrum), (sp.processing.fft_spectrum, o.fft_spectrum)):
+            r = ofn(fr2, nfft)
+            p = fn(fr2, nfft)
+            assert p.shape == r.shape and p.dtype == np.float64
+            assert np.max(np.abs(p - r)) <= 1e-11 * max(np.max(np.abs(r)), 1e-300), (nfft, L)
+        lp = sp.processing.log_power_spectrum(fr2, nfft, True)
+        ref_p = o.power_spectrum(fr2, nfft)
+        ref_lp = 10 * np.log10(np.maximum(ref_p, 1e-20))
+        assert np.max(np.abs(lp - (ref_lp - ref_lp.max()))) < 1e-9, (nfft, L)
 
 
 def test_preemphasis_and_log_power_spectrum_on_device(sp):
