@@ -258,7 +258,7 @@ SPB_API int spb_feature_cubes_batch(spb_context *ctx, const spb_batch *batch, co
 /* ------------------------------------------------------- a10  cosine scores
  * evaluation.py:76-77 over all (enrolment, test) pairs at once:
  * S[i, j] = <E_i, T_j> / (|E_i| |T_j|); zero-norm rows give 0 (sklearn).
- * E (m, d), T (n, d), S (m, n) row-major float32; d must be a multiple of 32.
+ * E (m, d), T (n, d), S (m, n) row-major float32; any d >= 1 (padded with zeros to a multiple of 16).
  * Tensor-core path: tcgen05 kind::tf32, 3-term split (hi*hi + hi*lo + lo*hi),
  * fp32 accumulation in TMEM. */
 SPB_API int spb_cosine_scores(spb_context *ctx, const float *E, int64_t m, const float *T,
@@ -273,7 +273,7 @@ SPB_API int spb_cosine_scores_dev(spb_context *ctx, const float *d_E, int64_t m,
  * context's grow-only scratch, and the call performs no cudaMalloc / cudaFree / allocating library
  * routine (the kernel-timing events of spb_timing_enable are not recorded for it).  Limit:
  * 2 * (pad256(m * dp) + pad256(n * dp)) * 4 bytes <= SPB_NOALLOC_SCRATCH_BYTES with dp = d rounded
- * up to a multiple of 32 and pad256 rounding up to 256 floats (e.g. m + n <= 2 048 rows at d = 512);
+ * up to a multiple of 16 and pad256 rounding up to 256 floats (e.g. m + n <= 2 048 rows at d = 512);
  * larger problems return SPB_ERR_INVALID with a message naming both sizes.  Every call on a device
  * shares the one array (each call rewrites all of it that it reads, so nothing has to be cleared):
  * calls that overlap on the GPU -- different contexts / streams of the same device -- race; calls

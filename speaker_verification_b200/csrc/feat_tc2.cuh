@@ -371,16 +371,30 @@ __device__ __forceinline__ void t2_epilogue_dyn(const T2Params &p, const uint32_
 // 16-byte (or, at the split 26 | 14, 8-byte) store.
 // prow: row base (filter 0) of this lane's output row.
 // ------------------------------------------------------------------------------------------
+// filters g0..m of a row (a run inside one group of eight, ov[e & 7] = filter e) with the widest stores
+// their alignment allows: a whole group is ONE 32-byte store = one full sector of the row (rows are
+// 160 B apart: 16-byte stores from lanes that each own a row filled every sector in two visits)
 template <int HALF>
-__device__ __forceinline__ void t2_store_run(float *prow, const float (&ov)[4], const int g0, const int m, const bool row_ok) {
-  const int count = m - g0 + 1;
+__device__ __forceinline__ void t2_store_run(float *prow, const float (&ov)[8], const int g0, const int m, const bool row_ok) {
   if (!row_ok) return;
-  if (count == 4) {
-    *reinterpret_cast<float4 *>(prow + g0) = make_float4(ov[0], ov[1], ov[2], ov[3]);
-  } else if (count == 2 && (g0 & 1) == 0) {
-    *reinterpret_cast<float2 *>(prow + g0) = make_float2(ov[g0 & 3], ov[(g0 + 1) & 3]);
-  } else {
-    for (int e = g0; e <= m; ++e) prow[e] = ov[e & 3];
+  int e = g0;
+  if (m - g0 + 1 == 8) {
+    asm volatile("st.global.v8.f32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::"l"(prow + g0), "f"(ov[0]), "f"(ov[1]),
+                 "f"(ov[2]), "f"(ov[3]), "f"(ov[4]), "f"(ov[5]), "f"(ov[6]), "f"(ov[7])
+                 : "memory");
+    return;
+  }
+  while (e <= m) {
+    if ((e & 3) == 0 && e + 3 <= m) {
+      *reinterpret_cast<float4 *>(prow + e) = make_float4(ov[e & 7], ov[(e + 1) & 7], ov[(e + 2) & 7], ov[(e + 3) & 7]);
+      e += 4;
+    } else if ((e & 1) == 0 && e + 1 <= m) {
+      *reinterpret_cast<float2 *>(prow + e) = make_float2(ov[e & 7], ov[(e + 1) & 7]);
+      e += 2;
+    } else {
+      prow[e] = ov[e & 7];
+      e += 1;
+    }
   }
 }
 
@@ -392,7 +406,7 @@ __device__ __forceinline__ void t2_epilogue_static(const T2Params &p, const uint
   constexpr int KM = kT2S.kmin & 15;
   float2 rf = make_float2(0.f, 0.f);
   float prev_u = 0.f;
-  float ov[4] = {0.f, 0.f, 0.f, 0.f};
+  float ov[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
   uint32_t fbits = 0u;
   int nfl = 0;  // flushes so far: a compile-time value once the loops below are unrolled
   const float ln_scale = p.ln_scale;
@@ -422,9 +436,9 @@ __device__ __forceinline__ void t2_epilogue_static(const T2Params &p, const uint
           const int m = OUT_LO + nfl - 1;  // filter this flush completes
           const float a = prev_u + rf.y;
           fbits |= (a < thr) ? (1u << (nfl - 1)) : 0u;
-          ov[m & 3] = t2_log_value(a, ln_scale);
-          if ((m & 3) == 3 || nfl == NOUT) {
-            const int g0 = ((m & ~3) > OUT_LO) ? (m & ~3) : OUT_LO;
+          ov[m & 7] = t2_log_value(a, ln_scale);
+          if ((m & 7) == 7 || nfl == NOUT) {
+            const int g0 = ((m & ~7) > OUT_LO) ? (m & ~7) : OUT_LO;
             t2_store_run<HALF>(prow, ov, g0, m, row_ok);
           }
         }

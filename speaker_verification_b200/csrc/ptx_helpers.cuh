@@ -35,6 +35,32 @@ __device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity) {
       "}" ::"r"(a), "r"(parity)
       : "memory");
 }
+// mbarrier wait with a watchdog: a protocol bug must end as a launch error (trap after ~4 s), not as a hung GPU
+static __device__ __noinline__ void mbar_watchdog(unsigned long long &t0) {
+  unsigned long long now;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
+  if (t0 == 0) t0 = now;
+  else if (now - t0 > 4000000000ull) __trap();
+}
+__device__ __forceinline__ void mbar_wait_guarded(uint64_t *bar, uint32_t parity) {
+  const uint32_t a = smem_u32(bar);
+  uint32_t n = 0;
+  unsigned long long t0 = 0;
+  for (;;) {
+    uint32_t ok;
+    asm volatile(
+        "{\n\t"
+        ".reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t"
+        "}"
+        : "=r"(ok)
+        : "r"(a), "r"(parity), "r"(20000u)
+        : "memory");
+    if (ok) return;
+    if ((++n & 1023u) == 0) mbar_watchdog(t0);
+  }
+}
 __device__ __forceinline__ bool elect_one() {
   uint32_t pred;
   asm volatile(

@@ -9,14 +9,15 @@
 // Cosine matrix.  S = normalize(E) . normalize(T)^T (sklearn semantics: zero rows stay zero).
 //   prologue  : one warp per row: 1/|x| in fp32, x^ = x/|x|, split x^ = hi + lo with hi rounded
 //               to TF32 (cvt.rna) and lo = tf32(x^ - hi); rows padded with zeros to a multiple
-//               of 32 columns.  hi/lo live in context scratch (4 x 10 MB at 4874 x 512).
-//   GEMM      : persistent, warp-specialised, one CTA per SM.  Per 128 x 256 output tile and
-//               32-column k-block, TMA (SWIZZLE_128B) stages A_hi, A_lo (128 x 32) and B_hi, B_lo
-//               (256 x 32) once and one elected thread issues three groups of four
-//               tcgen05.mma.kind::tf32 (M128 N256 K8): lo.hi + hi.lo + hi.hi, all accumulating
+//               of 16 columns.  hi/lo live in context scratch (4 x 10 MB at 4874 x 512).
+//   GEMM      : persistent, warp-specialised, one CTA per SM.  Per 128 x BN output tile (BN = 256,
+//               224 or 192: whichever needs the fewest waves x width) and 16-column k-block, TMA
+//               (SWIZZLE_64B) stages A_hi, A_lo (128 x 16) and B_hi, B_lo (BN x 16) in one of four
+//               stages and one elected thread issues three groups of two
+//               tcgen05.mma.kind::tf32 (M128 N BN K8): lo.hi + hi.lo + hi.hi, all accumulating
 //               in the same fp32 TMEM tile -- the 3xTF32 split the 1e-5 tolerance needs
 //               (single-pass TF32 is ~7e-4 relative on 512-d embeddings).  TMEM accumulation
-//               truncates, so a chain is cut every 4 k-blocks: chunks alternate between two
+//               truncates, so a chain is cut every 8 k-blocks (48 MMAs): chunks alternate between two
 //               TMEM accumulators (2 x 256 columns) and are summed by the epilogue warps.
 //   epilogue  : 8 warps, tcgen05.ld 32x32b.x32 of every chunk -> fp32 register accumulators
 //               (round-to-nearest adds) -> at the end of a tile padded smem transpose ->
@@ -45,6 +46,16 @@ __device__ __forceinline__ uint64_t umma_desc_sw128(const void *smem) {
   d |= (uint64_t)(1024 >> 4) << 32;
   d |= (uint64_t)1 << 46;
   d |= (uint64_t)2 << 61;
+  return d;
+}
+// the same with rows of 64 bytes, SWIZZLE_64B: SBO = 512 B between 8-row groups, layout type 4
+__device__ __forceinline__ uint64_t umma_desc_sw64(const void *smem) {
+  uint64_t d = 0;
+  d |= (uint64_t)((smem_u32(smem) & 0x3FFFF) >> 4);
+  d |= (uint64_t)1 << 16;
+  d |= (uint64_t)(512 >> 4) << 32;
+  d |= (uint64_t)1 << 46;
+  d |= (uint64_t)4 << 61;
   return d;
 }
 
@@ -85,21 +96,34 @@ normalize_split_kernel(const float *__restrict__ X, long long rows, int d, int d
 // ------------------------------------------------------------------------------------
 // cosine GEMM
 // ------------------------------------------------------------------------------------
-constexpr int kBM = 128, kBN = 256, kBK = 32;  // kBK floats == one 128-byte swizzle row
-constexpr int kStages = 2;
+// k-block = 16 floats = one 64-byte swizzle row.  Four stages of 16 columns instead of two of 32: the same
+// shared memory, but three stages (up to 144 KB) can be in flight behind the one being multiplied --
+// with two stages the MMAs of a k-block (1.7 k cycles) did not cover a TMA round trip and the tensor pipe
+// sat at 73 % (ncu r02q).
+constexpr int kBM = 128, kBK = 16;
+// Tile width BN is a template parameter (256, 224 or 192 columns): the launcher picks the one with the
+// fewest (waves x BN) -- 4 874 columns are 20 tiles of 256 = 780 tiles = 5.27 waves on 148 SMs (a sixth
+// wave with 40 busy SMs), but 22 tiles of 224 = 858 tiles = 5.8 waves of narrower tiles: 12.5 % less time.
+constexpr int kAccStride = 256;                // TMEM columns between the two accumulators
+constexpr int kStages = 4;
 constexpr int kUmmaK = 8;                      // tf32
 constexpr int kGemmThreads = 320;              // warp 0 TMA, warp 1 MMA, warps 2..9 epilogue
-constexpr int kMaxChunkKB = 4;                 // at most this many k-blocks accumulate in TMEM before a drain
-constexpr uint32_t kABytes = kBM * kBK * 4;    // 16 KB
-constexpr uint32_t kBBytes = kBN * kBK * 4;    // 32 KB
-constexpr uint32_t kStageBytes = 2 * kABytes + 2 * kBBytes;  // 96 KB
+constexpr int kMaxChunkKB = 8;                 // at most this many k-blocks (48 MMAs) accumulate in TMEM before a drain
+constexpr uint32_t kABytes = kBM * kBK * 4;    // 8 KB
 constexpr int kEpiPitch = 33;
 constexpr uint32_t kEpiBytes = 8 * 32 * kEpiPitch * 4;
-constexpr uint32_t kGemmSmem = 1024 /* alignment slack */ + kStages * kStageBytes + kEpiBytes + 128;
-// instruction descriptor: D = F32 (bits 4-5 = 1), A = B = TF32 (bits 7-9, 10-12 = 2), both
-// K-major, N >> 3 at bit 17, M >> 4 at bit 24
-constexpr uint32_t kIdesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(kBN >> 3) << 17) |
-                            ((uint32_t)(kBM >> 4) << 24);
+template <int BN>
+struct GemmGeom {
+  static_assert(BN % 32 == 0 && BN > 128 && BN <= 256, "cosine GEMM tile width");
+  static constexpr uint32_t kBBytes = BN * kBK * 4;                    // 32 KB at BN = 256
+  static constexpr uint32_t kStageBytes = 2 * kABytes + 2 * kBBytes;   // 96 KB at BN = 256
+  static constexpr uint32_t kSmem = 1024 /* alignment slack */ + kStages * kStageBytes + kEpiBytes + 128;
+  // instruction descriptor: D = F32 (bits 4-5 = 1), A = B = TF32 (bits 7-9, 10-12 = 2), both
+  // K-major, N >> 3 at bit 17, M >> 4 at bit 24
+  static constexpr uint32_t kIdesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(BN >> 3) << 17) |
+                                     ((uint32_t)(kBM >> 4) << 24);
+  static constexpr int kChunks1 = (BN - 128) / 32;  // 32-column chunks of the second column half (the first has 4)
+};
 
 struct GemmParams {
   float *S;
@@ -109,13 +133,17 @@ struct GemmParams {
   int tiles_m, tiles_n;
 };
 
+template <int BN>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 cosine_gemm_kernel(const __grid_constant__ CUtensorMap map_ehi, const __grid_constant__ CUtensorMap map_elo,
                    const __grid_constant__ CUtensorMap map_thi, const __grid_constant__ CUtensorMap map_tlo,
                    const GemmParams p) {
+  using Gm = GemmGeom<BN>;
+  constexpr uint32_t kBBytes = Gm::kBBytes, kStageBytes = Gm::kStageBytes, kIdesc = Gm::kIdesc;
+  constexpr int kBN = BN;
   extern __shared__ unsigned char smem_raw[];
   unsigned char *base = reinterpret_cast<unsigned char *>(
-      ((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);  // SWIZZLE_128B wants 1024-byte alignment
+      ((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);  // swizzled stages: 1024-byte alignment
   float *s_epi = reinterpret_cast<float *>(base + kStages * kStageBytes);
   uint64_t *bars = reinterpret_cast<uint64_t *>(base + kStages * kStageBytes + kEpiBytes);
   uint64_t *full = bars;                 // [kStages]
@@ -163,7 +191,7 @@ cosine_gemm_kernel(const __grid_constant__ CUtensorMap map_ehi, const __grid_con
       for (long long t = blockIdx.x; t < num_tiles; t += gridDim.x) {
         const int tm = (int)(t % p.tiles_m), tn = (int)(t / p.tiles_m);
         for (int kb = 0; kb < p.kblocks; ++kb) {
-          mbar_wait(&empty[stage], phase ^ 1);
+          mbar_wait_guarded(&empty[stage], phase ^ 1);
           unsigned char *st = base + stage * kStageBytes;
           mbar_expect_tx(&full[stage], kStageBytes);
           tma_load_2d(&map_ehi, &full[stage], st, kb * kBK, tm * kBM);
@@ -188,18 +216,18 @@ cosine_gemm_kernel(const __grid_constant__ CUtensorMap map_ehi, const __grid_con
         for (int kb0 = 0; kb0 < p.kblocks; kb0 += p.chunk_kb, ++cit) {
           const uint32_t acc = (uint32_t)(cit & 1);
           const uint32_t acc_phase = (uint32_t)((cit >> 1) & 1);
-          mbar_wait(&acc_empty[acc], acc_phase ^ 1);  // epilogue has drained this accumulator
+          mbar_wait_guarded(&acc_empty[acc], acc_phase ^ 1);  // epilogue has drained this accumulator
           tc_fence_after();
-          const uint32_t tmem_d = tmem_base + acc * kBN;
+          const uint32_t tmem_d = tmem_base + acc * kAccStride;
           const int kb1 = min(kb0 + p.chunk_kb, p.kblocks);
           for (int kb = kb0; kb < kb1; ++kb) {
-            mbar_wait(&full[stage], phase);
+            mbar_wait_guarded(&full[stage], phase);
             tc_fence_after();
             unsigned char *st = base + stage * kStageBytes;
-            const uint64_t a_hi = umma_desc_sw128(st);
-            const uint64_t a_lo = umma_desc_sw128(st + kABytes);
-            const uint64_t b_hi = umma_desc_sw128(st + 2 * kABytes);
-            const uint64_t b_lo = umma_desc_sw128(st + 2 * kABytes + kBBytes);
+            const uint64_t a_hi = umma_desc_sw64(st);
+            const uint64_t a_lo = umma_desc_sw64(st + kABytes);
+            const uint64_t b_hi = umma_desc_sw64(st + 2 * kABytes);
+            const uint64_t b_lo = umma_desc_sw64(st + 2 * kABytes + kBBytes);
             // small terms first: lo.hi, hi.lo, then hi.hi
 #pragma unroll
             for (int k = 0; k < kBK / kUmmaK; ++k) {
@@ -228,6 +256,7 @@ cosine_gemm_kernel(const __grid_constant__ CUtensorMap map_ehi, const __grid_con
     const int quad = warp & 3;
     const int half = (warp - 2) >> 2;
     float *my = s_epi + (warp - 2) * 32 * kEpiPitch;
+    const int nch = (half == 0) ? 4 : Gm::kChunks1;
     long long cit = 0;
     for (long long t = blockIdx.x; t < num_tiles; t += gridDim.x) {
       const int tm = (int)(t % p.tiles_m), tn = (int)(t / p.tiles_m);
@@ -237,15 +266,17 @@ cosine_gemm_kernel(const __grid_constant__ CUtensorMap map_ehi, const __grid_con
       for (int kb0 = 0; kb0 < p.kblocks; kb0 += p.chunk_kb, ++cit) {
         const uint32_t acc = (uint32_t)(cit & 1);
         const uint32_t acc_phase = (uint32_t)((cit >> 1) & 1);
-        mbar_wait(&acc_full[acc], acc_phase);
+        mbar_wait_guarded(&acc_full[acc], acc_phase);
         tc_fence_after();
-        const uint32_t taddr = tmem_base + ((uint32_t)(quad * 32) << 16) + acc * kBN + half * 128;
+        const uint32_t taddr = tmem_base + ((uint32_t)(quad * 32) << 16) + acc * kAccStride + half * 128;
 #pragma unroll
         for (int ch = 0; ch < 4; ++ch) {
-          uint32_t v[32];
-          tmem_ld32(taddr + ch * 32, v);
+          if (ch < nch) {  // warp-uniform: the second column half is narrower when BN < 256
+            uint32_t v[32];
+            tmem_ld32(taddr + ch * 32, v);
 #pragma unroll
-          for (int j = 0; j < 32; ++j) accr[ch * 32 + j] += __uint_as_float(v[j]);
+            for (int j = 0; j < 32; ++j) accr[ch * 32 + j] += __uint_as_float(v[j]);
+          }
         }
         tc_fence_before();
         __syncwarp();
@@ -256,6 +287,7 @@ cosine_gemm_kernel(const __grid_constant__ CUtensorMap map_ehi, const __grid_con
       const long long col_base = (long long)tn * kBN + half * 128;
 #pragma unroll
       for (int ch = 0; ch < 4; ++ch) {
+        if (ch >= nch) break;
         __syncwarp();
 #pragma unroll
         for (int j = 0; j < 32; ++j) my[lane * kEpiPitch + j] = accr[ch * 32 + j];
@@ -302,7 +334,7 @@ static EncodeTiledFn get_encode_fn(spb_context *ctx) {
   return fn;
 }
 
-// (rows, dp) row-major fp32, box = (kBK columns, box_rows), SWIZZLE_128B, OOB rows read as 0
+// (rows, dp) row-major fp32, box = (kBK columns, box_rows), SWIZZLE_64B, OOB rows read as 0
 static int make_operand_map(spb_context *ctx, CUtensorMap *map, const float *ptr, long long rows, int dp,
                             int box_rows) {
   EncodeTiledFn enc = get_encode_fn(ctx);
@@ -312,7 +344,7 @@ static int make_operand_map(spb_context *ctx, CUtensorMap *map, const float *ptr
   cuuint32_t box[2] = {(cuuint32_t)kBK, (cuuint32_t)box_rows};
   cuuint32_t estr[2] = {1, 1};
   CUresult r = enc(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, (void *)ptr, dims, strides, box, estr,
-                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_64B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) return fail(ctx, SPB_ERR_CUDA, "cuTensorMapEncodeTiled failed (" + std::to_string((int)r) + ")");
   return SPB_OK;
@@ -340,28 +372,40 @@ static int cosine_scores_in(spb_context *ctx, const float *d_E, int64_t m, const
   normalize_split_kernel<<<(unsigned)((n + rows_per_block - 1) / rows_per_block), 256, 0, ctx->stream>>>(
       d_T, n, d, dp, t_hi, t_lo);
   SPB_LAUNCH_CHECK(ctx, "normalize_split_kernel(T)");
+  // tile width: fewest waves x width over the persistent grid (ties go to the wider tile)
+  const int tiles_m = (int)((m + kBM - 1) / kBM);
+  int bn = 256;
+  {
+    long long best = -1;
+    for (int cand : {256, 224, 192}) {
+      const long long tiles = (long long)tiles_m * ((n + cand - 1) / cand);
+      const long long cost = ((tiles + ctx->sm_count - 1) / ctx->sm_count) * cand;
+      if (best < 0 || cost < best) { best = cost; bn = cand; }
+    }
+  }
   CUtensorMap m_ehi, m_elo, m_thi, m_tlo;
   int rc;
   if ((rc = make_operand_map(ctx, &m_ehi, e_hi, m, dp, kBM)) || (rc = make_operand_map(ctx, &m_elo, e_lo, m, dp, kBM)) ||
-      (rc = make_operand_map(ctx, &m_thi, t_hi, n, dp, kBN)) || (rc = make_operand_map(ctx, &m_tlo, t_lo, n, dp, kBN)))
+      (rc = make_operand_map(ctx, &m_thi, t_hi, n, dp, bn)) || (rc = make_operand_map(ctx, &m_tlo, t_lo, n, dp, bn)))
     return rc;
   GemmParams p;
   p.S = d_S;
   p.m = m;
   p.n = n;
   p.kblocks = dp / kBK;
-  // short chains for small d (precision), up to 4 k-blocks (48 MMAs) for large d (drain bandwidth)
+  // short chains for small d (precision), up to 8 k-blocks (48 MMAs) for large d (drain bandwidth)
   p.chunk_kb = std::max(1, std::min(kMaxChunkKB, p.kblocks / 4));
-  p.tiles_m = (int)((m + kBM - 1) / kBM);
-  p.tiles_n = (int)((n + kBN - 1) / kBN);
-  static bool attr_set = false;
-  if (!attr_set) {
-    SPB_CUDA(ctx, cudaFuncSetAttribute(cosine_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kGemmSmem));
-    attr_set = true;
-  }
+  p.tiles_m = tiles_m;
+  p.tiles_n = (int)((n + bn - 1) / bn);
+  void (*kern)(const CUtensorMap, const CUtensorMap, const CUtensorMap, const CUtensorMap, const GemmParams) =
+      bn == 256 ? cosine_gemm_kernel<256> : (bn == 224 ? cosine_gemm_kernel<224> : cosine_gemm_kernel<192>);
+  const size_t smem = bn == 256 ? GemmGeom<256>::kSmem : (bn == 224 ? GemmGeom<224>::kSmem : GemmGeom<192>::kSmem);
+  int per_sm = 0;
+  if ((rc = configure_kernel(ctx, (const void *)kern, kGemmThreads, smem, &per_sm))) return rc;
+  if (per_sm < 1) return fail(ctx, SPB_ERR_INVALID, "cosine_gemm_kernel does not fit on an SM");
   long long grid = std::min<long long>((long long)p.tiles_m * p.tiles_n, ctx->sm_count);
   const size_t tb = timed ? timing_begin(ctx) : (size_t)-1;
-  cosine_gemm_kernel<<<(unsigned)grid, kGemmThreads, kGemmSmem, ctx->stream>>>(m_ehi, m_elo, m_thi, m_tlo, p);
+  kern<<<(unsigned)grid, kGemmThreads, smem, ctx->stream>>>(m_ehi, m_elo, m_thi, m_tlo, p);
   if (timed) timing_end(ctx, 3, tb);
   SPB_LAUNCH_CHECK(ctx, "cosine_gemm_kernel");
   return SPB_OK;
