@@ -17,7 +17,7 @@ vectors in ``tests/golden/``; ``tests/test_oracle.py`` re-checks the oracle
 against those vectors without needing the reference.  The reference's own
 tests pin only shapes, API presence and the cmvn mean/std property
 (sfe/tests/test_speechpy.py:24-106); those are reproduced in
-``tests/test_reference_suite.py``.
+``tests/test_gpu_features.py::test_reference_test_suite_semantics`` and, verbatim, by ``test_reference_test_file_runs_unchanged_against_the_dropin``.
 
 The loop structure of the reference (one numpy reduction per frame in cmvnw,
 filterbank rebuilt on every mfe call, index-matrix gather in stack_frames) is
