@@ -1115,6 +1115,7 @@ int spb_set_option(const char *name, double value) {
   else if (n == "tc_version" && (iv == 1 || iv == 2)) o.tc_version = iv;
   else if (n == "tc_epilogue" && iv >= -1 && iv <= 2) o.tc_epilogue = iv;
   else if (n == "redo" && (iv == 0 || iv == 1)) o.redo = iv;
+  else if (n == "gemm_multicast" && iv >= 0 && iv <= 1) o.gemm_multicast = iv;
   else if (n == "tau_tc" && value >= 0.0) o.tau_tc = value;
   else if (n == "tau_fft" && value >= 0.0) o.tau_fft = value;
   else return fail(nullptr, SPB_ERR_INVALID, "spb_set_option: unknown option or value out of range: " + n);
@@ -1130,6 +1131,7 @@ int spb_get_option(const char *name, double *value) {
   else if (n == "tc_version") *value = o.tc_version;
   else if (n == "tc_epilogue") *value = o.tc_epilogue;
   else if (n == "redo") *value = o.redo;
+  else if (n == "gemm_multicast") *value = o.gemm_multicast;
   else if (n == "tau_tc") *value = o.tau_tc;
   else if (n == "tau_fft") *value = o.tau_fft;
   else return fail(nullptr, SPB_ERR_INVALID, "spb_get_option: unknown option: " + n);

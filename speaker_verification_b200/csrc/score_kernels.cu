@@ -133,7 +133,41 @@ struct GemmParams {
   int tiles_m, tiles_n;
 };
 
-template <int BN>
+// TMA load of one box into the same shared-memory offset of every CTA in `mask` of the cluster; each
+// destination CTA's mbarrier (same offset) receives the bytes
+__device__ __forceinline__ void tma_load_2d_mc(const CUtensorMap *map, uint64_t *bar, void *dst, int c0, int c1,
+                                               uint16_t mask) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes.multicast::cluster"
+      " [%0], [%1, {%3, %4}], [%2], %5;" ::"r"(smem_u32(dst)),
+      "l"(map), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "h"(mask)
+      : "memory");
+}
+// tcgen05.commit that arrives on the same-offset mbarrier of every CTA in `mask`
+__device__ __forceinline__ void tc_commit_mc(uint64_t *bar, uint16_t mask) {
+  asm volatile(
+      "tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(
+          smem_u32(bar)),
+      "h"(mask)
+      : "memory");
+}
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+  asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+  asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+
+// MC: clusters of two CTAs work on two row tiles (tm, tm + 1) of the same column tile tn.  Each CTA loads its
+// own A tiles and HALF of the B tiles, multicast into both CTAs' stages: the L2 -> SM operand traffic per CTA
+// drops from 128 + BN to 128 + BN / 2 rows per k-block.  Measured on B200 at 4874 x 4874 x 512, both in one
+// process: 108.8-109.0 us against 113.8-115.6 us for the plain kernel (spb_set_option("gemm_multicast", 0));
+// results are bit-identical.  A stage may be refilled only when BOTH CTAs' MMAs have read it: the MMA
+// warps' commits arrive on both CTAs' `empty` barriers (count 2).
+template <int BN, bool MC>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 cosine_gemm_kernel(const __grid_constant__ CUtensorMap map_ehi, const __grid_constant__ CUtensorMap map_elo,
                    const __grid_constant__ CUtensorMap map_thi, const __grid_constant__ CUtensorMap map_tlo,
@@ -141,6 +175,12 @@ cosine_gemm_kernel(const __grid_constant__ CUtensorMap map_ehi, const __grid_con
   using Gm = GemmGeom<BN>;
   constexpr uint32_t kBBytes = Gm::kBBytes, kStageBytes = Gm::kStageBytes, kIdesc = Gm::kIdesc;
   constexpr int kBN = BN;
+  const uint32_t crank = MC ? cluster_ctarank() : 0u;
+  // work units: MC: (pair of row tiles, column tile), dealt to clusters; else tiles dealt to CTAs
+  const int unit_m = MC ? (p.tiles_m + 1) / 2 : p.tiles_m;
+  const long long num_tiles = (long long)unit_m * p.tiles_n;
+  const long long unit0 = MC ? (long long)(blockIdx.x >> 1) : (long long)blockIdx.x;
+  const long long unit_step = MC ? (long long)(gridDim.x >> 1) : (long long)gridDim.x;
   extern __shared__ unsigned char smem_raw[];
   unsigned char *base = reinterpret_cast<unsigned char *>(
       ((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);  // swizzled stages: 1024-byte alignment
@@ -154,7 +194,6 @@ cosine_gemm_kernel(const __grid_constant__ CUtensorMap map_ehi, const __grid_con
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
-  const long long num_tiles = (long long)p.tiles_m * p.tiles_n;
 
   if (warp == 0 && lane == 0) {
     asm volatile("prefetch.tensormap [%0];" ::"l"(&map_ehi) : "memory");
@@ -163,7 +202,7 @@ cosine_gemm_kernel(const __grid_constant__ CUtensorMap map_ehi, const __grid_con
     asm volatile("prefetch.tensormap [%0];" ::"l"(&map_tlo) : "memory");
     for (int s = 0; s < kStages; ++s) {
       mbar_init(&full[s], 1);
-      mbar_init(&empty[s], 1);
+      mbar_init(&empty[s], MC ? 2 : 1);
     }
     for (int a = 0; a < 2; ++a) {
       mbar_init(&acc_full[a], 1);
@@ -182,22 +221,31 @@ cosine_gemm_kernel(const __grid_constant__ CUtensorMap map_ehi, const __grid_con
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  if (MC) cluster_sync_all();  // the peer's barriers are initialised before anything arrives on them
 
   if (warp == 0) {
     // ===== TMA producer =====
     if (elect_one()) {
       int stage = 0;
       uint32_t phase = 0;
-      for (long long t = blockIdx.x; t < num_tiles; t += gridDim.x) {
-        const int tm = (int)(t % p.tiles_m), tn = (int)(t / p.tiles_m);
+      for (long long t = unit0; t < num_tiles; t += unit_step) {
+        const int tm = MC ? 2 * (int)(t % unit_m) + (int)crank : (int)(t % unit_m), tn = (int)(t / unit_m);
         for (int kb = 0; kb < p.kblocks; ++kb) {
           mbar_wait_guarded(&empty[stage], phase ^ 1);
           unsigned char *st = base + stage * kStageBytes;
           mbar_expect_tx(&full[stage], kStageBytes);
           tma_load_2d(&map_ehi, &full[stage], st, kb * kBK, tm * kBM);
           tma_load_2d(&map_elo, &full[stage], st + kABytes, kb * kBK, tm * kBM);
-          tma_load_2d(&map_thi, &full[stage], st + 2 * kABytes, kb * kBK, tn * kBN);
-          tma_load_2d(&map_tlo, &full[stage], st + 2 * kABytes + kBBytes, kb * kBK, tn * kBN);
+          if (MC) {
+            // this CTA's half of the B rows, into both CTAs
+            const uint32_t hb = crank * (kBBytes / 2);
+            const int r0 = tn * kBN + (int)crank * (kBN / 2);
+            tma_load_2d_mc(&map_thi, &full[stage], st + 2 * kABytes + hb, kb * kBK, r0, (uint16_t)3);
+            tma_load_2d_mc(&map_tlo, &full[stage], st + 2 * kABytes + kBBytes + hb, kb * kBK, r0, (uint16_t)3);
+          } else {
+            tma_load_2d(&map_thi, &full[stage], st + 2 * kABytes, kb * kBK, tn * kBN);
+            tma_load_2d(&map_tlo, &full[stage], st + 2 * kABytes + kBBytes, kb * kBK, tn * kBN);
+          }
           if (++stage == kStages) { stage = 0; phase ^= 1; }
         }
       }
@@ -212,7 +260,7 @@ cosine_gemm_kernel(const __grid_constant__ CUtensorMap map_ehi, const __grid_con
       int stage = 0;
       uint32_t phase = 0;
       long long cit = 0;  // chunk counter across tiles
-      for (long long t = blockIdx.x; t < num_tiles; t += gridDim.x) {
+      for (long long t = unit0; t < num_tiles; t += unit_step) {
         for (int kb0 = 0; kb0 < p.kblocks; kb0 += p.chunk_kb, ++cit) {
           const uint32_t acc = (uint32_t)(cit & 1);
           const uint32_t acc_phase = (uint32_t)((cit >> 1) & 1);
@@ -244,7 +292,9 @@ cosine_gemm_kernel(const __grid_constant__ CUtensorMap map_ehi, const __grid_con
               const uint64_t adv = (uint64_t)((k * kUmmaK * 4) >> 4);
               umma_tf32(tmem_d, a_hi + adv, b_hi + adv, kIdesc, 1u);
             }
-            tc_commit(&empty[stage]);  // frees the smem stage when these MMAs retire
+            // frees the smem stage when these MMAs retire (MC: in both CTAs, each of which writes into it)
+            if (MC) tc_commit_mc(&empty[stage], (uint16_t)3);
+            else tc_commit(&empty[stage]);
             if (++stage == kStages) { stage = 0; phase ^= 1; }
           }
           tc_commit(&acc_full[acc]);   // chunk complete -> epilogue
@@ -258,8 +308,8 @@ cosine_gemm_kernel(const __grid_constant__ CUtensorMap map_ehi, const __grid_con
     float *my = s_epi + (warp - 2) * 32 * kEpiPitch;
     const int nch = (half == 0) ? 4 : Gm::kChunks1;
     long long cit = 0;
-    for (long long t = blockIdx.x; t < num_tiles; t += gridDim.x) {
-      const int tm = (int)(t % p.tiles_m), tn = (int)(t / p.tiles_m);
+    for (long long t = unit0; t < num_tiles; t += unit_step) {
+      const int tm = MC ? 2 * (int)(t % unit_m) + (int)crank : (int)(t % unit_m), tn = (int)(t / unit_m);
       float accr[128];
 #pragma unroll
       for (int j = 0; j < 128; ++j) accr[j] = 0.f;
@@ -305,6 +355,7 @@ cosine_gemm_kernel(const __grid_constant__ CUtensorMap map_ehi, const __grid_con
   }
   tc_fence_before();
   __syncthreads();
+  if (MC) cluster_sync_all();  // no CTA retires while its peer may still write into its stages / barriers
   if (warp == 1) {
     tc_fence_after();
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512u) : "memory");
@@ -372,21 +423,59 @@ static int cosine_scores_in(spb_context *ctx, const float *d_E, int64_t m, const
   normalize_split_kernel<<<(unsigned)((n + rows_per_block - 1) / rows_per_block), 256, 0, ctx->stream>>>(
       d_T, n, d, dp, t_hi, t_lo);
   SPB_LAUNCH_CHECK(ctx, "normalize_split_kernel(T)");
-  // tile width: fewest waves x width over the persistent grid (ties go to the wider tile)
   const int tiles_m = (int)((m + kBM - 1) / kBM);
-  int bn = 256;
+  typedef void (*GemmKern)(const CUtensorMap, const CUtensorMap, const CUtensorMap, const CUtensorMap, const GemmParams);
+  struct Variant { int bn; GemmKern plain, mc; size_t smem; };
+  const Variant variants[3] = {
+      {256, cosine_gemm_kernel<256, false>, cosine_gemm_kernel<256, true>, GemmGeom<256>::kSmem},
+      {224, cosine_gemm_kernel<224, false>, cosine_gemm_kernel<224, true>, GemmGeom<224>::kSmem},
+      {192, cosine_gemm_kernel<192, false>, cosine_gemm_kernel<192, true>, GemmGeom<192>::kSmem}};
+  // 2-CTA clusters with the T tiles multicast when there are at least two row tiles and the device takes
+  // the clusters; how many fit is asked once per kernel
+  bool mc = tiles_m >= 2 && options().gemm_multicast != 0;
+  int clusters = 0;
+  if (mc) {
+    static int cached_clusters[3] = {-1, -1, -1};
+    for (int v = 0; v < 3 && mc; ++v) {
+      if (cached_clusters[v] < 0) {
+        int per_sm = 0;
+        int rc0 = configure_kernel(ctx, (const void *)variants[v].mc, kGemmThreads, variants[v].smem, &per_sm);
+        if (rc0) return rc0;
+        cudaLaunchConfig_t qc = {};
+        qc.gridDim = dim3((unsigned)(ctx->sm_count & ~1), 1, 1);
+        qc.blockDim = dim3(kGemmThreads, 1, 1);
+        qc.dynamicSmemBytes = variants[v].smem;
+        cudaLaunchAttribute at[1];
+        at[0].id = cudaLaunchAttributeClusterDimension;
+        at[0].val.clusterDim.x = 2; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+        qc.attrs = at;
+        qc.numAttrs = 1;
+        int n_cl = 0;
+        if (cudaOccupancyMaxActiveClusters(&n_cl, (const void *)variants[v].mc, &qc) != cudaSuccess) { cudaGetLastError(); n_cl = 0; }
+        cached_clusters[v] = n_cl;
+      }
+      mc = cached_clusters[v] >= 8;
+    }
+    if (mc) clusters = std::min(std::min(cached_clusters[0], cached_clusters[1]), cached_clusters[2]);
+  }
+  // tile width: fewest waves x width over the persistent grid (ties go to the wider tile)
+  int vi = 0;
   {
     long long best = -1;
-    for (int cand : {256, 224, 192}) {
-      const long long tiles = (long long)tiles_m * ((n + cand - 1) / cand);
-      const long long cost = ((tiles + ctx->sm_count - 1) / ctx->sm_count) * cand;
-      if (best < 0 || cost < best) { best = cost; bn = cand; }
+    for (int v = 0; v < 3; ++v) {
+      const int cand = variants[v].bn;
+      const long long units = (long long)(mc ? (tiles_m + 1) / 2 : tiles_m) * ((n + cand - 1) / cand);
+      const long long workers = mc ? clusters : ctx->sm_count;
+      const long long cost = ((units + workers - 1) / workers) * cand;
+      if (best < 0 || cost < best) { best = cost; vi = v; }
     }
   }
+  const int bn = variants[vi].bn;
   CUtensorMap m_ehi, m_elo, m_thi, m_tlo;
   int rc;
+  const int b_box = mc ? bn / 2 : bn;
   if ((rc = make_operand_map(ctx, &m_ehi, e_hi, m, dp, kBM)) || (rc = make_operand_map(ctx, &m_elo, e_lo, m, dp, kBM)) ||
-      (rc = make_operand_map(ctx, &m_thi, t_hi, n, dp, bn)) || (rc = make_operand_map(ctx, &m_tlo, t_lo, n, dp, bn)))
+      (rc = make_operand_map(ctx, &m_thi, t_hi, n, dp, b_box)) || (rc = make_operand_map(ctx, &m_tlo, t_lo, n, dp, b_box)))
     return rc;
   GemmParams p;
   p.S = d_S;
@@ -397,15 +486,29 @@ static int cosine_scores_in(spb_context *ctx, const float *d_E, int64_t m, const
   p.chunk_kb = std::max(1, std::min(kMaxChunkKB, p.kblocks / 4));
   p.tiles_m = tiles_m;
   p.tiles_n = (int)((n + bn - 1) / bn);
-  void (*kern)(const CUtensorMap, const CUtensorMap, const CUtensorMap, const CUtensorMap, const GemmParams) =
-      bn == 256 ? cosine_gemm_kernel<256> : (bn == 224 ? cosine_gemm_kernel<224> : cosine_gemm_kernel<192>);
-  const size_t smem = bn == 256 ? GemmGeom<256>::kSmem : (bn == 224 ? GemmGeom<224>::kSmem : GemmGeom<192>::kSmem);
+  const GemmKern kern = mc ? variants[vi].mc : variants[vi].plain;
+  const size_t smem = variants[vi].smem;
   int per_sm = 0;
   if ((rc = configure_kernel(ctx, (const void *)kern, kGemmThreads, smem, &per_sm))) return rc;
   if (per_sm < 1) return fail(ctx, SPB_ERR_INVALID, "cosine_gemm_kernel does not fit on an SM");
-  long long grid = std::min<long long>((long long)p.tiles_m * p.tiles_n, ctx->sm_count);
   const size_t tb = timed ? timing_begin(ctx) : (size_t)-1;
-  kern<<<(unsigned)grid, kGemmThreads, smem, ctx->stream>>>(m_ehi, m_elo, m_thi, m_tlo, p);
+  if (mc) {
+    const long long units = (long long)((tiles_m + 1) / 2) * p.tiles_n;
+    cudaLaunchConfig_t lc = {};
+    lc.gridDim = dim3((unsigned)(2 * std::min<long long>(units, clusters)), 1, 1);
+    lc.blockDim = dim3(kGemmThreads, 1, 1);
+    lc.dynamicSmemBytes = smem;
+    lc.stream = ctx->stream;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeClusterDimension;
+    at[0].val.clusterDim.x = 2; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+    lc.attrs = at;
+    lc.numAttrs = 1;
+    SPB_CUDA(ctx, cudaLaunchKernelEx(&lc, kern, m_ehi, m_elo, m_thi, m_tlo, p));
+  } else {
+    const long long grid = std::min<long long>((long long)p.tiles_m * p.tiles_n, ctx->sm_count);
+    kern<<<(unsigned)grid, kGemmThreads, smem, ctx->stream>>>(m_ehi, m_elo, m_thi, m_tlo, p);
+  }
   if (timed) timing_end(ctx, 3, tb);
   SPB_LAUNCH_CHECK(ctx, "cosine_gemm_kernel");
   return SPB_OK;

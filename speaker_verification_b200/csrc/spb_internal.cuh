@@ -204,6 +204,7 @@ struct Options {
   int tc_version = 2;      // tensor-core lmfe kernel generation: 2 (folded hop DFT) or 1
   int tc_epilogue = -1;    // -1 auto, 0 / 1 / 2: force that epilogue flavour of generation 2 where legal
   int redo = 1;            // float64 recomputation of low-energy filters (the 1e-4 guard)
+  int gemm_multicast = 1;  // cosine GEMM: 1 = 2-CTA clusters with the T tiles multicast (109 us vs 114-116 us, same process), 0 = one CTA per tile
   double tau_tc = 2e-5;    // flag when energy < tau x 80 (max_f^2 + max_f+1^2)  (tensor-core kernels)
   double tau_fft = 1e-4;   // flag when energy < tau x sum x^2 of the frame      (FFT kernels)
 };

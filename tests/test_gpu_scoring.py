@@ -39,6 +39,23 @@ def test_cosine_shapes(lib_built, m, n, d):
     assert_scores(scoring.cosine_scores(E, T), so.cosine_scores(E, T))
 
 
+def test_cosine_cluster_multicast_equals_plain_kernel(lib_built):
+    """The default 2-CTA cluster kernel (T tiles multicast, each CTA loads half of them) and the
+    one-CTA-per-tile kernel (option gemm_multicast=0) run the same MMAs in the same order: bit-identical scores, odd numbers of row tiles included
+    (the phantom tile of the last pair)."""
+    from speaker_verification_b200 import _lib
+    rng = np.random.Generator(np.random.Philox(4242))
+    for m, n, d in [(4874, 1200, 512), (129, 700, 64), (640, 333, 100), (256, 256, 16), (1000, 4874, 512)]:
+        E = rng.standard_normal((m, d)).astype(np.float32)
+        T = rng.standard_normal((n, d)).astype(np.float32)
+        a = scoring.cosine_scores(E, T)
+        with _lib.options(gemm_multicast=0):
+            b = scoring.cosine_scores(E, T)
+        assert np.array_equal(a, b), (m, n, d)
+        assert_scores(a[:64], so.cosine_scores(E[:64], T))
+        assert_scores(a[-64:], so.cosine_scores(E[-64:], T))
+
+
 def test_cosine_zero_rows_and_scale(lib_built):
     rng = np.random.Generator(np.random.Philox(77))
     E = rng.standard_normal((40, 128)).astype(np.float32)

@@ -11,16 +11,27 @@ E, T = so.synth_embeddings(m, n, d, seed=5)
 dE, dT = torch.from_numpy(E).cuda(), torch.from_numpy(T).cuda()
 S = torch.empty((m, n), dtype=torch.float32, device="cuda")
 ctx = _lib.context(0)
+flops = 2.0 * m * n * d
+K = 20
+for rep in range(2):
+    for mc in (0, 1):
+        with _lib.options(gemm_multicast=mc):
+            for _ in range(3):
+                scoring.cosine_scores_dev(dE, dT, S)
+            ctx.timing_enable(True)
+            for _ in range(K):
+                scoring.cosine_scores_dev(dE, dT, S)
+            ms, cnt = ctx.timing_read(3)
+            ctx.timing_enable(False)
+        print(f"gemm_multicast={mc}: {ms / cnt * 1e3:.1f} us/launch", flush=True)
 for _ in range(3):
     scoring.cosine_scores_dev(dE, dT, S)
 ctx.timing_enable(True)
-K = 20
 for _ in range(K):
     scoring.cosine_scores_dev(dE, dT, S)
 ms, cnt = ctx.timing_read(3)
 ctx.timing_enable(False)
 per = ms / cnt
-flops = 2.0 * m * n * d
 print(f"cosine_gemm_kernel: {per*1e3:.1f} us/launch over {cnt} launches; useful {flops/per/1e9:.1f} TFLOP/s "
       f"(3xTF32 issued {3*flops/per/1e9:.1f} TFLOP/s); output write {m*n*4/per/1e6:.1f} GB/s")
 rows = np.r_[0:256, 4700:4874]
