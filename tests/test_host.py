@@ -236,3 +236,27 @@ def test_fast1024_index_algebra():
     x0 = Zs[0][0].real + Zs[0][0].imag; xn = Zs[0][0].real - Zs[0][0].imag
     assert abs(x0 - Xref[0].real) < 1e-9 and abs(xn - Xref[512].real) < 1e-9
 
+
+
+def test_bench_reference_arm_runs_on_cpu_and_prints_the_contract_line():
+    """`bench.py --impl reference` (the driver's CPU arm) needs no GPU: one JSON line with the metric, the
+    strong-scaling config of the other arm, kind "reference" when oracle/_ref is staged ("port" otherwise), and
+    BLAS threads pinned before numpy is imported."""
+    import json
+    import os
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    r = subprocess.run([sys.executable, os.path.join(root, "bench.py"), "--impl", "reference", "--steps", "1",
+                        "--warmup", "0", "--cpu-utts", "8"], capture_output=True, text=True, timeout=600, cwd=root)
+    assert r.returncode == 0, r.stderr[-2000:]
+    lines = [ln for ln in r.stdout.splitlines() if ln.startswith("{")]
+    assert len(lines) == 1
+    d = json.loads(lines[0])
+    from oracle import ref_loader
+    assert d["impl"] == "reference" and d["unit"] == "audio-hours/s" and d["value"] > 0
+    assert d["cpu_baseline"]["kind"] == ("reference" if ref_loader.available() else "port")
+    assert d["cpu_baseline"]["cores"] >= 1 and d["e2e"]["h2d_bytes_per_step"] == 0
+    assert d["config"]["total_utterances"] == 148642 and d["scaling"] == "strong"
+    src = open(os.path.join(root, "bench.py")).read()
+    assert src.index('os.environ[_k] = "1"') < src.index("import numpy")
