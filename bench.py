@@ -217,7 +217,9 @@ def workload_config(args, gpus):
 
 
 def make_device_corpus(torch, lengths, seed, device):
-    align = 4
+    # utterance starts on 32-byte boundaries (8 samples): the 64-byte runs the converters fetch then cover whole
+    # sectors (measured at 20 000 utterances: features 4.24 ms with 16-byte starts, 3.92 ms with 32-byte starts)
+    align = int(os.environ.get("SPB_BENCH_ALIGN", "8"))
     padded = (lengths + align - 1) // align * align
     starts = np.zeros(len(lengths), dtype=np.int64)
     np.cumsum(padded[:-1], out=starts[1:])

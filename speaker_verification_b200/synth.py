@@ -35,7 +35,7 @@ def cfg3_lengths(num_utterances: int, seed: int = 3) -> np.ndarray:
     return np.round(dur * SAMPLE_RATE).astype(np.int64)
 
 
-def ragged_corpus(lengths: np.ndarray, seed: int, align: int = 4):
+def ragged_corpus(lengths: np.ndarray, seed: int, align: int = 8):
     """Concatenated fp32 arena + int64 offsets[U+1] for a ragged batch.
 
     Every utterance starts on a multiple of ``align`` samples (16 bytes for

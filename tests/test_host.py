@@ -159,8 +159,8 @@ def test_pack_and_shard_balance():
     loads = np.array([lengths[:500][s].sum() for s in shards])
     assert (loads.max() - loads.min()) <= lengths.max()
     sigs = [np.arange(n, dtype=np.float32) for n in (5, 8, 3)]
-    arena, starts, lens = batch.pack(sigs)
-    assert list(starts) == [0, 8, 16] and list(lens) == [5, 8, 3] and arena.shape[0] == 20
+    arena, starts, lens = batch.pack(sigs)  # starts on multiples of 8 samples (32 bytes: whole sectors)
+    assert list(starts) == [0, 8, 16] and list(lens) == [5, 8, 3] and arena.shape[0] == 24
     assert np.array_equal(arena[8:16], sigs[1]) and arena[5] == 0
 
 
