@@ -234,7 +234,7 @@ def make_device_corpus(torch, lengths, seed, device):
     return arena, starts
 
 
-KERNEL_NAMES = {0: "features", 1: "cmvnw_stage1", 2: "cmvnw_stage2", 4: "cmvnw_single_pass"}
+KERNEL_NAMES = {0: "features", 1: "cmvnw_stage1", 2: "cmvnw_stage2", 4: "cmvnw_streaming", 5: "cmvnw_resident"}
 
 
 def newest_ncu_traffic(kernel_substr):

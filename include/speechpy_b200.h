@@ -77,14 +77,16 @@ SPB_API int spb_launch_count(spb_context *ctx, uint64_t *count);
  * bracketed by CUDA events on the context's stream.  spb_timing_read synchronises,
  * sums the elapsed times recorded since the last read and clears them.
  * kernel: 0 = features (framing+FFT+mel+log), 1 = cmvnw stage 1, 2 = cmvnw stage 2,
- * 3 = cosine GEMM, 4 = cmvnw single pass (both stages in one streaming kernel), 5 = spare. */
+ * 3 = cosine GEMM, 4 = cmvnw single streaming pass (option cmvnw_kernel 3), 5 = cmvnw with the utterance resident in
+ * shared memory (both stages in one pass: the default for utterances of <= 930 rows). */
 SPB_API int spb_timing_enable(spb_context *ctx, int32_t on);
 SPB_API int spb_timing_read(spb_context *ctx, int32_t kernel, double *total_ms, uint64_t *launches);
 /* Process-wide kernel selection and guard knobs.  The defaults are the product path; the other
  * values exist so that tests can cross-check one kernel family against another on the same call
  * (parity of every variant) and so that the guard can be calibrated.
  *   "feature_kernel"  0 auto | 1 generic radix-2 FFT kernel | 2 CUDA-core FFT kernels only
- *   "cmvnw_kernel"    0 auto (large-tile two-pass) | 1 small-tile two-pass | 2 large-tile two-pass |
+ *   "cmvnw_kernel"    0 auto (utterances of <= 930 rows resident in shared memory, both stages in one pass; longer ones
+ *                     large-tile two-pass) | 1 small-tile two-pass | 2 large-tile two-pass |
  *                     3 single streaming pass (window 301, 40 columns, variance normalisation)
  *   "gemm_multicast"  1 cosine GEMM on 2-CTA clusters with the T tiles multicast (default) | 0 one CTA per tile
  *   "tc_version"      2 (default) | 1: generation of the tensor-core lmfe kernel

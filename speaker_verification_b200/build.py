@@ -21,7 +21,7 @@ INCLUDE = os.path.join(ROOT, "include")
 LIB = os.path.join(HERE, "libspeechpy_b200.so")
 BUILD_DIR = os.path.join(HERE, "build")
 
-SOURCES = ["api.cu", "feat_kernels.cu", "feat_tc_kernels.cu", "redo_kernels.cu", "cmvn_kernels.cu", "cmvn_stream_kernels.cu", "misc_kernels.cu", "cube_kernels.cu", "score_kernels.cu"]
+SOURCES = ["api.cu", "feat_kernels.cu", "feat_tc_kernels.cu", "redo_kernels.cu", "cmvn_kernels.cu", "cmvn_stream_kernels.cu", "cmvn_resident_kernels.cu", "misc_kernels.cu", "cube_kernels.cu", "score_kernels.cu"]
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
     "-Xcompiler", "-fPIC", "-Xcompiler", "-fvisibility=hidden",

@@ -647,7 +647,8 @@ int spb_batch_create(spb_context *ctx, const spb_plan *plan, const int64_t *star
   b->big_rmax = (win > 0) ? cmvnw_big_rmax(plan->p.num_filters, win) : 0;
   const int tile_target = (int)std::min<int64_t>(b->big_rmax, std::max<int64_t>(30, env_int("SPB_BIG_RMAX", b->big_rmax) / 30 * 30));
   // single-pass stream table (+ large tiles for the utterances too short for it), per chunk / group
-  std::vector<int4> streams;
+  std::vector<int4> streams, res;
+  const bool resident_ok = b->big_rmax > 0 && cmvnw_resident_supported(plan->p.num_filters, win, plan->p.cmvn_variance);
   const bool stream_ok = b->big_rmax > 0 && cmvnw_stream_supported(plan->p.num_filters, win, plan->p.cmvn_variance);
   auto add_cmvnw_tables = [&](BatchChunk &c) {
     if (b->big_rmax <= 0) return;
@@ -655,6 +656,24 @@ int spb_batch_create(spb_context *ctx, const spb_plan *plan, const int64_t *star
     for (int64_t u = c.u0; u < c.u1; ++u) append_big_tiles(big, (int)u, nframes[u], tile_target);
     c.big1 = (int64_t)big.size();
     std::stable_sort(big.begin() + c.big0, big.begin() + c.big1, [](const int4 &x, const int4 &y) { return x.z > y.z; });
+    if (resident_ok) {
+      c.rs0 = (int64_t)res.size() / 2;
+      std::vector<std::pair<int, int>> order;  // (F, utt)
+      for (int64_t u = c.u0; u < c.u1; ++u)
+        if (nframes[u] >= 1 && nframes[u] <= cmvnw_resident_max_rows()) order.push_back({nframes[u], (int)u});
+      std::stable_sort(order.begin(), order.end(), [](const std::pair<int, int> &x, const std::pair<int, int> &y) { return x.first > y.first; });
+      for (const auto &o : order) {
+        const long long base = b->h_frame_offsets[o.second];
+        res.push_back(make_int4(o.second, o.first, 0, 0));
+        res.push_back(make_int4((int)(unsigned)(base & 0xffffffffll), (int)(base >> 32), 0, 0));
+      }
+      c.rs1 = (int64_t)res.size() / 2;
+      c.lt0 = (int64_t)big.size();
+      for (int64_t u = c.u0; u < c.u1; ++u)
+        if (nframes[u] > cmvnw_resident_max_rows()) append_big_tiles(big, (int)u, nframes[u], tile_target);
+      c.lt1 = (int64_t)big.size();
+      std::stable_sort(big.begin() + c.lt0, big.begin() + c.lt1, [](const int4 &x, const int4 &y) { return x.z > y.z; });
+    }
     if (!stream_ok) return;
     c.st0 = (int64_t)streams.size();
     for (int64_t u = c.u0; u < c.u1; ++u) append_streams(streams, (int)u, nframes[u]);
@@ -734,6 +753,7 @@ int spb_batch_create(spb_context *ctx, const spb_plan *plan, const int64_t *star
       (e = cudaMalloc(&b->d_ftiles, (size_t)std::max<int64_t>(b->total_tiles, 1) * sizeof(FftTile))) != cudaSuccess ||
       (e = cudaMalloc(&b->d_cm_tiles, (size_t)std::max<int64_t>(b->total_cm_tiles, 1) * sizeof(int2))) != cudaSuccess ||
       (e = cudaMalloc(&b->d_big_tiles, std::max<size_t>(big.size(), 1) * sizeof(int4))) != cudaSuccess ||
+      (resident_ok && (e = cudaMalloc(&b->d_res_tiles, std::max<size_t>(res.size(), 1) * sizeof(int4))) != cudaSuccess) ||
       (stream_ok && (e = cudaMalloc(&b->d_streams, std::max<size_t>(streams.size(), 1) * sizeof(int4))) != cudaSuccess) ||
       (!tcg.empty() && (e = cudaMalloc(&b->d_tc_groups, tcg.size() * sizeof(TcGroup))) != cudaSuccess) ||
       (e = cudaMalloc(&d_tile_off, (u_bytes + 1) * 8)) != cudaSuccess ||
@@ -752,6 +772,9 @@ int spb_batch_create(spb_context *ctx, const spb_plan *plan, const int64_t *star
     if (!big.empty() &&
         (e = cudaMemcpyAsync(b->d_big_tiles, big.data(), big.size() * sizeof(int4), cudaMemcpyHostToDevice, ctx->stream)) != cudaSuccess)
       return cleanup(e, "cudaMemcpyAsync(big tiles)");
+    if (b->d_res_tiles && !res.empty() &&
+        (e = cudaMemcpyAsync(b->d_res_tiles, res.data(), res.size() * sizeof(int4), cudaMemcpyHostToDevice, ctx->stream)) != cudaSuccess)
+      return cleanup(e, "cudaMemcpyAsync(resident tiles)");
     if (b->d_streams && !streams.empty() &&
         (e = cudaMemcpyAsync(b->d_streams, streams.data(), streams.size() * sizeof(int4), cudaMemcpyHostToDevice, ctx->stream)) != cudaSuccess)
       return cleanup(e, "cudaMemcpyAsync(streams)");
@@ -787,6 +810,7 @@ int spb_batch_destroy(spb_batch *b) {
   cudaFree(b->d_cm_tiles);
   cudaFree(b->d_big_tiles);
   cudaFree(b->d_streams);
+  cudaFree(b->d_res_tiles);
   delete b;
   return SPB_OK;
 }
@@ -950,6 +974,14 @@ static int lmfe_cmvnw_chunk(spb_context *ctx, const spb_batch *b, const BatchChu
     if (rc || c.rt1 == c.rt0) return rc;
     return launch_cmvnw_big(ctx, lmfe_biased, ms_biased, d_out, b->d_nframes, b->d_frame_offsets,
                             b->d_big_tiles + c.rt0, c.rt1 - c.rt0, b->big_rmax, M, M, win, pl->p.cmvn_variance);
+  }
+  if (b->d_res_tiles != nullptr && options().cmvnw_kernel == 0 && (((size_t)d_out) & 15) == 0) {
+    // utterances that fit in shared memory: both stages in one resident pass (cmvn_resident_kernels.cu);
+    // the longer ones: the two-pass large-tile kernels
+    rc = launch_cmvnw_resident(ctx, lmfe_biased, d_out, b->d_res_tiles + 2 * c.rs0, c.rs1 - c.rs0);
+    if (rc || c.lt1 == c.lt0) return rc;
+    return launch_cmvnw_big(ctx, lmfe_biased, ms_biased, d_out, b->d_nframes, b->d_frame_offsets,
+                            b->d_big_tiles + c.lt0, c.lt1 - c.lt0, b->big_rmax, M, M, win, pl->p.cmvn_variance);
   }
   if (b->big_rmax > 0 && options().cmvnw_kernel != 1 && (((size_t)d_out) & 15) == 0)
     return launch_cmvnw_big(ctx, lmfe_biased, ms_biased, d_out, b->d_nframes, b->d_frame_offsets,

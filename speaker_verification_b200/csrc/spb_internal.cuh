@@ -162,6 +162,8 @@ struct BatchChunk {
   int64_t tc0 = 0, tc1 = 0;    // TcGroup range (multiples of 4)
   int64_t st0 = 0, st1 = 0;    // single-pass cmvnw streams (utterances of >= 150 rows), longest first
   int64_t rt0 = 0, rt1 = 0;    // large-tile cmvnw tiles of the utterances the stream kernel does not take
+  int64_t rs0 = 0, rs1 = 0;    // resident single-pass cmvnw: utterances of <= cmvnw_resident_max_rows() rows, longest first
+  int64_t lt0 = 0, lt1 = 0;    // large-tile cmvnw tiles of the utterances too long for the resident kernel
 };
 }  // namespace spb
 
@@ -186,6 +188,7 @@ struct spb_batch {
   int4 *d_big_tiles = nullptr;           // large-tile cmvnw: {utt, first row, rows, 0}, longest first per chunk
   int big_rmax = 0;                      // 0: large-tile path not usable for this plan
   int4 *d_streams = nullptr;             // single-pass cmvnw: {utt, first row, end row, 0} (nullptr: not usable)
+  int4 *d_res_tiles = nullptr;           // resident cmvnw: two int4 per utterance {utt, F, 0, 0}, {first global row lo, hi, 0, 0}
   bool has_short_utts = false;           // some utterance has fewer rows than the stream kernel takes
   std::vector<spb::BatchChunk> chunks;   // pipeline units of the host-pointer calls
   std::vector<spb::BatchChunk> groups;   // launch units of the device-pointer calls (runs of chunks)
@@ -200,7 +203,8 @@ namespace spb {
 // process-wide kernel selection / guard knobs behind spb_set_option (declared in the public header)
 struct Options {
   int feature_kernel = 0;  // 0 auto, 1 generic radix-2 kernel, 2 CUDA-core FFT kernels only (no tensor cores)
-  int cmvnw_kernel = 0;    // 0 auto (large-tile two-pass), 1 small-tile two-pass, 2 large-tile two-pass, 3 single streaming pass
+  int cmvnw_kernel = 0;    // 0 auto (resident single pass for utterances of <= 930 rows, large-tile two-pass for the rest),
+                           // 1 small-tile two-pass, 2 large-tile two-pass, 3 single streaming pass
   int tc_version = 2;      // tensor-core lmfe kernel generation: 2 (folded hop DFT) or 1
   int tc_epilogue = -1;    // -1 auto, 0 / 1 / 2: force that epilogue flavour of generation 2 where legal
   int redo = 1;            // float64 recomputation of low-energy filters (the 1e-4 guard)
@@ -299,6 +303,10 @@ int cmvnw_stream_min_rows();
 void append_streams(std::vector<int4> &v, int utt, int64_t F);
 int launch_cmvnw_stream(spb_context *ctx, const float *in, float *out, const int32_t *nframes,
                         const int64_t *frame_offsets, const int4 *streams, int64_t num_streams);
+// whole-utterance-resident single-pass cmvnw (cmvn_resident_kernels.cu): window 301, variance normalisation, 40 columns
+bool cmvnw_resident_supported(int cols, int win, int varnorm);
+int cmvnw_resident_max_rows();
+int launch_cmvnw_resident(spb_context *ctx, const float *in, float *out, const int4 *tiles, int64_t num_tiles);
 // balanced tiles of one utterance of F rows: appends {utt, r0, rows, 0}
 void append_big_tiles(std::vector<int4> &v, int utt, int64_t F, int rmax);
 bool cmvnw_supported(int cols, int win);

@@ -352,7 +352,8 @@ def test_single_pass_cmvnw_matches_two_pass_kernels_and_oracle(sp):
     default) and, on every value, against processing.cmvnw in float64."""
     from speaker_verification_b200 import _lib
     rows = [149, 150, 151, 164, 165, 179, 180, 181, 195, 299, 300, 301, 329, 330, 331, 345, 359, 360, 361,
-            524, 525, 526, 540, 659, 660, 661, 720, 900, 1998, 3000, 3001, 4801, 5998, 1, 31, 7205]
+            524, 525, 526, 540, 659, 660, 661, 720, 900, 1998, 3000, 3001, 4801, 5998, 1, 31, 7205,
+            2, 29, 30, 59, 60, 61, 74, 75, 76, 929, 930, 931, 899, 901]
     lengths = [320 + 160 * r + (7 * i) % 160 for i, r in enumerate(rows)]
     sigs = _signals(900, lengths)
     # digital silence inside an utterance: constant log-mel rows -> zero variance, the reference gives 0 / (0 + eps) = 0
@@ -360,7 +361,18 @@ def test_single_pass_cmvnw_matches_two_pass_kernels_and_oracle(sp):
     arena, starts, lens = batch.pack(sigs)
     fb = batch.FeatureBatch(starts, lens)
     assert [int(f) for f in np.diff(fb.frame_offsets)] == rows
-    two = fb.lmfe_cmvnw(arena)
+    # the default: utterances of <= 930 rows resident in shared memory (both stages in one pass, stage 1 in
+    # place: csrc/cmvn_resident_kernels.cu), the longer ones through the two-pass large-tile kernels
+    res = fb.lmfe_cmvnw(arena)
+    with _lib.options(cmvnw_kernel=2):
+        two = fb.lmfe_cmvnw(arena)
+    assert np.all(np.isfinite(res))
+    assert np.max(np.abs(res - two)) < 2e-5
+    for s_, got in zip(sigs, fb.split(res)):
+        ref = o.cmvnw_vectorised(o.lmfe(s_, FS), 301, True)
+        if ref.shape[0]:
+            assert float(np.max(np.abs(got - ref))) < TOL, ref.shape
+    assert np.max(np.abs(fb.split(res)[28][400:700])) < 1e-5  # the silent stretch
     with _lib.options(cmvnw_kernel=3):
         one = fb.lmfe_cmvnw(arena)
         # a NaN sample poisons the rows whose windows touch it, as in the two-pass kernels
