@@ -559,15 +559,27 @@ cmvnw_big_kernel(const CmBigParams p) {
             const float2 xo = *reinterpret_cast<const float2 *>(pout);
             const float2 m = __fadd2_rn(mh, __ffma2_rn(D, iw, ml));
             const float2 v = __ffma2_rn(make_float2(-m.x, -m.y), m, __ffma2_rn(Q, iw, e0));
-            const float vx = v.x < 1e-30f ? 1e-30f : v.x, vy = v.y < 1e-30f ? 1e-30f : v.y;
-            float rx, ry, cx, cy;
-            asm("rsqrt.approx.f32 %0, %1;" : "=f"(rx) : "f"(vx));
-            asm("rsqrt.approx.f32 %0, %1;" : "=f"(ry) : "f"(vy));
-            const float2 r = make_float2(rx, ry);
-            const float2 d = __ffma2_rn(r, neps, one);
-            asm("rcp.approx.f32 %0, %1;" : "=f"(cx) : "f"(d.x));
-            asm("rcp.approx.f32 %0, %1;" : "=f"(cy) : "f"(d.y));
-            *reinterpret_cast<float2 *>(dst) = __fmul2_rn(__fmul2_rn(xc, r), make_float2(cx, cy));
+            // one MUFU per value where the window is not near-constant (eps r < 1e-3: 1 / (1 + eps r) = 1 - eps r
+            // to float32); the exact rsqrt + rcp path otherwise (v <= 1e-12, rounding-negative, NaN)
+            float2 ov;
+            if (v.x > 1e-12f && v.y > 1e-12f) {
+              float rx, ry;
+              asm("rsqrt.approx.f32 %0, %1;" : "=f"(rx) : "f"(v.x));
+              asm("rsqrt.approx.f32 %0, %1;" : "=f"(ry) : "f"(v.y));
+              const float2 r = make_float2(rx, ry);
+              ov = __fmul2_rn(__fmul2_rn(xc, r), __ffma2_rn(r, big_neg(neps), one));
+            } else {
+              const float vx = v.x < 1e-30f ? 1e-30f : v.x, vy = v.y < 1e-30f ? 1e-30f : v.y;
+              float rx, ry, cx, cy;
+              asm("rsqrt.approx.f32 %0, %1;" : "=f"(rx) : "f"(vx));
+              asm("rsqrt.approx.f32 %0, %1;" : "=f"(ry) : "f"(vy));
+              const float2 r = make_float2(rx, ry);
+              const float2 d = __ffma2_rn(r, neps, one);
+              asm("rcp.approx.f32 %0, %1;" : "=f"(cx) : "f"(d.x));
+              asm("rcp.approx.f32 %0, %1;" : "=f"(cy) : "f"(d.y));
+              ov = __fmul2_rn(__fmul2_rn(xc, r), make_float2(cx, cy));
+            }
+            *reinterpret_cast<float2 *>(dst) = ov;
             D = __fadd2_rn(D, big_sub(xi, xo));
             Q = __fadd2_rn(Q, __ffma2_rn(xi, xi, big_neg(__fmul2_rn(xo, xo))));
             dst += ld; pc += cols; pin += cols; pout += cols;
