@@ -8,8 +8,8 @@ timeout -s KILL 900 python bench.py --steps 10 --warmup 3 > $O/bench_full.json 2
 timeout -s KILL 300 python tools/tc_time.py lmfe > $O/time_lmfe.log 2>&1
 timeout -s KILL 300 python tools/tc_time.py lmfe_cmvnw > $O/time_lmfe_cmvnw.log 2>&1
 timeout -s KILL 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file $O/launches.csv python bench.py --steps 2 --warmup 3 --no-cpu-baseline --no-extras > $O/ncu_launches.log 2>&1
-for K in features_tc2 cmvnw_big cosine_gemm; do
-  timeout -s KILL 900 ncu --set full --clock-control none --import-source on -k regex:$K -s 4 -c 2 -o $O/ncu_$K -f python tools/ncu_workload.py > $O/ncu_$K.log 2>&1
+for K in features_tc2 cmvnw_resident cmvnw_big cosine_gemm; do
+  timeout -s KILL 900 ncu --set full --clock-control none --import-source on -k regex:$K -s 1 -c 2 -o $O/ncu_$K -f python tools/ncu_workload.py > $O/ncu_$K.log 2>&1
   echo "ncu $K rc=$?"
 done
 for f in $O/pytest_gpu.log $O/bench_ref.err $O/bench_full.err $O/time_lmfe.log $O/time_lmfe_cmvnw.log; do echo "== $f"; tail -n 7 $f; done
