@@ -83,12 +83,25 @@ __device__ __forceinline__ float2 res_sub(const float2 a, const float2 b) { retu
 // symmetric-pad rows of the ext buffer (ext row e = utterance row e - 150) copied from the interior
 __device__ __forceinline__ void res_fill_pads(float *s, const int F, const int tid) {
   constexpr int n4 = kResCols / 4;
-  for (int i = tid; i < 2 * kResH * n4; i += kResThreads) {
-    const int k = i / n4, c4 = i - k * n4;
-    const int e = (k < kResH) ? k : F + k;  // [0, 150) and [F + 150, F + 300)
-    const int src = res_reflect(e - kResH, F) + kResH;
-    reinterpret_cast<float4 *>(s + (size_t)e * kResCols)[c4] = reinterpret_cast<const float4 *>(s + (size_t)src * kResCols)[c4];
+  constexpr int kItems = 2 * kResH * n4;                              // 3 000 16-byte pieces
+  constexpr int kPer = (kItems + kResThreads - 1) / kResThreads;      // 5 per thread: all loads, then all stores
+  float4 v[kPer];
+  int dst[kPer];
+#pragma unroll
+  for (int j = 0; j < kPer; ++j) {
+    const int i = tid + j * kResThreads;
+    dst[j] = -1;
+    if (i < kItems) {
+      const int k = i / n4, c4 = i - k * n4;
+      const int e = (k < kResH) ? k : F + k;  // [0, 150) and [F + 150, F + 300)
+      const int src = res_reflect(e - kResH, F) + kResH;
+      dst[j] = e * kResCols + c4 * 4;
+      v[j] = *reinterpret_cast<const float4 *>(s + (size_t)src * kResCols + c4 * 4);
+    }
   }
+#pragma unroll
+  for (int j = 0; j < kPer; ++j)
+    if (dst[j] >= 0) *reinterpret_cast<float4 *>(s + dst[j]) = v[j];
 }
 
 // float64 sums (and sums of squares) of the 30-row blocks of the ext buffer; rows past `rows` count as absent
