@@ -395,6 +395,31 @@ def test_single_pass_cmvnw_matches_two_pass_kernels_and_oracle(sp):
     fb.close()
 
 
+@pytest.mark.parametrize("kw", [dict(win_size=101), dict(win_size=31, num_filters=24), dict(win_size=301, num_filters=26),
+                                dict(win_size=301, variance_normalization=False), dict(win_size=601),
+                                dict(win_size=11, variance_normalization=False, num_filters=64, fft_length=1024,
+                                     frame_length=0.025)])
+def test_batch_cmvnw_other_windows_and_widths(sp, kw):
+    """The resident / streaming single-pass kernels take only the default shape (window 301, 40 columns,
+    variance normalisation); every other plan must fall through to the two-pass kernels and still match
+    processing.cmvnw(feature.lmfe(...)) of the reference."""
+    # (no single-frame utterance here: a constant window makes the reference's own output rounding noise of its
+    # float64 mean, amplified by 1 / 2^-30 -- 1e-4 at window 601; the ragged-batch test covers F = 1 at window 301)
+    lengths = [64000, 20000, 100321, 8000, 800, 154000]
+    sigs = _signals(1300, lengths)
+    arena, starts, lens = batch.pack(sigs)
+    fb = batch.FeatureBatch(starts, lens, **kw)
+    out = fb.lmfe_cmvnw(arena)
+    lkw = {k: v for k, v in kw.items() if k in ("num_filters", "fft_length", "frame_length")}
+    for s_, got in zip(sigs, fb.split(out)):
+        lm = o.lmfe(s_, FS, **lkw)
+        assert got.shape == lm.shape
+        if lm.shape[0]:
+            ref = o.cmvnw_vectorised(lm, kw.get("win_size", 301), kw.get("variance_normalization", True))
+            assert np.max(np.abs(got - ref)) < TOL, kw
+    fb.close()
+
+
 def test_nan_samples_poison_the_window_like_the_reference(sp):
     """A NaN sample makes its frames NaN and, through the window mean / std, every cmvnw row whose
     window touches them (processing.py:302-322) -- in every column (the block sums convert half of
