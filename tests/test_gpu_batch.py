@@ -395,6 +395,31 @@ def test_single_pass_cmvnw_matches_two_pass_kernels_and_oracle(sp):
     fb.close()
 
 
+def test_cmvnw_random_lengths_resident_and_two_pass(sp):
+    """160 utterances of random length (1 .. 1 100 frames, around the resident kernel's 930-row limit and every
+    30-row block phase) in one batch: the default dispatch (resident single pass / two-pass) against the two-pass
+    kernels alone and, on every value, against processing.cmvnw(feature.lmfe) of the reference."""
+    from speaker_verification_b200 import _lib
+    rng = np.random.Generator(np.random.Philox(20261105))
+    rows = np.concatenate([rng.integers(1, 1101, size=140), rng.integers(900, 961, size=20)])
+    lengths = [int(320 + 160 * r + rng.integers(0, 160)) for r in rows]
+    sigs = _signals(5000, lengths)
+    arena, starts, lens = batch.pack(sigs)
+    fb = batch.FeatureBatch(starts, lens)
+    assert [int(f) for f in np.diff(fb.frame_offsets)] == [int(r) for r in rows]
+    got = fb.lmfe_cmvnw(arena)
+    with _lib.options(cmvnw_kernel=2):
+        two = fb.lmfe_cmvnw(arena)
+    assert np.all(np.isfinite(got))
+    assert np.max(np.abs(got - two)) < 2e-5
+    for s_, g_, r in zip(sigs, fb.split(got), rows):
+        if r < 2:
+            continue  # a single frame: the reference's own output is rounding noise over 2^-30
+        ref = o.cmvnw_vectorised(o.lmfe(s_, FS), 301, True)
+        assert np.max(np.abs(g_ - ref)) < TOL, int(r)
+    fb.close()
+
+
 @pytest.mark.parametrize("kw", [dict(win_size=101), dict(win_size=31, num_filters=24), dict(win_size=301, num_filters=26),
                                 dict(win_size=301, variance_normalization=False), dict(win_size=601),
                                 dict(win_size=11, variance_normalization=False, num_filters=64, fft_length=1024,
