@@ -87,7 +87,9 @@ SPB_API int spb_timing_read(spb_context *ctx, int32_t kernel, double *total_ms, 
  *   "feature_kernel"  0 auto | 1 generic radix-2 FFT kernel | 2 CUDA-core FFT kernels only
  *   "cmvnw_kernel"    0 auto (utterances of <= 930 rows resident in shared memory, both stages in one pass; longer ones
  *                     large-tile two-pass) | 1 small-tile two-pass | 2 large-tile two-pass |
- *                     3 single streaming pass (window 301, 40 columns, variance normalisation)
+ *                     3 single streaming pass (window 301, 40 columns, variance normalisation) |
+ *                     4 as 0, and utterances of 931 .. 1 860 rows resident in the shared memory of a cluster of two CTAs
+ *                     (halves exchanged over DSMEM; one read + one write per row, but measured slower than two passes)
  *   "gemm_multicast"  1 cosine GEMM on 2-CTA clusters with the T tiles multicast (default) | 0 one CTA per tile
  *   "tc_version"      2 (default) | 1: generation of the tensor-core lmfe kernel
  *   "tc_epilogue"     -1 auto | 0 generic | 1 runs of four filters (when the bank allows) | 2 static

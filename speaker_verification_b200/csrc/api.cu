@@ -649,6 +649,8 @@ int spb_batch_create(spb_context *ctx, const spb_plan *plan, const int64_t *star
   // single-pass stream table (+ large tiles for the utterances too short for it), per chunk / group
   std::vector<int4> streams, res;
   const bool resident_ok = b->big_rmax > 0 && cmvnw_resident_supported(plan->p.num_filters, win, plan->p.cmvn_variance);
+  const bool resident_pairs = resident_ok && cmvnw_resident_clusters(ctx) >= 8;
+  b->resident_pairs = resident_pairs;
   const bool stream_ok = b->big_rmax > 0 && cmvnw_stream_supported(plan->p.num_filters, win, plan->p.cmvn_variance);
   auto add_cmvnw_tables = [&](BatchChunk &c) {
     if (b->big_rmax <= 0) return;
@@ -668,11 +670,33 @@ int spb_batch_create(spb_context *ctx, const spb_plan *plan, const int64_t *star
         res.push_back(make_int4((int)(unsigned)(base & 0xffffffffll), (int)(base >> 32), 0, 0));
       }
       c.rs1 = (int64_t)res.size() / 2;
+      // the longer ones: large tiles of the two-pass kernels
+      const int max1 = cmvnw_resident_max_rows();
       c.lt0 = (int64_t)big.size();
       for (int64_t u = c.u0; u < c.u1; ++u)
-        if (nframes[u] > cmvnw_resident_max_rows()) append_big_tiles(big, (int)u, nframes[u], tile_target);
+        if (nframes[u] > max1) append_big_tiles(big, (int)u, nframes[u], tile_target);
       c.lt1 = (int64_t)big.size();
       std::stable_sort(big.begin() + c.lt0, big.begin() + c.lt1, [](const int4 &x, const int4 &y) { return x.z > y.z; });
+      // option cmvnw_kernel = 4: utterances of up to twice the resident limit go to a cluster of two
+      // CTAs each (when the device takes such clusters), only those beyond to the two-pass kernels
+      c.r20 = c.r21 = (int64_t)res.size() / 2;
+      c.vl0 = c.vl1 = (int64_t)big.size();
+      if (resident_pairs) {
+        order.clear();
+        for (int64_t u = c.u0; u < c.u1; ++u)
+          if (nframes[u] > max1 && nframes[u] <= 2 * max1) order.push_back({nframes[u], (int)u});
+        std::stable_sort(order.begin(), order.end(), [](const std::pair<int, int> &x, const std::pair<int, int> &y) { return x.first > y.first; });
+        for (const auto &o : order) {
+          const long long base = b->h_frame_offsets[o.second];
+          res.push_back(make_int4(o.second, o.first, 0, 0));
+          res.push_back(make_int4((int)(unsigned)(base & 0xffffffffll), (int)(base >> 32), 0, 0));
+        }
+        c.r21 = (int64_t)res.size() / 2;
+        for (int64_t u = c.u0; u < c.u1; ++u)
+          if (nframes[u] > 2 * max1) append_big_tiles(big, (int)u, nframes[u], tile_target);
+        c.vl1 = (int64_t)big.size();
+        std::stable_sort(big.begin() + c.vl0, big.begin() + c.vl1, [](const int4 &x, const int4 &y) { return x.z > y.z; });
+      }
     }
     if (!stream_ok) return;
     c.st0 = (int64_t)streams.size();
@@ -975,13 +999,18 @@ static int lmfe_cmvnw_chunk(spb_context *ctx, const spb_batch *b, const BatchChu
     return launch_cmvnw_big(ctx, lmfe_biased, ms_biased, d_out, b->d_nframes, b->d_frame_offsets,
                             b->d_big_tiles + c.rt0, c.rt1 - c.rt0, b->big_rmax, M, M, win, pl->p.cmvn_variance);
   }
-  if (b->d_res_tiles != nullptr && options().cmvnw_kernel == 0 && (((size_t)d_out) & 15) == 0) {
+  const int cmk = options().cmvnw_kernel;
+  if (b->d_res_tiles != nullptr && (cmk == 0 || cmk == 4) && (((size_t)d_out) & 15) == 0) {
     // utterances that fit in shared memory: both stages in one resident pass (cmvn_resident_kernels.cu);
-    // the longer ones: the two-pass large-tile kernels
-    rc = launch_cmvnw_resident(ctx, lmfe_biased, d_out, b->d_res_tiles + 2 * c.rs0, c.rs1 - c.rs0);
-    if (rc || c.lt1 == c.lt0) return rc;
+    // the longer ones: the two-pass large-tile kernels (default), or -- option 4, measured slower --
+    // a cluster of two CTAs up to twice that length and the two-pass kernels beyond
+    const bool pairs = cmk == 4 && b->resident_pairs;
+    rc = launch_cmvnw_resident(ctx, lmfe_biased, d_out, b->d_res_tiles + 2 * c.rs0, c.rs1 - c.rs0, 1);
+    if (!rc && pairs) rc = launch_cmvnw_resident(ctx, lmfe_biased, d_out, b->d_res_tiles + 2 * c.r20, c.r21 - c.r20, 2);
+    const int64_t t0 = pairs ? c.vl0 : c.lt0, t1 = pairs ? c.vl1 : c.lt1;
+    if (rc || t1 == t0) return rc;
     return launch_cmvnw_big(ctx, lmfe_biased, ms_biased, d_out, b->d_nframes, b->d_frame_offsets,
-                            b->d_big_tiles + c.lt0, c.lt1 - c.lt0, b->big_rmax, M, M, win, pl->p.cmvn_variance);
+                            b->d_big_tiles + t0, t1 - t0, b->big_rmax, M, M, win, pl->p.cmvn_variance);
   }
   if (b->big_rmax > 0 && options().cmvnw_kernel != 1 && (((size_t)d_out) & 15) == 0)
     return launch_cmvnw_big(ctx, lmfe_biased, ms_biased, d_out, b->d_nframes, b->d_frame_offsets,
@@ -1143,7 +1172,7 @@ int spb_set_option(const char *name, double value) {
   const std::string n(name);
   const int iv = (int)value;
   if (n == "feature_kernel" && iv >= 0 && iv <= 2) o.feature_kernel = iv;
-  else if (n == "cmvnw_kernel" && iv >= 0 && iv <= 3) o.cmvnw_kernel = iv;
+  else if (n == "cmvnw_kernel" && iv >= 0 && iv <= 4) o.cmvnw_kernel = iv;
   else if (n == "tc_version" && (iv == 1 || iv == 2)) o.tc_version = iv;
   else if (n == "tc_epilogue" && iv >= -1 && iv <= 2) o.tc_epilogue = iv;
   else if (n == "redo" && (iv == 0 || iv == 1)) o.redo = iv;

@@ -80,11 +80,13 @@ __device__ __forceinline__ double res_f2d_alu(const float f) {
 __device__ __forceinline__ float2 res_neg(const float2 a) { return make_float2(-a.x, -a.y); }
 __device__ __forceinline__ float2 res_sub(const float2 a, const float2 b) { return __fadd2_rn(a, res_neg(b)); }
 
-// symmetric-pad rows of the ext buffer (ext row e = utterance row e - 150) copied from the interior
-__device__ __forceinline__ void res_fill_pads(float *s, const int F, const int tid) {
+// symmetric-pad rows of the ext buffer of a part [lo, lo + N) of an utterance of F rows (ext row e = utterance
+// row lo - 150 + e): the halo rows that fall outside [0, F) are copies of rows inside the part (all loads, then
+// all stores); halo rows that are real rows of the utterance (the side facing the other part) are left alone
+__device__ __forceinline__ void res_fill_pads(float *s, const int lo, const int N, const int F, const int tid) {
   constexpr int n4 = kResCols / 4;
   constexpr int kItems = 2 * kResH * n4;                              // 3 000 16-byte pieces
-  constexpr int kPer = (kItems + kResThreads - 1) / kResThreads;      // 5 per thread: all loads, then all stores
+  constexpr int kPer = (kItems + kResThreads - 1) / kResThreads;      // 5 per thread
   float4 v[kPer];
   int dst[kPer];
 #pragma unroll
@@ -93,15 +95,36 @@ __device__ __forceinline__ void res_fill_pads(float *s, const int F, const int t
     dst[j] = -1;
     if (i < kItems) {
       const int k = i / n4, c4 = i - k * n4;
-      const int e = (k < kResH) ? k : F + k;  // [0, 150) and [F + 150, F + 300)
-      const int src = res_reflect(e - kResH, F) + kResH;
-      dst[j] = e * kResCols + c4 * 4;
-      v[j] = *reinterpret_cast<const float4 *>(s + (size_t)src * kResCols + c4 * 4);
+      const int e = (k < kResH) ? k : N + k;  // [0, 150) and [N + 150, N + 300)
+      const int u = lo - kResH + e;
+      if (u < 0 || u >= F) {
+        const int src = res_reflect(u, F) - (lo - kResH);
+        dst[j] = e * kResCols + c4 * 4;
+        v[j] = *reinterpret_cast<const float4 *>(s + (size_t)src * kResCols + c4 * 4);
+      }
     }
   }
 #pragma unroll
   for (int j = 0; j < kPer; ++j)
     if (dst[j] >= 0) *reinterpret_cast<float4 *>(s + dst[j]) = v[j];
+}
+
+// thread-block clusters: rank, barrier, a 16-byte load from the peer CTA's shared memory (DSMEM)
+__device__ __forceinline__ uint32_t res_cluster_rank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ void res_cluster_sync() {
+  asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+  asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+__device__ __forceinline__ float4 res_ld_peer(const float *local_ptr, const uint32_t peer_rank) {
+  uint32_t remote;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(remote) : "r"(smem_u32(local_ptr)), "r"(peer_rank));
+  float4 v;
+  asm volatile("ld.shared::cluster.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(remote) : "memory");
+  return v;
 }
 
 // float64 sums (and sums of squares) of the 30-row blocks of the ext buffer; rows past `rows` count as absent
@@ -134,6 +157,13 @@ __device__ __forceinline__ void res_block_sums(const float *s, const int rows, d
   }
 }
 
+// CL = 1: one CTA per utterance (<= kResMaxRows rows), utterances pulled from an atomic queue.
+// CL = 2: a CLUSTER of two CTAs per utterance (<= 2 kResMaxRows rows): each CTA keeps one half (a multiple of 30
+// rows) with a 150-row halo -- the symmetric pad on its outer side, the neighbour half's rows on the inner side
+// (lmfe rows loaded from global memory like its own; the neighbour's mean-subtracted rows fetched from the peer
+// CTA's shared memory over DSMEM between two cluster barriers) --, utterances dealt statically to the clusters
+// so that both CTAs of a cluster walk the same list.
+template <int CL>
 __global__ void __launch_bounds__(kResThreads, 1) cmvnw_resident_kernel(const CmResParams p) {
   extern __shared__ __align__(16) unsigned char res_smem[];
   float *s = reinterpret_cast<float *>(res_smem);                                   // [ext rows][40]
@@ -153,8 +183,8 @@ __global__ void __launch_bounds__(kResThreads, 1) cmvnw_resident_kernel(const Cm
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   uint32_t bar_phase = 0;
-  auto fetch_desc = [&](int slot) {
-    const int t = atomicAdd(p.counter, 1);
+  const uint32_t crank = (CL == 2) ? res_cluster_rank() : 0u;
+  auto fetch_desc = [&](int slot, int t) {
     int4 d = make_int4(-1, 0, 0, 0);
     long long b = 0;
     if (t < p.num_tiles) {
@@ -169,20 +199,36 @@ __global__ void __launch_bounds__(kResThreads, 1) cmvnw_resident_kernel(const Cm
     s_desc[slot] = d;
     s_base[slot] = b;
   };
-  if (tid == 0) fetch_desc(0);
+  // CL = 1: tickets from the atomic counter; CL = 2: tile = cluster index + i x clusters (same in both CTAs)
+  int next_static = (CL == 2) ? (int)(blockIdx.x >> 1) : 0;
+  const int static_step = (CL == 2) ? (int)(gridDim.x >> 1) : 0;
+  auto next_ticket = [&]() {
+    if (CL == 2) {
+      const int t = next_static;
+      next_static += static_step;
+      return t;
+    }
+    return atomicAdd(p.counter, 1);
+  };
+  if (tid == kResThreads - 1) fetch_desc(0, next_ticket());
   for (int slot = 0;; slot ^= 1) {
     __syncthreads();  // previous utterance fully consumed; descriptor `slot` published
     const int4 td = s_desc[slot];
     if (td.x < 0) break;
-    if (tid == kResThreads - 1) fetch_desc(slot ^ 1);
+    if (tid == kResThreads - 1) fetch_desc(slot ^ 1, next_ticket());
     const int F = td.y;
     const long long base = s_base[slot];
-    const int ext = F + 2 * H;
-    // ---- the utterance's rows: one contiguous block, TMA bulk copies issued by one thread
+    // this CTA's part [lo, lo + N) of the utterance
+    const int N0 = (CL == 2) ? ((F / 2 + G - 1) / G) * G : F;
+    const int lo = crank ? N0 : 0;
+    const int N = crank ? F - N0 : N0;
+    const int ext = N + 2 * H;
+    // ---- the part's rows and the real halo rows next to them: one contiguous block, TMA bulk copies
     if (tid == 0) {
-      const char *src = reinterpret_cast<const char *>(p.in + base * (long long)C);
-      char *dst = reinterpret_cast<char *>(s + (size_t)H * C);
-      const uint32_t total = (uint32_t)F * (uint32_t)C * 4u;
+      const int u_lo = max(0, lo - H), u_hi = min(F, lo + N + H);
+      const char *src = reinterpret_cast<const char *>(p.in + (base + u_lo) * (long long)C);
+      char *dst = reinterpret_cast<char *>(s + (size_t)(u_lo - (lo - H)) * C);
+      const uint32_t total = (uint32_t)(u_hi - u_lo) * (uint32_t)C * 4u;
       asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
       mbar_expect_tx(&s_bar, total);
       for (uint32_t off = 0; off < total; off += 65536u) bulk_load(dst + off, src + off, min(65536u, total - off), &s_bar);
@@ -190,12 +236,12 @@ __global__ void __launch_bounds__(kResThreads, 1) cmvnw_resident_kernel(const Cm
     mbar_wait_guarded(&s_bar, bar_phase);
     bar_phase ^= 1;
     __syncthreads();
-    res_fill_pads(s, F, tid);
+    res_fill_pads(s, lo, N, F, tid);
     __syncthreads();
     res_block_sums<false>(s, ext, bs1, bs2, b0, c0);
     __syncthreads();
     // ---- stage 1 (processing.py:301-307), in place, in two halves of 15 rows (see the file header)
-    const int nbo = (F + G - 1) / G;
+    const int nbo = (N + G - 1) / G;
     {
       constexpr int HG = G / 2;
       const int b = b0;                      // one output block per thread (nbo <= 31 < 32 block-threads)
@@ -237,14 +283,25 @@ __global__ void __launch_bounds__(kResThreads, 1) cmvnw_resident_kernel(const Cm
 #pragma unroll
           for (int i = 0; i < HG; ++i) {
             const int q = q0 + half * HG + i;
-            if (q < F) *reinterpret_cast<float2 *>(s + (size_t)(q + H) * C + c0) = o[i];
+            if (q < N) *reinterpret_cast<float2 *>(s + (size_t)(q + H) * C + c0) = o[i];
           }
         }
         __syncthreads();
       }
     }
     // ---- the float32 mean-subtracted rows are padded themselves (processing.py:314-315), then summed
-    res_fill_pads(s, F, tid);
+    if (CL == 2) {
+      // the inner halo = the neighbour half's first / last 150 mean-subtracted rows, out of the peer's shared memory
+      res_cluster_sync();  // both halves' stage-1 rows are stored (release / acquire at cluster scope)
+      const int e_dst = crank ? 0 : N + H;          // my inner halo (ext rows)
+      const int e_src = crank ? N0 : H;             // the peer's boundary rows in ITS ext buffer
+      for (int i = tid; i < H * (C / 4); i += kResThreads) {
+        const int k = i / (C / 4), c4 = i - k * (C / 4);
+        reinterpret_cast<float4 *>(s + (size_t)(e_dst + k) * C)[c4] = res_ld_peer(s + (size_t)(e_src + k) * C + c4 * 4, crank ^ 1u);
+      }
+      res_cluster_sync();  // the peer has read my rows: from here on the two CTAs run free until the next exchange
+    }
+    res_fill_pads(s, lo, N, F, tid);
     __syncthreads();
     res_block_sums<true>(s, ext, bs1, bs2, b0, c0);
     __syncthreads();
@@ -258,7 +315,7 @@ __global__ void __launch_bounds__(kResThreads, 1) cmvnw_resident_kernel(const Cm
         w1x += t1.x; w1y += t1.y;
         w2x += t2.x; w2y += t2.y;
       }
-      const int q0 = b * G, q1 = min(q0 + G, F);
+      const int q0 = b * G, q1 = min(q0 + G, N);
       const float *pout = s + (size_t)q0 * C + c0;
       const float *pc = pout + (size_t)H * C;
       const float *pin = pout + (size_t)kResWin * C;
@@ -274,7 +331,7 @@ __global__ void __launch_bounds__(kResThreads, 1) cmvnw_resident_kernel(const Cm
       const float2 e0 = make_float2((float)(w2x * inv_win), (float)(w2y * inv_win));
       const float2 peps = make_float2(p.eps, p.eps), one = make_float2(1.f, 1.f);
       float2 D = make_float2(0.f, 0.f), Q = make_float2(0.f, 0.f);
-      float *dst = p.out + (base + q0) * (long long)C + c0;
+      float *dst = p.out + (base + lo + q0) * (long long)C + c0;
 #pragma unroll 2
       for (int q = q0; q < q1; ++q) {
         const float2 xc = *reinterpret_cast<const float2 *>(pc);
@@ -321,8 +378,10 @@ bool cmvnw_resident_supported(int cols, int win, int varnorm) {
 }
 int cmvnw_resident_max_rows() { return kResMaxRows; }
 
-// tiles: two int4 per utterance, {utt, F, 0, 0} and {first global row (lo, hi), 0, 0}
-int launch_cmvnw_resident(spb_context *ctx, const float *in, float *out, const int4 *tiles, int64_t num_tiles) {
+// tiles: two int4 per utterance, {utt, F, 0, 0} and {first global row (lo, hi), 0, 0}.
+// cluster = 1: utterances of <= kResMaxRows rows, one CTA each; cluster = 2: utterances of <= 2 kResMaxRows rows
+// (and >= 600, so that each half holds its 150 boundary rows), a cluster of two CTAs each.
+int launch_cmvnw_resident(spb_context *ctx, const float *in, float *out, const int4 *tiles, int64_t num_tiles, int cluster) {
   if (num_tiles <= 0) return SPB_OK;
   int *counters = (int *)scratch(ctx, 7, 256);
   if (!counters) return SPB_ERR_CUDA;
@@ -334,16 +393,57 @@ int launch_cmvnw_resident(spb_context *ctx, const float *in, float *out, const i
   p.num_tiles = (int)num_tiles;
   p.counter = counters + 3;
   p.eps = 9.313225746154785e-10f;  // 2^-30 (processing.py:292)
+  void (*kern)(const CmResParams) = (cluster == 2) ? cmvnw_resident_kernel<2> : cmvnw_resident_kernel<1>;
   int per_sm = 0;
-  int rc = configure_kernel(ctx, (const void *)cmvnw_resident_kernel, kResThreads, kResSmem, &per_sm);
+  int rc = configure_kernel(ctx, (const void *)kern, kResThreads, kResSmem, &per_sm);
   if (rc) return rc;
   if (per_sm < 1) return fail(ctx, SPB_ERR_UNSUPPORTED, "resident cmvnw kernel does not fit in shared memory");
-  const long long grid = std::min<long long>(ctx->sm_count, num_tiles);
   const size_t tb = timing_begin(ctx);
-  cmvnw_resident_kernel<<<(unsigned)grid, kResThreads, kResSmem, ctx->stream>>>(p);
+  if (cluster == 2) {
+    const int clusters = cmvnw_resident_clusters(ctx);
+    if (clusters < 1) return fail(ctx, SPB_ERR_UNSUPPORTED, "resident cmvnw: the device takes no 2-CTA clusters of this kernel");
+    cudaLaunchConfig_t lc = {};
+    lc.gridDim = dim3((unsigned)(2 * std::min<long long>(num_tiles, clusters)), 1, 1);
+    lc.blockDim = dim3(kResThreads, 1, 1);
+    lc.dynamicSmemBytes = kResSmem;
+    lc.stream = ctx->stream;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeClusterDimension;
+    at[0].val.clusterDim.x = 2; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+    lc.attrs = at;
+    lc.numAttrs = 1;
+    SPB_CUDA(ctx, cudaLaunchKernelEx(&lc, kern, p));
+  } else {
+    const long long grid = std::min<long long>(ctx->sm_count, num_tiles);
+    kern<<<(unsigned)grid, kResThreads, kResSmem, ctx->stream>>>(p);
+  }
   timing_end(ctx, 5, tb);
   SPB_LAUNCH_CHECK(ctx, "cmvnw_resident_kernel");
   return SPB_OK;
+}
+
+// how many 2-CTA clusters of the resident kernel the device runs at once (0: none); asked once
+int cmvnw_resident_clusters(spb_context *ctx) {
+  static int cached = -1;
+  if (cached >= 0) return cached;
+  int per_sm = 0;
+  if (configure_kernel(ctx, (const void *)cmvnw_resident_kernel<2>, kResThreads, kResSmem, &per_sm) != SPB_OK) return 0;
+  cudaLaunchConfig_t qc = {};
+  qc.gridDim = dim3((unsigned)(ctx->sm_count & ~1), 1, 1);
+  qc.blockDim = dim3(kResThreads, 1, 1);
+  qc.dynamicSmemBytes = kResSmem;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeClusterDimension;
+  at[0].val.clusterDim.x = 2; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+  qc.attrs = at;
+  qc.numAttrs = 1;
+  int n = 0;
+  if (cudaOccupancyMaxActiveClusters(&n, (const void *)cmvnw_resident_kernel<2>, &qc) != cudaSuccess) {
+    cudaGetLastError();
+    n = 0;
+  }
+  cached = n;
+  return cached;
 }
 
 }  // namespace spb

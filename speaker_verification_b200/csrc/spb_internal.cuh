@@ -163,7 +163,10 @@ struct BatchChunk {
   int64_t st0 = 0, st1 = 0;    // single-pass cmvnw streams (utterances of >= 150 rows), longest first
   int64_t rt0 = 0, rt1 = 0;    // large-tile cmvnw tiles of the utterances the stream kernel does not take
   int64_t rs0 = 0, rs1 = 0;    // resident single-pass cmvnw: utterances of <= cmvnw_resident_max_rows() rows, longest first
-  int64_t lt0 = 0, lt1 = 0;    // large-tile cmvnw tiles of the utterances too long for the resident kernel
+  int64_t lt0 = 0, lt1 = 0;    // large-tile cmvnw tiles of the utterances too long for the resident kernel (> 930 rows)
+  // option cmvnw_kernel = 4 only:
+  int64_t r20 = 0, r21 = 0;    // resident cmvnw on 2-CTA clusters: utterances of 931 .. 1 860 rows, longest first (in d_res_tiles)
+  int64_t vl0 = 0, vl1 = 0;    // large-tile cmvnw tiles of the utterances too long for the cluster pairs as well
 };
 }  // namespace spb
 
@@ -189,6 +192,7 @@ struct spb_batch {
   int big_rmax = 0;                      // 0: large-tile path not usable for this plan
   int4 *d_streams = nullptr;             // single-pass cmvnw: {utt, first row, end row, 0} (nullptr: not usable)
   int4 *d_res_tiles = nullptr;           // resident cmvnw: two int4 per utterance {utt, F, 0, 0}, {first global row lo, hi, 0, 0}
+  bool resident_pairs = false;           // the device takes 2-CTA clusters of the resident kernel (option cmvnw_kernel = 4)
   bool has_short_utts = false;           // some utterance has fewer rows than the stream kernel takes
   std::vector<spb::BatchChunk> chunks;   // pipeline units of the host-pointer calls
   std::vector<spb::BatchChunk> groups;   // launch units of the device-pointer calls (runs of chunks)
@@ -306,7 +310,8 @@ int launch_cmvnw_stream(spb_context *ctx, const float *in, float *out, const int
 // whole-utterance-resident single-pass cmvnw (cmvn_resident_kernels.cu): window 301, variance normalisation, 40 columns
 bool cmvnw_resident_supported(int cols, int win, int varnorm);
 int cmvnw_resident_max_rows();
-int launch_cmvnw_resident(spb_context *ctx, const float *in, float *out, const int4 *tiles, int64_t num_tiles);
+int launch_cmvnw_resident(spb_context *ctx, const float *in, float *out, const int4 *tiles, int64_t num_tiles, int cluster = 1);
+int cmvnw_resident_clusters(spb_context *ctx);  // 2-CTA clusters of the resident kernel the device runs at once (0: none)
 // balanced tiles of one utterance of F rows: appends {utt, r0, rows, 0}
 void append_big_tiles(std::vector<int4> &v, int utt, int64_t F, int rmax);
 bool cmvnw_supported(int cols, int win);

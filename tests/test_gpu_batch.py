@@ -353,7 +353,9 @@ def test_single_pass_cmvnw_matches_two_pass_kernels_and_oracle(sp):
     from speaker_verification_b200 import _lib
     rows = [149, 150, 151, 164, 165, 179, 180, 181, 195, 299, 300, 301, 329, 330, 331, 345, 359, 360, 361,
             524, 525, 526, 540, 659, 660, 661, 720, 900, 1998, 3000, 3001, 4801, 5998, 1, 31, 7205,
-            2, 29, 30, 59, 60, 61, 74, 75, 76, 929, 930, 931, 899, 901]
+            2, 29, 30, 59, 60, 61, 74, 75, 76, 929, 930, 931, 899, 901,
+            # 931 .. 1 860 rows: with option cmvnw_kernel=4 a cluster of two CTAs per utterance, halves exchanged over DSMEM
+            932, 959, 960, 961, 1200, 1499, 1500, 1501, 1830, 1859, 1860, 1861]
     lengths = [320 + 160 * r + (7 * i) % 160 for i, r in enumerate(rows)]
     sigs = _signals(900, lengths)
     # digital silence inside an utterance: constant log-mel rows -> zero variance, the reference gives 0 / (0 + eps) = 0
@@ -361,18 +363,21 @@ def test_single_pass_cmvnw_matches_two_pass_kernels_and_oracle(sp):
     arena, starts, lens = batch.pack(sigs)
     fb = batch.FeatureBatch(starts, lens)
     assert [int(f) for f in np.diff(fb.frame_offsets)] == rows
-    # the default: utterances of <= 930 rows resident in shared memory (both stages in one pass, stage 1 in
-    # place: csrc/cmvn_resident_kernels.cu), the longer ones through the two-pass large-tile kernels
-    res = fb.lmfe_cmvnw(arena)
+    # the default: utterances of <= 930 rows resident in one CTA's shared memory (both stages in one pass, stage 1
+    # in place: csrc/cmvn_resident_kernels.cu), longer ones two-pass; option 4: up to 1 860 rows in a 2-CTA
+    # cluster's shared memory (correct, measured slower than two passes: opt-in), only the longer ones two-pass
     with _lib.options(cmvnw_kernel=2):
         two = fb.lmfe_cmvnw(arena)
-    assert np.all(np.isfinite(res))
-    assert np.max(np.abs(res - two)) < 2e-5
-    for s_, got in zip(sigs, fb.split(res)):
-        ref = o.cmvnw_vectorised(o.lmfe(s_, FS), 301, True)
-        if ref.shape[0]:
-            assert float(np.max(np.abs(got - ref))) < TOL, ref.shape
-    assert np.max(np.abs(fb.split(res)[28][400:700])) < 1e-5  # the silent stretch
+    refs = [o.cmvnw_vectorised(o.lmfe(s_, FS), 301, True) for s_ in sigs]
+    for opt in (0, 4):
+        with _lib.options(cmvnw_kernel=opt):
+            res = fb.lmfe_cmvnw(arena)
+        assert np.all(np.isfinite(res)), opt
+        assert np.max(np.abs(res - two)) < 2e-5, opt
+        for ref, got in zip(refs, fb.split(res)):
+            if ref.shape[0]:
+                assert float(np.max(np.abs(got - ref))) < TOL, (opt, ref.shape)
+        assert np.max(np.abs(fb.split(res)[28][400:700])) < 1e-5  # the silent stretch
     with _lib.options(cmvnw_kernel=3):
         one = fb.lmfe_cmvnw(arena)
         # a NaN sample poisons the rows whose windows touch it, as in the two-pass kernels
@@ -382,8 +387,7 @@ def test_single_pass_cmvnw_matches_two_pass_kernels_and_oracle(sp):
     assert np.all(np.isfinite(one))
     assert np.max(np.abs(one - two)) < 2e-5
     worst = 0.0
-    for s, got in zip(sigs, fb.split(one)):
-        ref = o.cmvnw_vectorised(o.lmfe(s, FS), 301, True)
+    for ref, got in zip(refs, fb.split(one)):
         worst = max(worst, float(np.max(np.abs(got - ref))))
     assert worst < TOL, worst
     sil = fb.split(one)[28][400:700]
@@ -396,27 +400,30 @@ def test_single_pass_cmvnw_matches_two_pass_kernels_and_oracle(sp):
 
 
 def test_cmvnw_random_lengths_resident_and_two_pass(sp):
-    """160 utterances of random length (1 .. 1 100 frames, around the resident kernel's 930-row limit and every
-    30-row block phase) in one batch: the default dispatch (resident single pass / two-pass) against the two-pass
+    """160 utterances of random length (1 .. 1 900 frames: around the resident kernel's 930-row limit, the 2-CTA
+    cluster range up to 1 860 of option 4 and every 30-row block phase) in one batch: the default dispatch
+    (resident single pass / two-pass) and option 4 (resident / cluster pairs / two-pass) against the two-pass
     kernels alone and, on every value, against processing.cmvnw(feature.lmfe) of the reference."""
     from speaker_verification_b200 import _lib
     rng = np.random.Generator(np.random.Philox(20261105))
-    rows = np.concatenate([rng.integers(1, 1101, size=140), rng.integers(900, 961, size=20)])
+    rows = np.concatenate([rng.integers(1, 1101, size=110), rng.integers(900, 961, size=20), rng.integers(931, 1900, size=30)])
     lengths = [int(320 + 160 * r + rng.integers(0, 160)) for r in rows]
     sigs = _signals(5000, lengths)
     arena, starts, lens = batch.pack(sigs)
     fb = batch.FeatureBatch(starts, lens)
     assert [int(f) for f in np.diff(fb.frame_offsets)] == [int(r) for r in rows]
-    got = fb.lmfe_cmvnw(arena)
     with _lib.options(cmvnw_kernel=2):
         two = fb.lmfe_cmvnw(arena)
-    assert np.all(np.isfinite(got))
-    assert np.max(np.abs(got - two)) < 2e-5
-    for s_, g_, r in zip(sigs, fb.split(got), rows):
-        if r < 2:
-            continue  # a single frame: the reference's own output is rounding noise over 2^-30
-        ref = o.cmvnw_vectorised(o.lmfe(s_, FS), 301, True)
-        assert np.max(np.abs(g_ - ref)) < TOL, int(r)
+    refs = [o.cmvnw_vectorised(o.lmfe(s_, FS), 301, True) for s_ in sigs]
+    for opt in (0, 4):
+        with _lib.options(cmvnw_kernel=opt):
+            got = fb.lmfe_cmvnw(arena)
+        assert np.all(np.isfinite(got)), opt
+        assert np.max(np.abs(got - two)) < 2e-5, opt
+        for ref, g_, r in zip(refs, fb.split(got), rows):
+            if r < 2:
+                continue  # a single frame: the reference's own output is rounding noise over 2^-30
+            assert np.max(np.abs(g_ - ref)) < TOL, (opt, int(r))
     fb.close()
 
 

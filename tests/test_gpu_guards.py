@@ -33,10 +33,10 @@ def _check_guards(torch, buf, n, what):
 
 
 LENGTHS = [320 + 160 * r + 3 * i for i, r in enumerate(
-    [1, 30, 31, 32, 33, 61, 62, 63, 123, 124, 125, 149, 150, 151, 180, 329, 331, 525, 660, 959, 960, 961, 1998, 3001, 0])]
+    [1, 30, 31, 32, 33, 61, 62, 63, 123, 124, 125, 149, 150, 151, 180, 329, 331, 525, 660, 959, 960, 961, 1859, 1998, 3001, 0])]
 
 
-@pytest.mark.parametrize("opts", [dict(), dict(cmvnw_kernel=3), dict(cmvnw_kernel=1), dict(feature_kernel=2),
+@pytest.mark.parametrize("opts", [dict(), dict(cmvnw_kernel=3), dict(cmvnw_kernel=4), dict(cmvnw_kernel=1), dict(feature_kernel=2),
                                   dict(tc_version=1), dict(tc_epilogue=0)])
 def test_batch_entry_points_write_exactly_their_output(sp, opts):
     import torch
