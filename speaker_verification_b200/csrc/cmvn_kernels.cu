@@ -564,19 +564,19 @@ cmvnw_big_kernel(const CmBigParams p) {
             float2 ov;
             if (v.x > 1e-12f && v.y > 1e-12f) {
               float rx, ry;
-              asm("rsqrt.approx.f32 %0, %1;" : "=f"(rx) : "f"(v.x));
-              asm("rsqrt.approx.f32 %0, %1;" : "=f"(ry) : "f"(v.y));
+              asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(rx) : "f"(v.x));
+              asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(ry) : "f"(v.y));
               const float2 r = make_float2(rx, ry);
               ov = __fmul2_rn(__fmul2_rn(xc, r), __ffma2_rn(r, big_neg(neps), one));
             } else {
               const float vx = v.x < 1e-30f ? 1e-30f : v.x, vy = v.y < 1e-30f ? 1e-30f : v.y;
               float rx, ry, cx, cy;
-              asm("rsqrt.approx.f32 %0, %1;" : "=f"(rx) : "f"(vx));
-              asm("rsqrt.approx.f32 %0, %1;" : "=f"(ry) : "f"(vy));
+              asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(rx) : "f"(vx));
+              asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(ry) : "f"(vy));
               const float2 r = make_float2(rx, ry);
               const float2 d = __ffma2_rn(r, neps, one);
-              asm("rcp.approx.f32 %0, %1;" : "=f"(cx) : "f"(d.x));
-              asm("rcp.approx.f32 %0, %1;" : "=f"(cy) : "f"(d.y));
+              asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(cx) : "f"(d.x));
+              asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(cy) : "f"(d.y));
               ov = __fmul2_rn(__fmul2_rn(xc, r), make_float2(cx, cy));
             }
             *reinterpret_cast<float2 *>(dst) = ov;

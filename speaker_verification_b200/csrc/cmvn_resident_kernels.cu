@@ -346,19 +346,19 @@ __global__ void __launch_bounds__(kResThreads, 1) cmvnw_resident_kernel(const Cm
         float2 ov;
         if (v.x > 1e-12f && v.y > 1e-12f) {
           float rx, ry;
-          asm("rsqrt.approx.f32 %0, %1;" : "=f"(rx) : "f"(v.x));
-          asm("rsqrt.approx.f32 %0, %1;" : "=f"(ry) : "f"(v.y));
+          asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(rx) : "f"(v.x));
+          asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(ry) : "f"(v.y));
           const float2 rr = make_float2(rx, ry);
           ov = __fmul2_rn(__fmul2_rn(xc, rr), __ffma2_rn(rr, res_neg(peps), one));
         } else {
           const float vx = v.x < 1e-30f ? 1e-30f : v.x, vy = v.y < 1e-30f ? 1e-30f : v.y;
           float rx, ry, cx, cy;
-          asm("rsqrt.approx.f32 %0, %1;" : "=f"(rx) : "f"(vx));
-          asm("rsqrt.approx.f32 %0, %1;" : "=f"(ry) : "f"(vy));
+          asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(rx) : "f"(vx));
+          asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(ry) : "f"(vy));
           const float2 rr = make_float2(rx, ry);
           const float2 d = __ffma2_rn(rr, peps, one);
-          asm("rcp.approx.f32 %0, %1;" : "=f"(cx) : "f"(d.x));
-          asm("rcp.approx.f32 %0, %1;" : "=f"(cy) : "f"(d.y));
+          asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(cx) : "f"(d.x));
+          asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(cy) : "f"(d.y));
           ov = __fmul2_rn(__fmul2_rn(xc, rr), make_float2(cx, cy));
         }
         *reinterpret_cast<float2 *>(dst) = ov;

@@ -193,12 +193,12 @@ __device__ __forceinline__ float2 st_normalise(const float2 xc, const float2 D, 
   const float2 v = __ffma2_rn(st_neg(m), m, __ffma2_rn(Q, inv_w, e0));
   const float vx = v.x < 1e-30f ? 1e-30f : v.x, vy = v.y < 1e-30f ? 1e-30f : v.y;
   float rx, ry, cx, cy;
-  asm("rsqrt.approx.f32 %0, %1;" : "=f"(rx) : "f"(vx));
-  asm("rsqrt.approx.f32 %0, %1;" : "=f"(ry) : "f"(vy));
+  asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(rx) : "f"(vx));
+  asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(ry) : "f"(vy));
   const float2 r = make_float2(rx, ry);
   const float2 d = __ffma2_rn(r, make_float2(eps, eps), make_float2(1.f, 1.f));
-  asm("rcp.approx.f32 %0, %1;" : "=f"(cx) : "f"(d.x));
-  asm("rcp.approx.f32 %0, %1;" : "=f"(cy) : "f"(d.y));
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(cx) : "f"(d.x));
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(cy) : "f"(d.y));
   return __fmul2_rn(__fmul2_rn(xc, r), make_float2(cx, cy));
 }
 
