@@ -377,23 +377,31 @@ __device__ __forceinline__ void t2_epilogue_dyn(const T2Params &p, const uint32_
 template <int HALF>
 __device__ __forceinline__ void t2_store_run(float *prow, const float (&ov)[8], const int g0, const int m, const bool row_ok) {
   if (!row_ok) return;
-  int e = g0;
   if (m - g0 + 1 == 8) {
     asm volatile("st.global.v8.f32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::"l"(prow + g0), "f"(ov[0]), "f"(ov[1]),
                  "f"(ov[2]), "f"(ov[3]), "f"(ov[4]), "f"(ov[5]), "f"(ov[6]), "f"(ov[7])
                  : "memory");
     return;
   }
-  while (e <= m) {
+  // a shorter run (g0 and m are compile-time values at every call site): the widest aligned stores, chosen while
+  // the loop unrolls, so that ov[] is only ever indexed statically and stays in registers
+  int skip = 0;
+#pragma unroll
+  for (int k = 0; k < 8; ++k) {
+    const int e = g0 + k;
+    if (e > m) continue;
+    if (skip > 0) {
+      --skip;
+      continue;
+    }
     if ((e & 3) == 0 && e + 3 <= m) {
       *reinterpret_cast<float4 *>(prow + e) = make_float4(ov[e & 7], ov[(e + 1) & 7], ov[(e + 2) & 7], ov[(e + 3) & 7]);
-      e += 4;
+      skip = 3;
     } else if ((e & 1) == 0 && e + 1 <= m) {
       *reinterpret_cast<float2 *>(prow + e) = make_float2(ov[e & 7], ov[(e + 1) & 7]);
-      e += 2;
+      skip = 1;
     } else {
       prow[e] = ov[e & 7];
-      e += 1;
     }
   }
 }
