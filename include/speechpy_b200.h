@@ -156,6 +156,13 @@ typedef struct spb_feature_params {
 SPB_API int spb_plan_create(spb_context *ctx, const spb_feature_params *params,
                     const double *filterbank, spb_plan **plan);
 SPB_API int spb_plan_destroy(spb_plan *plan);
+/* 8f-2: pre-emphasis (sfe/speechpy/processing.py:45-58, shift = 1) as a prologue of the framing kernels: every
+ * feature call on this plan (single signal or batch) then works on y[i] = x[i] - cof * x[i-1], y[0] = x[0] -
+ * cof * x[N-1] (np.roll is circular) of each utterance, computed in float32 while a tile's samples are staged
+ * in shared memory -- the emphasised signal is never written.  Fused into the CUDA-core FFT kernels; plans with
+ * cof != 0 do not use the tensor-core kernel.  cof = 0 (the default) switches it off.  Set it before the plan
+ * is used by concurrent calls. */
+SPB_API int spb_plan_set_preemphasis(spb_plan *plan, double cof);
 
 /* --------------------------------------- a4-a6  mfe / lmfe / mfcc (one signal)
  * sfe/speechpy/feature.py:156-219 (mfe), 222-258 (lmfe), 102-153 (mfcc).

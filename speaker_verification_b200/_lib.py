@@ -48,6 +48,7 @@ PROTOTYPES = {
     "spb_power_spectrum": (C.c_int, [c_vp, c_vp, c_i64, c_i32, c_i32, c_i32, c_vp]),
     "spb_plan_create": (C.c_int, [c_vp, C.POINTER(FeatureParams), c_vp, C.POINTER(c_vp)]),
     "spb_plan_destroy": (C.c_int, [c_vp]),
+    "spb_plan_set_preemphasis": (C.c_int, [c_vp, C.c_double]),
     "spb_mfe": (C.c_int, [c_vp, c_vp, c_vp, c_i32, c_i64, c_vp, c_vp]),
     "spb_lmfe": (C.c_int, [c_vp, c_vp, c_vp, c_i32, c_i64, c_vp]),
     "spb_mfcc": (C.c_int, [c_vp, c_vp, c_vp, c_i32, c_i64, c_vp]),
@@ -178,9 +179,10 @@ class Context:
             self.lib.spb_destroy(self.handle)
             self.handle = None
 
-    def plan(self, L, S, nfft, M, C_, dc, bank: np.ndarray | None, cm_win=0, cm_var=0):
-        """Cached feature plan; `bank` is the dense float64 (M, nfft/2+1) filterbank."""
-        key = (L, S, nfft, M, C_, dc, cm_win, cm_var,
+    def plan(self, L, S, nfft, M, C_, dc, bank: np.ndarray | None, cm_win=0, cm_var=0, preemphasis=0.0):
+        """Cached feature plan; `bank` is the dense float64 (M, nfft/2+1) filterbank.  preemphasis != 0:
+        processing.preemphasis(signal, shift=1, cof=preemphasis) fused into the framing (processing.py:45-58)."""
+        key = (L, S, nfft, M, C_, dc, cm_win, cm_var, float(preemphasis),
                None if bank is None else hash(bank.tobytes()))
         p = self._plans.get(key)
         if p is None:
@@ -191,6 +193,8 @@ class Context:
                 bank = np.ascontiguousarray(bank, dtype=np.float64)
                 bptr = bank.ctypes.data
             check(self.lib.spb_plan_create(self.handle, C.byref(params), bptr, C.byref(h)), self.handle)
+            if preemphasis:
+                check(self.lib.spb_plan_set_preemphasis(h, float(preemphasis)), self.handle)
             self._plans[key] = p = h
         return p
 

@@ -97,13 +97,15 @@ class FeatureBatch:
     """Device descriptors of a ragged batch for one feature configuration.
 
     Parameters mirror ``speechpy.feature.lmfe`` / ``mfcc`` (feature.py:102-112,222-223) and
-    ``processing.cmvnw`` (processing.py:274).
+    ``processing.cmvnw`` (processing.py:274).  ``preemphasis`` != 0: every utterance is run through
+    ``processing.preemphasis(signal, shift=1, cof=preemphasis)`` (processing.py:45-58) first, fused into the
+    framing kernel (the emphasised signal is never written to memory).
     """
 
     def __init__(self, starts, lengths, sampling_frequency=16000, frame_length=0.020,
                  frame_stride=0.01, num_filters=40, fft_length=512, low_frequency=0,
                  high_frequency=None, num_cepstral=13, dc_elimination=True, win_size=301,
-                 variance_normalization=True, device=None):
+                 variance_normalization=True, device=None, preemphasis=0.0):
         assert isinstance(win_size, int), "Size must be of type 'int'!"
         assert win_size % 2 == 1, "Windows size must be odd!"
         self.ctx = _lib.context(device)
@@ -117,7 +119,7 @@ class FeatureBatch:
         self.num_cepstral = min(int(num_cepstral), int(num_filters))
         self.plan = self.ctx.plan(L, int(S), int(fft_length), self.num_filters, self.num_cepstral,
                                   1 if dc_elimination else 0, bank, int(win_size),
-                                  1 if variance_normalization else 0)
+                                  1 if variance_normalization else 0, preemphasis=float(preemphasis))
         h = _lib.c_vp()
         _lib.check(self.ctx.lib.spb_batch_create(self.ctx.handle, self.plan, _lib.ptr(self.starts),
                                                  _lib.ptr(self.lengths), len(self.starts), C.byref(h)),

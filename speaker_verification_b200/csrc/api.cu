@@ -527,6 +527,20 @@ int spb_plan_create(spb_context *ctx, const spb_feature_params *params, const do
   return SPB_OK;
 }
 
+// Pre-emphasis as a prologue of the framing (processing.py:45-58 with shift = 1): the
+// feature launches of this plan see y[i] = x[i] - cof x[i-1] (y[0] wraps to the utterance's last sample, as
+// np.roll does) without the emphasised signal ever being written.  Fused into the CUDA-core FFT kernels
+// (staged tile transformed in shared memory); the tensor-core kernel does not take it, so such plans run on
+// the FFT kernels.  cof = 0 switches it off again.
+int spb_plan_set_preemphasis(spb_plan *pl, double cof) {
+  if (!pl) return SPB_ERR_INVALID;
+  spb_context *ctx = pl->ctx;
+  SPB_REQUIRE(ctx, isfinite(cof), "plan_set_preemphasis: cof must be finite");
+  pl->pre_cof = cof;
+  pl->tc_ok = pl->tc_built && cof == 0.0;
+  return SPB_OK;
+}
+
 int spb_plan_destroy(spb_plan *pl) {
   if (!pl) return SPB_OK;
   if (pl->ctx) cudaSetDevice(pl->ctx->device);
@@ -773,6 +787,7 @@ int spb_batch_create(spb_context *ctx, const spb_plan *plan, const int64_t *star
   if ((e = cudaMalloc(&b->d_starts, u_bytes * 8)) != cudaSuccess ||
       (e = cudaMalloc(&b->d_nframes, u_bytes * 4)) != cudaSuccess ||
       (e = cudaMalloc(&b->d_frame_offsets, (u_bytes + 1) * 8)) != cudaSuccess ||
+      (e = cudaMalloc(&b->d_last, u_bytes * 8)) != cudaSuccess ||
       (e = cudaMalloc(&b->d_tiles, (size_t)std::max<int64_t>(b->total_tiles, 1) * sizeof(int2))) != cudaSuccess ||
       (e = cudaMalloc(&b->d_ftiles, (size_t)std::max<int64_t>(b->total_tiles, 1) * sizeof(FftTile))) != cudaSuccess ||
       (e = cudaMalloc(&b->d_cm_tiles, (size_t)std::max<int64_t>(b->total_cm_tiles, 1) * sizeof(int2))) != cudaSuccess ||
@@ -783,8 +798,11 @@ int spb_batch_create(spb_context *ctx, const spb_plan *plan, const int64_t *star
       (e = cudaMalloc(&d_tile_off, (u_bytes + 1) * 8)) != cudaSuccess ||
       (e = cudaMalloc(&d_cm_off, (u_bytes + 1) * 8)) != cudaSuccess)
     return cleanup(e, "cudaMalloc(batch)");
+  std::vector<int64_t> h_last((size_t)std::max<int64_t>(U, 1), 0);
+  for (int64_t u = 0; u < U; ++u) h_last[u] = starts[u] + std::max<int64_t>(lengths[u], 1) - 1;
   if (U > 0) {
     if ((e = cudaMemcpyAsync(b->d_starts, starts, (size_t)U * 8, cudaMemcpyHostToDevice, ctx->stream)) != cudaSuccess ||
+        (e = cudaMemcpyAsync(b->d_last, h_last.data(), (size_t)U * 8, cudaMemcpyHostToDevice, ctx->stream)) != cudaSuccess ||
         (e = cudaMemcpyAsync(b->d_nframes, nframes.data(), (size_t)U * 4, cudaMemcpyHostToDevice, ctx->stream)) != cudaSuccess ||
         (e = cudaMemcpyAsync(b->d_frame_offsets, b->h_frame_offsets.data(), (size_t)(U + 1) * 8, cudaMemcpyHostToDevice, ctx->stream)) != cudaSuccess ||
         (e = cudaMemcpyAsync(d_tile_off, tile_off.data(), (size_t)(U + 1) * 8, cudaMemcpyHostToDevice, ctx->stream)) != cudaSuccess ||
@@ -828,6 +846,7 @@ int spb_batch_destroy(spb_batch *b) {
   cudaFree(b->d_starts);
   cudaFree(b->d_nframes);
   cudaFree(b->d_frame_offsets);
+  cudaFree(b->d_last);
   cudaFree(b->d_tiles);
   cudaFree(b->d_ftiles);
   cudaFree(b->d_tc_groups);
@@ -864,6 +883,9 @@ static void fill_feat_args(FeatArgs &a, const spb_batch *b, const float *d_sampl
   a.starts = b->d_starts;
   a.nframes = b->d_nframes;
   a.frame_offsets = b->d_frame_offsets;
+  a.last = b->d_last;
+  a.num_utts = b->U;
+  a.pre_cof = pl->pre_cof;
   a.tiles = b->d_tiles;
   a.ftiles = b->d_ftiles;
   a.plan = pl;

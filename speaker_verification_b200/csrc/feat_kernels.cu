@@ -52,7 +52,39 @@ struct FeatParams {
   int need_level;     // per-frame sum x^2 for the exactness guard (redo.entries != nullptr, mfe / lmfe output)
   RedoList redo;      // filters below tau x sum x^2 are listed for the float64 redo (redo_kernels.cu)
   const int *run_if;  // fast512: when set, the launch is a no-op unless *run_if != 0
+  float pre_cof;      // pre-emphasis fused into the framing (0: off); processing.py:45-58, shift = 1
+  const int64_t *last;  // [U] index of each utterance's last sample: what sample 0 wraps to (np.roll)
 };
+
+// Pre-emphasis of a staged tile, in place: y[i] = x[i] - cof x[i-1], `prior` = the sample in front of the
+// tile's first one (the utterance's LAST sample for its first tile: np.roll is circular).  Every thread owns
+// a run of k consecutive samples (k odd: the strided walks touch 32 different banks) and reads it, with the
+// sample in front of it, into registers before anybody stores (longer runs: walked downwards, so that x[i-1] is
+// still the original when y[i] is formed).  Called by the whole CTA; ends with a barrier.
+__device__ __forceinline__ void preemphasis_tile(float *s, const int count, const float prior, const float cof,
+                                                 const int tid, const int nthreads) {
+  constexpr int kRun = 24;  // runs up to this length go through registers (the default tile: 5 280 samples / 256 threads = 21)
+  const int k = ((count + nthreads - 1) / nthreads) | 1;
+  const int lo = tid * k, hi = min(lo + k, count);
+  float front = 0.f;
+  if (lo < count) front = lo > 0 ? s[lo - 1] : prior;
+  if (k <= kRun) {
+    float r[kRun];
+#pragma unroll
+    for (int j = 0; j < kRun; ++j) r[j] = (lo + j < hi) ? s[lo + j] : 0.f;
+    __syncthreads();  // every thread holds its run and the sample in front of it
+#pragma unroll
+    for (int j = 0; j < kRun; ++j)
+      if (lo + j < hi) s[lo + j] = fmaf(-cof, j > 0 ? r[j - 1] : front, r[j]);
+  } else {
+    __syncthreads();
+    for (int i = hi - 1; i >= lo; --i) {
+      const float pv = (i > lo) ? s[i - 1] : front;
+      s[i] = fmaf(-cof, pv, s[i]);
+    }
+  }
+  __syncthreads();
+}
 
 // ------------------------------------------------------------------------------------
 // Output stage shared by both kernels.  s_p: [nf][pstride] UNSCALED |X|^2 rows (bins
@@ -362,12 +394,15 @@ features_fast512(const FeatParams p) {
     cp_async16(&s_fd[slot][1], src + 1);
     cp_async_commit();
   };
-  auto stage = [&](int slot, int b, long long &row0, int &nf, bool &bulk, long long &gs) {
+  auto stage = [&](int slot, int b, long long &row0, int &nf, bool &bulk, long long &gs, float &pri) {
     const int4 d0 = s_fd[slot][0];
     const longlong2 d1 = *reinterpret_cast<const longlong2 *>(&s_fd[slot][1]);
     nf = d0.z;
     const long long gstart = d1.x;
     gs = gstart;
+    // pre-emphasis: the sample in front of the tile (first tile of an utterance: its last sample), loaded a
+    // tile ahead like the tile itself
+    if (p.pre_cof != 0.f) pri = __ldg(p.samples + ((d0.y == 0) ? p.last[d0.x] : gstart - 1));
     row0 = d1.y;
     const int count = (nf - 1) * S + L;
     const float *src = p.samples + gstart;
@@ -389,6 +424,7 @@ features_fast512(const FeatParams p) {
   long long tile = blockIdx.x;
   int buf = 0;
   long long row0 = 0, gs = 0;
+  float pri = 0.f;
   int nf = 0;
   bool bulk = false;
   if (tid == 0) {
@@ -397,15 +433,16 @@ features_fast512(const FeatParams p) {
     cp_async_wait<0>();
   }
   __syncthreads();
-  if (tile < p.num_tiles) stage(0, 0, row0, nf, bulk, gs);
+  if (tile < p.num_tiles) stage(0, 0, row0, nf, bulk, gs, pri);
   for (; tile < p.num_tiles; buf ^= 1) {  // descriptor of the tile in sample buffer b sits in ring slot b
     const long long next = tile + gridDim.x;
     long long n_row0 = 0, n_gs = 0;
+    float n_pri = 0.f;
     int n_nf = 0;
     bool n_bulk = false;
     // prefetch the next tile while this one is transformed (its buffer was last read in
     // phase B of the previous iteration, which every thread has left)
-    if (next < p.num_tiles) stage(buf ^ 1, buf ^ 1, n_row0, n_nf, n_bulk, n_gs);
+    if (next < p.num_tiles) stage(buf ^ 1, buf ^ 1, n_row0, n_nf, n_bulk, n_gs, n_pri);
     // slot `buf` (this tile's descriptor, consumed an iteration ago) takes the tile after next;
     // thread 0 waits for it just before the barrier that ends phase B
     const bool refill = tid == 0 && next + gridDim.x < p.num_tiles;
@@ -416,6 +453,8 @@ features_fast512(const FeatParams p) {
     }
     __syncthreads();  // samples of this tile visible; previous tile's phase C is finished
     const float *s_x = s_xbuf + buf * xoff;
+    if (p.pre_cof != 0.f)  // pre-emphasis as a prologue of the framing: the staged tile, in place
+      preemphasis_tile(s_xbuf + buf * xoff, (nf - 1) * S + L, pri, p.pre_cof, tid, kFastThreads);
 
     // ---- phase B: each half-warp transforms two frames at once (packed fp32, fft_math2.cuh)
     {
@@ -551,7 +590,7 @@ features_fast512(const FeatParams p) {
       output_stage<kTile, false>(p, s_p, PSTRIDE, s_en, s_a, s_b, s_bw, s_bmeta, s_dct, nf, row0, s_rd, s_wr,
                                  s_U, s_D, fm, s_lvl, gs);
     tile = next;
-    row0 = n_row0; nf = n_nf; bulk = n_bulk; gs = n_gs;
+    row0 = n_row0; nf = n_nf; bulk = n_bulk; gs = n_gs; pri = n_pri;
   }
 }
 
@@ -650,12 +689,15 @@ features_fast1024(const FeatParams p) {
     cp_async16(&s_fd[slot][1], src + 1);
     cp_async_commit();
   };
-  auto stage = [&](int slot, int b, long long &row0, int &nf, bool &bulk, long long &gs) {
+  auto stage = [&](int slot, int b, long long &row0, int &nf, bool &bulk, long long &gs, float &pri) {
     const int4 d0 = s_fd[slot][0];
     const longlong2 d1 = *reinterpret_cast<const longlong2 *>(&s_fd[slot][1]);
     nf = d0.z;
     const long long gstart = d1.x;
     gs = gstart;
+    // pre-emphasis: the sample in front of the tile (first tile of an utterance: its last sample), loaded a
+    // tile ahead like the tile itself
+    if (p.pre_cof != 0.f) pri = __ldg(p.samples + ((d0.y == 0) ? p.last[d0.x] : gstart - 1));
     row0 = d1.y;
     const int count = (nf - 1) * S + L;
     const float *src = p.samples + gstart;
@@ -677,6 +719,7 @@ features_fast1024(const FeatParams p) {
   long long tile = blockIdx.x;
   int buf = 0;
   long long row0 = 0, gs = 0;
+  float pri = 0.f;
   int nf = 0;
   bool bulk = false;
   if (tid == 0) {
@@ -685,13 +728,14 @@ features_fast1024(const FeatParams p) {
     cp_async_wait<0>();
   }
   __syncthreads();
-  if (tile < p.num_tiles) stage(0, 0, row0, nf, bulk, gs);
+  if (tile < p.num_tiles) stage(0, 0, row0, nf, bulk, gs, pri);
   for (; tile < p.num_tiles; buf ^= 1) {
     const long long next = tile + gridDim.x;
     long long n_row0 = 0, n_gs = 0;
+    float n_pri = 0.f;
     int n_nf = 0;
     bool n_bulk = false;
-    if (next < p.num_tiles) stage(buf ^ 1, buf ^ 1, n_row0, n_nf, n_bulk, n_gs);
+    if (next < p.num_tiles) stage(buf ^ 1, buf ^ 1, n_row0, n_nf, n_bulk, n_gs, n_pri);
     const bool refill = tid == 0 && next + gridDim.x < p.num_tiles;
     if (refill) fetch_desc(next + gridDim.x, buf);
     if (bulk) {
@@ -700,6 +744,8 @@ features_fast1024(const FeatParams p) {
     }
     __syncthreads();  // samples of this tile visible; previous tile's phase C is finished
     const float *s_x = s_xbuf + buf * xoff;
+    if (p.pre_cof != 0.f)  // pre-emphasis as a prologue of the framing: the staged tile, in place
+      preemphasis_tile(s_xbuf + buf * xoff, (nf - 1) * S + L, pri, p.pre_cof, tid, kF1kThreads);
 
     // ---- phase B: one frame per warp and pass
     for (int pass = 0; pass < kTile / kF1kWarps; ++pass) {
@@ -787,7 +833,7 @@ features_fast1024(const FeatParams p) {
       output_stage<kTile, false>(p, s_p, PSTRIDE, s_en, s_a, s_b, s_bw, s_bmeta, s_dct, nf, row0, s_rd, s_wr,
                                  s_U, s_D, fm, s_lvl, gs);
     tile = next;
-    row0 = n_row0; nf = n_nf; bulk = n_bulk; gs = n_gs;
+    row0 = n_row0; nf = n_nf; bulk = n_bulk; gs = n_gs; pri = n_pri;
   }
 }
 
@@ -831,11 +877,19 @@ features_generic(const FeatParams p) {
       __syncthreads();
       if (warp < nf) {
         const float *x = p.samples + p.starts[utt] + (long long)(f0 + warp) * p.S;
+        // pre-emphasis fused into the load: y[i] = x[i] - cof x[i-1]; sample 0 of the utterance wraps to its last
+        const float cof = p.pre_cof;
+        const float *xw = (cof != 0.f && f0 + warp == 0) ? p.samples + p.last[utt] : x - 1;
+        auto ld = [&](const int i) {
+          float v = __ldg(x + i);
+          if (cof != 0.f) v = fmaf(-cof, __ldg(i > 0 ? x + i - 1 : xw), v);
+          return v;
+        };
         // bit-reversed load of z[m] = x[2m] + i x[2m+1]
         float sumsq = 0.f;
         for (int m = lane; m < nc; m += 32) {
-          float re = (2 * m < Leff) ? __ldg(x + 2 * m) : 0.f;
-          float im = (2 * m + 1 < Leff) ? __ldg(x + 2 * m + 1) : 0.f;
+          float re = (2 * m < Leff) ? ld(2 * m) : 0.f;
+          float im = (2 * m + 1 < Leff) ? ld(2 * m + 1) : 0.f;
           sumsq = fmaf(re, re, fmaf(im, im, sumsq));
           const int r = __brev((unsigned)m) >> (32 - p.log2nc);
           z[r] = c_make(re, im);
@@ -901,6 +955,8 @@ static FeatParams make_params(const FeatArgs &a, const FftTables &t) {
   p.tiles = a.tiles;
   p.ftiles = a.ftiles;
   p.run_if = a.run_if;
+  p.pre_cof = (float)a.pre_cof;
+  p.last = a.last;
   p.num_tiles = a.num_tiles;
   p.L = a.L; p.S = a.S; p.K = a.K;
   p.M = a.M; p.C = a.C; p.dc_elim = a.dc_elim;

@@ -639,7 +639,8 @@ int build_tc_plan(spb_context *ctx, spb_plan *pl, const float4 *seg_rd) {
       (e = cudaMemcpy(pl->d_tc2_w, w2.data(), 4 * kT2BMat, cudaMemcpyHostToDevice)) != cudaSuccess)
     return cuda_fail(ctx, e, "cudaMemcpy(tc plan)");
   pl->tc_serial = g_tc_serial.fetch_add(1);
-  pl->tc_ok = true;
+  pl->tc_built = true;
+  pl->tc_ok = pl->pre_cof == 0.0;
   return SPB_OK;
 }
 

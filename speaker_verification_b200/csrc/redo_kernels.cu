@@ -30,10 +30,25 @@ struct RedoParams {
   const double2 *tw;         // [nfft] (cos, -sin)(2 pi r / nfft)
   int mfe;                   // 1: energies (no log)
   float *out;
+  double pre_cof;            // pre-emphasis of the plan (0: off), applied in float64 like processing.py:45-58
+  const int64_t *last;       // [U] index of each utterance's last sample
+  const int64_t *frame_offsets;  // [U+1]
+  long long num_utts;
 };
 
+// the sample in front of a frame that starts at arena offset soff and is output row `row`: the previous sample,
+// or -- first frame of its utterance (np.roll is circular) -- the utterance's last one
+__device__ __forceinline__ const float *redo_prior(const RedoParams &p, const long long soff, const long long row) {
+  long long lo = 0, hi = p.num_utts;  // frame_offsets[lo] <= row < frame_offsets[hi]
+  while (hi - lo > 1) {
+    const long long mid = (lo + hi) >> 1;
+    if (p.frame_offsets[mid] <= row) lo = mid; else hi = mid;
+  }
+  return (p.frame_offsets[lo] == row) ? p.samples + p.last[lo] : p.samples + soff - 1;
+}
+
 // one (frame, filter) by a whole warp; every lane returns the value
-__device__ __forceinline__ float redo_value(const RedoParams &p, const float *x, const int m, const int lane) {
+__device__ __forceinline__ float redo_value(const RedoParams &p, const float *x, const float *xprior, const int m, const int lane) {
   const int lo = p.band_lo[m], n = p.band_n[m];
   const float *w = p.band_w + p.band_off[m];
   const int Leff = min(p.L, p.nfft);  // numpy rfft(n=): rows longer than NFFT are truncated
@@ -46,7 +61,8 @@ __device__ __forceinline__ float redo_value(const RedoParams &p, const float *x,
     double re = 0.0, im = 0.0;
     for (int i = lane; i < Leff; i += 32) {
       const double2 c = p.tw[(int)(((long long)k * i) & mask)];
-      const double v = (double)x[i];
+      double v = (double)x[i];
+      if (p.pre_cof != 0.0) v -= p.pre_cof * (double)(i > 0 ? x[i - 1] : *xprior);
       re = fma(v, c.x, re);
       im = fma(v, c.y, im);
     }
@@ -69,7 +85,8 @@ __global__ void __launch_bounds__(256) redo_list_kernel(const RedoParams p) {
   for (int e = blockIdx.x * wpb + (threadIdx.x >> 5); e < total; e += gridDim.x * wpb) {
     const RedoEntry en = p.list.entries[e];
     const int m = (int)(en.oidx % p.M);
-    const float v = redo_value(p, p.samples + en.soff, m, lane);
+    const float *xp = (p.pre_cof != 0.0) ? redo_prior(p, en.soff, en.oidx / p.M) : nullptr;
+    const float v = redo_value(p, p.samples + en.soff, xp, m, lane);
     if (lane == 0) p.out[en.oidx] = v;
   }
 }
@@ -86,7 +103,9 @@ __global__ void __launch_bounds__(256) redo_all_kernel(const RedoParams p) {
     const int f = (int)(tf - tile * kFftTileFrames);
     const FftTile td = p.ftiles[tile];
     if (f >= td.nf) continue;
-    const float v = redo_value(p, p.samples + td.gstart + (long long)f * p.S, m, lane);
+    const long long soff = td.gstart + (long long)f * p.S;
+    const float *xp = (p.pre_cof == 0.0) ? nullptr : (td.f0 + f == 0) ? p.samples + p.last[td.utt] : p.samples + soff - 1;
+    const float v = redo_value(p, p.samples + soff, xp, m, lane);
     if (lane == 0) p.out[(td.row0 + f) * p.M + m] = v;
   }
 }
@@ -112,6 +131,10 @@ int launch_redo(spb_context *ctx, const FeatArgs &a, const RedoList &list, const
   p.tw = t.d_tw64;
   p.mfe = (a.mode == FEAT_MFE) ? 1 : 0;
   p.out = a.out;
+  p.pre_cof = a.pre_cof;
+  p.last = a.last;
+  p.frame_offsets = a.frame_offsets;
+  p.num_utts = a.num_utts;
   const int grid = ctx->sm_count * 4;
   redo_list_kernel<<<grid, 256, 0, ctx->stream>>>(p);
   SPB_LAUNCH_CHECK(ctx, "redo_list");

@@ -90,6 +90,8 @@ struct spb_plan {
   // tensor-core hop-DFT kernel (feat_tc_kernels.cu): fp16 hi/lo DFT matrix in its shared-memory
   // layout, per-bin {rise, fall, cos, sin}; tc_ok == false: plan shape not covered
   bool tc_ok = false;
+  bool tc_built = false;   // build_tc_plan succeeded (tc_ok = tc_built && no pre-emphasis)
+  double pre_cof = 0.0;    // pre-emphasis fused into the framing of the FFT kernels (spb_plan_set_preemphasis); 0: off
   void *d_tc_whi = nullptr, *d_tc_wlo = nullptr;
   std::vector<float> h_tc_tab;        // [2][128][4]: per epilogue half {rise, fall, cos, sin}
   uint32_t tc_endmask[2][4] = {{0, 0, 0, 0}, {0, 0, 0, 0}};
@@ -184,6 +186,7 @@ struct spb_batch {
   int64_t *d_starts = nullptr;           // [U]
   int32_t *d_nframes = nullptr;          // [U]
   int64_t *d_frame_offsets = nullptr;    // [U+1]
+  int64_t *d_last = nullptr;             // [U] arena index of each utterance's last sample (pre-emphasis wraps to it)
   int2 *d_tiles = nullptr;               // [total_tiles] {utt, first frame}
   spb::FftTile *d_ftiles = nullptr;      // [total_tiles] full descriptors for the fast kernel
   int2 *d_cm_tiles = nullptr;            // [total_cm_tiles] {utt, first row}
@@ -252,6 +255,9 @@ struct FeatArgs {
   const int64_t *starts;     // [U]
   const int32_t *nframes;    // [U]
   const int64_t *frame_offsets;  // [U+1]
+  const int64_t *last = nullptr; // [U] index of each utterance's last sample (pre-emphasis only)
+  int64_t num_utts = 0;
+  double pre_cof = 0.0;          // pre-emphasis coefficient (0: off); processing.py:45-58 with shift = 1
   const int2 *tiles;         // [num_tiles]
   const FftTile *ftiles;     // [num_tiles] or nullptr
   const TcGroup *tc_groups = nullptr;  // tensor-core kernel: groups of this launch (4 per tile) or nullptr

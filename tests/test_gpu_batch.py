@@ -477,3 +477,61 @@ def test_nan_samples_poison_the_window_like_the_reference(sp):
                 assert np.max(np.abs(got[ok] - ref[ok])) < TOL
         fb.close()
     assert np.isnan(o.cmvnw_vectorised(lm, 301, True)).all()          # variance mode: +-300 rows cover this utterance
+
+
+def _lmfe_dev(fb, arena):
+    import torch
+    d = torch.from_numpy(arena).cuda()
+    out = torch.full((fb.total_frames, fb.num_filters), float("nan"), dtype=torch.float32, device="cuda")
+    fb.lmfe_dev(d.data_ptr(), d.numel(), out.data_ptr())
+    fb.ctx.sync()
+    return out.cpu().numpy()
+
+
+@pytest.mark.parametrize("kw", [dict(), dict(fft_length=1024, frame_length=0.025), dict(fft_length=256, frame_length=0.016, frame_stride=0.008, num_filters=26)])
+def test_preemphasis_fused_into_the_framing(sp, kw):
+    """FeatureBatch(preemphasis=0.98): processing.preemphasis(signal, shift=1, cof) (processing.py:45-58) as a
+    prologue of the framing kernels -- every utterance's y[i] = x[i] - cof x[i-1], y[0] wrapping to its LAST sample
+    (np.roll), formed while the tile is staged in shared memory.  Against the reference chain
+    lmfe(preemphasis(x)) / cmvnw / mfcc + deltas in float64, on the three FFT kernels (NFFT 512, 1024, generic),
+    with unaligned starts (plain loads instead of the bulk copy), a loud last sample (so that a missed wrap
+    shows) and lengths around the 32-frame tile boundary."""
+    cof = 0.98
+    L = int(round(FS * kw.get("frame_length", 0.020)))
+    S = int(round(FS * kw.get("frame_stride", 0.010)))
+    lengths = [L, L + S - 1, L + S, L + 31 * S, L + 32 * S, L + 33 * S + 7, 64000, 35001, 20002, 100003]
+    sigs = _signals(7100, lengths)
+    for s_ in sigs:
+        s_[-1] = 0.9  # the sample y[0] wraps to
+    refs = [o.preemphasis(s_.astype(np.float64), 1, cof) for s_ in sigs]
+    okw = {k: v for k, v in kw.items()}
+    for aligned in (True, False):
+        if aligned:
+            arena, starts, lens = batch.pack(sigs)
+        else:
+            lens = np.array(lengths, dtype=np.int64)
+            starts = np.cumsum([3] + [n + 5 for n in lengths[:-1]]).astype(np.int64)
+            arena = np.zeros(int(starts[-1] + lens[-1]) + 8, dtype=np.float32)
+            for s_, st in zip(sigs, starts):
+                arena[st:st + len(s_)] = s_
+        fb = batch.FeatureBatch(starts, lens, preemphasis=cof, **kw)
+        plain = batch.FeatureBatch(starts, lens, **kw)
+        lm = fb.split(_lmfe_dev(fb, arena))
+        cm = fb.split(fb.lmfe_cmvnw(arena))
+        mf = fb.split(fb.mfcc_delta(arena))
+        lm_plain = fb.split(_lmfe_dev(plain, arena))
+        for y, a, b_, c_, d_ in zip(refs, lm, cm, mf, lm_plain):
+            ref = o.lmfe(y, FS, **okw)
+            assert a.shape == ref.shape
+            if not ref.shape[0]:
+                continue
+            assert np.max(np.abs(a - ref)) < TOL, (aligned, len(y))
+            assert np.max(np.abs(a - d_)) > 0.1  # it is not the un-emphasised signal
+            assert np.max(np.abs(b_ - o.cmvnw_vectorised(ref, 301, True))) < TOL, (aligned, len(y))
+            # mfcc straight out of the FFT kernels has no float64 redo of low-energy filters (only their mfe / lmfe
+            # output and the tensor-core lmfe -> mfcc path have): with the 26-filter bank over 129 bins the lowest
+            # filter is one bin next to DC, which pre-emphasis pushes 34 dB down -- float32 resolves it to 3e-4
+            mtol = 1e-3 if kw.get("fft_length") == 256 else TOL
+            assert np.max(np.abs(c_ - o.extract_derivative_feature(o.mfcc(y, FS, **okw)))) < mtol, (aligned, len(y))
+        fb.close()
+        plain.close()
