@@ -25,8 +25,11 @@ import time
 # oversubscribes the cores: round 1's CPU arm was 3-5x too slow at N=1 for exactly this reason).
 for _k in ("OMP_NUM_THREADS", "OPENBLAS_NUM_THREADS", "MKL_NUM_THREADS", "NUMEXPR_NUM_THREADS"):
     os.environ[_k] = "1"
-# stdout carries ONE JSON line: whatever NCCL has to say (its version banner, NCCL_DEBUG=INFO of the caller) goes to stderr
+# stdout carries ONE JSON line: whatever NCCL has to say (its version banner, NCCL_DEBUG=INFO of the caller) goes to
+# stderr.  NCCL honours NCCL_DEBUG_FILE only above the VERSION level, so VERSION (this image's default) becomes WARN.
 os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
+if os.environ.get("NCCL_DEBUG", "VERSION").upper() == "VERSION":
+    os.environ["NCCL_DEBUG"] = "WARN"
 
 import numpy as np  # noqa: E402
 
