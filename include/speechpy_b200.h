@@ -172,8 +172,8 @@ SPB_API int spb_plan_set_preemphasis(spb_plan *plan, double cof);
  * become float64 eps before the log (functions.py:55-62).
  * Deviation from the reference: framing, FFT and filterbank run in float32 on the device (the
  * signal is narrowed after upload, results widened to float64); log-mel / MFCC values are within
- * 1e-4 of the float64 reference on every value (filters whose energy is too low for float32 are
- * recomputed in float64, csrc/redo_kernels.cu). */
+ * 1e-4 of the float64 reference on every value (filters whose energy is too low for float32 -- for
+ * mfcc: the rows that hold one -- are recomputed in float64, csrc/redo_kernels.cu). */
 SPB_API int spb_mfe(spb_context *ctx, const spb_plan *plan, const void *sig, int32_t dtype,
             int64_t num_samples, double *feat, double *energy);
 SPB_API int spb_lmfe(spb_context *ctx, const spb_plan *plan, const void *sig, int32_t dtype,

@@ -924,7 +924,11 @@ static int setup_redo(spb_context *ctx, FeatArgs &a, int64_t rows, bool tc) {
   a.redo_tc = RedoList();
   a.redo_fft = RedoList();
   const Options &opt = options();
-  if (!opt.redo || !a.plan || a.M < 1 || !(a.mode == FEAT_MFE || a.mode == FEAT_LMFE)) return SPB_OK;
+  if (!opt.redo || !a.plan || a.M < 1 || a.mode < FEAT_MFE) return SPB_OK;
+  // mfcc modes: the FFT kernels list whole rows (redo_kernels.cu recomputes them in float64); the tensor-core kernel
+  // only ever produces mfe / lmfe rows
+  if (a.mode >= FEAT_MFCC && (a.C < 1 || a.dct == nullptr)) return SPB_OK;
+  if (a.mode >= FEAT_MFCC) tc = false;
   const int64_t cap = std::min<int64_t>(std::max<int64_t>(rows / 4, 65536), (int64_t)1 << 26);
   int *flags = a.plan->d_tc_flag;
   if (tc) {

@@ -168,12 +168,13 @@ __device__ __forceinline__ void output_stage(const FeatParams &p, const float *s
       float *pa = s_a + fm.f0 * astride + m;
       float *dst = p.out + (row0 + fm.f0) * M + m;  // tile rows are contiguous in global memory
       const int ustep = rpp * upitch, astep = rpp * astride, dstep = rpp * M;
-      const bool guard = direct && p.need_level != 0;
+      const bool guard = p.need_level != 0;
       for (int f = fm.f0; f < nf; f += rpp) {
         const float raw = *pu + *pd;
-        // exactness guard: fp32 cannot resolve a filter this far below the frame's level
+        // exactness guard: fp32 cannot resolve a filter this far below the frame's level (mfe / lmfe: the value
+        // is listed; mfcc modes: its whole row, which mixes the filters)
         if (guard && raw < p.redo.tau * s_lvl[f])
-          redo_push(p.redo, gstart + (long long)f * p.S, (row0 + f) * (long long)M + m);
+          redo_push(p.redo, gstart + (long long)f * p.S, direct ? (row0 + f) * (long long)M + m : row0 + f);
         float acc = raw * scale;
         if (acc == 0.f) acc = kEpsF64AsF32;  // functions.zero_handling (feature.py:217)
         const float v = (mode == FEAT_MFE) ? acc : __logf(acc);
@@ -207,7 +208,8 @@ __device__ __forceinline__ void output_stage(const FeatParams &p, const float *s
           acc = fmaf(w.w, pr[k + 3], acc);
         }
         if (p.need_level != 0 && acc < p.redo.tau * s_lvl[f])
-          redo_push(p.redo, gstart + (long long)f * p.S, (row0 + f) * (long long)M + m);
+          redo_push(p.redo, gstart + (long long)f * p.S,
+                    (p.mode == FEAT_MFE || p.mode == FEAT_LMFE) ? (row0 + f) * (long long)M + m : row0 + f);
         acc *= scale;
         if (acc == 0.f) acc = kEpsF64AsF32;  // functions.zero_handling (feature.py:217)
         s_a[f * astride + m] = (p.mode == FEAT_MFE) ? acc : __logf(acc);
@@ -978,7 +980,7 @@ static FeatParams make_params(const FeatArgs &a, const FftTables &t) {
   p.need_energy = (a.mode == FEAT_MFE && a.energy != nullptr) ||
                   (a.mode >= FEAT_MFCC && a.dc_elim);
   p.redo = a.redo_fft;
-  p.need_level = (a.redo_fft.entries != nullptr && (a.mode == FEAT_MFE || a.mode == FEAT_LMFE)) ? 1 : 0;
+  p.need_level = (a.redo_fft.entries != nullptr && a.mode >= FEAT_MFE) ? 1 : 0;
   return p;
 }
 

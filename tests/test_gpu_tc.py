@@ -284,3 +284,29 @@ def test_full_size_properties_cfg4(sp):
         ref = o.cmvnw_vectorised(o.lmfe(x, FS), 301, True)
         assert np.max(np.abs(got - ref)) < TOL, u
     fb.close()
+
+
+@pytest.mark.parametrize("kw", [dict(), dict(fft_length=1024, frame_length=0.025), dict(fft_length=256, frame_length=0.016, frame_stride=0.008)])
+def test_mfcc_rows_of_the_fft_kernels_are_guarded(sp, kw):
+    """mfcc + deltas straight out of the CUDA-core FFT kernels (feature_kernel=2; every shape the tensor-core kernel does
+    not take ends up there): every value of 48 cfg3-shaped utterances within 1e-4 of the float64 reference
+    (feature.py:102-153, 261-282).  A row in which some filter lies too far below the frame's level for float32 is
+    listed by the kernel and recomputed whole in float64 (redo_kernels.cu: log-mel of all filters, DCT, ln(energy),
+    deltas); pre-emphasis makes such rows common (the lowest filters drop 34 dB), so it is switched on here."""
+    lengths = synth.cfg3_lengths(48, seed=31)
+    arena, starts, lens = synth.ragged_corpus(lengths, seed=32)
+    with _lib.options(feature_kernel=2):
+        fb = batch.FeatureBatch(starts, lens, preemphasis=0.97, **kw)
+        got = fb.mfcc_delta(arena)
+        with _lib.options(redo=0):
+            raw = fb.mfcc_delta(arena)
+    worst = 0.0
+    for u, g_ in enumerate(fb.split(got)):
+        y = o.preemphasis(arena[starts[u]:starts[u] + lens[u]].astype(np.float64), 1, 0.97)
+        ref = o.extract_derivative_feature(o.mfcc(y, FS, **kw))
+        worst = max(worst, float(np.max(np.abs(g_ - ref))))
+    assert worst < TOL, worst
+    rows_changed = np.any(raw != got, axis=(1, 2))
+    assert 0 < rows_changed.sum()  # the guard did recompute rows ...
+    assert np.max(np.abs(raw - got)) < 5e-3  # ... that were close already
+    fb.close()
