@@ -159,9 +159,9 @@ SPB_API int spb_plan_destroy(spb_plan *plan);
 /* 8f-2: pre-emphasis (sfe/speechpy/processing.py:45-58, shift = 1) as a prologue of the framing kernels: every
  * feature call on this plan (single signal or batch) then works on y[i] = x[i] - cof * x[i-1], y[0] = x[0] -
  * cof * x[N-1] (np.roll is circular) of each utterance, computed in float32 while a tile's samples are staged
- * in shared memory -- the emphasised signal is never written.  Fused into the CUDA-core FFT kernels; plans with
- * cof != 0 do not use the tensor-core kernel.  cof = 0 (the default) switches it off.  Set it before the plan
- * is used by concurrent calls. */
+ * in shared memory (CUDA-core FFT kernels) or applied in the spectral domain in the epilogue of the tensor-core
+ * kernel (log-mel rows of the default shape) -- the emphasised signal is never written.  cof = 0 (the default)
+ * switches it off.  Set it before the plan is used by concurrent calls. */
 SPB_API int spb_plan_set_preemphasis(spb_plan *plan, double cof);
 
 /* --------------------------------------- a4-a6  mfe / lmfe / mfcc (one signal)

@@ -530,14 +530,14 @@ int spb_plan_create(spb_context *ctx, const spb_feature_params *params, const do
 // Pre-emphasis as a prologue of the framing (processing.py:45-58 with shift = 1): the
 // feature launches of this plan see y[i] = x[i] - cof x[i-1] (y[0] wraps to the utterance's last sample, as
 // np.roll does) without the emphasised signal ever being written.  Fused into the CUDA-core FFT kernels
-// (staged tile transformed in shared memory); the tensor-core kernel does not take it, so such plans run on
-// the FFT kernels.  cof = 0 switches it off again.
+// (staged tile transformed in shared memory) and, for log-mel rows of the default bank, into the epilogue of the
+// tensor-core kernel (spectral form, feat_tc2.cuh t2_pre_power).  cof = 0 switches it off again.
 int spb_plan_set_preemphasis(spb_plan *pl, double cof) {
   if (!pl) return SPB_ERR_INVALID;
   spb_context *ctx = pl->ctx;
   SPB_REQUIRE(ctx, isfinite(cof), "plan_set_preemphasis: cof must be finite");
   pl->pre_cof = cof;
-  pl->tc_ok = pl->tc_built && cof == 0.0;
+  tc_plan_apply_preemphasis(pl);
   return SPB_OK;
 }
 
@@ -739,12 +739,13 @@ int spb_batch_create(spb_context *ctx, const spb_plan *plan, const int64_t *star
           g.gstart = starts[u] + f0 * S;
           g.row0 = b->h_frame_offsets[u] + f0;
           g.nf = (int)std::min<int64_t>(kTcGroupFrames, nframes[u] - f0);
-          g.pad[0] = g.pad[1] = g.pad[2] = 0;
+          g.pad = 0;
+          g.prior = (f0 == 0) ? starts[u] + std::max<int64_t>(lengths[u], 1) - 1 : g.gstart - 1;
           tcg.push_back(g);
         }
       while (tcg.size() & 3) {
         TcGroup g;
-        g.gstart = 0; g.row0 = 0; g.nf = 0; g.pad[0] = g.pad[1] = g.pad[2] = 0;
+        g.gstart = 0; g.row0 = 0; g.nf = 0; g.pad = 0; g.prior = 0;
         tcg.push_back(g);
       }
       c.tc1 = (int64_t)tcg.size();
@@ -1079,7 +1080,7 @@ static int run_lmfe_cmvnw(spb_context *ctx, const spb_batch *b, const float *d_s
 // into scratch, then energy + DCT + deltas (mfcc_post_kernel).  Usable when the plan and the batch
 // qualify for the tensor-core kernel.
 static bool mfcc_hybrid_ok(const spb_batch *b, int mode) {
-  return (mode == FEAT_MFCC || mode == FEAT_MFCC_DELTA) && b->d_tc_groups && b->plan->tc_ok &&
+  return (mode == FEAT_MFCC || mode == FEAT_MFCC_DELTA) && b->d_tc_groups && b->plan->tc_ok && b->plan->pre_cof == 0.0 &&
          options().feature_kernel == 0 && b->plan->p.num_cepstral >= 1;
 }
 

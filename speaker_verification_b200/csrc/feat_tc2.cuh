@@ -131,6 +131,9 @@ struct T2Params {
   const float *zeros;        // >= 640 B of zeros: the hop rows past the end of a group read these
   float4 *hopsum;            // optional [tiles * 128]: per hop row {sum x^2, sum x, sum (-1)^n x, 0} for the mfcc energy
   RedoList redo;             // low-energy filters to recompute exactly (entries == nullptr: off)
+  float pre_c;               // pre-emphasis coefficient (PRE kernels; processing.py:45-58, shift = 1)
+  float pre_h[40];           // PRE: per filter (max |H_k| over its bins + 0.05)^2 -- what pre-emphasis does to the error of X,
+                             // hence to the guard's threshold of that filter (0.05: rounding of the two boundary terms)
 };
 
 
@@ -253,11 +256,34 @@ struct T2Rot {
 __constant__ T2Rot c_rot5 = {{{-0.9238795325112868f, 0.7071067811865474f}, {0.38268343236508984f, -1.0f}, {0.38268343236509f, 0.7071067811865476f}, {-0.9238795325112867f, 0.f}, {0.9238795325112867f, -0.7071067811865475f}, {-0.38268343236509034f, 1.0f}, {-0.3826834323650897f, -0.7071067811865477f}, {0.9238795325112865f, 0.f}},
                              {{0.38268343236508967f, 0.7071067811865477f}, {-0.9238795325112867f, 0.f}, {0.9238795325112866f, -0.7071067811865475f}, {-0.3826834323650899f, 1.0f}, {-0.3826834323650898f, -0.7071067811865476f}, {0.9238795325112865f, 0.f}, {-0.9238795325112867f, 0.7071067811865475f}, {0.3826834323650904f, -1.0f}}};
 
+// Pre-emphasis in the spectral domain (static epilogue, PRE kernels).  With y[n] = x[n] - c x[n-1] the 512-point
+// transform of a 320-sample frame that starts at sample s is
+//     Y[k] = (1 - c W^k) X[k] - c x[s-1] + c x[s+319] W^(320 k),      W = exp(-2 pi i / 512),
+// (shift the sum by one sample: the frame gains x[s-1] in front and loses x[s+319] at the end).  The epilogue has
+// X[k] up to the phase of the folded transform -- X' = P_k X, P_k = exp(+i th_k 79.5): the hop blocks are folded
+// about their centres --, so Y' = H_k X' + P_k (-c x[s-1]) + Q_k (c x[s+319]) with Q_k = P_k W^(320 k).  H_k sits in
+// .z / .w of the static variant's table (the compile-time rotation leaves them free), (P_k, Q_k) in the table of the
+// second half, which the static epilogue does not use.  Two samples per frame, eight packed operations per bin pair.
+// (xr, xi) = X' of the bin pair (b, b + 1) -> |Y|^2; pa = -c x[s-1], pe = c x[s+319] in the accumulator's units
+__device__ __forceinline__ float2 t2_pre_power(const float2 xr, const float2 xi, const float4 *h, const float4 *pq, const float pa,
+                                               const float pe) {
+  const float2 hr = make_float2(h[0].z, h[1].z), hi = make_float2(h[0].w, h[1].w);
+  const float2 a2 = make_float2(pa, pa), e2 = make_float2(pe, pe);
+  const float2 tr = __ffma2_rn(e2, make_float2(pq[0].z, pq[1].z), __fmul2_rn(a2, make_float2(pq[0].x, pq[1].x)));
+  const float2 ti = __ffma2_rn(e2, make_float2(pq[0].w, pq[1].w), __fmul2_rn(a2, make_float2(pq[0].y, pq[1].y)));
+  float2 yr = __ffma2_rn(hr, xr, tr);
+  yr = __ffma2_rn(make_float2(-hi.x, -hi.y), xi, yr);
+  float2 yi = __ffma2_rn(hr, xi, ti);
+  yi = __ffma2_rn(hi, xr, yi);
+  return __ffma2_rn(yi, yi, __fmul2_rn(yr, yr));
+}
+
 // |A_own + rot A_next|^2 of one bin pair (j, j + 1) of a 16-bin chunk.  KM = kmin mod 16 (rotation
 // as compile-time constants, period 16 in k at S = 160, NFFT = 512) or -1 (rotation from the table).
-template <int KM>
+template <int KM, bool PRE = false>
 __device__ __forceinline__ float2 t2_pair_power(const uint32_t (&vr)[16], const uint32_t (&vi)[16], const int j,
-                                                const float4 *tb) {
+                                                const float4 *tb, const int pre_b = 0, const float pre_a = 0.f,
+                                                const float pre_e = 0.f) {
   float2 cr, ci;
   if (KM == 5) {
     // from the constant bank, not as immediates: ptxas then parks the 16 pairs in uniform registers
@@ -282,6 +308,7 @@ __device__ __forceinline__ float2 t2_pair_power(const uint32_t (&vr)[16], const 
   xr = __ffma2_rn(make_float2(-ci.x, -ci.y), b_im, xr);
   float2 xi = __ffma2_rn(cr, b_im, a_im);
   xi = __ffma2_rn(ci, b_re, xi);
+  if (PRE) return t2_pre_power(xr, xi, tb + j, tb + 128 + j, pre_a, pre_e);  // tab[1] follows tab[0]
   return __ffma2_rn(xi, xi, __fmul2_rn(xr, xr));
 }
 
@@ -406,9 +433,10 @@ __device__ __forceinline__ void t2_store_run(float *prow, const float (&ov)[8], 
   }
 }
 
-template <int HALF>
+template <int HALF, bool PRE>
 __device__ __forceinline__ void t2_epilogue_static(const T2Params &p, const uint32_t taddr, float *prow, const bool row_ok,
-                                                   const float thr, const long long soff, const long long oidx_row) {
+                                                   const float thr, const long long soff, const long long oidx_row,
+                                                   const float pre_a, const float pre_e) {
   constexpr int LO = kT2S.lo[HALF], HI = kT2S.hi[HALF];
   constexpr int OUT_LO = kT2S.out_lo[HALF], NOUT = kT2S.nout[HALF];
   constexpr int KM = kT2S.kmin & 15;
@@ -429,7 +457,7 @@ __device__ __forceinline__ void t2_epilogue_static(const T2Params &p, const uint
     for (int j = 0; j < 16; j += 2) {
       const int b = ch * 16 + j;
       if (b + 1 < LO || b > HI) continue;
-      const float2 pp = t2_pair_power<KM>(vr, vi, j, tb);
+      const float2 pp = t2_pair_power<KM, PRE>(vr, vi, j, tb, b, pre_a, pre_e);
       pw[j] = pp.x;
       pw[j + 1] = pp.y;
     }
@@ -443,7 +471,7 @@ __device__ __forceinline__ void t2_epilogue_static(const T2Params &p, const uint
         if (nfl >= 1) {
           const int m = OUT_LO + nfl - 1;  // filter this flush completes
           const float a = prev_u + rf.y;
-          fbits |= (a < thr) ? (1u << (nfl - 1)) : 0u;
+          fbits |= (a < (PRE ? thr * p.pre_h[m] : thr)) ? (1u << (nfl - 1)) : 0u;
           ov[m & 7] = t2_log_value(a, ln_scale);
           if ((m & 7) == 7 || nfl == NOUT) {
             const int g0 = ((m & ~7) > OUT_LO) ? (m & ~7) : OUT_LO;
@@ -487,8 +515,9 @@ __host__ __device__ constexpr int t2_epi_warps(const int epi) { return 4 * (epi 
 __host__ __device__ constexpr int t2_cvt_warps(const int epi) { return (epi == 2 && kT2Parts == 3) ? SPB_T2_CVT3 : kTcCvtWarps; }
 __host__ __device__ constexpr int t2_threads(const int epi) { return (t2_epi_warps(epi) + 1 + t2_cvt_warps(epi)) * 32; }
 
-template <int KM, int EPI, bool SUMS>
+template <int KM, int EPI, bool SUMS, bool PRE = false>
 __global__ void __launch_bounds__(t2_threads(EPI), 1) features_tc2_kernel(const T2Params p) {
+  static_assert(!PRE || (EPI == 2 && !SUMS), "pre-emphasis: static epilogue, log-mel output only");
   constexpr int kEpiW = t2_epi_warps(EPI), kMmaW = kEpiW, kCvt0 = kEpiW + 1, kCvtW = t2_cvt_warps(EPI);
   constexpr int kThreads = t2_threads(EPI);
   extern __shared__ __align__(128) unsigned char tc_smem[];
@@ -712,6 +741,16 @@ __global__ void __launch_bounds__(t2_threads(EPI), 1) features_tc2_kernel(const 
     for (long long t = blockIdx.x; t < p.num_tiles; t += gridDim.x, ++it) {
       const TcGroup g = p.groups[t * 4 + quad];
       const uint32_t acc = it & 1;
+      // pre-emphasis: the sample in front of this lane's frame (the utterance's last one for its first frame: np.roll)
+      // and the frame's last sample, fetched (L2 hits: the converters read them a moment ago) before the wait
+      float pre_a = 0.f, pre_e = 0.f;
+      if (PRE && lane < g.nf) {
+        const long long s0 = g.gstart + (long long)lane * kTcHop;
+        const float xm = __ldg(p.samples + (lane == 0 ? g.prior : s0 - 1));
+        const float xe = __ldg(p.samples + s0 + (2 * kTcHop - 1));
+        pre_a = -p.pre_c * kT2InScale * xm;
+        pre_e = p.pre_c * kT2InScale * xe;
+      }
       t2_wait_park(&acc_full[acc], (it >> 1) & 1);
       tc_fence_after();
       const uint32_t taddr = tmem_base + ((uint32_t)(quad * 32) << 16) + acc * (2 * kT2N);
@@ -723,9 +762,9 @@ __global__ void __launch_bounds__(t2_threads(EPI), 1) features_tc2_kernel(const 
       const long long soff = g.gstart + (long long)lane * kTcHop;
       const long long row = g.row0 + lane;
       if (EPI == 2) {
-        if (half == 0) t2_epilogue_static<0>(p, taddr, p.out + row * M, row_ok, thr, soff, row * M);
-        else if (half == 1) t2_epilogue_static<1>(p, taddr, p.out + row * M, row_ok, thr, soff, row * M);
-        else t2_epilogue_static<kT2Parts - 1>(p, taddr, p.out + row * M, row_ok, thr, soff, row * M);
+        if (half == 0) t2_epilogue_static<0, PRE>(p, taddr, p.out + row * M, row_ok, thr, soff, row * M, pre_a, pre_e);
+        else if (half == 1) t2_epilogue_static<1, PRE>(p, taddr, p.out + row * M, row_ok, thr, soff, row * M, pre_a, pre_e);
+        else t2_epilogue_static<kT2Parts - 1, PRE>(p, taddr, p.out + row * M, row_ok, thr, soff, row * M, pre_a, pre_e);
       } else {
         if (half == 0) t2_epilogue_dyn<KM, EPI, 0>(p, taddr, p.out + row * M, row_ok, thr, soff, row * M);
         else t2_epilogue_dyn<KM, EPI, 1>(p, taddr, p.out + row * M + p.half[1].out_lo, row_ok, thr, soff,

@@ -640,13 +640,50 @@ int build_tc_plan(spb_context *ctx, spb_plan *pl, const float4 *seg_rd) {
     return cuda_fail(ctx, e, "cudaMemcpy(tc plan)");
   pl->tc_serial = g_tc_serial.fetch_add(1);
   pl->tc_built = true;
-  pl->tc_ok = pl->pre_cof == 0.0;
+  pl->tc_ok = true;
+  tc_plan_apply_preemphasis(pl);
   return SPB_OK;
 }
 
+// Pre-emphasis constants of the static epilogue (feat_tc2.cuh, t2_pre_power): per bin H = 1 - c W^k in .z / .w of the
+// first table and (P, Q) = (exp(+i th_k 79.5), P W^(320 k)) as the second table; a new serial makes the next launch
+// upload them.  cof = 0 restores the rotation constants the table was built with.
+void tc_plan_apply_preemphasis(spb_plan *pl) {
+  if (!pl->tc_built || !pl->tc2_static || pl->h_tc_tab_s.size() < 2 * 128 * 4) return;
+  const double two_pi = 6.283185307179586476925286766559;
+  const int nb = pl->seg_nbins, kmin = pl->seg_kmin, nfft = pl->p.nfft, S = pl->p.frame_stride, L = pl->p.frame_len;
+  const double c = pl->pre_cof;
+  for (int j = 0; j < nb && j < 128; ++j) {
+    const int k = kmin + j;
+    float *e0 = &pl->h_tc_tab_s[((size_t)0 * 128 + j) * 4], *e1 = &pl->h_tc_tab_s[((size_t)1 * 128 + j) * 4];
+    const double rot = two_pi * (double)(((long long)k * S) % nfft) / (double)nfft;
+    if (c == 0.0) {
+      e0[2] = (float)cos(rot); e0[3] = (float)-sin(rot);
+      e1[0] = 0.f; e1[1] = 0.f; e1[2] = (float)cos(rot); e1[3] = (float)-sin(rot);
+      continue;
+    }
+    const double th = two_pi * (double)k / (double)nfft;
+    const double ph = th * ((double)S - 1.0) / 2.0;                       // P = exp(+i th (S - 1) / 2): fold centre of a hop
+    const double qh = ph - two_pi * (double)(((long long)k * L) % nfft) / (double)nfft;  // Q = P W^(L k)
+    e0[2] = (float)(1.0 - c * cos(th));
+    e0[3] = (float)(c * sin(th));
+    e1[0] = (float)cos(ph); e1[1] = (float)sin(ph);
+    e1[2] = (float)cos(qh); e1[3] = (float)sin(qh);
+  }
+  pl->tc_serial = g_tc_serial.fetch_add(1);
+}
+
 bool features_tc_supported(const FeatArgs &a) {
-  return a.plan && a.plan->tc_ok && a.tc_groups && a.num_tc_groups > 0 && (a.num_tc_groups % 4) == 0 &&
-         (a.mode == FEAT_LMFE || (a.mode == FEAT_MFE && a.energy == nullptr));
+  if (!(a.plan && a.plan->tc_ok && a.tc_groups && a.num_tc_groups > 0 && (a.num_tc_groups % 4) == 0 &&
+        (a.mode == FEAT_LMFE || (a.mode == FEAT_MFE && a.energy == nullptr))))
+    return false;
+  if (a.pre_cof != 0.0) {
+    // pre-emphasis: the static epilogue of generation 2 only (log-mel rows of the speechpy default bank)
+    const Options &opt = options();
+    return a.plan->tc2_ok && a.plan->tc2_static && opt.tc_version != 1 && (opt.tc_epilogue < 0 || opt.tc_epilogue == 2) &&
+           a.mode == FEAT_LMFE && a.tc_hopsum == nullptr && (reinterpret_cast<uintptr_t>(a.out) & 15) == 0;
+  }
+  return true;
 }
 
 static int launch_features_tc1(spb_context *ctx, const FeatArgs &a) {
@@ -724,6 +761,19 @@ static int launch_features_tc2(spb_context *ctx, const FeatArgs &a) {
   p.zeros = reinterpret_cast<const float *>(pl->d_tc_flag) + 64;
   p.hopsum = a.tc_hopsum;
   p.redo = a.redo_tc;
+  p.pre_c = (float)a.pre_cof;
+  for (int m = 0; m < 40; ++m) {
+    float h = 1.f;
+    if (a.pre_cof != 0.0 && m < a.M && m < (int)pl->h_band_lo.size()) {
+      double hm = 0.0;
+      for (int k : {pl->h_band_lo[m], pl->h_band_lo[m] + std::max(pl->h_band_n[m], 1) - 1}) {
+        const double th = 6.283185307179586476925286766559 * (double)k / (double)a.nfft;
+        hm = std::max(hm, sqrt(1.0 + a.pre_cof * a.pre_cof - 2.0 * a.pre_cof * cos(th)));  // |1 - c W^k|, monotonic in k
+      }
+      h = (float)((hm + 0.05) * (hm + 0.05));
+    }
+    p.pre_h[m] = h;
+  }
   const bool km5 = (pl->seg_kmin & 15) == 5;  // the speechpy default bank starts at bin 5
   const bool aligned16 = (reinterpret_cast<uintptr_t>(a.out) & 15) == 0;
   // epilogue flavour: 2 static default bank, 1 runs of four filters, 0 generic
@@ -753,8 +803,10 @@ static int launch_features_tc2(spb_context *ctx, const FeatArgs &a) {
     own.variant = variant;
   }
   const bool sums = p.hopsum != nullptr;
+  if (p.pre_c != 0.f && (epi != 2 || sums)) return fail(ctx, SPB_ERR_UNSUPPORTED, "features_tc2: pre-emphasis needs the static epilogue");
   void (*kern)(const T2Params) = nullptr;
-  if (epi == 2) kern = sums ? features_tc2_kernel<5, 2, true> : features_tc2_kernel<5, 2, false>;
+  if (epi == 2 && p.pre_c != 0.f) kern = features_tc2_kernel<5, 2, false, true>;
+  else if (epi == 2) kern = sums ? features_tc2_kernel<5, 2, true> : features_tc2_kernel<5, 2, false>;
   else if (epi == 1) kern = sums ? features_tc2_kernel<5, 1, true> : features_tc2_kernel<5, 1, false>;
   else if (km5) kern = sums ? features_tc2_kernel<5, 0, true> : features_tc2_kernel<5, 0, false>;
   else kern = sums ? features_tc2_kernel<-1, 0, true> : features_tc2_kernel<-1, 0, false>;

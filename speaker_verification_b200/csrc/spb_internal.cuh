@@ -125,7 +125,9 @@ struct __align__(16) TcGroup {
   long long gstart;  // first sample of the group's first hop in the arena
   long long row0;    // first output row
   int nf;            // frames (0: padding group)
-  int pad[3];
+  int pad;
+  long long prior;   // arena index of the sample in front of the group's first hop: gstart - 1, or -- first group of an
+                     // utterance -- the utterance's LAST sample (what np.roll puts in front of sample 0; pre-emphasis)
 };
 
 // Exactness guard of the log-mel kernels: a filter whose fp32 energy is below tau x the level of
@@ -293,6 +295,7 @@ bool features_tc_has_guard(const FeatArgs &a);
 int launch_redo(spb_context *ctx, const FeatArgs &a, const RedoList &list, const int *skip_if, const FftTables &t);
 // mfcc / mfcc+delta rows from log-mel rows (global row addressing) + frame energies from the samples
 int launch_mfcc_post(spb_context *ctx, const FeatArgs &a, const float *d_lmfe);
+void tc_plan_apply_preemphasis(spb_plan *pl);  // refresh the tensor-core epilogue's pre-emphasis constants from pl->pre_cof
 int build_tc_plan(spb_context *ctx, spb_plan *pl, const float4 *seg_rd);  // seg_rd: host copy, seg_nbins entries
 bool fast1024_supported(const FeatArgs &a);
 int launch_features_fast1024(spb_context *ctx, const FeatArgs &a, const FftTables &t);

@@ -310,3 +310,35 @@ def test_mfcc_rows_of_the_fft_kernels_are_guarded(sp, kw):
     assert 0 < rows_changed.sum()  # the guard did recompute rows ...
     assert np.max(np.abs(raw - got)) < 5e-3  # ... that were close already
     fb.close()
+
+
+def test_tc_preemphasis_in_the_epilogue(sp):
+    """FeatureBatch(preemphasis=c) on the default shape: the tensor-core kernel applies it in its epilogue, in the
+    spectral domain -- Y[k] = (1 - c W^k) X[k] - c x[s-1] + c x[s+319] W^(320 k) per frame, with the phase of the
+    folded transform (feat_tc2.cuh, t2_pre_power) -- and the guard's threshold follows |H_k| per filter.  Every
+    log-mel value of 96 cfg3-shaped utterances within 1e-4 of lmfe(preemphasis(x)) in float64 (processing.py:45-58,
+    feature.py:222-258), the utterances' last samples loud so that a missed wrap (np.roll) shows; the CUDA-core
+    FFT kernel (pre-emphasis on the staged tile) agrees; cmvnw on top of it; c < 0 as well."""
+    lengths = synth.cfg3_lengths(96, seed=41)
+    arena, starts, lens = synth.ragged_corpus(lengths, seed=42)
+    for u in range(len(starts)):
+        arena[starts[u] + lens[u] - 1] = 0.7
+    for cof in (0.97, -0.5):
+        fb = batch.FeatureBatch(starts, lens, preemphasis=cof)
+        ref = np.concatenate([o.lmfe(o.preemphasis(arena[starts[u]:starts[u] + lens[u]].astype(np.float64), 1, cof), FS)
+                              for u in range(len(starts))])
+        tc, n_tc = _lmfe_dev(fb, arena, True)
+        fft, n_fft = _lmfe_dev(fb, arena, False)
+        assert n_tc > n_fft  # the tensor-core path: its kernel, the guarded fallback launch and two redo passes
+        e_tc, e_fft = np.abs(tc - ref), np.abs(fft - ref)
+        assert e_tc.max() < TOL, (cof, e_tc.max(), np.unravel_index(e_tc.argmax(), e_tc.shape))
+        assert e_fft.max() < TOL, (cof, e_fft.max())
+        assert np.quantile(e_tc, 0.9999) < 2e-5
+        raw, _ = _lmfe_dev(fb, arena, True, redo=0)
+        assert (raw != tc).mean() < 2e-3  # the per-filter threshold keeps the float64 redo rare
+        if cof > 0:
+            full = fb.lmfe_cmvnw(arena)
+            for u in (0, 40, 95):
+                want = o.cmvnw_vectorised(ref[fb.frame_offsets[u]:fb.frame_offsets[u + 1]], 301, True)
+                assert np.max(np.abs(full[fb.frame_offsets[u]:fb.frame_offsets[u + 1]] - want)) < TOL, u
+        fb.close()
