@@ -366,7 +366,13 @@ cmvnw_big_kernel(const CmBigParams p) {
   uint32_t bar_phase = 0;
   const int ncg = cols >> 1;
   const int nbpt = kBigThreads / ncg;
-  const int g = tid % ncg, b0 = tid / ncg;
+  // (column pair g, block-thread b0).  40 columns: a row is 160 B = 20 pairs, 32 consecutive pairs straddle two rows
+  // 30 apart and 30 x 160 B = 64 (mod 128), so the plain tid % 20 layout paid a bank-conflict wavefront on every
+  // other 64-bit request (ncu r02ar, resident kernel: 34 % of the load wavefronts); instead warps 0 .. 15 take pairs
+  // 0 .. 15 of two blocks each (a half-warp = 128 contiguous bytes), warps 16 .. 19 the pairs 16 .. 19 of eight blocks
+  const bool remap = COLS == 40 && kBigThreads == 640;
+  const int g = remap ? (tid < 512 ? (tid & 15) : 16 + ((tid - 512) & 3)) : tid % ncg;
+  const int b0 = remap ? (tid < 512 ? (tid >> 4) : ((tid - 512) >> 2)) : tid / ncg;
   const bool worker = b0 < nbpt;
   const int c0 = 2 * g;
   const double inv_win = 1.0 / (double)win;

@@ -173,7 +173,14 @@ __global__ void __launch_bounds__(kResThreads, 1) cmvnw_resident_kernel(const Cm
   __shared__ long long s_base[2];
   __shared__ __align__(8) uint64_t s_bar;
   const int tid = threadIdx.x;
-  const int g = tid % kResPairs, b0 = tid / kResPairs;
+  // (block-thread b0, column pair g) of a thread.  A row is 160 B = 20 pairs, so 32 consecutive pairs straddle two
+  // rows 30 apart, and 30 x 160 B = 64 (mod 128): the second row's pairs land on the banks of the first row's last
+  // four and every such 64-bit request paid a conflict wavefront (ncu r02ar: 34 % of the load wavefronts).  Instead:
+  // warps 0 .. 15 take pairs 0 .. 15 of two blocks each (a half-warp = 128 contiguous bytes), warps 16 .. 19 the
+  // pairs 16 .. 19 of eight blocks each.
+  static_assert(kResPairs == 20 && kResThreads == 640 && kResBT == 32, "thread layout of the resident cmvnw kernel");
+  const int g = tid < 512 ? (tid & 15) : 16 + ((tid - 512) & 3);
+  const int b0 = tid < 512 ? (tid >> 4) : ((tid - 512) >> 2);
   const int c0 = 2 * g;
   constexpr int C = kResCols, G = kResG, H = kResH;
   const float2 iw = make_float2(1.0f / (float)kResWin, 1.0f / (float)kResWin);
