@@ -562,7 +562,7 @@ int spb_plan_destroy(spb_plan *pl) {
 // ------------------------------------------------------------------ batches
 static constexpr int kFftTile = spb::kFftTileFrames;
 static constexpr int64_t kChunkRowsDefault = 192 * 1024;  // pipeline unit of the host-pointer calls (~30 MB of rows)
-static constexpr int64_t kGroupRowsDefault = 4 * 1024 * 1024;  // launch unit of the device-pointer calls
+static constexpr int64_t kGroupRowsDefault = 32 * 1024 * 1024;  // launch unit of the device-pointer calls (5.4 GB x 2 of scratch at most; measured r02ba: 4 Mi rows 48.2 ms, 8 Mi 48.1, 16 Mi 47.8, 32 Mi 47.5 per cfg3 step)
 // tuning knobs (read when a batch is created): SPB_CHUNK_ROWS, SPB_GROUP_ROWS, SPB_BIG_RMAX
 static int64_t env_int(const char *name, int64_t dflt) {
   const char *v = getenv(name);

@@ -544,3 +544,40 @@ def test_preemphasis_fused_into_the_framing(sp, kw):
             assert np.max(np.abs(c_ - o.extract_derivative_feature(o.mfcc(y, FS, **okw)))) < TOL, (aligned, len(y))
         fb.close()
         plain.close()
+
+
+def test_launch_groups_and_pipeline_chunks_do_not_change_results(sp, monkeypatch):
+    """The device-pointer calls walk a batch in launch groups (SPB_GROUP_ROWS rows, default 32 Mi) and the host-pointer
+    calls in pipeline chunks (SPB_CHUNK_ROWS, default 192 Ki): sizing knobs read when a batch descriptor is created,
+    which only cut the batch at utterance boundaries.  The same ragged batch with tiny groups / chunks (dozens of
+    launches, every group with its own resident / two-pass / tensor-core tables) gives bit-identical rows, through
+    both kinds of call, and matches the reference."""
+    import torch
+    lengths = synth.cfg3_lengths(40, seed=51)
+    arena, starts, lens = synth.ragged_corpus(lengths, seed=52)
+    d = torch.from_numpy(arena).cuda()
+
+    def run():
+        fb = batch.FeatureBatch(starts, lens)
+        out = torch.full((fb.total_frames, 40), float("nan"), dtype=torch.float32, device="cuda")
+        n0 = fb.ctx.launch_count()
+        fb.lmfe_cmvnw_dev(d.data_ptr(), d.numel(), out.data_ptr())
+        fb.ctx.sync()
+        launches = fb.ctx.launch_count() - n0
+        host = fb.lmfe_cmvnw(arena)
+        mf = fb.mfcc_delta(arena)
+        res = (out.cpu().numpy(), host, mf, launches, fb.frame_offsets.copy())
+        fb.close()
+        return res
+
+    dev0, host0, mf0, l0, offs = run()
+    monkeypatch.setenv("SPB_GROUP_ROWS", "3000")
+    monkeypatch.setenv("SPB_CHUNK_ROWS", "2000")
+    dev1, host1, mf1, l1, _ = run()
+    assert l1 > 4 * l0  # many groups
+    assert np.array_equal(dev0, dev1) and np.array_equal(host0, host1) and np.array_equal(mf0, mf1)
+    assert np.array_equal(dev0, host0)
+    for u in (0, 13, 39):
+        s_ = arena[starts[u]:starts[u] + lens[u]]
+        ref = o.cmvnw_vectorised(o.lmfe(s_, FS), 301, True)
+        assert np.max(np.abs(dev1[offs[u]:offs[u + 1]] - ref)) < TOL
