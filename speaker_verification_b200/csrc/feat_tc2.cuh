@@ -282,8 +282,7 @@ __device__ __forceinline__ float2 t2_pre_power(const float2 xr, const float2 xi,
 // as compile-time constants, period 16 in k at S = 160, NFFT = 512) or -1 (rotation from the table).
 template <int KM, bool PRE = false>
 __device__ __forceinline__ float2 t2_pair_power(const uint32_t (&vr)[16], const uint32_t (&vi)[16], const int j,
-                                                const float4 *tb, const int pre_b = 0, const float pre_a = 0.f,
-                                                const float pre_e = 0.f) {
+                                                const float4 *tb, const float pre_a = 0.f, const float pre_e = 0.f) {
   float2 cr, ci;
   if (KM == 5) {
     // from the constant bank, not as immediates: ptxas then parks the 16 pairs in uniform registers
@@ -457,7 +456,7 @@ __device__ __forceinline__ void t2_epilogue_static(const T2Params &p, const uint
     for (int j = 0; j < 16; j += 2) {
       const int b = ch * 16 + j;
       if (b + 1 < LO || b > HI) continue;
-      const float2 pp = t2_pair_power<KM, PRE>(vr, vi, j, tb, b, pre_a, pre_e);
+      const float2 pp = t2_pair_power<KM, PRE>(vr, vi, j, tb, pre_a, pre_e);
       pw[j] = pp.x;
       pw[j + 1] = pp.y;
     }

@@ -90,8 +90,8 @@ struct spb_plan {
   // tensor-core hop-DFT kernel (feat_tc_kernels.cu): fp16 hi/lo DFT matrix in its shared-memory
   // layout, per-bin {rise, fall, cos, sin}; tc_ok == false: plan shape not covered
   bool tc_ok = false;
-  bool tc_built = false;   // build_tc_plan succeeded (tc_ok = tc_built && no pre-emphasis)
-  double pre_cof = 0.0;    // pre-emphasis fused into the framing of the FFT kernels (spb_plan_set_preemphasis); 0: off
+  bool tc_built = false;   // build_tc_plan succeeded
+  double pre_cof = 0.0;    // pre-emphasis fused into the framing kernels (spb_plan_set_preemphasis); 0: off
   void *d_tc_whi = nullptr, *d_tc_wlo = nullptr;
   std::vector<float> h_tc_tab;        // [2][128][4]: per epilogue half {rise, fall, cos, sin}
   uint32_t tc_endmask[2][4] = {{0, 0, 0, 0}, {0, 0, 0, 0}};
