@@ -56,18 +56,44 @@ __device__ __forceinline__ double redo_energy(const RedoParams &p, const float *
   const float *w = p.band_w + p.band_off[m];
   const int Leff = min(p.L, p.nfft);  // numpy rfft(n=): rows longer than NFFT are truncated
   const int mask = p.nfft - 1;
+  // frames of up to 320 samples (the speechpy default): a lane's ten samples are read and widened once, not once per bin
+  constexpr int kPer = 10;
+  const bool small = Leff <= 32 * kPer;
+  double xv[kPer];
+  if (small) {
+#pragma unroll
+    for (int j = 0; j < kPer; ++j) {
+      const int i = lane + 32 * j;
+      double v = 0.0;
+      if (i < Leff) {
+        v = (double)x[i];
+        if (p.pre_cof != 0.0) v -= p.pre_cof * (double)(i > 0 ? x[i - 1] : *xprior);
+      }
+      xv[j] = v;
+    }
+  }
   double acc = 0.0;
   for (int t = 0; t < n; ++t) {
     const double wt = (double)w[t];
     if (wt == 0.0) continue;  // zero padding of the tap table (warp-uniform)
     const int k = lo + t;
     double re = 0.0, im = 0.0;
-    for (int i = lane; i < Leff; i += 32) {
-      const double2 c = p.tw[(int)(((long long)k * i) & mask)];
-      double v = (double)x[i];
-      if (p.pre_cof != 0.0) v -= p.pre_cof * (double)(i > 0 ? x[i - 1] : *xprior);
-      re = fma(v, c.x, re);
-      im = fma(v, c.y, im);
+    if (small) {
+#pragma unroll
+      for (int j = 0; j < kPer; ++j) {
+        const int i = lane + 32 * j;
+        const double2 c = p.tw[(k * i) & mask];  // k, i < 4096; rows past Leff carry xv = 0
+        re = fma(xv[j], c.x, re);
+        im = fma(xv[j], c.y, im);
+      }
+    } else {
+      for (int i = lane; i < Leff; i += 32) {
+        const double2 c = p.tw[(int)(((long long)k * i) & mask)];
+        double v = (double)x[i];
+        if (p.pre_cof != 0.0) v -= p.pre_cof * (double)(i > 0 ? x[i - 1] : *xprior);
+        re = fma(v, c.x, re);
+        im = fma(v, c.y, im);
+      }
     }
 #pragma unroll
     for (int o = 16; o >= 1; o >>= 1) {
