@@ -42,6 +42,9 @@ constexpr int kT2MaxBins = 128;
 #ifndef SPB_T2_SLOTS
 #define SPB_T2_SLOTS 7
 #endif
+#ifndef SPB_T2_PF
+#define SPB_T2_PF 2  // L2 prefetch distance of the converters, in tiles of this CTA
+#endif
 #ifndef SPB_T2_STAGE
 #define SPB_T2_STAGE 2
 #endif
@@ -618,7 +621,7 @@ __global__ void __launch_bounds__(t2_threads(EPI), 1) features_tc2_kernel(const 
       for (int j = 0; j < RPT; ++j) { mx[j] = 0u; q2[j] = 0.f; q0[j] = 0.f; qa[j] = 0.f; }
       if (c < 4) {
         // pull the samples of the tile after next into L2 with the TMA engine (one run per group)
-        const long long tp = t + 2 * (long long)gridDim.x;
+        const long long tp = t + SPB_T2_PF * (long long)gridDim.x;
         if (tp < p.num_tiles) {
           const TcGroup g = p.groups[tp * 4 + c];
           if (g.nf > 0) bulk_prefetch_l2(p.samples + g.gstart, (uint32_t)(g.nf + 1) * (kTcHop * 4));
