@@ -42,6 +42,9 @@ constexpr int kT2MaxBins = 128;
 #ifndef SPB_T2_SLOTS
 #define SPB_T2_SLOTS 7
 #endif
+#ifndef SPB_T2_INTERLEAVE
+#define SPB_T2_INTERLEAVE 0
+#endif
 #ifndef SPB_T2_PF
 #define SPB_T2_PF 2  // L2 prefetch distance of the converters, in tiles of this CTA
 #endif
@@ -719,12 +722,18 @@ __global__ void __launch_bounds__(t2_threads(EPI), 1) features_tc2_kernel(const 
           umma_f16(tm_re, d_shi, umma_desc_plain(w_clo + ko, kT2BLbo), kT2Idesc, 1u);
           umma_f16(tm_im, d_dlo, umma_desc_plain(w_shi + ko, kT2BLbo), kT2Idesc, s ? 1u : 0u);
           umma_f16(tm_im, d_dhi, umma_desc_plain(w_slo + ko, kT2BLbo), kT2Idesc, 1u);
+#if SPB_T2_INTERLEAVE
+          // experiment: the large terms of the k-step right away, the ring slot handed back at once
+          umma_f16(tm_re, d_shi, umma_desc_plain(w_chi + ko, kT2BLbo), kT2Idesc, 1u);
+          umma_f16(tm_im, d_dhi, umma_desc_plain(w_shi + ko, kT2BLbo), kT2Idesc, 1u);
+          tc_commit(&empty[slot]);
+#endif
           if (++slot == kT2Slots) { slot = 0; par ^= 1; }
         }
         // then the large ones; every k-step hands its ring slot back
         uint32_t sl2 = slot0;
 #pragma unroll
-        for (int s = 0; s < kT2KSteps; ++s) {
+        for (int s = 0; s < (SPB_T2_INTERLEAVE ? 0 : kT2KSteps); ++s) {
           const uint32_t a = sbase + kT2OffA + sl2 * kT2SlotBytes;
           const uint32_t ko = s * 2 * kT2BLbo;
           umma_f16(tm_re, umma_desc_plain(a, kTcRows * 16), umma_desc_plain(w_chi + ko, kT2BLbo), kT2Idesc, 1u);
