@@ -55,8 +55,12 @@ constexpr int kT2Slots = SPB_T2_SLOTS;          // A-operand ring depth (k-steps
 constexpr int kT2Stage = SPB_T2_STAGE;          // raw-sample staging depth (k-steps of cp.async in flight per converter)
 constexpr uint32_t kT2BLbo = kT2N * 16;                 // 2 048 B between the k-chunks of a W matrix
 constexpr uint32_t kT2BMat = (kT2K / 8) * kT2BLbo;      // 20 480 B: [k/8][col][8 halves]
-constexpr uint32_t kT2APart = 2 * kTcRows * 16;         // 4 096 B: [2][row][8 halves] of one k-step
-constexpr uint32_t kT2SlotBytes = 4 * kT2APart;         // s_hi | s_lo | d_hi | d_lo
+// A-operand ring slot (one k-step): the first k-chunk column ([row][8 halves], 2 048 B) of s_hi | s_lo | d_hi | d_lo, 64 B of
+// padding, then their second columns.  The padding puts the two columns of an array 64 bytes apart modulo 128, so that a
+// half-warp of converters -- four rows x (two columns x two 8-byte halves) -- stores without bank conflicts.
+constexpr uint32_t kT2APart = kTcRows * 16;             // 2 048 B: one column of one array; array k starts at k * kT2APart
+constexpr uint32_t kT2ALbo = 4 * kT2APart + 64;         // 8 256 B between the two k-chunk columns of an array
+constexpr uint32_t kT2SlotBytes = 8 * kT2APart + 64;    // 16 448 B
 constexpr uint32_t kT2OffA = 4 * kT2BMat;               // C_hi | C_lo | S_hi | S_lo, then the ring
 constexpr uint32_t kT2OffStage = kT2OffA + kT2Slots * kT2SlotBytes;       // [stage][4 loads][256 converters][16 B]
 constexpr uint32_t kT2StageBytes = 4 * kTcCvtWarps * 32 * 16;              // 16 KB per k-step
@@ -571,16 +575,19 @@ __global__ void __launch_bounds__(t2_threads(EPI), 1) features_tc2_kernel(const 
 
   if (warp >= kCvt0) {
     // ===== converters =====
-    // lane = (k-chunk, row of 8, 8-byte half): a half-warp's st.shared.v2 covers 128 contiguous bytes of the
-    // operand; a thread feeds RPT hop rows (r0 + 8 CW j)
+    // lane = (row of 8, k-chunk, 8-byte half): the four lanes of a row are adjacent, so their four 16-byte cp.async
+    // pieces of a k-step are 64 contiguous bytes of the hop and reach shared memory as ONE write wavefront (with the
+    // row's pieces 16 lanes apart every 32-byte sector arrived on its own: ncu r02ar counted 16 wavefronts per
+    // LDGSTS.128 where 4 is the ideal -- half of all the kernel's shared-memory wavefronts); a thread feeds RPT
+    // hop rows (r0 + 8 CW j)
     constexpr int CW = kCvtW, RPT = kTcRows / (CW * 8), NLD = 2 * RPT;
     constexpr uint32_t kPlane = CW * 32 * 16;      // one 16-byte load of every converter thread
     static_assert(NLD * kPlane == kT2StageBytes, "features_tc2: staging layout");
     const int cw = warp - kCvt0;
-    const int kc = lane >> 4, r8 = (lane >> 1) & 7, hf = lane & 1;
+    const int kc = (lane >> 1) & 1, r8 = lane >> 2, hf = lane & 1;
     const int qq = 2 * kc + hf;                    // which 4 of the 16 m values of a k-step
     const int r0 = cw * 8 + r8;
-    const uint32_t d0 = (uint32_t)(kc * (kTcRows * 16) + r0 * 16 + hf * 8);
+    const uint32_t d0 = (uint32_t)(kc * kT2ALbo + r0 * 16 + hf * 8);
     const int c = cw * 32 + lane;
     auto row_ptr = [&](long long t, int r) -> const float * {
       if (t >= p.num_tiles) return p.zeros;
@@ -661,10 +668,10 @@ __global__ void __launch_bounds__(t2_threads(EPI), 1) features_tc2_kernel(const 
 #pragma unroll
           for (int j = 0; j < RPT; ++j) {
             mx[j] = __vmaxu2(mx[j], __shfl_xor_sync(0xffffffffu, mx[j], 1));
-            mx[j] = __vmaxu2(mx[j], __shfl_xor_sync(0xffffffffu, mx[j], 16));
+            mx[j] = __vmaxu2(mx[j], __shfl_xor_sync(0xffffffffu, mx[j], 2));
             const uint32_t m = max(mx[j] & 0xffffu, mx[j] >> 16);
             bad |= (m >= 0x7c00u) ? 1u : 0u;
-            if ((lane & 17) == 0) lvl[(it & 3) * kTcRows + r0 + j * CW * 8] = t2_level_of(m);
+            if ((lane & 3) == 0) lvl[(it & 3) * kTcRows + r0 + j * CW * 8] = t2_level_of(m);
           }
         }
         t2_wait_nap(&empty[slot], par);
@@ -683,13 +690,13 @@ __global__ void __launch_bounds__(t2_threads(EPI), 1) features_tc2_kernel(const 
         if (++slot == kT2Slots) { slot = 0; par ^= 1; }
       }
       if (SUMS) {
-        // the four lanes of a row: lane bits 0 and 4
+        // the four lanes of a row: lane bits 0 and 1
         constexpr float u1 = 1.0f / kT2InScale, u2 = 0.5f / (kT2InScale * kT2InScale);
 #pragma unroll
         for (int j = 0; j < RPT; ++j) {
           q2[j] += __shfl_xor_sync(0xffffffffu, q2[j], 1); q0[j] += __shfl_xor_sync(0xffffffffu, q0[j], 1); qa[j] += __shfl_xor_sync(0xffffffffu, qa[j], 1);
-          q2[j] += __shfl_xor_sync(0xffffffffu, q2[j], 16); q0[j] += __shfl_xor_sync(0xffffffffu, q0[j], 16); qa[j] += __shfl_xor_sync(0xffffffffu, qa[j], 16);
-          if ((lane & 17) == 0) p.hopsum[t * kTcRows + r0 + j * CW * 8] = make_float4(q2[j] * u2, q0[j] * u1, qa[j] * u1, 0.f);
+          q2[j] += __shfl_xor_sync(0xffffffffu, q2[j], 2); q0[j] += __shfl_xor_sync(0xffffffffu, q0[j], 2); qa[j] += __shfl_xor_sync(0xffffffffu, qa[j], 2);
+          if ((lane & 3) == 0) p.hopsum[t * kTcRows + r0 + j * CW * 8] = make_float4(q2[j] * u2, q0[j] * u1, qa[j] * u1, 0.f);
         }
       }
 #pragma unroll
@@ -714,9 +721,9 @@ __global__ void __launch_bounds__(t2_threads(EPI), 1) features_tc2_kernel(const 
           t2_wait_park(&full[slot], par);
           tc_fence_after();
           const uint32_t a = sbase + kT2OffA + slot * kT2SlotBytes;
-          const uint64_t d_shi = umma_desc_plain(a, kTcRows * 16), d_slo = umma_desc_plain(a + kT2APart, kTcRows * 16);
-          const uint64_t d_dhi = umma_desc_plain(a + 2 * kT2APart, kTcRows * 16);
-          const uint64_t d_dlo = umma_desc_plain(a + 3 * kT2APart, kTcRows * 16);
+          const uint64_t d_shi = umma_desc_plain(a, kT2ALbo), d_slo = umma_desc_plain(a + kT2APart, kT2ALbo);
+          const uint64_t d_dhi = umma_desc_plain(a + 2 * kT2APart, kT2ALbo);
+          const uint64_t d_dlo = umma_desc_plain(a + 3 * kT2APart, kT2ALbo);
           const uint32_t ko = s * 2 * kT2BLbo;
           umma_f16(tm_re, d_slo, umma_desc_plain(w_chi + ko, kT2BLbo), kT2Idesc, s ? 1u : 0u);
           umma_f16(tm_re, d_shi, umma_desc_plain(w_clo + ko, kT2BLbo), kT2Idesc, 1u);
@@ -736,8 +743,8 @@ __global__ void __launch_bounds__(t2_threads(EPI), 1) features_tc2_kernel(const 
         for (int s = 0; s < (SPB_T2_INTERLEAVE ? 0 : kT2KSteps); ++s) {
           const uint32_t a = sbase + kT2OffA + sl2 * kT2SlotBytes;
           const uint32_t ko = s * 2 * kT2BLbo;
-          umma_f16(tm_re, umma_desc_plain(a, kTcRows * 16), umma_desc_plain(w_chi + ko, kT2BLbo), kT2Idesc, 1u);
-          umma_f16(tm_im, umma_desc_plain(a + 2 * kT2APart, kTcRows * 16), umma_desc_plain(w_shi + ko, kT2BLbo), kT2Idesc, 1u);
+          umma_f16(tm_re, umma_desc_plain(a, kT2ALbo), umma_desc_plain(w_chi + ko, kT2BLbo), kT2Idesc, 1u);
+          umma_f16(tm_im, umma_desc_plain(a + 2 * kT2APart, kT2ALbo), umma_desc_plain(w_shi + ko, kT2BLbo), kT2Idesc, 1u);
           tc_commit(&empty[sl2]);
           if (++sl2 == kT2Slots) sl2 = 0;
         }
